@@ -1,0 +1,160 @@
+/* bramble_b200 -- C ABI of the B200 projection engine.
+ *
+ * The reference (zrudnick/bramble, C++) has no plugin/FFI surface; the seam this library replaces
+ * is the per-bundle call
+ *     void convert_reads(std::vector<CReadAln>&, std::shared_ptr<g2tTree>, std::shared_ptr<ReadEvaluator>,
+ *                        quill::Logger*, BamIO*)                  reference include/evaluate.h:377-381, src/core.cpp:220
+ * plus the one-time index build
+ *     std::shared_ptr<g2tTree> build_g2t_tree(GVec<GRefData>, BamIO*)   reference src/bramble.cpp:132-211
+ * A maintainer of the reference would call brb_index_create() where build_g2t_tree() is called
+ * (src/bramble.cpp:639) and brb_project() inside process_bundle() (src/threads.cpp:100-104); see
+ * INTEGRATION.md for the binding.
+ *
+ * Everything is plain pointers + sizes.  All arrays are host memory owned by the caller unless stated
+ * otherwise; output arrays are owned by the brb_ctx and stay valid until the next call on that ctx.
+ * Every function returns 0 on success or a negative brb_status; nothing exits or throws.  There is no
+ * CPU implementation behind this ABI: without a CUDA device every compute entry point returns
+ * BRB_E_NO_DEVICE.
+ */
+#ifndef BRAMBLE_B200_H
+#define BRAMBLE_B200_H
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum brb_status {
+  BRB_OK = 0,
+  BRB_E_NO_DEVICE = -1,   /* no CUDA device / driver */
+  BRB_E_CUDA = -2,        /* a CUDA call failed; brb_last_error() has the text */
+  BRB_E_ARG = -3,         /* malformed input (NULL pointer, inconsistent CSR, ...) */
+  BRB_E_NOMEM = -4,
+  BRB_E_UNSUPPORTED = -5  /* e.g. use_fasta requested but the index holds no genome */
+} brb_status;
+
+typedef struct brb_index brb_index;   /* device-resident flattened g2t table; immutable after create */
+typedef struct brb_ctx brb_ctx;       /* one CUDA stream + scratch + pinned staging; one per host thread */
+
+/* Resolved thresholds: reference ShortReadEvaluator/LongReadEvaluator::evaluate,
+ * src/evaluate.cpp:1136-1221, struct ReadEvaluationConfig include/evaluate.h:275-285. */
+typedef struct brb_params {
+  uint32_t max_clip, max_junc_ins, max_junc_gap, max_error_exon;
+  float    similarity_threshold;        /* compared as (double)float, src/evaluate.cpp:854-856 */
+  uint8_t  long_reads;                  /* LONG_READS global, src/bramble.cpp:504 */
+  uint8_t  use_fasta;                   /* USE_FASTA global, src/bramble.cpp:499-502 */
+  uint8_t  ignore_small_exons;          /* max_error_exon > 0 */
+  uint8_t  filter_by_similarity;        /* similarity_threshold < 1.0 */
+} brb_params;
+
+/* Flattened interval table = the reference's per-(refid,strand) IITree<int,IITData> arrays
+ * (include/g2t.h:27-43, src/g2t.cpp:34-62) concatenated; table t = 2*refid + (strand=='-').
+ * Records of one table are in the reference's own order (std::sort by start on the reference's
+ * insertion sequence, cgranges IITree::index), so "hit order" == ascending record index. */
+typedef struct brb_index_desc {
+  uint32_t n_tables;                    /* 2 * number of annotated chromosomes */
+  const uint64_t* table_off;            /* n_tables+1 offsets into the record arrays */
+  const int32_t*  st;                   /* interval start, 1-based */
+  const int32_t*  en;                   /* interval end, exclusive */
+  const uint32_t* tid;                  /* output-header index of the transcript */
+  const uint8_t*  exon_id;              /* (uint8_t) genomic exon index -- wraps at 256 like the reference */
+  const uint32_t* pos_start;            /* cumulative transcript offset of the exon (5'->3') */
+  const uint32_t* prev_st; const uint32_t* prev_en;   /* neighbour exons in transcript order, 0,0 if none */
+  const uint32_t* next_st; const uint32_t* next_en;
+  const uint8_t*  has_prev_next;        /* bit0 has_prev, bit1 has_next */
+  const uint32_t* transcript_len;
+  /* genome, only for use_fasta: per-refid base codes 0..3 = A,C,G,T, 4 = anything else (the ksw2
+   * encoding of reference src/evaluate.cpp:299-305), one byte per base, 0-based genomic offset. */
+  uint32_t n_chrom;
+  const uint64_t* chrom_off;            /* n_chrom+1 offsets into genome_codes, or NULL */
+  const uint8_t*  genome_codes;         /* or NULL */
+} brb_index_desc;
+
+/* One bundle (reference BundleData::reads, include/bramble.h:153-183) as structure-of-arrays. */
+typedef struct brb_batch_in {
+  uint32_t n_aln, n_groups;
+  const uint32_t* group_off;            /* n_groups+1: read-name groups (src/core.cpp:347-380) */
+  const int32_t*  refid;                /* n_aln: annotated chromosome index, <0 or >=n_tables/2: none */
+  const int8_t*   strand;               /* n_aln: '+', '-', '.' (src/bramble.cpp:213-244,382) */
+  const uint32_t* exon_off;             /* n_aln+1 */
+  const uint32_t* exon_st;              /* read exon segments, 1-based half-open (src/bramble.cpp:246-255) */
+  const uint32_t* exon_en;
+  const uint32_t* cigar_off;            /* n_aln+1 */
+  const uint32_t* cigar;                /* raw BAM CIGAR words */
+  const int32_t*  mate_idx;             /* n_aln: batch-local index of the linked mate or -1 (process_pairs) */
+  const uint64_t* group_seq_off;        /* n_groups+1 base offsets into seq_codes; NULL unless use_fasta */
+  const uint8_t*  seq_codes;            /* group-shared read sequence (src/core.cpp:353-378), codes 0..4 */
+} brb_batch_in;
+
+/* One row per output BAM record, in the reference's emit order (src/core.cpp:384-415,
+ * src/mates.cpp:28-119): for a paired BamInfo the read1 row is immediately followed by its read2 row. */
+#define BRB_REC_FIRST  1u   /* this row is BamInfo::read1 */
+#define BRB_REC_PAIRED 2u   /* BamInfo::is_paired */
+#define BRB_REC_SAMETX 4u   /* BamInfo::same_transcript */
+typedef struct brb_batch_out {
+  uint32_t n_rec;
+  uint64_t n_cigar_words;               /* size of the cigar pool (with slack; use cigar_off/cigar_len) */
+  const uint32_t* group_rec_off;        /* n_groups+1: rows of group g */
+  const uint32_t* src_aln;              /* input alignment the record is a projection of */
+  const uint32_t* tid;
+  const uint32_t* pos;                  /* fwpos or rcpos by transcript strand (src/core.cpp:153-158) */
+  const int8_t*   tx_strand;            /* '+' or '-' */
+  const uint8_t*  flags;                /* BRB_REC_* */
+  const double*   sim_score;            /* AlignInfo::similarity_score */
+  const int32_t*  clip_score;           /* AlignInfo::clip_score */
+  const uint32_t* cigar_off;            /* n_rec: start of the merged CIGAR in `cigar` */
+  const uint32_t* cigar_len;            /* n_rec: number of words; ALREADY reversed for '-' transcripts */
+  const uint32_t* cigar;
+} brb_batch_out;
+
+typedef struct brb_stats {
+  uint64_t n_launches;                  /* kernels launched by the last brb_project* call */
+  float    kernel_ms;                   /* CUDA-event time of those kernels on the ctx stream */
+  float    ms_lookup, ms_chain, ms_rescue, ms_finalize, ms_pair, ms_merge;   /* per phase */
+  uint64_t n_candidates, n_matches, n_rescue, n_rec;
+  uint64_t alg_bytes;                   /* algorithmic bytes of the batch (DESIGN.md formula) */
+  uint64_t h2d_bytes, d2h_bytes;
+} brb_stats;
+
+int brb_device_count(void);
+const char* brb_last_error(void);
+const char* brb_version(void);
+
+int brb_index_create(int device, const brb_index_desc* desc, brb_index** out);
+int brb_index_destroy(brb_index* idx);
+
+int brb_ctx_create(brb_index* idx, brb_ctx** out);
+int brb_ctx_destroy(brb_ctx* ctx);
+
+/* End to end: H2D of the batch, all kernels, D2H of the result, stream synchronised on return. */
+int brb_project(brb_ctx* ctx, const brb_params* p, const brb_batch_in* in, brb_batch_out* out);
+
+/* The same split in three so the kernels can be timed with the batch resident in HBM. */
+int brb_batch_upload(brb_ctx* ctx, const brb_batch_in* in);
+int brb_project_resident(brb_ctx* ctx, const brb_params* p);
+int brb_batch_download(brb_ctx* ctx, brb_batch_out* out);
+
+int brb_ctx_stats(const brb_ctx* ctx, brb_stats* out);
+
+/* Standalone kernel entry points used by the parity tests (device work, host buffers). */
+/* G1/G2: hits of one query per row, filtered like IntervalTree::findOverlapping (src/g2t.cpp:103-257).
+ * status: 0 FIRST, 1 MIDDLE, 2 LAST, 3 ONLY.  Writes up to cap hit record indices per query into
+ * hits[q*cap..], the full count into n_hits[q]. */
+int brb_lookup(brb_ctx* ctx, const brb_params* p, uint32_t n_query, const int32_t* refid, const int8_t* strand,
+               const uint32_t* qs, const uint32_t* qe, const uint8_t* status, uint32_t cap,
+               uint32_t* hits, uint32_t* n_hits);
+/* B1: merge_cigars (src/bam.cpp:113-315,443-472) for n pairs of (real, ideal) CIGARs given as CSR. */
+int brb_merge_cigars(brb_ctx* ctx, uint32_t n, const uint32_t* real_off, const uint32_t* real,
+                     const uint32_t* ideal_off, const uint32_t* ideal, uint32_t* out_off /* n+1, in: capacity layout */,
+                     uint32_t* out_len, uint32_t* out);
+/* K3/K4: ksw_extz2 with bramble's fixed parameters (src/evaluate.cpp:285-317) for n problems.
+ * Sequences are codes 0..4.  cigar_out row i holds up to cigar_cap words (len<<4|op, op 0=M,1=I,2=D). */
+int brb_ksw_extend(brb_ctx* ctx, uint32_t n, const uint64_t* q_off, const uint8_t* q, const uint64_t* t_off,
+                   const uint8_t* t, int32_t* max, int32_t* score, int32_t* max_q, int32_t* max_t,
+                   uint8_t* zdropped, uint32_t cigar_cap, uint32_t* n_cigar, uint32_t* cigar_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
