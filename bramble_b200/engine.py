@@ -1,0 +1,104 @@
+"""Thin object wrapper over the C ABI: index + context lifetime, project(), stats().
+Mirrors the reference seam `convert_reads(reads, g2t, evaluator, ...)` (src/core.cpp:220): the index is
+the g2t tree, a Batch is one bundle, the returned rows are the BamInfo ends in emit order."""
+import ctypes as C
+
+import numpy as np
+
+from . import capi
+
+
+def _rows(o, n_groups):
+    n = int(o.n_rec)
+
+    def arr(p, cnt, dt):
+        if cnt == 0:
+            return np.zeros(0, dtype=dt)
+        return np.ctypeslib.as_array(p, shape=(cnt,)).astype(dt, copy=True)
+    d = dict(n_rec=n, group_rec_off=arr(o.group_rec_off, n_groups + 1, np.uint32), src_aln=arr(o.src_aln, n, np.uint32),
+             tid=arr(o.tid, n, np.uint32), pos=arr(o.pos, n, np.uint32), tx_strand=arr(o.tx_strand, n, np.int8),
+             flags=arr(o.flags, n, np.uint8), sim_score=arr(o.sim_score, n, np.float64), clip_score=arr(o.clip_score, n, np.int32),
+             cigar_off=arr(o.cigar_off, n, np.uint32), cigar_len=arr(o.cigar_len, n, np.uint32))
+    pool = arr(o.cigar, int(o.n_cigar_words), np.uint32)
+    d["cigars"] = [pool[int(a):int(a) + int(l)].copy() for a, l in zip(d["cigar_off"], d["cigar_len"])]
+    return d
+
+
+class Engine:
+    def __init__(self, index, device=0):
+        self.lib = capi.lib()
+        if self.lib.brb_device_count() <= 0:
+            raise capi.EngineError("no CUDA device: bramble_b200 has no CPU path")
+        self.index = index
+        self._ix = C.c_void_p()
+        self._ctx = C.c_void_p()
+        capi.check(self.lib.brb_index_create(device, C.byref(index.desc), C.byref(self._ix)), "brb_index_create")
+        capi.check(self.lib.brb_ctx_create(self._ix, C.byref(self._ctx)), "brb_ctx_create")
+
+    def close(self):
+        if self._ctx:
+            self.lib.brb_ctx_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+        if self._ix:
+            self.lib.brb_index_destroy(self._ix)
+            self._ix = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def project(self, params, batch, raw=False):
+        out = capi.BatchOut()
+        capi.check(self.lib.brb_project(self._ctx, C.byref(params), C.byref(batch.desc), C.byref(out)), "brb_project")
+        return out if raw else _rows(out, batch.desc.n_groups)
+
+    def upload(self, batch):
+        capi.check(self.lib.brb_batch_upload(self._ctx, C.byref(batch.desc)), "brb_batch_upload")
+
+    def run_resident(self, params):
+        capi.check(self.lib.brb_project_resident(self._ctx, C.byref(params)), "brb_project_resident")
+
+    def download(self, n_groups, raw=False):
+        out = capi.BatchOut()
+        capi.check(self.lib.brb_batch_download(self._ctx, C.byref(out)), "brb_batch_download")
+        return out if raw else _rows(out, n_groups)
+
+    def stats(self):
+        s = capi.Stats()
+        capi.check(self.lib.brb_ctx_stats(self._ctx, C.byref(s)), "brb_ctx_stats")
+        return s
+
+    def lookup(self, params, refid, strand, qs, qe, status, cap):
+        n = len(refid)
+        hits = np.zeros((n, cap), dtype=np.uint32)
+        nh = np.zeros(n, dtype=np.uint32)
+        capi.check(self.lib.brb_lookup(self._ctx, C.byref(params), n, capi.ptr(refid), capi.ptr(strand), capi.ptr(qs), capi.ptr(qe),
+                                       capi.ptr(status), cap, capi.ptr(hits.reshape(-1)), capi.ptr(nh)), "brb_lookup")
+        return hits, nh
+
+    def merge_cigars(self, real_off, real, ideal_off, ideal):
+        n = len(real_off) - 1
+        caps = (np.diff(real_off.astype(np.int64)) + np.diff(ideal_off.astype(np.int64)) + 2)
+        out_off = np.concatenate([[0], np.cumsum(caps)]).astype(np.uint32)
+        out_len = np.zeros(n, dtype=np.uint32)
+        out = np.zeros(max(1, int(out_off[-1])), dtype=np.uint32)
+        real = real if len(real) else np.zeros(1, np.uint32)
+        ideal = ideal if len(ideal) else np.zeros(1, np.uint32)
+        capi.check(self.lib.brb_merge_cigars(self._ctx, n, capi.ptr(real_off), capi.ptr(real), capi.ptr(ideal_off), capi.ptr(ideal),
+                                             capi.ptr(out_off), capi.ptr(out_len), capi.ptr(out)), "brb_merge_cigars")
+        return [out[int(o):int(o) + int(l)].copy() for o, l in zip(out_off[:-1], out_len)]
+
+    def ksw_extend(self, queries, targets, cigar_cap=256):
+        n = len(queries)
+        q_off = np.concatenate([[0], np.cumsum([len(q) for q in queries])]).astype(np.uint64)
+        t_off = np.concatenate([[0], np.cumsum([len(t) for t in targets])]).astype(np.uint64)
+        q = np.ascontiguousarray(np.concatenate(queries).astype(np.uint8)) if n else np.zeros(1, np.uint8)
+        t = np.ascontiguousarray(np.concatenate(targets).astype(np.uint8)) if n else np.zeros(1, np.uint8)
+        mx = np.zeros(n, np.int32); sc = np.zeros(n, np.int32); mq = np.zeros(n, np.int32); mt = np.zeros(n, np.int32)
+        zd = np.zeros(n, np.uint8); nc = np.zeros(n, np.uint32); cg = np.zeros((n, cigar_cap), np.uint32)
+        capi.check(self.lib.brb_ksw_extend(self._ctx, n, capi.ptr(q_off), capi.ptr(q), capi.ptr(t_off), capi.ptr(t), capi.ptr(mx),
+                                           capi.ptr(sc), capi.ptr(mq), capi.ptr(mt), capi.ptr(zd), cigar_cap, capi.ptr(nc),
+                                           capi.ptr(cg.reshape(-1))), "brb_ksw_extend")
+        return dict(max=mx, score=sc, max_q=mq, max_t=mt, zdropped=zd, cigars=[cg[i, :min(int(nc[i]), cigar_cap)].copy() for i in range(n)], n_cigar=nc)

@@ -154,6 +154,14 @@ int brb_ksw_extend(brb_ctx* ctx, uint32_t n, const uint64_t* q_off, const uint8_
                    const uint8_t* t, int32_t* max, int32_t* score, int32_t* max_q, int32_t* max_t,
                    uint8_t* zdropped, uint32_t cigar_cap, uint32_t* n_cigar, uint32_t* cigar_out);
 
+/* ---- host-side helpers (no device work) ---- */
+/* Permutation cgranges' IITree::index() applies to one tree: libstdc++ std::sort (unstable) by start
+ * only, on the reference's insertion sequence (src/g2t.cpp:57-62).  perm[k] = input index of sorted record k. */
+int brb_sort_by_start(uint64_t n, const int32_t* st, uint32_t* perm);
+/* Pinned host memory for batch columns (makes the H2D copies of brb_project asynchronous DMA). */
+int brb_host_alloc(size_t bytes, void** out);
+int brb_host_free(void* p);
+
 #ifdef __cplusplus
 }
 #endif

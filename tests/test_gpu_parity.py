@@ -1,0 +1,132 @@
+"""GPU parity: the CUDA engine (through the C ABI) against the CPU oracle on the same seeded inputs.
+Bit-exact for every integer column and CIGAR; similarity scores bit-exact (tolerance 1e-6 relative is
+the north_star fallback, asserted in oracle_lib.assert_rows_equal)."""
+import numpy as np
+import pytest
+
+from bramble_b200 import capi, engine
+import common
+import oracle_lib
+
+pytestmark = pytest.mark.gpu
+
+
+def _check(wl, what):
+    ix, p = wl["index"], wl["params"]
+    n_rec = 0
+    with engine.Engine(ix) as eng:
+        for bi, b in enumerate(wl["batches"]):
+            got = eng.project(p, b)
+            exp = oracle_lib.port_project(ix, p, b)
+            oracle_lib.assert_rows_equal(exp, got, f"{what} batch {bi}")
+            st = eng.stats()
+            assert st.n_rec == got["n_rec"] and st.n_launches > 0
+            assert st.n_matches == exp["n_matches"]
+            n_rec += got["n_rec"]
+    assert n_rec > 0
+    return n_rec
+
+
+@pytest.mark.parametrize("mode", ["default", "fr", "rf", "strict", "lr_nofasta", "lrhq"])
+@pytest.mark.parametrize("seed", [21, 22])
+def test_project_matches_oracle(mode, seed):
+    wl = common.make_workload(mode, seed, n_names=1500 if common.MODES[mode]["long"] else 3000)
+    _check(wl, f"{mode}/{seed}")
+
+
+@pytest.mark.parametrize("mode", ["default", "lr_nofasta", "lrhq"])
+def test_micro_introns_duplicate_tids(mode):
+    wl = common.make_workload(mode, 31, n_names=2000, micro_introns=True)
+    _check(wl, f"micro/{mode}")
+
+
+def test_multiple_bundles_and_ragged():
+    wl = common.make_workload("default", 41, n_names=3000, chunk_size=700)
+    assert len(wl["batches"]) > 3
+    _check(wl, "bundles")
+
+
+def test_param_overrides():
+    wl = common.make_workload("default", 51, n_names=2000)
+    for kw in (dict(max_clip=0), dict(max_clip=25, max_junc_ins=3, max_junc_gap=3), dict(max_error_exon=35),
+               dict(similarity_threshold=0.5, max_junc_ins=5, max_junc_gap=5)):
+        wl["params"] = capi.resolve_params(**kw)
+        _check(wl, f"override {kw}")
+    wl = common.make_workload("lr_nofasta", 52, n_names=1000)
+    for kw in (dict(lr=True, max_error_exon=0), dict(lr=True, similarity_threshold=0.2, max_junc_gap=100), dict(lr_hq=True)):
+        wl["params"] = capi.resolve_params(**kw)
+        _check(wl, f"override {kw}")
+
+
+def test_empty_batch_and_no_match():
+    wl = common.make_workload("default", 61, n_names=50)
+    ix, p = wl["index"], wl["params"]
+    from bramble_b200 import pack
+    empty = pack.pack_batches([], ix, wl["ann"].chroms)
+    assert empty == []
+    b = pack.Batch().finish([], [], [], [0], [], [], [0], [], [], [0], None, None, [], [])
+    with engine.Engine(ix) as eng:
+        got = eng.project(p, b)
+        assert got["n_rec"] == 0
+        # alignments on an unannotated chromosome -> nothing projects
+        recs = [dict(r, chrom=7) for r in wl["recs"] if not r["flag"] & 4][:20]
+        for r in recs:
+            r["mchrom"] = 7 if r["mchrom"] >= 0 else -1
+        bs = pack.pack_batches(recs, ix, wl["ann"].chroms)
+        got = eng.project(p, bs[0])
+        assert got["n_rec"] == 0 and len(got["group_rec_off"]) == bs[0].desc.n_groups + 1
+
+
+def test_lookup_kernel():
+    wl = common.make_workload("lr_nofasta", 71, n_names=600)
+    ix, p = wl["index"], wl["params"]
+    refid, strand, qs, qe, status = [], [], [], [], []
+    for b in wl["batches"]:
+        A = b.arrays
+        for a in range(b.desc.n_aln):
+            e0, e1 = int(A["exon_off"][a]), int(A["exon_off"][a + 1])
+            for j in range(e0, e1):
+                n = e1 - e0
+                st = 3 if n == 1 else (0 if j == e0 else (1 if j < e1 - 1 else 2))
+                for sd in "+-":
+                    refid.append(A["refid"][a]); strand.append(ord(sd)); qs.append(A["exon_st"][j]); qe.append(A["exon_en"][j]); status.append(st)
+    refid = np.array(refid, np.int32); strand = np.array(strand, np.int8); qs = np.array(qs, np.uint32); qe = np.array(qe, np.uint32)
+    status = np.array(status, np.uint8)
+    cap = 64
+    with engine.Engine(ix) as eng:
+        hits, nh = eng.lookup(p, refid, strand, qs, qe, status, cap)
+    eh = np.zeros((len(refid), cap), np.uint32); en = np.zeros(len(refid), np.uint32)
+    import ctypes as C
+    rc = oracle_lib.port().brb_port_lookup(C.byref(ix.desc), C.byref(p), len(refid), capi.ptr(refid), capi.ptr(strand), capi.ptr(qs),
+                                           capi.ptr(qe), capi.ptr(status), cap, capi.ptr(eh.reshape(-1)), capi.ptr(en))
+    assert rc == 0
+    assert np.array_equal(nh, en)
+    assert en.max() > 1
+    for q in range(len(refid)):
+        k = min(int(en[q]), cap)
+        assert np.array_equal(hits[q, :k], eh[q, :k])
+
+
+def test_merge_kernel_golden_and_random():
+    from test_oracle_golden import UPDATE_CIGAR_CASES, cig
+    wl = common.make_workload("default", 81, n_names=20)
+    rng = np.random.default_rng(5)
+    reals = [cig(r) for r, _, _ in UPDATE_CIGAR_CASES]
+    ideals = [cig(i) for _, i, _ in UPDATE_CIGAR_CASES]
+    ops_r = [0, 1, 2, 3, 4, 5, 7, 8]
+    ops_i = [0, 1, 2, 4, 10, 11, 12, 13]
+    for _ in range(3000):
+        nr, ni = int(rng.integers(0, 9)), int(rng.integers(0, 9))
+        reals.append(np.array([(int(rng.integers(1, 40)) << 4) | int(rng.choice(ops_r)) for _ in range(nr)], np.uint32))
+        ideals.append(np.array([(int(rng.integers(1, 40)) << 4) | int(rng.choice(ops_i)) for _ in range(ni)], np.uint32))
+    real_off = np.concatenate([[0], np.cumsum([len(x) for x in reals])]).astype(np.uint32)
+    ideal_off = np.concatenate([[0], np.cumsum([len(x) for x in ideals])]).astype(np.uint32)
+    real = np.concatenate(reals).astype(np.uint32); ideal = np.concatenate(ideals).astype(np.uint32)
+    with engine.Engine(wl["index"]) as eng:
+        got = eng.merge_cigars(real_off, real, ideal_off, ideal)
+    from test_oracle_golden import port_merge
+    exp = port_merge(reals, ideals)
+    for k, (g, e) in enumerate(zip(got, exp)):
+        assert np.array_equal(g, e), (k, reals[k], ideals[k], g, e)
+    for k, (_, _, want) in enumerate(UPDATE_CIGAR_CASES):
+        assert np.array_equal(got[k], cig(want))
