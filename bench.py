@@ -1,0 +1,259 @@
+#!/usr/bin/env python
+"""bench.py -- projected alignments/sec of the genome->transcriptome projection hot path.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--names M]
+
+A "step" is one pass of the whole kernel sequence (lookup -> chain walk -> pairing -> CIGAR merge)
+over one synthetic bundle set.  Workload = BASELINE.json configs[1] shape (C2): GENCODE-shaped
+annotation (~250k transcripts, ~2.2M exons, 25 chromosomes) + stranded (--fr) paired-end 150 bp
+name-collated reads, `--names` read names per GPU (default 2M names = ~4.6M alignments; the full C2
+is 100M pairs, scaled down so that the default run finishes in minutes -- see DESIGN.md).
+Ranks shard by read name (weak scaling: every GPU gets its own seeded shard, annotation replicated,
+no collective on the data path).
+
+  value  : alignments/s, inputs resident in HBM, CUDA-event time over K steps, max over ranks
+  e2e    : alignments/s through brb_project() with pinned HOST columns (H2D + kernels + D2H per step)
+  roofline / cpu_baseline : see DESIGN.md "Measurement"
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+
+def _peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    def __init__(self, gpu):
+        self.gpu, self.rows, self.stop_flag, self.th = gpu, [], False, None
+
+    def _run(self):
+        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+            "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        while not self.stop_flag:
+            try:
+                o = subprocess.run(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={q}", "--format=csv,noheader,nounits"],
+                                   capture_output=True, text=True, timeout=5).stdout.strip()
+                if o:
+                    self.rows.append([x.strip() for x in o.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def start(self):
+        self.th = threading.Thread(target=self._run, daemon=True)
+        self.th.start()
+
+    def stop(self):
+        self.stop_flag = True
+        if self.th:
+            self.th.join(timeout=6)
+        sm = sorted(int(r[0]) for r in self.rows if r[0].isdigit())
+        mx = max([int(r[1]) for r in self.rows if r[1].isdigit()] or [0])
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows for i in range(4) if len(r) >= 6 and r[2 + i].lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": reasons, "samples": len(sm)}
+
+
+def workload(seed, names):
+    from bramble_b200 import synth_fast as sf
+    A = sf.make_annotation(2002)
+    ix = sf.build_index(A)
+    B = sf.make_short_batch(A, ix, seed, names, stranded="fr")
+    return A, ix, B
+
+
+def ref_cmd(cores):
+    return ["--fr", "-p", str(max(1, min(cores, 255)))]
+
+
+def time_reference(A, ix, B, n_small, n_big, cores, repeats=1):
+    """Reference C++ (oracle/_ref/bramble_ref, unmodified sources) on a bounded sample of the same
+    workload.  Throughput is MARGINAL: (aln_big - aln_small) / (t_big - t_small), which removes the GTF
+    load + index build the reference pays once per run.  BGZF level 1 for the output, all host cores."""
+    from bramble_b200 import synth, synth_fast as sf
+    ref = os.path.join(ROOT, "oracle", "_ref", "bramble_ref")
+    if not os.path.exists(ref):
+        return None
+    d = tempfile.mkdtemp(prefix="brb_bench_")
+    sf.write_gtf(A, os.path.join(d, "a.gtf"))
+
+    class Ann:
+        chroms, chrom_len = A.chroms, A.chrom_len
+    out = []
+    for n in (n_small, n_big):
+        recs = sf.to_records(B, 0, n)
+        bam = os.path.join(d, f"in{n}.bam")
+        synth.write_bam(bam, Ann, recs)
+        n_aln = len(recs)
+        best = None
+        for _ in range(repeats):
+            wd = tempfile.mkdtemp(dir=d)
+            env = dict(os.environ, BRB_SHIM_LEVEL="1")
+            t0 = time.perf_counter()
+            r = subprocess.run([ref, bam, "-G", os.path.join(d, "a.gtf"), "-o", os.path.join(wd, "out.bam"), "--quiet"] + ref_cmd(cores),
+                               cwd=wd, env=env, capture_output=True, text=True)
+            dt = time.perf_counter() - t0
+            if r.returncode != 0:
+                raise RuntimeError("reference failed: " + r.stderr[-500:])
+            best = dt if best is None else min(best, dt)
+        out.append((n_aln, best))
+    (a0, t0), (a1, t1) = out
+    rate = (a1 - a0) / max(1e-9, (t1 - t0))
+    return dict(value=rate, n_aln=a1 - a0, seconds=t1 - t0, startup_s=t0, sample=f"first {n_big} read names ({a1} alignments) of the rank-0 shard, "
+                f"marginal over a {n_small}-name run (startup {t0:.1f}s excluded), BAM in -> BAM out, BGZF level 1")
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours")
+    ap.add_argument("--names", type=int, default=2_000_000)
+    ap.add_argument("--ref-names", type=int, default=150_000)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    cores = os.cpu_count() or 1
+    unit = "alignments/s"
+    metric = "projected alignments/sec (input BAM records consumed)"
+    config = {"workload": "C2: synthetic GENCODE-shaped GTF (252,687 transcripts, 2.24M exons, 25 chromosomes) + --fr paired-end "
+                          f"150bp name-collated reads, {args.names} read names per GPU", "flags": "--fr", "names_per_gpu": args.names,
+              "l2": "inputs + intermediates (>1 GB per step) exceed the 126 MB L2"}
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        A, ix, B = workload(1000, max(args.ref_names, 2000))
+        vals = []
+        res = None
+        for _ in range(max(1, min(args.steps, 3))):
+            res = time_reference(A, ix, B, 2000, args.ref_names, cores)
+            if res is None:
+                print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/bramble_ref not built (reference sources absent)"}))
+                return
+            vals.append(res["value"])
+        v = max(vals)
+        print(json.dumps({"impl": "reference", "metric": metric, "value": v, "unit": unit, "n_gpus": args.gpus, "steps": args.steps,
+                          "warmup": args.warmup, "ms_per_step": 1e3 * res["seconds"], "higher_is_better": True, "scaling": "weak",
+                          "vs_baseline": None, "dtype": "int32", "data": "synthetic", "config": config,
+                          "cpu_baseline": {"value": v, "unit": unit, "cores": min(cores, 255), "kind": "reference", "sample": res["sample"]},
+                          "e2e": {"value": v, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
+
+    import torch
+    import torch.distributed as dist
+    from bramble_b200 import capi, engine
+    import __graft_entry__ as g
+    g.build_engine()
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    A, ix, B = workload(1000 + rank, args.names)
+    n_aln = int(B.desc.n_aln)
+    p = capi.resolve_params()            # --fr only affects ingest (strand column), thresholds are the short-read preset
+    eng = engine.Engine(ix, device=local)
+    tbar = torch.zeros(1, device=f"cuda:{local}")
+
+    def barrier():
+        if world > 1:
+            dist.all_reduce(tbar)
+        torch.cuda.synchronize()
+
+    # ---- resident (kernel-only) timing
+    eng.upload(B)
+    for _ in range(max(3, args.warmup)):
+        eng.run_resident(p)
+    st = eng.stats()
+    sampler = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    phase = {k: 0.0 for k in ("ms_lookup", "ms_chain", "ms_rescue", "ms_finalize", "ms_pair", "ms_merge")}
+    eng.timer_start()
+    launches = 0
+    for _ in range(args.steps):
+        eng.run_resident(p)
+        s = eng.stats()
+        launches += int(s.n_launches)
+        for k in phase:
+            phase[k] += getattr(s, k)
+    ms = eng.timer_stop()
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    st = eng.stats()
+    # ---- end to end through the C ABI with pinned host columns
+    PB = eng.pinned_copy(B)
+    for _ in range(2):
+        eng.project(p, PB, raw=True)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        eng.project(p, PB, raw=True)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    st2 = eng.stats()
+    barrier()
+    t = torch.tensor([ms, e2e_s * 1e3, float(n_aln)], dtype=torch.float64, device=f"cuda:{local}")
+    tmax = t.clone()
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    total_aln = float(t[2].item()) if world > 1 else float(n_aln)
+    ms_max, e2e_ms_max = float(tmax[0].item()), float(tmax[1].item())
+    if rank == 0:
+        peak, peak_src = _peaks()
+        step_ms = ms_max / args.steps
+        value = total_aln * args.steps / (ms_max / 1e3)
+        e2e = total_aln * args.steps / (e2e_ms_max / 1e3)
+        alg = int(st.alg_bytes)
+        achieved = alg / (ms / args.steps / 1e3) / 1e9
+        names = {"ms_lookup": "k_lookup+k_fill_cand", "ms_chain": "k_chain", "ms_finalize": "k_build", "ms_pair": "k_pair_count+k_pair_emit",
+                 "ms_merge": "k_merge", "ms_rescue": "k_ksw"}
+        top = max(phase, key=lambda k: phase[k])
+        line = {"metric": metric, "value": value, "unit": unit, "n_gpus": args.gpus, "steps": args.steps, "warmup": max(3, args.warmup),
+                "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32",
+                "data": "synthetic", "config": config, "gpu_launches": launches, "clocks": clocks,
+                "e2e": {"value": e2e, "unit": unit, "h2d_bytes_per_step": int(st2.h2d_bytes), "d2h_bytes_per_step": int(st2.d2h_bytes)},
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                             "peak_source": peak_src, "scope": "whole kernel sequence of one step (algorithmic bytes of SURVEY 8(d) / DESIGN.md)",
+                             "alg_bytes_per_step": alg, "alg_bytes_per_alignment": alg / max(1, n_aln),
+                             "top_kernel": names[top], "top_kernel_share": phase[top] / max(1e-9, sum(phase.values())),
+                             "phase_ms_per_step": {names[k]: v / args.steps for k, v in phase.items()}},
+                "work": {"alignments_per_gpu": n_aln, "candidates": int(st.n_candidates), "matches": int(st.n_matches), "records": int(st.n_rec)}}
+        if args.gpus == 1 and not args.no_cpu_baseline:
+            try:
+                res = time_reference(A, ix, B, 2000, args.ref_names, cores)
+            except Exception as e:     # the baseline is a reported number, never a reason to lose the bench line
+                res = None
+                line["cpu_baseline_error"] = str(e)[:200]
+            if res:
+                line["cpu_baseline"] = {"value": res["value"], "unit": unit, "cores": min(cores, 255), "kind": "reference", "sample": res["sample"]}
+        print(json.dumps(line))
+    eng.pinned_free(PB)
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

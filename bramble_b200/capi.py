@@ -108,6 +108,8 @@ def _declare(lib):
     lib.brb_project_resident.argtypes = [C.c_void_p, C.POINTER(Params)]
     lib.brb_batch_download.argtypes = [C.c_void_p, C.POINTER(BatchOut)]
     lib.brb_ctx_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
+    lib.brb_ctx_timer_start.argtypes = [C.c_void_p]
+    lib.brb_ctx_timer_stop.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
     lib.brb_lookup.argtypes = [C.c_void_p, C.POINTER(Params), C.c_uint32, i32p, i8p, u32p, u32p, u8p, C.c_uint32, u32p, u32p]
     lib.brb_merge_cigars.argtypes = [C.c_void_p, C.c_uint32, u32p, u32p, u32p, u32p, u32p, u32p, u32p]
     lib.brb_ksw_extend.argtypes = [C.c_void_p, C.c_uint32, u64p, u8p, u64p, u8p, i32p, i32p, i32p, i32p, u8p,
@@ -116,7 +118,8 @@ def _declare(lib):
     lib.brb_host_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]
     lib.brb_host_free.argtypes = [C.c_void_p]
     for f in ("brb_index_create", "brb_index_destroy", "brb_ctx_create", "brb_ctx_destroy", "brb_project",
-              "brb_batch_upload", "brb_project_resident", "brb_batch_download", "brb_ctx_stats", "brb_lookup",
+              "brb_batch_upload", "brb_project_resident", "brb_batch_download", "brb_ctx_stats", "brb_ctx_timer_start",
+              "brb_ctx_timer_stop", "brb_lookup",
               "brb_merge_cigars", "brb_ksw_extend", "brb_sort_by_start", "brb_host_alloc", "brb_host_free"):
         getattr(lib, f).restype = C.c_int
     return lib

@@ -73,6 +73,7 @@ struct brb_ctx {
   brb_index* idx = nullptr;
   cudaStream_t st = nullptr;
   cudaEvent_t ev[8]{};
+  cudaEvent_t tev[2]{};
   // resident batch
   DevBatch b{};
   Buf in_group_off, in_refid, in_strand, in_exon_off, in_exon_st, in_exon_en, in_cigar_off, in_cigar, in_mate, in_seq_off, in_seq;
@@ -179,6 +180,7 @@ int brb_ctx_create(brb_index* ix, brb_ctx** out) {
   brb_ctx* c = new brb_ctx(); c->idx = ix;
   CU(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));
   for (auto& e : c->ev) CU(cudaEventCreate(&e));
+  for (auto& e : c->tev) CU(cudaEventCreate(&e));
   ENS(c->counters, 64); ENS(c->h_small, 256);
   *out = c;
   return BRB_OK;
@@ -197,6 +199,7 @@ int brb_ctx_destroy(brb_ctx* c) {
   for (Buf* b : all) b->release();
   c->h_small.release(); c->h_out.release();
   for (auto& e : c->ev) if (e) cudaEventDestroy(e);
+  for (auto& e : c->tev) if (e) cudaEventDestroy(e);
   if (c->st) cudaStreamDestroy(c->st);
   delete c;
   return BRB_OK;
@@ -459,6 +462,21 @@ int brb_project(brb_ctx* c, const brb_params* p, const brb_batch_in* in, brb_bat
   int rc = brb_batch_upload(c, in); if (rc) return rc;
   rc = brb_project_resident(c, p); if (rc) return rc;
   return brb_batch_download(c, out);
+}
+
+int brb_ctx_timer_start(brb_ctx* c) {
+  if (!c) return fail(BRB_E_ARG, "null ctx");
+  CU(cudaSetDevice(c->idx->device));
+  CU(cudaEventRecord(c->tev[0], c->st));
+  return BRB_OK;
+}
+int brb_ctx_timer_stop(brb_ctx* c, float* ms) {
+  if (!c || !ms) return fail(BRB_E_ARG, "null argument");
+  CU(cudaSetDevice(c->idx->device));
+  CU(cudaEventRecord(c->tev[1], c->st));
+  CU(cudaEventSynchronize(c->tev[1]));
+  CU(cudaEventElapsedTime(ms, c->tev[0], c->tev[1]));
+  return BRB_OK;
 }
 
 int brb_ctx_stats(const brb_ctx* c, brb_stats* out) {

@@ -65,6 +65,39 @@ class Engine:
         capi.check(self.lib.brb_batch_download(self._ctx, C.byref(out)), "brb_batch_download")
         return out if raw else _rows(out, n_groups)
 
+    def timer_start(self):
+        capi.check(self.lib.brb_ctx_timer_start(self._ctx), "brb_ctx_timer_start")
+
+    def timer_stop(self):
+        ms = C.c_float()
+        capi.check(self.lib.brb_ctx_timer_stop(self._ctx, C.byref(ms)), "brb_ctx_timer_stop")
+        return float(ms.value)
+
+    def pinned_copy(self, batch):
+        """Copy of `batch` whose columns live in pinned host memory (brb_host_alloc)."""
+        import copy
+        nb = copy.copy(batch)
+        nb.desc = capi.BatchIn()
+        nb.desc.n_aln, nb.desc.n_groups = batch.desc.n_aln, batch.desc.n_groups
+        nb.arrays = {}
+        nb._pins = []
+        for k, a in batch.arrays.items():
+            p = C.c_void_p()
+            capi.check(self.lib.brb_host_alloc(max(1, a.nbytes), C.byref(p)), "brb_host_alloc")
+            nb._pins.append(p)
+            buf = (C.c_uint8 * max(1, a.nbytes)).from_address(p.value)
+            na = np.frombuffer(buf, dtype=a.dtype, count=a.size).reshape(a.shape)
+            na[...] = a
+            nb.arrays[k] = na
+            if hasattr(nb.desc, k):
+                setattr(nb.desc, k, capi.ptr(na))
+        return nb
+
+    def pinned_free(self, nb):
+        for p in nb._pins:
+            self.lib.brb_host_free(p)
+        nb._pins = []
+
     def stats(self):
         s = capi.Stats()
         capi.check(self.lib.brb_ctx_stats(self._ctx, C.byref(s)), "brb_ctx_stats")

@@ -136,6 +136,9 @@ int brb_project_resident(brb_ctx* ctx, const brb_params* p);
 int brb_batch_download(brb_ctx* ctx, brb_batch_out* out);
 
 int brb_ctx_stats(const brb_ctx* ctx, brb_stats* out);
+/* CUDA-event stopwatch on the ctx stream (what bench.py brackets its K timed steps with). */
+int brb_ctx_timer_start(brb_ctx* ctx);
+int brb_ctx_timer_stop(brb_ctx* ctx, float* ms);   /* records, synchronises, returns elapsed ms */
 
 /* Standalone kernel entry points used by the parity tests (device work, host buffers). */
 /* G1/G2: hits of one query per row, filtered like IntervalTree::findOverlapping (src/g2t.cpp:103-257).
