@@ -77,7 +77,7 @@ struct brb_ctx {
   // resident batch
   DevBatch b{};
   Buf in_group_off, in_refid, in_strand, in_exon_off, in_exon_st, in_exon_en, in_cigar_off, in_cigar, in_mate, in_seq_off, in_seq;
-  uint64_t in_bytes = 0, n_mates = 0, seq_bytes = 0;
+  uint64_t in_bytes = 0, n_mates = 0, seq_bytes = 0, rescue_bytes = 0;
   bool have_batch = false, have_result = false;
   // intermediates
   Buf q_lo, q_hi, t_ncand, t_coff, scan_tmp, counters;
@@ -288,7 +288,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   brb_stats& S = c->stats;
   uint64_t L = 0;
   const uint32_t n = b.n_aln, n_task = 2 * n;
-  c->have_result = false; c->n_cand = 0; c->n_rec = 0; c->n_out_words = 0; c->n_ideal_words = 0;
+  c->have_result = false; c->rescue_bytes = 0; c->n_cand = 0; c->n_rec = 0; c->n_out_words = 0; c->n_ideal_words = 0;
   S.n_candidates = S.n_matches = S.n_rescue = S.n_rec = 0;
   S.ms_lookup = S.ms_chain = S.ms_rescue = S.ms_finalize = S.ms_pair = S.ms_merge = 0; S.kernel_ms = 0;
   ENS(c->g_roff, (size_t)(b.n_groups + 1) * 4);
@@ -383,17 +383,18 @@ int project_resident(brb_ctx* c, const brb_params& p) {
                                               c->ipool.as<uint32_t>(), c->o_clen.as<uint32_t>(), c->opool.as<uint32_t>(), counters + 1); L++;
   }
   CU(cudaEventRecord(c->ev[6], st));
-  CU(cudaMemcpyAsync(c->h_small.p, counters, 32, cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(c->h_small.p, counters, 64, cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
   CU(cudaGetLastError());
-  unsigned long long hc[4]; memcpy(hc, c->h_small.p, 32);
+  unsigned long long hc[8]; memcpy(hc, c->h_small.p, 64);
   S.n_launches = L; S.n_matches = hc[3];
   S.ms_lookup = ms_between(c->ev[0], c->ev[1]); S.ms_chain = ms_between(c->ev[1], c->ev[2]); S.ms_rescue = ms_between(c->ev[2], c->ev[3]);
   S.ms_finalize = ms_between(c->ev[3], c->ev[4]); S.ms_pair = ms_between(c->ev[4], c->ev[5]); S.ms_merge = ms_between(c->ev[5], c->ev[6]);
   S.kernel_ms = ms_between(c->ev[0], c->ev[6]);
   // algorithmic bytes, SURVEY.md 8(d) / DESIGN.md: per-alignment SoA + 56 B per index hit + output rows + rescue bases
   S.alg_bytes = (uint64_t)n * 16 + (uint64_t)b.n_exon * 8 + (uint64_t)b.n_cigar * 4 + c->n_mates * 4 + hc[0] * 56 +
-                (uint64_t)R * 40 + hc[1] * 4 + hc[2];
+                (uint64_t)R * 40 + hc[1] * 4 + c->rescue_bytes;
+  S.n_rescue = hc[4];
   c->have_result = true;
   return BRB_OK;
 }

@@ -22,19 +22,20 @@ def _check(wl, what):
             st = eng.stats()
             assert st.n_rec == got["n_rec"] and st.n_launches > 0
             assert st.n_matches == exp["n_matches"]
+            assert st.n_rescue == exp["n_rescue"]
             n_rec += got["n_rec"]
     assert n_rec > 0
     return n_rec
 
 
-@pytest.mark.parametrize("mode", ["default", "fr", "rf", "strict", "lr_nofasta", "lrhq"])
+@pytest.mark.parametrize("mode", ["default", "fr", "rf", "strict", "lr", "lr_nofasta", "lrhq"])
 @pytest.mark.parametrize("seed", [21, 22])
 def test_project_matches_oracle(mode, seed):
     wl = common.make_workload(mode, seed, n_names=1500 if common.MODES[mode]["long"] else 3000)
     _check(wl, f"{mode}/{seed}")
 
 
-@pytest.mark.parametrize("mode", ["default", "lr_nofasta", "lrhq"])
+@pytest.mark.parametrize("mode", ["default", "lr", "lr_nofasta", "lrhq"])
 def test_micro_introns_duplicate_tids(mode):
     wl = common.make_workload(mode, 31, n_names=2000, micro_introns=True)
     _check(wl, f"micro/{mode}")
@@ -130,3 +131,36 @@ def test_merge_kernel_golden_and_random():
         assert np.array_equal(g, e), (k, reals[k], ideals[k], g, e)
     for k, (_, _, want) in enumerate(UPDATE_CIGAR_CASES):
         assert np.array_equal(got[k], cig(want))
+
+
+def test_ksw_kernel_golden_and_random():
+    from test_oracle_golden import KSW_Q, KSW_T, codes, port_ksw
+    wl = common.make_workload("default", 91, n_names=20)
+    rng = np.random.default_rng(17)
+    qs, ts = [codes(KSW_Q)], [codes(KSW_T)]
+    for k in range(400):
+        ql = int(rng.integers(1, 120)) if k % 10 else int(rng.integers(300, 900))
+        q = rng.integers(0, 4, size=ql).astype(np.uint8)
+        kind = k % 4
+        if kind == 0:       # unrelated target
+            t = rng.integers(0, 4, size=int(rng.integers(1, ql + 41))).astype(np.uint8)
+        else:               # target = query with substitutions / indels / Ns, plus a tail
+            t = list(q)
+            for _ in range(int(rng.integers(0, max(2, ql // 12)))):
+                pos = int(rng.integers(0, len(t)))
+                r = rng.random()
+                if r < 0.4: t[pos] = int(rng.integers(0, 5))
+                elif r < 0.7: del t[pos]
+                else: t.insert(pos, int(rng.integers(0, 4)))
+                if not t: t = [0]
+            t = np.array(t + list(rng.integers(0, 4, size=int(rng.integers(0, 41)))), dtype=np.uint8)[:ql + 40]
+        qs.append(q); ts.append(t)
+    with engine.Engine(wl["index"]) as eng:
+        got = eng.ksw_extend(qs, ts, cigar_cap=2048)
+    exp = port_ksw(qs, ts, cap=2048)
+    for k in ("max", "score", "max_q", "max_t", "zdropped", "n_cigar"):
+        assert np.array_equal(got[k], exp[k]), k
+    for i, (g, e) in enumerate(zip(got["cigars"], exp["cigars"])):
+        assert np.array_equal(g, e), i
+    assert (int(got["max"][0]), int(got["score"][0]), int(got["max_t"][0]), int(got["max_q"][0])) == (37, 11, 53, 54)
+    assert exp["zdropped"].sum() > 0 and (exp["score"] > -0x40000000).sum() > 50
