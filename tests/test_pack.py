@@ -1,0 +1,70 @@
+"""CPU: host-side ingest logic (Python mirror of the reference's pre-kernel half)."""
+import numpy as np
+
+from bramble_b200 import pack, shard
+import common
+
+
+def w(s):
+    import re
+    return [(int(n) << 4) | "MIDNSHP=X".index(o) for n, o in re.findall(r"(\d+)([MIDNSHP=X])", s)]
+
+
+def test_read_exons_follow_gsam_setup_coordinates():
+    assert pack.read_exons(100, w("50M")) == [(101, 151)]
+    assert pack.read_exons(100, w("5S20M100N30M3S")) == [(101, 121), (221, 251)]
+    assert pack.read_exons(100, w("10M2I10M3D10M")) == [(101, 134)]          # I ignored, D extends
+    assert pack.read_exons(100, w("100N20M")) == [(101, 121)]                 # leading N before any M is ignored
+    assert pack.read_exons(100, w("10M50N5I50N10M")) == [(101, 111), (211, 221)]   # I between two N's suppresses the close
+    assert pack.read_exons(100, w("10M50N")) == [(101, 111)]                  # trailing intron: no final exon
+    assert pack.read_exons(100, w("10=1X10=")) == [(101, 122)]
+
+
+def test_strand_rules():
+    r = dict(flag=0, tags=[("XS", "A", "-")])
+    assert pack.read_strand(r) == "-"
+    assert pack.read_strand(dict(flag=16, tags=[("ts", "A", "+")])) == "-"    # minimap2 ts flipped by FREVERSE
+    assert pack.read_strand(dict(flag=0, tags=[("ts", "A", "+")])) == "+"
+    assert pack.read_strand(dict(flag=0, tags=[])) == "."
+    # --fr: read1 forward -> '-', read2 forward -> '+'; unpaired forward -> '-'
+    assert pack.read_strand(dict(flag=1 | 0x40, tags=[]), fr=True) == "-"
+    assert pack.read_strand(dict(flag=1 | 0x40 | 16, tags=[]), fr=True) == "+"
+    assert pack.read_strand(dict(flag=1 | 0x80, tags=[]), fr=True) == "+"
+    assert pack.read_strand(dict(flag=0, tags=[]), fr=True) == "-"
+    assert pack.read_strand(dict(flag=1 | 0x40 | 16, tags=[]), rf=True) == "-"
+
+
+def test_mates_groups_and_bundles():
+    wl = common.make_workload("default", 5, n_names=600, n_genes=20, chunk_size=150)
+    assert len(wl["batches"]) > 2
+    total = 0
+    for b in wl["batches"]:
+        A = b.arrays
+        n = b.desc.n_aln
+        total += n
+        m = A["mate_idx"]
+        for a in range(n):
+            if m[a] >= 0:
+                assert m[m[a]] == a and m[a] != a                      # single, symmetric links
+                assert b.names[a] == b.names[m[a]]
+        go = A["group_off"]
+        assert go[0] == 0 and go[-1] == n
+        for g in range(len(go) - 1):
+            names = {b.names[a] for a in range(go[g], go[g + 1])}
+            assert len(names) == 1
+        if b is not wl["batches"][-1]:
+            assert n >= 150                                             # cut only at a name change after >= chunk alignments
+    assert total == sum(1 for r in wl["recs"] if not r["flag"] & 4)
+
+
+def test_sort_perm_is_a_permutation_sorted_by_start():
+    rng = np.random.default_rng(1)
+    st = rng.integers(0, 50, size=5000).astype(np.int32)
+    perm = pack.sort_perm_by_start(st)
+    assert sorted(perm.tolist()) == list(range(5000))
+    assert np.all(np.diff(st[perm]) >= 0)
+
+
+def test_shard_dealing():
+    assert shard.bundles_of_rank(7, 2, 0) == [0, 2, 4, 6] and shard.bundles_of_rank(7, 2, 1) == [1, 3, 5]
+    assert [shard.owner_of(k, 4) for k in range(6)] == [0, 1, 2, 3, 0, 1]
