@@ -1,0 +1,146 @@
+// BGZF (blocked gzip) reader and writer over zlib.  Host-side I/O of the drop-in CLI; htslib/libdeflate are
+// not in this image, so the codec is written here (same container format: 64 KiB blocks, BC extra field,
+// EOF marker block).  The writer compresses blocks on a small thread pool, keeping block order.
+#pragma once
+#include <zlib.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <condition_variable>
+#include <deque>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <thread>
+#include <vector>
+
+namespace brbhost {
+
+class BgzfReader {
+ public:
+  explicit BgzfReader(const std::string& path) {
+    f_ = fopen(path.c_str(), "rb");
+    if (!f_) throw std::runtime_error("cannot open " + path);
+    setvbuf(f_, nullptr, _IOFBF, 1 << 20);
+  }
+  ~BgzfReader() { if (f_) fclose(f_); }
+  // reads exactly n bytes unless EOF; returns bytes read
+  size_t read(void* dst, size_t n) {
+    uint8_t* d = static_cast<uint8_t*>(dst); size_t got = 0;
+    while (got < n) {
+      if (pos_ == buf_.size()) { if (!fill()) break; }
+      size_t k = std::min(n - got, buf_.size() - pos_);
+      memcpy(d + got, buf_.data() + pos_, k); pos_ += k; got += k;
+    }
+    return got;
+  }
+ private:
+  bool fill() {
+    for (;;) {
+      uint8_t h[12];
+      if (fread(h, 1, 12, f_) != 12) return false;
+      if (h[0] != 0x1f || h[1] != 0x8b) throw std::runtime_error("not a BGZF file");
+      const unsigned xlen = h[10] | (h[11] << 8);
+      extra_.resize(xlen);
+      if (xlen && fread(extra_.data(), 1, xlen, f_) != xlen) return false;
+      unsigned bsize = 0; bool found = false;
+      for (size_t p = 0; p + 4 <= xlen;) {
+        const unsigned slen = extra_[p + 2] | (extra_[p + 3] << 8);
+        if (extra_[p] == 'B' && extra_[p + 1] == 'C' && slen == 2) { bsize = extra_[p + 4] | (extra_[p + 5] << 8); found = true; }
+        p += 4 + slen;
+      }
+      if (!found) throw std::runtime_error("BGZF block without BC field");
+      const size_t clen = (size_t)bsize + 1 - xlen - 12 - 8;
+      comp_.resize(clen + 8);
+      if (fread(comp_.data(), 1, clen + 8, f_) != clen + 8) return false;
+      const uint32_t isize = comp_[clen + 4] | (comp_[clen + 5] << 8) | (comp_[clen + 6] << 16) | ((uint32_t)comp_[clen + 7] << 24);
+      buf_.resize(isize); pos_ = 0;
+      if (isize == 0) continue;
+      z_stream zs; memset(&zs, 0, sizeof zs);
+      if (inflateInit2(&zs, -15) != Z_OK) throw std::runtime_error("inflateInit2");
+      zs.next_in = comp_.data(); zs.avail_in = (uInt)clen; zs.next_out = buf_.data(); zs.avail_out = isize;
+      const int rc = inflate(&zs, Z_FINISH); inflateEnd(&zs);
+      if (rc != Z_STREAM_END) throw std::runtime_error("BGZF inflate failed");
+      return true;
+    }
+  }
+  FILE* f_ = nullptr; std::vector<uint8_t> buf_, comp_, extra_; size_t pos_ = 0;
+};
+
+class BgzfWriter {
+ public:
+  static constexpr size_t BLOCK = 0xff00;
+  BgzfWriter(const std::string& path, int level, int threads) : level_(level) {
+    f_ = fopen(path.c_str(), "wb");
+    if (!f_) throw std::runtime_error("cannot create " + path);
+    setvbuf(f_, nullptr, _IOFBF, 1 << 20);
+    if (threads < 1) threads = 1;
+    for (int i = 0; i < threads; i++) pool_.emplace_back([this] { worker(); });
+  }
+  ~BgzfWriter() { try { close(); } catch (...) {} }
+  void write(const void* src, size_t n) {
+    const uint8_t* s = static_cast<const uint8_t*>(src);
+    while (n) {
+      size_t k = std::min(n, BLOCK - cur_.size());
+      cur_.insert(cur_.end(), s, s + k); s += k; n -= k;
+      if (cur_.size() == BLOCK) submit();
+    }
+  }
+  void flush_block() { if (!cur_.empty()) submit(); }   // htslib flushes after the header
+  void close() {
+    if (!f_) return;
+    flush_block();
+    { std::unique_lock<std::mutex> lk(m_); done_ = true; }
+    cv_.notify_all();
+    for (auto& t : pool_) t.join();
+    pool_.clear();
+    drain(true);
+    static const uint8_t eof[28] = {0x1f, 0x8b, 8, 4, 0, 0, 0, 0, 0, 0xff, 6, 0, 'B', 'C', 2, 0, 0x1b, 0, 3, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    fwrite(eof, 1, 28, f_);
+    fclose(f_); f_ = nullptr;
+  }
+ private:
+  struct Job { std::vector<uint8_t> in, out; bool ready = false; };
+  void submit() {
+    Job* j = new Job(); j->in.swap(cur_); cur_.reserve(BLOCK);
+    { std::unique_lock<std::mutex> lk(m_); order_.push_back(j); todo_.push_back(j); }
+    cv_.notify_one();
+    drain(false);
+    // bound memory: wait when too many blocks are in flight
+    std::unique_lock<std::mutex> lk(m_);
+    while (order_.size() > 256) { lk.unlock(); drain(false); std::this_thread::yield(); lk.lock(); }
+  }
+  void worker() {
+    for (;;) {
+      Job* j = nullptr;
+      { std::unique_lock<std::mutex> lk(m_); cv_.wait(lk, [this] { return done_ || !todo_.empty(); }); if (todo_.empty()) return; j = todo_.front(); todo_.pop_front(); }
+      compress(*j);
+      { std::unique_lock<std::mutex> lk(m_); j->ready = true; }
+    }
+  }
+  void compress(Job& j) {
+    j.out.resize(compressBound((uLong)j.in.size()) + 32);
+    z_stream zs; memset(&zs, 0, sizeof zs);
+    deflateInit2(&zs, level_, Z_DEFLATED, -15, 8, Z_DEFAULT_STRATEGY);
+    zs.next_in = j.in.data(); zs.avail_in = (uInt)j.in.size(); zs.next_out = j.out.data() + 18; zs.avail_out = (uInt)(j.out.size() - 26);
+    deflate(&zs, Z_FINISH); const size_t clen = zs.total_out; deflateEnd(&zs);
+    static const uint8_t head[16] = {0x1f, 0x8b, 8, 4, 0, 0, 0, 0, 0, 0xff, 6, 0, 'B', 'C', 2, 0};
+    memcpy(j.out.data(), head, 16);
+    const uint16_t bs = (uint16_t)(clen + 25); memcpy(j.out.data() + 16, &bs, 2);
+    const uint32_t crc = (uint32_t)crc32(crc32(0, nullptr, 0), j.in.data(), (uInt)j.in.size()), isz = (uint32_t)j.in.size();
+    memcpy(j.out.data() + 18 + clen, &crc, 4); memcpy(j.out.data() + 22 + clen, &isz, 4);
+    j.out.resize(clen + 26);
+  }
+  void drain(bool all) {
+    for (;;) {
+      Job* j = nullptr;
+      { std::unique_lock<std::mutex> lk(m_); if (order_.empty()) return; if (!order_.front()->ready) { if (!all) return; lk.unlock(); std::this_thread::yield(); continue; } j = order_.front(); order_.pop_front(); }
+      fwrite(j->out.data(), 1, j->out.size(), f_); delete j;
+    }
+  }
+  FILE* f_ = nullptr; int level_; std::vector<uint8_t> cur_;
+  std::vector<std::thread> pool_; std::mutex m_; std::condition_variable cv_;
+  std::deque<Job*> order_, todo_; bool done_ = false;
+};
+
+}  // namespace brbhost

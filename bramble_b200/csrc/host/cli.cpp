@@ -1,0 +1,367 @@
+// bramble_b200 -- drop-in CLI for the reference's projection path (same surface as `bramble`,
+// reference src/bramble.cpp:449-485): positional BAM, -G/-S/-o/-p, --fr/--rf/--lr/--lr-hq/--strict,
+// the --max-* / --similarity-threshold overrides, --quiet, -V; output = transcriptome-coordinate BAM.
+// Host keeps BAM/BGZF decode+encode, GTF/FASTA loading, ingest (process_reads src/bramble.cpp:329-435) and
+// the flush()/write_to_bam bookkeeping (src/core.cpp:96-332, incl. the libstdc++ unordered_map order and
+// mt19937_64 tie-break); everything between (convert_reads' evaluate/pair/merge) runs behind the C ABI.
+// Extra flags: --gpus N (bundles dealt round-robin to N devices, ordered merge), --level L (BGZF level).
+#include <atomic>
+#include <cmath>
+#include <condition_variable>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <deque>
+#include <limits>
+#include <memory>
+#include <mutex>
+#include <optional>
+#include <random>
+#include <string>
+#include <thread>
+#include <unordered_map>
+#include <unordered_set>
+#include <vector>
+
+#include "annot.hpp"
+#include "bamrec.hpp"
+#include "bgzf.hpp"
+#include "engine_if.hpp"
+
+using namespace brbhost;
+
+namespace {
+
+const char* VERSION = "0.1.6";     // reference include/bramble.h VERSION: appears in the @PG line
+
+struct Options {
+  std::string in_bam, gtf, out_bam, fasta, cmdline;
+  bool quiet = false, fr = false, rf = false, lr = false, lr_hq = false, strict = false;
+  std::optional<uint32_t> max_clip, max_ins, max_gap, max_err; std::optional<float> sim;
+  int threads = 1, gpus = 1, level = 6; uint32_t chunk = 100000;
+};
+
+[[noreturn]] void usage(const char* msg) {
+  fprintf(stderr, "%s\nusage: bramble_b200 <in.bam> -G <gtf> -o <out.bam> [-S genome.fa] [-p N] [--fr|--rf] [--lr|--lr-hq] [--strict]\n"
+                  "       [--max-soft-clip N] [--max-junction-insertion N] [--max-junction-deletion N] [--max-error-exon N]\n"
+                  "       [--similarity-threshold F] [--quiet] [--gpus N] [--level L] [-V]\n", msg);
+  exit(msg[0] ? 106 : 0);          // CLI11 exits with its own error codes on a parse error
+}
+
+Options parse(int argc, char** argv) {
+  Options o;
+  for (int i = 0; i < argc; i++) { if (i) o.cmdline += " "; o.cmdline += argv[i]; }
+  auto need = [&](int& i) -> const char* { if (i + 1 >= argc) usage("missing value"); return argv[++i]; };
+  for (int i = 1; i < argc; i++) {
+    std::string a = argv[i], v; size_t eq = a.find('=');
+    bool has_v = false;
+    if (a.rfind("--", 0) == 0 && eq != std::string::npos) { v = a.substr(eq + 1); a = a.substr(0, eq); has_v = true; }
+    auto val = [&]() -> std::string { return has_v ? v : std::string(need(i)); };
+    if (a == "--quiet") o.quiet = true; else if (a == "--fr") o.fr = true; else if (a == "--rf") o.rf = true;
+    else if (a == "--lr") o.lr = true; else if (a == "--lr-hq") o.lr_hq = true; else if (a == "--strict") o.strict = true;
+    else if (a == "--max-soft-clip") o.max_clip = (uint32_t)std::stoul(val());
+    else if (a == "--max-junction-insertion") o.max_ins = (uint32_t)std::stoul(val());
+    else if (a == "--max-junction-deletion") o.max_gap = (uint32_t)std::stoul(val());
+    else if (a == "--max-error-exon") o.max_err = (uint32_t)std::stoul(val());
+    else if (a == "--similarity-threshold") o.sim = std::stof(val());
+    else if (a == "-G" || a == "--guide") o.gtf = val(); else if (a == "-S" || a == "--genome") o.fasta = val();
+    else if (a == "-o" || a == "--out") o.out_bam = val(); else if (a == "-p") o.threads = std::stoi(val());
+    else if (a == "--gpus") o.gpus = std::stoi(val()); else if (a == "--level") o.level = std::stoi(val());
+    else if (a == "--chunk") o.chunk = (uint32_t)std::stoul(val());
+    else if (a == "-V" || a == "--version") { printf("version: %s\n", VERSION); exit(0); }
+    else if (a == "-h" || a == "--help") usage("");
+    else if (a[0] == '-' && a.size() > 1) usage(("unknown option " + a).c_str());
+    else if (o.in_bam.empty()) o.in_bam = a; else usage("more than one positional argument");
+  }
+  if (const char* g = getenv("BRB_GPUS")) o.gpus = atoi(g);      // same as --gpus, without changing the @PG CL: text
+  if (const char* l = getenv("BRB_LEVEL")) o.level = atoi(l);
+  if (o.in_bam.empty()) usage("in.bam is required");
+  if (o.out_bam.empty()) usage("-o is required");         // required in code, src/bramble.cpp:477-478
+  return o;
+}
+
+brb_params resolve(const Options& o) {                     // src/evaluate.cpp:1136-1221
+  brb_params p{}; const bool lng = o.lr || o.lr_hq;
+  uint32_t clip, ins, gap, err; float sim;
+  if (!lng) { clip = o.strict ? 0 : 5; ins = 0; gap = 0; sim = 1.0f; err = 0; }
+  else if (o.lr) { clip = 40; ins = 40; gap = 40; sim = 0.60f; err = 35; }
+  else { clip = 5; ins = 10; gap = 10; sim = 0.90f; err = 35; }
+  p.max_clip = o.max_clip.value_or(clip); p.max_junc_ins = o.max_ins.value_or(ins); p.max_junc_gap = o.max_gap.value_or(gap);
+  p.max_error_exon = o.max_err.value_or(err); p.similarity_threshold = o.sim.value_or(sim);
+  p.long_reads = lng; p.use_fasta = !o.fasta.empty(); p.ignore_small_exons = p.max_error_exon > 0;
+  p.filter_by_similarity = p.similarity_threshold < 1.0f;
+  return p;
+}
+
+std::string field_of(const std::string& line, const char* key) {
+  size_t p = 0; const size_t kl = strlen(key);
+  while ((p = line.find('\t', p)) != std::string::npos) {
+    p++;
+    if (line.compare(p, kl, key) == 0) { size_t e = line.find('\t', p); return line.substr(p + kl, e == std::string::npos ? std::string::npos : e - p - kl); }
+  }
+  return std::string();
+}
+
+// htslib sam_hdr_add_pg(hdr, "bramble", "VN", v, "CL", cl, NULL): unique ID, PP chained to every chain end.
+std::string add_pg(std::string text, const std::string& name, const std::string& extra) {
+  std::vector<std::string> ids, pps;
+  for (size_t p = 0; p < text.size();) {
+    size_t e = text.find('\n', p); if (e == std::string::npos) e = text.size();
+    const std::string line = text.substr(p, e - p);
+    if (line.compare(0, 3, "@PG") == 0) { ids.push_back(field_of(line, "ID:")); pps.push_back(field_of(line, "PP:")); }
+    p = e + 1;
+  }
+  std::vector<std::string> ends;
+  for (size_t i = 0; i < ids.size(); i++) {
+    bool referenced = false;
+    for (size_t j = 0; j < pps.size(); j++) if (j != i && pps[j] == ids[i]) referenced = true;
+    if (!referenced) ends.push_back(ids[i]);
+  }
+  auto unique_id = [&]() { std::string id = name; int n = 0; for (;;) { bool taken = false; for (auto& x : ids) if (x == id) taken = true; if (!taken) break; id = name + "." + std::to_string(++n); } ids.push_back(id); return id; };
+  if (!text.empty() && text.back() != '\n') text += "\n";
+  if (ends.empty()) text += "@PG\tID:" + unique_id() + "\tPN:" + name + extra + "\n";
+  else for (auto& pp : ends) text += "@PG\tID:" + unique_id() + "\tPN:" + name + "\tPP:" + pp + extra + "\n";
+  return text;
+}
+
+struct InHeader { std::string text; std::vector<std::string> ref_names; };
+
+InHeader read_bam_header(BgzfReader& in) {
+  InHeader h; char magic[4]; int32_t l_text = 0, n_ref = 0;
+  if (in.read(magic, 4) != 4 || memcmp(magic, "BAM\1", 4)) throw std::runtime_error("input is not a BAM file");
+  in.read(&l_text, 4); h.text.resize(l_text); if (l_text) in.read(&h.text[0], l_text);
+  while (!h.text.empty() && h.text.back() == 0) h.text.pop_back();
+  in.read(&n_ref, 4);
+  for (int i = 0; i < n_ref; i++) { int32_t ln = 0, len = 0; in.read(&ln, 4); std::string nm(ln, 0); in.read(&nm[0], ln); nm.resize(strlen(nm.c_str())); in.read(&len, 4); h.ref_names.push_back(nm); }
+  return h;
+}
+
+// output header text, reference src/bramble.cpp:552-623
+std::string make_header(const InHeader& ih, const Annotation& A, const Options& o) {
+  const std::string with_pg = add_pg(ih.text, "bramble", std::string("\tVN:") + VERSION + "\tCL:" + o.cmdline);
+  std::string out;
+  auto each = [&](auto fn) { for (size_t p = 0; p < with_pg.size();) { size_t e = with_pg.find('\n', p); if (e == std::string::npos) e = with_pg.size(); fn(with_pg.substr(p, e - p)); p = e + 1; } };
+  each([&](const std::string& l) { if (l.compare(0, 3, "@HD") == 0) out += l + "\n"; });
+  for (auto& t : A.tx) if (t.tlen > 0) out += "@SQ\tSN:" + t.id + "\tLN:" + std::to_string((int)t.tlen) + "\n";
+  each([&](const std::string& l) { if (l.compare(0, 3, "@SQ") != 0 && l.compare(0, 3, "@HD") != 0) out += l + "\n"; });
+  out += "@CO\tGenerated from GTF: " + o.gtf + "\n";
+  return out;
+}
+
+// ------------------------------------------------------------------------------------------------ bundles
+struct Bundle {
+  uint64_t index = 0;
+  std::vector<uint8_t> raw; std::vector<uint64_t> rec_off; std::vector<uint32_t> rec_len;       // record bodies
+  std::vector<uint32_t> group_off, exon_off, exon_st, exon_en, cigar_off, cigar; std::vector<int32_t> refid, mate; std::vector<int8_t> strand;
+  std::vector<uint64_t> seq_off; std::vector<uint8_t> seq;
+  // result (copied out of the engine's staging)
+  std::vector<uint32_t> g_roff, src, tid, pos, coff, clen, cig; std::vector<int8_t> tstrand; std::vector<uint8_t> flags; std::vector<double> sim; std::vector<int32_t> clip;
+  RecView view(uint32_t a) const { return RecView{raw.data() + rec_off[a], rec_len[a]}; }
+  uint32_t n_aln() const { return (uint32_t)refid.size(); }
+};
+
+struct Stats { uint64_t total_reads = 0, unmapped = 0, dropped = 0, total_complete = 0, total_unique = 0; };
+
+void fill_batch(const Bundle& b, bool use_fasta, brb_batch_in& in) {
+  in.n_aln = b.n_aln(); in.n_groups = (uint32_t)b.group_off.size() - 1; in.group_off = b.group_off.data(); in.refid = b.refid.data();
+  in.strand = b.strand.data(); in.exon_off = b.exon_off.data(); in.exon_st = b.exon_st.data(); in.exon_en = b.exon_en.data();
+  in.cigar_off = b.cigar_off.data(); in.cigar = b.cigar.data(); in.mate_idx = b.mate.data();
+  in.group_seq_off = use_fasta ? b.seq_off.data() : nullptr; in.seq_codes = use_fasta ? (b.seq.empty() ? (const uint8_t*)"" : b.seq.data()) : nullptr;
+}
+
+void store_result(Bundle& b, const brb_batch_out& o) {
+  const uint32_t R = o.n_rec, G = (uint32_t)b.group_off.size() - 1;
+  b.g_roff.assign(o.group_rec_off, o.group_rec_off + G + 1); b.src.assign(o.src_aln, o.src_aln + R); b.tid.assign(o.tid, o.tid + R);
+  b.pos.assign(o.pos, o.pos + R); b.tstrand.assign(o.tx_strand, o.tx_strand + R); b.flags.assign(o.flags, o.flags + R);
+  b.sim.assign(o.sim_score, o.sim_score + R); b.clip.assign(o.clip_score, o.clip_score + R);
+  b.coff.assign(o.cigar_off, o.cigar_off + R); b.clen.assign(o.cigar_len, o.cigar_len + R); b.cig.assign(o.cigar, o.cigar + o.n_cigar_words);
+}
+
+uint32_t get_mapq(uint32_t nh, bool lng) {                 // src/core.cpp:46-58
+  if (!lng) return nh == 1 ? 255 : nh == 2 ? 3 : (nh == 3 || nh == 4) ? 1 : 0;
+  return nh > 1 ? 0 : 3;
+}
+int32_t get_rand(uint32_t x, uint64_t seed_key) {          // src/core.cpp:214-218 (libstdc++ mt19937_64 + uniform_int_distribution)
+  std::mt19937_64 gen(seed_key); std::uniform_int_distribution<uint32_t> dis(0, x - 1); return dis(gen);
+}
+
+// flush() + write_to_bam of the reference for one bundle's rows.
+void assemble_bundle(const Bundle& b, bool lng, Stats& st, std::vector<uint8_t>& out) {
+  struct Unit { uint32_t row; bool paired; int32_t hi_r = 0, hi_m = 0; bool primary = false; uint32_t nh = 0, mapq = 0; };
+  std::unordered_map<std::string, std::vector<Unit>> pairs_by_name;
+  uint32_t n_pairs = 0; std::vector<uint8_t> aux;
+  auto flush = [&]() {
+    std::vector<Unit*> filtered;
+    for (auto& [read_name, pairs] : pairs_by_name) {
+      double best_score = -std::numeric_limits<double>::infinity(); int count_at_best = 0; size_t best = pairs.size(); int32_t hit_index = 1; int total = 0;
+      auto score_of = [&](const Unit& u) { double s = b.sim[u.row]; if (u.paired) s = std::max(s, b.sim[u.row + 1]); return s; };
+      for (size_t i = 0; i < pairs.size(); i++) {
+        Unit& u = pairs[i]; u.hi_r = hit_index++; total++;
+        if (u.paired) { u.hi_m = hit_index++; total++; }
+        const double ps = score_of(u);
+        if (ps > best_score) { best_score = ps; best = i; count_at_best = 1; } else if (ps == best_score) count_at_best++;
+      }
+      if (best != pairs.size()) {
+        if (count_at_best == 1) pairs[best].primary = true;
+        else {
+          std::vector<size_t> tied;
+          for (size_t i = 0; i < pairs.size(); i++) if (score_of(pairs[i]) == best_score) tied.push_back(i);
+          const uint64_t seed_key = std::hash<std::string>{}(read_name);
+          pairs[tied[get_rand((uint32_t)tied.size(), seed_key)]].primary = true;
+        }
+      }
+      st.total_complete += total; if (total == 1) st.total_unique++;
+      for (auto& u : pairs) { u.nh = (uint32_t)total; u.mapq = get_mapq((uint32_t)total, lng); filtered.push_back(&u); }
+    }
+    for (Unit* u : filtered) {
+      for (int k = 0; k < (u->paired ? 2 : 1); k++) {
+        const uint32_t r = u->row + k, other = u->row + (1 - k);
+        OutInfo o{}; o.tid = b.tid[r]; o.pos = b.pos[r]; o.strand = (char)b.tstrand[r]; o.paired = u->paired; o.same_tx = b.flags[r] & BRB_REC_SAMETX;
+        o.primary = u->primary; o.long_reads = lng; o.mapq = u->mapq; o.nh = (int32_t)u->nh; o.hi = k == 0 ? u->hi_r : u->hi_m;
+        o.sim = b.sim[r]; o.clip = b.clip[r]; o.cigar = b.cig.data() + b.coff[r]; o.n_cigar = b.clen[r];
+        if (u->paired) { o.mate_tid = b.tid[other]; o.mate_pos = b.pos[other]; }
+        assemble_record(b.view(b.src[r]), o, aux, out);
+      }
+    }
+    pairs_by_name.clear(); n_pairs = 0;
+  };
+  const uint32_t G = (uint32_t)b.group_off.size() - 1;
+  for (uint32_t g = 0; g < G; g++) {
+    const uint32_t lo = b.g_roff[g], hi = b.g_roff[g + 1];
+    if (lo == hi) st.dropped++;
+    for (uint32_t r = lo; r < hi;) {
+      const bool paired = b.flags[r] & BRB_REC_PAIRED;
+      const RecView v = b.view(b.src[r]);
+      pairs_by_name[std::string(v.name())].push_back(Unit{r, paired});
+      n_pairs++; r += paired ? 2 : 1;
+    }
+    if (n_pairs >= 5000) flush();                          // CHUNK_SIZE, src/core.cpp:27,421-423
+  }
+  if (!pairs_by_name.empty()) flush();
+}
+
+}  // namespace
+
+int main(int argc, char** argv) {
+  Options o = parse(argc, argv);
+  try {
+    const bool lng = o.lr || o.lr_hq; const brb_params params = resolve(o);
+    if (!o.quiet) printf("\n[bramble_b200] starting (reference surface version %s)\n", VERSION);
+    Annotation A;
+    try { load_annotation(o.gtf, A); } catch (const std::exception& e) { fprintf(stderr, "error: %s\n", e.what()); return 0; }   // reference returns 0, src/bramble.cpp:520-525
+    if (A.tx.empty()) { fprintf(stderr, "error: could not find valid reference transcripts in %s\n", o.gtf.c_str()); return 0; }
+    IndexColumns cols;
+    if (!o.fasta.empty()) load_genome(o.fasta, A, cols.chrom_off, cols.genome);
+    build_index_columns(A, cols);
+    BgzfReader in(o.in_bam);
+    const InHeader ih = read_bam_header(in);
+    const std::string header = make_header(ih, A, o);
+    std::vector<int> ref2refid(ih.ref_names.size(), -1);
+    for (size_t i = 0; i < ih.ref_names.size(); i++) { auto it = A.refid_of.find(ih.ref_names[i]); if (it != A.refid_of.end()) ref2refid[i] = it->second; }
+
+    const int n_gpu = std::max(1, o.gpus);
+    std::vector<std::unique_ptr<EngineIf>> engines;
+    for (int g = 0; g < n_gpu; g++) { engines.emplace_back(make_engine()); engines.back()->open(g, cols.desc); }
+
+    BgzfWriter out(o.out_bam, o.level, std::max(1, o.threads));
+    { std::vector<uint8_t> hb; auto put = [&](const void* p, size_t n) { hb.insert(hb.end(), (const uint8_t*)p, (const uint8_t*)p + n); };
+      put("BAM\1", 4); int32_t lt = (int32_t)header.size(); put(&lt, 4); put(header.data(), header.size());
+      int32_t nt = 0; for (auto& t : A.tx) if (t.tlen > 0) nt++; put(&nt, 4);
+      for (auto& t : A.tx) if (t.tlen > 0) { int32_t l = (int32_t)t.id.size() + 1; put(&l, 4); put(t.id.c_str(), l); uint32_t ln = t.tlen; put(&ln, 4); }
+      out.write(hb.data(), hb.size()); out.flush_block(); }
+
+    // pipeline: producer (this thread) -> per-GPU worker -> ordered assembler/writer
+    Stats st; std::mutex m; std::condition_variable cv;
+    std::vector<std::deque<std::shared_ptr<Bundle>>> todo(n_gpu); std::deque<std::shared_ptr<Bundle>> inflight; bool eof = false; std::string err;
+    std::vector<std::shared_ptr<Bundle>> done_flags;
+    std::unordered_set<uint64_t> finished;
+    auto worker = [&](int g) {
+      for (;;) {
+        std::shared_ptr<Bundle> b;
+        { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return eof || !todo[g].empty() || !err.empty(); }); if (!err.empty()) return; if (todo[g].empty()) { if (eof) return; continue; } b = todo[g].front(); todo[g].pop_front(); }
+        brb_batch_in bi{}; fill_batch(*b, params.use_fasta, bi); brb_batch_out bo{};
+        const int rc = engines[g]->project(params, bi, bo);
+        std::unique_lock<std::mutex> lk(m);
+        if (rc != 0) { err = engines[g]->last_error(); cv.notify_all(); return; }
+        store_result(*b, bo); finished.insert(b->index); cv.notify_all();
+      }
+    };
+    auto writer = [&]() {
+      std::vector<uint8_t> buf;
+      for (;;) {
+        std::shared_ptr<Bundle> b;
+        { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return !err.empty() || (!inflight.empty() && finished.count(inflight.front()->index)) || (eof && inflight.empty()); });
+          if (!err.empty()) return; if (inflight.empty()) return; b = inflight.front(); inflight.pop_front(); finished.erase(b->index); cv.notify_all(); }
+        buf.clear(); assemble_bundle(*b, lng, st, buf); out.write(buf.data(), buf.size());
+      }
+    };
+    std::vector<std::thread> threads; for (int g = 0; g < n_gpu; g++) threads.emplace_back(worker, g);
+    std::thread wthread(writer);
+
+    auto bundle = std::make_shared<Bundle>(); uint64_t n_bundles = 0;
+    std::unordered_map<std::string, uint32_t> hashread; std::string prev_name; std::vector<std::string> names;
+    auto new_bundle = [&]() { auto b = std::make_shared<Bundle>(); b->group_off.push_back(0); b->exon_off.push_back(0); b->cigar_off.push_back(0); b->seq_off.push_back(0); return b; };
+    bundle = new_bundle();
+    auto push_bundle = [&]() {
+      if (bundle->n_aln() == 0) return;
+      Bundle& b = *bundle; b.group_off.push_back(b.n_aln());
+      if (params.use_fasta) {                                // group-shared sequence = first record of the group with l_qseq > 0 (src/core.cpp:353-378)
+        static const char nt16[] = "=ACMGRSVTWYHKDBN";
+        for (size_t g = 0; g + 1 < b.group_off.size(); g++) {
+          for (uint32_t a = b.group_off[g]; a < b.group_off[g + 1]; a++) {
+            const RecView v = b.view(a); const int32_t lq = v.l_seq();
+            if (lq > 0) { const uint8_t* s = v.seq(); for (int32_t i = 0; i < lq; i++) { const char c = nt16[(s[i >> 1] >> ((~i & 1) << 2)) & 0xf]; b.seq.push_back(c == 'A' ? 0 : c == 'C' ? 1 : c == 'G' ? 2 : c == 'T' ? 3 : 4); } break; }
+          }
+          b.seq_off.push_back(b.seq.size());
+        }
+      }
+      b.index = n_bundles++;
+      { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return inflight.size() < (size_t)(2 * n_gpu + 2) || !err.empty(); }); todo[b.index % n_gpu].push_back(bundle); inflight.push_back(bundle); }
+      cv.notify_all();
+      bundle = new_bundle(); hashread.clear();
+    };
+    std::vector<uint8_t> rec;
+    for (;;) {
+      int32_t bs = 0;
+      if (in.read(&bs, 4) != 4) break;
+      rec.resize(bs); if (in.read(rec.data(), bs) != (size_t)bs) throw std::runtime_error("truncated BAM record");
+      st.total_reads++;
+      const RecView v{rec.data(), (uint32_t)bs};
+      if (v.flag() & 4) { st.unmapped++; continue; }
+      const std::string name = v.name();
+      const uint32_t id = bundle->n_aln();
+      const bool new_name = (id == 0) || name != prev_name;
+      if (id >= o.chunk && new_name) push_bundle();
+      Bundle& b = *bundle; const uint32_t a = b.n_aln();
+      if (a > 0 && new_name) b.group_off.push_back(a);
+      b.rec_off.push_back(b.raw.size()); b.rec_len.push_back((uint32_t)bs); b.raw.insert(b.raw.end(), rec.begin(), rec.end());
+      const RecView w = b.view(a);
+      if (!read_exons(w, b.exon_st, b.exon_en)) { fprintf(stderr, "Error: invalid CIGAR record for %s !\n", w.name()); exit(1); }
+      b.exon_off.push_back((uint32_t)b.exon_st.size());
+      for (uint32_t i = 0; i < w.n_cigar(); i++) b.cigar.push_back(rd32(w.cigar() + 4 * i));
+      b.cigar_off.push_back((uint32_t)b.cigar.size());
+      b.strand.push_back(lng ? '.' : get_strand(w, o.fr, o.rf));
+      const int32_t t = w.tid(); b.refid.push_back(t >= 0 && (size_t)t < ref2refid.size() ? ref2refid[t] : -1);
+      b.mate.push_back(-1);
+      if ((w.flag() & 1) && w.tid() == w.mtid()) {          // process_pairs, src/bramble.cpp:272-311
+        const int32_t start = w.pos() + 1, mate_start = w.mpos() < 0 ? 0 : w.mpos() + 1;
+        const std::string mate_key = name + '-' + std::to_string(mate_start);
+        auto it = hashread.find(mate_key);
+        if (it != hashread.end()) { const uint32_t mt = it->second; if (b.mate[a] < 0) b.mate[a] = (int32_t)mt; if (b.mate[mt] < 0) b.mate[mt] = (int32_t)a; hashread.erase(it); }
+        else hashread[name + '-' + std::to_string(start)] = a;
+      }
+      prev_name = name;
+    }
+    push_bundle();
+    { std::unique_lock<std::mutex> lk(m); eof = true; } cv.notify_all();
+    for (auto& t : threads) t.join();
+    wthread.join();
+    if (!err.empty()) { fprintf(stderr, "error: %s\n", err.c_str()); return 1; }
+    out.close();
+    if (!o.quiet) {
+      printf("\n[bramble_b200] final report:\n# input alignments:   %llu\n# unmapped reads:     %llu\n# dropped alignments: %llu\n# total alignments:   %llu\n# unique alignments:  %llu\n\n",
+             (unsigned long long)st.total_reads, (unsigned long long)st.unmapped, (unsigned long long)st.dropped, (unsigned long long)st.total_complete, (unsigned long long)st.total_unique);
+    }
+  } catch (const std::exception& e) { fprintf(stderr, "error: %s\n", e.what()); return 1; }
+  return 0;
+}

@@ -1,0 +1,17 @@
+// The one seam between the host CLI and the projection engine: the C ABI of include/bramble_b200.h.
+// The product binary binds it to libbramble_b200.so (engine_cuda.cpp); the CPU oracle build used ONLY by
+// tests binds the same interface to oracle/brb_port.cpp (oracle/port_engine.cpp) so that the host half
+// (ingest, flush replay, record assembly, BGZF) can be checked byte-for-byte without a GPU.
+#pragma once
+#include <string>
+#include "../../../include/bramble_b200.h"
+
+namespace brbhost {
+struct EngineIf {
+  virtual ~EngineIf() {}
+  virtual void open(int device, const brb_index_desc& desc) = 0;                 // throws std::runtime_error
+  virtual int project(const brb_params& p, const brb_batch_in& in, brb_batch_out& out) = 0;   // out valid until the next call
+  virtual std::string last_error() = 0;
+};
+EngineIf* make_engine();
+}  // namespace brbhost
