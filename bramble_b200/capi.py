@@ -45,8 +45,7 @@ class BatchIn(C.Structure):
 class BatchOut(C.Structure):
     _fields_ = [("n_rec", C.c_uint32), ("n_cigar_words", C.c_uint64), ("group_rec_off", u32p),
                 ("src_aln", u32p), ("tid", u32p), ("pos", u32p), ("tx_strand", i8p), ("flags", u8p),
-                ("sim_score", f64p), ("clip_score", i32p), ("cigar_off", u32p), ("cigar_len", u32p),
-                ("cigar", u32p)]
+                ("sim_score", f64p), ("clip_score", i32p), ("cigar_off", u32p), ("cigar", u32p)]
 
 
 class Stats(C.Structure):

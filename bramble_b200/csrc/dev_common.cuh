@@ -11,21 +11,31 @@ enum { FIRST_EXON = 0, MIDDLE_EXON = 1, LAST_EXON = 2, ONLY_EXON = 3 };
 enum { CM = 0, CI = 1, CD = 2, CN = 3, CS = 4, CH = 5, CP = 6, CEQ = 7, CX = 8,
        OV_M = 10, OV_D = 11, OV_I = 12, OV_S = 13 };   // override codes: include/evaluate.h:10-13
 #define BRB_KSW_NEG_INF (-0x40000000)
+constexpr uint32_t NONE = 0xffffffffu;
 
-// One guide exon = one IITree node (include/g2t.h:12-43), 48 B, three 16-byte sectors:
-//   .k  search/filter key   .nb neighbours in transcript order   .x  transcript length + exon id
-struct __align__(16) Rec {
+// One guide exon = one IITree node (include/g2t.h:12-43) = one 32-byte, 32-byte-aligned record: exactly one
+// L2/HBM sector.  First half = search/filter key (the only part the overlap scan reads), second half = the
+// links of the exon chain in GENOMIC order.  gclib merges overlapping and adjacent exons of a transcript
+// (gclib/gff.cpp:988-1075), so the exons of one tid inside a table are disjoint and ascending; that is
+// validated at brb_index_create and lets a candidate follow its transcript with one gather per read exon
+// instead of re-scanning the hit range of every exon.
+struct __align__(32) Rec {
   int32_t st, en; uint32_t tid, pos_start;
-  uint32_t prev_st, prev_en, next_st, next_en;
-  uint32_t tlen, meta /* exon_id | has_prev<<8 | has_next<<9 */, pad0, pad1;
+  int32_t gprev_en;        // end of the genomically previous exon of this tid (0 if none)
+  int32_t gnext_st;        // start of the genomically next exon of this tid (INT32_MAX if none)
+  uint32_t gnext;          // its record index (NONE if none)
+  uint32_t meta;           // exon_id | has_prev<<8 | has_next<<9  (prev/next in TRANSCRIPT order, include/g2t.h)
 };
 
 struct DevIndex {
-  uint32_t n_tables; uint32_t n_chrom; uint64_t n_rec;
+  uint32_t n_tables; uint32_t n_chrom; uint64_t n_rec; uint32_t bin_shift;
   const uint32_t* table_off;     // n_tables+1
   const int32_t* st;             // sorted starts (search key, SoA)
   const int32_t* pmax;           // running max of `en` inside each table (monotone -> binary search)
   const Rec* rec;
+  const uint32_t* gprev;         // record index of the genomically previous exon of the same tid (NONE if none)
+  const uint32_t* bin_off;       // n_tables+1 offsets into bins
+  const uint2* bins;             // per table, per bin b: .x = first i with pmax[i] > b<<shift, .y = first i with st[i] >= b<<shift
   const uint64_t* chrom_off; const uint8_t* genome;   // codes 0..4, or null
 };
 
@@ -37,11 +47,35 @@ struct DevBatch {
   const uint64_t* group_seq_off; const uint8_t* seq; const uint32_t* aln_group;
 };
 
+// Device-side control block of one brb_project_resident call: capacities of the pre-allocated pools and the
+// running totals.  No kernel of the sequence needs a host round trip; a pool that turns out too small makes
+// the producers stop writing (they keep counting), every later kernel returns at once, and the host grows
+// the pool and replays the sequence.
+struct Ctl {
+  unsigned long long n_hits, out_words, rescue_bytes, n_matches, n_rescue, ksw_max_mat, ksw_max_tlen, n_mates;   // work counters
+  uint32_t n_cand, cap_cand;          // candidate slots allocated / capacity
+  uint32_t n_ideal, cap_ideal;        // ideal-CIGAR pool words
+  uint32_t n_rows, cap_rows;          // output rows
+  uint32_t n_tmpw, cap_tmpw;          // merge scratch pool words
+  uint32_t n_outw, cap_outw;          // dense output CIGAR words
+  uint32_t bad_input;                 // 1: mate link not symmetric, 2: read exons not ascending/disjoint
+  uint32_t pad1;
+};
+__device__ __forceinline__ bool ctl_overflow(const Ctl* c) {
+  return c->n_cand > c->cap_cand || c->n_ideal > c->cap_ideal || c->n_rows > c->cap_rows || c->n_tmpw > c->cap_tmpw ||
+         c->n_outw > c->cap_outw || c->bad_input != 0;
+}
+
 __device__ __forceinline__ uint4 ldg4(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
 
 struct RecKey { int32_t st, en; uint32_t tid, pos_start; };
 __device__ __forceinline__ RecKey rec_key(const Rec* r, uint32_t i) {
   uint4 v = ldg4(&r[i]); RecKey k; k.st = (int32_t)v.x; k.en = (int32_t)v.y; k.tid = v.z; k.pos_start = v.w; return k;
+}
+struct RecLink { int32_t gprev_en, gnext_st; uint32_t gnext, meta; };
+__device__ __forceinline__ RecLink rec_link(const Rec* r, uint32_t i) {
+  uint4 v = ldg4(reinterpret_cast<const uint4*>(&r[i]) + 1);
+  RecLink k; k.gprev_en = (int32_t)v.x; k.gnext_st = (int32_t)v.y; k.gnext = v.z; k.meta = v.w; return k;
 }
 
 __device__ __forceinline__ int exon_status(uint32_t n, uint32_t j) {   // src/evaluate.cpp:44-56
@@ -70,33 +104,70 @@ __device__ __forceinline__ bool filter_hit(const brb_params& c, bool minus, int 
   }
   return true;
 }
+// Same filters, result only (the overlap scan does not need the Hit fields).
+__device__ __forceinline__ bool passes_filter(const brb_params& c, bool minus, int status, uint32_t qs, uint32_t qe, uint32_t s, uint32_t e) {
+  const bool ml = (status == MIDDLE_EXON || status == LAST_EXON), fm = (status == FIRST_EXON || status == MIDDLE_EXON);
+  const uint32_t lim_l = ml ? c.max_junc_ins : c.max_clip;
+  const uint32_t lim_r = minus ? c.max_junc_ins : (fm ? c.max_junc_ins : c.max_clip);
+  bool ok = true;
+  if (s <= qs) { if (ml && qs - s > c.max_junc_gap) ok = false; } else { if (s - qs > lim_l) ok = false; }
+  if (e < qe) { if (qe - e > lim_r) ok = false; } else { if (fm && e - qe > c.max_junc_gap) ok = false; }
+  return ok;
+}
 
 // cgranges IITree::overlap(qs,qe) == { i : st[i] < qe && qs < en[i] } in ascending i.
 // On the flattened table: hi = first i with st[i] >= qe; lo = first i with pmax[i] > qs; members of
-// [lo,hi) still need the `qs < en[i]` test.  Two branch-free binary searches.
+// [lo,hi) still need the `qs < en[i]` test.  A coarse bin table (one uint2 per 2^shift bases) brackets both
+// bounds, then a branch-free binary search over the few records of the bracket finishes them exactly.
 __device__ __forceinline__ void overlap_range(const DevIndex& ix, int32_t refid, bool minus, uint32_t qs, uint32_t qe,
                                               uint32_t& lo, uint32_t& hi) {
   lo = hi = 0;
   if (refid < 0 || (uint32_t)refid * 2u + 1u >= ix.n_tables) return;            // src/g2t.cpp:275-276
-  uint32_t t = (uint32_t)refid * 2u + (minus ? 1u : 0u);
-  uint32_t b = __ldg(&ix.table_off[t]), e = __ldg(&ix.table_off[t + 1]);
-  uint32_t l = b, n = e - b;
+  const uint32_t t = (uint32_t)refid * 2u + (minus ? 1u : 0u);
+  const uint32_t bo = __ldg(&ix.bin_off[t]), nb = __ldg(&ix.bin_off[t + 1]) - bo;
+  if (nb < 2) return;                                                           // empty table
+  uint32_t b0 = qs >> ix.bin_shift, b1 = qe >> ix.bin_shift;
+  if (b0 > nb - 2) b0 = nb - 2;
+  if (b1 > nb - 2) b1 = nb - 2;
+  const uint2 A0 = __ldg(&ix.bins[bo + b0]), A1 = __ldg(&ix.bins[bo + b0 + 1]);
+  const uint2 B0 = __ldg(&ix.bins[bo + b1]), B1 = __ldg(&ix.bins[bo + b1 + 1]);
+  uint32_t l = B0.y, n = B1.y - B0.y;
   while (n > 0) { uint32_t h = n >> 1; if (__ldg(&ix.st[l + h]) < (int32_t)qe) { l += h + 1; n -= h + 1; } else n = h; }
   hi = l;
-  l = b; n = hi - b;
+  l = A0.x; n = A1.x - A0.x;
   while (n > 0) { uint32_t h = n >> 1; if (__ldg(&ix.pmax[l + h]) <= (int32_t)qs) { l += h + 1; n -= h + 1; } else n = h; }
-  lo = l;
+  lo = l < hi ? l : hi;
 }
 
-// IntervalTree::findOverlappingForTid, src/g2t.cpp:70-101: first overlapping record (ascending index) of `tid`.
-__device__ __forceinline__ bool find_for_tid(const DevIndex& ix, int32_t refid, bool minus, uint32_t tid, uint32_t qs, uint32_t qe, uint32_t& out) {
-  if (qs == 0 && qe == 0) return false;
-  uint32_t lo, hi; overlap_range(ix, refid, minus, qs, qe, lo, hi);
-  for (uint32_t i = lo; i < hi; i++) {
-    RecKey k = rec_key(ix.rec, i);
-    if ((int32_t)qs < k.en && k.tid == tid) { out = i; return true; }
-  }
-  return false;
+// ---- warp helpers
+__device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, unsigned lane) {
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, v, d); if (lane >= (unsigned)d) v += y; }
+  return v;
+}
+// Owner lane of flat item `item` given the warp's inclusive prefix sums (item < total): the first lane L with incl[L] > item.
+__device__ __forceinline__ unsigned warp_owner(uint32_t incl, uint32_t item) {
+  unsigned pos = 0;
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) { const uint32_t v = __shfl_sync(0xffffffffu, incl, pos + d - 1); if (v <= item) pos += d; }
+  return pos;
+}
+// bits [a,b) of a 32-bit word, 0 <= a <= b <= 32
+__device__ __forceinline__ uint32_t bit_range(uint32_t a, uint32_t b) {
+  const uint32_t hi = b >= 32 ? 0xffffffffu : ((1u << b) - 1u);
+  const uint32_t lo = a >= 32 ? 0xffffffffu : ((1u << a) - 1u);
+  return hi & ~lo;
+}
+
+// Warp-aggregated allocation of `want` words per lane from a bump pool; returns the lane's offset.
+// `ok` is false for every lane of the warp when the pool is exhausted (the counter still advances).
+__device__ __forceinline__ uint32_t warp_alloc(uint32_t* __restrict__ counter, uint32_t cap, uint32_t want, unsigned lane, bool& ok) {
+  const uint32_t incl = warp_incl_scan(want, lane), tot = __shfl_sync(0xffffffffu, incl, 31);
+  uint32_t base = 0;
+  if (lane == 31 && tot) base = atomicAdd(counter, tot);
+  base = __shfl_sync(0xffffffffu, base, 31);
+  ok = (unsigned long long)base + tot <= cap;
+  return base + incl - want;
 }
 
 }  // namespace brb

@@ -6,6 +6,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -60,13 +61,18 @@ struct HBuf {                      // growable pinned host allocation
 
 inline unsigned grid_for(size_t n, unsigned block) { return (unsigned)((n + block - 1) / block); }
 
+struct RescueBufs;                       // rescue_host.inl
+
 }  // namespace
 
+struct brb_ctx;
+namespace { void free_rescue_bufs(brb_ctx* c); }
 struct brb_index {
   int device = 0;
   DevIndex d{};
-  Buf table_off, st, pmax, rec, chrom_off, genome;
+  Buf table_off, st, pmax, rec, gprev, bin_off, bins, chrom_off, genome;
   uint64_t bytes = 0;
+  void release_all() { for (Buf* b : {&table_off, &st, &pmax, &rec, &gprev, &bin_off, &bins, &chrom_off, &genome}) b->release(); }
 };
 
 struct brb_ctx {
@@ -78,17 +84,26 @@ struct brb_ctx {
   DevBatch b{};
   Buf in_group_off, in_refid, in_strand, in_exon_off, in_exon_st, in_exon_en, in_cigar_off, in_cigar, in_mate, in_seq_off, in_seq;
   uint64_t in_bytes = 0, n_mates = 0, seq_bytes = 0, rescue_bytes = 0;
-  bool have_batch = false, have_result = false;
-  // intermediates
-  Buf q_lo, q_hi, t_ncand, t_coff, scan_tmp, counters;
-  Buf c_rec, c_task, c_first, c_last, c_nseg, c_nguide, c_cap, c_ioff, ipool;
-  Buf r_left, r_right, rpool, r_prob;
-  Buf m_valid, m_tid, m_pos, m_sim, m_clip, m_ilen, c_partner;
+  bool have_batch = false, have_result = false, have_scores = false;
+  // control block + pools (capacities persist across calls and only grow)
+  Buf ctl;
+  uint32_t cap_cand = 0, cap_ideal = 0, cap_rows = 0, cap_tmpw = 0, cap_outw = 0;
+  Buf q_any, a_cand, a_cnt, scan_tmp;
+  Buf c_rec, c_task, c_first, c_last, c_nseg, c_nguide, c_cap, ipool;
+  Buf r_left, r_right, rpool;
+  Buf m_tid, m_pos, m_sim, m_clip, m_ilen, m_ioff, c_partner;
   Buf u_nrows, u_roff, u_case, g_roff;
-  Buf o_src, o_tid, o_pos, o_strand, o_flags, o_sim, o_clip, o_cand, o_ccap, o_coff, o_clen, opool;
+  Buf o_src, o_tid, o_pos, o_strand, o_flags, o_sim, o_clip, o_cand, o_tmpoff, o_clen, o_coff, tpool, opool;
   HBuf h_small, h_out;
-  uint32_t n_cand = 0, n_rec = 0; uint64_t n_ideal_words = 0, n_out_words = 0;
+  RescueBufs* rb = nullptr;
+  uint32_t n_cand = 0, n_rec = 0; uint64_t n_out_words = 0;
   brb_stats stats{};
+  std::vector<Buf*> all() {
+    return {&in_group_off, &in_refid, &in_strand, &in_exon_off, &in_exon_st, &in_exon_en, &in_cigar_off, &in_cigar, &in_mate, &in_seq_off,
+            &in_seq, &ctl, &q_any, &a_cand, &a_cnt, &scan_tmp, &c_rec, &c_task, &c_first, &c_last, &c_nseg, &c_nguide, &c_cap, &ipool,
+            &r_left, &r_right, &rpool, &m_tid, &m_pos, &m_sim, &m_clip, &m_ilen, &m_ioff, &c_partner, &u_nrows, &u_roff, &u_case, &g_roff,
+            &o_src, &o_tid, &o_pos, &o_strand, &o_flags, &o_sim, &o_clip, &o_cand, &o_tmpoff, &o_clen, &o_coff, &tpool, &opool};
+  }
 };
 
 extern "C" {
@@ -99,7 +114,7 @@ int brb_device_count(void) {
   return n;
 }
 const char* brb_last_error(void) { return g_err.c_str(); }
-const char* brb_version(void) { return "bramble_b200 0.1 (sm_100a)"; }
+const char* brb_version(void) { return "bramble_b200 0.2 (sm_100a)"; }
 
 int brb_host_alloc(size_t bytes, void** out) {
   if (!out) return fail(BRB_E_ARG, "brb_host_alloc: null out");
@@ -110,6 +125,11 @@ int brb_host_alloc(size_t bytes, void** out) {
 int brb_host_free(void* p) { if (p) cudaFreeHost(p); return BRB_OK; }
 
 // ---- index: the g2t tree of the reference (src/bramble.cpp:132-211, src/g2t.cpp:34-62), flattened.
+// Besides the reference's own columns the device records carry the exon chain of every transcript in
+// genomic order (gprev/gnext) and each table gets a coarse bin directory.  Both are derived here; the
+// derivation doubles as validation of what the reference's GTF loader guarantees (gclib/gff.cpp:988-1075:
+// exons of a transcript are merged when they overlap or touch, hence disjoint and ascending) and of the
+// neighbour columns (src/bramble.cpp:161-199).
 int brb_index_create(int device, const brb_index_desc* d, brb_index** out) {
   if (!d || !out) return fail(BRB_E_ARG, "brb_index_create: null argument");
   if (brb_device_count() <= device || device < 0) return fail(BRB_E_NO_DEVICE, "no CUDA device %d", device);
@@ -119,28 +139,82 @@ int brb_index_create(int device, const brb_index_desc* d, brb_index** out) {
   if (n >= 0xfffffff0ull) return fail(BRB_E_ARG, "too many index records");
   if (n && (!d->st || !d->en || !d->tid || !d->exon_id || !d->pos_start || !d->prev_st || !d->prev_en || !d->next_st ||
             !d->next_en || !d->has_prev_next || !d->transcript_len)) return fail(BRB_E_ARG, "null index column");
-  CU(cudaSetDevice(device));
-  brb_index* ix = new brb_index(); ix->device = device;
   std::vector<uint32_t> toff(d->n_tables + 1, 0);
   std::vector<int32_t> pmax(n);
   std::vector<Rec> rec(n);
+  std::vector<uint32_t> gprev(n, NONE);
+  uint64_t span = 0;
   for (uint32_t t = 0; t < d->n_tables; t++) {
     toff[t] = (uint32_t)d->table_off[t];
-    if (d->table_off[t + 1] < d->table_off[t]) { delete ix; return fail(BRB_E_ARG, "table_off not monotone"); }
+    if (d->table_off[t + 1] < d->table_off[t]) return fail(BRB_E_ARG, "table_off not monotone");
     int32_t m = INT32_MIN, prev = INT32_MIN;
     for (uint64_t i = d->table_off[t]; i < d->table_off[t + 1]; i++) {
-      if (d->st[i] < prev) { delete ix; return fail(BRB_E_ARG, "table %u is not sorted by start", t); }
+      if (d->st[i] < prev) return fail(BRB_E_ARG, "table %u is not sorted by start", t);
+      if (d->st[i] < 0 || d->en[i] <= d->st[i]) return fail(BRB_E_ARG, "record %llu: empty or negative interval", (unsigned long long)i);
       prev = d->st[i];
       m = std::max(m, d->en[i]); pmax[i] = m;
       Rec& r = rec[i];
       r.st = d->st[i]; r.en = d->en[i]; r.tid = d->tid[i]; r.pos_start = d->pos_start[i];
-      r.prev_st = d->prev_st[i]; r.prev_en = d->prev_en[i]; r.next_st = d->next_st[i]; r.next_en = d->next_en[i];
-      r.tlen = d->transcript_len[i];
+      r.gprev_en = 0; r.gnext_st = INT32_MAX; r.gnext = NONE;
       r.meta = (uint32_t)d->exon_id[i] | ((uint32_t)(d->has_prev_next[i] & 1) << 8) | ((uint32_t)((d->has_prev_next[i] >> 1) & 1) << 9);
-      r.pad0 = r.pad1 = 0;
     }
+    if (d->table_off[t + 1] > d->table_off[t]) span += (uint64_t)m;
   }
   toff[d->n_tables] = (uint32_t)n;
+  // exon chains: records of a table grouped by tid, ascending start
+  {
+    std::vector<uint32_t> ord;
+    for (uint32_t t = 0; t < d->n_tables; t++) {
+      const uint32_t b = toff[t], e = toff[t + 1];
+      const bool minus = t & 1;
+      ord.resize(e - b);
+      for (uint32_t i = b; i < e; i++) ord[i - b] = i;
+      std::sort(ord.begin(), ord.end(), [&](uint32_t x, uint32_t y) { return d->tid[x] != d->tid[y] ? d->tid[x] < d->tid[y] : (d->st[x] != d->st[y] ? d->st[x] < d->st[y] : x < y); });
+      for (size_t k = 0; k < ord.size(); k++) {
+        const uint32_t i = ord[k];
+        const bool has_p = k > 0 && d->tid[ord[k - 1]] == d->tid[i], has_n = k + 1 < ord.size() && d->tid[ord[k + 1]] == d->tid[i];
+        if (has_p) {
+          const uint32_t q = ord[k - 1];
+          if (d->en[q] > d->st[i]) return fail(BRB_E_UNSUPPORTED, "transcript %u has overlapping exons (records %u, %u); the reference's GTF loader merges those (gclib/gff.cpp:988)", d->tid[i], q, i);
+          gprev[i] = q; rec[i].gprev_en = d->en[q];
+        }
+        if (has_n) { const uint32_t q = ord[k + 1]; rec[i].gnext = q; rec[i].gnext_st = d->st[q]; }
+        // neighbour columns are in TRANSCRIPT order: '+' prev = genomic prev, '-' prev = genomic next
+        const bool hp = d->has_prev_next[i] & 1, hn = (d->has_prev_next[i] >> 1) & 1;
+        const bool g_has_p = minus ? hn : hp, g_has_n = minus ? hp : hn;
+        const uint32_t gp_st = minus ? d->next_st[i] : d->prev_st[i], gp_en = minus ? d->next_en[i] : d->prev_en[i];
+        const uint32_t gn_st = minus ? d->prev_st[i] : d->next_st[i], gn_en = minus ? d->prev_en[i] : d->next_en[i];
+        bool okc = g_has_p == has_p && g_has_n == has_n;
+        if (okc && has_p) okc = gp_st == (uint32_t)d->st[ord[k - 1]] && gp_en == (uint32_t)d->en[ord[k - 1]];
+        if (okc && !has_p) okc = gp_st == 0 && gp_en == 0;
+        if (okc && has_n) okc = gn_st == (uint32_t)d->st[ord[k + 1]] && gn_en == (uint32_t)d->en[ord[k + 1]];
+        if (okc && !has_n) okc = gn_st == 0 && gn_en == 0;
+        if (!okc) return fail(BRB_E_ARG, "record %u: prev/next columns do not describe the neighbouring exons of transcript %u", i, d->tid[i]);
+      }
+    }
+  }
+  // bin directory: 2^shift bases per bin, about two bins per record overall
+  uint32_t shift = 4;
+  { const uint64_t target = std::max<uint64_t>(2 * n, 1024); while (shift < 24 && (span >> shift) > target) shift++; }
+  if (const char* e = getenv("BRB_BIN_SHIFT")) { int v = atoi(e); if (v >= 2 && v <= 28) shift = (uint32_t)v; }
+  std::vector<uint32_t> boff(d->n_tables + 1, 0);
+  for (uint32_t t = 0; t < d->n_tables; t++) {
+    const uint32_t b = toff[t], e = toff[t + 1];
+    boff[t + 1] = boff[t] + (e > b ? ((uint32_t)pmax[e - 1] >> shift) + 2 : 0);
+  }
+  std::vector<uint2> bins(boff[d->n_tables]);
+  for (uint32_t t = 0; t < d->n_tables; t++) {
+    const uint32_t b = toff[t], e = toff[t + 1], nb = boff[t + 1] - boff[t];
+    uint32_t il = b, ih = b;
+    for (uint32_t k = 0; k < nb; k++) {
+      const int64_t x = (int64_t)k << shift;
+      while (il < e && (int64_t)pmax[il] <= x) il++;
+      while (ih < e && (int64_t)d->st[ih] < x) ih++;
+      bins[boff[t] + k] = make_uint2(il, ih);
+    }
+  }
+  CU(cudaSetDevice(device));
+  brb_index* ix = new brb_index(); ix->device = device;
   int rc = 0;
   auto up = [&](Buf& b, const void* src, size_t bytes) -> int {
     int r = b.ensure(bytes ? bytes : 16); if (r) return r;
@@ -151,15 +225,19 @@ int brb_index_create(int device, const brb_index_desc* d, brb_index** out) {
   if (!rc) rc = up(ix->st, d->st, n * 4);
   if (!rc) rc = up(ix->pmax, pmax.data(), n * 4);
   if (!rc) rc = up(ix->rec, rec.data(), n * sizeof(Rec));
-  ix->d.n_tables = d->n_tables; ix->d.n_rec = n; ix->d.n_chrom = 0;
+  if (!rc) rc = up(ix->gprev, gprev.data(), n * 4);
+  if (!rc) rc = up(ix->bin_off, boff.data(), boff.size() * 4);
+  if (!rc) rc = up(ix->bins, bins.data(), bins.size() * sizeof(uint2));
+  ix->d.n_tables = d->n_tables; ix->d.n_rec = n; ix->d.n_chrom = 0; ix->d.bin_shift = shift;
   if (!rc && d->genome_codes && d->chrom_off && d->n_chrom) {
     rc = up(ix->chrom_off, d->chrom_off, (size_t)(d->n_chrom + 1) * 8);
     if (!rc) rc = up(ix->genome, d->genome_codes, d->chrom_off[d->n_chrom]);
     ix->d.n_chrom = d->n_chrom;
   }
-  if (rc) { ix->table_off.release(); ix->st.release(); ix->pmax.release(); ix->rec.release(); ix->chrom_off.release(); ix->genome.release(); delete ix; return rc; }
+  if (rc) { ix->release_all(); delete ix; return rc; }
   ix->d.table_off = ix->table_off.as<uint32_t>(); ix->d.st = ix->st.as<int32_t>(); ix->d.pmax = ix->pmax.as<int32_t>();
-  ix->d.rec = ix->rec.as<Rec>();
+  ix->d.rec = ix->rec.as<Rec>(); ix->d.gprev = ix->gprev.as<uint32_t>();
+  ix->d.bin_off = ix->bin_off.as<uint32_t>(); ix->d.bins = ix->bins.as<uint2>();
   ix->d.chrom_off = ix->d.n_chrom ? ix->chrom_off.as<uint64_t>() : nullptr;
   ix->d.genome = ix->d.n_chrom ? ix->genome.as<uint8_t>() : nullptr;
   *out = ix;
@@ -169,7 +247,7 @@ int brb_index_create(int device, const brb_index_desc* d, brb_index** out) {
 int brb_index_destroy(brb_index* ix) {
   if (!ix) return BRB_OK;
   cudaSetDevice(ix->device);
-  ix->table_off.release(); ix->st.release(); ix->pmax.release(); ix->rec.release(); ix->chrom_off.release(); ix->genome.release();
+  ix->release_all();
   delete ix;
   return BRB_OK;
 }
@@ -181,7 +259,7 @@ int brb_ctx_create(brb_index* ix, brb_ctx** out) {
   CU(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));
   for (auto& e : c->ev) CU(cudaEventCreate(&e));
   for (auto& e : c->tev) CU(cudaEventCreate(&e));
-  ENS(c->counters, 64); ENS(c->h_small, 256);
+  ENS(c->ctl, sizeof(Ctl)); ENS(c->h_small, 256);
   *out = c;
   return BRB_OK;
 }
@@ -190,13 +268,8 @@ int brb_ctx_destroy(brb_ctx* c) {
   if (!c) return BRB_OK;
   cudaSetDevice(c->idx->device);
   cudaStreamSynchronize(c->st);
-  Buf* all[] = {&c->in_group_off, &c->in_refid, &c->in_strand, &c->in_exon_off, &c->in_exon_st, &c->in_exon_en, &c->in_cigar_off,
-                &c->in_cigar, &c->in_mate, &c->in_seq_off, &c->in_seq, &c->q_lo, &c->q_hi, &c->t_ncand, &c->t_coff, &c->scan_tmp,
-                &c->counters, &c->c_rec, &c->c_task, &c->c_first, &c->c_last, &c->c_nseg, &c->c_nguide, &c->c_cap, &c->c_ioff,
-                &c->ipool, &c->r_left, &c->r_right, &c->rpool, &c->r_prob, &c->m_valid, &c->m_tid, &c->m_pos, &c->m_sim, &c->m_clip,
-                &c->m_ilen, &c->c_partner, &c->u_nrows, &c->u_roff, &c->u_case, &c->g_roff, &c->o_src, &c->o_tid, &c->o_pos,
-                &c->o_strand, &c->o_flags, &c->o_sim, &c->o_clip, &c->o_cand, &c->o_ccap, &c->o_coff, &c->o_clen, &c->opool};
-  for (Buf* b : all) b->release();
+  for (Buf* b : c->all()) b->release();
+  free_rescue_bufs(c);
   c->h_small.release(); c->h_out.release();
   for (auto& e : c->ev) if (e) cudaEventDestroy(e);
   for (auto& e : c->tev) if (e) cudaEventDestroy(e);
@@ -205,7 +278,8 @@ int brb_ctx_destroy(brb_ctx* c) {
   return BRB_OK;
 }
 
-// ---- batch upload: one bundle (reference BundleData::reads) as structure-of-arrays.
+// ---- batch upload: one bundle (reference BundleData::reads) as structure-of-arrays.  Content checks that
+// need a pass over the data (symmetric mate links, ascending read exons) run on the device inside k_lookup.
 int brb_batch_upload(brb_ctx* c, const brb_batch_in* in) {
   if (!c || !in) return fail(BRB_E_ARG, "brb_batch_upload: null argument");
   CU(cudaSetDevice(c->idx->device));
@@ -217,13 +291,6 @@ int brb_batch_upload(brb_ctx* c, const brb_batch_in* in) {
   const uint32_t n_exon = n ? in->exon_off[n] : 0, n_cigar = n ? in->cigar_off[n] : 0;
   if (n && (in->group_off[0] != 0 || in->group_off[ng] != n || in->exon_off[0] != 0 || in->cigar_off[0] != 0))
     return fail(BRB_E_ARG, "inconsistent CSR offsets");
-  uint64_t n_mates = 0;
-  for (uint32_t a = 0; a < n; a++) {        // process_pairs links are single and symmetric (src/bramble.cpp:272-311)
-    const int32_t m = in->mate_idx[a];
-    if (m < 0) continue;
-    if ((uint32_t)m >= n || (uint32_t)m == a || in->mate_idx[m] != (int32_t)a) return fail(BRB_E_ARG, "mate_idx[%u]=%d is not a symmetric link", a, m);
-    n_mates++;
-  }
   c->in_bytes = 0;
   auto up = [&](Buf& b, const void* src, size_t bytes) -> int {
     int r = b.ensure(bytes ? bytes : 16); if (r) return r;
@@ -256,7 +323,6 @@ int brb_batch_upload(brb_ctx* c, const brb_batch_in* in) {
   b.cigar_off = c->in_cigar_off.as<uint32_t>(); b.cigar = c->in_cigar.as<uint32_t>(); b.mate_idx = c->in_mate.as<int32_t>();
   b.group_seq_off = have_seq ? c->in_seq_off.as<uint64_t>() : nullptr; b.seq = have_seq ? c->in_seq.as<uint8_t>() : nullptr;
   b.aln_group = nullptr;
-  c->n_mates = n_mates;
   c->stats.h2d_bytes = c->in_bytes;
   c->have_batch = true;
   return BRB_OK;
@@ -266,17 +332,29 @@ int brb_batch_upload(brb_ctx* c, const brb_batch_in* in) {
 
 namespace {
 
-int run_rescue(brb_ctx* c, const brb_params& p);   // k_ksw host driver, below
-
-// read back `n` uint32 values at device pointer `src` (synchronises the stream)
-int read_u32(brb_ctx* c, const uint32_t* src, uint32_t* dst, size_t n) {
-  CU(cudaMemcpyAsync(c->h_small.p, src, n * 4, cudaMemcpyDeviceToHost, c->st));
-  CU(cudaStreamSynchronize(c->st));
-  memcpy(dst, c->h_small.p, n * 4);
-  return 0;
-}
+int run_rescue(brb_ctx* c, const brb_params& p);   // k_ksw host driver, rescue_host.inl
 
 float ms_between(cudaEvent_t a, cudaEvent_t b) { float ms = 0; cudaEventElapsedTime(&ms, a, b); return ms; }
+
+uint32_t grown(uint64_t need) { const uint64_t w = need + need / 4 + 4096; return (uint32_t)std::min<uint64_t>(w, 0xfffffff0ull); }
+
+// Sizes every pool for the current capacities (Buf::ensure keeps what is already large enough).
+int ensure_pools(brb_ctx* c, bool rescue) {
+  const DevBatch& b = c->b;
+  const size_t n = b.n_aln, C = c->cap_cand, R = c->cap_rows;
+  ENS(c->q_any, (size_t)2 * b.n_exon + 16); ENS(c->a_cand, n * 16); ENS(c->a_cnt, n * 8);
+  ENS(c->u_nrows, n * 4); ENS(c->u_roff, (n + 1) * 4); ENS(c->u_case, n); ENS(c->g_roff, (size_t)(b.n_groups + 1) * 4);
+  ENS(c->c_rec, C * 4); ENS(c->c_task, C * 4); ENS(c->c_partner, C * 4);
+  ENS(c->m_tid, C * 4); ENS(c->m_pos, C * 4); ENS(c->m_sim, C * 8); ENS(c->m_clip, C * 4); ENS(c->m_ilen, C * 4); ENS(c->m_ioff, C * 4);
+  if (rescue) { ENS(c->c_first, C * 4); ENS(c->c_last, C * 4); ENS(c->c_nseg, C * 4); ENS(c->c_nguide, C * 4); ENS(c->c_cap, C * 4); }
+  ENS(c->ipool, (size_t)c->cap_ideal * 4);
+  ENS(c->o_src, R * 4); ENS(c->o_tid, R * 4); ENS(c->o_pos, R * 4); ENS(c->o_strand, R); ENS(c->o_flags, R); ENS(c->o_cand, R * 4);
+  ENS(c->o_sim, R * 8); ENS(c->o_clip, R * 4);
+  ENS(c->o_tmpoff, R * 4); ENS(c->o_clen, R * 4); ENS(c->o_coff, (R + 1) * 4);
+  ENS(c->tpool, (size_t)c->cap_tmpw * 4); ENS(c->opool, (size_t)c->cap_outw * 4);
+  ENS(c->scan_tmp, scan_scratch_words(std::max<size_t>(std::max<size_t>(n, R), 1)) * 4);
+  return 0;
+}
 
 int project_resident(brb_ctx* c, const brb_params& p) {
   if (!c->have_batch) return fail(BRB_E_ARG, "no batch resident: call brb_batch_upload first");
@@ -286,115 +364,101 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   const DevBatch& b = c->b; const DevIndex& ix = c->idx->d;
   cudaStream_t st = c->st;
   brb_stats& S = c->stats;
-  uint64_t L = 0;
-  const uint32_t n = b.n_aln, n_task = 2 * n;
-  c->have_result = false; c->rescue_bytes = 0; c->n_cand = 0; c->n_rec = 0; c->n_out_words = 0; c->n_ideal_words = 0;
-  S.n_candidates = S.n_matches = S.n_rescue = S.n_rec = 0;
+  const uint32_t n = b.n_aln;
+  c->have_result = false; c->rescue_bytes = 0; c->n_cand = 0; c->n_rec = 0; c->n_out_words = 0;
+  c->have_scores = p.filter_by_similarity || rescue;     // otherwise similarity_score and clip_score are 0 for every record
+  S.n_candidates = S.n_matches = S.n_rescue = S.n_rec = 0; S.n_launches = 0; S.alg_bytes = 0;
   S.ms_lookup = S.ms_chain = S.ms_rescue = S.ms_finalize = S.ms_pair = S.ms_merge = 0; S.kernel_ms = 0;
-  ENS(c->g_roff, (size_t)(b.n_groups + 1) * 4);
   if (n == 0) {
-    CU(cudaMemsetAsync(c->g_roff.p, 0, 4, st)); CU(cudaStreamSynchronize(st));
-    S.n_launches = 0; S.alg_bytes = 0; c->have_result = true; return BRB_OK;
+    ENS(c->g_roff, (size_t)(b.n_groups + 1) * 4); ENS(c->o_coff, 4);
+    CU(cudaMemsetAsync(c->g_roff.p, 0, 4, st)); CU(cudaMemsetAsync(c->o_coff.p, 0, 4, st)); CU(cudaStreamSynchronize(st));
+    c->have_result = true; return BRB_OK;
   }
-  unsigned long long* counters = c->counters.as<unsigned long long>();   // [0] n_hits [1] out cigar words [2] rescue bytes
-  CU(cudaMemsetAsync(counters, 0, 64, st));
-  ENS(c->q_lo, (size_t)2 * b.n_exon * 4 + 16); ENS(c->q_hi, (size_t)2 * b.n_exon * 4 + 16);
-  ENS(c->t_ncand, (size_t)n_task * 4); ENS(c->t_coff, (size_t)(n_task + 1) * 4);
-  ENS(c->u_nrows, (size_t)n * 4); ENS(c->u_roff, (size_t)(n + 1) * 4); ENS(c->u_case, n);
-  ENS(c->scan_tmp, scan_scratch_words(std::max<size_t>(n_task, 1)) * 4);
-
-  // ---- phase 1: lookup
-  CU(cudaEventRecord(c->ev[0], st));
-  k_lookup<<<grid_for(n_task, 256), 256, 0, st>>>(ix, b, p, c->q_lo.as<uint32_t>(), c->q_hi.as<uint32_t>(), c->t_ncand.as<uint32_t>(), counters); L++;
-  exclusive_scan(c->t_ncand.as<uint32_t>(), c->t_coff.as<uint32_t>(), n_task, c->scan_tmp.as<uint32_t>(), st, &L);
-  uint32_t C = 0;
-  { int r = read_u32(c, c->t_coff.as<uint32_t>() + n_task, &C, 1); if (r) return r; }
-  c->n_cand = C; S.n_candidates = C;
-  const size_t Cz = std::max<uint32_t>(C, 1);
-  ENS(c->c_rec, Cz * 4); ENS(c->c_task, Cz * 4); ENS(c->c_first, Cz * 4); ENS(c->c_last, Cz * 4); ENS(c->c_nseg, Cz * 4);
-  ENS(c->c_nguide, Cz * 4); ENS(c->c_cap, Cz * 4); ENS(c->c_ioff, (Cz + 1) * 4);
-  ENS(c->m_valid, Cz); ENS(c->m_tid, Cz * 4); ENS(c->m_pos, Cz * 4); ENS(c->m_sim, Cz * 8); ENS(c->m_clip, Cz * 4); ENS(c->m_ilen, Cz * 4);
-  ENS(c->c_partner, Cz * 4);
-  ENS(c->scan_tmp, scan_scratch_words(std::max<size_t>(std::max<size_t>(n_task, Cz), 1)) * 4);
-  if (C) { k_fill_cand<<<grid_for(n_task, 256), 256, 0, st>>>(ix, b, p, c->q_lo.as<uint32_t>(), c->q_hi.as<uint32_t>(), c->t_coff.as<uint32_t>(),
-                                                              c->c_rec.as<uint32_t>(), c->c_task.as<uint32_t>()); L++; }
-  CU(cudaEventRecord(c->ev[1], st));
-
-  // ---- phase 2: chain walk, pass 1
-  uint32_t I = 0;
-  if (C) {
-    k_chain<<<grid_for(C, 256), 256, 0, st>>>(ix, b, p, C, c->q_lo.as<uint32_t>(), c->q_hi.as<uint32_t>(), c->c_rec.as<uint32_t>(),
-                                              c->c_task.as<uint32_t>(), c->c_first.as<uint32_t>(), c->c_last.as<uint32_t>(),
-                                              c->c_nseg.as<uint32_t>(), c->c_nguide.as<uint32_t>(), c->c_cap.as<uint32_t>()); L++;
+  if (!c->cap_cand) {           // first guess from the batch shape; a pool that overflows grows and the sequence replays
+    c->cap_cand = grown((uint64_t)8 * n); c->cap_rows = grown((uint64_t)6 * n);
+    c->cap_ideal = grown((uint64_t)4 * c->cap_cand + b.n_exon); c->cap_tmpw = grown((uint64_t)8 * c->cap_rows + 2 * (uint64_t)b.n_cigar);
+    c->cap_outw = grown((uint64_t)3 * c->cap_rows + b.n_cigar);
+    if (getenv("BRB_TEST_SMALL_POOLS")) c->cap_cand = c->cap_rows = c->cap_ideal = c->cap_tmpw = c->cap_outw = 64;   // tests: force the grow-and-replay path
   }
-  CU(cudaEventRecord(c->ev[2], st));
-
-  // ---- phase 3: long-read clip rescue (ksw2), adds its CIGAR lengths to c_cap
-  if (C && rescue) { S.n_launches = L; int r = run_rescue(c, p); if (r) return r; L = S.n_launches; }
-  CU(cudaEventRecord(c->ev[3], st));
-
-  // ---- phase 4: pass 2 (ideal CIGAR, scores, similarity filter)
-  if (C) {
-    exclusive_scan(c->c_cap.as<uint32_t>(), c->c_ioff.as<uint32_t>(), C, c->scan_tmp.as<uint32_t>(), st, &L);
-    { int r = read_u32(c, c->c_ioff.as<uint32_t>() + C, &I, 1); if (r) return r; }
-    c->n_ideal_words = I;
-    ENS(c->ipool, (size_t)std::max<uint32_t>(I, 1) * 4);
-    k_build<<<grid_for(C, 256), 256, 0, st>>>(ix, b, p, C, c->q_lo.as<uint32_t>(), c->q_hi.as<uint32_t>(), c->c_task.as<uint32_t>(),
-                                              c->c_first.as<uint32_t>(), c->c_last.as<uint32_t>(), c->c_nseg.as<uint32_t>(),
-                                              c->c_nguide.as<uint32_t>(), c->c_cap.as<uint32_t>(), c->c_ioff.as<uint32_t>(),
-                                              rescue ? c->r_left.as<RescueSeg>() : nullptr, rescue ? c->r_right.as<RescueSeg>() : nullptr,
-                                              rescue ? c->rpool.as<uint32_t>() : nullptr, c->ipool.as<uint32_t>(),
-                                              c->m_valid.as<uint8_t>(), c->m_tid.as<uint32_t>(), c->m_pos.as<uint32_t>(),
-                                              c->m_sim.as<double>(), c->m_clip.as<int32_t>(), c->m_ilen.as<uint32_t>(), counters + 3); L++;
-  }
-  CU(cudaEventRecord(c->ev[4], st));
-
-  // ---- phase 5: pairing + emission
-  PairView pv; pv.t_coff = c->t_coff.as<uint32_t>(); pv.m_valid = c->m_valid.as<uint8_t>(); pv.m_tid = c->m_tid.as<uint32_t>();
-  k_pair_count<<<grid_for(n, 256), 256, 0, st>>>(b, pv, c->c_partner.as<uint32_t>(), c->u_nrows.as<uint32_t>(), c->u_case.as<uint8_t>()); L++;
-  exclusive_scan(c->u_nrows.as<uint32_t>(), c->u_roff.as<uint32_t>(), n, c->scan_tmp.as<uint32_t>(), st, &L);
-  uint32_t R = 0;
-  { int r = read_u32(c, c->u_roff.as<uint32_t>() + n, &R, 1); if (r) return r; }
-  c->n_rec = R; S.n_rec = R;
-  const size_t Rz = std::max<uint32_t>(R, 1);
-  ENS(c->o_src, Rz * 4); ENS(c->o_tid, Rz * 4); ENS(c->o_pos, Rz * 4); ENS(c->o_strand, Rz); ENS(c->o_flags, Rz); ENS(c->o_sim, Rz * 8);
-  ENS(c->o_clip, Rz * 4); ENS(c->o_cand, Rz * 4); ENS(c->o_ccap, Rz * 4); ENS(c->o_coff, (Rz + 1) * 4); ENS(c->o_clen, Rz * 4);
-  ENS(c->scan_tmp, scan_scratch_words(std::max<size_t>(std::max<size_t>(n_task, Cz), Rz)) * 4);
-  k_group_rows<<<grid_for(b.n_groups + 1, 256), 256, 0, st>>>(b, c->u_roff.as<uint32_t>(), c->g_roff.as<uint32_t>()); L++;
-  uint32_t W = 0;
-  if (R) {
+  int ncta = 148 * 8;
+  { int sm = 0; if (cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, c->idx->device) == cudaSuccess && sm > 0) ncta = sm * 8; }
+  Ctl* ctl = c->ctl.as<Ctl>();
+  Ctl* hctl = c->h_small.as<Ctl>();
+  uint64_t L = 0;
+  for (int attempt = 0;; attempt++) {
+    if (attempt > 12) return fail(BRB_E_NOMEM, "pool sizing did not converge");
+    { int r = ensure_pools(c, rescue); if (r) return r; }
+    memset(hctl, 0, sizeof(Ctl));
+    hctl->cap_cand = c->cap_cand; hctl->cap_ideal = c->cap_ideal; hctl->cap_rows = c->cap_rows; hctl->cap_tmpw = c->cap_tmpw; hctl->cap_outw = c->cap_outw;
+    CU(cudaMemcpyAsync(ctl, hctl, sizeof(Ctl), cudaMemcpyHostToDevice, st));
+    CU(cudaMemsetAsync(c->a_cnt.p, 0, (size_t)n * 8, st));
+    Matches M; M.tid = c->m_tid.as<uint32_t>(); M.pos = c->m_pos.as<uint32_t>(); M.sim = c->m_sim.as<double>(); M.clip = c->m_clip.as<int32_t>();
+    M.ilen = c->m_ilen.as<uint32_t>(); M.ioff = c->m_ioff.as<uint32_t>();
+    // ---- phase 1: lookup + candidate lists
+    CU(cudaEventRecord(c->ev[0], st));
+    k_lookup<<<grid_for(n, 256), 256, 0, st>>>(ix, b, p, ctl, c->q_any.as<uint8_t>(), c->a_cand.as<uint4>(), c->c_rec.as<uint32_t>(), c->c_task.as<uint32_t>()); L++;
+    CU(cudaEventRecord(c->ev[1], st));
+    // ---- phase 2..4: chain walk, (clip rescue), ideal CIGAR + scores
+    if (!rescue) {
+      k_eval<<<ncta, 256, 0, st>>>(ix, b, p, ctl, c->q_any.as<uint8_t>(), c->c_rec.as<uint32_t>(), c->c_task.as<uint32_t>(), c->ipool.as<uint32_t>(), M); L++;
+      CU(cudaEventRecord(c->ev[2], st)); CU(cudaEventRecord(c->ev[3], st)); CU(cudaEventRecord(c->ev[4], st));
+    } else {
+      CandFacts F; F.first = c->c_first.as<uint32_t>(); F.last = c->c_last.as<uint32_t>(); F.nseg = c->c_nseg.as<uint32_t>();
+      F.nguide = c->c_nguide.as<uint32_t>(); F.cap = c->c_cap.as<uint32_t>();
+      k_chain<<<ncta, 256, 0, st>>>(ix, b, p, ctl, c->q_any.as<uint8_t>(), c->c_rec.as<uint32_t>(), c->c_task.as<uint32_t>(), F); L++;
+      CU(cudaEventRecord(c->ev[2], st));
+      CU(cudaMemcpyAsync(hctl, ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, st));
+      CU(cudaStreamSynchronize(st));
+      if (hctl->bad_input) break;
+      if (hctl->n_cand > c->cap_cand) { c->cap_cand = grown(hctl->n_cand); c->cap_ideal = std::max(c->cap_ideal, grown((uint64_t)4 * c->cap_cand)); continue; }
+      c->n_cand = hctl->n_cand;
+      if (c->n_cand) { S.n_launches = L; int r = run_rescue(c, p); if (r) return r; L = S.n_launches; }
+      CU(cudaEventRecord(c->ev[3], st));
+      k_build<<<ncta, 256, 0, st>>>(ix, b, p, ctl, c->q_any.as<uint8_t>(), c->c_task.as<uint32_t>(), F, c->r_left.as<RescueSeg>(),
+                                    c->r_right.as<RescueSeg>(), c->rpool.as<uint32_t>(), c->ipool.as<uint32_t>(), M); L++;
+      CU(cudaEventRecord(c->ev[4], st));
+    }
+    // ---- phase 5: pairing + emission
+    PairView pv; pv.a_cand = c->a_cand.as<uint4>(); pv.c_task = c->c_task.as<uint32_t>(); pv.m_tid = c->m_tid.as<uint32_t>();
+    k_partner<<<ncta, 256, 0, st>>>(b, ctl, pv, c->c_partner.as<uint32_t>(), c->a_cnt.as<uint2>()); L++;
+    k_pair_count<<<grid_for(n, 256), 256, 0, st>>>(b, ctl, pv, c->a_cnt.as<uint2>(), c->c_partner.as<uint32_t>(), c->u_nrows.as<uint32_t>(), c->u_case.as<uint8_t>()); L++;
+    exclusive_scan(c->u_nrows.as<uint32_t>(), c->u_roff.as<uint32_t>(), n, c->scan_tmp.as<uint32_t>(), st, &L);
+    k_group_rows<<<grid_for(b.n_groups + 1, 256), 256, 0, st>>>(b, c->u_roff.as<uint32_t>(), c->g_roff.as<uint32_t>()); L++;
     Rows o; o.src = c->o_src.as<uint32_t>(); o.tid = c->o_tid.as<uint32_t>(); o.pos = c->o_pos.as<uint32_t>(); o.strand = c->o_strand.as<int8_t>();
     o.flags = c->o_flags.as<uint8_t>(); o.sim = c->o_sim.as<double>(); o.clip = c->o_clip.as<int32_t>(); o.cand = c->o_cand.as<uint32_t>();
-    o.ccap = c->o_ccap.as<uint32_t>();
-    k_pair_emit<<<grid_for(n, 256), 256, 0, st>>>(b, pv, c->c_partner.as<uint32_t>(), c->u_roff.as<uint32_t>(), c->u_case.as<uint8_t>(),
-                                                  c->c_task.as<uint32_t>(), c->m_pos.as<uint32_t>(), c->m_sim.as<double>(),
-                                                  c->m_clip.as<int32_t>(), c->m_ilen.as<uint32_t>(), o); L++;
-    exclusive_scan(c->o_ccap.as<uint32_t>(), c->o_coff.as<uint32_t>(), R, c->scan_tmp.as<uint32_t>(), st, &L);
-    { int r = read_u32(c, c->o_coff.as<uint32_t>() + R, &W, 1); if (r) return r; }
+    k_pair_emit<<<ncta, 256, 0, st>>>(b, ctl, pv, c->c_partner.as<uint32_t>(), c->u_roff.as<uint32_t>(), c->u_case.as<uint8_t>(),
+                                      c->m_pos.as<uint32_t>(), c->m_sim.as<double>(), c->m_clip.as<int32_t>(), c->have_scores ? 1 : 0, o); L++;
+    CU(cudaEventRecord(c->ev[5], st));
+    // ---- phase 6: CIGAR merge + dense row-ordered pool
+    k_merge<<<ncta, 256, 0, st>>>(b, ctl, c->o_src.as<uint32_t>(), c->o_cand.as<uint32_t>(), c->m_ioff.as<uint32_t>(), c->m_ilen.as<uint32_t>(),
+                                  c->ipool.as<uint32_t>(), c->o_tmpoff.as<uint32_t>(), c->o_clen.as<uint32_t>(), c->tpool.as<uint32_t>()); L++;
+    exclusive_scan(c->o_clen.as<uint32_t>(), c->o_coff.as<uint32_t>(), c->cap_rows, c->scan_tmp.as<uint32_t>(), st, &L, &ctl->n_rows);
+    k_compact<<<ncta, 256, 0, st>>>(ctl, c->o_strand.as<int8_t>(), c->o_tmpoff.as<uint32_t>(), c->o_coff.as<uint32_t>(), c->tpool.as<uint32_t>(),
+                                    c->opool.as<uint32_t>()); L++;
+    CU(cudaEventRecord(c->ev[6], st));
+    CU(cudaMemcpyAsync(hctl, ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    CU(cudaGetLastError());
+    if (hctl->bad_input) break;
+    bool again = false;
+    if (hctl->n_cand > c->cap_cand) { c->cap_cand = grown(hctl->n_cand); c->cap_ideal = std::max(c->cap_ideal, grown((uint64_t)4 * c->cap_cand)); again = true; }
+    else if (hctl->n_ideal > c->cap_ideal) { c->cap_ideal = grown(hctl->n_ideal); again = true; }
+    else if (hctl->n_rows > c->cap_rows) { c->cap_rows = grown(hctl->n_rows); c->cap_tmpw = std::max(c->cap_tmpw, grown((uint64_t)8 * c->cap_rows));
+                                           c->cap_outw = std::max(c->cap_outw, grown((uint64_t)3 * c->cap_rows)); again = true; }
+    else if (hctl->n_tmpw > c->cap_tmpw) { c->cap_tmpw = grown(hctl->n_tmpw); again = true; }
+    else if (hctl->n_outw > c->cap_outw) { c->cap_outw = grown(hctl->n_outw); again = true; }
+    if (!again) break;
   }
-  c->n_out_words = W;
-  CU(cudaEventRecord(c->ev[5], st));
-
-  // ---- phase 6: CIGAR merge
-  if (R) {
-    ENS(c->opool, (size_t)std::max<uint32_t>(W, 1) * 4);
-    k_merge<<<grid_for(R, 256), 256, 0, st>>>(b, R, c->o_src.as<uint32_t>(), c->o_cand.as<uint32_t>(), c->o_strand.as<int8_t>(),
-                                              c->o_coff.as<uint32_t>(), c->c_ioff.as<uint32_t>(), c->m_ilen.as<uint32_t>(),
-                                              c->ipool.as<uint32_t>(), c->o_clen.as<uint32_t>(), c->opool.as<uint32_t>(), counters + 1); L++;
-  }
-  CU(cudaEventRecord(c->ev[6], st));
-  CU(cudaMemcpyAsync(c->h_small.p, counters, 64, cudaMemcpyDeviceToHost, st));
-  CU(cudaStreamSynchronize(st));
-  CU(cudaGetLastError());
-  unsigned long long hc[8]; memcpy(hc, c->h_small.p, 64);
-  S.n_launches = L; S.n_matches = hc[3];
+  if (hctl->bad_input == 1) return fail(BRB_E_ARG, "mate_idx is not a symmetric single link (src/bramble.cpp:272-311)");
+  if (hctl->bad_input) return fail(BRB_E_ARG, "read exons of an alignment must be ascending and disjoint");
+  c->n_cand = hctl->n_cand; c->n_rec = hctl->n_rows; c->n_out_words = hctl->n_outw;
+  S.n_candidates = hctl->n_cand; S.n_rec = hctl->n_rows; S.n_launches = L; S.n_matches = hctl->n_matches; S.n_rescue = hctl->n_rescue;
   S.ms_lookup = ms_between(c->ev[0], c->ev[1]); S.ms_chain = ms_between(c->ev[1], c->ev[2]); S.ms_rescue = ms_between(c->ev[2], c->ev[3]);
   S.ms_finalize = ms_between(c->ev[3], c->ev[4]); S.ms_pair = ms_between(c->ev[4], c->ev[5]); S.ms_merge = ms_between(c->ev[5], c->ev[6]);
   S.kernel_ms = ms_between(c->ev[0], c->ev[6]);
   // algorithmic bytes, SURVEY.md 8(d) / DESIGN.md: per-alignment SoA + 56 B per index hit + output rows + rescue bases
-  S.alg_bytes = (uint64_t)n * 16 + (uint64_t)b.n_exon * 8 + (uint64_t)b.n_cigar * 4 + c->n_mates * 4 + hc[0] * 56 +
-                (uint64_t)R * 40 + hc[1] * 4 + c->rescue_bytes;
-  S.n_rescue = hc[4];
+  S.alg_bytes = (uint64_t)n * 16 + (uint64_t)b.n_exon * 8 + (uint64_t)b.n_cigar * 4 + hctl->n_mates * 4 + hctl->n_hits * 56 +
+                (uint64_t)hctl->n_rows * 40 + hctl->out_words * 4 + c->rescue_bytes;
   c->have_result = true;
   return BRB_OK;
 }
@@ -416,16 +480,16 @@ int brb_batch_download(brb_ctx* c, brb_batch_out* out) {
   if (!c->have_result) return fail(BRB_E_ARG, "no result resident: call brb_project_resident first");
   CU(cudaSetDevice(c->idx->device));
   const size_t R = c->n_rec, W = c->n_out_words, G = c->b.n_groups;
+  const bool sc = c->have_scores && R;
   auto al = [](size_t x) { return (x + 15) & ~(size_t)15; };
   size_t off = 0;
   const size_t o_groff = off; off += al((G + 1) * 4);
   const size_t o_src = off; off += al(R * 4);
   const size_t o_tid = off; off += al(R * 4);
   const size_t o_pos = off; off += al(R * 4);
-  const size_t o_sim = off; off += al(R * 8);
-  const size_t o_clip = off; off += al(R * 4);
-  const size_t o_coff = off; off += al(R * 4);
-  const size_t o_clen = off; off += al(R * 4);
+  const size_t o_sim = off; off += sc ? al(R * 8) : 0;
+  const size_t o_clip = off; off += sc ? al(R * 4) : 0;
+  const size_t o_coff = off; off += al((R + 1) * 4);
   const size_t o_strand = off; off += al(R);
   const size_t o_flags = off; off += al(R);
   const size_t o_cig = off; off += al(W * 4);
@@ -441,10 +505,9 @@ int brb_batch_download(brb_ctx* c, brb_batch_out* out) {
   if (!rc) rc = dn(o_src, c->o_src, R * 4);
   if (!rc) rc = dn(o_tid, c->o_tid, R * 4);
   if (!rc) rc = dn(o_pos, c->o_pos, R * 4);
-  if (!rc) rc = dn(o_sim, c->o_sim, R * 8);
-  if (!rc) rc = dn(o_clip, c->o_clip, R * 4);
-  if (!rc) rc = dn(o_coff, c->o_coff, R * 4);
-  if (!rc) rc = dn(o_clen, c->o_clen, R * 4);
+  if (!rc && sc) rc = dn(o_sim, c->o_sim, R * 8);
+  if (!rc && sc) rc = dn(o_clip, c->o_clip, R * 4);
+  if (!rc) rc = dn(o_coff, c->o_coff, (R + 1) * 4);
   if (!rc) rc = dn(o_strand, c->o_strand, R);
   if (!rc) rc = dn(o_flags, c->o_flags, R);
   if (!rc) rc = dn(o_cig, c->opool, W * 4);
@@ -453,8 +516,8 @@ int brb_batch_download(brb_ctx* c, brb_batch_out* out) {
   out->n_rec = (uint32_t)R; out->n_cigar_words = W;
   out->group_rec_off = (const uint32_t*)(h + o_groff); out->src_aln = (const uint32_t*)(h + o_src); out->tid = (const uint32_t*)(h + o_tid);
   out->pos = (const uint32_t*)(h + o_pos); out->tx_strand = (const int8_t*)(h + o_strand); out->flags = h + o_flags;
-  out->sim_score = (const double*)(h + o_sim); out->clip_score = (const int32_t*)(h + o_clip);
-  out->cigar_off = (const uint32_t*)(h + o_coff); out->cigar_len = (const uint32_t*)(h + o_clen); out->cigar = (const uint32_t*)(h + o_cig);
+  out->sim_score = sc ? (const double*)(h + o_sim) : nullptr; out->clip_score = sc ? (const int32_t*)(h + o_clip) : nullptr;
+  out->cigar_off = (const uint32_t*)(h + o_coff); out->cigar = (const uint32_t*)(h + o_cig);
   c->stats.d2h_bytes = bytes;
   return BRB_OK;
 }

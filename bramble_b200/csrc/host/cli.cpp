@@ -155,7 +155,7 @@ struct Bundle {
   std::vector<uint32_t> group_off, exon_off, exon_st, exon_en, cigar_off, cigar; std::vector<int32_t> refid, mate; std::vector<int8_t> strand;
   std::vector<uint64_t> seq_off; std::vector<uint8_t> seq;
   // result (copied out of the engine's staging)
-  std::vector<uint32_t> g_roff, src, tid, pos, coff, clen, cig; std::vector<int8_t> tstrand; std::vector<uint8_t> flags; std::vector<double> sim; std::vector<int32_t> clip;
+  std::vector<uint32_t> g_roff, src, tid, pos, coff, cig; std::vector<int8_t> tstrand; std::vector<uint8_t> flags; std::vector<double> sim; std::vector<int32_t> clip;
   RecView view(uint32_t a) const { return RecView{raw.data() + rec_off[a], rec_len[a]}; }
   uint32_t n_aln() const { return (uint32_t)refid.size(); }
 };
@@ -173,8 +173,9 @@ void store_result(Bundle& b, const brb_batch_out& o) {
   const uint32_t R = o.n_rec, G = (uint32_t)b.group_off.size() - 1;
   b.g_roff.assign(o.group_rec_off, o.group_rec_off + G + 1); b.src.assign(o.src_aln, o.src_aln + R); b.tid.assign(o.tid, o.tid + R);
   b.pos.assign(o.pos, o.pos + R); b.tstrand.assign(o.tx_strand, o.tx_strand + R); b.flags.assign(o.flags, o.flags + R);
-  b.sim.assign(o.sim_score, o.sim_score + R); b.clip.assign(o.clip_score, o.clip_score + R);
-  b.coff.assign(o.cigar_off, o.cigar_off + R); b.clen.assign(o.cigar_len, o.cigar_len + R); b.cig.assign(o.cigar, o.cigar + o.n_cigar_words);
+  if (o.sim_score) b.sim.assign(o.sim_score, o.sim_score + R); else b.sim.assign(R, 0.0);      // NULL: every score is 0 (header)
+  if (o.clip_score) b.clip.assign(o.clip_score, o.clip_score + R); else b.clip.assign(R, 0);
+  b.coff.assign(o.cigar_off, o.cigar_off + R + 1); b.cig.assign(o.cigar, o.cigar + o.n_cigar_words);
 }
 
 uint32_t get_mapq(uint32_t nh, bool lng) {                 // src/core.cpp:46-58
@@ -218,7 +219,7 @@ void assemble_bundle(const Bundle& b, bool lng, Stats& st, std::vector<uint8_t>&
         const uint32_t r = u->row + k, other = u->row + (1 - k);
         OutInfo o{}; o.tid = b.tid[r]; o.pos = b.pos[r]; o.strand = (char)b.tstrand[r]; o.paired = u->paired; o.same_tx = b.flags[r] & BRB_REC_SAMETX;
         o.primary = u->primary; o.long_reads = lng; o.mapq = u->mapq; o.nh = (int32_t)u->nh; o.hi = k == 0 ? u->hi_r : u->hi_m;
-        o.sim = b.sim[r]; o.clip = b.clip[r]; o.cigar = b.cig.data() + b.coff[r]; o.n_cigar = b.clen[r];
+        o.sim = b.sim[r]; o.clip = b.clip[r]; o.cigar = b.cig.data() + b.coff[r]; o.n_cigar = b.coff[r + 1] - b.coff[r];
         if (u->paired) { o.mate_tid = b.tid[other]; o.mate_pos = b.pos[other]; }
         assemble_record(b.view(b.src[r]), o, aux, out);
       }

@@ -1,22 +1,27 @@
 // Kernel group 2: per-candidate exon-chain evaluation (one thread per candidate transcript).
 // The reference evaluates exon-major over an insertion-ordered map (src/evaluate.cpp:184-282,
-// 888-1134); here every candidate (alignment, strand, exon-0 hit) walks the read's exons on its own,
-// re-reading the already located index ranges, which is equivalent because candidates only interact
-// through (a) the strand-level failure decided in k_lookup and (b) duplicate tids, handled below.
+// 888-1134); here every candidate (alignment, strand, exon-0 hit) walks the read's exons on its own.
+// That is equivalent because candidates only interact through (a) the strand-level failure decided in
+// k_lookup and (b) duplicate tids, handled below.  The walk follows the transcript's own exon chain
+// (Rec::gnext) instead of re-scanning each exon's hit range: the exons of a tid are disjoint and ascending
+// (validated at brb_index_create), and read exons are ascending, so every record of the tid that overlaps
+// read exon j is reachable from the record matched at exon j-1 by gnext links.
 #pragma once
 #include "dev_common.cuh"
 
 namespace brb {
 
 // Ideal-CIGAR / score accumulator: ExonChainMatch + AlignInfo, include/evaluate.h:152-181.
+// The open (last) op lives in a register and is stored when the next op starts.
 struct Builder {
-  uint32_t* cig; uint32_t n; uint32_t prev_op;
+  uint32_t* cig; uint32_t n; uint32_t last; uint32_t prev_op;
   double cov, ops; int32_t ref, junc, clip;
-  __device__ __forceinline__ void init(uint32_t* pool) { cig = pool; n = 0; prev_op = CM; cov = 0.0; ops = 0.0; ref = 0; junc = 0; clip = 0; }
+  __device__ __forceinline__ void init(uint32_t* pool) { cig = pool; n = 0; last = 0; prev_op = CM; cov = 0.0; ops = 0.0; ref = 0; junc = 0; clip = 0; }
   __device__ __forceinline__ void add(uint32_t len, uint32_t op) {          // Cigar::add_operation, include/evaluate.h:108-126
-    if (n > 0 && (cig[n - 1] & 0xfu) == op) cig[n - 1] = (((cig[n - 1] >> 4) + len) << 4) | op;
-    else cig[n++] = (len << 4) | op;
+    if (n > 0 && (last & 0xfu) == op) last = (((last >> 4) + len) << 4) | op;
+    else { if (n > 0) cig[n - 1] = last; last = (len << 4) | op; n++; }
   }
+  __device__ __forceinline__ void finish() { if (n > 0) cig[n - 1] = last; }
 };
 
 // build_cigar_match, src/evaluate.cpp:675-786
@@ -66,31 +71,15 @@ struct WalkOut {         // pass-1 facts about a surviving candidate
   uint32_t first_rec, last_rec, n_seg, n_guide, cap;
 };
 
-// Scan exon j's hit range for records of transcript `tid` that pass the filters.
-__device__ __forceinline__ uint32_t find_tid_hits(const DevIndex& ix, const brb_params& p, bool minus, int status, uint32_t qs, uint32_t qe,
-                                                  uint32_t lo, uint32_t hi, uint32_t tid, uint32_t& rec, RecKey& key, Hit& hit) {
-  uint32_t cnt = 0;
-  for (uint32_t i = lo; i < hi; i++) {
-    RecKey k = rec_key(ix.rec, i);
-    if (k.tid != tid || (int32_t)qs >= k.en) continue;
-    Hit h;
-    if (!filter_hit(p, minus, status, qs, qe, (uint32_t)k.st, (uint32_t)k.en, k.pos_start, h)) continue;
-    if (cnt == 0) { rec = i; key = k; hit = h; }
-    cnt++;
-  }
-  return cnt;
-}
-
 // The chain walk.  BUILD=false: pass 1 (continuity, injectivity, counts; src/evaluate.cpp:111-182, 1004-1065).
 // BUILD=true: pass 2 (ideal CIGAR and score accumulators; :1067-1109).  Returns false if eliminated.
 template <bool BUILD>
-__device__ bool walk(const DevIndex& ix, const DevBatch& b, const brb_params& p, const uint32_t* __restrict__ q_lo,
-                     const uint32_t* __restrict__ q_hi, uint32_t a, int s, uint32_t first_rec, WalkOut& w,
+__device__ bool walk(const DevIndex& ix, const DevBatch& b, const brb_params& p, const uint8_t* __restrict__ q_any,
+                     uint32_t a, int s, uint32_t first_rec, WalkOut& w,
                      Builder* m, const RescueSeg* lres, const RescueSeg* rres, const uint32_t* __restrict__ rpool,
                      uint32_t& first_pos, uint32_t& last_pos) {
   const bool minus = s;
   const uint32_t e0 = __ldg(&b.exon_off[a]), n_ex = __ldg(&b.exon_off[a + 1]) - e0;
-  const int32_t refid = __ldg(&b.refid[a]);
   const bool has_lc = BUILD && lres && lres->ok, has_rc = BUILD && rres && rres->ok;
   uint32_t k = 0;                                   // segment index
   uint32_t n_seg = 0, n_guide = 0, cap = 0;
@@ -99,12 +88,12 @@ __device__ bool walk(const DevIndex& ix, const DevBatch& b, const brb_params& p,
   // segment 0
   uint32_t qs = __ldg(&b.exon_st[e0]), qe = __ldg(&b.exon_en[e0]);
   RecKey key = rec_key(ix.rec, first_rec);
-  const uint32_t tid = key.tid;
+  RecLink lk = rec_link(ix.rec, first_rec);
   Hit h; int status = exon_status(n_ex, 0);
   filter_hit(p, minus, status, qs, qe, (uint32_t)key.st, (uint32_t)key.en, key.pos_start, h);
   uint32_t prev_gs = (uint32_t)key.st, prev_ge = (uint32_t)key.en, prev_qs = qs, prev_qe = qe;
-  uint32_t prev_eid = ix.rec[first_rec].meta & 0xffu;
-  uint32_t last_rec = first_rec;
+  uint32_t prev_eid = lk.meta & 0xffu;
+  uint32_t cur = first_rec;                         // record of the last guide-bearing segment (key/lk describe it)
   if (BUILD) {
     if (has_lc) {                                   // LEFTC segment, build_left_clip_segment :397-448 + build_cigar_clip :824-841
       first_pos = key.pos_start - (uint32_t)lres->rc;
@@ -124,8 +113,7 @@ __device__ bool walk(const DevIndex& ix, const DevBatch& b, const brb_params& p,
   for (uint32_t j = 1; j < n_ex; j++) {
     qs = __ldg(&b.exon_st[e0 + j]); qe = __ldg(&b.exon_en[e0 + j]);
     status = exon_status(n_ex, j);
-    const uint32_t lo = q_lo[2 * (e0 + j) + s], hi = q_hi[2 * (e0 + j) + s];
-    if (lo == hi) {                                 // INS_EXON segment (:256-268); build_cigar_ins :788-806
+    if (!q_any[2 * (e0 + j) + s]) {                 // INS_EXON segment (:256-268); build_cigar_ins :788-806
       if (!BUILD) {
         if (qs == prev_qs && qe == prev_qe) return false;
         n_seg++; cap++;
@@ -138,24 +126,42 @@ __device__ bool walk(const DevIndex& ix, const DevBatch& b, const brb_params& p,
       prev_qs = qs; prev_qe = qe;
       continue;
     }
-    uint32_t rec; const uint32_t cnt = find_tid_hits(ix, p, minus, status, qs, qe, lo, hi, tid, rec, key, h);
-    if (!BUILD) { if (cnt != 1) return false; }     // 0: tid not hit by this exon; >=2: non-injective (same q exon twice)
-    const Rec* R = &ix.rec[rec];
-    const uint32_t eid = R->meta & 0xffu;
+    // surviving hits of this transcript on read exon j: `cur` itself (a guide exon spanning the read's
+    // intron) and its genomic successors that start before qe.  Exactly one must survive
+    // (0: tid not hit by this exon; >=2: non-injective, src/evaluate.cpp:1031-1052).
+    uint32_t cnt = 0, rec = cur; RecKey nk = key; RecLink nl = lk;
+    if ((int32_t)qs < key.en) {
+      Hit hh;
+      if (filter_hit(p, minus, status, qs, qe, (uint32_t)key.st, (uint32_t)key.en, key.pos_start, hh)) { cnt = 1; h = hh; }
+    }
+    {
+      uint32_t r = lk.gnext; int32_t r_st = lk.gnext_st;
+      while (r != NONE && r_st < (int32_t)qe) {
+        const RecKey K = rec_key(ix.rec, r); const RecLink Lr = rec_link(ix.rec, r);
+        if ((int32_t)qs < K.en) {
+          Hit hh;
+          if (filter_hit(p, minus, status, qs, qe, (uint32_t)K.st, (uint32_t)K.en, K.pos_start, hh)) {
+            if (cnt == 0) { rec = r; nk = K; nl = Lr; h = hh; }
+            cnt++;
+          }
+        }
+        r = Lr.gnext; r_st = Lr.gnext_st;
+      }
+    }
+    if (cnt != 1) return false;                     // (cannot happen in pass 2)
+    const uint32_t eid = nl.meta & 0xffu;
     const uint32_t gap = (eid - prev_eid) & 0xffu;  // uint8_t wrap, src/evaluate.cpp:131
     if (!p.long_reads) { if (!BUILD && gap != 1) return false; }
     else {
       if (!BUILD && gap > 2) return false;
       if (gap == 2) {                               // skipped guide exon -> GAP_EXON segment (:148-176), build_cigar_gap :808-822
-        uint4 nb = ldg4(&R->prev_st);
-        const uint32_t gs = minus ? nb.z : nb.x, ge = minus ? nb.w : nb.y;
+        // prev_* ('+') / next_* ('-') of seg2 = the genomically previous exon of the same transcript;
+        // getGuideExonForTid on its own coordinates returns that very record
+        const uint32_t grec = __ldg(&ix.gprev[rec]);
+        if (grec == NONE) return false;             // coordinates (0,0)
+        const RecKey gk = rec_key(ix.rec, grec);
         if (!BUILD) {
-          if ((gs == 0 && ge == 0) || (ge - gs > p.max_error_exon)) return false;
-        }
-        uint32_t grec;
-        if (!find_for_tid(ix, refid, minus, tid, gs, ge, grec)) return false;
-        RecKey gk = rec_key(ix.rec, grec);
-        if (!BUILD) {
+          if ((uint32_t)(gk.en - gk.st) > p.max_error_exon) return false;
           if ((uint32_t)gk.st == prev_gs && (uint32_t)gk.en == prev_ge) return false;
           n_seg++; n_guide++; cap++;
         } else {
@@ -166,6 +172,7 @@ __device__ bool walk(const DevIndex& ix, const DevBatch& b, const brb_params& p,
         prev_gs = (uint32_t)gk.st; prev_ge = (uint32_t)gk.en;
       }
     }
+    key = nk; lk = nl; cur = rec;
     if (!BUILD) {
       if ((uint32_t)key.st == prev_gs && (uint32_t)key.en == prev_ge) return false;
       if (qs == prev_qs && qe == prev_qe) return false;
@@ -176,12 +183,12 @@ __device__ bool walk(const DevIndex& ix, const DevBatch& b, const brb_params& p,
       build_match(*m, status, qs, qe, (uint32_t)key.st, (uint32_t)key.en, h, has_lc, has_rc, k == 0, k == last_idx);
       k++;
     }
-    prev_gs = (uint32_t)key.st; prev_ge = (uint32_t)key.en; prev_qs = qs; prev_qe = qe; prev_eid = eid; last_rec = rec;
+    prev_gs = (uint32_t)key.st; prev_ge = (uint32_t)key.en; prev_qs = qs; prev_qe = qe; prev_eid = eid;
   }
   if (BUILD) {
     if (has_rc) {                                   // RIGHTC segment, build_right_clip_segment :548-598
-      RecKey lk = rec_key(ix.rec, w.last_rec);
-      last_pos = lk.pos_start - (uint32_t)rres->rc;
+      RecKey lastk = rec_key(ix.rec, w.last_rec);
+      last_pos = lastk.pos_start - (uint32_t)rres->rc;
       for (uint32_t x = 0; x < rres->cig_len; x++) {
         const uint32_t wd = rpool[rres->cig_off + x], op = wd & 0xfu, len = wd >> 4;
         m->add(len, op); if (op == OV_M || op == OV_D) m->ref += (int32_t)len;
@@ -189,74 +196,50 @@ __device__ bool walk(const DevIndex& ix, const DevBatch& b, const brb_params& p,
       m->clip += rres->score;
     }
     if (m->junc < 0) m->junc = 0;
-  } else { w.first_rec = first_rec; w.last_rec = last_rec; w.n_seg = n_seg; w.n_guide = n_guide; w.cap = cap; }
+    m->finish();
+  } else { w.first_rec = first_rec; w.last_rec = cur; w.n_seg = n_seg; w.n_guide = n_guide; w.cap = cap; }
   return true;
 }
 
 // Exon-0 duplicate handling: `data[tid] = td` (src/evaluate.cpp:218-224) keeps the FIRST hit's slot
-// and the LAST hit's content.  Returns false if this candidate slot is not the first hit of its tid.
-__device__ __forceinline__ bool dedupe_first(const DevIndex& ix, const DevBatch& b, const brb_params& p, const uint32_t* q_lo,
-                                             const uint32_t* q_hi, uint32_t a, int s, uint32_t& rec0) {
+// and the LAST hit's content.  Returns false if this candidate slot is not the first surviving hit of its
+// tid.  Duplicates can only be genomic neighbours of rec0 in the same transcript that also overlap read
+// exon 0, so the common case is decided by two compares on rec0's own link words.
+__device__ __forceinline__ bool dedupe_first(const DevIndex& ix, const DevBatch& b, const brb_params& p,
+                                             uint32_t a, int s, uint32_t& rec0) {
   const uint32_t e0 = __ldg(&b.exon_off[a]), n_ex = __ldg(&b.exon_off[a + 1]) - e0;
   const uint32_t qs = __ldg(&b.exon_st[e0]), qe = __ldg(&b.exon_en[e0]);
+  const RecLink lk = rec_link(ix.rec, rec0);
+  if (lk.gprev_en <= (int32_t)qs && lk.gnext_st >= (int32_t)qe) return true;
   const int status = exon_status(n_ex, 0);
-  const uint32_t lo = q_lo[2 * e0 + s], hi = q_hi[2 * e0 + s];
-  const uint32_t tid = rec_key(ix.rec, rec0).tid;
-  uint32_t last = rec0;
-  for (uint32_t i = lo; i < hi; i++) {
-    if (i == rec0) continue;
-    RecKey k = rec_key(ix.rec, i);
-    if (k.tid != tid || (int32_t)qs >= k.en) continue;
-    Hit h;
-    if (!filter_hit(p, s, status, qs, qe, (uint32_t)k.st, (uint32_t)k.en, k.pos_start, h)) continue;
-    if (i < rec0) return false;
-    last = i;
+  for (uint32_t r = __ldg(&ix.gprev[rec0]); r != NONE; r = __ldg(&ix.gprev[r])) {      // an earlier surviving hit owns the slot
+    const RecKey k = rec_key(ix.rec, r);
+    if (k.en <= (int32_t)qs) break;
+    if (passes_filter(p, s, status, qs, qe, (uint32_t)k.st, (uint32_t)k.en)) return false;
   }
-  rec0 = last;
+  uint32_t r = lk.gnext; int32_t r_st = lk.gnext_st;
+  while (r != NONE && r_st < (int32_t)qe) {                                            // the last surviving hit provides the content
+    const RecKey k = rec_key(ix.rec, r); const RecLink l2 = rec_link(ix.rec, r);
+    if ((int32_t)qs < k.en && passes_filter(p, s, status, qs, qe, (uint32_t)k.st, (uint32_t)k.en)) rec0 = r;
+    r = l2.gnext; r_st = l2.gnext_st;
+  }
   return true;
 }
 
-// Pass 1, one thread per candidate.  c_cap[c] = ideal-CIGAR capacity (0 = eliminated).
-__global__ void __launch_bounds__(256) k_chain(DevIndex ix, DevBatch b, brb_params p, uint32_t n_cand,
-                                               const uint32_t* __restrict__ q_lo, const uint32_t* __restrict__ q_hi,
-                                               const uint32_t* __restrict__ c_rec, const uint32_t* __restrict__ c_task,
-                                               uint32_t* __restrict__ c_first, uint32_t* __restrict__ c_last,
-                                               uint32_t* __restrict__ c_nseg, uint32_t* __restrict__ c_nguide,
-                                               uint32_t* __restrict__ c_cap) {
-  const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= n_cand) return;
-  const uint32_t task = c_task[c], a = task >> 1; const int s = task & 1;
-  uint32_t rec0 = c_rec[c];
-  WalkOut w; w.cap = 0; w.first_rec = rec0; w.last_rec = rec0; w.n_seg = 0; w.n_guide = 0;
-  uint32_t fp, lp;
-  bool ok = dedupe_first(ix, b, p, q_lo, q_hi, a, s, rec0);
-  if (ok) ok = walk<false>(ix, b, p, q_lo, q_hi, a, s, rec0, w, nullptr, nullptr, nullptr, nullptr, fp, lp);
-  c_first[c] = w.first_rec; c_last[c] = w.last_rec; c_nseg[c] = w.n_seg; c_nguide[c] = w.n_guide;
-  c_cap[c] = ok ? w.cap : 0;
-}
+struct Matches {          // per candidate slot; tid == NONE marks "no match"
+  uint32_t* tid; uint32_t* pos; double* sim; int32_t* clip; uint32_t* ilen; uint32_t* ioff;
+};
 
-// Pass 2 + filter_by_similarity (src/evaluate.cpp:843-865), one thread per surviving candidate.
-// Writes the match row: valid flag, tid, position (fwpos or rcpos by strand), scores, ideal CIGAR length.
-__device__ __forceinline__ uint32_t build_one(const DevIndex& ix, const DevBatch& b, const brb_params& p, uint32_t c,
-                                              const uint32_t* __restrict__ q_lo, const uint32_t* __restrict__ q_hi,
-                                              const uint32_t* __restrict__ c_task,
-                                              const uint32_t* __restrict__ c_first, const uint32_t* __restrict__ c_last,
-                                              const uint32_t* __restrict__ c_nseg, const uint32_t* __restrict__ c_nguide,
-                                              const uint32_t* __restrict__ c_cap, const uint32_t* __restrict__ c_ioff,
-                                              const RescueSeg* __restrict__ r_left, const RescueSeg* __restrict__ r_right,
-                                              const uint32_t* __restrict__ rpool, uint32_t* __restrict__ ipool,
-                                              uint8_t* __restrict__ m_valid, uint32_t* __restrict__ m_tid, uint32_t* __restrict__ m_pos,
-                                              double* __restrict__ m_sim, int32_t* __restrict__ m_clip, uint32_t* __restrict__ m_ilen) {
-  if (c_cap[c] == 0) { m_valid[c] = 0; return 0; }
-  const uint32_t task = c_task[c], a = task >> 1; const int s = task & 1;
-  WalkOut w; w.first_rec = c_first[c]; w.last_rec = c_last[c]; w.n_seg = c_nseg[c]; w.n_guide = c_nguide[c]; w.cap = c_cap[c];
-  RescueSeg L, R; L.ok = 0; R.ok = 0;
-  if (r_left) { L = r_left[c]; R = r_right[c]; }
-  if (L.ok) { w.n_seg++; w.n_guide++; }
-  if (R.ok) { w.n_seg++; w.n_guide++; }
-  Builder m; m.init(ipool + c_ioff[c]);
+// Pass 2 for one candidate whose pass-1 facts are in `w`: ideal CIGAR into pool, scores, similarity filter
+// (src/evaluate.cpp:843-865, FP64, operation order kept), match row.
+__device__ __forceinline__ bool build_one(const DevIndex& ix, const DevBatch& b, const brb_params& p, uint32_t c, uint32_t a, int s,
+                                          const uint8_t* __restrict__ q_any, WalkOut w, const RescueSeg* L, const RescueSeg* R,
+                                          const uint32_t* __restrict__ rpool, uint32_t* __restrict__ ipool, uint32_t ioff, const Matches& M) {
+  if (L && L->ok) { w.n_seg++; w.n_guide++; }
+  if (R && R->ok) { w.n_seg++; w.n_guide++; }
+  Builder m; m.init(ipool + ioff);
   uint32_t fp = 0, lp = 0;
-  walk<true>(ix, b, p, q_lo, q_hi, a, s, w.first_rec, w, &m, r_left ? &L : nullptr, r_left ? &R : nullptr, rpool, fp, lp);
+  walk<true>(ix, b, p, q_any, a, s, w.first_rec, w, &m, L, R, rpool, fp, lp);
   double sim_score = 0.0; bool keep = true;
   if (p.filter_by_similarity) {
     const double thr = (double)p.similarity_threshold;
@@ -264,30 +247,91 @@ __device__ __forceinline__ uint32_t build_one(const DevIndex& ix, const DevBatch
     if (sim > thr) { const double x = (sim - thr) / (1.0 - thr); sim_score = x * x * (double)(m.junc + 1); }
     else keep = false;
   }
-  m_valid[c] = keep ? 1 : 0;
-  m_tid[c] = rec_key(ix.rec, w.first_rec).tid;
-  m_pos[c] = s ? lp : fp;
-  m_sim[c] = sim_score; m_clip[c] = m.clip; m_ilen[c] = m.n;
-  return keep ? 1u : 0u;
+  M.tid[c] = keep ? rec_key(ix.rec, w.first_rec).tid : NONE;
+  M.pos[c] = s ? lp : fp;
+  M.sim[c] = sim_score; M.clip[c] = m.clip; M.ilen[c] = m.n; M.ioff[c] = ioff;
+  return keep;
 }
 
-__global__ void __launch_bounds__(256) k_build(DevIndex ix, DevBatch b, brb_params p, uint32_t n_cand,
-                                               const uint32_t* __restrict__ q_lo, const uint32_t* __restrict__ q_hi,
-                                               const uint32_t* __restrict__ c_task,
-                                               const uint32_t* __restrict__ c_first, const uint32_t* __restrict__ c_last,
-                                               const uint32_t* __restrict__ c_nseg, const uint32_t* __restrict__ c_nguide,
-                                               const uint32_t* __restrict__ c_cap, const uint32_t* __restrict__ c_ioff,
-                                               const RescueSeg* __restrict__ r_left, const RescueSeg* __restrict__ r_right,
-                                               const uint32_t* __restrict__ rpool, uint32_t* __restrict__ ipool,
-                                               uint8_t* __restrict__ m_valid, uint32_t* __restrict__ m_tid, uint32_t* __restrict__ m_pos,
-                                               double* __restrict__ m_sim, int32_t* __restrict__ m_clip, uint32_t* __restrict__ m_ilen,
-                                               unsigned long long* __restrict__ n_matches) {
-  const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+// Fused evaluation (no clip rescue): pass 1, pool allocation and pass 2 in one kernel.  Persistent warps
+// over the candidate slots; the slot count is read from the control block (no host round trip).
+__global__ void __launch_bounds__(256) k_eval(DevIndex ix, DevBatch b, brb_params p, Ctl* __restrict__ ctl,
+                                              const uint8_t* __restrict__ q_any, const uint32_t* __restrict__ c_rec,
+                                              const uint32_t* __restrict__ c_task, uint32_t* __restrict__ ipool, Matches M) {
+  if (ctl_overflow(ctl)) return;
+  const unsigned lane = threadIdx.x & 31;
+  const uint32_t n_cand = ctl->n_cand;
+  const uint32_t stride = gridDim.x * blockDim.x;
   uint32_t kept = 0;
-  if (c < n_cand) kept = build_one(ix, b, p, c, q_lo, q_hi, c_task, c_first, c_last, c_nseg, c_nguide, c_cap, c_ioff, r_left, r_right, rpool,
-                                   ipool, m_valid, m_tid, m_pos, m_sim, m_clip, m_ilen);
+  for (uint32_t base = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); base < n_cand; base += stride) {
+    const uint32_t c = base + lane;
+    const bool act = c < n_cand;
+    uint32_t a = 0; int s = 0; WalkOut w; w.cap = 0;
+    bool ok = false;
+    if (act) {
+      const uint32_t task = c_task[c]; a = task >> 1; s = task & 1;
+      uint32_t rec0 = c_rec[c];
+      uint32_t fp, lp;
+      ok = dedupe_first(ix, b, p, a, s, rec0);
+      if (ok) ok = walk<false>(ix, b, p, q_any, a, s, rec0, w, nullptr, nullptr, nullptr, nullptr, fp, lp);
+    }
+    bool fits;
+    const uint32_t ioff = warp_alloc(&ctl->n_ideal, ctl->cap_ideal, ok ? w.cap : 0, lane, fits);
+    if (act) {
+      if (ok && fits) kept += build_one(ix, b, p, c, a, s, q_any, w, nullptr, nullptr, nullptr, ipool, ioff, M) ? 1u : 0u;
+      else M.tid[c] = NONE;
+    }
+  }
   for (int d = 16; d; d >>= 1) kept += __shfl_down_sync(0xffffffffu, kept, d);
-  if ((threadIdx.x & 31) == 0 && kept) atomicAdd(n_matches, (unsigned long long)kept);
+  if (lane == 0 && kept) atomicAdd(&ctl->n_matches, (unsigned long long)kept);
+}
+
+// Split form for the clip-rescue path (long reads with a genome): pass 1 here, then k_rescue_* / k_ksw
+// (which add their CIGAR lengths to c_cap), then k_build.
+struct CandFacts { uint32_t* first; uint32_t* last; uint32_t* nseg; uint32_t* nguide; uint32_t* cap; };
+
+__global__ void __launch_bounds__(256) k_chain(DevIndex ix, DevBatch b, brb_params p, const Ctl* __restrict__ ctl,
+                                               const uint8_t* __restrict__ q_any, const uint32_t* __restrict__ c_rec,
+                                               const uint32_t* __restrict__ c_task, CandFacts F) {
+  if (ctl_overflow(ctl)) return;
+  const uint32_t n_cand = ctl->n_cand;
+  for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < n_cand; c += gridDim.x * blockDim.x) {
+    const uint32_t task = c_task[c], a = task >> 1; const int s = task & 1;
+    uint32_t rec0 = c_rec[c];
+    WalkOut w; w.cap = 0; w.first_rec = rec0; w.last_rec = rec0; w.n_seg = 0; w.n_guide = 0;
+    uint32_t fp, lp;
+    bool ok = dedupe_first(ix, b, p, a, s, rec0);
+    if (ok) ok = walk<false>(ix, b, p, q_any, a, s, rec0, w, nullptr, nullptr, nullptr, nullptr, fp, lp);
+    F.first[c] = w.first_rec; F.last[c] = w.last_rec; F.nseg[c] = w.n_seg; F.nguide[c] = w.n_guide;
+    F.cap[c] = ok ? w.cap : 0;
+  }
+}
+
+__global__ void __launch_bounds__(256) k_build(DevIndex ix, DevBatch b, brb_params p, Ctl* __restrict__ ctl,
+                                               const uint8_t* __restrict__ q_any, const uint32_t* __restrict__ c_task, CandFacts F,
+                                               const RescueSeg* __restrict__ r_left, const RescueSeg* __restrict__ r_right,
+                                               const uint32_t* __restrict__ rpool, uint32_t* __restrict__ ipool, Matches M) {
+  if (ctl_overflow(ctl)) return;
+  const unsigned lane = threadIdx.x & 31;
+  const uint32_t n_cand = ctl->n_cand;
+  const uint32_t stride = gridDim.x * blockDim.x;
+  uint32_t kept = 0;
+  for (uint32_t base = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); base < n_cand; base += stride) {
+    const uint32_t c = base + lane;
+    const bool act = c < n_cand;
+    const uint32_t cap = act ? F.cap[c] : 0;
+    bool fits;
+    const uint32_t ioff = warp_alloc(&ctl->n_ideal, ctl->cap_ideal, cap, lane, fits);
+    if (!act) continue;
+    if (cap == 0 || !fits) { M.tid[c] = NONE; continue; }
+    const uint32_t task = c_task[c], a = task >> 1; const int s = task & 1;
+    WalkOut w; w.first_rec = F.first[c]; w.last_rec = F.last[c]; w.n_seg = F.nseg[c]; w.n_guide = F.nguide[c]; w.cap = cap;
+    RescueSeg L, R; L.ok = 0; R.ok = 0;
+    if (r_left) { L = r_left[c]; R = r_right[c]; }
+    kept += build_one(ix, b, p, c, a, s, q_any, w, r_left ? &L : nullptr, r_left ? &R : nullptr, rpool, ipool, ioff, M) ? 1u : 0u;
+  }
+  for (int d = 16; d; d >>= 1) kept += __shfl_down_sync(0xffffffffu, kept, d);
+  if (lane == 0 && kept) atomicAdd(&ctl->n_matches, (unsigned long long)kept);
 }
 
 }  // namespace brb

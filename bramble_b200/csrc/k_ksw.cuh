@@ -155,20 +155,16 @@ __device__ __forceinline__ void get_clips(const uint32_t* cg, uint32_t n, bool& 
 // :513-546).  WRITE=false: returns the total collected length (0 = no rescue).  WRITE=true: emits `tlen`
 // target codes into `dst` (left: already reversed, i.e. nearest base first going leftwards).
 template <bool WRITE>
-__device__ uint32_t collect_exons(const DevIndex& ix, int32_t refid, bool minus, bool left, uint32_t tid, uint32_t rec, uint32_t qlen,
+__device__ uint32_t collect_exons(const DevIndex& ix, int32_t refid, bool left, uint32_t rec, uint32_t qlen,
                                   uint8_t* dst, uint32_t tlen) {
   uint32_t gathered = 0, n_ex = 0, i = 0, cur = rec, w = 0;
-  const bool use_next = left ? minus : !minus;        // left: prev for '+', next for '-'; right: the other way round
   const uint64_t base = ix.chrom_off[refid], lim = ix.chrom_off[refid + 1];
   while (qlen > gathered) {
     i++;
-    const Rec* R = &ix.rec[cur];
-    const uint32_t meta = R->meta;
-    const bool has_nb = use_next ? ((meta >> 9) & 1) : ((meta >> 8) & 1);
-    if (!has_nb) { if (i == 1) return 0; break; }
-    const uint32_t gs = use_next ? R->next_st : R->prev_st, ge = use_next ? R->next_en : R->prev_en;
-    uint32_t nx;
-    if (!find_for_tid(ix, refid, minus, tid, gs, ge, nx)) return 0;
+    // transcript-order neighbour away from the read = genomic neighbour on that side; getGuideExonForTid on the
+    // neighbour's own coordinates returns that very record (exons of a tid are disjoint)
+    const uint32_t nx = left ? __ldg(&ix.gprev[cur]) : rec_link(ix.rec, cur).gnext;
+    if (nx == NONE) { if (i == 1) return 0; break; }
     const RecKey k = rec_key(ix.rec, nx);
     const uint32_t len = (uint32_t)(k.en - k.st);
     if (WRITE) {
@@ -212,7 +208,7 @@ __device__ __forceinline__ bool rescue_inputs(const DevIndex& ix, const DevBatch
 __global__ void __launch_bounds__(128) k_rescue_plan(DevIndex ix, DevBatch b, brb_params p, uint32_t n_cand, const uint32_t* __restrict__ c_task,
                                                      const uint32_t* __restrict__ c_first, const uint32_t* __restrict__ c_last,
                                                      const uint32_t* __restrict__ c_cap, RescuePlan R,
-                                                     unsigned long long* __restrict__ counters) {
+                                                     Ctl* __restrict__ ctl) {
   const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
   if (slot >= 2 * n_cand) return;
   const uint32_t c = slot >> 1; const int side = slot & 1;
@@ -221,15 +217,14 @@ __global__ void __launch_bounds__(128) k_rescue_plan(DevIndex ix, DevBatch b, br
     const uint32_t task = c_task[c], a = task >> 1; const int s = task & 1;
     uint32_t rec, total;
     if (rescue_inputs(ix, b, p, a, s, c_first[c], c_last[c], side, rec, total)) {
-      const uint32_t tid = rec_key(ix.rec, rec).tid;
-      const uint32_t got = collect_exons<false>(ix, b.refid[a], s, side == 0, tid, rec, total, nullptr, 0);
+      const uint32_t got = collect_exons<false>(ix, b.refid[a], side == 0, rec, total, nullptr, 0);
       if (got) { qlen = total; tlen = got < total + 40 ? got : total + 40; }   // align_reversed keeps the last qlen+40; right truncates to qlen+40
     }
   }
   R.qlen[slot] = qlen; R.tlen[slot] = tlen; R.tbcap[slot] = qlen ? qlen + tlen + 2 : 0;
   if (qlen) {       // scratch sizing for k_ksw: largest direction matrix and longest target
     const unsigned long long mat = (unsigned long long)(qlen + tlen - 1) * (qlen < tlen ? qlen : tlen);
-    atomicMax(&counters[5], mat); atomicMax(&counters[6], (unsigned long long)tlen);
+    atomicMax(&ctl->ksw_max_mat, mat); atomicMax(&ctl->ksw_max_tlen, (unsigned long long)tlen);
   }
 }
 
@@ -250,14 +245,14 @@ __global__ void __launch_bounds__(128) k_rescue_gather(DevIndex ix, DevBatch b, 
   if (side == 0) for (uint32_t i = 0; i < qlen; i++) qd[i] = seq[qlen - 1 - i];           // get_left_rescue_query + reversal (:320-330, 368-395)
   else for (uint32_t i = 0; i < qlen; i++) qd[i] = seq[seq_len - qlen + i];               // get_right_rescue_query (:500-511)
   const uint32_t rec = side == 0 ? c_first[c] : c_last[c];
-  collect_exons<true>(ix, b.refid[a], s, side == 0, rec_key(ix.rec, rec).tid, rec, qlen, tbuf + t_off[slot], tlen);
+  collect_exons<true>(ix, b.refid[a], side == 0, rec, qlen, tbuf + t_off[slot], tlen);
 }
 
 // build_left_clip_segment / build_right_clip_segment: KswOut + traceback-order ops -> RescueSeg + override-coded CIGAR.
 __global__ void __launch_bounds__(128) k_rescue_finish(uint32_t n_cand, const uint32_t* __restrict__ q_off, const uint32_t* __restrict__ tb_off,
                                                        const KswOut* __restrict__ ko, const uint32_t* __restrict__ tb, uint32_t* __restrict__ rpool,
                                                        RescueSeg* __restrict__ r_left, RescueSeg* __restrict__ r_right, uint32_t* __restrict__ c_cap,
-                                                       unsigned long long* __restrict__ counters) {
+                                                       Ctl* __restrict__ ctl) {
   const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
   if (slot >= 2 * n_cand) return;
   const uint32_t c = slot >> 1; const int side = slot & 1;
@@ -288,7 +283,7 @@ __global__ void __launch_bounds__(128) k_rescue_finish(uint32_t n_cand, const ui
       sgm.ok = 1; sgm.score = o.max; sgm.rc = rc; sgm.cig_off = tb_off[slot]; sgm.cig_len = m;
       atomicAdd(&c_cap[c], m);
     }
-    atomicAdd(&counters[4], 1ull);
+    atomicAdd(&ctl->n_rescue, 1ull);
   }
   (side == 0 ? r_left : r_right)[c] = sgm;
 }

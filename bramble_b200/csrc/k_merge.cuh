@@ -117,26 +117,46 @@ __device__ uint32_t merge_cigars(const uint32_t* __restrict__ real, uint32_t n_r
   return n;
 }
 
-__global__ void __launch_bounds__(256) k_merge(DevBatch b, uint32_t n_rec, const uint32_t* __restrict__ o_src,
-                                               const uint32_t* __restrict__ o_cand, const int8_t* __restrict__ o_strand,
-                                               const uint32_t* __restrict__ o_coff, const uint32_t* __restrict__ c_ioff,
+// One thread per output row: merged CIGAR into a bump-allocated scratch pool (capacity n_real + n_ideal + 2
+// words per row, one atomic per warp), its exact length into o_clen.
+__global__ void __launch_bounds__(256) k_merge(DevBatch b, Ctl* __restrict__ ctl, const uint32_t* __restrict__ o_src,
+                                               const uint32_t* __restrict__ o_cand, const uint32_t* __restrict__ m_ioff,
                                                const uint32_t* __restrict__ m_ilen, const uint32_t* __restrict__ ipool,
-                                               uint32_t* __restrict__ o_clen, uint32_t* __restrict__ opool,
-                                               unsigned long long* __restrict__ n_words) {
-  const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
-  uint32_t n = 0;
-  if (r < n_rec) {
-    const uint32_t a = o_src[r], c = o_cand[r];
-    const uint32_t ro = b.cigar_off[a], nr = b.cigar_off[a + 1] - ro;
-    uint32_t* out = opool + o_coff[r];
-    n = merge_cigars(b.cigar + ro, nr, ipool + c_ioff[c], m_ilen[c], out);
-    if (o_strand[r] == '-')
-      for (uint32_t i = 0; i < n / 2; i++) { const uint32_t t = out[i]; out[i] = out[n - 1 - i]; out[n - 1 - i] = t; }
-    o_clen[r] = n;
+                                               uint32_t* __restrict__ o_tmpoff, uint32_t* __restrict__ o_clen, uint32_t* __restrict__ tpool) {
+  if (ctl_overflow(ctl)) return;
+  const unsigned lane = threadIdx.x & 31;
+  const uint32_t n_rec = ctl->n_rows;
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (uint32_t base = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); base < n_rec; base += stride) {
+    const uint32_t r = base + lane;
+    const bool act = r < n_rec;
+    uint32_t ro = 0, nr = 0, c = 0, ni = 0;
+    if (act) { const uint32_t a = o_src[r]; c = o_cand[r]; ro = b.cigar_off[a]; nr = b.cigar_off[a + 1] - ro; ni = m_ilen[c]; }
+    bool fits;
+    const uint32_t off = warp_alloc(&ctl->n_tmpw, ctl->cap_tmpw, act ? nr + ni + 2 : 0, lane, fits);
+    if (act && fits) {
+      o_tmpoff[r] = off;
+      o_clen[r] = merge_cigars(b.cigar + ro, nr, ipool + m_ioff[c], ni, tpool + off);
+    }
   }
-  uint32_t tot = n;                                  // work counter: output CIGAR words (algorithmic bytes)
-  for (int d = 16; d; d >>= 1) tot += __shfl_down_sync(0xffffffffu, tot, d);
-  if ((threadIdx.x & 31) == 0 && tot) atomicAdd(n_words, (unsigned long long)tot);
+}
+
+// Dense, row-ordered CIGAR pool: row r's words go to opool[o_coff[r] .. o_coff[r+1]) (o_coff = exclusive scan of
+// o_clen), reversed for '-' transcripts (reverse_complement_bam, src/bam.cpp:636-702).
+__global__ void __launch_bounds__(256) k_compact(Ctl* __restrict__ ctl, const int8_t* __restrict__ o_strand,
+                                                 const uint32_t* __restrict__ o_tmpoff, const uint32_t* __restrict__ o_coff,
+                                                 const uint32_t* __restrict__ tpool, uint32_t* __restrict__ opool) {
+  if (ctl_overflow(ctl)) return;
+  const uint32_t n_rec = ctl->n_rows;
+  const uint32_t W = o_coff[n_rec];
+  if (blockIdx.x == 0 && threadIdx.x == 0) { ctl->n_outw = W; ctl->out_words = W; }
+  if (W > ctl->cap_outw) return;
+  for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n_rec; r += gridDim.x * blockDim.x) {
+    const uint32_t d0 = o_coff[r], n = o_coff[r + 1] - d0;
+    const uint32_t* src = tpool + o_tmpoff[r];
+    if (o_strand[r] == '-') for (uint32_t i = 0; i < n; i++) opool[d0 + i] = src[n - 1 - i];
+    else for (uint32_t i = 0; i < n; i++) opool[d0 + i] = src[i];
+  }
 }
 
 // Standalone entry for the parity tests (brb_merge_cigars).

@@ -24,12 +24,12 @@ int launch_ksw(cudaStream_t st, KswProblems P, unsigned long long max_mat, unsig
 }
 
 struct RescueBufs { Buf qlen, tlen, tbcap, q_off, t_off, tb_off, qbuf, tbuf, tb, kout, aln_group; KswScratch ks; };
-RescueBufs& rescue_bufs(brb_ctx* c) {
-  // one set per ctx, kept in a side table so that brb_ctx stays a plain aggregate of Bufs
-  static thread_local std::vector<std::pair<brb_ctx*, RescueBufs*>> tab;
-  for (auto& e : tab) if (e.first == c) return *e.second;
-  tab.emplace_back(c, new RescueBufs());
-  return *tab.back().second;
+RescueBufs& rescue_bufs(brb_ctx* c) { if (!c->rb) c->rb = new RescueBufs(); return *c->rb; }
+void free_rescue_bufs(brb_ctx* c) {
+  if (!c->rb) return;
+  RescueBufs& R = *c->rb;
+  for (Buf* b : {&R.qlen, &R.tlen, &R.tbcap, &R.q_off, &R.t_off, &R.tb_off, &R.qbuf, &R.tbuf, &R.tb, &R.kout, &R.aln_group, &R.ks.pmat, &R.ks.state}) b->release();
+  delete c->rb; c->rb = nullptr;
 }
 
 int run_rescue(brb_ctx* c, const brb_params& p) {
@@ -38,7 +38,7 @@ int run_rescue(brb_ctx* c, const brb_params& p) {
   uint64_t L = c->stats.n_launches;
   const uint32_t C = c->n_cand, slots = 2 * C;
   DevBatch& b = c->b; const DevIndex& ix = c->idx->d;
-  unsigned long long* counters = c->counters.as<unsigned long long>();
+  Ctl* ctl = c->ctl.as<Ctl>();
   ENS(R.aln_group, (size_t)b.n_aln * 4);
   ENS(R.qlen, (size_t)slots * 4); ENS(R.tlen, (size_t)slots * 4); ENS(R.tbcap, (size_t)slots * 4);
   ENS(R.q_off, (size_t)(slots + 1) * 4); ENS(R.t_off, (size_t)(slots + 1) * 4); ENS(R.tb_off, (size_t)(slots + 1) * 4);
@@ -49,7 +49,7 @@ int run_rescue(brb_ctx* c, const brb_params& p) {
   b.aln_group = R.aln_group.as<uint32_t>();
   RescuePlan plan; plan.qlen = R.qlen.as<uint32_t>(); plan.tlen = R.tlen.as<uint32_t>(); plan.tbcap = R.tbcap.as<uint32_t>();
   k_rescue_plan<<<grid_for(slots, 128), 128, 0, st>>>(ix, b, p, C, c->c_task.as<uint32_t>(), c->c_first.as<uint32_t>(), c->c_last.as<uint32_t>(),
-                                                      c->c_cap.as<uint32_t>(), plan, counters); L++;
+                                                      c->c_cap.as<uint32_t>(), plan, ctl); L++;
   exclusive_scan(plan.qlen, R.q_off.as<uint32_t>(), slots, c->scan_tmp.as<uint32_t>(), st, &L);
   exclusive_scan(plan.tlen, R.t_off.as<uint32_t>(), slots, c->scan_tmp.as<uint32_t>(), st, &L);
   exclusive_scan(plan.tbcap, R.tb_off.as<uint32_t>(), slots, c->scan_tmp.as<uint32_t>(), st, &L);
@@ -57,7 +57,7 @@ int run_rescue(brb_ctx* c, const brb_params& p) {
   CU(cudaMemcpyAsync(hs, R.q_off.as<uint32_t>() + slots, 4, cudaMemcpyDeviceToHost, st));
   CU(cudaMemcpyAsync(hs + 1, R.t_off.as<uint32_t>() + slots, 4, cudaMemcpyDeviceToHost, st));
   CU(cudaMemcpyAsync(hs + 2, R.tb_off.as<uint32_t>() + slots, 4, cudaMemcpyDeviceToHost, st));
-  CU(cudaMemcpyAsync(hs + 4, counters + 5, 16, cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(hs + 4, &ctl->ksw_max_mat, 16, cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
   const uint32_t Q = hs[0], T = hs[1], TB = hs[2];
   unsigned long long mx[2]; memcpy(mx, hs + 4, 16);
@@ -72,7 +72,7 @@ int run_rescue(brb_ctx* c, const brb_params& p) {
   }
   k_rescue_finish<<<grid_for(slots, 128), 128, 0, st>>>(C, R.q_off.as<uint32_t>(), R.tb_off.as<uint32_t>(), R.kout.as<KswOut>(), R.tb.as<uint32_t>(),
                                                         c->rpool.as<uint32_t>(), c->r_left.as<RescueSeg>(), c->r_right.as<RescueSeg>(),
-                                                        c->c_cap.as<uint32_t>(), counters); L++;
+                                                        c->c_cap.as<uint32_t>(), ctl); L++;
   c->stats.n_launches = L;
   return 0;
 }

@@ -31,9 +31,13 @@ __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* t
 }
 
 // tile-local exclusive scan; tile total -> sums[blockIdx.x]
+// n_dev (optional): the live element count in device memory (<= n); tiles beyond it only report a zero sum,
+// so a scan launched for a pool's CAPACITY costs what its live part costs.
 __global__ void __launch_bounds__(SCAN_THREADS) k_scan_tiles(const uint32_t* __restrict__ in, uint32_t* __restrict__ out,
-                                                             uint32_t* __restrict__ sums, uint32_t n) {
+                                                             uint32_t* __restrict__ sums, uint32_t n, const uint32_t* __restrict__ n_dev) {
   __shared__ uint32_t sh[33];
+  if (n_dev) { const uint32_t live = *n_dev; if (live < n) n = live; }
+  if (blockIdx.x * SCAN_TILE >= n) { if (threadIdx.x == 0) sums[blockIdx.x] = 0; return; }
   const uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
   uint32_t v[SCAN_ITEMS], s = 0;
 #pragma unroll
@@ -45,7 +49,9 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_tiles(const uint32_t* __r
 }
 
 __global__ void __launch_bounds__(SCAN_THREADS) k_scan_add(uint32_t* __restrict__ out, const uint32_t* __restrict__ sums_ex,
-                                                           uint32_t n, uint32_t n_tiles) {
+                                                           uint32_t n, uint32_t n_tiles, const uint32_t* __restrict__ n_dev) {
+  if (n_dev) { const uint32_t live = *n_dev; if (live < n) n = live; }
+  if (blockIdx.x * SCAN_TILE >= n) { if (blockIdx.x == 0 && threadIdx.x == 0) out[n] = sums_ex[n_tiles]; return; }
   const uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
   const uint32_t add = sums_ex[blockIdx.x];
 #pragma unroll
@@ -60,17 +66,23 @@ inline size_t scan_scratch_words(size_t n) {
   return w + 8;
 }
 
-inline int exclusive_scan(const uint32_t* in, uint32_t* out, uint32_t n, uint32_t* scratch, cudaStream_t st, uint64_t* launches) {
+__global__ void k_scan_total1(uint32_t* __restrict__ out, const uint32_t* __restrict__ sums, uint32_t n, const uint32_t* __restrict__ n_dev) {
+  if (n_dev) { const uint32_t live = *n_dev; if (live < n) n = live; }
+  out[n] = sums[0];
+}
+
+// out[live n] receives the total.  n = launch size (capacity); n_dev = optional live count on the device.
+inline int exclusive_scan(const uint32_t* in, uint32_t* out, uint32_t n, uint32_t* scratch, cudaStream_t st, uint64_t* launches,
+                          const uint32_t* n_dev = nullptr) {
   uint32_t tiles = (n + SCAN_TILE - 1) / SCAN_TILE; if (tiles == 0) tiles = 1;
   uint32_t* sums = scratch; uint32_t* sums_ex = scratch + (tiles + 1);
-  k_scan_tiles<<<tiles, SCAN_THREADS, 0, st>>>(in, out, sums, n); (*launches)++;
+  k_scan_tiles<<<tiles, SCAN_THREADS, 0, st>>>(in, out, sums, n, n_dev); (*launches)++;
   if (tiles == 1) {
-    // single tile: total is sums[0]; out[n] = total
-    cudaMemcpyAsync(out + n, sums, 4, cudaMemcpyDeviceToDevice, st);
+    k_scan_total1<<<1, 1, 0, st>>>(out, sums, n, n_dev); (*launches)++;   // single tile: total is sums[0]
     return 0;
   }
   exclusive_scan(sums, sums_ex, tiles, scratch + 2 * (tiles + 1), st, launches);
-  k_scan_add<<<tiles, SCAN_THREADS, 0, st>>>(out, sums_ex, n, tiles); (*launches)++;
+  k_scan_add<<<tiles, SCAN_THREADS, 0, st>>>(out, sums_ex, n, tiles, n_dev); (*launches)++;
   return 0;
 }
 

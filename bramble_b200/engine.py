@@ -12,15 +12,17 @@ def _rows(o, n_groups):
     n = int(o.n_rec)
 
     def arr(p, cnt, dt):
-        if cnt == 0:
-            return np.zeros(0, dtype=dt)
+        if cnt == 0 or not p:          # NULL score columns: all zero (see include/bramble_b200.h)
+            return np.zeros(cnt, dtype=dt)
         return np.ctypeslib.as_array(p, shape=(cnt,)).astype(dt, copy=True)
     d = dict(n_rec=n, group_rec_off=arr(o.group_rec_off, n_groups + 1, np.uint32), src_aln=arr(o.src_aln, n, np.uint32),
              tid=arr(o.tid, n, np.uint32), pos=arr(o.pos, n, np.uint32), tx_strand=arr(o.tx_strand, n, np.int8),
              flags=arr(o.flags, n, np.uint8), sim_score=arr(o.sim_score, n, np.float64), clip_score=arr(o.clip_score, n, np.int32),
-             cigar_off=arr(o.cigar_off, n, np.uint32), cigar_len=arr(o.cigar_len, n, np.uint32))
+             cigar_off=arr(o.cigar_off, n + 1, np.uint32))
     pool = arr(o.cigar, int(o.n_cigar_words), np.uint32)
-    d["cigars"] = [pool[int(a):int(a) + int(l)].copy() for a, l in zip(d["cigar_off"], d["cigar_len"])]
+    co = d["cigar_off"]
+    d["cigar_len"] = np.diff(co.astype(np.int64)).astype(np.uint32)
+    d["cigars"] = [pool[int(co[r]):int(co[r + 1])].copy() for r in range(n)]
     return d
 
 

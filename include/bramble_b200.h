@@ -94,17 +94,18 @@ typedef struct brb_batch_in {
 #define BRB_REC_SAMETX 4u   /* BamInfo::same_transcript */
 typedef struct brb_batch_out {
   uint32_t n_rec;
-  uint64_t n_cigar_words;               /* size of the cigar pool (with slack; use cigar_off/cigar_len) */
+  uint64_t n_cigar_words;               /* size of the cigar pool == cigar_off[n_rec] (dense, row order) */
   const uint32_t* group_rec_off;        /* n_groups+1: rows of group g */
   const uint32_t* src_aln;              /* input alignment the record is a projection of */
   const uint32_t* tid;
   const uint32_t* pos;                  /* fwpos or rcpos by transcript strand (src/core.cpp:153-158) */
   const int8_t*   tx_strand;            /* '+' or '-' */
   const uint8_t*  flags;                /* BRB_REC_* */
-  const double*   sim_score;            /* AlignInfo::similarity_score */
-  const int32_t*  clip_score;           /* AlignInfo::clip_score */
-  const uint32_t* cigar_off;            /* n_rec: start of the merged CIGAR in `cigar` */
-  const uint32_t* cigar_len;            /* n_rec: number of words; ALREADY reversed for '-' transcripts */
+  const double*   sim_score;            /* AlignInfo::similarity_score; NULL when filter_by_similarity == 0 and no clip rescue
+                                         * ran: every score is then 0.0, as in the reference (src/evaluate.cpp:843-865) */
+  const int32_t*  clip_score;           /* AlignInfo::clip_score; NULL under the same condition (all 0) */
+  const uint32_t* cigar_off;            /* n_rec+1: merged CIGAR of row r = cigar[cigar_off[r] .. cigar_off[r+1]),
+                                         * ALREADY reversed for '-' transcripts */
   const uint32_t* cigar;
 } brb_batch_out;
 

