@@ -181,6 +181,12 @@ def main():
 
     # ---- resident (kernel-only) timing
     eng.upload(B)
+    # algorithmic bytes are defined on the reference's algorithm, which looks up EVERY read exon: take
+    # them once, untimed, from the generic front kernel; the timed path is the engine's default choice
+    eng.set_option(capi.OPT_GENERIC_FRONT, 1)
+    eng.run_resident(p)
+    alg_ref = int(eng.stats().alg_bytes)
+    eng.set_option(capi.OPT_GENERIC_FRONT, 0)
     for _ in range(max(3, args.warmup)):
         eng.run_resident(p)
     st = eng.stats()
@@ -225,7 +231,7 @@ def main():
         step_ms = ms_max / args.steps
         value = total_aln * args.steps / (ms_max / 1e3)
         e2e = total_aln * args.steps / (e2e_ms_max / 1e3)
-        alg = int(st.alg_bytes)
+        alg = alg_ref
         achieved = alg / (ms / args.steps / 1e3) / 1e9
         names = {"ms_lookup": "k_lookup+k_fill_cand", "ms_chain": "k_chain", "ms_finalize": "k_build", "ms_pair": "k_pair_count+k_pair_emit",
                  "ms_merge": "k_merge", "ms_rescue": "k_ksw"}

@@ -15,6 +15,7 @@ LIB_PATH = os.path.join(_HERE, "libbramble_b200.so")
 
 BRB_OK, BRB_E_NO_DEVICE, BRB_E_CUDA, BRB_E_ARG, BRB_E_NOMEM, BRB_E_UNSUPPORTED = 0, -1, -2, -3, -4, -5
 REC_FIRST, REC_PAIRED, REC_SAMETX = 1, 2, 4
+OPT_GENERIC_FRONT = 1
 
 u8p, i8p = C.POINTER(C.c_uint8), C.POINTER(C.c_int8)
 u32p, i32p = C.POINTER(C.c_uint32), C.POINTER(C.c_int32)
@@ -107,6 +108,7 @@ def _declare(lib):
     lib.brb_project_resident.argtypes = [C.c_void_p, C.POINTER(Params)]
     lib.brb_batch_download.argtypes = [C.c_void_p, C.POINTER(BatchOut)]
     lib.brb_ctx_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
+    lib.brb_ctx_set_option.argtypes = [C.c_void_p, C.c_int, C.c_int]
     lib.brb_ctx_timer_start.argtypes = [C.c_void_p]
     lib.brb_ctx_timer_stop.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
     lib.brb_lookup.argtypes = [C.c_void_p, C.POINTER(Params), C.c_uint32, i32p, i8p, u32p, u32p, u8p, C.c_uint32, u32p, u32p]
@@ -117,7 +119,7 @@ def _declare(lib):
     lib.brb_host_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]
     lib.brb_host_free.argtypes = [C.c_void_p]
     for f in ("brb_index_create", "brb_index_destroy", "brb_ctx_create", "brb_ctx_destroy", "brb_project",
-              "brb_batch_upload", "brb_project_resident", "brb_batch_download", "brb_ctx_stats", "brb_ctx_timer_start",
+              "brb_batch_upload", "brb_project_resident", "brb_batch_download", "brb_ctx_stats", "brb_ctx_set_option", "brb_ctx_timer_start",
               "brb_ctx_timer_stop", "brb_lookup",
               "brb_merge_cigars", "brb_ksw_extend", "brb_sort_by_start", "brb_host_alloc", "brb_host_free"):
         getattr(lib, f).restype = C.c_int

@@ -59,7 +59,7 @@ struct Ctl {
   uint32_t n_tmpw, cap_tmpw;          // merge scratch pool words
   uint32_t n_outw, cap_outw;          // dense output CIGAR words
   uint32_t bad_input;                 // 1: mate link not symmetric, 2: read exons not ascending/disjoint
-  uint32_t pad1;
+  uint32_t ticket;                    // next batch of 32 alignments for k_front (dynamic scheduling)
 };
 __device__ __forceinline__ bool ctl_overflow(const Ctl* c) {
   return c->n_cand > c->cap_cand || c->n_ideal > c->cap_ideal || c->n_rows > c->cap_rows || c->n_tmpw > c->cap_tmpw ||
@@ -168,6 +168,28 @@ __device__ __forceinline__ uint32_t warp_alloc(uint32_t* __restrict__ counter, u
   base = __shfl_sync(0xffffffffu, base, 31);
   ok = (unsigned long long)base + tot <= cap;
   return base + incl - want;
+}
+
+
+// Bump allocation for PERSISTENT warps: the warp owns a private chunk of the pool and serves its lanes from
+// it; the global counter is touched once per chunk (a same-address atomic per 32 items was the top stall of
+// the first fused kernels).  Chunk tails left at the end are simply unused pool words.
+struct WarpPool { uint32_t cur, end; };
+constexpr uint32_t POOL_CHUNK = 2048;
+__device__ __forceinline__ uint32_t warp_pool_alloc(WarpPool& wp, uint32_t* __restrict__ counter, uint32_t cap, uint32_t want,
+                                                    unsigned lane, bool& ok) {
+  const uint32_t incl = warp_incl_scan(want, lane), tot = __shfl_sync(0xffffffffu, incl, 31);
+  if (tot > wp.end - wp.cur) {
+    const uint32_t grab = tot > POOL_CHUNK ? tot : POOL_CHUNK;
+    uint32_t base = 0;
+    if (lane == 0) base = atomicAdd(counter, grab);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    wp.cur = base; wp.end = base + grab;
+  }
+  ok = wp.end <= cap && wp.end >= wp.cur;          // the whole chunk lies inside the pool (and did not wrap)
+  const uint32_t off = wp.cur + incl - want;
+  wp.cur += tot;
+  return off;
 }
 
 }  // namespace brb

@@ -15,6 +15,7 @@
 #include "scan.cuh"
 #include "k_lookup.cuh"
 #include "k_chain.cuh"
+#include "k_fused.cuh"
 #include "k_ksw.cuh"
 #include "k_pair.cuh"
 #include "k_merge.cuh"
@@ -84,7 +85,7 @@ struct brb_ctx {
   DevBatch b{};
   Buf in_group_off, in_refid, in_strand, in_exon_off, in_exon_st, in_exon_en, in_cigar_off, in_cigar, in_mate, in_seq_off, in_seq;
   uint64_t in_bytes = 0, n_mates = 0, seq_bytes = 0, rescue_bytes = 0;
-  bool have_batch = false, have_result = false, have_scores = false;
+  bool have_batch = false, have_result = false, have_scores = false, opt_generic_front = false;
   // control block + pools (capacities persist across calls and only grow)
   Buf ctl;
   uint32_t cap_cand = 0, cap_ideal = 0, cap_rows = 0, cap_tmpw = 0, cap_outw = 0;
@@ -344,12 +345,12 @@ int ensure_pools(brb_ctx* c, bool rescue) {
   const size_t n = b.n_aln, C = c->cap_cand, R = c->cap_rows;
   ENS(c->q_any, (size_t)2 * b.n_exon + 16); ENS(c->a_cand, n * 16); ENS(c->a_cnt, n * 8);
   ENS(c->u_nrows, n * 4); ENS(c->u_roff, (n + 1) * 4); ENS(c->u_case, n); ENS(c->g_roff, (size_t)(b.n_groups + 1) * 4);
-  ENS(c->c_rec, C * 4); ENS(c->c_task, C * 4); ENS(c->c_partner, C * 4);
-  ENS(c->m_tid, C * 4); ENS(c->m_pos, C * 4); ENS(c->m_sim, C * 8); ENS(c->m_clip, C * 4); ENS(c->m_ilen, C * 4); ENS(c->m_ioff, C * 4);
-  if (rescue) { ENS(c->c_first, C * 4); ENS(c->c_last, C * 4); ENS(c->c_nseg, C * 4); ENS(c->c_nguide, C * 4); ENS(c->c_cap, C * 4); }
+  ENS(c->c_task, C * 4); ENS(c->c_partner, C * 4);
+  ENS(c->m_tid, C * 4); ENS(c->m_pos, C * 4); ENS(c->m_ilen, C * 4); ENS(c->m_ioff, C * 4);
+  if (c->have_scores) { ENS(c->m_sim, C * 8); ENS(c->m_clip, C * 4); ENS(c->o_sim, R * 8); ENS(c->o_clip, R * 4); }
+  if (rescue) { ENS(c->c_rec, C * 4); ENS(c->c_first, C * 4); ENS(c->c_last, C * 4); ENS(c->c_nseg, C * 4); ENS(c->c_nguide, C * 4); ENS(c->c_cap, C * 4); }
   ENS(c->ipool, (size_t)c->cap_ideal * 4);
   ENS(c->o_src, R * 4); ENS(c->o_tid, R * 4); ENS(c->o_pos, R * 4); ENS(c->o_strand, R); ENS(c->o_flags, R); ENS(c->o_cand, R * 4);
-  ENS(c->o_sim, R * 8); ENS(c->o_clip, R * 4);
   ENS(c->o_tmpoff, R * 4); ENS(c->o_clen, R * 4); ENS(c->o_coff, (R + 1) * 4);
   ENS(c->tpool, (size_t)c->cap_tmpw * 4); ENS(c->opool, (size_t)c->cap_outw * 4);
   ENS(c->scan_tmp, scan_scratch_words(std::max<size_t>(std::max<size_t>(n, R), 1)) * 4);
@@ -375,13 +376,21 @@ int project_resident(brb_ctx* c, const brb_params& p) {
     c->have_result = true; return BRB_OK;
   }
   if (!c->cap_cand) {           // first guess from the batch shape; a pool that overflows grows and the sequence replays
-    c->cap_cand = grown((uint64_t)8 * n); c->cap_rows = grown((uint64_t)6 * n);
-    c->cap_ideal = grown((uint64_t)4 * c->cap_cand + b.n_exon); c->cap_tmpw = grown((uint64_t)8 * c->cap_rows + 2 * (uint64_t)b.n_cigar);
+    c->cap_cand = grown((uint64_t)12 * n); c->cap_rows = grown((uint64_t)6 * n);
+    const uint64_t slack = (uint64_t)148 * 8 * 8 * POOL_CHUNK;          // unused chunk tails of the persistent warps
+    c->cap_ideal = grown((uint64_t)4 * c->cap_cand + b.n_exon + slack); c->cap_tmpw = grown((uint64_t)8 * c->cap_rows + 2 * (uint64_t)b.n_cigar + slack);
     c->cap_outw = grown((uint64_t)3 * c->cap_rows + b.n_cigar);
     if (getenv("BRB_TEST_SMALL_POOLS")) c->cap_cand = c->cap_rows = c->cap_ideal = c->cap_tmpw = c->cap_outw = 64;   // tests: force the grow-and-replay path
   }
-  int ncta = 148 * 8;
-  { int sm = 0; if (cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, c->idx->device) == cudaSuccess && sm > 0) ncta = sm * 8; }
+  int n_sm = 148;
+  { int sm = 0; if (cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, c->idx->device) == cudaSuccess && sm > 0) n_sm = sm; }
+  const int ncta = n_sm * 8;
+  auto resident = [&](const void* kern) { int nb = 0; if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, 256, 0) != cudaSuccess || nb < 1) nb = 1; return n_sm * nb; };
+  // short-read presets: only exon 0 is looked up, candidates verify the later exons themselves (k_front_short)
+  const bool short_front = !p.long_reads && !p.ignore_small_exons && !rescue && !c->opt_generic_front;
+  const void* front_fn = short_front ? (p.filter_by_similarity ? (const void*)k_front_short<true> : (const void*)k_front_short<false>)
+                                     : (rescue ? (const void*)k_front<false> : (const void*)k_front<true>);
+  const int ncta_front = resident(front_fn);
   Ctl* ctl = c->ctl.as<Ctl>();
   Ctl* hctl = c->h_small.as<Ctl>();
   uint64_t L = 0;
@@ -392,17 +401,25 @@ int project_resident(brb_ctx* c, const brb_params& p) {
     hctl->cap_cand = c->cap_cand; hctl->cap_ideal = c->cap_ideal; hctl->cap_rows = c->cap_rows; hctl->cap_tmpw = c->cap_tmpw; hctl->cap_outw = c->cap_outw;
     CU(cudaMemcpyAsync(ctl, hctl, sizeof(Ctl), cudaMemcpyHostToDevice, st));
     CU(cudaMemsetAsync(c->a_cnt.p, 0, (size_t)n * 8, st));
-    Matches M; M.tid = c->m_tid.as<uint32_t>(); M.pos = c->m_pos.as<uint32_t>(); M.sim = c->m_sim.as<double>(); M.clip = c->m_clip.as<int32_t>();
+    Matches M; M.tid = c->m_tid.as<uint32_t>(); M.pos = c->m_pos.as<uint32_t>();
+    M.sim = c->have_scores ? c->m_sim.as<double>() : nullptr; M.clip = c->have_scores ? c->m_clip.as<int32_t>() : nullptr;
     M.ilen = c->m_ilen.as<uint32_t>(); M.ioff = c->m_ioff.as<uint32_t>();
     // ---- phase 1: lookup + candidate lists
     CU(cudaEventRecord(c->ev[0], st));
-    k_lookup<<<grid_for(n, 256), 256, 0, st>>>(ix, b, p, ctl, c->q_any.as<uint8_t>(), c->a_cand.as<uint4>(), c->c_rec.as<uint32_t>(), c->c_task.as<uint32_t>()); L++;
-    CU(cudaEventRecord(c->ev[1], st));
-    // ---- phase 2..4: chain walk, (clip rescue), ideal CIGAR + scores
-    if (!rescue) {
-      k_eval<<<ncta, 256, 0, st>>>(ix, b, p, ctl, c->q_any.as<uint8_t>(), c->c_rec.as<uint32_t>(), c->c_task.as<uint32_t>(), c->ipool.as<uint32_t>(), M); L++;
-      CU(cudaEventRecord(c->ev[2], st)); CU(cudaEventRecord(c->ev[3], st)); CU(cudaEventRecord(c->ev[4], st));
+    // ---- phases 1..4: lookup, candidates, chain walk, (clip rescue), ideal CIGAR + scores
+    if (short_front) {
+      if (p.filter_by_similarity) k_front_short<true><<<ncta_front, 256, 0, st>>>(ix, b, p, ctl, c->a_cand.as<uint4>(), c->c_task.as<uint32_t>(), c->ipool.as<uint32_t>(), M);
+      else k_front_short<false><<<ncta_front, 256, 0, st>>>(ix, b, p, ctl, c->a_cand.as<uint4>(), c->c_task.as<uint32_t>(), c->ipool.as<uint32_t>(), M);
+      L++;
+      CU(cudaEventRecord(c->ev[1], st)); CU(cudaEventRecord(c->ev[2], st)); CU(cudaEventRecord(c->ev[3], st)); CU(cudaEventRecord(c->ev[4], st));
+    } else if (!rescue) {
+      k_front<true><<<ncta_front, 256, 0, st>>>(ix, b, p, ctl, c->q_any.as<uint8_t>(), c->a_cand.as<uint4>(), nullptr, c->c_task.as<uint32_t>(),
+                                          c->ipool.as<uint32_t>(), M); L++;
+      CU(cudaEventRecord(c->ev[1], st)); CU(cudaEventRecord(c->ev[2], st)); CU(cudaEventRecord(c->ev[3], st)); CU(cudaEventRecord(c->ev[4], st));
     } else {
+      k_front<false><<<ncta_front, 256, 0, st>>>(ix, b, p, ctl, c->q_any.as<uint8_t>(), c->a_cand.as<uint4>(), c->c_rec.as<uint32_t>(), c->c_task.as<uint32_t>(),
+                                           nullptr, M); L++;
+      CU(cudaEventRecord(c->ev[1], st));
       CandFacts F; F.first = c->c_first.as<uint32_t>(); F.last = c->c_last.as<uint32_t>(); F.nseg = c->c_nseg.as<uint32_t>();
       F.nguide = c->c_nguide.as<uint32_t>(); F.cap = c->c_cap.as<uint32_t>();
       k_chain<<<ncta, 256, 0, st>>>(ix, b, p, ctl, c->q_any.as<uint8_t>(), c->c_rec.as<uint32_t>(), c->c_task.as<uint32_t>(), F); L++;
@@ -526,6 +543,12 @@ int brb_project(brb_ctx* c, const brb_params* p, const brb_batch_in* in, brb_bat
   int rc = brb_batch_upload(c, in); if (rc) return rc;
   rc = brb_project_resident(c, p); if (rc) return rc;
   return brb_batch_download(c, out);
+}
+
+int brb_ctx_set_option(brb_ctx* c, int option, int value) {
+  if (!c) return fail(BRB_E_ARG, "null ctx");
+  if (option == BRB_OPT_GENERIC_FRONT) { c->opt_generic_front = value != 0; return BRB_OK; }
+  return fail(BRB_E_ARG, "unknown option %d", option);
 }
 
 int brb_ctx_timer_start(brb_ctx* c) {

@@ -71,22 +71,30 @@ struct WalkOut {         // pass-1 facts about a surviving candidate
   uint32_t first_rec, last_rec, n_seg, n_guide, cap;
 };
 
+struct ReadExons {       // the read side of a candidate: exon list of the alignment and its first exon
+  uint32_t e0, n_ex, qs0, qe0;
+};
+__device__ __forceinline__ ReadExons read_exons(const DevBatch& b, uint32_t a) {
+  ReadExons r; r.e0 = __ldg(&b.exon_off[a]); r.n_ex = __ldg(&b.exon_off[a + 1]) - r.e0;
+  r.qs0 = __ldg(&b.exon_st[r.e0]); r.qe0 = __ldg(&b.exon_en[r.e0]); return r;
+}
+
 // The chain walk.  BUILD=false: pass 1 (continuity, injectivity, counts; src/evaluate.cpp:111-182, 1004-1065).
 // BUILD=true: pass 2 (ideal CIGAR and score accumulators; :1067-1109).  Returns false if eliminated.
 template <bool BUILD>
-__device__ bool walk(const DevIndex& ix, const DevBatch& b, const brb_params& p, const uint8_t* __restrict__ q_any,
-                     uint32_t a, int s, uint32_t first_rec, WalkOut& w,
+__device__ bool walk(const DevIndex& ix, const DevBatch& b, const brb_params& p, const uint8_t* q_any,
+                     const ReadExons& rx, int s, uint32_t first_rec, WalkOut& w,
                      Builder* m, const RescueSeg* lres, const RescueSeg* rres, const uint32_t* __restrict__ rpool,
                      uint32_t& first_pos, uint32_t& last_pos) {
   const bool minus = s;
-  const uint32_t e0 = __ldg(&b.exon_off[a]), n_ex = __ldg(&b.exon_off[a + 1]) - e0;
+  const uint32_t e0 = rx.e0, n_ex = rx.n_ex;
   const bool has_lc = BUILD && lres && lres->ok, has_rc = BUILD && rres && rres->ok;
   uint32_t k = 0;                                   // segment index
   uint32_t n_seg = 0, n_guide = 0, cap = 0;
   uint32_t last_idx = BUILD ? w.n_guide - 1 : 0;    // last_match_idx: a COUNTER compared with the segment index (:1010-1011,1075-1076)
   uint32_t n_seg_total = BUILD ? w.n_seg : 0;
   // segment 0
-  uint32_t qs = __ldg(&b.exon_st[e0]), qe = __ldg(&b.exon_en[e0]);
+  uint32_t qs = rx.qs0, qe = rx.qe0;
   RecKey key = rec_key(ix.rec, first_rec);
   RecLink lk = rec_link(ix.rec, first_rec);
   Hit h; int status = exon_status(n_ex, 0);
@@ -113,7 +121,9 @@ __device__ bool walk(const DevIndex& ix, const DevBatch& b, const brb_params& p,
   for (uint32_t j = 1; j < n_ex; j++) {
     qs = __ldg(&b.exon_st[e0 + j]); qe = __ldg(&b.exon_en[e0 + j]);
     status = exon_status(n_ex, j);
-    if (!q_any[2 * (e0 + j) + s]) {                 // INS_EXON segment (:256-268); build_cigar_ins :788-806
+    // k_front records "no surviving hit" only for MIDDLE exons (any other hit-less exon failed the strand); the
+    // flag may have been written by another lane of this very kernel, hence the volatile load
+    if (p.ignore_small_exons && status == MIDDLE_EXON && !*(volatile const uint8_t*)(q_any + 2 * (e0 + j) + s)) {   // INS_EXON segment (:256-268); build_cigar_ins :788-806
       if (!BUILD) {
         if (qs == prev_qs && qe == prev_qe) return false;
         n_seg++; cap++;
@@ -205,10 +215,8 @@ __device__ bool walk(const DevIndex& ix, const DevBatch& b, const brb_params& p,
 // and the LAST hit's content.  Returns false if this candidate slot is not the first surviving hit of its
 // tid.  Duplicates can only be genomic neighbours of rec0 in the same transcript that also overlap read
 // exon 0, so the common case is decided by two compares on rec0's own link words.
-__device__ __forceinline__ bool dedupe_first(const DevIndex& ix, const DevBatch& b, const brb_params& p,
-                                             uint32_t a, int s, uint32_t& rec0) {
-  const uint32_t e0 = __ldg(&b.exon_off[a]), n_ex = __ldg(&b.exon_off[a + 1]) - e0;
-  const uint32_t qs = __ldg(&b.exon_st[e0]), qe = __ldg(&b.exon_en[e0]);
+__device__ __forceinline__ bool dedupe_first(const DevIndex& ix, const brb_params& p, const ReadExons& rx, int s, uint32_t& rec0) {
+  const uint32_t n_ex = rx.n_ex, qs = rx.qs0, qe = rx.qe0;
   const RecLink lk = rec_link(ix.rec, rec0);
   if (lk.gprev_en <= (int32_t)qs && lk.gnext_st >= (int32_t)qe) return true;
   const int status = exon_status(n_ex, 0);
@@ -232,14 +240,14 @@ struct Matches {          // per candidate slot; tid == NONE marks "no match"
 
 // Pass 2 for one candidate whose pass-1 facts are in `w`: ideal CIGAR into pool, scores, similarity filter
 // (src/evaluate.cpp:843-865, FP64, operation order kept), match row.
-__device__ __forceinline__ bool build_one(const DevIndex& ix, const DevBatch& b, const brb_params& p, uint32_t c, uint32_t a, int s,
-                                          const uint8_t* __restrict__ q_any, WalkOut w, const RescueSeg* L, const RescueSeg* R,
+__device__ __forceinline__ bool build_one(const DevIndex& ix, const DevBatch& b, const brb_params& p, uint32_t c, const ReadExons& rx, int s,
+                                          const uint8_t* q_any, WalkOut w, const RescueSeg* L, const RescueSeg* R,
                                           const uint32_t* __restrict__ rpool, uint32_t* __restrict__ ipool, uint32_t ioff, const Matches& M) {
   if (L && L->ok) { w.n_seg++; w.n_guide++; }
   if (R && R->ok) { w.n_seg++; w.n_guide++; }
   Builder m; m.init(ipool + ioff);
   uint32_t fp = 0, lp = 0;
-  walk<true>(ix, b, p, q_any, a, s, w.first_rec, w, &m, L, R, rpool, fp, lp);
+  walk<true>(ix, b, p, q_any, rx, s, w.first_rec, w, &m, L, R, rpool, fp, lp);
   double sim_score = 0.0; bool keep = true;
   if (p.filter_by_similarity) {
     const double thr = (double)p.similarity_threshold;
@@ -249,41 +257,9 @@ __device__ __forceinline__ bool build_one(const DevIndex& ix, const DevBatch& b,
   }
   M.tid[c] = keep ? rec_key(ix.rec, w.first_rec).tid : NONE;
   M.pos[c] = s ? lp : fp;
-  M.sim[c] = sim_score; M.clip[c] = m.clip; M.ilen[c] = m.n; M.ioff[c] = ioff;
+  if (M.sim) { M.sim[c] = sim_score; M.clip[c] = m.clip; }      // null when every score is 0 by construction
+  M.ilen[c] = m.n; M.ioff[c] = ioff;
   return keep;
-}
-
-// Fused evaluation (no clip rescue): pass 1, pool allocation and pass 2 in one kernel.  Persistent warps
-// over the candidate slots; the slot count is read from the control block (no host round trip).
-__global__ void __launch_bounds__(256) k_eval(DevIndex ix, DevBatch b, brb_params p, Ctl* __restrict__ ctl,
-                                              const uint8_t* __restrict__ q_any, const uint32_t* __restrict__ c_rec,
-                                              const uint32_t* __restrict__ c_task, uint32_t* __restrict__ ipool, Matches M) {
-  if (ctl_overflow(ctl)) return;
-  const unsigned lane = threadIdx.x & 31;
-  const uint32_t n_cand = ctl->n_cand;
-  const uint32_t stride = gridDim.x * blockDim.x;
-  uint32_t kept = 0;
-  for (uint32_t base = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); base < n_cand; base += stride) {
-    const uint32_t c = base + lane;
-    const bool act = c < n_cand;
-    uint32_t a = 0; int s = 0; WalkOut w; w.cap = 0;
-    bool ok = false;
-    if (act) {
-      const uint32_t task = c_task[c]; a = task >> 1; s = task & 1;
-      uint32_t rec0 = c_rec[c];
-      uint32_t fp, lp;
-      ok = dedupe_first(ix, b, p, a, s, rec0);
-      if (ok) ok = walk<false>(ix, b, p, q_any, a, s, rec0, w, nullptr, nullptr, nullptr, nullptr, fp, lp);
-    }
-    bool fits;
-    const uint32_t ioff = warp_alloc(&ctl->n_ideal, ctl->cap_ideal, ok ? w.cap : 0, lane, fits);
-    if (act) {
-      if (ok && fits) kept += build_one(ix, b, p, c, a, s, q_any, w, nullptr, nullptr, nullptr, ipool, ioff, M) ? 1u : 0u;
-      else M.tid[c] = NONE;
-    }
-  }
-  for (int d = 16; d; d >>= 1) kept += __shfl_down_sync(0xffffffffu, kept, d);
-  if (lane == 0 && kept) atomicAdd(&ctl->n_matches, (unsigned long long)kept);
 }
 
 // Split form for the clip-rescue path (long reads with a genome): pass 1 here, then k_rescue_* / k_ksw
@@ -291,7 +267,7 @@ __global__ void __launch_bounds__(256) k_eval(DevIndex ix, DevBatch b, brb_param
 struct CandFacts { uint32_t* first; uint32_t* last; uint32_t* nseg; uint32_t* nguide; uint32_t* cap; };
 
 __global__ void __launch_bounds__(256) k_chain(DevIndex ix, DevBatch b, brb_params p, const Ctl* __restrict__ ctl,
-                                               const uint8_t* __restrict__ q_any, const uint32_t* __restrict__ c_rec,
+                                               const uint8_t* q_any, const uint32_t* __restrict__ c_rec,
                                                const uint32_t* __restrict__ c_task, CandFacts F) {
   if (ctl_overflow(ctl)) return;
   const uint32_t n_cand = ctl->n_cand;
@@ -300,15 +276,16 @@ __global__ void __launch_bounds__(256) k_chain(DevIndex ix, DevBatch b, brb_para
     uint32_t rec0 = c_rec[c];
     WalkOut w; w.cap = 0; w.first_rec = rec0; w.last_rec = rec0; w.n_seg = 0; w.n_guide = 0;
     uint32_t fp, lp;
-    bool ok = dedupe_first(ix, b, p, a, s, rec0);
-    if (ok) ok = walk<false>(ix, b, p, q_any, a, s, rec0, w, nullptr, nullptr, nullptr, nullptr, fp, lp);
+    const ReadExons rx = read_exons(b, a);
+    bool ok = dedupe_first(ix, p, rx, s, rec0);
+    if (ok) ok = walk<false>(ix, b, p, q_any, rx, s, rec0, w, nullptr, nullptr, nullptr, nullptr, fp, lp);
     F.first[c] = w.first_rec; F.last[c] = w.last_rec; F.nseg[c] = w.n_seg; F.nguide[c] = w.n_guide;
     F.cap[c] = ok ? w.cap : 0;
   }
 }
 
 __global__ void __launch_bounds__(256) k_build(DevIndex ix, DevBatch b, brb_params p, Ctl* __restrict__ ctl,
-                                               const uint8_t* __restrict__ q_any, const uint32_t* __restrict__ c_task, CandFacts F,
+                                               const uint8_t* q_any, const uint32_t* __restrict__ c_task, CandFacts F,
                                                const RescueSeg* __restrict__ r_left, const RescueSeg* __restrict__ r_right,
                                                const uint32_t* __restrict__ rpool, uint32_t* __restrict__ ipool, Matches M) {
   if (ctl_overflow(ctl)) return;
@@ -316,22 +293,130 @@ __global__ void __launch_bounds__(256) k_build(DevIndex ix, DevBatch b, brb_para
   const uint32_t n_cand = ctl->n_cand;
   const uint32_t stride = gridDim.x * blockDim.x;
   uint32_t kept = 0;
+  WarpPool wp; wp.cur = 0; wp.end = 0;
+  const uint32_t cap_ideal = ctl->cap_ideal;
   for (uint32_t base = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); base < n_cand; base += stride) {
     const uint32_t c = base + lane;
     const bool act = c < n_cand;
     const uint32_t cap = act ? F.cap[c] : 0;
     bool fits;
-    const uint32_t ioff = warp_alloc(&ctl->n_ideal, ctl->cap_ideal, cap, lane, fits);
+    const uint32_t ioff = warp_pool_alloc(wp, &ctl->n_ideal, cap_ideal, cap, lane, fits);
     if (!act) continue;
     if (cap == 0 || !fits) { M.tid[c] = NONE; continue; }
     const uint32_t task = c_task[c], a = task >> 1; const int s = task & 1;
     WalkOut w; w.first_rec = F.first[c]; w.last_rec = F.last[c]; w.n_seg = F.nseg[c]; w.n_guide = F.nguide[c]; w.cap = cap;
     RescueSeg L, R; L.ok = 0; R.ok = 0;
     if (r_left) { L = r_left[c]; R = r_right[c]; }
-    kept += build_one(ix, b, p, c, a, s, q_any, w, r_left ? &L : nullptr, r_left ? &R : nullptr, rpool, ipool, ioff, M) ? 1u : 0u;
+    kept += build_one(ix, b, p, c, read_exons(b, a), s, q_any, w, r_left ? &L : nullptr, r_left ? &R : nullptr, rpool, ipool, ioff, M) ? 1u : 0u;
   }
   for (int d = 16; d; d >>= 1) kept += __shfl_down_sync(0xffffffffu, kept, d);
   if (lane == 0 && kept) atomicAdd(&ctl->n_matches, (unsigned long long)kept);
+}
+
+}  // namespace brb
+
+namespace brb {
+
+// ---- short-read specialisation -----------------------------------------------------------------------------
+// With the short-read presets (ShortReadEvaluator, src/evaluate.cpp:1136-1175: !LONG_READS, max_error_exon == 0)
+// there are no INS_EXON / GAP_EXON / clip segments, so a surviving candidate has exactly one guide-bearing
+// segment per read exon: n_seg = n_guide = n_ex is known up front, and pass 1 (elimination) and pass 2
+// (ideal CIGAR + scores) collapse into one walk.  SIM=false removes the FP64 accumulators, which only feed
+// filter_by_similarity.
+template <bool SIM>
+struct ShortBuilder {
+  uint32_t* cig; uint32_t n, last, prev_op; int32_t junc; double cov, ops;
+  __device__ __forceinline__ void init(uint32_t* pool) { cig = pool; n = 0; last = 0; prev_op = CM; junc = 0; cov = 0.0; ops = 0.0; }
+  __device__ __forceinline__ void add(uint32_t len, uint32_t op) {
+    if (n > 0 && (last & 0xfu) == op) last = (((last >> 4) + len) << 4) | op;
+    else { if (n > 0) cig[n - 1] = last; last = (len << 4) | op; n++; }
+  }
+  __device__ __forceinline__ void finish() { if (n > 0) cig[n - 1] = last; }
+  __device__ __forceinline__ void add_ops(uint32_t v) { if (SIM) ops += v; }
+  __device__ __forceinline__ void add_cov(uint32_t v) { if (SIM) cov += v; }
+  __device__ __forceinline__ void penal() { if (SIM) ops += (ops * 0.2); }
+};
+
+// build_cigar_match (src/evaluate.cpp:675-786) without clip segments (has_left_clip = has_right_clip = false)
+template <bool SIM>
+__device__ __forceinline__ void build_match_short(ShortBuilder<SIM>& m, int st, uint32_t qs, uint32_t qe, uint32_t gs, uint32_t ge, const Hit& h,
+                                                  bool first_match, bool last_match) {
+  if (h.left_ins > 0) {
+    if (st == FIRST_EXON || st == ONLY_EXON) { m.add(h.left_ins, CS); m.add_ops(h.left_ins); m.prev_op = CS; }
+    else {
+      m.add(h.left_ins, CI); m.add_ops(h.left_ins);
+      if (m.prev_op == CD) m.add_cov(h.left_ins); else if (m.prev_op == CI) m.penal();
+      m.prev_op = CI;
+    }
+  } else if (h.left_gap > 0) {
+    if (!first_match && (st == MIDDLE_EXON || st == LAST_EXON)) {
+      m.add(h.left_gap, CD); m.add_ops(h.left_gap);
+      if (m.prev_op == CI) m.add_cov(h.left_gap); else if (m.prev_op == CD) m.penal();
+      m.prev_op = CD;
+    }
+  } else m.junc++;
+  const uint32_t os = qs > gs ? qs : gs, oe = qe < ge ? qe : ge;
+  if (oe >= os) { const uint32_t len = oe - os; m.add(len, CM); m.add_ops(len); m.add_cov(len); m.prev_op = CM; }
+  if (h.right_ins > 0) {
+    if (st == LAST_EXON || st == ONLY_EXON) { m.add(h.right_ins, CS); m.add_ops(h.right_ins); m.prev_op = CS; }
+    else { m.add(h.right_ins, CI); m.add_ops(h.right_ins); if (m.prev_op == CD) m.add_cov(h.right_ins); m.prev_op = CI; }
+  } else if (h.right_gap > 0) {
+    if (!last_match && (st == FIRST_EXON || st == MIDDLE_EXON)) {
+      m.add(h.right_gap, CD); m.add_ops(h.right_gap); if (m.prev_op == CI) m.add_cov(h.right_gap); m.prev_op = CD;
+    }
+  } else m.junc++;
+}
+
+// One candidate, one walk.  `key`/`lk` describe rec0 (already the duplicate-rule winner).  Returns false when the
+// candidate is eliminated; otherwise the ideal CIGAR is in cig[0..ilen) and pos / sim_score are set.
+template <bool SIM>
+__device__ __forceinline__ bool eval_short(const DevIndex& ix, const DevBatch& b, const brb_params& p, const ReadExons& rx, int s,
+                                           RecKey key, RecLink lk, uint32_t* __restrict__ cig, uint32_t& pos, uint32_t& ilen, double& sim_score) {
+  const bool minus = s;
+  const uint32_t n_ex = rx.n_ex;
+  ShortBuilder<SIM> m; m.init(cig);
+  uint32_t qs = rx.qs0, qe = rx.qe0;
+  int status = exon_status(n_ex, 0);
+  Hit h;
+  filter_hit(p, minus, status, qs, qe, (uint32_t)key.st, (uint32_t)key.en, key.pos_start, h);
+  const uint32_t first_pos = h.pos; uint32_t last_pos = h.pos;
+  build_match_short<SIM>(m, status, qs, qe, (uint32_t)key.st, (uint32_t)key.en, h, true, n_ex == 1);
+  uint32_t prev_eid = lk.meta & 0xffu;
+  for (uint32_t j = 1; j < n_ex; j++) {
+    const uint32_t prev_qs = qs, prev_qe = qe;
+    qs = __ldg(&b.exon_st[rx.e0 + j]); qe = __ldg(&b.exon_en[rx.e0 + j]);
+    status = exon_status(n_ex, j);
+    // surviving hits of this transcript on read exon j (see walk<>): exactly one, and not the previous record again
+    uint32_t cnt = 0; RecKey nk = key; RecLink nl = lk;
+    if ((int32_t)qs < key.en && passes_filter(p, minus, status, qs, qe, (uint32_t)key.st, (uint32_t)key.en)) return false;   // same guide exon twice: gap 0
+    uint32_t r = lk.gnext; int32_t r_st = lk.gnext_st;
+    while (r != NONE && r_st < (int32_t)qe) {
+      const RecKey K = rec_key(ix.rec, r); const RecLink Lr = rec_link(ix.rec, r);
+      if ((int32_t)qs < K.en) {
+        Hit hh;
+        if (filter_hit(p, minus, status, qs, qe, (uint32_t)K.st, (uint32_t)K.en, K.pos_start, hh)) { if (cnt == 0) { nk = K; nl = Lr; h = hh; } cnt++; }
+      }
+      r = Lr.gnext; r_st = Lr.gnext_st;
+    }
+    if (cnt != 1) return false;
+    const uint32_t eid = nl.meta & 0xffu;
+    if (((eid - prev_eid) & 0xffu) != 1) return false;            // correct_for_gaps, short reads: uint8_t gap != 1 (src/evaluate.cpp:131-140)
+    if (qs == prev_qs && qe == prev_qe) return false;             // injectivity on the read side (:1031-1052); guide side differs since gap == 1
+    key = nk; lk = nl; prev_eid = eid;
+    last_pos = h.pos;
+    build_match_short<SIM>(m, status, qs, qe, (uint32_t)key.st, (uint32_t)key.en, h, false, j == n_ex - 1);
+  }
+  m.finish();
+  if (m.junc < 0) m.junc = 0;
+  sim_score = 0.0;
+  if (SIM) {                                                      // filter_by_similarity, src/evaluate.cpp:843-865 (FP64, operation order kept)
+    const double thr = (double)p.similarity_threshold;
+    const double sim = (m.ops > 0) ? (m.cov / m.ops) : 0.0;
+    if (!(sim > thr)) return false;
+    const double x = (sim - thr) / (1.0 - thr); sim_score = x * x * (double)(m.junc + 1);
+  }
+  pos = minus ? last_pos : first_pos; ilen = m.n;
+  return true;
 }
 
 }  // namespace brb

@@ -1,0 +1,270 @@
+// The front half of the projection as ONE persistent kernel: exon-overlap lookup, candidate enumeration and
+// (FUSED) the whole per-candidate evaluation -- reference g2tTree::getGuideExons (src/g2t.cpp:103-257),
+// get_intervals (src/evaluate.cpp:184-282) and evaluate_exon_chains (:888-1134) for a bundle.
+//
+// Work mapping.  A warp takes batches of 32 consecutive alignments (lane = alignment) in a grid-stride loop.
+//   pass 1  for every (strand, exon index) round each lane brackets its query's index range through the bin
+//           directory, then the warp walks the CONCATENATION of the 32 ranges 32 records at a time
+//           (lane = record): a read hitting 200 isoforms of a hot gene costs 7 full rounds, not 200 single-lane
+//           ones.  Ballots return survivors / first / last survivor to the owning lane.
+//   alloc   one atomic per batch reserves the candidate slots of its 32 alignments ('+' task before '-' task,
+//           slots of an alignment contiguous -- pairing relies on that).
+//   pass 2  the tightened exon-0 ranges are walked again the same way; now lane = candidate transcript.  FUSED:
+//           the lane evaluates its candidate in place (duplicate-tid rule, chain walk, ideal CIGAR, similarity)
+//           with the record key already in registers and the read's exons hot in L1, and writes the match row.
+//           !FUSED (clip-rescue path): the lane only records (record, task) for k_chain / k_ksw / k_build.
+#pragma once
+#include "dev_common.cuh"
+#include "k_lookup.cuh"
+#include "k_chain.cuh"
+
+namespace brb {
+
+// a_cand[a] = { first candidate slot, #slots of task 2a ('+'), #slots of task 2a+1 ('-'), 0 }
+template <bool FUSED>
+__global__ void __launch_bounds__(256) k_front(DevIndex ix, DevBatch b, brb_params p, Ctl* __restrict__ ctl,
+                                               uint8_t* q_any, uint4* __restrict__ a_cand,
+                                               uint32_t* __restrict__ c_rec, uint32_t* __restrict__ c_task,
+                                               uint32_t* __restrict__ ipool, Matches M) {
+  const unsigned lane = threadIdx.x & 31;
+  const uint32_t n_batches = (b.n_aln + 31) >> 5;
+  const uint32_t cap_cand = ctl->cap_cand, cap_ideal = ctl->cap_ideal;       // constant during the launch
+  WarpPool wp; wp.cur = 0; wp.end = 0;
+  unsigned long long my_hits = 0;
+  uint32_t bad = 0, n_mates = 0, kept = 0;
+  for (;;) {
+    uint32_t wb = 0;                                        // dynamic batch tickets: batches differ a lot in cost (hot genes)
+    if (lane == 0) wb = atomicAdd(&ctl->ticket, 1u);
+    wb = __shfl_sync(0xffffffffu, wb, 0);
+    if (wb >= n_batches) break;
+    const uint32_t a = wb * 32 + lane;
+    const bool valid = a < b.n_aln;
+    uint32_t e0 = 0, n_ex = 0; int32_t refid = -1; bool act[2] = {false, false};
+    if (valid) {
+      e0 = __ldg(&b.exon_off[a]); n_ex = __ldg(&b.exon_off[a + 1]) - e0; refid = __ldg(&b.refid[a]);
+      const int8_t sd = b.strand[a];
+      act[0] = task_active(p, sd, 0); act[1] = task_active(p, sd, 1);
+      const int32_t m = __ldg(&b.mate_idx[a]);             // process_pairs links are single and symmetric (src/bramble.cpp:272-311)
+      if (m >= 0 && ((uint32_t)m >= b.n_aln || (uint32_t)m == a || __ldg(&b.mate_idx[m]) != (int32_t)a)) bad = 1;
+      if (m >= 0) n_mates++;
+    }
+    bool fail[2]; uint32_t ncand[2] = {0, 0}, clo[2] = {0, 0}, chi[2] = {0, 0};
+    uint32_t st0 = 0, en0 = 0;                              // exon 0 (kept for pass 2)
+    // ---- pass 1
+#pragma unroll
+    for (int s = 0; s < 2; s++) {
+      fail[s] = (n_ex == 0);
+      const uint32_t maxj = __reduce_max_sync(0xffffffffu, (valid && (act[s] || s == 0)) ? n_ex : 0u);
+      uint32_t prev_en = 0;
+      for (uint32_t j = 0; j < maxj; j++) {
+        const bool in = valid && j < n_ex;
+        const bool have = in && act[s] && !fail[s];
+        uint32_t qs = 0, qe = 0, lo = 0, n = 0; int status = 0;
+        if (in && (have || s == 0)) {
+          qs = __ldg(&b.exon_st[e0 + j]); qe = __ldg(&b.exon_en[e0 + j]);
+          if (s == 0) { if (qe < qs || (j > 0 && qs < prev_en)) bad = 2; prev_en = qe; }   // read exons ascending and disjoint (CIGAR order)
+          if (j == 0) { st0 = qs; en0 = qe; }
+        }
+        if (have) {
+          status = exon_status(n_ex, j);
+          uint32_t hi; overlap_range(ix, refid, s, qs, qe, lo, hi); n = hi - lo;
+        }
+        FlatOut f;
+        warp_flat_count(ix, p, s, lane, lo, n, qs, qe, status, f);
+        if (have) {
+          my_hits += f.nhit;
+          if (status == MIDDLE_EXON) q_any[2 * (e0 + j) + s] = f.nf ? 1 : 0;     // only a MIDDLE exon can become an INS_EXON segment
+          if (j == 0) { ncand[s] = f.nf; clo[s] = f.first; chi[s] = f.last; }
+          if (f.nf == 0) {
+            // src/evaluate.cpp:249-281: only a small MIDDLE exon may be skipped (data is non-empty for j>0)
+            const bool small = (qe - qs <= p.max_error_exon);
+            if (!(status == MIDDLE_EXON && p.ignore_small_exons && small)) fail[s] = true;
+          }
+        }
+      }
+      if (fail[s] || !act[s]) ncand[s] = 0;
+    }
+    // ---- candidate slots of the batch
+    const uint32_t tot = ncand[0] + ncand[1];
+    const uint32_t incl_t = warp_incl_scan(tot, lane), wtot = __shfl_sync(0xffffffffu, incl_t, 31);
+    uint32_t sbase = 0;
+    if (lane == 31 && wtot) sbase = atomicAdd(&ctl->n_cand, wtot);
+    sbase = __shfl_sync(0xffffffffu, sbase, 31);
+    const uint32_t off0 = sbase + incl_t - tot, off1 = off0 + ncand[0];
+    if (valid) a_cand[a] = make_uint4(off0, ncand[0], ncand[1], 0);
+    const bool slots_fit = (unsigned long long)sbase + wtot <= cap_cand;
+    if (!wtot) continue;
+    __syncwarp();                                           // q_any of this batch is visible to its candidate lanes
+    // ---- pass 2
+#pragma unroll
+    for (int s = 0; s < 2; s++) {
+      const uint32_t lo = clo[s], n = ncand[s] ? chi[s] - clo[s] : 0, dst = s ? off1 : off0;
+      const uint32_t incl = warp_incl_scan(n, lane), excl = incl - n;
+      const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+      uint32_t written = 0;
+      for (uint32_t base = 0; base < total; base += 32) {
+        const uint32_t item = base + lane;
+        const bool actv = item < total;
+        const unsigned L = warp_owner(incl, actv ? item : total - 1);
+        const uint32_t o_lo = __shfl_sync(0xffffffffu, lo, L), o_ex = __shfl_sync(0xffffffffu, excl, L);
+        ReadExons rx;
+        rx.qs0 = __shfl_sync(0xffffffffu, st0, L); rx.qe0 = __shfl_sync(0xffffffffu, en0, L);
+        rx.e0 = __shfl_sync(0xffffffffu, e0, L); rx.n_ex = __shfl_sync(0xffffffffu, n_ex, L);
+        const uint32_t i = o_lo + (item - o_ex);
+        bool sv = false;
+        if (actv) {
+          const RecKey k = rec_key(ix.rec, i);
+          sv = (int32_t)rx.qs0 < k.en && passes_filter(p, s, exon_status(rx.n_ex, 0), rx.qs0, rx.qe0, (uint32_t)k.st, (uint32_t)k.en);
+        }
+        const uint32_t B = __ballot_sync(0xffffffffu, sv);
+        uint32_t mine = 0;
+        if (n && incl > base && excl < base + 32) mine = bit_range(excl > base ? excl - base : 0, incl - base < 32 ? incl - base : 32);
+        const uint32_t o_mine = __shfl_sync(0xffffffffu, mine, L), o_wr = __shfl_sync(0xffffffffu, written, L);
+        const uint32_t o_dst = __shfl_sync(0xffffffffu, dst, L);
+        const uint32_t slot = o_dst + o_wr + __popc(B & o_mine & ((1u << lane) - 1u));
+        const uint32_t task = 2 * (wb * 32 + L) + s;
+        written += __popc(B & mine);
+        if (!FUSED) {
+          if (sv && slots_fit) { c_rec[slot] = i; c_task[slot] = task; }
+        } else {
+          bool ok = false; WalkOut w; w.cap = 0; w.first_rec = i; w.last_rec = i; w.n_seg = 0; w.n_guide = 0;
+          if (sv) {
+            uint32_t rec0 = i, fp, lp;
+            ok = dedupe_first(ix, p, rx, s, rec0);
+            if (ok) ok = walk<false>(ix, b, p, q_any, rx, s, rec0, w, nullptr, nullptr, nullptr, nullptr, fp, lp);
+          }
+          bool pool_fit;
+          const uint32_t ioff = warp_pool_alloc(wp, &ctl->n_ideal, cap_ideal, ok ? w.cap : 0, lane, pool_fit);
+          if (sv && slots_fit) {
+            c_task[slot] = task;
+            if (ok && pool_fit) kept += build_one(ix, b, p, slot, rx, s, q_any, w, nullptr, nullptr, nullptr, ipool, ioff, M) ? 1u : 0u;
+            else M.tid[slot] = NONE;
+          }
+        }
+      }
+    }
+  }
+  // work counters (algorithmic-bytes numerator) + input validation: one atomic per warp
+  for (int d = 16; d; d >>= 1) { my_hits += __shfl_down_sync(0xffffffffu, my_hits, d); kept += __shfl_down_sync(0xffffffffu, kept, d);
+                                 n_mates += __shfl_down_sync(0xffffffffu, n_mates, d); }
+  if (lane == 0) {
+    if (my_hits) atomicAdd(&ctl->n_hits, my_hits);
+    if (kept) atomicAdd(&ctl->n_matches, (unsigned long long)kept);
+    if (n_mates) atomicAdd(&ctl->n_mates, (unsigned long long)n_mates);
+  }
+  const uint32_t anybad = __reduce_max_sync(0xffffffffu, bad);
+  if (lane == 0 && anybad) atomicMax(&ctl->bad_input, anybad);
+}
+
+
+// ---- short-read front kernel ---------------------------------------------------------------------------------
+// Short-read presets (!long_reads, max_error_exon == 0, no clip rescue): a read exon without a surviving hit
+// fails the strand (src/evaluate.cpp:249-281), and a candidate whose transcript misses an exon is eliminated by
+// its own walk -- so only EXON 0 has to be looked up; every later exon is checked by following the candidate's
+// exon chain.  That leaves one flat pass per batch of 32 alignments: bracket the exon-0 range(s) of each lane
+// (both strands side by side), reserve one candidate slot per record of those ranges with a single atomic, then
+// walk the concatenated ranges 32 records at a time; a lane whose record survives the overlap + tolerance
+// filters evaluates that candidate on the spot (eval_short) and writes its match row, every other slot is
+// marked empty.  (n_hits then only counts exon-0 hits; the reference-defined figure for the roofline numerator
+// comes from the generic kernel, see BRB_OPT_GENERIC_FRONT.)
+template <bool SIM>
+__global__ void __launch_bounds__(256) k_front_short(DevIndex ix, DevBatch b, brb_params p, Ctl* __restrict__ ctl,
+                                                     uint4* __restrict__ a_cand, uint32_t* __restrict__ c_task,
+                                                     uint32_t* __restrict__ ipool, Matches M) {
+  const unsigned lane = threadIdx.x & 31;
+  const uint32_t n_batches = (b.n_aln + 31) >> 5;
+  const uint32_t cap_cand = ctl->cap_cand, cap_ideal = ctl->cap_ideal;       // constant during the launch
+  WarpPool wp; wp.cur = 0; wp.end = 0;
+  unsigned long long my_hits = 0;
+  uint32_t bad = 0, n_mates = 0, kept = 0;
+  for (;;) {
+    uint32_t wb = 0;                                        // dynamic batch tickets: batches differ a lot in cost (hot genes)
+    if (lane == 0) wb = atomicAdd(&ctl->ticket, 1u);
+    wb = __shfl_sync(0xffffffffu, wb, 0);
+    if (wb >= n_batches) break;
+    const uint32_t a = wb * 32 + lane;
+    ReadExons rx; rx.e0 = 0; rx.n_ex = 0; rx.qs0 = 0; rx.qe0 = 0;
+    uint32_t lo0 = 0, n0 = 0, lo1 = 0, n1 = 0;
+    if (a < b.n_aln) {
+      rx.e0 = __ldg(&b.exon_off[a]); rx.n_ex = __ldg(&b.exon_off[a + 1]) - rx.e0;
+      const int32_t refid = __ldg(&b.refid[a]);
+      const int8_t sd = b.strand[a];
+      const int32_t m = __ldg(&b.mate_idx[a]);             // process_pairs links are single and symmetric (src/bramble.cpp:272-311)
+      if (m >= 0 && ((uint32_t)m >= b.n_aln || (uint32_t)m == a || __ldg(&b.mate_idx[m]) != (int32_t)a)) bad = 1;
+      if (m >= 0) n_mates++;
+      if (rx.n_ex) {
+        rx.qs0 = __ldg(&b.exon_st[rx.e0]); rx.qe0 = __ldg(&b.exon_en[rx.e0]);
+        uint32_t pe = rx.qe0; if (rx.qe0 < rx.qs0) bad = 2;
+        for (uint32_t j = 1; j < rx.n_ex; j++) {            // read exons ascending and disjoint (CIGAR order)
+          const uint32_t qs = __ldg(&b.exon_st[rx.e0 + j]), qe = __ldg(&b.exon_en[rx.e0 + j]);
+          if (qe < qs || qs < pe) bad = 2;
+          pe = qe;
+        }
+        uint32_t hi;
+        if (task_active(p, sd, 0)) { overlap_range(ix, refid, false, rx.qs0, rx.qe0, lo0, hi); n0 = hi - lo0; }
+        if (task_active(p, sd, 1)) { overlap_range(ix, refid, true, rx.qs0, rx.qe0, lo1, hi); n1 = hi - lo1; }
+      }
+    }
+    const uint32_t n = n0 + n1;
+    const uint32_t incl = warp_incl_scan(n, lane), excl = incl - n, total = __shfl_sync(0xffffffffu, incl, 31);
+    uint32_t sbase = 0;
+    if (lane == 31 && total) sbase = atomicAdd(&ctl->n_cand, total);
+    sbase = __shfl_sync(0xffffffffu, sbase, 31);
+    if (a < b.n_aln) a_cand[a] = make_uint4(sbase + excl, n0, n1, 0);
+    const bool slots_fit = (unsigned long long)sbase + total <= cap_cand;
+    const int status0 = exon_status(rx.n_ex, 0);
+    for (uint32_t base = 0; base < total; base += 32) {
+      const uint32_t item = base + lane;
+      const bool actv = item < total;
+      const unsigned L = warp_owner(incl, actv ? item : total - 1);
+      ReadExons ox;
+      ox.qs0 = __shfl_sync(0xffffffffu, rx.qs0, L); ox.qe0 = __shfl_sync(0xffffffffu, rx.qe0, L);
+      ox.e0 = __shfl_sync(0xffffffffu, rx.e0, L); ox.n_ex = __shfl_sync(0xffffffffu, rx.n_ex, L);
+      const uint32_t o_ex = __shfl_sync(0xffffffffu, excl, L), o_n0 = __shfl_sync(0xffffffffu, n0, L);
+      const uint32_t o_lo0 = __shfl_sync(0xffffffffu, lo0, L), o_lo1 = __shfl_sync(0xffffffffu, lo1, L);
+      const int o_status = __shfl_sync(0xffffffffu, status0, L);
+      const uint32_t idx = item - o_ex;
+      const int s = idx >= o_n0;
+      uint32_t rec0 = s ? o_lo1 + (idx - o_n0) : o_lo0 + idx;
+      const uint32_t slot = sbase + item;
+      bool sv = false, ov = false; RecKey key;
+      if (actv) {
+        key = rec_key(ix.rec, rec0);
+        ov = (int32_t)ox.qs0 < key.en;                     // st < qe holds for every record below hi
+        sv = ov && passes_filter(p, s, o_status, ox.qs0, ox.qe0, (uint32_t)key.st, (uint32_t)key.en);
+      }
+      my_hits += __popc(__ballot_sync(0xffffffffu, ov)) * (lane == 0);
+      const uint32_t want = sv ? 3 * ox.n_ex : 0;           // at most S/I/D + M + S/I/D per read exon
+      bool pool_fit;
+      const uint32_t ioff = warp_pool_alloc(wp, &ctl->n_ideal, cap_ideal, want, lane, pool_fit);
+      if (!actv || !slots_fit) continue;
+      bool ok = false; uint32_t pos = 0, ilen = 0; double sim = 0.0;
+      if (sv && pool_fit) {
+        RecLink lk = rec_link(ix.rec, rec0);
+        ok = true;
+        if (lk.gprev_en > (int32_t)ox.qs0 || lk.gnext_st < (int32_t)ox.qe0) {      // a neighbour exon of this tid also overlaps read exon 0
+          const uint32_t r1 = rec0;
+          ok = dedupe_first(ix, p, ox, s, rec0);
+          if (ok && rec0 != r1) { key = rec_key(ix.rec, rec0); lk = rec_link(ix.rec, rec0); }
+        }
+        if (ok) ok = eval_short<SIM>(ix, b, p, ox, s, key, lk, ipool + ioff, pos, ilen, sim);
+      }
+      if (ok) {
+        M.tid[slot] = key.tid; M.pos[slot] = pos; M.ilen[slot] = ilen; M.ioff[slot] = ioff; c_task[slot] = 2 * (wb * 32 + L) + s;
+        if (SIM) { M.sim[slot] = sim; M.clip[slot] = 0; }
+        kept++;
+      } else M.tid[slot] = NONE;
+    }
+  }
+  for (int d = 16; d; d >>= 1) { my_hits += __shfl_down_sync(0xffffffffu, my_hits, d); kept += __shfl_down_sync(0xffffffffu, kept, d);
+                                 n_mates += __shfl_down_sync(0xffffffffu, n_mates, d); }
+  if (lane == 0) {
+    if (my_hits) atomicAdd(&ctl->n_hits, my_hits);
+    if (kept) atomicAdd(&ctl->n_matches, (unsigned long long)kept);
+    if (n_mates) atomicAdd(&ctl->n_mates, (unsigned long long)n_mates);
+  }
+  const uint32_t anybad = __reduce_max_sync(0xffffffffu, bad);
+  if (lane == 0 && anybad) atomicMax(&ctl->bad_input, anybad);
+}
+
+}  // namespace brb

@@ -127,13 +127,15 @@ __global__ void __launch_bounds__(256) k_merge(DevBatch b, Ctl* __restrict__ ctl
   const unsigned lane = threadIdx.x & 31;
   const uint32_t n_rec = ctl->n_rows;
   const uint32_t stride = gridDim.x * blockDim.x;
+  WarpPool wp; wp.cur = 0; wp.end = 0;
+  const uint32_t cap_tmpw = ctl->cap_tmpw;
   for (uint32_t base = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); base < n_rec; base += stride) {
     const uint32_t r = base + lane;
     const bool act = r < n_rec;
     uint32_t ro = 0, nr = 0, c = 0, ni = 0;
     if (act) { const uint32_t a = o_src[r]; c = o_cand[r]; ro = b.cigar_off[a]; nr = b.cigar_off[a + 1] - ro; ni = m_ilen[c]; }
     bool fits;
-    const uint32_t off = warp_alloc(&ctl->n_tmpw, ctl->cap_tmpw, act ? nr + ni + 2 : 0, lane, fits);
+    const uint32_t off = warp_pool_alloc(wp, &ctl->n_tmpw, cap_tmpw, act ? nr + ni + 2 : 0, lane, fits);
     if (act && fits) {
       o_tmpoff[r] = off;
       o_clen[r] = merge_cigars(b.cigar + ro, nr, ipool + m_ioff[c], ni, tpool + off);

@@ -35,10 +35,10 @@ __global__ void __launch_bounds__(256) k_partner(DevBatch b, const Ctl* __restri
     const bool act = c < n_cand;
     uint32_t a = NONE, part = NONE; bool valid = false;
     if (act) {
-      a = v.c_task[c] >> 1;
       const uint32_t tid = v.m_tid[c];
       valid = tid != NONE;
       if (valid) {
+        a = v.c_task[c] >> 1;                                // (c_task is only defined for slots that hold a match)
         const int32_t mate = __ldg(&b.mate_idx[a]);
         if (mate < 0) part = SELF;
         else if ((uint32_t)mate > a) {                       // only the unit owner (lower index) needs partners
@@ -46,7 +46,7 @@ __global__ void __launch_bounds__(256) k_partner(DevBatch b, const Ctl* __restri
           for (uint32_t d = mc.x, e = mc.x + mc.y + mc.z; d < e; d++) if (v.m_tid[d] == tid) part = d;
         }
       }
-      c_partner[c] = part;
+      if (valid) c_partner[c] = part;
     }
     const uint32_t same = __match_any_sync(0xffffffffu, a);
     const uint32_t Bv = __ballot_sync(0xffffffffu, valid);

@@ -67,6 +67,9 @@ class Engine:
         capi.check(self.lib.brb_batch_download(self._ctx, C.byref(out)), "brb_batch_download")
         return out if raw else _rows(out, n_groups)
 
+    def set_option(self, option, value):
+        capi.check(self.lib.brb_ctx_set_option(self._ctx, option, int(value)), "brb_ctx_set_option")
+
     def timer_start(self):
         capi.check(self.lib.brb_ctx_timer_start(self._ctx), "brb_ctx_timer_start")
 

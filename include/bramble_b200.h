@@ -137,6 +137,12 @@ int brb_project_resident(brb_ctx* ctx, const brb_params* p);
 int brb_batch_download(brb_ctx* ctx, brb_batch_out* out);
 
 int brb_ctx_stats(const brb_ctx* ctx, brb_stats* out);
+/* Options of a context.  BRB_OPT_GENERIC_FRONT != 0: use the generic lookup/evaluate kernel (every read exon is
+ * looked up, as the reference does) even where the short-read kernel (exon 0 only, later exons verified along
+ * the transcript's exon chain) applies.  Results are identical; brb_stats.alg_bytes is the reference-defined
+ * figure only on the generic path (it counts the index hits of ALL exons). */
+#define BRB_OPT_GENERIC_FRONT 1
+int brb_ctx_set_option(brb_ctx* ctx, int option, int value);
 /* CUDA-event stopwatch on the ctx stream (what bench.py brackets its K timed steps with). */
 int brb_ctx_timer_start(brb_ctx* ctx);
 int brb_ctx_timer_stop(brb_ctx* ctx, float* ms);   /* records, synchronises, returns elapsed ms */

@@ -16,13 +16,16 @@ def _check(wl, what):
     n_rec = 0
     with engine.Engine(ix) as eng:
         for bi, b in enumerate(wl["batches"]):
-            got = eng.project(p, b)
             exp = oracle_lib.port_project(ix, p, b)
-            oracle_lib.assert_rows_equal(exp, got, f"{what} batch {bi}")
-            st = eng.stats()
-            assert st.n_rec == got["n_rec"] and st.n_launches > 0
-            assert st.n_matches == exp["n_matches"]
-            assert st.n_rescue == exp["n_rescue"]
+            # both front kernels: the default choice (short-read kernel where it applies) and the generic one
+            for generic in (0, 1):
+                eng.set_option(capi.OPT_GENERIC_FRONT, generic)
+                got = eng.project(p, b)
+                oracle_lib.assert_rows_equal(exp, got, f"{what} batch {bi} generic={generic}")
+                st = eng.stats()
+                assert st.n_rec == got["n_rec"] and st.n_launches > 0
+                assert st.n_matches == exp["n_matches"]
+                assert st.n_rescue == exp["n_rescue"]
             n_rec += got["n_rec"]
     assert n_rec > 0
     return n_rec
@@ -208,10 +211,11 @@ def test_c2_shape_hot_genes(stranded, multi_mean):
     B = sf.make_short_batch(A, ix, 8, 6000, stranded=stranded, multi_mean=multi_mean)
     p = capi.resolve_params()
     with engine.Engine(ix) as eng:
-        got = eng.project(p, B)
         exp = oracle_lib.port_project(ix, p, B)
-        oracle_lib.assert_rows_equal(exp, got, "c2 shape")
-        st = eng.stats()
-        assert st.n_matches == exp["n_matches"] and got["n_rec"] > 10000
-        # algorithmic-bytes numerator: the engine's hit counter equals the oracle's
+        for generic in (0, 1):
+            eng.set_option(capi.OPT_GENERIC_FRONT, generic)
+            got = eng.project(p, B)
+            oracle_lib.assert_rows_equal(exp, got, f"c2 shape generic={generic}")
+            st = eng.stats()
+            assert st.n_matches == exp["n_matches"] and got["n_rec"] > 10000
         assert exp["n_hits"] > 0
