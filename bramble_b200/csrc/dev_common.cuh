@@ -60,6 +60,7 @@ struct Ctl {
   uint32_t n_outw, cap_outw;          // dense output CIGAR words
   uint32_t bad_input;                 // 1: mate link not symmetric, 2: read exons not ascending/disjoint
   uint32_t ticket;                    // next batch of 32 alignments for k_front (dynamic scheduling)
+  uint32_t ticket_a, ticket_b;        // same for k_pair_a / k_pair_b
 };
 __device__ __forceinline__ bool ctl_overflow(const Ctl* c) {
   return c->n_cand > c->cap_cand || c->n_ideal > c->cap_ideal || c->n_rows > c->cap_rows || c->n_tmpw > c->cap_tmpw ||

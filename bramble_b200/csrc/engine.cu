@@ -89,21 +89,21 @@ struct brb_ctx {
   // control block + pools (capacities persist across calls and only grow)
   Buf ctl;
   uint32_t cap_cand = 0, cap_ideal = 0, cap_rows = 0, cap_tmpw = 0, cap_outw = 0;
-  Buf q_any, a_cand, a_cnt, scan_tmp;
+  Buf q_any, a_cand, scan_tmp;
   Buf c_rec, c_task, c_first, c_last, c_nseg, c_nguide, c_cap, ipool;
   Buf r_left, r_right, rpool;
-  Buf m_tid, m_pos, m_sim, m_clip, m_ilen, m_ioff, c_partner;
-  Buf u_nrows, u_roff, u_case, g_roff;
-  Buf o_src, o_tid, o_pos, o_strand, o_flags, o_sim, o_clip, o_cand, o_tmpoff, o_clen, o_coff, tpool, opool;
+  Buf m_tid, m_pos, m_sim, m_clip, m_ilen, m_ioff, c_partner, c_tmpoff, c_clen_r, c_clen_m, c_key;
+  Buf u_cnt, u_off, g_roff;
+  Buf o_src, o_tid, o_pos, o_strand, o_flags, o_sim, o_clip, o_coff, tpool, opool;
   HBuf h_small, h_out;
   RescueBufs* rb = nullptr;
   uint32_t n_cand = 0, n_rec = 0; uint64_t n_out_words = 0;
   brb_stats stats{};
   std::vector<Buf*> all() {
     return {&in_group_off, &in_refid, &in_strand, &in_exon_off, &in_exon_st, &in_exon_en, &in_cigar_off, &in_cigar, &in_mate, &in_seq_off,
-            &in_seq, &ctl, &q_any, &a_cand, &a_cnt, &scan_tmp, &c_rec, &c_task, &c_first, &c_last, &c_nseg, &c_nguide, &c_cap, &ipool,
-            &r_left, &r_right, &rpool, &m_tid, &m_pos, &m_sim, &m_clip, &m_ilen, &m_ioff, &c_partner, &u_nrows, &u_roff, &u_case, &g_roff,
-            &o_src, &o_tid, &o_pos, &o_strand, &o_flags, &o_sim, &o_clip, &o_cand, &o_tmpoff, &o_clen, &o_coff, &tpool, &opool};
+            &in_seq, &ctl, &q_any, &a_cand, &scan_tmp, &c_rec, &c_task, &c_first, &c_last, &c_nseg, &c_nguide, &c_cap, &ipool,
+            &r_left, &r_right, &rpool, &m_tid, &m_pos, &m_sim, &m_clip, &m_ilen, &m_ioff, &c_partner, &c_tmpoff, &c_clen_r, &c_clen_m, &c_key, &u_cnt, &u_off, &g_roff,
+            &o_src, &o_tid, &o_pos, &o_strand, &o_flags, &o_sim, &o_clip, &o_coff, &tpool, &opool};
   }
 };
 
@@ -343,17 +343,17 @@ uint32_t grown(uint64_t need) { const uint64_t w = need + need / 4 + 4096; retur
 int ensure_pools(brb_ctx* c, bool rescue) {
   const DevBatch& b = c->b;
   const size_t n = b.n_aln, C = c->cap_cand, R = c->cap_rows;
-  ENS(c->q_any, (size_t)2 * b.n_exon + 16); ENS(c->a_cand, n * 16); ENS(c->a_cnt, n * 8);
-  ENS(c->u_nrows, n * 4); ENS(c->u_roff, (n + 1) * 4); ENS(c->u_case, n); ENS(c->g_roff, (size_t)(b.n_groups + 1) * 4);
-  ENS(c->c_task, C * 4); ENS(c->c_partner, C * 4);
+  ENS(c->q_any, (size_t)2 * b.n_exon + 16); ENS(c->a_cand, n * 16);
+  ENS(c->u_cnt, n * 8); ENS(c->u_off, (n + 1) * 8); ENS(c->g_roff, (size_t)(b.n_groups + 1) * 4);
+  ENS(c->c_task, C * 4); ENS(c->c_partner, C * 4); ENS(c->c_tmpoff, C * 4); ENS(c->c_clen_r, C * 4); ENS(c->c_clen_m, C * 4); ENS(c->c_key, C * 8);
   ENS(c->m_tid, C * 4); ENS(c->m_pos, C * 4); ENS(c->m_ilen, C * 4); ENS(c->m_ioff, C * 4);
   if (c->have_scores) { ENS(c->m_sim, C * 8); ENS(c->m_clip, C * 4); ENS(c->o_sim, R * 8); ENS(c->o_clip, R * 4); }
   if (rescue) { ENS(c->c_rec, C * 4); ENS(c->c_first, C * 4); ENS(c->c_last, C * 4); ENS(c->c_nseg, C * 4); ENS(c->c_nguide, C * 4); ENS(c->c_cap, C * 4); }
   ENS(c->ipool, (size_t)c->cap_ideal * 4);
-  ENS(c->o_src, R * 4); ENS(c->o_tid, R * 4); ENS(c->o_pos, R * 4); ENS(c->o_strand, R); ENS(c->o_flags, R); ENS(c->o_cand, R * 4);
-  ENS(c->o_tmpoff, R * 4); ENS(c->o_clen, R * 4); ENS(c->o_coff, (R + 1) * 4);
+  ENS(c->o_src, R * 4); ENS(c->o_tid, R * 4); ENS(c->o_pos, R * 4); ENS(c->o_strand, R); ENS(c->o_flags, R);
+  ENS(c->o_coff, (R + 1) * 4);
   ENS(c->tpool, (size_t)c->cap_tmpw * 4); ENS(c->opool, (size_t)c->cap_outw * 4);
-  ENS(c->scan_tmp, scan_scratch_words(std::max<size_t>(std::max<size_t>(n, R), 1)) * 4);
+  ENS(c->scan_tmp, scan_scratch_words(std::max<size_t>(n, 1)) * 8);
   return 0;
 }
 
@@ -391,6 +391,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   const void* front_fn = short_front ? (p.filter_by_similarity ? (const void*)k_front_short<true> : (const void*)k_front_short<false>)
                                      : (rescue ? (const void*)k_front<false> : (const void*)k_front<true>);
   const int ncta_front = resident(front_fn);
+  const int ncta_pa = resident((const void*)k_pair_a), ncta_pb = resident((const void*)k_pair_b);
   Ctl* ctl = c->ctl.as<Ctl>();
   Ctl* hctl = c->h_small.as<Ctl>();
   uint64_t L = 0;
@@ -400,7 +401,6 @@ int project_resident(brb_ctx* c, const brb_params& p) {
     memset(hctl, 0, sizeof(Ctl));
     hctl->cap_cand = c->cap_cand; hctl->cap_ideal = c->cap_ideal; hctl->cap_rows = c->cap_rows; hctl->cap_tmpw = c->cap_tmpw; hctl->cap_outw = c->cap_outw;
     CU(cudaMemcpyAsync(ctl, hctl, sizeof(Ctl), cudaMemcpyHostToDevice, st));
-    CU(cudaMemsetAsync(c->a_cnt.p, 0, (size_t)n * 8, st));
     Matches M; M.tid = c->m_tid.as<uint32_t>(); M.pos = c->m_pos.as<uint32_t>();
     M.sim = c->have_scores ? c->m_sim.as<double>() : nullptr; M.clip = c->have_scores ? c->m_clip.as<int32_t>() : nullptr;
     M.ilen = c->m_ilen.as<uint32_t>(); M.ioff = c->m_ioff.as<uint32_t>();
@@ -436,22 +436,21 @@ int project_resident(brb_ctx* c, const brb_params& p) {
       CU(cudaEventRecord(c->ev[4], st));
     }
     // ---- phase 5: pairing + emission
-    PairView pv; pv.a_cand = c->a_cand.as<uint4>(); pv.c_task = c->c_task.as<uint32_t>(); pv.m_tid = c->m_tid.as<uint32_t>();
-    k_partner<<<ncta, 256, 0, st>>>(b, ctl, pv, c->c_partner.as<uint32_t>(), c->a_cnt.as<uint2>()); L++;
-    k_pair_count<<<grid_for(n, 256), 256, 0, st>>>(b, ctl, pv, c->a_cnt.as<uint2>(), c->c_partner.as<uint32_t>(), c->u_nrows.as<uint32_t>(), c->u_case.as<uint8_t>()); L++;
-    exclusive_scan(c->u_nrows.as<uint32_t>(), c->u_roff.as<uint32_t>(), n, c->scan_tmp.as<uint32_t>(), st, &L);
-    k_group_rows<<<grid_for(b.n_groups + 1, 256), 256, 0, st>>>(b, c->u_roff.as<uint32_t>(), c->g_roff.as<uint32_t>()); L++;
-    Rows o; o.src = c->o_src.as<uint32_t>(); o.tid = c->o_tid.as<uint32_t>(); o.pos = c->o_pos.as<uint32_t>(); o.strand = c->o_strand.as<int8_t>();
-    o.flags = c->o_flags.as<uint8_t>(); o.sim = c->o_sim.as<double>(); o.clip = c->o_clip.as<int32_t>(); o.cand = c->o_cand.as<uint32_t>();
-    k_pair_emit<<<ncta, 256, 0, st>>>(b, ctl, pv, c->c_partner.as<uint32_t>(), c->u_roff.as<uint32_t>(), c->u_case.as<uint8_t>(),
-                                      c->m_pos.as<uint32_t>(), c->m_sim.as<double>(), c->m_clip.as<int32_t>(), c->have_scores ? 1 : 0, o); L++;
+    PairIn pv; pv.a_cand = c->a_cand.as<uint4>(); pv.c_task = c->c_task.as<uint32_t>(); pv.m_tid = c->m_tid.as<uint32_t>();
+    pv.m_pos = c->m_pos.as<uint32_t>(); pv.m_ilen = c->m_ilen.as<uint32_t>(); pv.m_ioff = c->m_ioff.as<uint32_t>();
+    pv.m_sim = M.sim; pv.m_clip = M.clip; pv.ipool = c->ipool.as<uint32_t>();
+    SlotOut so; so.key = c->c_key.as<unsigned long long>(); so.partner = c->c_partner.as<uint32_t>(); so.tmpoff = c->c_tmpoff.as<uint32_t>(); so.clen_r = c->c_clen_r.as<uint32_t>();
+    so.clen_m = c->c_clen_m.as<uint32_t>();
+    if (rescue) { k_count_valid<<<grid_for(n, 256), 256, 0, st>>>(b, ctl, c->a_cand.as<uint4>(), c->m_tid.as<uint32_t>()); L++; }
+    k_pair_a<<<ncta_pa, 256, 0, st>>>(b, ctl, pv, so, c->tpool.as<uint32_t>(), c->u_cnt.as<unsigned long long>()); L++;
     CU(cudaEventRecord(c->ev[5], st));
-    // ---- phase 6: CIGAR merge + dense row-ordered pool
-    k_merge<<<ncta, 256, 0, st>>>(b, ctl, c->o_src.as<uint32_t>(), c->o_cand.as<uint32_t>(), c->m_ioff.as<uint32_t>(), c->m_ilen.as<uint32_t>(),
-                                  c->ipool.as<uint32_t>(), c->o_tmpoff.as<uint32_t>(), c->o_clen.as<uint32_t>(), c->tpool.as<uint32_t>()); L++;
-    exclusive_scan(c->o_clen.as<uint32_t>(), c->o_coff.as<uint32_t>(), c->cap_rows, c->scan_tmp.as<uint32_t>(), st, &L, &ctl->n_rows);
-    k_compact<<<ncta, 256, 0, st>>>(ctl, c->o_strand.as<int8_t>(), c->o_tmpoff.as<uint32_t>(), c->o_coff.as<uint32_t>(), c->tpool.as<uint32_t>(),
-                                    c->opool.as<uint32_t>()); L++;
+    // ---- phase 6: row / CIGAR-word offsets in bundle order, then the rows themselves
+    exclusive_scan(c->u_cnt.as<unsigned long long>(), c->u_off.as<unsigned long long>(), n, c->scan_tmp.as<unsigned long long>(), st, &L);
+    k_group_rows<<<grid_for(b.n_groups + 1, 256), 256, 0, st>>>(b, c->u_off.as<unsigned long long>(), c->g_roff.as<uint32_t>()); L++;
+    Rows o; o.src = c->o_src.as<uint32_t>(); o.tid = c->o_tid.as<uint32_t>(); o.pos = c->o_pos.as<uint32_t>(); o.strand = c->o_strand.as<int8_t>();
+    o.flags = c->o_flags.as<uint8_t>(); o.sim = c->o_sim.as<double>(); o.clip = c->o_clip.as<int32_t>(); o.coff = c->o_coff.as<uint32_t>();
+    o.pool = c->opool.as<uint32_t>();
+    k_pair_b<<<ncta_pb, 256, 0, st>>>(b, ctl, pv, so, c->tpool.as<uint32_t>(), c->u_cnt.as<unsigned long long>(), c->u_off.as<unsigned long long>(), o); L++;
     CU(cudaEventRecord(c->ev[6], st));
     CU(cudaMemcpyAsync(hctl, ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));

@@ -20,7 +20,8 @@
 
 namespace brb {
 
-// a_cand[a] = { first candidate slot, #slots of task 2a ('+'), #slots of task 2a+1 ('-'), 0 }
+// a_cand[a] = { first candidate slot, #slots of task 2a ('+'), #slots of task 2a+1 ('-'), #slots that hold a match }
+// (on the clip-rescue path the last field is filled in later by k_count_valid)
 template <bool FUSED>
 __global__ void __launch_bounds__(256) k_front(DevIndex ix, DevBatch b, brb_params p, Ctl* __restrict__ ctl,
                                                uint8_t* q_any, uint4* __restrict__ a_cand,
@@ -91,9 +92,9 @@ __global__ void __launch_bounds__(256) k_front(DevIndex ix, DevBatch b, brb_para
     if (lane == 31 && wtot) sbase = atomicAdd(&ctl->n_cand, wtot);
     sbase = __shfl_sync(0xffffffffu, sbase, 31);
     const uint32_t off0 = sbase + incl_t - tot, off1 = off0 + ncand[0];
-    if (valid) a_cand[a] = make_uint4(off0, ncand[0], ncand[1], 0);
     const bool slots_fit = (unsigned long long)sbase + wtot <= cap_cand;
-    if (!wtot) continue;
+    if (!wtot) { if (valid) a_cand[a] = make_uint4(off0, 0, 0, 0); continue; }
+    uint32_t nvalid = 0;                                    // matches kept for MY alignment (pairing reads it from a_cand.w)
     __syncwarp();                                           // q_any of this batch is visible to its candidate lanes
     // ---- pass 2
 #pragma unroll
@@ -135,14 +136,18 @@ __global__ void __launch_bounds__(256) k_front(DevIndex ix, DevBatch b, brb_para
           }
           bool pool_fit;
           const uint32_t ioff = warp_pool_alloc(wp, &ctl->n_ideal, cap_ideal, ok ? w.cap : 0, lane, pool_fit);
+          bool keep = false;
           if (sv && slots_fit) {
             c_task[slot] = task;
-            if (ok && pool_fit) kept += build_one(ix, b, p, slot, rx, s, q_any, w, nullptr, nullptr, nullptr, ipool, ioff, M) ? 1u : 0u;
+            if (ok && pool_fit) keep = build_one(ix, b, p, slot, rx, s, q_any, w, nullptr, nullptr, nullptr, ipool, ioff, M);
             else M.tid[slot] = NONE;
           }
+          kept += keep ? 1u : 0u;
+          nvalid += __popc(__ballot_sync(0xffffffffu, keep) & mine);
         }
       }
     }
+    if (valid) a_cand[a] = make_uint4(off0, ncand[0], ncand[1], nvalid);
   }
   // work counters (algorithmic-bytes numerator) + input validation: one atomic per warp
   for (int d = 16; d; d >>= 1) { my_hits += __shfl_down_sync(0xffffffffu, my_hits, d); kept += __shfl_down_sync(0xffffffffu, kept, d);
@@ -168,10 +173,12 @@ __global__ void __launch_bounds__(256) k_front(DevIndex ix, DevBatch b, brb_para
 // marked empty.  (n_hits then only counts exon-0 hits; the reference-defined figure for the roofline numerator
 // comes from the generic kernel, see BRB_OPT_GENERIC_FRONT.)
 template <bool SIM>
-__global__ void __launch_bounds__(256) k_front_short(DevIndex ix, DevBatch b, brb_params p, Ctl* __restrict__ ctl,
-                                                     uint4* __restrict__ a_cand, uint32_t* __restrict__ c_task,
-                                                     uint32_t* __restrict__ ipool, Matches M) {
+__global__ void __launch_bounds__(256, 4) k_front_short(DevIndex ix, DevBatch b, brb_params p, Ctl* __restrict__ ctl,
+                                                        uint4* __restrict__ a_cand, uint32_t* __restrict__ c_task,
+                                                        uint32_t* __restrict__ ipool, Matches M) {
+  __shared__ uint32_t s_nvalid[8][32];                      // per warp: matches kept per alignment of the current batch
   const unsigned lane = threadIdx.x & 31;
+  uint32_t* nval = s_nvalid[threadIdx.x >> 5];
   const uint32_t n_batches = (b.n_aln + 31) >> 5;
   const uint32_t cap_cand = ctl->cap_cand, cap_ideal = ctl->cap_ideal;       // constant during the launch
   WarpPool wp; wp.cur = 0; wp.end = 0;
@@ -210,9 +217,10 @@ __global__ void __launch_bounds__(256) k_front_short(DevIndex ix, DevBatch b, br
     uint32_t sbase = 0;
     if (lane == 31 && total) sbase = atomicAdd(&ctl->n_cand, total);
     sbase = __shfl_sync(0xffffffffu, sbase, 31);
-    if (a < b.n_aln) a_cand[a] = make_uint4(sbase + excl, n0, n1, 0);
     const bool slots_fit = (unsigned long long)sbase + total <= cap_cand;
     const int status0 = exon_status(rx.n_ex, 0);
+    nval[lane] = 0;                                         // matches kept for MY alignment (pairing reads it from a_cand.w)
+    __syncwarp();
     for (uint32_t base = 0; base < total; base += 32) {
       const uint32_t item = base + lane;
       const bool actv = item < total;
@@ -252,9 +260,12 @@ __global__ void __launch_bounds__(256) k_front_short(DevIndex ix, DevBatch b, br
       if (ok) {
         M.tid[slot] = key.tid; M.pos[slot] = pos; M.ilen[slot] = ilen; M.ioff[slot] = ioff; c_task[slot] = 2 * (wb * 32 + L) + s;
         if (SIM) { M.sim[slot] = sim; M.clip[slot] = 0; }
-        kept++;
+        kept++; atomicAdd(&nval[L], 1u);
       } else M.tid[slot] = NONE;
     }
+    __syncwarp();
+    if (a < b.n_aln) a_cand[a] = make_uint4(sbase + excl, n0, n1, nval[lane]);
+    __syncwarp();
   }
   for (int d = 16; d; d >>= 1) { my_hits += __shfl_down_sync(0xffffffffu, my_hits, d); kept += __shfl_down_sync(0xffffffffu, kept, d);
                                  n_mates += __shfl_down_sync(0xffffffffu, n_mates, d); }

@@ -1,6 +1,6 @@
 // Kernel group 4: CIGAR projection -- merge the alignment's real CIGAR with the ideal (transcript-side)
 // CIGAR of the match.  Replaces merge_ops / merge_cigars / get_new_cigar (reference src/bam.cpp:22-315,
-// 443-472) and the CIGAR reversal of reverse_complement_bam (:636-702).  One thread per output row.
+// 443-472).  Device function, called by k_pair_a for every emitted row.
 #pragma once
 #include "dev_common.cuh"
 
@@ -34,19 +34,31 @@ __device__ __forceinline__ uint32_t merge_ops(uint32_t r, uint32_t i) {        /
   return i;
 }
 
-struct CigOut {
-  uint32_t* p; uint32_t n;
+struct CigOut {                 // coalescing appender; the open (last) op lives in a register
+  uint32_t* p; uint32_t n; uint32_t last; bool saw_i;
   __device__ __forceinline__ void add(uint32_t op, uint32_t len) {
     if (len == 0 || op == OP_SKIP) return;
-    if (n > 0 && (p[n - 1] & 0xfu) == op) p[n - 1] += (len << 4);
-    else p[n++] = (len << 4) | op;
+    if (n > 0 && (last & 0xfu) == op) last += (len << 4);
+    else { if (n > 0) p[n - 1] = last; last = (len << 4) | op; n++; saw_i |= (op == CI); }
   }
+  __device__ __forceinline__ void finish() { if (n > 0) p[n - 1] = last; }
 };
 
 // Returns the number of words written to `out` (capacity >= n_real + n_ideal + 2).
 __device__ uint32_t merge_cigars(const uint32_t* __restrict__ real, uint32_t n_real, const uint32_t* __restrict__ ideal,
                                  uint32_t n_ideal, uint32_t* __restrict__ out) {
-  CigOut res; res.p = out; res.n = 0;
+  // The common short-read row: the real CIGAR only has M/=/X and N, the ideal CIGAR is one M of the same aligned
+  // length.  The two-cursor merge below then skips every N, turns every chunk into M (merge_ops) and both
+  // sides end together: the result is the ideal CIGAR itself.
+  if (n_ideal == 1 && n_real > 0 && (ideal[0] & 0xfu) == CM) {
+    uint32_t sum = 0; bool simple = true;
+    for (uint32_t i = 0; i < n_real; i++) {
+      const uint32_t rw = real[i], op = rw & 0xfu;
+      if (op == CM || op == CEQ || op == CX) sum += rw >> 4; else if (op != CN) { simple = false; break; }
+    }
+    if (simple && sum > 0 && sum == (ideal[0] >> 4)) { out[0] = ideal[0]; return 1; }
+  }
+  CigOut res; res.p = out; res.n = 0; res.last = 0; res.saw_i = false;
   uint32_t front_hard = 0, front_soft = 0, ci = 0;
   if (n_real > 0 && (real[0] & 0xfu) == CH) { front_hard = real[0] >> 4; ci++; }
   if (ci < n_real && (real[ci] & 0xfu) == CS) front_soft = real[ci] >> 4;
@@ -104,6 +116,8 @@ __device__ uint32_t merge_cigars(const uint32_t* __restrict__ real, uint32_t n_r
       if (ipos >= (iw >> 4)) { ii++; ipos = 0; }
     }
   }
+  res.finish();
+  if (!res.saw_i) return res.n;                                                 // (4) and (5) only ever change a CIGAR that contains an I
   for (uint32_t i = 1; i + 1 < res.n; i++) {                                    // (4) I between clips becomes that clip
     if ((out[i] & 0xfu) != CI) continue;
     const uint32_t prev = out[i - 1] & 0xfu, next = out[i + 1] & 0xfu;
@@ -115,50 +129,6 @@ __device__ uint32_t merge_cigars(const uint32_t* __restrict__ real, uint32_t n_r
     if (n > 0 && (out[n - 1] & 0xfu) == op) out[n - 1] += (len << 4); else out[n++] = (len << 4) | op;
   }
   return n;
-}
-
-// One thread per output row: merged CIGAR into a bump-allocated scratch pool (capacity n_real + n_ideal + 2
-// words per row, one atomic per warp), its exact length into o_clen.
-__global__ void __launch_bounds__(256) k_merge(DevBatch b, Ctl* __restrict__ ctl, const uint32_t* __restrict__ o_src,
-                                               const uint32_t* __restrict__ o_cand, const uint32_t* __restrict__ m_ioff,
-                                               const uint32_t* __restrict__ m_ilen, const uint32_t* __restrict__ ipool,
-                                               uint32_t* __restrict__ o_tmpoff, uint32_t* __restrict__ o_clen, uint32_t* __restrict__ tpool) {
-  if (ctl_overflow(ctl)) return;
-  const unsigned lane = threadIdx.x & 31;
-  const uint32_t n_rec = ctl->n_rows;
-  const uint32_t stride = gridDim.x * blockDim.x;
-  WarpPool wp; wp.cur = 0; wp.end = 0;
-  const uint32_t cap_tmpw = ctl->cap_tmpw;
-  for (uint32_t base = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); base < n_rec; base += stride) {
-    const uint32_t r = base + lane;
-    const bool act = r < n_rec;
-    uint32_t ro = 0, nr = 0, c = 0, ni = 0;
-    if (act) { const uint32_t a = o_src[r]; c = o_cand[r]; ro = b.cigar_off[a]; nr = b.cigar_off[a + 1] - ro; ni = m_ilen[c]; }
-    bool fits;
-    const uint32_t off = warp_pool_alloc(wp, &ctl->n_tmpw, cap_tmpw, act ? nr + ni + 2 : 0, lane, fits);
-    if (act && fits) {
-      o_tmpoff[r] = off;
-      o_clen[r] = merge_cigars(b.cigar + ro, nr, ipool + m_ioff[c], ni, tpool + off);
-    }
-  }
-}
-
-// Dense, row-ordered CIGAR pool: row r's words go to opool[o_coff[r] .. o_coff[r+1]) (o_coff = exclusive scan of
-// o_clen), reversed for '-' transcripts (reverse_complement_bam, src/bam.cpp:636-702).
-__global__ void __launch_bounds__(256) k_compact(Ctl* __restrict__ ctl, const int8_t* __restrict__ o_strand,
-                                                 const uint32_t* __restrict__ o_tmpoff, const uint32_t* __restrict__ o_coff,
-                                                 const uint32_t* __restrict__ tpool, uint32_t* __restrict__ opool) {
-  if (ctl_overflow(ctl)) return;
-  const uint32_t n_rec = ctl->n_rows;
-  const uint32_t W = o_coff[n_rec];
-  if (blockIdx.x == 0 && threadIdx.x == 0) { ctl->n_outw = W; ctl->out_words = W; }
-  if (W > ctl->cap_outw) return;
-  for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n_rec; r += gridDim.x * blockDim.x) {
-    const uint32_t d0 = o_coff[r], n = o_coff[r + 1] - d0;
-    const uint32_t* src = tpool + o_tmpoff[r];
-    if (o_strand[r] == '-') for (uint32_t i = 0; i < n; i++) opool[d0 + i] = src[n - 1 - i];
-    else for (uint32_t i = 0; i < n; i++) opool[d0 + i] = src[i];
-  }
 }
 
 // Standalone entry for the parity tests (brb_merge_cigars).

@@ -1,143 +1,218 @@
-// Kernel group 3: mate pairing and record emission.
-// Replaces process_mate_pair / add_mate_info (reference src/mates.cpp:28-261) and the group loop of
-// convert_reads (src/core.cpp:384-415).  process_pairs (src/bramble.cpp:272-311) links every
-// alignment to at most one mate and the link is symmetric, so inside a name group the units
-// {i unpaired} and {i < mate(i)} are independent: the lower index is `this_read` (read1 of the
-// BamInfo), the higher one the mate.  Rows of a unit come out ascending by tid (sorted tid lists +
-// set_intersection in the reference), the read row immediately followed by its mate row.
+// Kernel group 3: mate pairing, CIGAR projection and record emission -- the back half of a bundle.
+// Replaces process_mate_pair / add_mate_info (reference src/mates.cpp:28-261), the group loop of convert_reads
+// (src/core.cpp:384-415) and update_cigar / merge_cigars (src/bam.cpp:113-315,443-528).
+// process_pairs (src/bramble.cpp:272-311) links every alignment to at most one mate and the link is symmetric,
+// so inside a name group the units {i unpaired} and {i < mate(i)} are independent: the lower index is
+// `this_read` (read1 of the BamInfo), the higher one the mate.  Rows of a unit come out ascending by tid (sorted
+// tid lists + set_intersection in the reference), the read row immediately followed by its mate row.
 //
-// Work mapping: one thread per CANDIDATE SLOT (not per alignment), so the lanes of a warp that belong to
-// the same read run the same trip count over that read's (or its mate's) match list and a 200-isoform
-// gene does not leave 31 lanes idle.  Per-alignment totals are folded with match.any + one atomic per run.
+// Whether a match of the read is emitted can be decided per match, from the match counts of the two ends that
+// the front kernel left in a_cand.w (nr, nm):
+//   nm == 0                      -> every match, unpaired            (case 0, src/mates.cpp:150-176)
+//   the mate has the same tid    -> paired, same transcript          (case 1: a non-empty intersection keeps only
+//                                                                      the common tids)
+//   no common tid, nr == nm == 1 -> paired, different transcripts    (case 2)
+// Work mapping (both kernels): a warp takes batches of 32 alignments (lane = alignment) and walks the
+// concatenated candidate slots of the batch's UNIT OWNERS 32 at a time (lane = slot), so a 200-isoform gene
+// fills the warp instead of idling 31 lanes, and slots of mates / non-owners cost nothing.
+//   k_pair_a : partner search on the mate's slot list, the merged CIGAR of each emitted row into a scratch
+//              pool (exact length known afterwards), rows + CIGAR words per alignment.
+//   (scan)   : one 64-bit exclusive scan turns those into row / word offsets in bundle order.
+//   k_pair_b : rank of each emitted match inside its unit, the row columns, and the CIGAR words copied to their
+//              final, dense, row-ordered place (reversed for '-' transcripts).
 #pragma once
 #include "dev_common.cuh"
+#include "k_merge.cuh"
 
 namespace brb {
 
 constexpr uint32_t SELF = 0xfffffffeu;   // emitted without a mate row
 
-struct PairView {
-  const uint4* a_cand;          // per alignment: first slot, #slots '+', #slots '-'
-  const uint32_t* c_task;       // per slot: 2a+s
+struct PairIn {
+  const uint4* a_cand;          // per alignment: first slot, #slots '+', #slots '-', #matches
+  const uint32_t* c_task;       // per slot holding a match: 2a+s
   const uint32_t* m_tid;        // per slot: tid of the match or NONE
+  const uint32_t* m_pos; const uint32_t* m_ilen; const uint32_t* m_ioff;
+  const double* m_sim; const int32_t* m_clip;      // null when every score is 0
+  const uint32_t* ipool;        // ideal CIGARs
+};
+constexpr unsigned long long NONE64 = ~0ull;
+struct SlotOut {                // per slot of a unit owner that has matches
+  unsigned long long* key;      // emitted match: tid << 32 | CIGAR words of its row(s); otherwise NONE64
+  uint32_t* partner;            // (emitted matches) SELF: unpaired row; else the mate's slot
+  uint32_t* tmpoff;             // merged CIGARs in the scratch pool: read row at tmpoff, mate row right after the read row's capacity
+  uint32_t* clen_r; uint32_t* clen_m;
 };
 
-// Pass A (per slot): partner match on the mate (last one wins, like the reference's map overwrite) and the
-// per-alignment totals  a_cnt[a] = {valid matches, matches with a partner}.
-__global__ void __launch_bounds__(256) k_partner(DevBatch b, const Ctl* __restrict__ ctl, PairView v,
-                                                 uint32_t* __restrict__ c_partner, uint2* __restrict__ a_cnt) {
-  if (ctl_overflow(ctl)) return;
-  const unsigned lane = threadIdx.x & 31;
-  const uint32_t n_cand = ctl->n_cand;
-  const uint32_t stride = gridDim.x * blockDim.x;
-  for (uint32_t base = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); base < n_cand; base += stride) {
-    const uint32_t c = base + lane;
-    const bool act = c < n_cand;
-    uint32_t a = NONE, part = NONE; bool valid = false;
-    if (act) {
-      const uint32_t tid = v.m_tid[c];
-      valid = tid != NONE;
-      if (valid) {
-        a = v.c_task[c] >> 1;                                // (c_task is only defined for slots that hold a match)
-        const int32_t mate = __ldg(&b.mate_idx[a]);
-        if (mate < 0) part = SELF;
-        else if ((uint32_t)mate > a) {                       // only the unit owner (lower index) needs partners
-          const uint4 mc = __ldg(&v.a_cand[mate]);
-          for (uint32_t d = mc.x, e = mc.x + mc.y + mc.z; d < e; d++) if (v.m_tid[d] == tid) part = d;
-        }
-      }
-      if (valid) c_partner[c] = part;
-    }
-    const uint32_t same = __match_any_sync(0xffffffffu, a);
-    const uint32_t Bv = __ballot_sync(0xffffffffu, valid);
-    const uint32_t Bp = __ballot_sync(0xffffffffu, valid && part != NONE && part != SELF);
-    if (act && lane == (unsigned)__ffs(same) - 1) {
-      const uint32_t nv = __popc(same & Bv), np = __popc(same & Bp);
-      if (nv) atomicAdd(&a_cnt[a].x, nv);
-      if (np) atomicAdd(&a_cnt[a].y, np);
-    }
-  }
+// [lo,hi) = my lanes of this chunk; sum over them of a per-lane value given its inclusive warp prefix P
+__device__ __forceinline__ uint32_t seg_sum(uint32_t P, uint32_t lo, uint32_t hi) {
+  const uint32_t top = __shfl_sync(0xffffffffu, P, hi ? hi - 1 : 0), bot = __shfl_sync(0xffffffffu, P, lo ? lo - 1 : 0);
+  return hi > lo ? top - (lo ? bot : 0) : 0;
 }
 
-// Pass B (per alignment): the pairing case and the number of rows of the unit (src/mates.cpp:150-261).
-__global__ void __launch_bounds__(256) k_pair_count(DevBatch b, const Ctl* __restrict__ ctl, PairView v, const uint2* __restrict__ a_cnt,
-                                                    uint32_t* __restrict__ c_partner, uint32_t* __restrict__ u_nrows,
-                                                    uint8_t* __restrict__ u_case) {
-  const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
-  if (a >= b.n_aln) return;
-  uint32_t rows = 0; uint8_t ucase = 255;
-  if (!ctl_overflow(ctl)) {
-    const int32_t mate = b.mate_idx[a];
-    if (mate < 0 || (uint32_t)mate > a) {
-      const uint2 cr = a_cnt[a];
-      const uint32_t nr = cr.x, nm = mate >= 0 ? a_cnt[mate].x : 0;
-      if (nr > 0) {
-        if (nm == 0) { ucase = 0; rows = nr; }                             // case 0: mate absent or without a match
-        else if (cr.y > 0) { ucase = 1; rows = 2 * cr.y; }                 // same transcript
-        else if (nr == 1 && nm == 1) {                                     // different transcripts
-          ucase = 2; rows = 2;
-          const uint4 rc = v.a_cand[a], mc = v.a_cand[mate];
-          uint32_t r_only = NONE, m_only = NONE;
-          for (uint32_t c = rc.x, e = rc.x + rc.y + rc.z; c < e; c++) if (v.m_tid[c] != NONE) r_only = c;
-          for (uint32_t c = mc.x, e = mc.x + mc.y + mc.z; c < e; c++) if (v.m_tid[c] != NONE) m_only = c;
-          c_partner[r_only] = m_only;
+__global__ void __launch_bounds__(256) k_pair_a(DevBatch b, Ctl* __restrict__ ctl, PairIn v, SlotOut so, uint32_t* __restrict__ tpool,
+                                                unsigned long long* __restrict__ u_cnt /* rows | words << 32 */) {
+  if (ctl_overflow(ctl)) return;
+  const unsigned lane = threadIdx.x & 31;
+  const uint32_t n_batches = (b.n_aln + 31) >> 5;
+  const uint32_t cap_tmpw = ctl->cap_tmpw;
+  WarpPool wp; wp.cur = 0; wp.end = 0;
+  for (;;) {
+    uint32_t wb = 0;
+    if (lane == 0) wb = atomicAdd(&ctl->ticket_a, 1u);
+    wb = __shfl_sync(0xffffffffu, wb, 0);
+    if (wb >= n_batches) break;
+    const uint32_t a = wb * 32 + lane;
+    uint32_t off = 0, n = 0, nr = 0, nm = 0, m_off = 0, m_n = 0, ro = 0, nrc = 0, mro = 0, mnrc = 0;
+    if (a < b.n_aln) {
+      const uint4 ac = __ldg(&v.a_cand[a]);
+      const int32_t mate = __ldg(&b.mate_idx[a]);
+      if ((mate < 0 || (uint32_t)mate > a) && ac.w) {         // unit owner with at least one match
+        off = ac.x; n = ac.y + ac.z; nr = ac.w;
+        ro = __ldg(&b.cigar_off[a]); nrc = __ldg(&b.cigar_off[a + 1]) - ro;
+        if (mate >= 0) {
+          const uint4 mc = __ldg(&v.a_cand[mate]);
+          m_off = mc.x; m_n = mc.y + mc.z; nm = mc.w;
+          mro = __ldg(&b.cigar_off[mate]); mnrc = __ldg(&b.cigar_off[mate + 1]) - mro;
         }
       }
     }
+    const uint32_t incl = warp_incl_scan(n, lane), excl = incl - n, total = __shfl_sync(0xffffffffu, incl, 31);
+    uint32_t rows = 0, words = 0;
+    for (uint32_t base = 0; base < total; base += 32) {
+      const uint32_t item = base + lane;
+      const bool actv = item < total;
+      const unsigned L = warp_owner(incl, actv ? item : total - 1);
+      const uint32_t c = __shfl_sync(0xffffffffu, off, L) + (item - __shfl_sync(0xffffffffu, excl, L));
+      const uint32_t o_nr = __shfl_sync(0xffffffffu, nr, L), o_nm = __shfl_sync(0xffffffffu, nm, L);
+      const uint32_t o_moff = __shfl_sync(0xffffffffu, m_off, L), o_mn = __shfl_sync(0xffffffffu, m_n, L);
+      const uint32_t o_ro = __shfl_sync(0xffffffffu, ro, L), o_nrc = __shfl_sync(0xffffffffu, nrc, L);
+      const uint32_t o_mro = __shfl_sync(0xffffffffu, mro, L), o_mnrc = __shfl_sync(0xffffffffu, mnrc, L);
+      const uint32_t tid = actv ? v.m_tid[c] : NONE;
+      uint32_t part = NONE;
+      if (tid != NONE) {
+        if (o_nm == 0) part = SELF;
+        else {
+          uint32_t only = NONE;
+          for (uint32_t d = o_moff, e = o_moff + o_mn; d < e; d++) { const uint32_t t = v.m_tid[d]; if (t == tid) part = d; if (t != NONE) only = d; }
+          if (part == NONE && o_nr == 1 && o_nm == 1) part = only;          // different transcripts
+        }
+      }
+      const bool emitted = part != NONE, paired = emitted && part != SELF;
+      uint32_t il = 0, io = 0, pil = 0, pio = 0;
+      if (emitted) { il = v.m_ilen[c]; io = v.m_ioff[c]; }
+      if (paired) { pil = v.m_ilen[part]; pio = v.m_ioff[part]; }
+      const uint32_t cap_r = o_nrc + il + 2, want = emitted ? cap_r + (paired ? o_mnrc + pil + 2 : 0) : 0;
+      bool fit;
+      const uint32_t toff = warp_pool_alloc(wp, &ctl->n_tmpw, cap_tmpw, want, lane, fit);
+      uint32_t clr = 0, clm = 0;
+      if (emitted && fit) {
+        clr = merge_cigars(b.cigar + o_ro, o_nrc, v.ipool + io, il, tpool + toff);
+        if (paired) clm = merge_cigars(b.cigar + o_mro, o_mnrc, v.ipool + pio, pil, tpool + toff + cap_r);
+      }
+      if (actv) {
+        so.key[c] = emitted ? ((unsigned long long)tid << 32) | (clr + clm) : NONE64;
+        if (emitted) { so.partner[c] = part; so.tmpoff[c] = toff; so.clen_r[c] = clr; so.clen_m[c] = clm; }
+      }
+      // rows / words of MY alignment in this chunk
+      const uint32_t Pr = warp_incl_scan(emitted ? (paired ? 2u : 1u) : 0u, lane), Pw = warp_incl_scan(clr + clm, lane);
+      uint32_t lo_b = 0, hi_b = 0;
+      if (n && incl > base && excl < base + 32) { lo_b = excl > base ? excl - base : 0; hi_b = incl - base < 32 ? incl - base : 32; }
+      rows += seg_sum(Pr, lo_b, hi_b); words += seg_sum(Pw, lo_b, hi_b);
+    }
+    if (a < b.n_aln) u_cnt[a] = (unsigned long long)rows | ((unsigned long long)words << 32);
   }
-  u_nrows[a] = rows; u_case[a] = ucase;
 }
 
 struct Rows {
   uint32_t* src; uint32_t* tid; uint32_t* pos; int8_t* strand; uint8_t* flags; double* sim; int32_t* clip;
-  uint32_t* cand;
+  uint32_t* coff;               // n_rows+1: dense CIGAR pool offsets (CSR)
+  uint32_t* pool;               // dense, row-ordered merged CIGARs
 };
 
-// Pass C (per slot of a unit owner): rank of the match among the emitted matches of its read (ascending tid,
-// slot order among equals) and the row(s) themselves.
-__global__ void __launch_bounds__(256) k_pair_emit(DevBatch b, Ctl* __restrict__ ctl, PairView v, const uint32_t* __restrict__ c_partner,
-                                                   const uint32_t* __restrict__ u_roff, const uint8_t* __restrict__ u_case,
-                                                   const uint32_t* __restrict__ m_pos, const double* __restrict__ m_sim,
-                                                   const int32_t* __restrict__ m_clip, int has_scores, Rows o) {
+// u_off = exclusive scan of u_cnt (n_aln+1 entries; low half rows, high half CIGAR words).
+__global__ void __launch_bounds__(256) k_pair_b(DevBatch b, Ctl* __restrict__ ctl, PairIn v, SlotOut so, const uint32_t* __restrict__ tpool,
+                                                const unsigned long long* __restrict__ u_cnt, const unsigned long long* __restrict__ u_off,
+                                                Rows o) {
   if (ctl_overflow(ctl)) return;
-  const uint32_t R = u_roff[b.n_aln];
-  if (blockIdx.x == 0 && threadIdx.x == 0) ctl->n_rows = R;
-  if (R > ctl->cap_rows) return;
-  const uint32_t n_cand = ctl->n_cand;
-  for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < n_cand; c += gridDim.x * blockDim.x) {
-    const uint32_t tid = v.m_tid[c];
-    if (tid == NONE) continue;
-    const uint32_t task = v.c_task[c], a = task >> 1;
-    const uint8_t ucase = u_case[a];
-    if (ucase == 255) continue;
-    const uint32_t part = c_partner[c];
-    if (ucase != 0 && (part == NONE || part == SELF)) continue;
-    const uint4 ac = __ldg(&v.a_cand[a]);
-    uint32_t rank = 0;
-    for (uint32_t d = ac.x, e = ac.x + ac.y + ac.z; d < e; d++) {
-      const uint32_t t2 = v.m_tid[d];
-      if (d == c || t2 == NONE) continue;
-      if (ucase != 0) { const uint32_t pd = c_partner[d]; if (pd == NONE || pd == SELF) continue; }
-      if (t2 < tid || (t2 == tid && d < c)) rank++;
+  const unsigned long long tot = u_off[b.n_aln];
+  const uint32_t R = (uint32_t)tot, W = (uint32_t)(tot >> 32);
+  if (blockIdx.x == 0 && threadIdx.x == 0) { ctl->n_rows = R; ctl->n_outw = W; ctl->out_words = W; }
+  if (R > ctl->cap_rows || W > ctl->cap_outw) return;
+  if (blockIdx.x == 0 && threadIdx.x == 0) o.coff[R] = W;
+  const unsigned lane = threadIdx.x & 31;
+  const uint32_t n_batches = (b.n_aln + 31) >> 5;
+  for (;;) {
+    uint32_t wb = 0;
+    if (lane == 0) wb = atomicAdd(&ctl->ticket_b, 1u);
+    wb = __shfl_sync(0xffffffffu, wb, 0);
+    if (wb >= n_batches) break;
+    const uint32_t a = wb * 32 + lane;
+    uint32_t off = 0, n = 0, roff = 0, woff = 0, nrc = 0; int32_t mate = -1;
+    if (a < b.n_aln && (uint32_t)u_cnt[a]) {                    // the alignment emits rows
+      const uint4 ac = __ldg(&v.a_cand[a]);
+      off = ac.x; n = ac.y + ac.z;
+      const unsigned long long uo = u_off[a];
+      roff = (uint32_t)uo; woff = (uint32_t)(uo >> 32);
+      nrc = __ldg(&b.cigar_off[a + 1]) - __ldg(&b.cigar_off[a]);
+      mate = __ldg(&b.mate_idx[a]);
     }
-    const uint32_t base = u_roff[a];
-    auto put = [&](uint32_t row, uint32_t cc, uint32_t aln, uint32_t t, uint8_t fl) {
-      o.src[row] = aln; o.tid[row] = t; o.pos[row] = m_pos[cc]; o.strand[row] = (v.c_task[cc] & 1) ? '-' : '+';
-      o.flags[row] = fl; o.cand[row] = cc;
-      if (has_scores) { o.sim[row] = m_sim[cc]; o.clip[row] = m_clip[cc]; }
-    };
-    if (ucase == 0) put(base + rank, c, a, tid, BRB_REC_FIRST);
-    else {
-      const uint8_t fl = BRB_REC_PAIRED | (ucase == 1 ? BRB_REC_SAMETX : 0);
-      put(base + 2 * rank, c, a, tid, fl | BRB_REC_FIRST);
-      put(base + 2 * rank + 1, part, (uint32_t)b.mate_idx[a], v.m_tid[part], fl);
+    const uint32_t incl = warp_incl_scan(n, lane), excl = incl - n, total = __shfl_sync(0xffffffffu, incl, 31);
+    for (uint32_t base = 0; base < total; base += 32) {
+      const uint32_t item = base + lane;
+      const bool actv = item < total;
+      const unsigned L = warp_owner(incl, actv ? item : total - 1);
+      const uint32_t o_off = __shfl_sync(0xffffffffu, off, L), o_n = __shfl_sync(0xffffffffu, n, L);
+      const uint32_t c = o_off + (item - __shfl_sync(0xffffffffu, excl, L));
+      const uint32_t o_roff = __shfl_sync(0xffffffffu, roff, L), o_woff = __shfl_sync(0xffffffffu, woff, L);
+      const uint32_t o_nrc = __shfl_sync(0xffffffffu, nrc, L);
+      const int32_t o_mate = __shfl_sync(0xffffffffu, mate, L);
+      if (!actv) continue;
+      const unsigned long long mykey = so.key[c];
+      if (mykey == NONE64) continue;
+      const uint32_t tid = (uint32_t)(mykey >> 32), part = so.partner[c];
+      // rank among the emitted matches of the read: ascending tid, slot order among equals; CIGAR words before me
+      uint32_t rank = 0, wpre = 0;
+      for (uint32_t d = o_off, e = o_off + o_n; d < e; d++) {
+        const unsigned long long k = so.key[d];
+        const uint32_t t2 = (uint32_t)(k >> 32);
+        if (k != NONE64 && (t2 < tid || (t2 == tid && d < c))) { rank++; wpre += (uint32_t)k; }
+      }
+      const bool paired = part != SELF;
+      const uint32_t row = o_roff + (paired ? 2 * rank : rank), w0 = o_woff + wpre;
+      const uint32_t toff = so.tmpoff[c], clr = so.clen_r[c];
+      auto put = [&](uint32_t r, uint32_t cc, uint32_t aln, uint32_t t, uint8_t fl, uint32_t wpos, const uint32_t* src, uint32_t len) {
+        const bool minus = v.c_task[cc] & 1;
+        o.src[r] = aln; o.tid[r] = t; o.pos[r] = v.m_pos[cc]; o.strand[r] = minus ? '-' : '+'; o.flags[r] = fl; o.coff[r] = wpos;
+        if (v.m_sim) { o.sim[r] = v.m_sim[cc]; o.clip[r] = v.m_clip[cc]; }
+        if (minus) for (uint32_t i = 0; i < len; i++) o.pool[wpos + i] = src[len - 1 - i];      // reverse_complement_bam, src/bam.cpp:636-702
+        else for (uint32_t i = 0; i < len; i++) o.pool[wpos + i] = src[i];
+      };
+      if (!paired) put(row, c, wb * 32 + L, tid, BRB_REC_FIRST, w0, tpool + toff, clr);
+      else {
+        const uint32_t t2 = v.m_tid[part];
+        const uint8_t fl = BRB_REC_PAIRED | (t2 == tid ? BRB_REC_SAMETX : 0);
+        put(row, c, wb * 32 + L, tid, fl | BRB_REC_FIRST, w0, tpool + toff, clr);
+        put(row + 1, part, (uint32_t)o_mate, t2, fl, w0 + clr, tpool + toff + (o_nrc + v.m_ilen[c] + 2), so.clen_m[c]);
+      }
     }
   }
 }
 
-__global__ void k_group_rows(DevBatch b, const uint32_t* __restrict__ u_roff, uint32_t* __restrict__ g_roff) {
+// Clip-rescue path only: the front kernel cannot know which candidates survive k_ksw / k_build, so the match
+// count of each alignment (a_cand.w) is filled in afterwards.
+__global__ void __launch_bounds__(256) k_count_valid(DevBatch b, const Ctl* __restrict__ ctl, uint4* __restrict__ a_cand, const uint32_t* __restrict__ m_tid) {
+  if (ctl_overflow(ctl)) return;
+  const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= b.n_aln) return;
+  uint4 ac = a_cand[a]; uint32_t nv = 0;
+  for (uint32_t c = ac.x, e = ac.x + ac.y + ac.z; c < e; c++) nv += m_tid[c] != NONE;
+  ac.w = nv; a_cand[a] = ac;
+}
+
+__global__ void k_group_rows(DevBatch b, const unsigned long long* __restrict__ u_off, uint32_t* __restrict__ g_roff) {
   const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
-  if (g <= b.n_groups) g_roff[g] = u_roff[g < b.n_groups ? b.group_off[g] : b.n_aln];
+  if (g <= b.n_groups) g_roff[g] = (uint32_t)u_off[g < b.n_groups ? b.group_off[g] : b.n_aln];
 }
 
 }  // namespace brb
