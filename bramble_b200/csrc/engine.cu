@@ -92,7 +92,7 @@ struct brb_ctx {
   Buf q_any, a_cand, scan_tmp;
   Buf c_rec, c_task, c_first, c_last, c_nseg, c_nguide, c_cap, ipool;
   Buf r_left, r_right, rpool;
-  Buf m_tid, m_pos, m_sim, m_clip, m_ilen, m_ioff, c_partner, c_tmpoff, c_clen_r, c_clen_m, c_key;
+  Buf m_tid, m_rec, m_sim, m_clip, c_srec, c_key;
   Buf u_cnt, u_off, g_roff;
   Buf o_src, o_tid, o_pos, o_strand, o_flags, o_sim, o_clip, o_coff, tpool, opool;
   HBuf h_small, h_out;
@@ -102,7 +102,7 @@ struct brb_ctx {
   std::vector<Buf*> all() {
     return {&in_group_off, &in_refid, &in_strand, &in_exon_off, &in_exon_st, &in_exon_en, &in_cigar_off, &in_cigar, &in_mate, &in_seq_off,
             &in_seq, &ctl, &q_any, &a_cand, &scan_tmp, &c_rec, &c_task, &c_first, &c_last, &c_nseg, &c_nguide, &c_cap, &ipool,
-            &r_left, &r_right, &rpool, &m_tid, &m_pos, &m_sim, &m_clip, &m_ilen, &m_ioff, &c_partner, &c_tmpoff, &c_clen_r, &c_clen_m, &c_key, &u_cnt, &u_off, &g_roff,
+            &r_left, &r_right, &rpool, &m_tid, &m_rec, &m_sim, &m_clip, &c_srec, &c_key, &u_cnt, &u_off, &g_roff,
             &o_src, &o_tid, &o_pos, &o_strand, &o_flags, &o_sim, &o_clip, &o_coff, &tpool, &opool};
   }
 };
@@ -345,10 +345,10 @@ int ensure_pools(brb_ctx* c, bool rescue) {
   const size_t n = b.n_aln, C = c->cap_cand, R = c->cap_rows;
   ENS(c->q_any, (size_t)2 * b.n_exon + 16); ENS(c->a_cand, n * 16);
   ENS(c->u_cnt, n * 8); ENS(c->u_off, (n + 1) * 8); ENS(c->g_roff, (size_t)(b.n_groups + 1) * 4);
-  ENS(c->c_task, C * 4); ENS(c->c_partner, C * 4); ENS(c->c_tmpoff, C * 4); ENS(c->c_clen_r, C * 4); ENS(c->c_clen_m, C * 4); ENS(c->c_key, C * 8);
-  ENS(c->m_tid, C * 4); ENS(c->m_pos, C * 4); ENS(c->m_ilen, C * 4); ENS(c->m_ioff, C * 4);
+  ENS(c->c_srec, C * 16); ENS(c->c_key, C * 8);
+  ENS(c->m_tid, C * 4); ENS(c->m_rec, C * 16);
   if (c->have_scores) { ENS(c->m_sim, C * 8); ENS(c->m_clip, C * 4); ENS(c->o_sim, R * 8); ENS(c->o_clip, R * 4); }
-  if (rescue) { ENS(c->c_rec, C * 4); ENS(c->c_first, C * 4); ENS(c->c_last, C * 4); ENS(c->c_nseg, C * 4); ENS(c->c_nguide, C * 4); ENS(c->c_cap, C * 4); }
+  if (rescue) { ENS(c->c_rec, C * 4); ENS(c->c_task, C * 4); ENS(c->c_first, C * 4); ENS(c->c_last, C * 4); ENS(c->c_nseg, C * 4); ENS(c->c_nguide, C * 4); ENS(c->c_cap, C * 4); }
   ENS(c->ipool, (size_t)c->cap_ideal * 4);
   ENS(c->o_src, R * 4); ENS(c->o_tid, R * 4); ENS(c->o_pos, R * 4); ENS(c->o_strand, R); ENS(c->o_flags, R);
   ENS(c->o_coff, (R + 1) * 4);
@@ -401,19 +401,18 @@ int project_resident(brb_ctx* c, const brb_params& p) {
     memset(hctl, 0, sizeof(Ctl));
     hctl->cap_cand = c->cap_cand; hctl->cap_ideal = c->cap_ideal; hctl->cap_rows = c->cap_rows; hctl->cap_tmpw = c->cap_tmpw; hctl->cap_outw = c->cap_outw;
     CU(cudaMemcpyAsync(ctl, hctl, sizeof(Ctl), cudaMemcpyHostToDevice, st));
-    Matches M; M.tid = c->m_tid.as<uint32_t>(); M.pos = c->m_pos.as<uint32_t>();
+    Matches M; M.tid = c->m_tid.as<uint32_t>(); M.rec = c->m_rec.as<uint4>();
     M.sim = c->have_scores ? c->m_sim.as<double>() : nullptr; M.clip = c->have_scores ? c->m_clip.as<int32_t>() : nullptr;
-    M.ilen = c->m_ilen.as<uint32_t>(); M.ioff = c->m_ioff.as<uint32_t>();
     // ---- phase 1: lookup + candidate lists
     CU(cudaEventRecord(c->ev[0], st));
     // ---- phases 1..4: lookup, candidates, chain walk, (clip rescue), ideal CIGAR + scores
     if (short_front) {
-      if (p.filter_by_similarity) k_front_short<true><<<ncta_front, 256, 0, st>>>(ix, b, p, ctl, c->a_cand.as<uint4>(), c->c_task.as<uint32_t>(), c->ipool.as<uint32_t>(), M);
-      else k_front_short<false><<<ncta_front, 256, 0, st>>>(ix, b, p, ctl, c->a_cand.as<uint4>(), c->c_task.as<uint32_t>(), c->ipool.as<uint32_t>(), M);
+      if (p.filter_by_similarity) k_front_short<true><<<ncta_front, 256, 0, st>>>(ix, b, p, ctl, c->a_cand.as<uint4>(), c->ipool.as<uint32_t>(), M);
+      else k_front_short<false><<<ncta_front, 256, 0, st>>>(ix, b, p, ctl, c->a_cand.as<uint4>(), c->ipool.as<uint32_t>(), M);
       L++;
       CU(cudaEventRecord(c->ev[1], st)); CU(cudaEventRecord(c->ev[2], st)); CU(cudaEventRecord(c->ev[3], st)); CU(cudaEventRecord(c->ev[4], st));
     } else if (!rescue) {
-      k_front<true><<<ncta_front, 256, 0, st>>>(ix, b, p, ctl, c->q_any.as<uint8_t>(), c->a_cand.as<uint4>(), nullptr, c->c_task.as<uint32_t>(),
+      k_front<true><<<ncta_front, 256, 0, st>>>(ix, b, p, ctl, c->q_any.as<uint8_t>(), c->a_cand.as<uint4>(), nullptr, nullptr,
                                           c->ipool.as<uint32_t>(), M); L++;
       CU(cudaEventRecord(c->ev[1], st)); CU(cudaEventRecord(c->ev[2], st)); CU(cudaEventRecord(c->ev[3], st)); CU(cudaEventRecord(c->ev[4], st));
     } else {
@@ -436,11 +435,9 @@ int project_resident(brb_ctx* c, const brb_params& p) {
       CU(cudaEventRecord(c->ev[4], st));
     }
     // ---- phase 5: pairing + emission
-    PairIn pv; pv.a_cand = c->a_cand.as<uint4>(); pv.c_task = c->c_task.as<uint32_t>(); pv.m_tid = c->m_tid.as<uint32_t>();
-    pv.m_pos = c->m_pos.as<uint32_t>(); pv.m_ilen = c->m_ilen.as<uint32_t>(); pv.m_ioff = c->m_ioff.as<uint32_t>();
+    PairIn pv; pv.a_cand = c->a_cand.as<uint4>(); pv.m_tid = c->m_tid.as<uint32_t>(); pv.m_rec = c->m_rec.as<uint4>();
     pv.m_sim = M.sim; pv.m_clip = M.clip; pv.ipool = c->ipool.as<uint32_t>();
-    SlotOut so; so.key = c->c_key.as<unsigned long long>(); so.partner = c->c_partner.as<uint32_t>(); so.tmpoff = c->c_tmpoff.as<uint32_t>(); so.clen_r = c->c_clen_r.as<uint32_t>();
-    so.clen_m = c->c_clen_m.as<uint32_t>();
+    SlotOut so; so.key = c->c_key.as<unsigned long long>(); so.rec = c->c_srec.as<uint4>();
     if (rescue) { k_count_valid<<<grid_for(n, 256), 256, 0, st>>>(b, ctl, c->a_cand.as<uint4>(), c->m_tid.as<uint32_t>()); L++; }
     k_pair_a<<<ncta_pa, 256, 0, st>>>(b, ctl, pv, so, c->tpool.as<uint32_t>(), c->u_cnt.as<unsigned long long>()); L++;
     CU(cudaEventRecord(c->ev[5], st));

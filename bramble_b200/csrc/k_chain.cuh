@@ -235,12 +235,14 @@ __device__ __forceinline__ bool dedupe_first(const DevIndex& ix, const brb_param
 }
 
 struct Matches {          // per candidate slot; tid == NONE marks "no match"
-  uint32_t* tid; uint32_t* pos; double* sim; int32_t* clip; uint32_t* ilen; uint32_t* ioff;
+  uint32_t* tid;
+  uint4* rec;             // .x pos  .y ideal-CIGAR length  .z its offset in the ideal pool, or the CIGAR word itself when the length is 1  .w task (2a+s)
+  double* sim; int32_t* clip;     // null when every score is 0 by construction
 };
 
 // Pass 2 for one candidate whose pass-1 facts are in `w`: ideal CIGAR into pool, scores, similarity filter
 // (src/evaluate.cpp:843-865, FP64, operation order kept), match row.
-__device__ __forceinline__ bool build_one(const DevIndex& ix, const DevBatch& b, const brb_params& p, uint32_t c, const ReadExons& rx, int s,
+__device__ __forceinline__ bool build_one(const DevIndex& ix, const DevBatch& b, const brb_params& p, uint32_t c, uint32_t task, const ReadExons& rx, int s,
                                           const uint8_t* q_any, WalkOut w, const RescueSeg* L, const RescueSeg* R,
                                           const uint32_t* __restrict__ rpool, uint32_t* __restrict__ ipool, uint32_t ioff, const Matches& M) {
   if (L && L->ok) { w.n_seg++; w.n_guide++; }
@@ -256,9 +258,10 @@ __device__ __forceinline__ bool build_one(const DevIndex& ix, const DevBatch& b,
     else keep = false;
   }
   M.tid[c] = keep ? rec_key(ix.rec, w.first_rec).tid : NONE;
-  M.pos[c] = s ? lp : fp;
-  if (M.sim) { M.sim[c] = sim_score; M.clip[c] = m.clip; }      // null when every score is 0 by construction
-  M.ilen[c] = m.n; M.ioff[c] = ioff;
+  if (keep) {
+    M.rec[c] = make_uint4(s ? lp : fp, m.n, m.n == 1 ? m.last : ioff, task);
+    if (M.sim) { M.sim[c] = sim_score; M.clip[c] = m.clip; }
+  }
   return keep;
 }
 
@@ -307,7 +310,7 @@ __global__ void __launch_bounds__(256) k_build(DevIndex ix, DevBatch b, brb_para
     WalkOut w; w.first_rec = F.first[c]; w.last_rec = F.last[c]; w.n_seg = F.nseg[c]; w.n_guide = F.nguide[c]; w.cap = cap;
     RescueSeg L, R; L.ok = 0; R.ok = 0;
     if (r_left) { L = r_left[c]; R = r_right[c]; }
-    kept += build_one(ix, b, p, c, read_exons(b, a), s, q_any, w, r_left ? &L : nullptr, r_left ? &R : nullptr, rpool, ipool, ioff, M) ? 1u : 0u;
+    kept += build_one(ix, b, p, c, task, read_exons(b, a), s, q_any, w, r_left ? &L : nullptr, r_left ? &R : nullptr, rpool, ipool, ioff, M) ? 1u : 0u;
   }
   for (int d = 16; d; d >>= 1) kept += __shfl_down_sync(0xffffffffu, kept, d);
   if (lane == 0 && kept) atomicAdd(&ctl->n_matches, (unsigned long long)kept);
@@ -331,7 +334,7 @@ struct ShortBuilder {
     if (n > 0 && (last & 0xfu) == op) last = (((last >> 4) + len) << 4) | op;
     else { if (n > 0) cig[n - 1] = last; last = (len << 4) | op; n++; }
   }
-  __device__ __forceinline__ void finish() { if (n > 0) cig[n - 1] = last; }
+  __device__ __forceinline__ void finish() { if (n > 1) cig[n - 1] = last; }      // a one-word CIGAR stays in the match record
   __device__ __forceinline__ void add_ops(uint32_t v) { if (SIM) ops += v; }
   __device__ __forceinline__ void add_cov(uint32_t v) { if (SIM) cov += v; }
   __device__ __forceinline__ void penal() { if (SIM) ops += (ops * 0.2); }
@@ -371,7 +374,8 @@ __device__ __forceinline__ void build_match_short(ShortBuilder<SIM>& m, int st, 
 // candidate is eliminated; otherwise the ideal CIGAR is in cig[0..ilen) and pos / sim_score are set.
 template <bool SIM>
 __device__ __forceinline__ bool eval_short(const DevIndex& ix, const DevBatch& b, const brb_params& p, const ReadExons& rx, int s,
-                                           RecKey key, RecLink lk, uint32_t* __restrict__ cig, uint32_t& pos, uint32_t& ilen, double& sim_score) {
+                                           RecKey key, RecLink lk, uint32_t* __restrict__ cig, uint32_t& pos, uint32_t& ilen, uint32_t& word,
+                                           double& sim_score) {
   const bool minus = s;
   const uint32_t n_ex = rx.n_ex;
   ShortBuilder<SIM> m; m.init(cig);
@@ -415,7 +419,7 @@ __device__ __forceinline__ bool eval_short(const DevIndex& ix, const DevBatch& b
     if (!(sim > thr)) return false;
     const double x = (sim - thr) / (1.0 - thr); sim_score = x * x * (double)(m.junc + 1);
   }
-  pos = minus ? last_pos : first_pos; ilen = m.n;
+  pos = minus ? last_pos : first_pos; ilen = m.n; word = m.last;
   return true;
 }
 

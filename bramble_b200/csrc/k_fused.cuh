@@ -138,8 +138,7 @@ __global__ void __launch_bounds__(256) k_front(DevIndex ix, DevBatch b, brb_para
           const uint32_t ioff = warp_pool_alloc(wp, &ctl->n_ideal, cap_ideal, ok ? w.cap : 0, lane, pool_fit);
           bool keep = false;
           if (sv && slots_fit) {
-            c_task[slot] = task;
-            if (ok && pool_fit) keep = build_one(ix, b, p, slot, rx, s, q_any, w, nullptr, nullptr, nullptr, ipool, ioff, M);
+            if (ok && pool_fit) keep = build_one(ix, b, p, slot, task, rx, s, q_any, w, nullptr, nullptr, nullptr, ipool, ioff, M);
             else M.tid[slot] = NONE;
           }
           kept += keep ? 1u : 0u;
@@ -174,8 +173,7 @@ __global__ void __launch_bounds__(256) k_front(DevIndex ix, DevBatch b, brb_para
 // comes from the generic kernel, see BRB_OPT_GENERIC_FRONT.)
 template <bool SIM>
 __global__ void __launch_bounds__(256, 4) k_front_short(DevIndex ix, DevBatch b, brb_params p, Ctl* __restrict__ ctl,
-                                                        uint4* __restrict__ a_cand, uint32_t* __restrict__ c_task,
-                                                        uint32_t* __restrict__ ipool, Matches M) {
+                                                        uint4* __restrict__ a_cand, uint32_t* __restrict__ ipool, Matches M) {
   __shared__ uint32_t s_nvalid[8][32];                      // per warp: matches kept per alignment of the current batch
   const unsigned lane = threadIdx.x & 31;
   uint32_t* nval = s_nvalid[threadIdx.x >> 5];
@@ -246,7 +244,7 @@ __global__ void __launch_bounds__(256, 4) k_front_short(DevIndex ix, DevBatch b,
       bool pool_fit;
       const uint32_t ioff = warp_pool_alloc(wp, &ctl->n_ideal, cap_ideal, want, lane, pool_fit);
       if (!actv || !slots_fit) continue;
-      bool ok = false; uint32_t pos = 0, ilen = 0; double sim = 0.0;
+      bool ok = false; uint32_t pos = 0, ilen = 0, word = 0; double sim = 0.0;
       if (sv && pool_fit) {
         RecLink lk = rec_link(ix.rec, rec0);
         ok = true;
@@ -255,10 +253,10 @@ __global__ void __launch_bounds__(256, 4) k_front_short(DevIndex ix, DevBatch b,
           ok = dedupe_first(ix, p, ox, s, rec0);
           if (ok && rec0 != r1) { key = rec_key(ix.rec, rec0); lk = rec_link(ix.rec, rec0); }
         }
-        if (ok) ok = eval_short<SIM>(ix, b, p, ox, s, key, lk, ipool + ioff, pos, ilen, sim);
+        if (ok) ok = eval_short<SIM>(ix, b, p, ox, s, key, lk, ipool + ioff, pos, ilen, word, sim);
       }
       if (ok) {
-        M.tid[slot] = key.tid; M.pos[slot] = pos; M.ilen[slot] = ilen; M.ioff[slot] = ioff; c_task[slot] = 2 * (wb * 32 + L) + s;
+        M.tid[slot] = key.tid; M.rec[slot] = make_uint4(pos, ilen, ilen == 1 ? word : ioff, 2 * (wb * 32 + L) + s);
         if (SIM) { M.sim[slot] = sim; M.clip[slot] = 0; }
         kept++; atomicAdd(&nval[L], 1u);
       } else M.tid[slot] = NONE;

@@ -44,20 +44,24 @@ struct CigOut {                 // coalescing appender; the open (last) op lives
   __device__ __forceinline__ void finish() { if (n > 0) p[n - 1] = last; }
 };
 
-// Returns the number of words written to `out` (capacity >= n_real + n_ideal + 2).
-__device__ uint32_t merge_cigars(const uint32_t* __restrict__ real, uint32_t n_real, const uint32_t* __restrict__ ideal,
-                                 uint32_t n_ideal, uint32_t* __restrict__ out) {
-  // The common short-read row: the real CIGAR only has M/=/X and N, the ideal CIGAR is one M of the same aligned
-  // length.  The two-cursor merge below then skips every N, turns every chunk into M (merge_ops) and both
-  // sides end together: the result is the ideal CIGAR itself.
-  if (n_ideal == 1 && n_real > 0 && (ideal[0] & 0xfu) == CM) {
-    uint32_t sum = 0; bool simple = true;
-    for (uint32_t i = 0; i < n_real; i++) {
-      const uint32_t rw = real[i], op = rw & 0xfu;
-      if (op == CM || op == CEQ || op == CX) sum += rw >> 4; else if (op != CN) { simple = false; break; }
-    }
-    if (simple && sum > 0 && sum == (ideal[0] >> 4)) { out[0] = ideal[0]; return 1; }
+// The common short-read row: the real CIGAR only has M/=/X and N, the ideal CIGAR is the single word `iword` = one
+// M of the same aligned length.  merge_cigars then skips every N, turns every chunk into M (merge_ops) and both
+// sides end together: the result is the ideal CIGAR itself.  Returns false when the row needs the general merge.
+__device__ __forceinline__ bool merge_is_trivial(const uint32_t* __restrict__ real, uint32_t n_real, uint32_t iword) {
+  if (n_real == 0 || (iword & 0xfu) != CM) return false;
+  uint32_t sum = 0;
+  for (uint32_t i = 0; i < n_real; i++) {
+    const uint32_t rw = __ldg(&real[i]), op = rw & 0xfu;
+    if (op == CM || op == CEQ || op == CX) sum += rw >> 4; else if (op != CN) return false;
   }
+  return sum > 0 && sum == (iword >> 4);
+}
+
+// Returns the number of words written to `out` (capacity >= n_real + n_ideal + 2).
+// A one-word ideal CIGAR is passed by value in `iword` (match records keep it inline; `ideal` is then unused).
+__device__ uint32_t merge_cigars(const uint32_t* __restrict__ real, uint32_t n_real, const uint32_t* __restrict__ ideal_,
+                                 uint32_t n_ideal, uint32_t iword, uint32_t* __restrict__ out) {
+  auto ideal = [&](uint32_t k) -> uint32_t { return n_ideal == 1 ? iword : ideal_[k]; };
   CigOut res; res.p = out; res.n = 0; res.last = 0; res.saw_i = false;
   uint32_t front_hard = 0, front_soft = 0, ci = 0;
   if (n_real > 0 && (real[0] & 0xfu) == CH) { front_hard = real[0] >> 4; ci++; }
@@ -74,7 +78,7 @@ __device__ uint32_t merge_cigars(const uint32_t* __restrict__ real, uint32_t n_r
   while (clips > 0 && ri < n_real) {                                            // (2) leading soft clip vs override ops
     const uint32_t rw = real[ri], rop = rw & 0xfu, rrem = (rw >> 4) - rpos;
     const bool have_i = ii < n_ideal;
-    const uint32_t iw = have_i ? ideal[ii] : 0, iop = have_i ? (iw & 0xfu) : 0xffu, irem = have_i ? (iw >> 4) - ipos : 0xffffffffu;
+    const uint32_t iw = have_i ? ideal(ii) : 0, iop = have_i ? (iw & 0xfu) : 0xffu, irem = have_i ? (iw >> 4) - ipos : 0xffffffffu;
     const bool ov = have_i && (iop == OV_M || iop == OV_D || iop == OV_I || iop == OV_S);
     if (ov) {
       if (iop == OV_D) {
@@ -96,9 +100,9 @@ __device__ uint32_t merge_cigars(const uint32_t* __restrict__ real, uint32_t n_r
     }
   }
   while (ri < n_real || ii < n_ideal) {                                         // (3) main two-cursor merge
-    if (ri >= n_real) { const uint32_t iw = ideal[ii]; res.add(iw & 0xfu, (iw >> 4) - ipos); ii++; ipos = 0; continue; }
+    if (ri >= n_real) { const uint32_t iw = ideal(ii); res.add(iw & 0xfu, (iw >> 4) - ipos); ii++; ipos = 0; continue; }
     if (ii >= n_ideal) { const uint32_t rw = real[ri]; res.add(rw & 0xfu, (rw >> 4) - rpos); ri++; rpos = 0; continue; }
-    const uint32_t rw = real[ri], iw = ideal[ii], rop = rw & 0xfu, iop = iw & 0xfu;
+    const uint32_t rw = real[ri], iw = ideal(ii), rop = rw & 0xfu, iop = iw & 0xfu;
     const uint32_t rrem = (rw >> 4) - rpos, irem = (iw >> 4) - ipos;
     if (rop == CN) { ri++; rpos = 0; }
     else if (rop == CD && (iop == CS || iop == OV_S || iop == CI || iop == OV_I)) {
@@ -136,7 +140,8 @@ __global__ void k_merge_pairs(uint32_t n, const uint32_t* real_off, const uint32
                               const uint32_t* ideal, const uint32_t* out_off, uint32_t* out_len, uint32_t* out) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  out_len[i] = merge_cigars(real + real_off[i], real_off[i + 1] - real_off[i], ideal + ideal_off[i], ideal_off[i + 1] - ideal_off[i],
+  const uint32_t ni = ideal_off[i + 1] - ideal_off[i];
+  out_len[i] = merge_cigars(real + real_off[i], real_off[i + 1] - real_off[i], ideal + ideal_off[i], ni, ni == 1 ? ideal[ideal_off[i]] : 0,
                             out + out_off[i]);
 }
 

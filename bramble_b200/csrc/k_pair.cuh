@@ -27,21 +27,21 @@
 namespace brb {
 
 constexpr uint32_t SELF = 0xfffffffeu;   // emitted without a mate row
+constexpr uint32_t INLINE = 0xffffffffu; // SlotOut::rec.w: both merged CIGARs are one word each and live in the record
+constexpr unsigned long long NONE64 = ~0ull;
 
 struct PairIn {
   const uint4* a_cand;          // per alignment: first slot, #slots '+', #slots '-', #matches
-  const uint32_t* c_task;       // per slot holding a match: 2a+s
   const uint32_t* m_tid;        // per slot: tid of the match or NONE
-  const uint32_t* m_pos; const uint32_t* m_ilen; const uint32_t* m_ioff;
+  const uint4* m_rec;           // per slot holding a match: pos, ideal-CIGAR length, pool offset or the word itself, task
   const double* m_sim; const int32_t* m_clip;      // null when every score is 0
-  const uint32_t* ipool;        // ideal CIGARs
+  const uint32_t* ipool;        // ideal CIGARs longer than one word
 };
-constexpr unsigned long long NONE64 = ~0ull;
 struct SlotOut {                // per slot of a unit owner that has matches
   unsigned long long* key;      // emitted match: tid << 32 | CIGAR words of its row(s); otherwise NONE64
-  uint32_t* partner;            // (emitted matches) SELF: unpaired row; else the mate's slot
-  uint32_t* tmpoff;             // merged CIGARs in the scratch pool: read row at tmpoff, mate row right after the read row's capacity
-  uint32_t* clen_r; uint32_t* clen_m;
+  uint4* rec;                   // emitted match: .x partner (SELF: unpaired row, else the mate's slot) and
+                                //   .w == INLINE: .y / .z = the one-word merged CIGAR of the read row / mate row
+                                //   otherwise   : .y / .z = CIGAR lengths, .w = scratch-pool offset (mate row after the read row's capacity)
 };
 
 // [lo,hi) = my lanes of this chunk; sum over them of a per-lane value given its inclusive warp prefix P
@@ -99,20 +99,25 @@ __global__ void __launch_bounds__(256) k_pair_a(DevBatch b, Ctl* __restrict__ ct
         }
       }
       const bool emitted = part != NONE, paired = emitted && part != SELF;
-      uint32_t il = 0, io = 0, pil = 0, pio = 0;
-      if (emitted) { il = v.m_ilen[c]; io = v.m_ioff[c]; }
-      if (paired) { pil = v.m_ilen[part]; pio = v.m_ioff[part]; }
-      const uint32_t cap_r = o_nrc + il + 2, want = emitted ? cap_r + (paired ? o_mnrc + pil + 2 : 0) : 0;
+      uint4 mr = make_uint4(0, 0, 0, 0), pr = make_uint4(0, 0, 0, 0);
+      if (emitted) mr = v.m_rec[c];
+      if (paired) pr = v.m_rec[part];
+      // one-word results stay in the slot record: no scratch traffic for the common short-read row
+      const bool inl = emitted && mr.y == 1 && merge_is_trivial(b.cigar + o_ro, o_nrc, mr.z) &&
+                       (!paired || (pr.y == 1 && merge_is_trivial(b.cigar + o_mro, o_mnrc, pr.z)));
+      const uint32_t cap_r = o_nrc + mr.y + 2, want = (emitted && !inl) ? cap_r + (paired ? o_mnrc + pr.y + 2 : 0) : 0;
       bool fit;
       const uint32_t toff = warp_pool_alloc(wp, &ctl->n_tmpw, cap_tmpw, want, lane, fit);
       uint32_t clr = 0, clm = 0;
-      if (emitted && fit) {
-        clr = merge_cigars(b.cigar + o_ro, o_nrc, v.ipool + io, il, tpool + toff);
-        if (paired) clm = merge_cigars(b.cigar + o_mro, o_mnrc, v.ipool + pio, pil, tpool + toff + cap_r);
+      if (inl) { clr = 1; clm = paired ? 1 : 0; }
+      else if (emitted && fit) {
+        // (one-word ideal CIGARs are not in the pool: .z is the word)
+        clr = merge_cigars(b.cigar + o_ro, o_nrc, v.ipool + mr.z, mr.y, mr.z, tpool + toff);
+        if (paired) clm = merge_cigars(b.cigar + o_mro, o_mnrc, v.ipool + pr.z, pr.y, pr.z, tpool + toff + cap_r);
       }
       if (actv) {
         so.key[c] = emitted ? ((unsigned long long)tid << 32) | (clr + clm) : NONE64;
-        if (emitted) { so.partner[c] = part; so.tmpoff[c] = toff; so.clen_r[c] = clr; so.clen_m[c] = clm; }
+        if (emitted) so.rec[c] = inl ? make_uint4(part, mr.z, pr.z, INLINE) : make_uint4(part, clr, clm, toff);
       }
       // rows / words of MY alignment in this chunk
       const uint32_t Pr = warp_incl_scan(emitted ? (paired ? 2u : 1u) : 0u, lane), Pw = warp_incl_scan(clr + clm, lane);
@@ -170,7 +175,7 @@ __global__ void __launch_bounds__(256) k_pair_b(DevBatch b, Ctl* __restrict__ ct
       if (!actv) continue;
       const unsigned long long mykey = so.key[c];
       if (mykey == NONE64) continue;
-      const uint32_t tid = (uint32_t)(mykey >> 32), part = so.partner[c];
+      const uint32_t tid = (uint32_t)(mykey >> 32);
       // rank among the emitted matches of the read: ascending tid, slot order among equals; CIGAR words before me
       uint32_t rank = 0, wpre = 0;
       for (uint32_t d = o_off, e = o_off + o_n; d < e; d++) {
@@ -178,22 +183,26 @@ __global__ void __launch_bounds__(256) k_pair_b(DevBatch b, Ctl* __restrict__ ct
         const uint32_t t2 = (uint32_t)(k >> 32);
         if (k != NONE64 && (t2 < tid || (t2 == tid && d < c))) { rank++; wpre += (uint32_t)k; }
       }
-      const bool paired = part != SELF;
+      const uint4 sr = so.rec[c], mr = v.m_rec[c];
+      const uint32_t part = sr.x;
+      const bool paired = part != SELF, inl = sr.w == INLINE;
       const uint32_t row = o_roff + (paired ? 2 * rank : rank), w0 = o_woff + wpre;
-      const uint32_t toff = so.tmpoff[c], clr = so.clen_r[c];
-      auto put = [&](uint32_t r, uint32_t cc, uint32_t aln, uint32_t t, uint8_t fl, uint32_t wpos, const uint32_t* src, uint32_t len) {
-        const bool minus = v.c_task[cc] & 1;
-        o.src[r] = aln; o.tid[r] = t; o.pos[r] = v.m_pos[cc]; o.strand[r] = minus ? '-' : '+'; o.flags[r] = fl; o.coff[r] = wpos;
+      const uint32_t clr = inl ? 1u : sr.y;
+      auto put = [&](uint32_t r, uint32_t cc, const uint4& m, uint32_t aln, uint32_t t, uint8_t fl, uint32_t wpos, uint32_t word, const uint32_t* src, uint32_t len) {
+        const bool minus = m.w & 1;
+        o.src[r] = aln; o.tid[r] = t; o.pos[r] = m.x; o.strand[r] = minus ? '-' : '+'; o.flags[r] = fl; o.coff[r] = wpos;
         if (v.m_sim) { o.sim[r] = v.m_sim[cc]; o.clip[r] = v.m_clip[cc]; }
-        if (minus) for (uint32_t i = 0; i < len; i++) o.pool[wpos + i] = src[len - 1 - i];      // reverse_complement_bam, src/bam.cpp:636-702
+        if (inl) o.pool[wpos] = word;
+        else if (minus) for (uint32_t i = 0; i < len; i++) o.pool[wpos + i] = src[len - 1 - i];      // reverse_complement_bam, src/bam.cpp:636-702
         else for (uint32_t i = 0; i < len; i++) o.pool[wpos + i] = src[i];
       };
-      if (!paired) put(row, c, wb * 32 + L, tid, BRB_REC_FIRST, w0, tpool + toff, clr);
+      if (!paired) put(row, c, mr, wb * 32 + L, tid, BRB_REC_FIRST, w0, sr.y, tpool + sr.w, clr);
       else {
         const uint32_t t2 = v.m_tid[part];
+        const uint4 pm = v.m_rec[part];
         const uint8_t fl = BRB_REC_PAIRED | (t2 == tid ? BRB_REC_SAMETX : 0);
-        put(row, c, wb * 32 + L, tid, fl | BRB_REC_FIRST, w0, tpool + toff, clr);
-        put(row + 1, part, (uint32_t)o_mate, t2, fl, w0 + clr, tpool + toff + (o_nrc + v.m_ilen[c] + 2), so.clen_m[c]);
+        put(row, c, mr, wb * 32 + L, tid, fl | BRB_REC_FIRST, w0, sr.y, tpool + sr.w, clr);
+        put(row + 1, part, pm, (uint32_t)o_mate, t2, fl, w0 + clr, sr.z, tpool + sr.w + (o_nrc + mr.y + 2), inl ? 1u : sr.z);
       }
     }
   }
