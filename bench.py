@@ -70,6 +70,19 @@ class ClockSampler:
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": reasons, "samples": len(sm)}
 
 
+def _traffic(names):
+    """dram__bytes_read.sum + dram__bytes_write.sum per step from the committed `ncu --set full` capture
+    (profiles/r01_v8_traffic.json), valid for the default workload size only; else None."""
+    try:
+        if names != 2_000_000:
+            return None, None
+        with open(os.path.join(ROOT, "profiles", "r01_v8_traffic.json")) as f:
+            t = json.load(f)
+        return int(sum(t.values())), {k: int(v) for k, v in t.items()}
+    except Exception:
+        return None, None
+
+
 def workload(seed, names):
     from bramble_b200 import synth_fast as sf
     A = sf.make_annotation(2002)
@@ -185,7 +198,7 @@ def main():
     # them once, untimed, from the generic front kernel; the timed path is the engine's default choice
     eng.set_option(capi.OPT_GENERIC_FRONT, 1)
     eng.run_resident(p)
-    alg_ref = int(eng.stats().alg_bytes)
+    alg_ref, alg_front = int(eng.stats().alg_bytes), int(eng.stats().alg_bytes_front)
     eng.set_option(capi.OPT_GENERIC_FRONT, 0)
     for _ in range(max(3, args.warmup)):
         eng.run_resident(p)
@@ -233,17 +246,24 @@ def main():
         e2e = total_aln * args.steps / (e2e_ms_max / 1e3)
         alg = alg_ref
         achieved = alg / (ms / args.steps / 1e3) / 1e9
-        names = {"ms_lookup": "k_lookup+k_fill_cand", "ms_chain": "k_chain", "ms_finalize": "k_build", "ms_pair": "k_pair_count+k_pair_emit",
-                 "ms_merge": "k_merge", "ms_rescue": "k_ksw"}
+        names = {"ms_lookup": "k_front_short (lookup + evaluate)", "ms_chain": "k_chain (rescue path only)", "ms_finalize": "k_build (rescue path only)",
+                 "ms_pair": "k_pair_a (pairing + CIGAR merge)", "ms_merge": "scan + k_pair_b (rank + rows)", "ms_rescue": "k_ksw (rescue path only)"}
         top = max(phase, key=lambda k: phase[k])
+        traffic, traffic_by_kernel = _traffic(args.names)
+        alg_of = {"ms_lookup": alg_front, "ms_pair": alg - alg_front, "ms_merge": alg - alg_front}
+        top_ms = phase[top] / args.steps
+        top_alg = alg_of.get(top, alg)
         line = {"metric": metric, "value": value, "unit": unit, "n_gpus": args.gpus, "steps": args.steps, "warmup": max(3, args.warmup),
                 "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32",
                 "data": "synthetic", "config": config, "gpu_launches": launches, "clocks": clocks,
                 "e2e": {"value": e2e, "unit": unit, "h2d_bytes_per_step": int(st2.h2d_bytes), "d2h_bytes_per_step": int(st2.d2h_bytes)},
-                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                             "traffic_by_kernel": traffic_by_kernel, "traffic_source": "profiles/r01_v8_summary.md (ncu --set full, one step)",
                              "peak_source": peak_src, "scope": "whole kernel sequence of one step (algorithmic bytes of SURVEY 8(d) / DESIGN.md)",
                              "alg_bytes_per_step": alg, "alg_bytes_per_alignment": alg / max(1, n_aln),
                              "top_kernel": names[top], "top_kernel_share": phase[top] / max(1e-9, sum(phase.values())),
+                             "top_kernel_ms": top_ms, "top_kernel_alg_bytes": top_alg,
+                             "top_kernel_achieved": top_alg / (top_ms / 1e3) / 1e9, "top_kernel_frac": top_alg / (top_ms / 1e3) / 1e9 / peak,
                              "phase_ms_per_step": {names[k]: v / args.steps for k, v in phase.items()}},
                 "work": {"alignments_per_gpu": n_aln, "candidates": int(st.n_candidates), "matches": int(st.n_matches), "records": int(st.n_rec)}}
         if args.gpus == 1 and not args.no_cpu_baseline:

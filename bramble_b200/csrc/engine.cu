@@ -470,8 +470,8 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   S.ms_finalize = ms_between(c->ev[3], c->ev[4]); S.ms_pair = ms_between(c->ev[4], c->ev[5]); S.ms_merge = ms_between(c->ev[5], c->ev[6]);
   S.kernel_ms = ms_between(c->ev[0], c->ev[6]);
   // algorithmic bytes, SURVEY.md 8(d) / DESIGN.md: per-alignment SoA + 56 B per index hit + output rows + rescue bases
-  S.alg_bytes = (uint64_t)n * 16 + (uint64_t)b.n_exon * 8 + (uint64_t)b.n_cigar * 4 + hctl->n_mates * 4 + hctl->n_hits * 56 +
-                (uint64_t)hctl->n_rows * 40 + hctl->out_words * 4 + c->rescue_bytes;
+  S.alg_bytes_front = (uint64_t)n * 16 + (uint64_t)b.n_exon * 8 + hctl->n_mates * 4 + hctl->n_hits * 56;
+  S.alg_bytes = S.alg_bytes_front + (uint64_t)b.n_cigar * 4 + (uint64_t)hctl->n_rows * 40 + hctl->out_words * 4 + c->rescue_bytes;
   c->have_result = true;
   return BRB_OK;
 }

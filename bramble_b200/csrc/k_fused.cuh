@@ -172,7 +172,7 @@ __global__ void __launch_bounds__(256) k_front(DevIndex ix, DevBatch b, brb_para
 // marked empty.  (n_hits then only counts exon-0 hits; the reference-defined figure for the roofline numerator
 // comes from the generic kernel, see BRB_OPT_GENERIC_FRONT.)
 template <bool SIM>
-__global__ void __launch_bounds__(256, 4) k_front_short(DevIndex ix, DevBatch b, brb_params p, Ctl* __restrict__ ctl,
+__global__ void __launch_bounds__(256, 6) k_front_short(DevIndex ix, DevBatch b, brb_params p, Ctl* __restrict__ ctl,
                                                         uint4* __restrict__ a_cand, uint32_t* __restrict__ ipool, Matches M) {
   __shared__ uint32_t s_nvalid[8][32];                      // per warp: matches kept per alignment of the current batch
   const unsigned lane = threadIdx.x & 31;

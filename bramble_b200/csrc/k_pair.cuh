@@ -50,7 +50,7 @@ __device__ __forceinline__ uint32_t seg_sum(uint32_t P, uint32_t lo, uint32_t hi
   return hi > lo ? top - (lo ? bot : 0) : 0;
 }
 
-__global__ void __launch_bounds__(256) k_pair_a(DevBatch b, Ctl* __restrict__ ctl, PairIn v, SlotOut so, uint32_t* __restrict__ tpool,
+__global__ void __launch_bounds__(256, 6) k_pair_a(DevBatch b, Ctl* __restrict__ ctl, PairIn v, SlotOut so, uint32_t* __restrict__ tpool,
                                                 unsigned long long* __restrict__ u_cnt /* rows | words << 32 */) {
   if (ctl_overflow(ctl)) return;
   const unsigned lane = threadIdx.x & 31;
@@ -136,7 +136,7 @@ struct Rows {
 };
 
 // u_off = exclusive scan of u_cnt (n_aln+1 entries; low half rows, high half CIGAR words).
-__global__ void __launch_bounds__(256) k_pair_b(DevBatch b, Ctl* __restrict__ ctl, PairIn v, SlotOut so, const uint32_t* __restrict__ tpool,
+__global__ void __launch_bounds__(256, 6) k_pair_b(DevBatch b, Ctl* __restrict__ ctl, PairIn v, SlotOut so, const uint32_t* __restrict__ tpool,
                                                 const unsigned long long* __restrict__ u_cnt, const unsigned long long* __restrict__ u_off,
                                                 Rows o) {
   if (ctl_overflow(ctl)) return;

@@ -112,10 +112,12 @@ typedef struct brb_batch_out {
 typedef struct brb_stats {
   uint64_t n_launches;                  /* kernels launched by the last brb_project* call */
   float    kernel_ms;                   /* CUDA-event time of those kernels on the ctx stream */
-  float    ms_lookup, ms_chain, ms_rescue, ms_finalize, ms_pair, ms_merge;   /* per phase */
+  float    ms_lookup, ms_chain, ms_rescue, ms_finalize, ms_pair, ms_merge;   /* per phase: front kernel (lookup + evaluation; on the
+                                         * clip-rescue path lookup | chain | rescue | build), k_pair_a, scan + k_pair_b */
   uint64_t n_candidates, n_matches, n_rescue, n_rec;
   uint64_t alg_bytes;                   /* algorithmic bytes of the batch (DESIGN.md formula) */
   uint64_t h2d_bytes, d2h_bytes;
+  uint64_t alg_bytes_front;             /* the part of alg_bytes that belongs to the front kernel (alignment columns + index hits) */
 } brb_stats;
 
 int brb_device_count(void);

@@ -4,6 +4,7 @@ usage: ncu_src.py report.ncu-rep kernel_regex [top_n]"""
 import csv, io, subprocess, sys
 rep, kern = sys.argv[1], sys.argv[2]
 top = int(sys.argv[3]) if len(sys.argv) > 3 else 25
+sort_key = sys.argv[4] if len(sys.argv) > 4 else "smp"      # smp | ins
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass", "--kernel-name", "regex:" + kern],
                      capture_output=True, text=True).stdout
 rows = []
@@ -22,6 +23,6 @@ keyS = "Warp Stall Sampling (All Samples)"
 tot = sum(num(d, keyS) for d in rows) or 1
 toti = sum(num(d, "Instructions Executed") for d in rows) or 1
 print(f"total samples {tot:.0f}, warp instructions {toti:.0f}")
-for d in sorted(rows, key=lambda d: -num(d, keyS))[:top]:
+for d in sorted(rows, key=lambda d: -num(d, keyS if sort_key == "smp" else "Instructions Executed"))[:top]:
     print(f"{100*num(d,keyS)/tot:5.1f}% smp {100*num(d,'Instructions Executed')/toti:5.1f}% ins thr/ins {num(d,'Avg. Threads Executed'):4.1f} "
           f"L2sect {num(d,'L2 Theoretical Sectors Global'):10.0f} | {d['file']}:{d['Line No']} {d['Source'].strip()[:110]}")
