@@ -53,12 +53,13 @@ struct DevBatch {
 // the pool and replays the sequence.
 struct Ctl {
   unsigned long long n_hits, out_words, rescue_bytes, n_matches, n_rescue, ksw_max_mat, ksw_max_tlen, n_mates;   // work counters
+  unsigned long long claimed;         // k_back: rows | CIGAR words << 32 handed out so far
   uint32_t n_cand, cap_cand;          // candidate slots allocated / capacity
   uint32_t n_ideal, cap_ideal;        // ideal-CIGAR pool words
   uint32_t n_rows, cap_rows;          // output rows
   uint32_t n_tmpw, cap_tmpw;          // merge scratch pool words
   uint32_t n_outw, cap_outw;          // dense output CIGAR words
-  uint32_t bad_input;                 // 1: mate link not symmetric, 2: read exons not ascending/disjoint
+  uint32_t bad_input;                 // 1: mate link not symmetric, 2: read exons not ascending/disjoint, 3: >= 2^28 CIGAR words in one batch of 32 alignments
   uint32_t ticket;                    // next batch of 32 alignments for k_front (dynamic scheduling)
   uint32_t ticket_a, ticket_b;        // same for k_pair_a / k_pair_b
 };

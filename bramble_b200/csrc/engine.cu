@@ -17,7 +17,7 @@
 #include "k_chain.cuh"
 #include "k_fused.cuh"
 #include "k_ksw.cuh"
-#include "k_pair.cuh"
+#include "k_back.cuh"
 #include "k_merge.cuh"
 
 using namespace brb;
@@ -92,8 +92,8 @@ struct brb_ctx {
   Buf q_any, a_cand, scan_tmp;
   Buf c_rec, c_task, c_first, c_last, c_nseg, c_nguide, c_cap, ipool;
   Buf r_left, r_right, rpool;
-  Buf m_tid, m_rec, m_sim, m_clip, c_srec, c_key;
-  Buf u_cnt, u_off, g_roff;
+  Buf m_rec, m_sim, m_clip, c_stage, t_agg, t_claim, t_off, p_row, p_pool, p_sim, p_clip;
+  Buf a_roff, g_roff;
   Buf o_src, o_tid, o_pos, o_strand, o_flags, o_sim, o_clip, o_coff, tpool, opool;
   HBuf h_small, h_out;
   RescueBufs* rb = nullptr;
@@ -102,7 +102,7 @@ struct brb_ctx {
   std::vector<Buf*> all() {
     return {&in_group_off, &in_refid, &in_strand, &in_exon_off, &in_exon_st, &in_exon_en, &in_cigar_off, &in_cigar, &in_mate, &in_seq_off,
             &in_seq, &ctl, &q_any, &a_cand, &scan_tmp, &c_rec, &c_task, &c_first, &c_last, &c_nseg, &c_nguide, &c_cap, &ipool,
-            &r_left, &r_right, &rpool, &m_tid, &m_rec, &m_sim, &m_clip, &c_srec, &c_key, &u_cnt, &u_off, &g_roff,
+            &r_left, &r_right, &rpool, &m_rec, &m_sim, &m_clip, &c_stage, &t_agg, &t_claim, &t_off, &p_row, &p_pool, &p_sim, &p_clip, &a_roff, &g_roff,
             &o_src, &o_tid, &o_pos, &o_strand, &o_flags, &o_sim, &o_clip, &o_coff, &tpool, &opool};
   }
 };
@@ -344,16 +344,18 @@ int ensure_pools(brb_ctx* c, bool rescue) {
   const DevBatch& b = c->b;
   const size_t n = b.n_aln, C = c->cap_cand, R = c->cap_rows;
   ENS(c->q_any, (size_t)2 * b.n_exon + 16); ENS(c->a_cand, n * 16);
-  ENS(c->u_cnt, n * 8); ENS(c->u_off, (n + 1) * 8); ENS(c->g_roff, (size_t)(b.n_groups + 1) * 4);
-  ENS(c->c_srec, C * 16); ENS(c->c_key, C * 8);
-  ENS(c->m_tid, C * 4); ENS(c->m_rec, C * 16);
-  if (c->have_scores) { ENS(c->m_sim, C * 8); ENS(c->m_clip, C * 4); ENS(c->o_sim, R * 8); ENS(c->o_clip, R * 4); }
+  ENS(c->a_roff, (n + 1) * 4); ENS(c->g_roff, (size_t)(b.n_groups + 1) * 4);
+  const size_t nbat = (n + 31) / 32;
+  ENS(c->c_stage, C * 16); ENS(c->t_agg, nbat * 8 + 8); ENS(c->t_claim, nbat * 8 + 8); ENS(c->t_off, (nbat + 1) * 8);
+  ENS(c->scan_tmp, scan_scratch_words(std::max<size_t>(nbat, 1)) * 8);
+  ENS(c->p_row, R * 16); ENS(c->p_pool, (size_t)c->cap_outw * 4);
+  ENS(c->m_rec, C * 16);
+  if (c->have_scores) { ENS(c->m_sim, C * 8); ENS(c->m_clip, C * 4); ENS(c->o_sim, R * 8); ENS(c->o_clip, R * 4); ENS(c->p_sim, R * 8); ENS(c->p_clip, R * 4); }
   if (rescue) { ENS(c->c_rec, C * 4); ENS(c->c_task, C * 4); ENS(c->c_first, C * 4); ENS(c->c_last, C * 4); ENS(c->c_nseg, C * 4); ENS(c->c_nguide, C * 4); ENS(c->c_cap, C * 4); }
   ENS(c->ipool, (size_t)c->cap_ideal * 4);
   ENS(c->o_src, R * 4); ENS(c->o_tid, R * 4); ENS(c->o_pos, R * 4); ENS(c->o_strand, R); ENS(c->o_flags, R);
   ENS(c->o_coff, (R + 1) * 4);
   ENS(c->tpool, (size_t)c->cap_tmpw * 4); ENS(c->opool, (size_t)c->cap_outw * 4);
-  ENS(c->scan_tmp, scan_scratch_words(std::max<size_t>(n, 1)) * 8);
   return 0;
 }
 
@@ -391,7 +393,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   const void* front_fn = short_front ? (p.filter_by_similarity ? (const void*)k_front_short<true> : (const void*)k_front_short<false>)
                                      : (rescue ? (const void*)k_front<false> : (const void*)k_front<true>);
   const int ncta_front = resident(front_fn);
-  const int ncta_pa = resident((const void*)k_pair_a), ncta_pb = resident((const void*)k_pair_b);
+  const int ncta_back = resident((const void*)k_back);
   Ctl* ctl = c->ctl.as<Ctl>();
   Ctl* hctl = c->h_small.as<Ctl>();
   uint64_t L = 0;
@@ -401,7 +403,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
     memset(hctl, 0, sizeof(Ctl));
     hctl->cap_cand = c->cap_cand; hctl->cap_ideal = c->cap_ideal; hctl->cap_rows = c->cap_rows; hctl->cap_tmpw = c->cap_tmpw; hctl->cap_outw = c->cap_outw;
     CU(cudaMemcpyAsync(ctl, hctl, sizeof(Ctl), cudaMemcpyHostToDevice, st));
-    Matches M; M.tid = c->m_tid.as<uint32_t>(); M.rec = c->m_rec.as<uint4>();
+    Matches M; M.rec = c->m_rec.as<uint4>();
     M.sim = c->have_scores ? c->m_sim.as<double>() : nullptr; M.clip = c->have_scores ? c->m_clip.as<int32_t>() : nullptr;
     // ---- phase 1: lookup + candidate lists
     CU(cudaEventRecord(c->ev[0], st));
@@ -434,20 +436,22 @@ int project_resident(brb_ctx* c, const brb_params& p) {
                                     c->r_right.as<RescueSeg>(), c->rpool.as<uint32_t>(), c->ipool.as<uint32_t>(), M); L++;
       CU(cudaEventRecord(c->ev[4], st));
     }
-    // ---- phase 5: pairing + emission
-    PairIn pv; pv.a_cand = c->a_cand.as<uint4>(); pv.m_tid = c->m_tid.as<uint32_t>(); pv.m_rec = c->m_rec.as<uint4>();
-    pv.m_sim = M.sim; pv.m_clip = M.clip; pv.ipool = c->ipool.as<uint32_t>();
-    SlotOut so; so.key = c->c_key.as<unsigned long long>(); so.rec = c->c_srec.as<uint4>();
-    if (rescue) { k_count_valid<<<grid_for(n, 256), 256, 0, st>>>(b, ctl, c->a_cand.as<uint4>(), c->m_tid.as<uint32_t>()); L++; }
-    k_pair_a<<<ncta_pa, 256, 0, st>>>(b, ctl, pv, so, c->tpool.as<uint32_t>(), c->u_cnt.as<unsigned long long>()); L++;
-    CU(cudaEventRecord(c->ev[5], st));
-    // ---- phase 6: row / CIGAR-word offsets in bundle order, then the rows themselves
-    exclusive_scan(c->u_cnt.as<unsigned long long>(), c->u_off.as<unsigned long long>(), n, c->scan_tmp.as<unsigned long long>(), st, &L);
-    k_group_rows<<<grid_for(b.n_groups + 1, 256), 256, 0, st>>>(b, c->u_off.as<unsigned long long>(), c->g_roff.as<uint32_t>()); L++;
+    // ---- phase 5: pairing, CIGAR merge, rows in bundle order (one kernel; batch offsets by decoupled look-back)
+    BackIn pv; pv.a_cand = c->a_cand.as<uint4>(); pv.m_rec = c->m_rec.as<uint4>(); pv.m_sim = M.sim; pv.m_clip = M.clip; pv.ipool = c->ipool.as<uint32_t>();
     Rows o; o.src = c->o_src.as<uint32_t>(); o.tid = c->o_tid.as<uint32_t>(); o.pos = c->o_pos.as<uint32_t>(); o.strand = c->o_strand.as<int8_t>();
     o.flags = c->o_flags.as<uint8_t>(); o.sim = c->o_sim.as<double>(); o.clip = c->o_clip.as<int32_t>(); o.coff = c->o_coff.as<uint32_t>();
-    o.pool = c->opool.as<uint32_t>();
-    k_pair_b<<<ncta_pb, 256, 0, st>>>(b, ctl, pv, so, c->tpool.as<uint32_t>(), c->u_cnt.as<unsigned long long>(), c->u_off.as<unsigned long long>(), o); L++;
+    o.pool = c->opool.as<uint32_t>(); o.a_roff = c->a_roff.as<uint32_t>();
+    if (rescue) { k_count_valid<<<grid_for(n, 256), 256, 0, st>>>(b, ctl, c->a_cand.as<uint4>(), c->m_rec.as<uint4>()); L++; }
+    const uint32_t nbat = (n + 31) / 32;
+    BatchTotals tl; tl.agg = c->t_agg.as<unsigned long long>(); tl.claim = c->t_claim.as<unsigned long long>();
+    ProvRows pr; pr.row = c->p_row.as<uint4>(); pr.pool = c->p_pool.as<uint32_t>();
+    pr.sim = c->have_scores ? c->p_sim.as<double>() : nullptr; pr.clip = c->have_scores ? c->p_clip.as<int32_t>() : nullptr;
+    k_back<<<ncta_back, 256, 0, st>>>(b, ctl, pv, c->c_stage.as<uint4>(), c->tpool.as<uint32_t>(), tl, pr, o); L++;
+    CU(cudaEventRecord(c->ev[5], st));
+    // ---- phase 6: batch totals -> offsets in bundle order; rows to their final place
+    exclusive_scan(tl.agg, c->t_off.as<unsigned long long>(), nbat, c->scan_tmp.as<unsigned long long>(), st, &L);
+    k_place<<<ncta, 256, 0, st>>>(b, ctl, tl, c->t_off.as<unsigned long long>(), pr, o); L++;
+    k_group_rows<<<grid_for(b.n_groups + 1, 256), 256, 0, st>>>(b, ctl, c->a_roff.as<uint32_t>(), c->g_roff.as<uint32_t>()); L++;
     CU(cudaEventRecord(c->ev[6], st));
     CU(cudaMemcpyAsync(hctl, ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
@@ -462,6 +466,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
     else if (hctl->n_outw > c->cap_outw) { c->cap_outw = grown(hctl->n_outw); again = true; }
     if (!again) break;
   }
+  if (hctl->bad_input == 3) return fail(BRB_E_UNSUPPORTED, "a batch of 32 alignments emits 2^28 or more CIGAR words");
   if (hctl->bad_input == 1) return fail(BRB_E_ARG, "mate_idx is not a symmetric single link (src/bramble.cpp:272-311)");
   if (hctl->bad_input) return fail(BRB_E_ARG, "read exons of an alignment must be ascending and disjoint");
   c->n_cand = hctl->n_cand; c->n_rec = hctl->n_rows; c->n_out_words = hctl->n_outw;

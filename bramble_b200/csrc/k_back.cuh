@@ -1,0 +1,322 @@
+// Kernel group 3: mate pairing, CIGAR projection and record emission -- the back half of a bundle, ONE kernel.
+// Replaces process_mate_pair / add_mate_info (reference src/mates.cpp:28-261), the group loop of convert_reads
+// (src/core.cpp:384-415) and update_cigar / merge_cigars (src/bam.cpp:113-315,443-528).
+// process_pairs (src/bramble.cpp:272-311) links every alignment to at most one mate and the link is symmetric,
+// so inside a name group the units {i unpaired} and {i < mate(i)} are independent: the lower index is
+// `this_read` (read1 of the BamInfo), the higher one the mate.  Rows of a unit come out ascending by tid (sorted
+// tid lists + set_intersection in the reference), the read row immediately followed by its mate row.
+//
+// Whether a match of the read is emitted can be decided per match, from the match counts of the two ends that
+// the front kernel left in a_cand.z (nr, nm):
+//   nm == 0                      -> every match, unpaired            (case 0, src/mates.cpp:150-176)
+//   the mate has the same tid    -> paired, same transcript          (case 1: a non-empty intersection keeps only
+//                                                                      the common tids)
+//   no common tid, nr == nm == 1 -> paired, different transcripts    (case 2)
+//
+// Work mapping (k_back): persistent warps take batches of 32 alignments by ticket (lane = alignment) and walk the
+// concatenated match slots of the batch's UNIT OWNERS 32 at a time (lane = slot), so a 200-isoform gene fills
+// the warp instead of idling 31 lanes, and slots of mates / non-owners cost nothing.
+//   phase 1   partner search on the mate's slot list; the common short-read row (real CIGAR = M/N only, ideal
+//             CIGAR = one M of the same length) is recognised from a per-alignment sum and needs no merge; every
+//             other emitted row is queued and merged afterwards with all lanes busy (merge_cigars into a scratch
+//             pool).  Per-match results stay in shared memory (global scratch for batches beyond BACK_STAGE).
+//   claim     one atomic reserves the batch's rows and CIGAR words in a dense buffer -- in COMPLETION order, so a
+//             batch full of hot-gene reads never stalls the batches after it (an in-order single-pass scan did:
+//             half of the issue slots went to the look-back spin).
+//   phase 2   rank of each emitted match inside its unit (ascending tid), one 16-byte row record, and the CIGAR
+//             words (reversed for '-' transcripts).
+// k_place (after a scan of the 32-alignment batch totals) then moves every batch to its place in bundle order
+// and unpacks the row records into the output columns: streaming, fully coalesced.
+#pragma once
+#include "dev_common.cuh"
+#include "k_merge.cuh"
+
+namespace brb {
+
+constexpr uint32_t SELF = 0xfffffffeu;     // partner: emitted without a mate row
+constexpr uint32_t INLINE = 0xffffffffu;   // Stage.w: every merged CIGAR of the row(s) is the one-word ideal CIGAR itself
+constexpr uint32_t PENDING = 0xfffffffeu;  // Stage.w: general merge queued
+constexpr uint32_t NOFIT = 0xfffffffdu;    // Stage.w: the scratch pool is exhausted (the host grows it and replays)
+constexpr uint32_t BACK_STAGE = 256;       // matches per batch staged in shared memory
+
+// match record written by the front kernels, one uint4 per candidate slot:
+//   .x pos   .y ideal-CIGAR length << 1 | transcript strand is '-'   .z its pool offset, or the word itself when the length is 1
+//   .w tid (NONE: the slot holds no match)
+struct BackIn {
+  const uint4* a_cand;          // per alignment: first slot, #slots to walk, #matches among them
+  const uint4* m_rec;
+  const double* m_sim; const int32_t* m_clip;      // null when every score is 0
+  const uint32_t* ipool;        // ideal CIGARs longer than one word
+};
+struct Rows {
+  uint32_t* src; uint32_t* tid; uint32_t* pos; int8_t* strand; uint8_t* flags; double* sim; int32_t* clip;
+  uint32_t* coff;               // n_rows+1: dense CIGAR pool offsets (CSR)
+  uint32_t* pool;               // dense, row-ordered merged CIGARs
+  uint32_t* a_roff;             // n_aln+1: first row of each alignment's unit (bundle order)
+};
+
+// Rows as k_back leaves them: dense, but batches in completion order.  One 16-byte record per row:
+//   .x source alignment  .y tid  .z pos  .w first CIGAR word relative to the batch (28 bits) | '-' strand << 28 | BRB_REC_* flags << 29
+struct ProvRows { uint4* row; uint32_t* pool; double* sim; int32_t* clip; };
+// Per batch of 32 alignments: rows | CIGAR words << 32, and where k_back put them.
+struct BatchTotals { unsigned long long* agg; unsigned long long* claim; };
+
+// Sum of the M/=/X lengths when the real CIGAR holds nothing but M/=/X and N, else 0.  With an ideal CIGAR of one
+// M word of that length merge_cigars skips every N, turns every chunk into M (merge_ops) and both sides end
+// together: the merged CIGAR is the ideal word itself.
+__device__ __forceinline__ uint32_t real_msum(const uint32_t* __restrict__ real, uint32_t n) {
+  uint32_t sum = 0;
+  for (uint32_t i = 0; i < n; i++) {
+    const uint32_t rw = __ldg(&real[i]), op = rw & 0xfu;
+    if (op == CM || op == CEQ || op == CX) sum += rw >> 4; else if (op != CN) return 0;
+  }
+  return sum;
+}
+__device__ __forceinline__ bool merge_trivial(uint32_t iword, uint32_t msum) { return (iword & 0xfu) == CM && msum && msum == (iword >> 4); }
+
+__device__ __forceinline__ bool front_overflow(const Ctl* c) { return c->n_cand > c->cap_cand || c->n_ideal > c->cap_ideal || c->bad_input != 0; }
+
+__global__ void __launch_bounds__(256, 5) k_back(DevBatch b, Ctl* __restrict__ ctl, BackIn v, uint4* __restrict__ gstage, uint32_t* __restrict__ tpool,
+                                                 BatchTotals tl, ProvRows pv_, Rows o) {
+  __shared__ uint4 s_stage[8][BACK_STAGE];                 // per match of the batch: tid (NONE: not emitted), CIGAR words, partner, scratch offset
+  __shared__ uint16_t s_queue[8][BACK_STAGE];              // matches that need the general merge
+  __shared__ uint32_t s_own[8][7][32];                     // per alignment of the batch: off, excl, ro, nrc, mro, mnrc, words of merged rows
+  if (front_overflow(ctl)) return;                         // uniform for the whole grid: nothing was published, nobody waits
+  const unsigned lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  uint32_t* s_off = s_own[wid][0]; uint32_t* s_excl = s_own[wid][1]; uint32_t* s_ro = s_own[wid][2]; uint32_t* s_nrc = s_own[wid][3];
+  uint32_t* s_mro = s_own[wid][4]; uint32_t* s_mnrc = s_own[wid][5]; uint32_t* s_words = s_own[wid][6];
+  uint16_t* queue = s_queue[wid];
+  const uint32_t n_batches = (b.n_aln + 31) >> 5;
+  const uint32_t cap_tmpw = ctl->cap_tmpw, cap_rows = ctl->cap_rows, cap_outw = ctl->cap_outw;
+  WarpPool wp; wp.cur = 0; wp.end = 0;
+  for (;;) {
+    uint32_t wb = 0;
+    if (lane == 0) wb = atomicAdd(&ctl->ticket_a, 1u);
+    wb = __shfl_sync(0xffffffffu, wb, 0);
+    if (wb >= n_batches) break;
+    const uint32_t a = wb * 32 + lane;
+    uint32_t off = 0, n = 0, m_off = 0, m_n = 0, ro = 0, nrc = 0, mro = 0, mnrc = 0, rsum = 0, mrsum = 0, pflag = 0;
+    int32_t mate = -1;
+    if (a < b.n_aln) {
+      const uint4 ac = __ldg(&v.a_cand[a]);
+      mate = __ldg(&b.mate_idx[a]);
+      if ((mate < 0 || (uint32_t)mate > a) && ac.z) {         // unit owner with at least one match
+        off = ac.x; n = ac.y;
+        ro = __ldg(&b.cigar_off[a]); nrc = __ldg(&b.cigar_off[a + 1]) - ro;
+        rsum = real_msum(b.cigar + ro, nrc);
+        uint32_t nm = 0;
+        if (mate >= 0) {
+          const uint4 mc = __ldg(&v.a_cand[mate]);
+          m_off = mc.x; m_n = mc.y; nm = mc.z;
+          mro = __ldg(&b.cigar_off[mate]); mnrc = __ldg(&b.cigar_off[mate + 1]) - mro;
+          if (nm) mrsum = real_msum(b.cigar + mro, mnrc);
+        }
+        pflag = (nm == 0 ? 1u : 0u) | ((ac.z == 1 && nm == 1) ? 2u : 0u);
+      }
+    }
+    const uint32_t incl = warp_incl_scan(n, lane), excl = incl - n, total = __shfl_sync(0xffffffffu, incl, 31);
+    const bool staged = total <= BACK_STAGE;
+    uint4* stage = staged ? s_stage[wid] : gstage;          // staged: indexed by item; otherwise by slot
+    s_off[lane] = off; s_excl[lane] = excl; s_ro[lane] = ro; s_nrc[lane] = nrc; s_mro[lane] = mro; s_mnrc[lane] = mnrc; s_words[lane] = 0;
+    __syncwarp();
+    uint32_t rows = 0, words = 0, qn = 0;
+    // general merge of one emitted row (pair): all lanes call, `go` lanes work
+    auto merge_rows = [&](bool go, uint32_t L, uint32_t sidx, uint32_t tid, uint32_t part, const uint4& mr, const uint4& pr) {
+      const bool paired = part != SELF;
+      const uint32_t l_nrc = go ? s_nrc[L] : 0, l_mnrc = go ? s_mnrc[L] : 0;
+      const uint32_t cap_r = l_nrc + (mr.y >> 1) + 2, want = go ? 1 + cap_r + (paired ? l_mnrc + (pr.y >> 1) + 2 : 0) : 0;
+      bool fit;
+      const uint32_t toff = warp_pool_alloc(wp, &ctl->n_tmpw, cap_tmpw, want, lane, fit);
+      if (!go) return;
+      uint32_t clr = 0, clm = 0;
+      if (fit) {
+        clr = merge_cigars(b.cigar + s_ro[L], l_nrc, v.ipool + mr.z, mr.y >> 1, mr.z, tpool + toff + 1);
+        if (paired) clm = merge_cigars(b.cigar + s_mro[L], l_mnrc, v.ipool + pr.z, pr.y >> 1, pr.z, tpool + toff + 1 + cap_r);
+        tpool[toff] = clr;
+      }
+      stage[sidx] = make_uint4(tid, clr + clm, part, fit ? toff : NOFIT);
+      atomicAdd(&s_words[L], clr + clm);
+    };
+    // ---- phase 1
+    for (uint32_t base = 0; base < total; base += 32) {
+      const uint32_t item = base + lane;
+      const bool actv = item < total;
+      const unsigned L = warp_owner(incl, actv ? item : total - 1);
+      const uint32_t c = __shfl_sync(0xffffffffu, off, L) + (item - __shfl_sync(0xffffffffu, excl, L));
+      const uint32_t o_pf = __shfl_sync(0xffffffffu, pflag, L);
+      const uint32_t o_moff = __shfl_sync(0xffffffffu, m_off, L), o_mn = __shfl_sync(0xffffffffu, m_n, L);
+      const uint32_t o_rsum = __shfl_sync(0xffffffffu, rsum, L), o_mrsum = __shfl_sync(0xffffffffu, mrsum, L);
+      uint4 mr = make_uint4(0, 0, 0, NONE);
+      if (actv) mr = __ldg(&v.m_rec[c]);
+      const uint32_t tid = mr.w;
+      uint32_t part = NONE;
+      if (tid != NONE) {
+        if (o_pf & 1u) part = SELF;
+        else {
+          uint32_t only = NONE;
+#pragma unroll 4
+          for (uint32_t d = o_moff, e = o_moff + o_mn; d < e; d++) { const uint32_t t = __ldg(&v.m_rec[d].w); if (t == tid) part = d; if (t != NONE) only = d; }
+          if (part == NONE && (o_pf & 2u)) part = only;           // different transcripts
+        }
+      }
+      const bool emitted = part != NONE, paired = emitted && part != SELF;
+      uint4 pr = make_uint4(0, 0, 0, NONE);
+      if (paired) pr = __ldg(&v.m_rec[part]);
+      const bool inl = emitted && (mr.y >> 1) == 1 && merge_trivial(mr.z, o_rsum) && (!paired || ((pr.y >> 1) == 1 && merge_trivial(pr.z, o_mrsum)));
+      const bool slow = emitted && !inl;
+      const uint32_t B_e = __ballot_sync(0xffffffffu, emitted), B_p = __ballot_sync(0xffffffffu, paired), B_s = __ballot_sync(0xffffffffu, slow);
+      if (n && incl > base && excl < base + 32) {           // rows / one-word CIGARs of MY alignment in this chunk
+        const uint32_t mine = bit_range(excl > base ? excl - base : 0, incl - base < 32 ? incl - base : 32);
+        rows += __popc(B_e & mine) + __popc(B_p & mine);
+        words += __popc(B_e & ~B_s & mine) + __popc(B_p & ~B_s & mine);
+      }
+      const uint32_t sidx = staged ? item : c;
+      if (actv) stage[sidx] = make_uint4(emitted ? tid : NONE, slow ? L : (paired ? 2u : 1u), part, slow ? PENDING : INLINE);
+      if (B_s) {
+        if (staged) { if (slow) queue[qn + __popc(B_s & lt_mask)] = (uint16_t)item; }
+        qn += __popc(B_s);
+      }
+    }
+    __syncwarp();
+    // ---- phase 1b: the general merges, 32 at a time (staged: from the queue; otherwise a second walk over the items)
+    for (uint32_t qi = 0, qe = qn ? (staged ? qn : total) : 0; qi < qe; qi += 32) {
+      bool go = qi + lane < qe;
+      uint32_t sidx = 0, L = 0, c = 0;
+      if (staged) { if (go) { sidx = queue[qi + lane]; L = stage[sidx].y; c = s_off[L] + (sidx - s_excl[L]); } }
+      else {
+        L = warp_owner(incl, go ? qi + lane : total - 1);
+        c = s_off[L] + (qi + lane - s_excl[L]); sidx = c;
+        go = go && stage[sidx].w == PENDING;
+      }
+      uint32_t tid = NONE, part = SELF; uint4 mr = make_uint4(0, 0, 0, NONE), pr = mr;
+      if (go) {
+        const uint4 sg = stage[sidx];
+        tid = sg.x; part = sg.z;
+        mr = __ldg(&v.m_rec[c]);
+        if (part != SELF) pr = __ldg(&v.m_rec[part]);
+      }
+      merge_rows(go, L, sidx, tid, part, mr, pr);
+    }
+    __syncwarp();
+    words += s_words[lane];
+    // ---- row / word room of the batch: claimed in completion order (no batch ever waits for another one);
+    //      k_place moves the rows to their place in bundle order once every batch total is known
+    const uint32_t irows = warp_incl_scan(rows, lane), iwords = warp_incl_scan(words, lane);
+    const uint32_t R_b = __shfl_sync(0xffffffffu, irows, 31), W_b = __shfl_sync(0xffffffffu, iwords, 31);
+    const unsigned long long agg = (unsigned long long)R_b | ((unsigned long long)W_b << 32);
+    unsigned long long claim = 0;
+    if (lane == 0) { claim = atomicAdd(&ctl->claimed, agg); tl.agg[wb] = agg; tl.claim[wb] = claim; }
+    claim = __shfl_sync(0xffffffffu, claim, 0);
+    const uint32_t prow0 = (uint32_t)claim, pword0 = (uint32_t)(claim >> 32);
+    const uint32_t row0 = prow0 + irows - rows, word0 = pword0 + iwords - words;
+    if (a < b.n_aln) o.a_roff[a] = irows - rows;             // batch-relative; k_place adds the first row of the batch
+    if (W_b >= (1u << 28)) { if (lane == 0) atomicMax(&ctl->bad_input, 3u); __syncwarp(); continue; }
+    if ((unsigned long long)prow0 + R_b > cap_rows || (unsigned long long)pword0 + W_b > cap_outw) { __syncwarp(); continue; }   // the host grows the row pools and replays
+    // ---- phase 2: rank inside the unit, rows, CIGAR words
+    for (uint32_t base = 0; base < total; base += 32) {
+      const uint32_t item = base + lane;
+      const bool actv = item < total;
+      const unsigned L = warp_owner(incl, actv ? item : total - 1);
+      const uint32_t o_off = __shfl_sync(0xffffffffu, off, L), o_n = __shfl_sync(0xffffffffu, n, L), o_ex = __shfl_sync(0xffffffffu, excl, L);
+      const uint32_t o_row0 = __shfl_sync(0xffffffffu, row0, L), o_word0 = __shfl_sync(0xffffffffu, word0, L);
+      const int32_t o_mate = __shfl_sync(0xffffffffu, mate, L);
+      if (!actv) continue;
+      const uint32_t c = o_off + (item - o_ex);
+      const uint32_t s0 = staged ? o_ex : o_off, sidx = staged ? item : c;
+      const uint4 sg = stage[sidx];
+      const uint32_t tid = sg.x;
+      if (tid == NONE || sg.w == NOFIT) continue;
+      // rank among the emitted matches of the read: ascending tid, slot order among equals; CIGAR words before me
+      uint32_t rank = 0, wpre = 0;
+#pragma unroll 4
+      for (uint32_t k = 0; k < o_n; k++) {
+        const uint2 e = *reinterpret_cast<const uint2*>(&stage[s0 + k]);
+        if (e.x != NONE && (e.x < tid || (e.x == tid && s0 + k < sidx))) { rank++; wpre += e.y; }
+      }
+      const uint32_t part = sg.z;
+      const bool paired = part != SELF, inl = sg.w == INLINE;
+      const uint4 mr = __ldg(&v.m_rec[c]);
+      const uint32_t row = o_row0 + (paired ? 2 * rank : rank), w0 = o_word0 + wpre;
+      const uint32_t clr = inl ? 1u : tpool[sg.w];
+      uint4 m = mr; uint32_t cc = c, aln = wb * 32 + L, fl = BRB_REC_FIRST, wpos = w0, len = clr;
+      const uint32_t* src = tpool + sg.w + 1;
+      if (paired) fl |= BRB_REC_PAIRED | (__ldg(&v.m_rec[part].w) == tid ? BRB_REC_SAMETX : 0);
+      for (uint32_t e = 0, ne = paired ? 2 : 1; e < ne; e++) {
+        if (e) {                                            // the mate row follows the read row
+          m = __ldg(&v.m_rec[part]); cc = part; aln = (uint32_t)o_mate; fl &= ~BRB_REC_FIRST; wpos = w0 + clr;
+          src = tpool + sg.w + 1 + (s_nrc[L] + (mr.y >> 1) + 2); len = inl ? 1u : sg.y - clr;
+        }
+        const uint32_t minus = m.y & 1u;
+        pv_.row[row + e] = make_uint4(aln, m.w, m.x, (wpos - pword0) | (minus << 28) | (fl << 29));
+        if (v.m_sim) { pv_.sim[row + e] = v.m_sim[cc]; pv_.clip[row + e] = v.m_clip[cc]; }
+        if (inl) pv_.pool[wpos] = m.z;
+        else if (minus) for (uint32_t i = 0; i < len; i++) pv_.pool[wpos + i] = src[len - 1 - i];      // reverse_complement_bam, src/bam.cpp:636-702
+        else for (uint32_t i = 0; i < len; i++) pv_.pool[wpos + i] = src[i];
+      }
+    }
+    __syncwarp();                                           // the staging area is reused by the next batch
+  }
+}
+
+// Clip-rescue path only: the front kernel cannot know which candidates survive k_ksw / k_build, so the match
+// count of each alignment (a_cand.z) is filled in afterwards.
+__global__ void __launch_bounds__(256) k_count_valid(DevBatch b, const Ctl* __restrict__ ctl, uint4* __restrict__ a_cand, const uint4* __restrict__ m_rec) {
+  if (front_overflow(ctl)) return;
+  const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= b.n_aln) return;
+  uint4 ac = a_cand[a]; uint32_t nv = 0;
+  for (uint32_t c = ac.x, e = ac.x + ac.y; c < e; c++) nv += m_rec[c].w != NONE;
+  ac.z = nv; a_cand[a] = ac;
+}
+
+// Rows of batch wb: from where k_back claimed room (tl.claim) to their place in bundle order (t_off = exclusive
+// scan of tl.agg; t_off[n_batches] = totals).  One warp per batch.
+__global__ void __launch_bounds__(256) k_place(DevBatch b, Ctl* __restrict__ ctl, BatchTotals tl, const unsigned long long* __restrict__ t_off,
+                                               ProvRows pv, Rows o) {
+  if (front_overflow(ctl)) return;
+  const uint32_t n_batches = (b.n_aln + 31) >> 5;
+  const unsigned long long tot = t_off[n_batches];
+  const uint32_t R = (uint32_t)tot, W = (uint32_t)(tot >> 32);
+  if (blockIdx.x == 0 && threadIdx.x == 0) { ctl->n_rows = R; ctl->n_outw = W; ctl->out_words = W; }
+  if (R > ctl->cap_rows || W > ctl->cap_outw) return;       // k_back skipped what did not fit; the host grows the pools and replays
+  if (blockIdx.x == 0 && threadIdx.x == 0) { o.coff[R] = W; o.a_roff[b.n_aln] = R; }
+  const unsigned lane = threadIdx.x & 31;
+  const uint32_t wstride = gridDim.x * (blockDim.x >> 5);
+  for (uint32_t wb = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); wb < n_batches; wb += wstride) {
+    const unsigned long long agg = tl.agg[wb], src = tl.claim[wb], dst = t_off[wb];
+    const uint32_t R_b = (uint32_t)agg, W_b = (uint32_t)(agg >> 32);
+    const uint32_t srow = (uint32_t)src, sword = (uint32_t)(src >> 32), drow = (uint32_t)dst, dword = (uint32_t)(dst >> 32);
+    const uint32_t a = wb * 32 + lane;
+    if (a < b.n_aln) o.a_roff[a] += drow;
+    for (uint32_t r0 = 0; r0 < R_b; r0 += 128) {            // four rows per lane in flight
+      uint4 x[4];
+#pragma unroll
+      for (int k = 0; k < 4; k++) { const uint32_t r = r0 + k * 32 + lane; if (r < R_b) x[k] = __ldcs(&pv.row[srow + r]); }
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        const uint32_t r = r0 + k * 32 + lane;
+        if (r < R_b) {
+          o.src[drow + r] = x[k].x; o.tid[drow + r] = x[k].y; o.pos[drow + r] = x[k].z; o.coff[drow + r] = dword + (x[k].w & 0x0fffffffu);
+          o.strand[drow + r] = (x[k].w >> 28) & 1u ? '-' : '+'; o.flags[drow + r] = (uint8_t)(x[k].w >> 29);
+          if (pv.sim) { o.sim[drow + r] = pv.sim[srow + r]; o.clip[drow + r] = pv.clip[srow + r]; }
+        }
+      }
+    }
+    for (uint32_t w0 = 0; w0 < W_b; w0 += 128) {
+      uint32_t y[4];
+#pragma unroll
+      for (int k = 0; k < 4; k++) { const uint32_t w = w0 + k * 32 + lane; if (w < W_b) y[k] = __ldcs(&pv.pool[sword + w]); }
+#pragma unroll
+      for (int k = 0; k < 4; k++) { const uint32_t w = w0 + k * 32 + lane; if (w < W_b) o.pool[dword + w] = y[k]; }
+    }
+  }
+}
+
+__global__ void k_group_rows(DevBatch b, const Ctl* __restrict__ ctl, const uint32_t* __restrict__ a_roff, uint32_t* __restrict__ g_roff) {
+  if (front_overflow(ctl)) return;
+  const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g <= b.n_groups) g_roff[g] = a_roff[g < b.n_groups ? b.group_off[g] : b.n_aln];
+}
+
+}  // namespace brb

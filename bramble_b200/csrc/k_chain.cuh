@@ -234,9 +234,9 @@ __device__ __forceinline__ bool dedupe_first(const DevIndex& ix, const brb_param
   return true;
 }
 
-struct Matches {          // per candidate slot; tid == NONE marks "no match"
-  uint32_t* tid;
-  uint4* rec;             // .x pos  .y ideal-CIGAR length  .z its offset in the ideal pool, or the CIGAR word itself when the length is 1  .w task (2a+s)
+struct Matches {          // per candidate slot
+  uint4* rec;             // .x pos  .y ideal-CIGAR length << 1 | strand  .z its offset in the ideal pool, or the CIGAR word itself when the
+                          // length is 1  .w tid (NONE marks "no match")
   double* sim; int32_t* clip;     // null when every score is 0 by construction
 };
 
@@ -257,11 +257,10 @@ __device__ __forceinline__ bool build_one(const DevIndex& ix, const DevBatch& b,
     if (sim > thr) { const double x = (sim - thr) / (1.0 - thr); sim_score = x * x * (double)(m.junc + 1); }
     else keep = false;
   }
-  M.tid[c] = keep ? rec_key(ix.rec, w.first_rec).tid : NONE;
   if (keep) {
-    M.rec[c] = make_uint4(s ? lp : fp, m.n, m.n == 1 ? m.last : ioff, task);
+    M.rec[c] = make_uint4(s ? lp : fp, (m.n << 1) | (uint32_t)s, m.n == 1 ? m.last : ioff, rec_key(ix.rec, w.first_rec).tid);
     if (M.sim) { M.sim[c] = sim_score; M.clip[c] = m.clip; }
-  }
+  } else M.rec[c] = make_uint4(0, 0, 0, NONE);
   return keep;
 }
 
@@ -305,7 +304,7 @@ __global__ void __launch_bounds__(256) k_build(DevIndex ix, DevBatch b, brb_para
     bool fits;
     const uint32_t ioff = warp_pool_alloc(wp, &ctl->n_ideal, cap_ideal, cap, lane, fits);
     if (!act) continue;
-    if (cap == 0 || !fits) { M.tid[c] = NONE; continue; }
+    if (cap == 0 || !fits) { M.rec[c] = make_uint4(0, 0, 0, NONE); continue; }
     const uint32_t task = c_task[c], a = task >> 1; const int s = task & 1;
     WalkOut w; w.first_rec = F.first[c]; w.last_rec = F.last[c]; w.n_seg = F.nseg[c]; w.n_guide = F.nguide[c]; w.cap = cap;
     RescueSeg L, R; L.ok = 0; R.ok = 0;

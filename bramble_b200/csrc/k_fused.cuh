@@ -20,8 +20,8 @@
 
 namespace brb {
 
-// a_cand[a] = { first candidate slot, #slots of task 2a ('+'), #slots of task 2a+1 ('-'), #slots that hold a match }
-// (on the clip-rescue path the last field is filled in later by k_count_valid)
+// a_cand[a] = { first candidate slot, #slots ('+' task first, then '-'), #slots that hold a match, - }
+// (on the clip-rescue path the match count is filled in later by k_count_valid)
 template <bool FUSED>
 __global__ void __launch_bounds__(256) k_front(DevIndex ix, DevBatch b, brb_params p, Ctl* __restrict__ ctl,
                                                uint8_t* q_any, uint4* __restrict__ a_cand,
@@ -139,14 +139,14 @@ __global__ void __launch_bounds__(256) k_front(DevIndex ix, DevBatch b, brb_para
           bool keep = false;
           if (sv && slots_fit) {
             if (ok && pool_fit) keep = build_one(ix, b, p, slot, task, rx, s, q_any, w, nullptr, nullptr, nullptr, ipool, ioff, M);
-            else M.tid[slot] = NONE;
+            else M.rec[slot] = make_uint4(0, 0, 0, NONE);
           }
           kept += keep ? 1u : 0u;
           nvalid += __popc(__ballot_sync(0xffffffffu, keep) & mine);
         }
       }
     }
-    if (valid) a_cand[a] = make_uint4(off0, ncand[0], ncand[1], nvalid);
+    if (valid) a_cand[a] = make_uint4(off0, ncand[0] + ncand[1], nvalid, 0);
   }
   // work counters (algorithmic-bytes numerator) + input validation: one atomic per warp
   for (int d = 16; d; d >>= 1) { my_hits += __shfl_down_sync(0xffffffffu, my_hits, d); kept += __shfl_down_sync(0xffffffffu, kept, d);
@@ -172,11 +172,9 @@ __global__ void __launch_bounds__(256) k_front(DevIndex ix, DevBatch b, brb_para
 // marked empty.  (n_hits then only counts exon-0 hits; the reference-defined figure for the roofline numerator
 // comes from the generic kernel, see BRB_OPT_GENERIC_FRONT.)
 template <bool SIM>
-__global__ void __launch_bounds__(256, 6) k_front_short(DevIndex ix, DevBatch b, brb_params p, Ctl* __restrict__ ctl,
+__global__ void __launch_bounds__(256, 5) k_front_short(DevIndex ix, DevBatch b, brb_params p, Ctl* __restrict__ ctl,
                                                         uint4* __restrict__ a_cand, uint32_t* __restrict__ ipool, Matches M) {
-  __shared__ uint32_t s_nvalid[8][32];                      // per warp: matches kept per alignment of the current batch
   const unsigned lane = threadIdx.x & 31;
-  uint32_t* nval = s_nvalid[threadIdx.x >> 5];
   const uint32_t n_batches = (b.n_aln + 31) >> 5;
   const uint32_t cap_cand = ctl->cap_cand, cap_ideal = ctl->cap_ideal;       // constant during the launch
   WarpPool wp; wp.cur = 0; wp.end = 0;
@@ -217,8 +215,7 @@ __global__ void __launch_bounds__(256, 6) k_front_short(DevIndex ix, DevBatch b,
     sbase = __shfl_sync(0xffffffffu, sbase, 31);
     const bool slots_fit = (unsigned long long)sbase + total <= cap_cand;
     const int status0 = exon_status(rx.n_ex, 0);
-    nval[lane] = 0;                                         // matches kept for MY alignment (pairing reads it from a_cand.w)
-    __syncwarp();
+    uint32_t nvalid = 0, wr = 0;                            // matches kept for MY alignment / by the batch so far
     for (uint32_t base = 0; base < total; base += 32) {
       const uint32_t item = base + lane;
       const bool actv = item < total;
@@ -232,7 +229,6 @@ __global__ void __launch_bounds__(256, 6) k_front_short(DevIndex ix, DevBatch b,
       const uint32_t idx = item - o_ex;
       const int s = idx >= o_n0;
       uint32_t rec0 = s ? o_lo1 + (idx - o_n0) : o_lo0 + idx;
-      const uint32_t slot = sbase + item;
       bool sv = false, ov = false; RecKey key;
       if (actv) {
         key = rec_key(ix.rec, rec0);
@@ -243,9 +239,8 @@ __global__ void __launch_bounds__(256, 6) k_front_short(DevIndex ix, DevBatch b,
       const uint32_t want = sv ? 3 * ox.n_ex : 0;           // at most S/I/D + M + S/I/D per read exon
       bool pool_fit;
       const uint32_t ioff = warp_pool_alloc(wp, &ctl->n_ideal, cap_ideal, want, lane, pool_fit);
-      if (!actv || !slots_fit) continue;
       bool ok = false; uint32_t pos = 0, ilen = 0, word = 0; double sim = 0.0;
-      if (sv && pool_fit) {
+      if (sv && pool_fit && slots_fit) {
         RecLink lk = rec_link(ix.rec, rec0);
         ok = true;
         if (lk.gprev_en > (int32_t)ox.qs0 || lk.gnext_st < (int32_t)ox.qe0) {      // a neighbour exon of this tid also overlaps read exon 0
@@ -255,15 +250,19 @@ __global__ void __launch_bounds__(256, 6) k_front_short(DevIndex ix, DevBatch b,
         }
         if (ok) ok = eval_short<SIM>(ix, b, p, ox, s, key, lk, ipool + ioff, pos, ilen, word, sim);
       }
+      // matches are written densely, in (alignment, record) order: slots of an alignment stay contiguous
+      const uint32_t B_ok = __ballot_sync(0xffffffffu, ok);
       if (ok) {
-        M.tid[slot] = key.tid; M.rec[slot] = make_uint4(pos, ilen, ilen == 1 ? word : ioff, 2 * (wb * 32 + L) + s);
+        const uint32_t slot = sbase + wr + __popc(B_ok & ((1u << lane) - 1u));
+        M.rec[slot] = make_uint4(pos, (ilen << 1) | (uint32_t)s, ilen == 1 ? word : ioff, key.tid);
         if (SIM) { M.sim[slot] = sim; M.clip[slot] = 0; }
-        kept++; atomicAdd(&nval[L], 1u);
-      } else M.tid[slot] = NONE;
+      }
+      wr += __popc(B_ok);
+      if (n && incl > base && excl < base + 32) nvalid += __popc(B_ok & bit_range(excl > base ? excl - base : 0, incl - base < 32 ? incl - base : 32));
     }
-    __syncwarp();
-    if (a < b.n_aln) a_cand[a] = make_uint4(sbase + excl, n0, n1, nval[lane]);
-    __syncwarp();
+    kept += nvalid;
+    const uint32_t first = sbase + warp_incl_scan(nvalid, lane) - nvalid;
+    if (a < b.n_aln) a_cand[a] = make_uint4(first, nvalid, nvalid, 0);
   }
   for (int d = 16; d; d >>= 1) { my_hits += __shfl_down_sync(0xffffffffu, my_hits, d); kept += __shfl_down_sync(0xffffffffu, kept, d);
                                  n_mates += __shfl_down_sync(0xffffffffu, n_mates, d); }

@@ -59,7 +59,7 @@ __device__ __forceinline__ bool merge_is_trivial(const uint32_t* __restrict__ re
 
 // Returns the number of words written to `out` (capacity >= n_real + n_ideal + 2).
 // A one-word ideal CIGAR is passed by value in `iword` (match records keep it inline; `ideal` is then unused).
-__device__ uint32_t merge_cigars(const uint32_t* __restrict__ real, uint32_t n_real, const uint32_t* __restrict__ ideal_,
+__device__ __noinline__ uint32_t merge_cigars(const uint32_t* __restrict__ real, uint32_t n_real, const uint32_t* __restrict__ ideal_,
                                  uint32_t n_ideal, uint32_t iword, uint32_t* __restrict__ out) {
   auto ideal = [&](uint32_t k) -> uint32_t { return n_ideal == 1 ? iword : ideal_[k]; };
   CigOut res; res.p = out; res.n = 0; res.last = 0; res.saw_i = false;
