@@ -11,7 +11,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libbramble_b200.so")
+LIB_PATH = os.environ.get("BRB_LIB") or os.path.join(_HERE, "libbramble_b200.so")     # BRB_LIB: tuning builds (tools/variants.py)
 
 BRB_OK, BRB_E_NO_DEVICE, BRB_E_CUDA, BRB_E_ARG, BRB_E_NOMEM, BRB_E_UNSUPPORTED = 0, -1, -2, -3, -4, -5
 REC_FIRST, REC_PAIRED, REC_SAMETX = 1, 2, 4

@@ -31,9 +31,26 @@
 #include "dev_common.cuh"
 #include "k_merge.cuh"
 
+#ifndef VAR_PARTNER
+#define VAR_PARTNER 0
+#endif
+#ifndef VAR_UNROLL
+#define VAR_UNROLL 4
+#endif
+#ifndef VAR_MSUM
+#define VAR_MSUM 1
+#endif
+#ifndef VAR_ROWTRIV
+#define VAR_ROWTRIV 1
+#endif
+#ifndef VAR_BACK_CTAS
+#define VAR_BACK_CTAS 4
+#endif
+
 namespace brb {
 
 constexpr uint32_t SELF = 0xfffffffeu;     // partner: emitted without a mate row
+constexpr int kUnroll = VAR_UNROLL;
 constexpr uint32_t INLINE = 0xffffffffu;   // Stage.w: every merged CIGAR of the row(s) is the one-word ideal CIGAR itself
 constexpr uint32_t PENDING = 0xfffffffeu;  // Stage.w: general merge queued
 constexpr uint32_t NOFIT = 0xfffffffdu;    // Stage.w: the scratch pool is exhausted (the host grows it and replays)
@@ -76,16 +93,17 @@ __device__ __forceinline__ bool merge_trivial(uint32_t iword, uint32_t msum) { r
 
 __device__ __forceinline__ bool front_overflow(const Ctl* c) { return c->n_cand > c->cap_cand || c->n_ideal > c->cap_ideal || c->bad_input != 0; }
 
-__global__ void __launch_bounds__(256, 5) k_back(DevBatch b, Ctl* __restrict__ ctl, BackIn v, uint4* __restrict__ gstage, uint32_t* __restrict__ tpool,
+__global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __restrict__ ctl, BackIn v, uint4* __restrict__ gstage, uint32_t* __restrict__ tpool,
                                                  BatchTotals tl, ProvRows pv_, Rows o) {
   __shared__ uint4 s_stage[8][BACK_STAGE];                 // per match of the batch: tid (NONE: not emitted), CIGAR words, partner, scratch offset
   __shared__ uint16_t s_queue[8][BACK_STAGE];              // matches that need the general merge
-  __shared__ uint32_t s_own[8][7][32];                     // per alignment of the batch: off, excl, ro, nrc, mro, mnrc, words of merged rows
+  __shared__ uint32_t s_own[8][9][32];                     // per alignment of the batch: off, excl, ro, nrc, mro, mnrc, words of merged rows, rsum, mrsum
   if (front_overflow(ctl)) return;                         // uniform for the whole grid: nothing was published, nobody waits
   const unsigned lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const uint32_t lt_mask = (1u << lane) - 1u;
   uint32_t* s_off = s_own[wid][0]; uint32_t* s_excl = s_own[wid][1]; uint32_t* s_ro = s_own[wid][2]; uint32_t* s_nrc = s_own[wid][3];
   uint32_t* s_mro = s_own[wid][4]; uint32_t* s_mnrc = s_own[wid][5]; uint32_t* s_words = s_own[wid][6];
+  uint32_t* s_rsum = s_own[wid][7]; uint32_t* s_mrsum = s_own[wid][8];
   uint16_t* queue = s_queue[wid];
   const uint32_t n_batches = (b.n_aln + 31) >> 5;
   const uint32_t cap_tmpw = ctl->cap_tmpw, cap_rows = ctl->cap_rows, cap_outw = ctl->cap_outw;
@@ -96,29 +114,41 @@ __global__ void __launch_bounds__(256, 5) k_back(DevBatch b, Ctl* __restrict__ c
     wb = __shfl_sync(0xffffffffu, wb, 0);
     if (wb >= n_batches) break;
     const uint32_t a = wb * 32 + lane;
-    uint32_t off = 0, n = 0, m_off = 0, m_n = 0, ro = 0, nrc = 0, mro = 0, mnrc = 0, rsum = 0, mrsum = 0, pflag = 0;
+    uint32_t off = 0, n = 0, m_off = 0, m_n = 0, ro = 0, nrc = 0, mro = 0, mnrc = 0, rsum = 0, mrsum = 0, pflag = 0, nm = 0;
     int32_t mate = -1;
+    bool owner = false;
     if (a < b.n_aln) {
       const uint4 ac = __ldg(&v.a_cand[a]);
       mate = __ldg(&b.mate_idx[a]);
-      if ((mate < 0 || (uint32_t)mate > a) && ac.z) {         // unit owner with at least one match
+      ro = __ldg(&b.cigar_off[a]); nrc = __ldg(&b.cigar_off[a + 1]) - ro;
+#if VAR_MSUM == 1
+      if (ac.z) rsum = real_msum(b.cigar + ro, nrc);          // every lane sums its OWN real CIGAR ...
+#endif
+      owner = (mate < 0 || (uint32_t)mate > a) && ac.z;       // unit owner with at least one match
+      if (owner) {
         off = ac.x; n = ac.y;
-        ro = __ldg(&b.cigar_off[a]); nrc = __ldg(&b.cigar_off[a + 1]) - ro;
-        rsum = real_msum(b.cigar + ro, nrc);
-        uint32_t nm = 0;
         if (mate >= 0) {
           const uint4 mc = __ldg(&v.a_cand[mate]);
           m_off = mc.x; m_n = mc.y; nm = mc.z;
           mro = __ldg(&b.cigar_off[mate]); mnrc = __ldg(&b.cigar_off[mate + 1]) - mro;
-          if (nm) mrsum = real_msum(b.cigar + mro, mnrc);
         }
         pflag = (nm == 0 ? 1u : 0u) | ((ac.z == 1 && nm == 1) ? 2u : 0u);
       }
     }
+    {                                                       // ... and an owner takes its mate's from the mate's lane when that is in the batch
+      const uint32_t ml = (uint32_t)mate - wb * 32;
+#if VAR_MSUM == 1
+      const uint32_t got = __shfl_sync(0xffffffffu, rsum, ml & 31u);
+      if (owner && nm) mrsum = ml < 32u ? got : real_msum(b.cigar + mro, mnrc);
+#else
+      (void)ml;
+      if (owner) { rsum = real_msum(b.cigar + ro, nrc); if (nm) mrsum = real_msum(b.cigar + mro, mnrc); }
+#endif
+    }
     const uint32_t incl = warp_incl_scan(n, lane), excl = incl - n, total = __shfl_sync(0xffffffffu, incl, 31);
     const bool staged = total <= BACK_STAGE;
     uint4* stage = staged ? s_stage[wid] : gstage;          // staged: indexed by item; otherwise by slot
-    s_off[lane] = off; s_excl[lane] = excl; s_ro[lane] = ro; s_nrc[lane] = nrc; s_mro[lane] = mro; s_mnrc[lane] = mnrc; s_words[lane] = 0;
+    s_off[lane] = off; s_excl[lane] = excl; s_ro[lane] = ro; s_nrc[lane] = nrc; s_mro[lane] = mro; s_mnrc[lane] = mnrc; s_words[lane] = 0; s_rsum[lane] = rsum; s_mrsum[lane] = mrsum;
     __syncwarp();
     uint32_t rows = 0, words = 0, qn = 0;
     // general merge of one emitted row (pair): all lanes call, `go` lanes work
@@ -131,8 +161,13 @@ __global__ void __launch_bounds__(256, 5) k_back(DevBatch b, Ctl* __restrict__ c
       if (!go) return;
       uint32_t clr = 0, clm = 0;
       if (fit) {
-        clr = merge_cigars(b.cigar + s_ro[L], l_nrc, v.ipool + mr.z, mr.y >> 1, mr.z, tpool + toff + 1);
-        if (paired) clm = merge_cigars(b.cigar + s_mro[L], l_mnrc, v.ipool + pr.z, pr.y >> 1, pr.z, tpool + toff + 1 + cap_r);
+        // a row of the pair may still be the trivial one-word case
+        if (VAR_ROWTRIV && (mr.y >> 1) == 1 && merge_trivial(mr.z, s_rsum[L])) { tpool[toff + 1] = mr.z; clr = 1; }
+        else clr = merge_cigars(b.cigar + s_ro[L], l_nrc, v.ipool + mr.z, mr.y >> 1, mr.z, tpool + toff + 1);
+        if (paired) {
+          if (VAR_ROWTRIV && (pr.y >> 1) == 1 && merge_trivial(pr.z, s_mrsum[L])) { tpool[toff + 1 + cap_r] = pr.z; clm = 1; }
+          else clm = merge_cigars(b.cigar + s_mro[L], l_mnrc, v.ipool + pr.z, pr.y >> 1, pr.z, tpool + toff + 1 + cap_r);
+        }
         tpool[toff] = clr;
       }
       stage[sidx] = make_uint4(tid, clr + clm, part, fit ? toff : NOFIT);
@@ -154,10 +189,21 @@ __global__ void __launch_bounds__(256, 5) k_back(DevBatch b, Ctl* __restrict__ c
       if (tid != NONE) {
         if (o_pf & 1u) part = SELF;
         else {
+          // (the matches of an alignment have distinct tids: one guide-exon chain per transcript)
+#if VAR_PARTNER == 0
           uint32_t only = NONE;
-#pragma unroll 4
+#pragma unroll kUnroll
           for (uint32_t d = o_moff, e = o_moff + o_mn; d < e; d++) { const uint32_t t = __ldg(&v.m_rec[d].w); if (t == tid) part = d; if (t != NONE) only = d; }
           if (part == NONE && (o_pf & 2u)) part = only;           // different transcripts
+#elif VAR_PARTNER == 1
+          for (uint32_t d = o_moff, e = o_moff + o_mn; d < e; d++) if (__ldg(&v.m_rec[d].w) == tid) { part = d; break; }
+          if (part == NONE && (o_pf & 2u))                        // one match each, different transcripts
+            for (uint32_t d = o_moff, e = o_moff + o_mn; d < e; d++) if (__ldg(&v.m_rec[d].w) != NONE) part = d;
+#else
+          for (uint32_t d = o_moff, e = o_moff + o_mn; d < e; d++) if (__ldg(&v.m_rec[d].w) == tid) part = d;
+          if (part == NONE && (o_pf & 2u))                        // one match each, different transcripts
+            for (uint32_t d = o_moff, e = o_moff + o_mn; d < e; d++) if (__ldg(&v.m_rec[d].w) != NONE) part = d;
+#endif
         }
       }
       const bool emitted = part != NONE, paired = emitted && part != SELF;
@@ -229,10 +275,10 @@ __global__ void __launch_bounds__(256, 5) k_back(DevBatch b, Ctl* __restrict__ c
       if (tid == NONE || sg.w == NOFIT) continue;
       // rank among the emitted matches of the read: ascending tid, slot order among equals; CIGAR words before me
       uint32_t rank = 0, wpre = 0;
-#pragma unroll 4
+#pragma unroll kUnroll
       for (uint32_t k = 0; k < o_n; k++) {
         const uint2 e = *reinterpret_cast<const uint2*>(&stage[s0 + k]);
-        if (e.x != NONE && (e.x < tid || (e.x == tid && s0 + k < sidx))) { rank++; wpre += e.y; }
+        if (e.x < tid || (e.x == tid && s0 + k < sidx)) { rank++; wpre += e.y; }        // (NONE is never below a tid)
       }
       const uint32_t part = sg.z;
       const bool paired = part != SELF, inl = sg.w == INLINE;
@@ -241,10 +287,11 @@ __global__ void __launch_bounds__(256, 5) k_back(DevBatch b, Ctl* __restrict__ c
       const uint32_t clr = inl ? 1u : tpool[sg.w];
       uint4 m = mr; uint32_t cc = c, aln = wb * 32 + L, fl = BRB_REC_FIRST, wpos = w0, len = clr;
       const uint32_t* src = tpool + sg.w + 1;
-      if (paired) fl |= BRB_REC_PAIRED | (__ldg(&v.m_rec[part].w) == tid ? BRB_REC_SAMETX : 0);
+      uint4 pm = make_uint4(0, 0, 0, NONE);
+      if (paired) { pm = __ldg(&v.m_rec[part]); fl |= BRB_REC_PAIRED | (pm.w == tid ? BRB_REC_SAMETX : 0); }
       for (uint32_t e = 0, ne = paired ? 2 : 1; e < ne; e++) {
         if (e) {                                            // the mate row follows the read row
-          m = __ldg(&v.m_rec[part]); cc = part; aln = (uint32_t)o_mate; fl &= ~BRB_REC_FIRST; wpos = w0 + clr;
+          m = pm; cc = part; aln = (uint32_t)o_mate; fl &= ~BRB_REC_FIRST; wpos = w0 + clr;
           src = tpool + sg.w + 1 + (s_nrc[L] + (mr.y >> 1) + 2); len = inl ? 1u : sg.y - clr;
         }
         const uint32_t minus = m.y & 1u;

@@ -18,6 +18,13 @@
 #include "k_lookup.cuh"
 #include "k_chain.cuh"
 
+#ifndef VAR_COMPACT
+#define VAR_COMPACT 1
+#endif
+#ifndef VAR_FRONT_CTAS
+#define VAR_FRONT_CTAS 5
+#endif
+
 namespace brb {
 
 // a_cand[a] = { first candidate slot, #slots ('+' task first, then '-'), #slots that hold a match, - }
@@ -172,9 +179,13 @@ __global__ void __launch_bounds__(256) k_front(DevIndex ix, DevBatch b, brb_para
 // marked empty.  (n_hits then only counts exon-0 hits; the reference-defined figure for the roofline numerator
 // comes from the generic kernel, see BRB_OPT_GENERIC_FRONT.)
 template <bool SIM>
-__global__ void __launch_bounds__(256, 5) k_front_short(DevIndex ix, DevBatch b, brb_params p, Ctl* __restrict__ ctl,
+__global__ void __launch_bounds__(256, VAR_FRONT_CTAS) k_front_short(DevIndex ix, DevBatch b, brb_params p, Ctl* __restrict__ ctl,
                                                         uint4* __restrict__ a_cand, uint32_t* __restrict__ ipool, Matches M) {
   const unsigned lane = threadIdx.x & 31;
+#if !VAR_COMPACT
+  __shared__ uint32_t s_nvalid[8][32];
+  uint32_t* nval = s_nvalid[threadIdx.x >> 5];
+#endif
   const uint32_t n_batches = (b.n_aln + 31) >> 5;
   const uint32_t cap_cand = ctl->cap_cand, cap_ideal = ctl->cap_ideal;       // constant during the launch
   WarpPool wp; wp.cur = 0; wp.end = 0;
@@ -215,7 +226,11 @@ __global__ void __launch_bounds__(256, 5) k_front_short(DevIndex ix, DevBatch b,
     sbase = __shfl_sync(0xffffffffu, sbase, 31);
     const bool slots_fit = (unsigned long long)sbase + total <= cap_cand;
     const int status0 = exon_status(rx.n_ex, 0);
+#if VAR_COMPACT
     uint32_t nvalid = 0, wr = 0;                            // matches kept for MY alignment / by the batch so far
+#else
+    nval[lane] = 0; __syncwarp();
+#endif
     for (uint32_t base = 0; base < total; base += 32) {
       const uint32_t item = base + lane;
       const bool actv = item < total;
@@ -239,6 +254,7 @@ __global__ void __launch_bounds__(256, 5) k_front_short(DevIndex ix, DevBatch b,
       const uint32_t want = sv ? 3 * ox.n_ex : 0;           // at most S/I/D + M + S/I/D per read exon
       bool pool_fit;
       const uint32_t ioff = warp_pool_alloc(wp, &ctl->n_ideal, cap_ideal, want, lane, pool_fit);
+#if VAR_COMPACT
       bool ok = false; uint32_t pos = 0, ilen = 0, word = 0; double sim = 0.0;
       if (sv && pool_fit && slots_fit) {
         RecLink lk = rec_link(ix.rec, rec0);
@@ -264,6 +280,31 @@ __global__ void __launch_bounds__(256, 5) k_front_short(DevIndex ix, DevBatch b,
     const uint32_t first = sbase + warp_incl_scan(nvalid, lane) - nvalid;
     if (a < b.n_aln) a_cand[a] = make_uint4(first, nvalid, nvalid, 0);
   }
+#else
+      if (!actv || !slots_fit) continue;
+      const uint32_t slot = sbase + item;
+      bool ok = false; uint32_t pos = 0, ilen = 0, word = 0; double sim = 0.0;
+      if (sv && pool_fit) {
+        RecLink lk = rec_link(ix.rec, rec0);
+        ok = true;
+        if (lk.gprev_en > (int32_t)ox.qs0 || lk.gnext_st < (int32_t)ox.qe0) {      // a neighbour exon of this tid also overlaps read exon 0
+          const uint32_t r1 = rec0;
+          ok = dedupe_first(ix, p, ox, s, rec0);
+          if (ok && rec0 != r1) { key = rec_key(ix.rec, rec0); lk = rec_link(ix.rec, rec0); }
+        }
+        if (ok) ok = eval_short<SIM>(ix, b, p, ox, s, key, lk, ipool + ioff, pos, ilen, word, sim);
+      }
+      if (ok) {
+        M.rec[slot] = make_uint4(pos, (ilen << 1) | (uint32_t)s, ilen == 1 ? word : ioff, key.tid);
+        if (SIM) { M.sim[slot] = sim; M.clip[slot] = 0; }
+        kept++; atomicAdd(&nval[L], 1u);
+      } else M.rec[slot].w = NONE;
+    }
+    __syncwarp();
+    if (a < b.n_aln) a_cand[a] = make_uint4(sbase + excl, n, nval[lane], 0);
+    __syncwarp();
+  }
+#endif
   for (int d = 16; d; d >>= 1) { my_hits += __shfl_down_sync(0xffffffffu, my_hits, d); kept += __shfl_down_sync(0xffffffffu, kept, d);
                                  n_mates += __shfl_down_sync(0xffffffffu, n_mates, d); }
   if (lane == 0) {

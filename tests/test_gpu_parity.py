@@ -44,6 +44,26 @@ def test_micro_introns_duplicate_tids(mode):
     _check(wl, f"micro/{mode}")
 
 
+@pytest.mark.parametrize("mode", ["default", "lr_nofasta"])
+def test_hot_genes_big_batches(mode):
+    """Genes with 50-200 isoforms: a batch of 32 alignments then carries far more matches than the back kernel
+    stages in shared memory (global staging, general CIGAR merges on the second walk) and the front kernels walk
+    index ranges much longer than a warp."""
+    from bramble_b200 import pack, synth
+    m = common.MODES[mode]
+    ann = synth.make_annotation(91, n_chrom=1, n_genes=6, hi_iso_genes=4, hi_iso_exons=14)
+    assert max(np.bincount([int(t["gene"][1:].split(".")[0]) for t in ann.tx])) >= 50
+    if m["long"]:
+        recs = synth.make_long_reads(ann, None, 93, 600, params=dict(err=0.08))
+    else:
+        recs = synth.make_short_reads(ann, 93, 1500, multi_mean=2.0)
+    ix = pack.build_index(ann)
+    batches = pack.pack_batches(recs, ix, ann.chroms, long_reads=m["long"])
+    wl = dict(index=ix, params=common.params_for(mode), batches=batches)
+    n_rec = _check(wl, f"hot/{mode}")
+    assert n_rec > 20 * len(recs) // 4
+
+
 def test_multiple_bundles_and_ragged():
     wl = common.make_workload("default", 41, n_names=3000, chunk_size=700)
     assert len(wl["batches"]) > 3
