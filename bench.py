@@ -71,16 +71,18 @@ class ClockSampler:
 
 
 def _traffic(names):
-    """dram__bytes_read.sum + dram__bytes_write.sum per step from the committed `ncu --set full` capture
-    (profiles/r01_v8_traffic.json), valid for the default workload size only; else None."""
+    """dram__bytes_read.sum + dram__bytes_write.sum per step from the newest committed `ncu --set full` capture
+    (profiles/r*_traffic.json), valid for the default workload size only; else None."""
     try:
         if names != 2_000_000:
-            return None, None
-        with open(os.path.join(ROOT, "profiles", "r01_v8_traffic.json")) as f:
-            t = json.load(f)
-        return int(sum(t.values())), {k: int(v) for k, v in t.items()}
+            return None, None, None
+        import glob
+        f = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_traffic.json")))[-1]
+        with open(f) as fh:
+            t = json.load(fh)
+        return int(sum(t.values())), {k: int(v) for k, v in t.items()}, os.path.relpath(f, ROOT)
     except Exception:
-        return None, None
+        return None, None, None
 
 
 def workload(seed, names):
@@ -141,6 +143,8 @@ def main():
     ap.add_argument("--names", type=int, default=2_000_000)
     ap.add_argument("--ref-names", type=int, default=150_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-bundles", type=int, default=8, help="bundles per step on the end-to-end path")
+    ap.add_argument("--e2e-contexts", type=int, default=3, help="brb_ctx (host threads / streams) on the end-to-end path")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -220,17 +224,33 @@ def main():
     barrier()
     clocks = sampler.stop() if rank == 0 else None
     st = eng.stats()
-    # ---- end to end through the C ABI with pinned host columns
-    PB = eng.pinned_copy(B)
+    # ---- end to end through the C ABI with pinned host columns: the step's alignments as `--e2e-bundles` bundles
+    # (cut at read-name boundaries, like the reference's bundles) through `--e2e-contexts` contexts, one host
+    # thread each, so that the H2D copy of a bundle overlaps the kernels of another and the D2H copy of a third;
+    # every brb_project() call = H2D of its bundle + all kernels + D2H of its rows
+    G = int(B.desc.n_groups)
+    nbun = max(1, min(args.e2e_bundles, G))
+    cuts = [G * i // nbun for i in range(nbun + 1)]
+    PBs = [eng.pinned_copy(B.slice_groups(g0, g1)) for g0, g1 in zip(cuts[:-1], cuts[1:])]
+    ctxs = [eng.context() for _ in range(max(1, args.e2e_contexts))]
     for _ in range(2):
-        eng.project(p, PB, raw=True)
+        engine.project_pipelined(ctxs, p, PBs)
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        eng.project(p, PB, raw=True)
+        res = engine.project_pipelined(ctxs, p, PBs)
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
-    st2 = eng.stats()
+    e2e_h2d, e2e_d2h, e2e_rec = sum(r[2] for r in res), sum(r[3] for r in res), sum(r[0] for r in res)
+    barrier()
+    # the same through ONE call on one context (no overlap), for comparison
+    PB = eng.pinned_copy(B)
+    eng.project(p, PB, raw=True)
+    t0 = time.perf_counter()
+    for _ in range(min(3, args.steps)):
+        eng.project(p, PB, raw=True)
+    torch.cuda.synchronize()
+    e2e_single_s = (time.perf_counter() - t0) / min(3, args.steps)
     barrier()
     t = torch.tensor([ms, e2e_s * 1e3, float(n_aln)], dtype=torch.float64, device=f"cuda:{local}")
     tmax = t.clone()
@@ -247,18 +267,22 @@ def main():
         alg = alg_ref
         achieved = alg / (ms / args.steps / 1e3) / 1e9
         names = {"ms_lookup": "k_front_short (lookup + evaluate)", "ms_chain": "k_chain (rescue path only)", "ms_finalize": "k_build (rescue path only)",
-                 "ms_pair": "k_pair_a (pairing + CIGAR merge)", "ms_merge": "scan + k_pair_b (rank + rows)", "ms_rescue": "k_ksw (rescue path only)"}
+                 "ms_pair": "k_back (pairing + CIGAR merge + rows)", "ms_merge": "scan + k_place + k_group_rows (rows to bundle order)",
+                 "ms_rescue": "k_ksw (rescue path only)"}
         top = max(phase, key=lambda k: phase[k])
-        traffic, traffic_by_kernel = _traffic(args.names)
+        traffic, traffic_by_kernel, traffic_src = _traffic(args.names)
         alg_of = {"ms_lookup": alg_front, "ms_pair": alg - alg_front, "ms_merge": alg - alg_front}
         top_ms = phase[top] / args.steps
         top_alg = alg_of.get(top, alg)
         line = {"metric": metric, "value": value, "unit": unit, "n_gpus": args.gpus, "steps": args.steps, "warmup": max(3, args.warmup),
                 "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32",
                 "data": "synthetic", "config": config, "gpu_launches": launches, "clocks": clocks,
-                "e2e": {"value": e2e, "unit": unit, "h2d_bytes_per_step": int(st2.h2d_bytes), "d2h_bytes_per_step": int(st2.d2h_bytes)},
+                "e2e": {"value": e2e, "unit": unit, "h2d_bytes_per_step": e2e_h2d, "d2h_bytes_per_step": e2e_d2h,
+                        "records_per_step": e2e_rec, "bundles_per_step": nbun, "contexts": len(ctxs),
+                        "how": "brb_project() per bundle from pinned host columns, one host thread per context",
+                        "single_call_value": n_aln / e2e_single_s, "single_call_note": "rank 0, one brb_project() call for the whole step, no overlap"},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                             "traffic_by_kernel": traffic_by_kernel, "traffic_source": "profiles/r01_v8_summary.md (ncu --set full, one step)",
+                             "traffic_by_kernel": traffic_by_kernel, "traffic_source": f"{traffic_src} (ncu --set full, one step)" if traffic_src else None,
                              "peak_source": peak_src, "scope": "whole kernel sequence of one step (algorithmic bytes of SURVEY 8(d) / DESIGN.md)",
                              "alg_bytes_per_step": alg, "alg_bytes_per_alignment": alg / max(1, n_aln),
                              "top_kernel": names[top], "top_kernel_share": phase[top] / max(1e-9, sum(phase.values())),
@@ -276,6 +300,10 @@ def main():
                 line["cpu_baseline"] = {"value": res["value"], "unit": unit, "cores": min(cores, 255), "kind": "reference", "sample": res["sample"]}
         print(json.dumps(line))
     eng.pinned_free(PB)
+    for x in PBs:
+        eng.pinned_free(x)
+    for c in ctxs:
+        c.close()
     eng.close()
     if world > 1:
         dist.destroy_process_group()

@@ -26,6 +26,57 @@ def _rows(o, n_groups):
     return d
 
 
+class Context:
+    """An extra brb_ctx on an Engine's index: own CUDA stream, scratch pools and pinned staging.  The C ABI wants
+    one context per host thread; several of them overlap the H2D copy of one bundle with the kernels of the
+    next and the D2H copy of the previous one (the reference runs its bundles on `-p` worker threads the same
+    way, src/threads.cpp:100-104)."""
+
+    def __init__(self, eng):
+        self.lib = eng.lib
+        self._ctx = C.c_void_p()
+        capi.check(self.lib.brb_ctx_create(eng._ix, C.byref(self._ctx)), "brb_ctx_create")
+
+    def project(self, params, batch, raw=False):
+        out = capi.BatchOut()
+        capi.check(self.lib.brb_project(self._ctx, C.byref(params), C.byref(batch.desc), C.byref(out)), "brb_project")
+        return out if raw else _rows(out, batch.desc.n_groups)
+
+    def stats(self):
+        s = capi.Stats()
+        capi.check(self.lib.brb_ctx_stats(self._ctx, C.byref(s)), "brb_ctx_stats")
+        return s
+
+    def close(self):
+        if self._ctx:
+            self.lib.brb_ctx_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+
+def project_pipelined(contexts, params, bundles, raw=True):
+    """Bundles through `contexts` (one host thread each, ctypes releases the GIL): results in bundle order.
+    A context's result arrays are only valid until its next call, so raw results have to be consumed by
+    the caller before that; with raw=True they are reduced here to (n_rec, n_cigar_words, h2d_bytes, d2h_bytes)."""
+    from concurrent.futures import ThreadPoolExecutor
+    import queue
+    free = queue.SimpleQueue()
+    for c in contexts:
+        free.put(c)
+
+    def run(b):
+        c = free.get()
+        try:
+            o = c.project(params, b, raw=raw)
+            if not raw:
+                return o
+            st = c.stats()
+            return (int(o.n_rec), int(o.n_cigar_words), int(st.h2d_bytes), int(st.d2h_bytes))
+        finally:
+            free.put(c)
+    with ThreadPoolExecutor(max_workers=len(contexts)) as ex:
+        return list(ex.map(run, bundles))
+
+
 class Engine:
     def __init__(self, index, device=0):
         self.lib = capi.lib()
@@ -44,6 +95,9 @@ class Engine:
         if self._ix:
             self.lib.brb_index_destroy(self._ix)
             self._ix = C.c_void_p()
+
+    def context(self):
+        return Context(self)
 
     def __enter__(self):
         return self

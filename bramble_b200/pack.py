@@ -247,6 +247,41 @@ class Batch:
             d.seq_codes = None
         return self
 
+    def slice_groups(self, g0, g1):
+        """Read-name groups [g0, g1) as a bundle of their own (mates never leave their group, src/bramble.cpp:272-311)."""
+        A = self.arrays
+        go = A["group_off"].astype(np.int64)
+        a0, a1 = int(go[g0]), int(go[g1])
+        eo, co = A["exon_off"].astype(np.int64), A["cigar_off"].astype(np.int64)
+        mate = A["mate_idx"][a0:a1].astype(np.int64)
+        nb = Batch()
+        B = nb.arrays
+        B["refid"] = np.ascontiguousarray(A["refid"][a0:a1]); B["strand"] = np.ascontiguousarray(A["strand"][a0:a1])
+        B["exon_off"] = (eo[a0:a1 + 1] - eo[a0]).astype(np.uint32)
+        B["exon_st"] = np.ascontiguousarray(A["exon_st"][eo[a0]:eo[a1]]); B["exon_en"] = np.ascontiguousarray(A["exon_en"][eo[a0]:eo[a1]])
+        B["cigar_off"] = (co[a0:a1 + 1] - co[a0]).astype(np.uint32)
+        B["cigar"] = np.ascontiguousarray(A["cigar"][co[a0]:co[a1]])
+        B["mate_idx"] = np.where(mate >= 0, mate - a0, -1).astype(np.int32)
+        B["group_off"] = (go[g0:g1 + 1] - a0).astype(np.uint32)
+        nb.src = self.src[a0:a1] if self.src is not None and len(self.src) else None
+        nb.names = self.names[g0:g1] if self.names else []
+        d = nb.desc
+        d.n_aln, d.n_groups = a1 - a0, g1 - g0
+        for k in ("group_off", "refid", "strand", "exon_off", "exon_st", "exon_en", "cigar_off", "cigar", "mate_idx"):
+            if B[k].size == 0:
+                B[k] = np.zeros(1, B[k].dtype)
+            setattr(d, k, capi.ptr(B[k]))
+        if "group_seq_off" in A:
+            so = A["group_seq_off"].astype(np.int64)
+            B["group_seq_off"] = (so[g0:g1 + 1] - so[g0]).astype(np.uint64)
+            B["seq_codes"] = np.ascontiguousarray(A["seq_codes"][so[g0]:so[g1]])
+            if B["seq_codes"].size == 0:
+                B["seq_codes"] = np.zeros(1, np.uint8)
+            d.group_seq_off = capi.ptr(B["group_seq_off"]); d.seq_codes = capi.ptr(B["seq_codes"])
+        else:
+            d.group_seq_off = None; d.seq_codes = None
+        return nb
+
 
 _NT16 = "=ACMGRSVTWYHKDBN"
 

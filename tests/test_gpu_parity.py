@@ -64,6 +64,32 @@ def test_hot_genes_big_batches(mode):
     assert n_rec > 20 * len(recs) // 4
 
 
+def test_contexts_in_parallel():
+    """Several brb_ctx on one index, one host thread each (the end-to-end path of bench.py): bundle slices projected
+    concurrently give exactly the rows of the whole bundle."""
+    wl = common.make_workload("default", 43, n_names=4000)
+    ix, p, b = wl["index"], wl["params"], wl["batches"][0]
+    exp = oracle_lib.port_project(ix, p, b)
+    G = b.desc.n_groups
+    cuts = [G * i // 7 for i in range(8)]
+    parts = [b.slice_groups(g0, g1) for g0, g1 in zip(cuts[:-1], cuts[1:])]
+    with engine.Engine(ix) as eng:
+        ctxs = [eng.context() for _ in range(3)]
+        try:
+            for _ in range(3):
+                got = engine.project_pipelined(ctxs, p, parts, raw=False)
+                assert sum(g["n_rec"] for g in got) == exp["n_rec"]
+                for k in ("tid", "pos", "flags", "tx_strand"):
+                    assert np.array_equal(np.concatenate([g[k] for g in got]), exp[k]), k
+                a0 = np.concatenate([[0], np.cumsum([q.desc.n_aln for q in parts])])
+                assert np.array_equal(np.concatenate([g["src_aln"] + a0[i] for i, g in enumerate(got)]), exp["src_aln"])
+                cg = [c for g in got for c in g["cigars"]]
+                assert all(np.array_equal(x, y) for x, y in zip(cg, exp["cigars"]))
+        finally:
+            for c in ctxs:
+                c.close()
+
+
 def test_multiple_bundles_and_ragged():
     wl = common.make_workload("default", 41, n_names=3000, chunk_size=700)
     assert len(wl["batches"]) > 3
