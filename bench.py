@@ -143,6 +143,7 @@ def main():
     ap.add_argument("--names", type=int, default=2_000_000)
     ap.add_argument("--ref-names", type=int, default=150_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="profiling runs: resident steps only")
     ap.add_argument("--e2e-bundles", type=int, default=8, help="bundles per step on the end-to-end path")
     ap.add_argument("--e2e-contexts", type=int, default=3, help="brb_ctx (host threads / streams) on the end-to-end path")
     args = ap.parse_args()
@@ -228,30 +229,33 @@ def main():
     # (cut at read-name boundaries, like the reference's bundles) through `--e2e-contexts` contexts, one host
     # thread each, so that the H2D copy of a bundle overlaps the kernels of another and the D2H copy of a third;
     # every brb_project() call = H2D of its bundle + all kernels + D2H of its rows
-    G = int(B.desc.n_groups)
-    nbun = max(1, min(args.e2e_bundles, G))
-    cuts = [G * i // nbun for i in range(nbun + 1)]
-    PBs = [eng.pinned_copy(B.slice_groups(g0, g1)) for g0, g1 in zip(cuts[:-1], cuts[1:])]
-    ctxs = [eng.context() for _ in range(max(1, args.e2e_contexts))]
-    for _ in range(2):
-        engine.project_pipelined(ctxs, p, PBs)
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        res = engine.project_pipelined(ctxs, p, PBs)
-    torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    e2e_h2d, e2e_d2h, e2e_rec = sum(r[2] for r in res), sum(r[3] for r in res), sum(r[0] for r in res)
-    barrier()
-    # the same through ONE call on one context (no overlap), for comparison
-    PB = eng.pinned_copy(B)
-    eng.project(p, PB, raw=True)
-    t0 = time.perf_counter()
-    for _ in range(min(3, args.steps)):
+    PB, PBs, ctxs, nbun = None, [], [], 0
+    e2e_s, e2e_single_s, e2e_h2d, e2e_d2h, e2e_rec = 0.0, 1.0, 0, 0, 0
+    if not args.no_e2e:
+        G = int(B.desc.n_groups)
+        nbun = max(1, min(args.e2e_bundles, G))
+        cuts = [G * i // nbun for i in range(nbun + 1)]
+        PBs = [eng.pinned_copy(B.slice_groups(g0, g1)) for g0, g1 in zip(cuts[:-1], cuts[1:])]
+        ctxs = [eng.context() for _ in range(max(1, args.e2e_contexts))]
+        for _ in range(2):
+            engine.project_pipelined(ctxs, p, PBs)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            res = engine.project_pipelined(ctxs, p, PBs)
+        torch.cuda.synchronize()
+        e2e_s = time.perf_counter() - t0
+        e2e_h2d, e2e_d2h, e2e_rec = sum(r[2] for r in res), sum(r[3] for r in res), sum(r[0] for r in res)
+        barrier()
+        # the same through ONE call on one context (no overlap), for comparison
+        PB = eng.pinned_copy(B)
         eng.project(p, PB, raw=True)
-    torch.cuda.synchronize()
-    e2e_single_s = (time.perf_counter() - t0) / min(3, args.steps)
-    barrier()
+        t0 = time.perf_counter()
+        for _ in range(min(3, args.steps)):
+            eng.project(p, PB, raw=True)
+        torch.cuda.synchronize()
+        e2e_single_s = (time.perf_counter() - t0) / min(3, args.steps)
+        barrier()
     t = torch.tensor([ms, e2e_s * 1e3, float(n_aln)], dtype=torch.float64, device=f"cuda:{local}")
     tmax = t.clone()
     if world > 1:
@@ -263,7 +267,7 @@ def main():
         peak, peak_src = _peaks()
         step_ms = ms_max / args.steps
         value = total_aln * args.steps / (ms_max / 1e3)
-        e2e = total_aln * args.steps / (e2e_ms_max / 1e3)
+        e2e = total_aln * args.steps / (e2e_ms_max / 1e3) if not args.no_e2e else None
         alg = alg_ref
         achieved = alg / (ms / args.steps / 1e3) / 1e9
         names = {"ms_lookup": "k_front_short (lookup + evaluate)", "ms_chain": "k_chain (rescue path only)", "ms_finalize": "k_build (rescue path only)",
@@ -277,7 +281,7 @@ def main():
         line = {"metric": metric, "value": value, "unit": unit, "n_gpus": args.gpus, "steps": args.steps, "warmup": max(3, args.warmup),
                 "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32",
                 "data": "synthetic", "config": config, "gpu_launches": launches, "clocks": clocks,
-                "e2e": {"value": e2e, "unit": unit, "h2d_bytes_per_step": e2e_h2d, "d2h_bytes_per_step": e2e_d2h,
+                "e2e": None if args.no_e2e else {"value": e2e, "unit": unit, "h2d_bytes_per_step": e2e_h2d, "d2h_bytes_per_step": e2e_d2h,
                         "records_per_step": e2e_rec, "bundles_per_step": nbun, "contexts": len(ctxs),
                         "how": "brb_project() per bundle from pinned host columns, one host thread per context",
                         "single_call_value": n_aln / e2e_single_s, "single_call_note": "rank 0, one brb_project() call for the whole step, no overlap"},
@@ -299,7 +303,8 @@ def main():
             if res:
                 line["cpu_baseline"] = {"value": res["value"], "unit": unit, "cores": min(cores, 255), "kind": "reference", "sample": res["sample"]}
         print(json.dumps(line))
-    eng.pinned_free(PB)
+    if PB is not None:
+        eng.pinned_free(PB)
     for x in PBs:
         eng.pinned_free(x)
     for c in ctxs:

@@ -154,6 +154,13 @@ __device__ __forceinline__ unsigned warp_owner(uint32_t incl, uint32_t item) {
   for (int d = 16; d > 0; d >>= 1) { const uint32_t v = __shfl_sync(0xffffffffu, incl, pos + d - 1); if (v <= item) pos += d; }
   return pos;
 }
+// The same search with the prefix sums in shared memory (any lane may ask for any item, no convergence needed).
+__device__ __forceinline__ unsigned warp_owner_smem(const uint32_t* incl, uint32_t item) {
+  unsigned pos = 0;
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) if (incl[pos + d - 1] <= item) pos += d;
+  return pos;
+}
 // bits [a,b) of a 32-bit word, 0 <= a <= b <= 32
 __device__ __forceinline__ uint32_t bit_range(uint32_t a, uint32_t b) {
   const uint32_t hi = b >= 32 ? 0xffffffffu : ((1u << b) - 1u);

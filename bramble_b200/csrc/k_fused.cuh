@@ -21,6 +21,12 @@
 #ifndef VAR_COMPACT
 #define VAR_COMPACT 1
 #endif
+#ifndef VAR_PREFETCH
+#define VAR_PREFETCH 0
+#endif
+#ifndef VAR_FRONT_SMEM
+#define VAR_FRONT_SMEM 1
+#endif
 #ifndef VAR_FRONT_CTAS
 #define VAR_FRONT_CTAS 5
 #endif
@@ -182,6 +188,11 @@ template <bool SIM>
 __global__ void __launch_bounds__(256, VAR_FRONT_CTAS) k_front_short(DevIndex ix, DevBatch b, brb_params p, Ctl* __restrict__ ctl,
                                                         uint4* __restrict__ a_cand, uint32_t* __restrict__ ipool, Matches M) {
   const unsigned lane = threadIdx.x & 31;
+#if VAR_FRONT_SMEM
+  __shared__ uint32_t s_all[8][9][32];
+  uint32_t (*s_al)[32] = s_all[threadIdx.x >> 5];
+  uint32_t* s_incl = s_al[8]; (void)s_incl;
+#endif
 #if !VAR_COMPACT
   __shared__ uint32_t s_nvalid[8][32];
   uint32_t* nval = s_nvalid[threadIdx.x >> 5];
@@ -225,7 +236,18 @@ __global__ void __launch_bounds__(256, VAR_FRONT_CTAS) k_front_short(DevIndex ix
     if (lane == 31 && total) sbase = atomicAdd(&ctl->n_cand, total);
     sbase = __shfl_sync(0xffffffffu, sbase, 31);
     const bool slots_fit = (unsigned long long)sbase + total <= cap_cand;
+#if VAR_FRONT_SMEM
+    // per-alignment facts of the batch go through shared memory: a lane fetches those of the alignment that owns
+    // its candidate (one LDS each) and they do not sit in registers across the evaluation
+    s_al[0][lane] = rx.qs0; s_al[1][lane] = rx.qe0; s_al[2][lane] = rx.e0; s_al[3][lane] = rx.n_ex;
+    s_al[4][lane] = excl; s_al[5][lane] = n0; s_al[6][lane] = lo0; s_al[7][lane] = lo1;
+#if VAR_PREFETCH
+    s_incl[lane] = incl;
+#endif
+    __syncwarp();
+#else
     const int status0 = exon_status(rx.n_ex, 0);
+#endif
 #if VAR_COMPACT
     uint32_t nvalid = 0, wr = 0;                            // matches kept for MY alignment / by the batch so far
 #else
@@ -236,6 +258,14 @@ __global__ void __launch_bounds__(256, VAR_FRONT_CTAS) k_front_short(DevIndex ix
       const bool actv = item < total;
       const unsigned L = warp_owner(incl, actv ? item : total - 1);
       ReadExons ox;
+#if VAR_FRONT_SMEM
+      ox.qs0 = s_al[0][L]; ox.qe0 = s_al[1][L]; ox.e0 = s_al[2][L]; ox.n_ex = s_al[3][L];
+      const uint32_t o_ex = s_al[4][L], o_n0 = s_al[5][L];
+      const int o_status = exon_status(ox.n_ex, 0);
+      const uint32_t idx = item - o_ex;
+      const int s = idx >= o_n0;
+      uint32_t rec0 = s ? s_al[7][L] + (idx - o_n0) : s_al[6][L] + idx;
+#else
       ox.qs0 = __shfl_sync(0xffffffffu, rx.qs0, L); ox.qe0 = __shfl_sync(0xffffffffu, rx.qe0, L);
       ox.e0 = __shfl_sync(0xffffffffu, rx.e0, L); ox.n_ex = __shfl_sync(0xffffffffu, rx.n_ex, L);
       const uint32_t o_ex = __shfl_sync(0xffffffffu, excl, L), o_n0 = __shfl_sync(0xffffffffu, n0, L);
@@ -244,9 +274,18 @@ __global__ void __launch_bounds__(256, VAR_FRONT_CTAS) k_front_short(DevIndex ix
       const uint32_t idx = item - o_ex;
       const int s = idx >= o_n0;
       uint32_t rec0 = s ? o_lo1 + (idx - o_n0) : o_lo0 + idx;
+#endif
       bool sv = false, ov = false; RecKey key;
       if (actv) {
         key = rec_key(ix.rec, rec0);
+#if VAR_PREFETCH && VAR_FRONT_SMEM
+        if (item + 32 < total) {                             // the record this lane evaluates in the next round: start its fetch now
+          const unsigned L2 = warp_owner_smem(s_incl, item + 32);
+          const uint32_t idx2 = item + 32 - s_al[4][L2], n02 = s_al[5][L2];
+          const uint32_t r2 = idx2 >= n02 ? s_al[7][L2] + (idx2 - n02) : s_al[6][L2] + idx2;
+          asm volatile("prefetch.global.L1 [%0];" ::"l"(&ix.rec[r2]));
+        }
+#endif
         ov = (int32_t)ox.qs0 < key.en;                     // st < qe holds for every record below hi
         sv = ov && passes_filter(p, s, o_status, ox.qs0, ox.qe0, (uint32_t)key.st, (uint32_t)key.en);
       }
@@ -276,6 +315,7 @@ __global__ void __launch_bounds__(256, VAR_FRONT_CTAS) k_front_short(DevIndex ix
       wr += __popc(B_ok);
       if (n && incl > base && excl < base + 32) nvalid += __popc(B_ok & bit_range(excl > base ? excl - base : 0, incl - base < 32 ? incl - base : 32));
     }
+    __syncwarp();                                           // the per-alignment facts in shared memory are rewritten by the next batch
     kept += nvalid;
     const uint32_t first = sbase + warp_incl_scan(nvalid, lane) - nvalid;
     if (a < b.n_aln) a_cand[a] = make_uint4(first, nvalid, nvalid, 0);
