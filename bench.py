@@ -97,12 +97,12 @@ def ref_cmd(cores):
     return ["--fr", "-p", str(max(1, min(cores, 255)))]
 
 
-def time_reference(A, ix, B, n_small, n_big, cores, repeats=1):
+def time_reference(A, ix, B, n_small, n_big, cores, repeats=1, binary=None, extra=()):
     """Reference C++ (oracle/_ref/bramble_ref, unmodified sources) on a bounded sample of the same
     workload.  Throughput is MARGINAL: (aln_big - aln_small) / (t_big - t_small), which removes the GTF
     load + index build the reference pays once per run.  BGZF level 1 for the output, all host cores."""
     from bramble_b200 import synth, synth_fast as sf
-    ref = os.path.join(ROOT, "oracle", "_ref", "bramble_ref")
+    ref = binary or os.path.join(ROOT, "oracle", "_ref", "bramble_ref")
     if not os.path.exists(ref):
         return None
     d = tempfile.mkdtemp(prefix="brb_bench_")
@@ -121,7 +121,7 @@ def time_reference(A, ix, B, n_small, n_big, cores, repeats=1):
             wd = tempfile.mkdtemp(dir=d)
             env = dict(os.environ, BRB_SHIM_LEVEL="1")
             t0 = time.perf_counter()
-            r = subprocess.run([ref, bam, "-G", os.path.join(d, "a.gtf"), "-o", os.path.join(wd, "out.bam"), "--quiet"] + ref_cmd(cores),
+            r = subprocess.run([ref, bam, "-G", os.path.join(d, "a.gtf"), "-o", os.path.join(wd, "out.bam"), "--quiet"] + ref_cmd(cores) + list(extra),
                                cwd=wd, env=env, capture_output=True, text=True)
             dt = time.perf_counter() - t0
             if r.returncode != 0:
@@ -302,6 +302,15 @@ def main():
                 line["cpu_baseline_error"] = str(e)[:200]
             if res:
                 line["cpu_baseline"] = {"value": res["value"], "unit": unit, "cores": min(cores, 255), "kind": "reference", "sample": res["sample"]}
+            # the drop-in CLI (host C++: BGZF/BAM decode, ingest, flush replay, record assembly, BGZF encode; CUDA engine
+            # through the C ABI) on the same BAM sample, same flags: end to end INCLUDING BGZF, marginal rate like the reference
+            try:
+                cli = time_reference(A, ix, B, 2000, args.ref_names, cores, binary=g.build_cli(), extra=["--level", "1"])
+                if cli:
+                    line["cli_e2e"] = {"value": cli["value"], "unit": unit, "sample": cli["sample"], "host_threads": min(cores, 255),
+                                       "what": "bramble_b200_cli BAM in -> BAM out (1 GPU), marginal over a 2000-name run"}
+            except Exception as e:
+                line["cli_e2e_error"] = str(e)[:200]
         print(json.dumps(line))
     if PB is not None:
         eng.pinned_free(PB)

@@ -1,6 +1,6 @@
 // BGZF (blocked gzip) reader and writer over zlib.  Host-side I/O of the drop-in CLI; htslib/libdeflate are
 // not in this image, so the codec is written here (same container format: 64 KiB blocks, BC extra field,
-// EOF marker block).  The writer compresses blocks on a small thread pool, keeping block order.
+// EOF marker block).  Reader and writer (de)compress the independent blocks on small thread pools, keeping block order.
 #pragma once
 #include <zlib.h>
 #include <cstdint>
@@ -16,55 +16,123 @@
 
 namespace brbhost {
 
+// Reader.  threads <= 1: blocks are inflated on the calling thread.  threads > 1: a feeder thread walks the file
+// block by block (the BC field gives every block's size without touching the payload), a pool inflates the
+// independent blocks, read() consumes them in file order.
 class BgzfReader {
  public:
-  explicit BgzfReader(const std::string& path) {
+  explicit BgzfReader(const std::string& path, int threads = 1) {
     f_ = fopen(path.c_str(), "rb");
     if (!f_) throw std::runtime_error("cannot open " + path);
     setvbuf(f_, nullptr, _IOFBF, 1 << 20);
+    if (threads > 1) {
+      max_jobs_ = (size_t)threads * 8;
+      for (int i = 0; i < threads; i++) pool_.emplace_back([this] { worker(); });
+      feeder_ = std::thread([this] { feed(); });
+    }
   }
-  ~BgzfReader() { if (f_) fclose(f_); }
+  ~BgzfReader() {
+    { std::unique_lock<std::mutex> lk(m_); stop_ = true; }
+    cv_.notify_all(); cv_room_.notify_all(); cv_ready_.notify_all();
+    if (feeder_.joinable()) feeder_.join();
+    for (auto& t : pool_) t.join();
+    for (Job* j : order_) delete j;
+    if (f_) fclose(f_);
+  }
   // reads exactly n bytes unless EOF; returns bytes read
   size_t read(void* dst, size_t n) {
     uint8_t* d = static_cast<uint8_t*>(dst); size_t got = 0;
     while (got < n) {
-      if (pos_ == buf_.size()) { if (!fill()) break; }
+      if (pos_ == buf_.size()) { if (!(pool_.empty() ? fill() : next_block())) break; }
       size_t k = std::min(n - got, buf_.size() - pos_);
       memcpy(d + got, buf_.data() + pos_, k); pos_ += k; got += k;
     }
     return got;
   }
  private:
+  struct Job { std::vector<uint8_t> comp, out; size_t clen = 0; uint32_t isize = 0; bool ready = false; std::string err; };
+  // next compressed block from the file: false at EOF
+  bool read_block(std::vector<uint8_t>& comp, size_t& clen, uint32_t& isize) {
+    uint8_t h[12];
+    if (fread(h, 1, 12, f_) != 12) return false;
+    if (h[0] != 0x1f || h[1] != 0x8b) throw std::runtime_error("not a BGZF file");
+    const unsigned xlen = h[10] | (h[11] << 8);
+    extra_.resize(xlen);
+    if (xlen && fread(extra_.data(), 1, xlen, f_) != xlen) return false;
+    unsigned bsize = 0; bool found = false;
+    for (size_t p = 0; p + 4 <= xlen;) {
+      const unsigned slen = extra_[p + 2] | (extra_[p + 3] << 8);
+      if (extra_[p] == 'B' && extra_[p + 1] == 'C' && slen == 2) { bsize = extra_[p + 4] | (extra_[p + 5] << 8); found = true; }
+      p += 4 + slen;
+    }
+    if (!found) throw std::runtime_error("BGZF block without BC field");
+    clen = (size_t)bsize + 1 - xlen - 12 - 8;
+    comp.resize(clen + 8);
+    if (fread(comp.data(), 1, clen + 8, f_) != clen + 8) return false;
+    isize = comp[clen + 4] | (comp[clen + 5] << 8) | (comp[clen + 6] << 16) | ((uint32_t)comp[clen + 7] << 24);
+    return true;
+  }
+  static void inflate_block(const std::vector<uint8_t>& comp, size_t clen, uint32_t isize, std::vector<uint8_t>& out) {
+    out.resize(isize);
+    if (isize == 0) return;
+    z_stream zs; memset(&zs, 0, sizeof zs);
+    if (inflateInit2(&zs, -15) != Z_OK) throw std::runtime_error("inflateInit2");
+    zs.next_in = const_cast<uint8_t*>(comp.data()); zs.avail_in = (uInt)clen; zs.next_out = out.data(); zs.avail_out = isize;
+    const int rc = inflate(&zs, Z_FINISH); inflateEnd(&zs);
+    if (rc != Z_STREAM_END) throw std::runtime_error("BGZF inflate failed");
+  }
   bool fill() {
     for (;;) {
-      uint8_t h[12];
-      if (fread(h, 1, 12, f_) != 12) return false;
-      if (h[0] != 0x1f || h[1] != 0x8b) throw std::runtime_error("not a BGZF file");
-      const unsigned xlen = h[10] | (h[11] << 8);
-      extra_.resize(xlen);
-      if (xlen && fread(extra_.data(), 1, xlen, f_) != xlen) return false;
-      unsigned bsize = 0; bool found = false;
-      for (size_t p = 0; p + 4 <= xlen;) {
-        const unsigned slen = extra_[p + 2] | (extra_[p + 3] << 8);
-        if (extra_[p] == 'B' && extra_[p + 1] == 'C' && slen == 2) { bsize = extra_[p + 4] | (extra_[p + 5] << 8); found = true; }
-        p += 4 + slen;
+      size_t clen; uint32_t isize;
+      if (!read_block(comp_, clen, isize)) return false;
+      pos_ = 0;
+      inflate_block(comp_, clen, isize, buf_);
+      if (isize) return true;
+    }
+  }
+  // ---- threaded path
+  void feed() {
+    try {
+      for (;;) {
+        Job* j = new Job();
+        if (!read_block(j->comp, j->clen, j->isize)) { delete j; break; }
+        std::unique_lock<std::mutex> lk(m_);
+        cv_room_.wait(lk, [this] { return stop_ || order_.size() < max_jobs_; });
+        if (stop_) { delete j; return; }
+        order_.push_back(j); todo_.push_back(j);
+        cv_.notify_one();
       }
-      if (!found) throw std::runtime_error("BGZF block without BC field");
-      const size_t clen = (size_t)bsize + 1 - xlen - 12 - 8;
-      comp_.resize(clen + 8);
-      if (fread(comp_.data(), 1, clen + 8, f_) != clen + 8) return false;
-      const uint32_t isize = comp_[clen + 4] | (comp_[clen + 5] << 8) | (comp_[clen + 6] << 16) | ((uint32_t)comp_[clen + 7] << 24);
-      buf_.resize(isize); pos_ = 0;
-      if (isize == 0) continue;
-      z_stream zs; memset(&zs, 0, sizeof zs);
-      if (inflateInit2(&zs, -15) != Z_OK) throw std::runtime_error("inflateInit2");
-      zs.next_in = comp_.data(); zs.avail_in = (uInt)clen; zs.next_out = buf_.data(); zs.avail_out = isize;
-      const int rc = inflate(&zs, Z_FINISH); inflateEnd(&zs);
-      if (rc != Z_STREAM_END) throw std::runtime_error("BGZF inflate failed");
-      return true;
+    } catch (const std::exception& e) { std::unique_lock<std::mutex> lk(m_); feed_err_ = e.what(); }
+    { std::unique_lock<std::mutex> lk(m_); eof_ = true; }
+    cv_.notify_all(); cv_ready_.notify_all();
+  }
+  void worker() {
+    for (;;) {
+      Job* j = nullptr;
+      { std::unique_lock<std::mutex> lk(m_); cv_.wait(lk, [this] { return stop_ || eof_ || !todo_.empty(); });
+        if (todo_.empty()) { if (stop_ || eof_) return; continue; }
+        j = todo_.front(); todo_.pop_front(); }
+      try { inflate_block(j->comp, j->clen, j->isize, j->out); } catch (const std::exception& e) { j->err = e.what(); }
+      { std::unique_lock<std::mutex> lk(m_); j->ready = true; }
+      cv_ready_.notify_all();
+    }
+  }
+  bool next_block() {
+    for (;;) {
+      Job* j = nullptr;
+      { std::unique_lock<std::mutex> lk(m_);
+        cv_ready_.wait(lk, [this] { return (!order_.empty() && order_.front()->ready) || (order_.empty() && eof_); });
+        if (order_.empty()) { if (!feed_err_.empty()) throw std::runtime_error(feed_err_); return false; }
+        j = order_.front(); order_.pop_front(); }
+      cv_room_.notify_one();
+      if (!j->err.empty()) { const std::string e = j->err; delete j; throw std::runtime_error(e); }
+      buf_.swap(j->out); pos_ = 0; delete j;
+      if (!buf_.empty()) return true;
     }
   }
   FILE* f_ = nullptr; std::vector<uint8_t> buf_, comp_, extra_; size_t pos_ = 0;
+  std::vector<std::thread> pool_; std::thread feeder_; std::mutex m_; std::condition_variable cv_, cv_room_, cv_ready_;
+  std::deque<Job*> order_, todo_; size_t max_jobs_ = 0; bool stop_ = false, eof_ = false; std::string feed_err_;
 };
 
 class BgzfWriter {

@@ -5,6 +5,7 @@
 // the flush()/write_to_bam bookkeeping (src/core.cpp:96-332, incl. the libstdc++ unordered_map order and
 // mt19937_64 tie-break); everything between (convert_reads' evaluate/pair/merge) runs behind the C ABI.
 // Extra flags: --gpus N (bundles dealt round-robin to N devices, ordered merge), --level L (BGZF level).
+#include <chrono>
 #include <atomic>
 #include <cmath>
 #include <condition_variable>
@@ -74,6 +75,7 @@ Options parse(int argc, char** argv) {
     else if (o.in_bam.empty()) o.in_bam = a; else usage("more than one positional argument");
   }
   if (const char* g = getenv("BRB_GPUS")) o.gpus = atoi(g);      // same as --gpus, without changing the @PG CL: text
+  if (const char* t = getenv("BRB_THREADS")) o.threads = atoi(t);   // same as -p, without changing the @PG CL: text
   if (const char* l = getenv("BRB_LEVEL")) o.level = atoi(l);
   if (o.in_bam.empty()) usage("in.bam is required");
   if (o.out_bam.empty()) usage("-o is required");         // required in code, src/bramble.cpp:477-478
@@ -156,6 +158,8 @@ struct Bundle {
   std::vector<uint64_t> seq_off; std::vector<uint8_t> seq;
   // result (copied out of the engine's staging)
   std::vector<uint32_t> g_roff, src, tid, pos, coff, cig; std::vector<int8_t> tstrand; std::vector<uint8_t> flags; std::vector<double> sim; std::vector<int32_t> clip;
+  // assembled output records of the bundle (uncompressed BAM bytes) and its share of the final report
+  std::vector<uint8_t> out; uint64_t dropped = 0, total_complete = 0, total_unique = 0; bool assembled = false;
   RecView view(uint32_t a) const { return RecView{raw.data() + rec_off[a], rec_len[a]}; }
   uint32_t n_aln() const { return (uint32_t)refid.size(); }
 };
@@ -254,7 +258,7 @@ int main(int argc, char** argv) {
     IndexColumns cols;
     if (!o.fasta.empty()) load_genome(o.fasta, A, cols.chrom_off, cols.genome);
     build_index_columns(A, cols);
-    BgzfReader in(o.in_bam);
+    BgzfReader in(o.in_bam, std::min(o.threads, 8));
     const InHeader ih = read_bam_header(in);
     const std::string header = make_header(ih, A, o);
     std::vector<int> ref2refid(ih.ref_names.size(), -1);
@@ -272,31 +276,66 @@ int main(int argc, char** argv) {
       out.write(hb.data(), hb.size()); out.flush_block(); }
 
     // pipeline: producer (this thread) -> per-GPU worker -> ordered assembler/writer
+    const bool timing = getenv("BRB_CLI_TIMING") != nullptr;      // stage seconds on stderr at the end
+    using clk = std::chrono::steady_clock;
+    auto secs = [](clk::time_point a, clk::time_point b) { return std::chrono::duration<double>(b - a).count(); };
+    double t_read = 0, t_ingest = 0, t_wait_push = 0, t_project = 0, t_store = 0, t_assemble = 0, t_write = 0;
+    const auto t_begin = clk::now();
     Stats st; std::mutex m; std::condition_variable cv;
     std::vector<std::deque<std::shared_ptr<Bundle>>> todo(n_gpu); std::deque<std::shared_ptr<Bundle>> inflight; bool eof = false; std::string err;
-    std::vector<std::shared_ptr<Bundle>> done_flags;
-    std::unordered_set<uint64_t> finished;
+    std::deque<std::shared_ptr<Bundle>> to_assemble;          // projected, waiting for flush replay + record assembly
+    int workers_left = n_gpu;
+    const int n_asm = std::max(1, o.threads);
     auto worker = [&](int g) {
       for (;;) {
         std::shared_ptr<Bundle> b;
-        { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return eof || !todo[g].empty() || !err.empty(); }); if (!err.empty()) return; if (todo[g].empty()) { if (eof) return; continue; } b = todo[g].front(); todo[g].pop_front(); }
+        { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return eof || !todo[g].empty() || !err.empty(); });
+          if (!err.empty() || (todo[g].empty() && eof)) { workers_left--; cv.notify_all(); return; }
+          if (todo[g].empty()) continue;
+          b = todo[g].front(); todo[g].pop_front(); }
         brb_batch_in bi{}; fill_batch(*b, params.use_fasta, bi); brb_batch_out bo{};
+        const auto t0 = clk::now();
         const int rc = engines[g]->project(params, bi, bo);
+        const auto t1 = clk::now();
+        if (rc == 0) store_result(*b, bo);
+        const auto t2 = clk::now();
         std::unique_lock<std::mutex> lk(m);
-        if (rc != 0) { err = engines[g]->last_error(); cv.notify_all(); return; }
-        store_result(*b, bo); finished.insert(b->index); cv.notify_all();
+        t_project += secs(t0, t1); t_store += secs(t1, t2);
+        if (rc != 0) { err = engines[g]->last_error(); workers_left--; cv.notify_all(); return; }
+        to_assemble.push_back(b); cv.notify_all();
+      }
+    };
+    // flush replay + record assembly of whole bundles on `-p` threads (bundles are independent: a read name never
+    // spans two of them); the writer below keeps the bundle order
+    auto assembler = [&]() {
+      for (;;) {
+        std::shared_ptr<Bundle> b;
+        { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return !err.empty() || !to_assemble.empty() || workers_left == 0; });
+          if (!err.empty()) return;
+          if (to_assemble.empty()) { if (workers_left == 0) return; continue; }
+          b = to_assemble.front(); to_assemble.pop_front(); }
+        const auto t0 = clk::now();
+        Stats bs; assemble_bundle(*b, lng, bs, b->out);
+        b->dropped = bs.dropped; b->total_complete = bs.total_complete; b->total_unique = bs.total_unique;
+        b->raw.clear(); b->raw.shrink_to_fit();
+        std::unique_lock<std::mutex> lk(m);
+        t_assemble += secs(t0, clk::now());
+        b->assembled = true; cv.notify_all();
       }
     };
     auto writer = [&]() {
-      std::vector<uint8_t> buf;
       for (;;) {
         std::shared_ptr<Bundle> b;
-        { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return !err.empty() || (!inflight.empty() && finished.count(inflight.front()->index)) || (eof && inflight.empty()); });
-          if (!err.empty()) return; if (inflight.empty()) return; b = inflight.front(); inflight.pop_front(); finished.erase(b->index); cv.notify_all(); }
-        buf.clear(); assemble_bundle(*b, lng, st, buf); out.write(buf.data(), buf.size());
+        { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return !err.empty() || (!inflight.empty() && inflight.front()->assembled) || (eof && inflight.empty()); });
+          if (!err.empty()) return; if (inflight.empty()) return; b = inflight.front(); inflight.pop_front(); cv.notify_all(); }
+        const auto t1 = clk::now();
+        out.write(b->out.data(), b->out.size());
+        st.dropped += b->dropped; st.total_complete += b->total_complete; st.total_unique += b->total_unique;
+        t_write += secs(t1, clk::now());
       }
     };
     std::vector<std::thread> threads; for (int g = 0; g < n_gpu; g++) threads.emplace_back(worker, g);
+    for (int i = 0; i < n_asm; i++) threads.emplace_back(assembler);
     std::thread wthread(writer);
 
     auto bundle = std::make_shared<Bundle>(); uint64_t n_bundles = 0;
@@ -317,15 +356,19 @@ int main(int argc, char** argv) {
         }
       }
       b.index = n_bundles++;
-      { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return inflight.size() < (size_t)(2 * n_gpu + 2) || !err.empty(); }); todo[b.index % n_gpu].push_back(bundle); inflight.push_back(bundle); }
+      const auto tw = clk::now();
+      { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return inflight.size() < (size_t)(2 * n_gpu + 2 + n_asm) || !err.empty(); }); todo[b.index % n_gpu].push_back(bundle); inflight.push_back(bundle); }
       cv.notify_all();
+      t_wait_push += secs(tw, clk::now());
       bundle = new_bundle(); hashread.clear();
     };
     std::vector<uint8_t> rec;
     for (;;) {
       int32_t bs = 0;
+      const auto tr0 = timing ? clk::now() : clk::time_point();
       if (in.read(&bs, 4) != 4) break;
       rec.resize(bs); if (in.read(rec.data(), bs) != (size_t)bs) throw std::runtime_error("truncated BAM record");
+      if (timing) t_read += secs(tr0, clk::now());
       st.total_reads++;
       const RecView v{rec.data(), (uint32_t)bs};
       if (v.flag() & 4) { st.unmapped++; continue; }
@@ -354,11 +397,20 @@ int main(int argc, char** argv) {
       prev_name = name;
     }
     push_bundle();
+    const auto t_loop_end = clk::now();
     { std::unique_lock<std::mutex> lk(m); eof = true; } cv.notify_all();
     for (auto& t : threads) t.join();
     wthread.join();
     if (!err.empty()) { fprintf(stderr, "error: %s\n", err.c_str()); return 1; }
+    const auto t_joined = clk::now();
     out.close();
+    if (timing) {
+      const double total = secs(t_begin, clk::now());
+      t_ingest = secs(t_begin, t_loop_end) - t_read - t_wait_push;
+      fprintf(stderr, "[timing] pipeline %.3fs: producer read+inflate %.3f, ingest %.3f, blocked on queue %.3f | engine project %.3f, copy-out %.3f | "
+                      "writer assemble %.3f, BGZF write %.3f | final drain %.3f\n",
+              total, t_read, t_ingest, t_wait_push, t_project, t_store, t_assemble, t_write, secs(t_joined, clk::now()));
+    }
     if (!o.quiet) {
       printf("\n[bramble_b200] final report:\n# input alignments:   %llu\n# unmapped reads:     %llu\n# dropped alignments: %llu\n# total alignments:   %llu\n# unique alignments:  %llu\n\n",
              (unsigned long long)st.total_reads, (unsigned long long)st.unmapped, (unsigned long long)st.dropped, (unsigned long long)st.total_complete, (unsigned long long)st.total_unique);

@@ -85,6 +85,24 @@ def test_host_half_with_oracle_engine_is_byte_identical(mode):
     assert len(a) > 100000
 
 
+@needs_ref
+@pytest.mark.parametrize("mode", ["default", "lr"])
+def test_host_threads_do_not_change_the_output(mode):
+    """-p N runs BGZF inflate, bundle assembly (flush replay + records) and BGZF deflate on thread pools; the
+    ordered merge keeps the stream identical to the single-threaded one (many small bundles in flight)."""
+    wl = common.make_workload(mode, 29, n_names=1200, n_genes=40)
+    d = tempfile.mkdtemp(prefix="brb_cli_")
+    args = write_inputs(wl, d, mode)
+    outs = []
+    for th in ("1", "5"):
+        os.makedirs(f"{d}/t{th}", exist_ok=True)
+        argv = ["bramble", "../in.bam", "-G", "../a.gtf", "-o", "out.bam", "--quiet", "--chunk", "150"] + args
+        r = subprocess.run(argv, executable=PORT_CLI, cwd=f"{d}/t{th}", capture_output=True, text=True, env=dict(os.environ, BRB_THREADS=th))
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs.append(raw_stream(f"{d}/t{th}/out.bam"))
+    assert outs[0] == outs[1] and len(outs[0]) > 100000
+
+
 def _pg_strip(stream):
     """drop the trailing extra flags our runs add to the @PG CL: field (--gpus N)"""
     return stream
