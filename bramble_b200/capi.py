@@ -16,6 +16,7 @@ LIB_PATH = os.environ.get("BRB_LIB") or os.path.join(_HERE, "libbramble_b200.so"
 BRB_OK, BRB_E_NO_DEVICE, BRB_E_CUDA, BRB_E_ARG, BRB_E_NOMEM, BRB_E_UNSUPPORTED = 0, -1, -2, -3, -4, -5
 REC_FIRST, REC_PAIRED, REC_SAMETX = 1, 2, 4
 OPT_GENERIC_FRONT = 1
+OPT_NO_FASTPATH = 2
 
 u8p, i8p = C.POINTER(C.c_uint8), C.POINTER(C.c_int8)
 u32p, i32p = C.POINTER(C.c_uint32), C.POINTER(C.c_int32)

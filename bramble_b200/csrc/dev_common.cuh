@@ -29,6 +29,7 @@ struct __align__(32) Rec {
 
 struct DevIndex {
   uint32_t n_tables; uint32_t n_chrom; uint64_t n_rec; uint32_t bin_shift;
+  uint32_t max_chain;            // most exons of one transcript (exon_id is a uint8_t: differences wrap beyond 256)
   const uint32_t* table_off;     // n_tables+1
   const int32_t* st;             // sorted starts (search key, SoA)
   const int32_t* pmax;           // running max of `en` inside each table (monotone -> binary search)

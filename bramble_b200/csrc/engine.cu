@@ -16,6 +16,7 @@
 #include "k_lookup.cuh"
 #include "k_chain.cuh"
 #include "k_fused.cuh"
+#include "k_front_fast.cuh"
 #include "k_ksw.cuh"
 #include "k_back.cuh"
 #include "k_merge.cuh"
@@ -85,7 +86,7 @@ struct brb_ctx {
   DevBatch b{};
   Buf in_group_off, in_refid, in_strand, in_exon_off, in_exon_st, in_exon_en, in_cigar_off, in_cigar, in_mate, in_seq_off, in_seq;
   uint64_t in_bytes = 0, n_mates = 0, seq_bytes = 0, rescue_bytes = 0;
-  bool have_batch = false, have_result = false, have_scores = false, opt_generic_front = false;
+  bool have_batch = false, have_result = false, have_scores = false, opt_generic_front = false, opt_no_fastpath = false;
   // control block + pools (capacities persist across calls and only grow)
   Buf ctl;
   uint32_t cap_cand = 0, cap_ideal = 0, cap_rows = 0, cap_tmpw = 0, cap_outw = 0;
@@ -163,6 +164,7 @@ int brb_index_create(int device, const brb_index_desc* d, brb_index** out) {
   }
   toff[d->n_tables] = (uint32_t)n;
   // exon chains: records of a table grouped by tid, ascending start
+  uint32_t max_chain = 0;
   {
     std::vector<uint32_t> ord;
     for (uint32_t t = 0; t < d->n_tables; t++) {
@@ -171,8 +173,10 @@ int brb_index_create(int device, const brb_index_desc* d, brb_index** out) {
       ord.resize(e - b);
       for (uint32_t i = b; i < e; i++) ord[i - b] = i;
       std::sort(ord.begin(), ord.end(), [&](uint32_t x, uint32_t y) { return d->tid[x] != d->tid[y] ? d->tid[x] < d->tid[y] : (d->st[x] != d->st[y] ? d->st[x] < d->st[y] : x < y); });
+      uint32_t run = 0;
       for (size_t k = 0; k < ord.size(); k++) {
         const uint32_t i = ord[k];
+        run = (k > 0 && d->tid[ord[k - 1]] == d->tid[i]) ? run + 1 : 1; max_chain = std::max(max_chain, run);
         const bool has_p = k > 0 && d->tid[ord[k - 1]] == d->tid[i], has_n = k + 1 < ord.size() && d->tid[ord[k + 1]] == d->tid[i];
         if (has_p) {
           const uint32_t q = ord[k - 1];
@@ -229,7 +233,7 @@ int brb_index_create(int device, const brb_index_desc* d, brb_index** out) {
   if (!rc) rc = up(ix->gprev, gprev.data(), n * 4);
   if (!rc) rc = up(ix->bin_off, boff.data(), boff.size() * 4);
   if (!rc) rc = up(ix->bins, bins.data(), bins.size() * sizeof(uint2));
-  ix->d.n_tables = d->n_tables; ix->d.n_rec = n; ix->d.n_chrom = 0; ix->d.bin_shift = shift;
+  ix->d.n_tables = d->n_tables; ix->d.n_rec = n; ix->d.n_chrom = 0; ix->d.bin_shift = shift; ix->d.max_chain = max_chain;
   if (!rc && d->genome_codes && d->chrom_off && d->n_chrom) {
     rc = up(ix->chrom_off, d->chrom_off, (size_t)(d->n_chrom + 1) * 8);
     if (!rc) rc = up(ix->genome, d->genome_codes, d->chrom_off[d->n_chrom]);
@@ -390,7 +394,9 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   auto resident = [&](const void* kern) { int nb = 0; if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, 256, 0) != cudaSuccess || nb < 1) nb = 1; return n_sm * nb; };
   // short-read presets: only exon 0 is looked up, candidates verify the later exons themselves (k_front_short)
   const bool short_front = !p.long_reads && !p.ignore_small_exons && !rescue && !c->opt_generic_front;
-  const void* front_fn = short_front ? (p.filter_by_similarity ? (const void*)k_front_short<true> : (const void*)k_front_short<false>)
+  const bool fast_front = short_front && !p.filter_by_similarity && !c->opt_no_fastpath;
+  const void* front_fn = fast_front ? (const void*)k_front_fast
+                       : short_front ? (p.filter_by_similarity ? (const void*)k_front_short<true> : (const void*)k_front_short<false>)
                                      : (rescue ? (const void*)k_front<false> : (const void*)k_front<true>);
   const int ncta_front = resident(front_fn);
   const int ncta_back = resident((const void*)k_back);
@@ -409,7 +415,8 @@ int project_resident(brb_ctx* c, const brb_params& p) {
     CU(cudaEventRecord(c->ev[0], st));
     // ---- phases 1..4: lookup, candidates, chain walk, (clip rescue), ideal CIGAR + scores
     if (short_front) {
-      if (p.filter_by_similarity) k_front_short<true><<<ncta_front, 256, 0, st>>>(ix, b, p, ctl, c->a_cand.as<uint4>(), c->ipool.as<uint32_t>(), M);
+      if (fast_front) k_front_fast<<<ncta_front, 256, 0, st>>>(ix, b, p, ctl, c->a_cand.as<uint4>(), c->ipool.as<uint32_t>(), M);
+      else if (p.filter_by_similarity) k_front_short<true><<<ncta_front, 256, 0, st>>>(ix, b, p, ctl, c->a_cand.as<uint4>(), c->ipool.as<uint32_t>(), M);
       else k_front_short<false><<<ncta_front, 256, 0, st>>>(ix, b, p, ctl, c->a_cand.as<uint4>(), c->ipool.as<uint32_t>(), M);
       L++;
       CU(cudaEventRecord(c->ev[1], st)); CU(cudaEventRecord(c->ev[2], st)); CU(cudaEventRecord(c->ev[3], st)); CU(cudaEventRecord(c->ev[4], st));
@@ -549,6 +556,7 @@ int brb_project(brb_ctx* c, const brb_params* p, const brb_batch_in* in, brb_bat
 int brb_ctx_set_option(brb_ctx* c, int option, int value) {
   if (!c) return fail(BRB_E_ARG, "null ctx");
   if (option == BRB_OPT_GENERIC_FRONT) { c->opt_generic_front = value != 0; return BRB_OK; }
+  if (option == BRB_OPT_NO_FASTPATH) { c->opt_no_fastpath = value != 0; return BRB_OK; }
   return fail(BRB_E_ARG, "unknown option %d", option);
 }
 

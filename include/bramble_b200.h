@@ -144,6 +144,9 @@ int brb_ctx_stats(const brb_ctx* ctx, brb_stats* out);
  * the transcript's exon chain) applies.  Results are identical; brb_stats.alg_bytes is the reference-defined
  * figure only on the generic path (it counts the index hits of ALL exons). */
 #define BRB_OPT_GENERIC_FRONT 1
+/* BRB_OPT_NO_FASTPATH != 0: short-read preset without the fast path for perfectly spliced candidates (every surviving
+ * candidate goes through the general evaluation).  Results are identical; for tests and A/B timing. */
+#define BRB_OPT_NO_FASTPATH 2
 int brb_ctx_set_option(brb_ctx* ctx, int option, int value);
 /* CUDA-event stopwatch on the ctx stream (what bench.py brackets its K timed steps with). */
 int brb_ctx_timer_start(brb_ctx* ctx);

@@ -17,11 +17,13 @@ def _check(wl, what):
     with engine.Engine(ix) as eng:
         for bi, b in enumerate(wl["batches"]):
             exp = oracle_lib.port_project(ix, p, b)
-            # both front kernels: the default choice (short-read kernel where it applies) and the generic one
-            for generic in (0, 1):
+            # every front kernel: the default choice (short-read fast-path kernel where it applies), the short-read
+            # kernel without the fast path, and the generic one
+            for generic, nofast in ((0, 0), (0, 1), (1, 0)):
                 eng.set_option(capi.OPT_GENERIC_FRONT, generic)
+                eng.set_option(capi.OPT_NO_FASTPATH, nofast)
                 got = eng.project(p, b)
-                oracle_lib.assert_rows_equal(exp, got, f"{what} batch {bi} generic={generic}")
+                oracle_lib.assert_rows_equal(exp, got, f"{what} batch {bi} generic={generic} nofast={nofast}")
                 st = eng.stats()
                 assert st.n_rec == got["n_rec"] and st.n_launches > 0
                 assert st.n_matches == exp["n_matches"]
