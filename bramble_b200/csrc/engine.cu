@@ -383,7 +383,8 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   }
   if (!c->cap_cand) {           // first guess from the batch shape; a pool that overflows grows and the sequence replays
     c->cap_cand = grown((uint64_t)12 * n); c->cap_rows = grown((uint64_t)6 * n);
-    const uint64_t slack = (uint64_t)148 * 8 * 8 * POOL_CHUNK;          // unused chunk tails of the persistent warps
+    const uint64_t slack = std::min<uint64_t>((n + 31) / 32, (uint64_t)148 * 8 * 8) * POOL_CHUNK;   // unused chunk tails of the persistent warps
+    c->cap_cand = grown((uint64_t)12 * n + slack);
     c->cap_ideal = grown((uint64_t)4 * c->cap_cand + b.n_exon + slack); c->cap_tmpw = grown((uint64_t)8 * c->cap_rows + 2 * (uint64_t)b.n_cigar + slack);
     c->cap_outw = grown((uint64_t)3 * c->cap_rows + b.n_cigar);
     if (getenv("BRB_TEST_SMALL_POOLS")) c->cap_cand = c->cap_rows = c->cap_ideal = c->cap_tmpw = c->cap_outw = 64;   // tests: force the grow-and-replay path
@@ -465,7 +466,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
     CU(cudaGetLastError());
     if (hctl->bad_input) break;
     bool again = false;
-    if (hctl->n_cand > c->cap_cand) { c->cap_cand = grown(hctl->n_cand); c->cap_ideal = std::max(c->cap_ideal, grown((uint64_t)4 * c->cap_cand)); again = true; }
+    if (hctl->n_cand > c->cap_cand) { c->cap_cand = grown((uint64_t)hctl->n_cand + std::min<uint64_t>((n + 31) / 32, (uint64_t)148 * 8 * 8) * POOL_CHUNK); c->cap_ideal = std::max(c->cap_ideal, grown((uint64_t)4 * c->cap_cand)); again = true; }
     else if (hctl->n_ideal > c->cap_ideal) { c->cap_ideal = grown(hctl->n_ideal); again = true; }
     else if (hctl->n_rows > c->cap_rows) { c->cap_rows = grown(hctl->n_rows); c->cap_tmpw = std::max(c->cap_tmpw, grown((uint64_t)8 * c->cap_rows));
                                            c->cap_outw = std::max(c->cap_outw, grown((uint64_t)3 * c->cap_rows)); again = true; }

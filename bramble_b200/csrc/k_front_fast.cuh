@@ -27,6 +27,13 @@
 #include "k_lookup.cuh"
 #include "k_chain.cuh"
 
+#ifndef VAR_SLOT_POOL
+#define VAR_SLOT_POOL 1
+#endif
+#ifndef VAR_FAST_CTAS
+#define VAR_FAST_CTAS 8
+#endif
+
 namespace brb {
 
 // Verdict of the fast path on one surviving exon-0 candidate.
@@ -69,7 +76,7 @@ __device__ __forceinline__ int fast_short(const DevIndex& ix, const DevBatch& b,
 
 constexpr uint32_t FQ_CAP = 64;          // queued candidates per warp (drained as soon as 32 are waiting)
 
-__global__ void __launch_bounds__(256, 5) k_front_fast(DevIndex ix, DevBatch b, brb_params p, Ctl* __restrict__ ctl,
+__global__ void __launch_bounds__(256, VAR_FAST_CTAS) k_front_fast(DevIndex ix, DevBatch b, brb_params p, Ctl* __restrict__ ctl,
                                                        uint4* __restrict__ a_cand, uint32_t* __restrict__ ipool, Matches M) {
   __shared__ uint32_t s_all[8][9][32];                    // per alignment of the batch: qs0, qe0, e0, n_ex, excl, n0, lo0, lo1, matches from the queue
   __shared__ uint32_t s_q[8][3][FQ_CAP];                  // queue: record, owner lane | strand << 5, slot
@@ -84,6 +91,7 @@ __global__ void __launch_bounds__(256, 5) k_front_fast(DevIndex ix, DevBatch b, 
   //  successor could pass for exon_id + 1, so the shortcut is only taken when no chain is that long)
   const bool strict = p.max_junc_ins == 0 && p.max_junc_gap == 0 && ix.max_chain <= 256;
   WarpPool wp; wp.cur = 0; wp.end = 0;
+  WarpPool sp; sp.cur = 0; sp.end = 0; (void)sp;
   unsigned long long my_hits = 0;
   uint32_t bad = 0, n_mates = 0, kept = 0;
   for (;;) {
@@ -116,10 +124,25 @@ __global__ void __launch_bounds__(256, 5) k_front_fast(DevIndex ix, DevBatch b, 
     }
     const uint32_t n = n0 + n1;
     const uint32_t incl = warp_incl_scan(n, lane), excl = incl - n, total = __shfl_sync(0xffffffffu, incl, 31);
+#if VAR_SLOT_POOL
+    // candidate slots come out of a per-warp chunk of the slot space: one atomic per ~2048 slots instead of one per
+    // batch (waiting for its return value was 10 % of the kernel's stall samples)
+    if (total > sp.end - sp.cur) {
+      const uint32_t grab = total > POOL_CHUNK ? total : POOL_CHUNK;
+      uint32_t g0 = 0;
+      if (lane == 0) g0 = atomicAdd(&ctl->n_cand, grab);
+      g0 = __shfl_sync(0xffffffffu, g0, 0);
+      sp.cur = g0; sp.end = g0 + grab;
+    }
+    const uint32_t sbase = sp.cur;
+    const bool slots_fit = sp.end <= cap_cand && sp.end >= sp.cur;
+    sp.cur += total;
+#else
     uint32_t sbase = 0;
     if (lane == 31 && total) sbase = atomicAdd(&ctl->n_cand, total);
     sbase = __shfl_sync(0xffffffffu, sbase, 31);
     const bool slots_fit = (unsigned long long)sbase + total <= cap_cand;
+#endif
     s_al[0][lane] = rx.qs0; s_al[1][lane] = rx.qe0; s_al[2][lane] = rx.e0; s_al[3][lane] = rx.n_ex;
     s_al[4][lane] = excl; s_al[5][lane] = n0; s_al[6][lane] = lo0; s_al[7][lane] = lo1; s_nv[lane] = 0;
     __syncwarp();
