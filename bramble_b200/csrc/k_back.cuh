@@ -43,8 +43,17 @@
 #ifndef VAR_ROWTRIV
 #define VAR_ROWTRIV 1
 #endif
+#ifndef VAR_PLACE_CTAS
+#define VAR_PLACE_CTAS 5
+#endif
+#ifndef VAR_PLACE_ROWS
+#define VAR_PLACE_ROWS 4
+#endif
+#ifndef VAR_BACK_STAGE
+#define VAR_BACK_STAGE 192
+#endif
 #ifndef VAR_BACK_CTAS
-#define VAR_BACK_CTAS 4
+#define VAR_BACK_CTAS 5
 #endif
 
 namespace brb {
@@ -54,7 +63,7 @@ constexpr int kUnroll = VAR_UNROLL;
 constexpr uint32_t INLINE = 0xffffffffu;   // Stage.w: every merged CIGAR of the row(s) is the one-word ideal CIGAR itself
 constexpr uint32_t PENDING = 0xfffffffeu;  // Stage.w: general merge queued
 constexpr uint32_t NOFIT = 0xfffffffdu;    // Stage.w: the scratch pool is exhausted (the host grows it and replays)
-constexpr uint32_t BACK_STAGE = 256;       // matches per batch staged in shared memory
+constexpr uint32_t BACK_STAGE = VAR_BACK_STAGE;       // matches per batch staged in shared memory
 
 // match record written by the front kernels, one uint4 per candidate slot:
 //   .x pos   .y ideal-CIGAR length << 1 | transcript strand is '-'   .z its pool offset, or the word itself when the length is 1
@@ -319,7 +328,7 @@ __global__ void __launch_bounds__(256) k_count_valid(DevBatch b, const Ctl* __re
 
 // Rows of batch wb: from where k_back claimed room (tl.claim) to their place in bundle order (t_off = exclusive
 // scan of tl.agg; t_off[n_batches] = totals).  One warp per batch.
-__global__ void __launch_bounds__(256) k_place(DevBatch b, Ctl* __restrict__ ctl, BatchTotals tl, const unsigned long long* __restrict__ t_off,
+__global__ void __launch_bounds__(256, VAR_PLACE_CTAS) k_place(DevBatch b, Ctl* __restrict__ ctl, BatchTotals tl, const unsigned long long* __restrict__ t_off,
                                                ProvRows pv, Rows o) {
   if (front_overflow(ctl)) return;
   const uint32_t n_batches = (b.n_aln + 31) >> 5;
@@ -336,12 +345,12 @@ __global__ void __launch_bounds__(256) k_place(DevBatch b, Ctl* __restrict__ ctl
     const uint32_t srow = (uint32_t)src, sword = (uint32_t)(src >> 32), drow = (uint32_t)dst, dword = (uint32_t)(dst >> 32);
     const uint32_t a = wb * 32 + lane;
     if (a < b.n_aln) o.a_roff[a] += drow;
-    for (uint32_t r0 = 0; r0 < R_b; r0 += 128) {            // four rows per lane in flight
-      uint4 x[4];
+    for (uint32_t r0 = 0; r0 < R_b; r0 += 32 * VAR_PLACE_ROWS) {            // several rows per lane in flight
+      uint4 x[VAR_PLACE_ROWS];
 #pragma unroll
-      for (int k = 0; k < 4; k++) { const uint32_t r = r0 + k * 32 + lane; if (r < R_b) x[k] = __ldcs(&pv.row[srow + r]); }
+      for (int k = 0; k < VAR_PLACE_ROWS; k++) { const uint32_t r = r0 + k * 32 + lane; if (r < R_b) x[k] = __ldcs(&pv.row[srow + r]); }
 #pragma unroll
-      for (int k = 0; k < 4; k++) {
+      for (int k = 0; k < VAR_PLACE_ROWS; k++) {
         const uint32_t r = r0 + k * 32 + lane;
         if (r < R_b) {
           o.src[drow + r] = x[k].x; o.tid[drow + r] = x[k].y; o.pos[drow + r] = x[k].z; o.coff[drow + r] = dword + (x[k].w & 0x0fffffffu);
