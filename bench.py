@@ -4,7 +4,7 @@
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--names M]
 
 A "step" is one pass of the whole kernel sequence (lookup -> chain walk -> pairing -> CIGAR merge)
-over one synthetic bundle set.  Workload = BASELINE.json configs[1] shape (C2): GENCODE-shaped
+over one synthetic bundle.  Workload = BASELINE.json configs[1] shape (C2): GENCODE-shaped
 annotation (~250k transcripts, ~2.2M exons, 25 chromosomes) + stranded (--fr) paired-end 150 bp
 name-collated reads, `--names` read names per GPU (default 2M names = ~4.6M alignments; the full C2
 is 100M pairs, scaled down so that the default run finishes in minutes -- see DESIGN.md).
@@ -77,7 +77,8 @@ def _traffic(names):
         if names != 2_000_000:
             return None, None, None
         import glob
-        f = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_traffic.json")))[-1]
+        import re
+        f = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_traffic.json")), key=lambda x: [int(t) for t in re.findall(r"\d+", os.path.basename(x))])[-1]
         with open(f) as fh:
             t = json.load(fh)
         return int(sum(t.values())), {k: int(v) for k, v in t.items()}, os.path.relpath(f, ROOT)
@@ -270,7 +271,7 @@ def main():
         e2e = total_aln * args.steps / (e2e_ms_max / 1e3) if not args.no_e2e else None
         alg = alg_ref
         achieved = alg / (ms / args.steps / 1e3) / 1e9
-        names = {"ms_lookup": "k_front_short (lookup + evaluate)", "ms_chain": "k_chain (rescue path only)", "ms_finalize": "k_build (rescue path only)",
+        names = {"ms_lookup": "k_front_fast (lookup + evaluate)", "ms_chain": "k_chain (rescue path only)", "ms_finalize": "k_build (rescue path only)",
                  "ms_pair": "k_back (pairing + CIGAR merge + rows)", "ms_merge": "scan + k_place + k_group_rows (rows to bundle order)",
                  "ms_rescue": "k_ksw (rescue path only)"}
         top = max(phase, key=lambda k: phase[k])
