@@ -225,6 +225,17 @@ def main():
     ms = eng.timer_stop()
     barrier()
     clocks = sampler.stop() if rank == 0 else None
+    # the same with BRB_OPT_ORDERED_ROWS: one more streaming pass (scan + k_place) lays the rows out in emit order on the device
+    eng.set_option(capi.OPT_ORDERED_ROWS, 1)
+    for _ in range(3):
+        eng.run_resident(p)
+    eng.timer_start()
+    for _ in range(args.steps):
+        eng.run_resident(p)
+    ms_ordered = eng.timer_stop()
+    eng.set_option(capi.OPT_ORDERED_ROWS, 0)
+    eng.run_resident(p)
+    barrier()
     st = eng.stats()
     # ---- end to end through the C ABI with pinned host columns: the step's alignments as `--e2e-bundles` bundles
     # (cut at read-name boundaries, like the reference's bundles) through `--e2e-contexts` contexts, one host
@@ -272,7 +283,7 @@ def main():
         alg = alg_ref
         achieved = alg / (ms / args.steps / 1e3) / 1e9
         names = {"ms_lookup": "k_front_fast (lookup + evaluate)", "ms_chain": "k_chain (rescue path only)", "ms_finalize": "k_build (rescue path only)",
-                 "ms_pair": "k_back (pairing + CIGAR merge + rows)", "ms_merge": "scan + k_place + k_group_rows (rows to bundle order)",
+                 "ms_pair": "k_back (pairing + CIGAR merge + rows)", "ms_merge": "k_back_finish (totals)",
                  "ms_rescue": "k_ksw (rescue path only)"}
         top = max(phase, key=lambda k: phase[k])
         traffic, traffic_by_kernel, traffic_src = _traffic(args.names)
@@ -293,7 +304,10 @@ def main():
                              "top_kernel": names[top], "top_kernel_share": phase[top] / max(1e-9, sum(phase.values())),
                              "top_kernel_ms": top_ms, "top_kernel_alg_bytes": top_alg,
                              "top_kernel_achieved": top_alg / (top_ms / 1e3) / 1e9, "top_kernel_frac": top_alg / (top_ms / 1e3) / 1e9 / peak,
-                             "phase_ms_per_step": {names[k]: v / args.steps for k, v in phase.items()}},
+                             "phase_ms_per_step": {names[k]: v / args.steps for k, v in phase.items()},
+                             "ordered_rows": {"ms_per_step": ms_ordered / args.steps, "frac": alg / (ms_ordered / args.steps / 1e3) / 1e9 / peak,
+                                              "what": "rank 0, BRB_OPT_ORDERED_ROWS=1: rows moved into emit order on the device (scan + k_place + k_group_rows) "
+                                                      "instead of unit blocks + aln_rec_off/aln_rec_cnt"}},
                 "work": {"alignments_per_gpu": n_aln, "candidates": int(st.n_candidates), "matches": int(st.n_matches), "records": int(st.n_rec)}}
         if args.gpus == 1 and not args.no_cpu_baseline:
             try:

@@ -89,7 +89,7 @@ struct brb_ctx {
   DevBatch b{};
   Buf in_group_off, in_refid, in_strand, in_exon_off, in_exon_st, in_exon_en, in_cigar_off, in_cigar, in_mate, in_seq_off, in_seq;
   uint64_t in_bytes = 0, n_mates = 0, seq_bytes = 0, rescue_bytes = 0;
-  bool have_batch = false, have_result = false, have_scores = false, opt_generic_front = false, opt_no_fastpath = false;
+  bool have_batch = false, have_result = false, have_scores = false, opt_generic_front = false, opt_no_fastpath = false, opt_ordered = false, result_ordered = false;
   // control block + pools (capacities persist across calls and only grow)
   Buf ctl;
   uint32_t cap_cand = 0, cap_ideal = 0, cap_rows = 0, cap_tmpw = 0, cap_outw = 0;
@@ -97,7 +97,7 @@ struct brb_ctx {
   Buf c_rec, c_task, c_first, c_last, c_nseg, c_nguide, c_cap, ipool;
   Buf r_left, r_right, rpool;
   Buf m_rec, m_sim, m_clip, c_stage, t_agg, t_claim, t_off, p_row, p_pool, p_sim, p_clip;
-  Buf a_roff, g_roff;
+  Buf a_roff, a_rcnt, g_roff;
   Buf o_src, o_tid, o_pos, o_strand, o_flags, o_sim, o_clip, o_coff, tpool, opool;
   HBuf h_small, h_out;
   RescueBufs* rb = nullptr;
@@ -106,7 +106,7 @@ struct brb_ctx {
   std::vector<Buf*> all() {
     return {&in_group_off, &in_refid, &in_strand, &in_exon_off, &in_exon_st, &in_exon_en, &in_cigar_off, &in_cigar, &in_mate, &in_seq_off,
             &in_seq, &ctl, &q_any, &a_cand, &scan_tmp, &c_rec, &c_task, &c_first, &c_last, &c_nseg, &c_nguide, &c_cap, &ipool,
-            &r_left, &r_right, &rpool, &m_rec, &m_sim, &m_clip, &c_stage, &t_agg, &t_claim, &t_off, &p_row, &p_pool, &p_sim, &p_clip, &a_roff, &g_roff,
+            &r_left, &r_right, &rpool, &m_rec, &m_sim, &m_clip, &c_stage, &t_agg, &t_claim, &t_off, &p_row, &p_pool, &p_sim, &p_clip, &a_roff, &a_rcnt, &g_roff,
             &o_src, &o_tid, &o_pos, &o_strand, &o_flags, &o_sim, &o_clip, &o_coff, &tpool, &opool};
   }
 };
@@ -351,13 +351,13 @@ int ensure_pools(brb_ctx* c, bool rescue) {
   const DevBatch& b = c->b;
   const size_t n = b.n_aln, C = c->cap_cand, R = c->cap_rows;
   ENS(c->q_any, (size_t)2 * b.n_exon + 16); ENS(c->a_cand, n * 16);
-  ENS(c->a_roff, (n + 1) * 4); ENS(c->g_roff, (size_t)(b.n_groups + 1) * 4);
+  ENS(c->a_roff, (n + 1) * 4); ENS(c->a_rcnt, (n + 1) * 4); ENS(c->g_roff, (size_t)(b.n_groups + 1) * 4);
   const size_t nbat = (n + 31) / 32;
   ENS(c->c_stage, C * 16); ENS(c->t_agg, nbat * 8 + 8); ENS(c->t_claim, nbat * 8 + 8); ENS(c->t_off, (nbat + 1) * 8);
   ENS(c->scan_tmp, scan_scratch_words(std::max<size_t>(nbat, 1)) * 8);
-  ENS(c->p_row, R * 16); ENS(c->p_pool, (size_t)c->cap_outw * 4);
+  if (c->opt_ordered) { ENS(c->p_row, R * 16); ENS(c->p_pool, (size_t)c->cap_outw * 4); }
   ENS(c->m_rec, C * 16);
-  if (c->have_scores) { ENS(c->m_sim, C * 8); ENS(c->m_clip, C * 4); ENS(c->o_sim, R * 8); ENS(c->o_clip, R * 4); ENS(c->p_sim, R * 8); ENS(c->p_clip, R * 4); }
+  if (c->have_scores) { ENS(c->m_sim, C * 8); ENS(c->m_clip, C * 4); ENS(c->o_sim, R * 8); ENS(c->o_clip, R * 4); if (c->opt_ordered) { ENS(c->p_sim, R * 8); ENS(c->p_clip, R * 4); } }
   if (rescue) { ENS(c->c_rec, C * 4); ENS(c->c_task, C * 4); ENS(c->c_first, C * 4); ENS(c->c_last, C * 4); ENS(c->c_nseg, C * 4); ENS(c->c_nguide, C * 4); ENS(c->c_cap, C * 4); }
   ENS(c->ipool, (size_t)c->cap_ideal * 4);
   ENS(c->o_src, R * 4); ENS(c->o_tid, R * 4); ENS(c->o_pos, R * 4); ENS(c->o_strand, R); ENS(c->o_flags, R);
@@ -382,7 +382,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   if (n == 0) {
     ENS(c->g_roff, (size_t)(b.n_groups + 1) * 4); ENS(c->o_coff, 4);
     CU(cudaMemsetAsync(c->g_roff.p, 0, 4, st)); CU(cudaMemsetAsync(c->o_coff.p, 0, 4, st)); CU(cudaStreamSynchronize(st));
-    c->have_result = true; return BRB_OK;
+    c->have_result = true; c->result_ordered = c->opt_ordered; return BRB_OK;
   }
   if (!c->cap_cand) {           // first guess from the batch shape; a pool that overflows grows and the sequence replays
     c->cap_cand = grown((uint64_t)12 * n); c->cap_rows = grown((uint64_t)6 * n);
@@ -403,7 +403,8 @@ int project_resident(brb_ctx* c, const brb_params& p) {
                        : short_front ? (p.filter_by_similarity ? (const void*)k_front_short<true> : (const void*)k_front_short<false>)
                                      : (rescue ? (const void*)k_front<false> : (const void*)k_front<true>);
   const int ncta_front = resident(front_fn);
-  const int ncta_back = resident((const void*)k_back);
+  const bool ordered = c->opt_ordered;
+  const int ncta_back = resident(ordered ? (const void*)k_back<true> : (const void*)k_back<false>);
   Ctl* ctl = c->ctl.as<Ctl>();
   Ctl* hctl = c->h_small.as<Ctl>();
   uint64_t L = 0;
@@ -451,18 +452,24 @@ int project_resident(brb_ctx* c, const brb_params& p) {
     BackIn pv; pv.a_cand = c->a_cand.as<uint4>(); pv.m_rec = c->m_rec.as<uint4>(); pv.m_sim = M.sim; pv.m_clip = M.clip; pv.ipool = c->ipool.as<uint32_t>();
     Rows o; o.src = c->o_src.as<uint32_t>(); o.tid = c->o_tid.as<uint32_t>(); o.pos = c->o_pos.as<uint32_t>(); o.strand = c->o_strand.as<int8_t>();
     o.flags = c->o_flags.as<uint8_t>(); o.sim = c->o_sim.as<double>(); o.clip = c->o_clip.as<int32_t>(); o.coff = c->o_coff.as<uint32_t>();
-    o.pool = c->opool.as<uint32_t>(); o.a_roff = c->a_roff.as<uint32_t>();
+    o.pool = c->opool.as<uint32_t>(); o.a_roff = c->a_roff.as<uint32_t>(); o.a_rcnt = c->a_rcnt.as<uint32_t>();
     if (rescue) { k_count_valid<<<grid_for(n, 256), 256, 0, st>>>(b, ctl, c->a_cand.as<uint4>(), c->m_rec.as<uint4>()); L++; }
     const uint32_t nbat = (n + 31) / 32;
     BatchTotals tl; tl.agg = c->t_agg.as<unsigned long long>(); tl.claim = c->t_claim.as<unsigned long long>();
     ProvRows pr; pr.row = c->p_row.as<uint4>(); pr.pool = c->p_pool.as<uint32_t>();
     pr.sim = c->have_scores ? c->p_sim.as<double>() : nullptr; pr.clip = c->have_scores ? c->p_clip.as<int32_t>() : nullptr;
-    k_back<<<ncta_back, 256, 0, st>>>(b, ctl, pv, c->c_stage.as<uint4>(), c->tpool.as<uint32_t>(), tl, pr, o); L++;
-    CU(cudaEventRecord(c->ev[5], st));
-    // ---- phase 6: batch totals -> offsets in bundle order; rows to their final place
-    exclusive_scan(tl.agg, c->t_off.as<unsigned long long>(), nbat, c->scan_tmp.as<unsigned long long>(), st, &L);
-    k_place<<<VAR_PLACE_GRID ? grid_for(nbat, 8) : (unsigned)ncta, 256, 0, st>>>(b, ctl, tl, c->t_off.as<unsigned long long>(), pr, o); L++;   // one warp per batch
-    k_group_rows<<<grid_for(b.n_groups + 1, 256), 256, 0, st>>>(b, ctl, c->a_roff.as<uint32_t>(), c->g_roff.as<uint32_t>()); L++;
+    if (ordered) {
+      k_back<true><<<ncta_back, 256, 0, st>>>(b, ctl, pv, c->c_stage.as<uint4>(), c->tpool.as<uint32_t>(), tl, pr, o); L++;
+      CU(cudaEventRecord(c->ev[5], st));
+      // ---- phase 6: batch totals -> offsets in bundle order; rows to their final place
+      exclusive_scan(tl.agg, c->t_off.as<unsigned long long>(), nbat, c->scan_tmp.as<unsigned long long>(), st, &L);
+      k_place<<<VAR_PLACE_GRID ? grid_for(nbat, 8) : (unsigned)ncta, 256, 0, st>>>(b, ctl, tl, c->t_off.as<unsigned long long>(), pr, o); L++;   // one warp per batch
+      k_group_rows<<<grid_for(b.n_groups + 1, 256), 256, 0, st>>>(b, ctl, c->a_roff.as<uint32_t>(), c->g_roff.as<uint32_t>()); L++;
+    } else {
+      k_back<false><<<ncta_back, 256, 0, st>>>(b, ctl, pv, c->c_stage.as<uint4>(), c->tpool.as<uint32_t>(), tl, pr, o); L++;
+      CU(cudaEventRecord(c->ev[5], st));
+      k_back_finish<<<1, 1, 0, st>>>(ctl, o); L++;
+    }
     CU(cudaEventRecord(c->ev[6], st));
     CU(cudaMemcpyAsync(hctl, ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
@@ -488,7 +495,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   // algorithmic bytes, SURVEY.md 8(d) / DESIGN.md: per-alignment SoA + 56 B per index hit + output rows + rescue bases
   S.alg_bytes_front = (uint64_t)n * 16 + (uint64_t)b.n_exon * 8 + hctl->n_mates * 4 + hctl->n_hits * 56;
   S.alg_bytes = S.alg_bytes_front + (uint64_t)b.n_cigar * 4 + (uint64_t)hctl->n_rows * 40 + hctl->out_words * 4 + c->rescue_bytes;
-  c->have_result = true;
+  c->have_result = true; c->result_ordered = ordered;
   return BRB_OK;
 }
 
@@ -512,7 +519,11 @@ int brb_batch_download(brb_ctx* c, brb_batch_out* out) {
   const bool sc = c->have_scores && R;
   auto al = [](size_t x) { return (x + 15) & ~(size_t)15; };
   size_t off = 0;
-  const size_t o_groff = off; off += al((G + 1) * 4);
+  const bool ord = c->result_ordered;
+  const size_t N = c->b.n_aln;
+  const size_t o_groff = off; off += ord ? al((G + 1) * 4) : 0;
+  const size_t o_aoff = off; off += al(N * 4);
+  const size_t o_acnt = off; off += al(N * 4);
   const size_t o_src = off; off += al(R * 4);
   const size_t o_tid = off; off += al(R * 4);
   const size_t o_pos = off; off += al(R * 4);
@@ -530,7 +541,9 @@ int brb_batch_download(brb_ctx* c, brb_batch_out* out) {
     if (cudaMemcpyAsync(h + dst, b.p, n, cudaMemcpyDeviceToHost, c->st) != cudaSuccess) return fail(BRB_E_CUDA, "download failed: %s", cudaGetErrorString(cudaGetLastError()));
     bytes += n; return 0;
   };
-  int rc = dn(o_groff, c->g_roff, (G + 1) * 4);
+  int rc = ord ? dn(o_groff, c->g_roff, (G + 1) * 4) : 0;
+  if (!rc) rc = dn(o_aoff, c->a_roff, N * 4);
+  if (!rc) rc = dn(o_acnt, c->a_rcnt, N * 4);
   if (!rc) rc = dn(o_src, c->o_src, R * 4);
   if (!rc) rc = dn(o_tid, c->o_tid, R * 4);
   if (!rc) rc = dn(o_pos, c->o_pos, R * 4);
@@ -543,7 +556,9 @@ int brb_batch_download(brb_ctx* c, brb_batch_out* out) {
   if (rc) return rc;
   CU(cudaStreamSynchronize(c->st));
   out->n_rec = (uint32_t)R; out->n_cigar_words = W;
-  out->group_rec_off = (const uint32_t*)(h + o_groff); out->src_aln = (const uint32_t*)(h + o_src); out->tid = (const uint32_t*)(h + o_tid);
+  out->group_rec_off = ord ? (const uint32_t*)(h + o_groff) : nullptr;
+  out->aln_rec_off = (const uint32_t*)(h + o_aoff); out->aln_rec_cnt = (const uint32_t*)(h + o_acnt);
+  out->src_aln = (const uint32_t*)(h + o_src); out->tid = (const uint32_t*)(h + o_tid);
   out->pos = (const uint32_t*)(h + o_pos); out->tx_strand = (const int8_t*)(h + o_strand); out->flags = h + o_flags;
   out->sim_score = sc ? (const double*)(h + o_sim) : nullptr; out->clip_score = sc ? (const int32_t*)(h + o_clip) : nullptr;
   out->cigar_off = (const uint32_t*)(h + o_coff); out->cigar = (const uint32_t*)(h + o_cig);
@@ -561,6 +576,7 @@ int brb_ctx_set_option(brb_ctx* c, int option, int value) {
   if (!c) return fail(BRB_E_ARG, "null ctx");
   if (option == BRB_OPT_GENERIC_FRONT) { c->opt_generic_front = value != 0; return BRB_OK; }
   if (option == BRB_OPT_NO_FASTPATH) { c->opt_no_fastpath = value != 0; return BRB_OK; }
+  if (option == BRB_OPT_ORDERED_ROWS) { c->opt_ordered = value != 0; return BRB_OK; }
   return fail(BRB_E_ARG, "unknown option %d", option);
 }
 

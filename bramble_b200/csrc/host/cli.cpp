@@ -157,7 +157,7 @@ struct Bundle {
   std::vector<uint32_t> group_off, exon_off, exon_st, exon_en, cigar_off, cigar; std::vector<int32_t> refid, mate; std::vector<int8_t> strand;
   std::vector<uint64_t> seq_off; std::vector<uint8_t> seq;
   // result (copied out of the engine's staging)
-  std::vector<uint32_t> g_roff, src, tid, pos, coff, cig; std::vector<int8_t> tstrand; std::vector<uint8_t> flags; std::vector<double> sim; std::vector<int32_t> clip;
+  std::vector<uint32_t> a_roff, a_rcnt, src, tid, pos, coff, cig; std::vector<int8_t> tstrand; std::vector<uint8_t> flags; std::vector<double> sim; std::vector<int32_t> clip;
   // assembled output records of the bundle (uncompressed BAM bytes) and its share of the final report
   std::vector<uint8_t> out; uint64_t dropped = 0, total_complete = 0, total_unique = 0; bool assembled = false;
   RecView view(uint32_t a) const { return RecView{raw.data() + rec_off[a], rec_len[a]}; }
@@ -175,7 +175,7 @@ void fill_batch(const Bundle& b, bool use_fasta, brb_batch_in& in) {
 
 void store_result(Bundle& b, const brb_batch_out& o) {
   const uint32_t R = o.n_rec, G = (uint32_t)b.group_off.size() - 1;
-  b.g_roff.assign(o.group_rec_off, o.group_rec_off + G + 1); b.src.assign(o.src_aln, o.src_aln + R); b.tid.assign(o.tid, o.tid + R);
+  (void)G; b.a_roff.assign(o.aln_rec_off, o.aln_rec_off + b.n_aln()); b.a_rcnt.assign(o.aln_rec_cnt, o.aln_rec_cnt + b.n_aln()); b.src.assign(o.src_aln, o.src_aln + R); b.tid.assign(o.tid, o.tid + R);
   b.pos.assign(o.pos, o.pos + R); b.tstrand.assign(o.tx_strand, o.tx_strand + R); b.flags.assign(o.flags, o.flags + R);
   if (o.sim_score) b.sim.assign(o.sim_score, o.sim_score + R); else b.sim.assign(R, 0.0);      // NULL: every score is 0 (header)
   if (o.clip_score) b.clip.assign(o.clip_score, o.clip_score + R); else b.clip.assign(R, 0);
@@ -232,14 +232,17 @@ void assemble_bundle(const Bundle& b, bool lng, Stats& st, std::vector<uint8_t>&
   };
   const uint32_t G = (uint32_t)b.group_off.size() - 1;
   for (uint32_t g = 0; g < G; g++) {
-    const uint32_t lo = b.g_roff[g], hi = b.g_roff[g + 1];
-    if (lo == hi) st.dropped++;
-    for (uint32_t r = lo; r < hi;) {
-      const bool paired = b.flags[r] & BRB_REC_PAIRED;
-      const RecView v = b.view(b.src[r]);
-      pairs_by_name[std::string(v.name())].push_back(Unit{r, paired});
-      n_pairs++; r += paired ? 2 : 1;
+    bool any = false;
+    for (uint32_t a = b.group_off[g]; a < b.group_off[g + 1]; a++) {       // unit blocks of the group, in alignment order = emit order
+      const uint32_t lo = b.a_roff[a], hi = lo + b.a_rcnt[a];
+      for (uint32_t r = lo; r < hi;) {
+        const bool paired = b.flags[r] & BRB_REC_PAIRED;
+        const RecView v = b.view(b.src[r]);
+        pairs_by_name[std::string(v.name())].push_back(Unit{r, paired});
+        n_pairs++; r += paired ? 2 : 1; any = true;
+      }
     }
+    if (!any) st.dropped++;
     if (n_pairs >= 5000) flush();                          // CHUNK_SIZE, src/core.cpp:27,421-423
   }
   if (!pairs_by_name.empty()) flush();

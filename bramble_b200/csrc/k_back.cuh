@@ -78,7 +78,8 @@ struct Rows {
   uint32_t* src; uint32_t* tid; uint32_t* pos; int8_t* strand; uint8_t* flags; double* sim; int32_t* clip;
   uint32_t* coff;               // n_rows+1: dense CIGAR pool offsets (CSR)
   uint32_t* pool;               // dense, row-ordered merged CIGARs
-  uint32_t* a_roff;             // n_aln+1: first row of each alignment's unit (bundle order)
+  uint32_t* a_roff;             // n_aln (+1 when ordered): first row of each alignment's unit
+  uint32_t* a_rcnt;             // n_aln: rows of each alignment's unit (0 for mates and for units that emit nothing)
 };
 
 // Rows as k_back leaves them: dense, but batches in completion order.  One 16-byte record per row:
@@ -102,6 +103,10 @@ __device__ __forceinline__ bool merge_trivial(uint32_t iword, uint32_t msum) { r
 
 __device__ __forceinline__ bool front_overflow(const Ctl* c) { return c->n_cand > c->cap_cand || c->n_ideal > c->cap_ideal || c->bad_input != 0; }
 
+// ORDERED: rows go to a provisional buffer as packed records and k_place moves them into bundle order afterwards.
+// !ORDERED: the claimed place is final -- rows are written straight into the output columns, blocks of 32 alignments in
+// completion order, and a_roff / a_rcnt tell the consumer where the rows of each unit are.
+template <bool ORDERED>
 __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __restrict__ ctl, BackIn v, uint4* __restrict__ gstage, uint32_t* __restrict__ tpool,
                                                  BatchTotals tl, ProvRows pv_, Rows o) {
   __shared__ uint4 s_stage[8][BACK_STAGE];                 // per match of the batch: tid (NONE: not emitted), CIGAR words, partner, scratch offset
@@ -261,12 +266,12 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
     const uint32_t R_b = __shfl_sync(0xffffffffu, irows, 31), W_b = __shfl_sync(0xffffffffu, iwords, 31);
     const unsigned long long agg = (unsigned long long)R_b | ((unsigned long long)W_b << 32);
     unsigned long long claim = 0;
-    if (lane == 0) { claim = atomicAdd(&ctl->claimed, agg); tl.agg[wb] = agg; tl.claim[wb] = claim; }
+    if (lane == 0) { claim = atomicAdd(&ctl->claimed, agg); if (ORDERED) { tl.agg[wb] = agg; tl.claim[wb] = claim; } }
     claim = __shfl_sync(0xffffffffu, claim, 0);
     const uint32_t prow0 = (uint32_t)claim, pword0 = (uint32_t)(claim >> 32);
     const uint32_t row0 = prow0 + irows - rows, word0 = pword0 + iwords - words;
-    if (a < b.n_aln) o.a_roff[a] = irows - rows;             // batch-relative; k_place adds the first row of the batch
-    if (W_b >= (1u << 28)) { if (lane == 0) atomicMax(&ctl->bad_input, 3u); __syncwarp(); continue; }
+    if (a < b.n_aln) { o.a_roff[a] = ORDERED ? irows - rows : row0; o.a_rcnt[a] = rows; }     // ORDERED: batch-relative, k_place adds the first row of the batch
+    if (ORDERED && W_b >= (1u << 28)) { if (lane == 0) atomicMax(&ctl->bad_input, 3u); __syncwarp(); continue; }
     if ((unsigned long long)prow0 + R_b > cap_rows || (unsigned long long)pword0 + W_b > cap_outw) { __syncwarp(); continue; }   // the host grows the row pools and replays
     // ---- phase 2: rank inside the unit, rows, CIGAR words
     for (uint32_t base = 0; base < total; base += 32) {
@@ -303,12 +308,18 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
           m = pm; cc = part; aln = (uint32_t)o_mate; fl &= ~BRB_REC_FIRST; wpos = w0 + clr;
           src = tpool + sg.w + 1 + (s_nrc[L] + (mr.y >> 1) + 2); len = inl ? 1u : sg.y - clr;
         }
-        const uint32_t minus = m.y & 1u;
-        pv_.row[row + e] = make_uint4(aln, m.w, m.x, (wpos - pword0) | (minus << 28) | (fl << 29));
-        if (v.m_sim) { pv_.sim[row + e] = v.m_sim[cc]; pv_.clip[row + e] = v.m_clip[cc]; }
-        if (inl) pv_.pool[wpos] = m.z;
-        else if (minus) for (uint32_t i = 0; i < len; i++) pv_.pool[wpos + i] = src[len - 1 - i];      // reverse_complement_bam, src/bam.cpp:636-702
-        else for (uint32_t i = 0; i < len; i++) pv_.pool[wpos + i] = src[i];
+        const uint32_t minus = m.y & 1u, r = row + e;
+        uint32_t* pool = ORDERED ? pv_.pool : o.pool;
+        if (ORDERED) {
+          pv_.row[r] = make_uint4(aln, m.w, m.x, (wpos - pword0) | (minus << 28) | (fl << 29));
+          if (v.m_sim) { pv_.sim[r] = v.m_sim[cc]; pv_.clip[r] = v.m_clip[cc]; }
+        } else {
+          o.src[r] = aln; o.tid[r] = m.w; o.pos[r] = m.x; o.strand[r] = minus ? '-' : '+'; o.flags[r] = (uint8_t)fl; o.coff[r] = wpos;
+          if (v.m_sim) { o.sim[r] = v.m_sim[cc]; o.clip[r] = v.m_clip[cc]; }
+        }
+        if (inl) pool[wpos] = m.z;
+        else if (minus) for (uint32_t i = 0; i < len; i++) pool[wpos + i] = src[len - 1 - i];      // reverse_complement_bam, src/bam.cpp:636-702
+        else for (uint32_t i = 0; i < len; i++) pool[wpos + i] = src[i];
       }
     }
     __syncwarp();                                           // the staging area is reused by the next batch
@@ -324,6 +335,14 @@ __global__ void __launch_bounds__(256) k_count_valid(DevBatch b, const Ctl* __re
   uint4 ac = a_cand[a]; uint32_t nv = 0;
   for (uint32_t c = ac.x, e = ac.x + ac.y; c < e; c++) nv += m_rec[c].w != NONE;
   ac.z = nv; a_cand[a] = ac;
+}
+
+// !ORDERED: the totals k_back claimed are the result sizes.
+__global__ void k_back_finish(Ctl* __restrict__ ctl, Rows o) {
+  if (front_overflow(ctl)) return;
+  const uint32_t R = (uint32_t)ctl->claimed, W = (uint32_t)(ctl->claimed >> 32);
+  ctl->n_rows = R; ctl->n_outw = W; ctl->out_words = W;
+  if (R <= ctl->cap_rows && W <= ctl->cap_outw) o.coff[R] = W;
 }
 
 // Rows of batch wb: from where k_back claimed room (tl.claim) to their place in bundle order (t_off = exclusive

@@ -8,21 +8,34 @@ import numpy as np
 from . import capi
 
 
-def _rows(o, n_groups):
+def _rows(o, batch):
+    """Rows of a brb_batch_out in the reference's emit order: the unit blocks (aln_rec_off / aln_rec_cnt) concatenated in
+    alignment order; group_rec_off follows from the block sizes."""
     n = int(o.n_rec)
+    n_aln, n_groups = int(batch.desc.n_aln), int(batch.desc.n_groups)
 
     def arr(p, cnt, dt):
         if cnt == 0 or not p:          # NULL score columns: all zero (see include/bramble_b200.h)
             return np.zeros(cnt, dtype=dt)
         return np.ctypeslib.as_array(p, shape=(cnt,)).astype(dt, copy=True)
-    d = dict(n_rec=n, group_rec_off=arr(o.group_rec_off, n_groups + 1, np.uint32), src_aln=arr(o.src_aln, n, np.uint32),
-             tid=arr(o.tid, n, np.uint32), pos=arr(o.pos, n, np.uint32), tx_strand=arr(o.tx_strand, n, np.int8),
-             flags=arr(o.flags, n, np.uint8), sim_score=arr(o.sim_score, n, np.float64), clip_score=arr(o.clip_score, n, np.int32),
-             cigar_off=arr(o.cigar_off, n + 1, np.uint32))
+    aoff, acnt = arr(o.aln_rec_off, n_aln, np.int64), arr(o.aln_rec_cnt, n_aln, np.int64)
+    assert int(acnt.sum()) == n, "unit blocks do not cover the rows"
+    start = np.cumsum(acnt) - acnt
+    order = np.repeat(aoff - start, acnt) + np.arange(n, dtype=np.int64)        # row index in memory of the k-th row in emit order
+    go = batch.arrays["group_off"].astype(np.int64)[:n_groups + 1]
+    cum = np.concatenate([[0], np.cumsum(acnt)])
+    d = dict(n_rec=n, group_rec_off=cum[go].astype(np.uint32) if n_aln else np.zeros(n_groups + 1, np.uint32),
+             src_aln=arr(o.src_aln, n, np.uint32)[order],
+             tid=arr(o.tid, n, np.uint32)[order], pos=arr(o.pos, n, np.uint32)[order], tx_strand=arr(o.tx_strand, n, np.int8)[order],
+             flags=arr(o.flags, n, np.uint8)[order], sim_score=arr(o.sim_score, n, np.float64)[order],
+             clip_score=arr(o.clip_score, n, np.int32)[order])
+    if o.group_rec_off:                                                          # BRB_OPT_ORDERED_ROWS: already in emit order
+        assert np.array_equal(order, np.arange(n)) and np.array_equal(arr(o.group_rec_off, n_groups + 1, np.uint32), d["group_rec_off"])
+    co = arr(o.cigar_off, n + 1, np.uint32).astype(np.int64)
     pool = arr(o.cigar, int(o.n_cigar_words), np.uint32)
-    co = d["cigar_off"]
-    d["cigar_len"] = np.diff(co.astype(np.int64)).astype(np.uint32)
-    d["cigars"] = [pool[int(co[r]):int(co[r + 1])].copy() for r in range(n)]
+    d["cigar_len"] = np.diff(co).astype(np.uint32)[order]
+    d["cigars"] = [pool[int(co[r]):int(co[r + 1])].copy() for r in order]
+    d["cigar_off"] = (np.cumsum(d["cigar_len"]) - d["cigar_len"]).astype(np.uint32)
     return d
 
 
@@ -40,7 +53,7 @@ class Context:
     def project(self, params, batch, raw=False):
         out = capi.BatchOut()
         capi.check(self.lib.brb_project(self._ctx, C.byref(params), C.byref(batch.desc), C.byref(out)), "brb_project")
-        return out if raw else _rows(out, batch.desc.n_groups)
+        return out if raw else _rows(out, batch)
 
     def stats(self):
         s = capi.Stats()
@@ -108,7 +121,7 @@ class Engine:
     def project(self, params, batch, raw=False):
         out = capi.BatchOut()
         capi.check(self.lib.brb_project(self._ctx, C.byref(params), C.byref(batch.desc), C.byref(out)), "brb_project")
-        return out if raw else _rows(out, batch.desc.n_groups)
+        return out if raw else _rows(out, batch)
 
     def upload(self, batch):
         capi.check(self.lib.brb_batch_upload(self._ctx, C.byref(batch.desc)), "brb_batch_upload")
@@ -116,10 +129,10 @@ class Engine:
     def run_resident(self, params):
         capi.check(self.lib.brb_project_resident(self._ctx, C.byref(params)), "brb_project_resident")
 
-    def download(self, n_groups, raw=False):
+    def download(self, batch, raw=False):
         out = capi.BatchOut()
         capi.check(self.lib.brb_batch_download(self._ctx, C.byref(out)), "brb_batch_download")
-        return out if raw else _rows(out, n_groups)
+        return out if raw else _rows(out, batch)
 
     def set_option(self, option, value):
         capi.check(self.lib.brb_ctx_set_option(self._ctx, option, int(value)), "brb_ctx_set_option")

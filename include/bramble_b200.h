@@ -87,15 +87,20 @@ typedef struct brb_batch_in {
   const uint8_t*  seq_codes;            /* group-shared read sequence (src/core.cpp:353-378), codes 0..4 */
 } brb_batch_in;
 
-/* One row per output BAM record, in the reference's emit order (src/core.cpp:384-415,
- * src/mates.cpp:28-119): for a paired BamInfo the read1 row is immediately followed by its read2 row. */
+/* One row per output BAM record.  Rows come in UNIT blocks: the unit owned by alignment a (an unpaired alignment, or
+ * the lower-indexed end of a linked pair -- `this_read` of src/core.cpp:384-415) has its rows at
+ * [aln_rec_off[a], aln_rec_off[a] + aln_rec_cnt[a]), ascending by tid exactly as add_mate_info emits them
+ * (src/mates.cpp:28-119); for a paired BamInfo the read1 row is immediately followed by its read2 row.  The reference's
+ * emit order of a bundle is the concatenation of these blocks in alignment order (group by group).  By default the
+ * blocks of different 32-alignment batches sit in the row arrays in the order the GPU finished them; with
+ * BRB_OPT_ORDERED_ROWS the row arrays themselves are in emit order and group_rec_off is filled in as well. */
 #define BRB_REC_FIRST  1u   /* this row is BamInfo::read1 */
 #define BRB_REC_PAIRED 2u   /* BamInfo::is_paired */
 #define BRB_REC_SAMETX 4u   /* BamInfo::same_transcript */
 typedef struct brb_batch_out {
   uint32_t n_rec;
   uint64_t n_cigar_words;               /* size of the cigar pool == cigar_off[n_rec] (dense, row order) */
-  const uint32_t* group_rec_off;        /* n_groups+1: rows of group g */
+  const uint32_t* group_rec_off;        /* n_groups+1: rows of group g -- only with BRB_OPT_ORDERED_ROWS, else NULL */
   const uint32_t* src_aln;              /* input alignment the record is a projection of */
   const uint32_t* tid;
   const uint32_t* pos;                  /* fwpos or rcpos by transcript strand (src/core.cpp:153-158) */
@@ -107,6 +112,8 @@ typedef struct brb_batch_out {
   const uint32_t* cigar_off;            /* n_rec+1: merged CIGAR of row r = cigar[cigar_off[r] .. cigar_off[r+1]),
                                          * ALREADY reversed for '-' transcripts */
   const uint32_t* cigar;
+  const uint32_t* aln_rec_off;          /* n_aln: first row of the unit owned by alignment a */
+  const uint32_t* aln_rec_cnt;          /* n_aln: its rows (0 for the higher-indexed end of a pair and for units that emit nothing) */
 } brb_batch_out;
 
 typedef struct brb_stats {
@@ -147,6 +154,9 @@ int brb_ctx_stats(const brb_ctx* ctx, brb_stats* out);
 /* BRB_OPT_NO_FASTPATH != 0: short-read preset without the fast path for perfectly spliced candidates (every surviving
  * candidate goes through the general evaluation).  Results are identical; for tests and A/B timing. */
 #define BRB_OPT_NO_FASTPATH 2
+/* BRB_OPT_ORDERED_ROWS != 0: one more pass on the device moves the unit blocks into the reference's emit order
+ * (group_rec_off is then valid and aln_rec_off is ascending).  Costs one streaming copy of the rows. */
+#define BRB_OPT_ORDERED_ROWS 3
 int brb_ctx_set_option(brb_ctx* ctx, int option, int value);
 /* CUDA-event stopwatch on the ctx stream (what bench.py brackets its K timed steps with). */
 int brb_ctx_timer_start(brb_ctx* ctx);

@@ -18,12 +18,13 @@ def _check(wl, what):
         for bi, b in enumerate(wl["batches"]):
             exp = oracle_lib.port_project(ix, p, b)
             # every front kernel: the default choice (short-read fast-path kernel where it applies), the short-read
-            # kernel without the fast path, and the generic one
-            for generic, nofast in ((0, 0), (0, 1), (1, 0)):
+            # kernel without the fast path, and the generic one; rows as unit blocks (default) and in emit order
+            for generic, nofast, ordered in ((0, 0, 0), (0, 1, 0), (1, 0, 0), (0, 0, 1)):
                 eng.set_option(capi.OPT_GENERIC_FRONT, generic)
                 eng.set_option(capi.OPT_NO_FASTPATH, nofast)
+                eng.set_option(capi.OPT_ORDERED_ROWS, ordered)
                 got = eng.project(p, b)
-                oracle_lib.assert_rows_equal(exp, got, f"{what} batch {bi} generic={generic} nofast={nofast}")
+                oracle_lib.assert_rows_equal(exp, got, f"{what} batch {bi} generic={generic} nofast={nofast} ordered={ordered}")
                 st = eng.stats()
                 assert st.n_rec == got["n_rec"] and st.n_launches > 0
                 assert st.n_matches == exp["n_matches"]
