@@ -144,7 +144,7 @@ def main():
     ap.add_argument("--names", type=int, default=2_000_000)
     ap.add_argument("--ref-names", type=int, default=150_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-e2e", action="store_true", help="profiling runs: resident steps only")
+    ap.add_argument("--no-e2e", action="store_true", help="profiling runs: resident steps only (also skips the ordered-rows leg)")
     ap.add_argument("--e2e-bundles", type=int, default=8, help="bundles per step on the end-to-end path")
     ap.add_argument("--e2e-contexts", type=int, default=3, help="brb_ctx (host threads / streams) on the end-to-end path")
     args = ap.parse_args()
@@ -226,15 +226,17 @@ def main():
     barrier()
     clocks = sampler.stop() if rank == 0 else None
     # the same with BRB_OPT_ORDERED_ROWS: one more streaming pass (scan + k_place) lays the rows out in emit order on the device
-    eng.set_option(capi.OPT_ORDERED_ROWS, 1)
-    for _ in range(3):
+    ms_ordered = None
+    if not args.no_e2e:
+        eng.set_option(capi.OPT_ORDERED_ROWS, 1)
+        for _ in range(3):
+            eng.run_resident(p)
+        eng.timer_start()
+        for _ in range(args.steps):
+            eng.run_resident(p)
+        ms_ordered = eng.timer_stop()
+        eng.set_option(capi.OPT_ORDERED_ROWS, 0)
         eng.run_resident(p)
-    eng.timer_start()
-    for _ in range(args.steps):
-        eng.run_resident(p)
-    ms_ordered = eng.timer_stop()
-    eng.set_option(capi.OPT_ORDERED_ROWS, 0)
-    eng.run_resident(p)
     barrier()
     st = eng.stats()
     # ---- end to end through the C ABI with pinned host columns: the step's alignments as `--e2e-bundles` bundles
@@ -305,7 +307,7 @@ def main():
                              "top_kernel_ms": top_ms, "top_kernel_alg_bytes": top_alg,
                              "top_kernel_achieved": top_alg / (top_ms / 1e3) / 1e9, "top_kernel_frac": top_alg / (top_ms / 1e3) / 1e9 / peak,
                              "phase_ms_per_step": {names[k]: v / args.steps for k, v in phase.items()},
-                             "ordered_rows": {"ms_per_step": ms_ordered / args.steps, "frac": alg / (ms_ordered / args.steps / 1e3) / 1e9 / peak,
+                             "ordered_rows": None if ms_ordered is None else {"ms_per_step": ms_ordered / args.steps, "frac": alg / (ms_ordered / args.steps / 1e3) / 1e9 / peak,
                                               "what": "rank 0, BRB_OPT_ORDERED_ROWS=1: rows moved into emit order on the device (scan + k_place + k_group_rows) "
                                                       "instead of unit blocks + aln_rec_off/aln_rec_cnt"}},
                 "work": {"alignments_per_gpu": n_aln, "candidates": int(st.n_candidates), "matches": int(st.n_matches), "records": int(st.n_rec)}}
