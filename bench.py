@@ -178,6 +178,16 @@ def main():
                           "e2e": {"value": v, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
         return
 
+    # stdout carries exactly one JSON line: whatever libraries print there (NCCL's version banner under torchrun) goes to
+    # stderr instead; the line itself is written to the saved descriptor at the end
+    sys.stdout.flush()
+    out_fd = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(line):
+        sys.stdout.flush()
+        os.write(out_fd, (json.dumps(line) + "\n").encode())
+
     import torch
     import torch.distributed as dist
     from bramble_b200 import capi, engine
@@ -328,7 +338,7 @@ def main():
                                        "what": "bramble_b200_cli BAM in -> BAM out (1 GPU), marginal over a 2000-name run"}
             except Exception as e:
                 line["cli_e2e_error"] = str(e)[:200]
-        print(json.dumps(line))
+        emit(line)
     if PB is not None:
         eng.pinned_free(PB)
     for x in PBs:

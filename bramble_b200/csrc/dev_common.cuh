@@ -5,9 +5,6 @@
 #include <stdint.h>
 #include "../../include/bramble_b200.h"
 
-#ifndef VAR_SEARCH2
-#define VAR_SEARCH2 1
-#endif
 
 namespace brb {
 
@@ -138,7 +135,6 @@ __device__ __forceinline__ void overlap_range(const DevIndex& ix, int32_t refid,
   if (b1 > nb - 2) b1 = nb - 2;
   const uint2 A0 = __ldg(&ix.bins[bo + b0]), A1 = __ldg(&ix.bins[bo + b0 + 1]);
   const uint2 B0 = __ldg(&ix.bins[bo + b1]), B1 = __ldg(&ix.bins[bo + b1 + 1]);
-#if VAR_SEARCH2
   // both searches step together: two independent loads in flight per round instead of one
   uint32_t l = B0.y, n = B1.y - B0.y, l2 = A0.x, n2 = A1.x - A0.x;
   while (n > 0 || n2 > 0) {
@@ -148,14 +144,6 @@ __device__ __forceinline__ void overlap_range(const DevIndex& ix, int32_t refid,
     if (n2 > 0) { if (v2 <= (int32_t)qs) { l2 += h2 + 1; n2 -= h2 + 1; } else n2 = h2; }
   }
   hi = l; lo = l2 < hi ? l2 : hi;
-#else
-  uint32_t l = B0.y, n = B1.y - B0.y;
-  while (n > 0) { uint32_t h = n >> 1; if (__ldg(&ix.st[l + h]) < (int32_t)qe) { l += h + 1; n -= h + 1; } else n = h; }
-  hi = l;
-  l = A0.x; n = A1.x - A0.x;
-  while (n > 0) { uint32_t h = n >> 1; if (__ldg(&ix.pmax[l + h]) <= (int32_t)qs) { l += h + 1; n -= h + 1; } else n = h; }
-  lo = l < hi ? l : hi;
-#endif
 }
 
 // ---- warp helpers

@@ -22,9 +22,6 @@
 #include "k_merge.cuh"
 
 using namespace brb;
-#ifndef VAR_PLACE_GRID
-#define VAR_PLACE_GRID 1
-#endif
 
 namespace {
 
@@ -463,7 +460,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
       CU(cudaEventRecord(c->ev[5], st));
       // ---- phase 6: batch totals -> offsets in bundle order; rows to their final place
       exclusive_scan(tl.agg, c->t_off.as<unsigned long long>(), nbat, c->scan_tmp.as<unsigned long long>(), st, &L);
-      k_place<<<VAR_PLACE_GRID ? grid_for(nbat, 8) : (unsigned)ncta, 256, 0, st>>>(b, ctl, tl, c->t_off.as<unsigned long long>(), pr, o); L++;   // one warp per batch
+      k_place<<<grid_for(nbat, 8), 256, 0, st>>>(b, ctl, tl, c->t_off.as<unsigned long long>(), pr, o); L++;   // one warp per batch
       k_group_rows<<<grid_for(b.n_groups + 1, 256), 256, 0, st>>>(b, ctl, c->a_roff.as<uint32_t>(), c->g_roff.as<uint32_t>()); L++;
     } else {
       k_back<false><<<ncta_back, 256, 0, st>>>(b, ctl, pv, c->c_stage.as<uint4>(), c->tpool.as<uint32_t>(), tl, pr, o); L++;

@@ -23,25 +23,19 @@
 //   claim     one atomic reserves the batch's rows and CIGAR words in a dense buffer -- in COMPLETION order, so a
 //             batch full of hot-gene reads never stalls the batches after it (an in-order single-pass scan did:
 //             half of the issue slots went to the look-back spin).
-//   phase 2   rank of each emitted match inside its unit (ascending tid), one 16-byte row record, and the CIGAR
-//             words (reversed for '-' transcripts).
-// k_place (after a scan of the 32-alignment batch totals) then moves every batch to its place in bundle order
-// and unpacks the row records into the output columns: streaming, fully coalesced.
+//   phase 2   rank of each emitted match inside its unit (ascending tid), its row(s) and the CIGAR words (reversed
+//             for '-' transcripts), written where the batch claimed room.
+// Default: that place is final -- the rows of a unit are found through a_roff / a_rcnt (brb_batch_out::aln_rec_off /
+// aln_rec_cnt).  BRB_OPT_ORDERED_ROWS: phase 2 writes 16-byte packed row records into a provisional buffer and k_place
+// (after a scan of the 32-alignment batch totals) moves every batch to its place in bundle order while unpacking
+// them into the output columns: streaming, fully coalesced.
 #pragma once
 #include "dev_common.cuh"
 #include "k_merge.cuh"
 
-#ifndef VAR_PARTNER
-#define VAR_PARTNER 0
-#endif
+// Tuning knobs (defaults = measured best on B200; tools/variants.py builds alternatives with -DVAR_...=x)
 #ifndef VAR_UNROLL
 #define VAR_UNROLL 4
-#endif
-#ifndef VAR_MSUM
-#define VAR_MSUM 1
-#endif
-#ifndef VAR_ROWTRIV
-#define VAR_ROWTRIV 1
 #endif
 #ifndef VAR_PLACE_CTAS
 #define VAR_PLACE_CTAS 5
@@ -135,9 +129,7 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
       const uint4 ac = __ldg(&v.a_cand[a]);
       mate = __ldg(&b.mate_idx[a]);
       ro = __ldg(&b.cigar_off[a]); nrc = __ldg(&b.cigar_off[a + 1]) - ro;
-#if VAR_MSUM == 1
       if (ac.z) rsum = real_msum(b.cigar + ro, nrc);          // every lane sums its OWN real CIGAR ...
-#endif
       owner = (mate < 0 || (uint32_t)mate > a) && ac.z;       // unit owner with at least one match
       if (owner) {
         off = ac.x; n = ac.y;
@@ -151,13 +143,8 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
     }
     {                                                       // ... and an owner takes its mate's from the mate's lane when that is in the batch
       const uint32_t ml = (uint32_t)mate - wb * 32;
-#if VAR_MSUM == 1
       const uint32_t got = __shfl_sync(0xffffffffu, rsum, ml & 31u);
       if (owner && nm) mrsum = ml < 32u ? got : real_msum(b.cigar + mro, mnrc);
-#else
-      (void)ml;
-      if (owner) { rsum = real_msum(b.cigar + ro, nrc); if (nm) mrsum = real_msum(b.cigar + mro, mnrc); }
-#endif
     }
     const uint32_t incl = warp_incl_scan(n, lane), excl = incl - n, total = __shfl_sync(0xffffffffu, incl, 31);
     const bool staged = total <= BACK_STAGE;
@@ -176,10 +163,10 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
       uint32_t clr = 0, clm = 0;
       if (fit) {
         // a row of the pair may still be the trivial one-word case
-        if (VAR_ROWTRIV && (mr.y >> 1) == 1 && merge_trivial(mr.z, s_rsum[L])) { tpool[toff + 1] = mr.z; clr = 1; }
+        if ((mr.y >> 1) == 1 && merge_trivial(mr.z, s_rsum[L])) { tpool[toff + 1] = mr.z; clr = 1; }
         else clr = merge_cigars(b.cigar + s_ro[L], l_nrc, v.ipool + mr.z, mr.y >> 1, mr.z, tpool + toff + 1);
         if (paired) {
-          if (VAR_ROWTRIV && (pr.y >> 1) == 1 && merge_trivial(pr.z, s_mrsum[L])) { tpool[toff + 1 + cap_r] = pr.z; clm = 1; }
+          if ((pr.y >> 1) == 1 && merge_trivial(pr.z, s_mrsum[L])) { tpool[toff + 1 + cap_r] = pr.z; clm = 1; }
           else clm = merge_cigars(b.cigar + s_mro[L], l_mnrc, v.ipool + pr.z, pr.y >> 1, pr.z, tpool + toff + 1 + cap_r);
         }
         tpool[toff] = clr;
@@ -204,20 +191,10 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
         if (o_pf & 1u) part = SELF;
         else {
           // (the matches of an alignment have distinct tids: one guide-exon chain per transcript)
-#if VAR_PARTNER == 0
           uint32_t only = NONE;
 #pragma unroll kUnroll
           for (uint32_t d = o_moff, e = o_moff + o_mn; d < e; d++) { const uint32_t t = __ldg(&v.m_rec[d].w); if (t == tid) part = d; if (t != NONE) only = d; }
           if (part == NONE && (o_pf & 2u)) part = only;           // different transcripts
-#elif VAR_PARTNER == 1
-          for (uint32_t d = o_moff, e = o_moff + o_mn; d < e; d++) if (__ldg(&v.m_rec[d].w) == tid) { part = d; break; }
-          if (part == NONE && (o_pf & 2u))                        // one match each, different transcripts
-            for (uint32_t d = o_moff, e = o_moff + o_mn; d < e; d++) if (__ldg(&v.m_rec[d].w) != NONE) part = d;
-#else
-          for (uint32_t d = o_moff, e = o_moff + o_mn; d < e; d++) if (__ldg(&v.m_rec[d].w) == tid) part = d;
-          if (part == NONE && (o_pf & 2u))                        // one match each, different transcripts
-            for (uint32_t d = o_moff, e = o_moff + o_mn; d < e; d++) if (__ldg(&v.m_rec[d].w) != NONE) part = d;
-#endif
         }
       }
       const bool emitted = part != NONE, paired = emitted && part != SELF;

@@ -317,9 +317,6 @@ __global__ void __launch_bounds__(256) k_build(DevIndex ix, DevBatch b, brb_para
 
 }  // namespace brb
 
-#ifndef VAR_PREFETCH_NEXT
-#define VAR_PREFETCH_NEXT 1
-#endif
 namespace brb {
 
 // ---- short-read specialisation -----------------------------------------------------------------------------
@@ -386,9 +383,7 @@ __device__ __forceinline__ bool eval_short(const DevIndex& ix, const DevBatch& b
   Hit h;
   filter_hit(p, minus, status, qs, qe, (uint32_t)key.st, (uint32_t)key.en, key.pos_start, h);
   const uint32_t first_pos = h.pos; uint32_t last_pos = h.pos;
-#if VAR_PREFETCH_NEXT
   if (n_ex > 1 && lk.gnext != NONE) asm volatile("prefetch.global.L1 [%0];" ::"l"(&ix.rec[lk.gnext]));   // the walk continues there
-#endif
   build_match_short<SIM>(m, status, qs, qe, (uint32_t)key.st, (uint32_t)key.en, h, true, n_ex == 1);
   uint32_t prev_eid = lk.meta & 0xffu;
   for (uint32_t j = 1; j < n_ex; j++) {

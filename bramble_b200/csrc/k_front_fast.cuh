@@ -27,9 +27,6 @@
 #include "k_lookup.cuh"
 #include "k_chain.cuh"
 
-#ifndef VAR_SLOT_POOL
-#define VAR_SLOT_POOL 1
-#endif
 #ifndef VAR_FAST_CTAS
 #define VAR_FAST_CTAS 8
 #endif
@@ -124,7 +121,6 @@ __global__ void __launch_bounds__(256, VAR_FAST_CTAS) k_front_fast(DevIndex ix, 
     }
     const uint32_t n = n0 + n1;
     const uint32_t incl = warp_incl_scan(n, lane), excl = incl - n, total = __shfl_sync(0xffffffffu, incl, 31);
-#if VAR_SLOT_POOL
     // candidate slots come out of a per-warp chunk of the slot space: one atomic per ~2048 slots instead of one per
     // batch (waiting for its return value was 10 % of the kernel's stall samples)
     if (total > sp.end - sp.cur) {
@@ -137,12 +133,6 @@ __global__ void __launch_bounds__(256, VAR_FAST_CTAS) k_front_fast(DevIndex ix, 
     const uint32_t sbase = sp.cur;
     const bool slots_fit = sp.end <= cap_cand && sp.end >= sp.cur;
     sp.cur += total;
-#else
-    uint32_t sbase = 0;
-    if (lane == 31 && total) sbase = atomicAdd(&ctl->n_cand, total);
-    sbase = __shfl_sync(0xffffffffu, sbase, 31);
-    const bool slots_fit = (unsigned long long)sbase + total <= cap_cand;
-#endif
     s_al[0][lane] = rx.qs0; s_al[1][lane] = rx.qe0; s_al[2][lane] = rx.e0; s_al[3][lane] = rx.n_ex;
     s_al[4][lane] = excl; s_al[5][lane] = n0; s_al[6][lane] = lo0; s_al[7][lane] = lo1; s_nv[lane] = 0;
     __syncwarp();

@@ -18,15 +18,6 @@
 #include "k_lookup.cuh"
 #include "k_chain.cuh"
 
-#ifndef VAR_COMPACT
-#define VAR_COMPACT 1
-#endif
-#ifndef VAR_PREFETCH
-#define VAR_PREFETCH 0
-#endif
-#ifndef VAR_FRONT_SMEM
-#define VAR_FRONT_SMEM 1
-#endif
 #ifndef VAR_FRONT_CTAS
 #define VAR_FRONT_CTAS 5
 #endif
@@ -181,22 +172,18 @@ __global__ void __launch_bounds__(256) k_front(DevIndex ix, DevBatch b, brb_para
 // exon chain.  That leaves one flat pass per batch of 32 alignments: bracket the exon-0 range(s) of each lane
 // (both strands side by side), reserve one candidate slot per record of those ranges with a single atomic, then
 // walk the concatenated ranges 32 records at a time; a lane whose record survives the overlap + tolerance
-// filters evaluates that candidate on the spot (eval_short) and writes its match row, every other slot is
-// marked empty.  (n_hits then only counts exon-0 hits; the reference-defined figure for the roofline numerator
+// filters evaluates that candidate on the spot (eval_short); matches are ballot-compacted so that those of an
+// alignment are contiguous.  k_front_fast (k_front_fast.cuh) is this kernel with a fast path for perfectly spliced
+// candidates and is what the default short-read preset runs; this one serves the similarity-filter overrides and
+// the A/B tests (BRB_OPT_NO_FASTPATH).  (n_hits then only counts exon-0 hits; the reference-defined figure for the roofline numerator
 // comes from the generic kernel, see BRB_OPT_GENERIC_FRONT.)
 template <bool SIM>
 __global__ void __launch_bounds__(256, VAR_FRONT_CTAS) k_front_short(DevIndex ix, DevBatch b, brb_params p, Ctl* __restrict__ ctl,
                                                         uint4* __restrict__ a_cand, uint32_t* __restrict__ ipool, Matches M) {
   const unsigned lane = threadIdx.x & 31;
-#if VAR_FRONT_SMEM
   __shared__ uint32_t s_all[8][9][32];
   uint32_t (*s_al)[32] = s_all[threadIdx.x >> 5];
   uint32_t* s_incl = s_al[8]; (void)s_incl;
-#endif
-#if !VAR_COMPACT
-  __shared__ uint32_t s_nvalid[8][32];
-  uint32_t* nval = s_nvalid[threadIdx.x >> 5];
-#endif
   const uint32_t n_batches = (b.n_aln + 31) >> 5;
   const uint32_t cap_cand = ctl->cap_cand, cap_ideal = ctl->cap_ideal;       // constant during the launch
   WarpPool wp; wp.cur = 0; wp.end = 0;
@@ -236,56 +223,26 @@ __global__ void __launch_bounds__(256, VAR_FRONT_CTAS) k_front_short(DevIndex ix
     if (lane == 31 && total) sbase = atomicAdd(&ctl->n_cand, total);
     sbase = __shfl_sync(0xffffffffu, sbase, 31);
     const bool slots_fit = (unsigned long long)sbase + total <= cap_cand;
-#if VAR_FRONT_SMEM
     // per-alignment facts of the batch go through shared memory: a lane fetches those of the alignment that owns
     // its candidate (one LDS each) and they do not sit in registers across the evaluation
     s_al[0][lane] = rx.qs0; s_al[1][lane] = rx.qe0; s_al[2][lane] = rx.e0; s_al[3][lane] = rx.n_ex;
     s_al[4][lane] = excl; s_al[5][lane] = n0; s_al[6][lane] = lo0; s_al[7][lane] = lo1;
-#if VAR_PREFETCH
-    s_incl[lane] = incl;
-#endif
     __syncwarp();
-#else
-    const int status0 = exon_status(rx.n_ex, 0);
-#endif
-#if VAR_COMPACT
     uint32_t nvalid = 0, wr = 0;                            // matches kept for MY alignment / by the batch so far
-#else
-    nval[lane] = 0; __syncwarp();
-#endif
     for (uint32_t base = 0; base < total; base += 32) {
       const uint32_t item = base + lane;
       const bool actv = item < total;
       const unsigned L = warp_owner(incl, actv ? item : total - 1);
       ReadExons ox;
-#if VAR_FRONT_SMEM
       ox.qs0 = s_al[0][L]; ox.qe0 = s_al[1][L]; ox.e0 = s_al[2][L]; ox.n_ex = s_al[3][L];
       const uint32_t o_ex = s_al[4][L], o_n0 = s_al[5][L];
       const int o_status = exon_status(ox.n_ex, 0);
       const uint32_t idx = item - o_ex;
       const int s = idx >= o_n0;
       uint32_t rec0 = s ? s_al[7][L] + (idx - o_n0) : s_al[6][L] + idx;
-#else
-      ox.qs0 = __shfl_sync(0xffffffffu, rx.qs0, L); ox.qe0 = __shfl_sync(0xffffffffu, rx.qe0, L);
-      ox.e0 = __shfl_sync(0xffffffffu, rx.e0, L); ox.n_ex = __shfl_sync(0xffffffffu, rx.n_ex, L);
-      const uint32_t o_ex = __shfl_sync(0xffffffffu, excl, L), o_n0 = __shfl_sync(0xffffffffu, n0, L);
-      const uint32_t o_lo0 = __shfl_sync(0xffffffffu, lo0, L), o_lo1 = __shfl_sync(0xffffffffu, lo1, L);
-      const int o_status = __shfl_sync(0xffffffffu, status0, L);
-      const uint32_t idx = item - o_ex;
-      const int s = idx >= o_n0;
-      uint32_t rec0 = s ? o_lo1 + (idx - o_n0) : o_lo0 + idx;
-#endif
       bool sv = false, ov = false; RecKey key;
       if (actv) {
         key = rec_key(ix.rec, rec0);
-#if VAR_PREFETCH && VAR_FRONT_SMEM
-        if (item + 32 < total) {                             // the record this lane evaluates in the next round: start its fetch now
-          const unsigned L2 = warp_owner_smem(s_incl, item + 32);
-          const uint32_t idx2 = item + 32 - s_al[4][L2], n02 = s_al[5][L2];
-          const uint32_t r2 = idx2 >= n02 ? s_al[7][L2] + (idx2 - n02) : s_al[6][L2] + idx2;
-          asm volatile("prefetch.global.L1 [%0];" ::"l"(&ix.rec[r2]));
-        }
-#endif
         ov = (int32_t)ox.qs0 < key.en;                     // st < qe holds for every record below hi
         sv = ov && passes_filter(p, s, o_status, ox.qs0, ox.qe0, (uint32_t)key.st, (uint32_t)key.en);
       }
@@ -293,7 +250,6 @@ __global__ void __launch_bounds__(256, VAR_FRONT_CTAS) k_front_short(DevIndex ix
       const uint32_t want = sv ? 3 * ox.n_ex : 0;           // at most S/I/D + M + S/I/D per read exon
       bool pool_fit;
       const uint32_t ioff = warp_pool_alloc(wp, &ctl->n_ideal, cap_ideal, want, lane, pool_fit);
-#if VAR_COMPACT
       bool ok = false; uint32_t pos = 0, ilen = 0, word = 0; double sim = 0.0;
       if (sv && pool_fit && slots_fit) {
         RecLink lk = rec_link(ix.rec, rec0);
@@ -320,31 +276,6 @@ __global__ void __launch_bounds__(256, VAR_FRONT_CTAS) k_front_short(DevIndex ix
     const uint32_t first = sbase + warp_incl_scan(nvalid, lane) - nvalid;
     if (a < b.n_aln) a_cand[a] = make_uint4(first, nvalid, nvalid, 0);
   }
-#else
-      if (!actv || !slots_fit) continue;
-      const uint32_t slot = sbase + item;
-      bool ok = false; uint32_t pos = 0, ilen = 0, word = 0; double sim = 0.0;
-      if (sv && pool_fit) {
-        RecLink lk = rec_link(ix.rec, rec0);
-        ok = true;
-        if (lk.gprev_en > (int32_t)ox.qs0 || lk.gnext_st < (int32_t)ox.qe0) {      // a neighbour exon of this tid also overlaps read exon 0
-          const uint32_t r1 = rec0;
-          ok = dedupe_first(ix, p, ox, s, rec0);
-          if (ok && rec0 != r1) { key = rec_key(ix.rec, rec0); lk = rec_link(ix.rec, rec0); }
-        }
-        if (ok) ok = eval_short<SIM>(ix, b, p, ox, s, key, lk, ipool + ioff, pos, ilen, word, sim);
-      }
-      if (ok) {
-        M.rec[slot] = make_uint4(pos, (ilen << 1) | (uint32_t)s, ilen == 1 ? word : ioff, key.tid);
-        if (SIM) { M.sim[slot] = sim; M.clip[slot] = 0; }
-        kept++; atomicAdd(&nval[L], 1u);
-      } else M.rec[slot].w = NONE;
-    }
-    __syncwarp();
-    if (a < b.n_aln) a_cand[a] = make_uint4(sbase + excl, n, nval[lane], 0);
-    __syncwarp();
-  }
-#endif
   for (int d = 16; d; d >>= 1) { my_hits += __shfl_down_sync(0xffffffffu, my_hits, d); kept += __shfl_down_sync(0xffffffffu, kept, d);
                                  n_mates += __shfl_down_sync(0xffffffffu, n_mates, d); }
   if (lane == 0) {
