@@ -212,9 +212,12 @@ def main():
     eng.upload(B)
     # algorithmic bytes are defined on the reference's algorithm, which looks up EVERY read exon: take
     # them once, untimed, from the generic front kernel; the timed path is the engine's default choice
+    checks = {}
     eng.set_option(capi.OPT_GENERIC_FRONT, 1)
     eng.run_resident(p)
     alg_ref, alg_front = int(eng.stats().alg_bytes), int(eng.stats().alg_bytes_front)
+    if not args.no_e2e:       # full-size parity property: every engine variant must produce the same row set (order-independent checksum)
+        checks["generic_front"] = engine.rows_checksum(eng.download(B, raw=True))
     eng.set_option(capi.OPT_GENERIC_FRONT, 0)
     for _ in range(max(3, args.warmup)):
         eng.run_resident(p)
@@ -245,8 +248,10 @@ def main():
         for _ in range(args.steps):
             eng.run_resident(p)
         ms_ordered = eng.timer_stop()
+        checks["ordered_rows"] = engine.rows_checksum(eng.download(B, raw=True))
         eng.set_option(capi.OPT_ORDERED_ROWS, 0)
         eng.run_resident(p)
+        checks["default"] = engine.rows_checksum(eng.download(B, raw=True))
     barrier()
     st = eng.stats()
     # ---- end to end through the C ABI with pinned host columns: the step's alignments as `--e2e-bundles` bundles
@@ -261,8 +266,9 @@ def main():
         cuts = [G * i // nbun for i in range(nbun + 1)]
         PBs = [eng.pinned_copy(B.slice_groups(g0, g1)) for g0, g1 in zip(cuts[:-1], cuts[1:])]
         ctxs = [eng.context() for _ in range(max(1, args.e2e_contexts))]
-        for _ in range(2):
-            engine.project_pipelined(ctxs, p, PBs)
+        engine.project_pipelined(ctxs, p, PBs)
+        res = engine.project_pipelined(ctxs, p, PBs, checksum=True)
+        checks["e2e_bundles"] = (sum(r[4] for r in res) & 0xFFFFFFFFFFFFFFFF, sum(r[0] for r in res))
         barrier()
         t0 = time.perf_counter()
         for _ in range(args.steps):
@@ -320,6 +326,11 @@ def main():
                              "ordered_rows": None if ms_ordered is None else {"ms_per_step": ms_ordered / args.steps, "frac": alg / (ms_ordered / args.steps / 1e3) / 1e9 / peak,
                                               "what": "rank 0, BRB_OPT_ORDERED_ROWS=1: rows moved into emit order on the device (scan + k_place + k_group_rows) "
                                                       "instead of unit blocks + aln_rec_off/aln_rec_cnt"}},
+                "parity_at_bench_size": None if not checks else {
+                    "property": "order-independent checksum of all rows (source alignment, tid, pos, strand, flags, CIGAR) and row count agree between "
+                                "the default kernels, the generic front kernel, BRB_OPT_ORDERED_ROWS and the 8-bundle / 3-context end-to-end path (rank 0)",
+                    "rows": checks["default"][1], "checksum": "%016x" % checks["default"][0],
+                    "agree": len({(int(c[0]), int(c[1])) for c in checks.values()}) == 1},
                 "work": {"alignments_per_gpu": n_aln, "candidates": int(st.n_candidates), "matches": int(st.n_matches), "records": int(st.n_rec)}}
         if args.gpus == 1 and not args.no_cpu_baseline:
             try:

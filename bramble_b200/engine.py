@@ -66,10 +66,32 @@ class Context:
             self._ctx = C.c_void_p()
 
 
-def project_pipelined(contexts, params, bundles, raw=True):
+def rows_checksum(o, src_offset=0):
+    """Order-independent 64-bit checksum of the rows of a raw brb_batch_out (sum of a per-row mix of source alignment,
+    tid, pos, strand, flags, CIGAR length and CIGAR words): equal for any layout of the same row set."""
+    n = int(o.n_rec)
+    if n == 0:
+        return 0, 0
+    def arr(p, cnt):
+        return np.ctypeslib.as_array(p, shape=(cnt,))
+    M = np.uint64(0x9E3779B97F4A7C15)
+    with np.errstate(over="ignore"):
+        co = arr(o.cigar_off, n + 1).astype(np.uint64)
+        pool = arr(o.cigar, int(o.n_cigar_words)).astype(np.uint64)
+        wsum = np.concatenate([[np.uint64(0)], np.cumsum(pool * M + (pool >> np.uint64(7)), dtype=np.uint64)])
+        h = (arr(o.src_aln, n).astype(np.uint64) + np.uint64(src_offset)) * M
+        h ^= arr(o.tid, n).astype(np.uint64) * np.uint64(0xC2B2AE3D27D4EB4F)
+        h = h * M + arr(o.pos, n).astype(np.uint64)
+        h = h * M + (arr(o.tx_strand, n).astype(np.uint64) << np.uint64(8)) + arr(o.flags, n).astype(np.uint64)
+        h = h * M + (co[1:] - co[:-1])
+        h = h * M + (wsum[co[1:].astype(np.int64)] - wsum[co[:-1].astype(np.int64)])
+        return int(h.sum(dtype=np.uint64)), n
+
+
+def project_pipelined(contexts, params, bundles, raw=True, checksum=False):
     """Bundles through `contexts` (one host thread each, ctypes releases the GIL): results in bundle order.
     A context's result arrays are only valid until its next call, so raw results have to be consumed by
-    the caller before that; with raw=True they are reduced here to (n_rec, n_cigar_words, h2d_bytes, d2h_bytes)."""
+    the caller before that; with raw=True they are reduced here to (n_rec, n_cigar_words, h2d_bytes, d2h_bytes, rows_checksum or 0)."""
     from concurrent.futures import ThreadPoolExecutor
     import queue
     free = queue.SimpleQueue()
@@ -83,7 +105,8 @@ def project_pipelined(contexts, params, bundles, raw=True):
             if not raw:
                 return o
             st = c.stats()
-            return (int(o.n_rec), int(o.n_cigar_words), int(st.h2d_bytes), int(st.d2h_bytes))
+            cs = rows_checksum(o, b.src_offset)[0] if checksum else 0
+            return (int(o.n_rec), int(o.n_cigar_words), int(st.h2d_bytes), int(st.d2h_bytes), cs)
         finally:
             free.put(c)
     with ThreadPoolExecutor(max_workers=len(contexts)) as ex:

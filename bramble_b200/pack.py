@@ -215,6 +215,7 @@ class Batch:
         self.desc = capi.BatchIn()
         self.arrays = {}
         self.src = None
+        self.src_offset = 0
         self.names = []
 
     def finish(self, refid, strand, flag, exon_off, exon_st, exon_en, cigar_off, cigar, mate, group_off, seq_off, seq_codes, src, names):
@@ -263,6 +264,7 @@ class Batch:
         B["cigar"] = np.ascontiguousarray(A["cigar"][co[a0]:co[a1]])
         B["mate_idx"] = np.where(mate >= 0, mate - a0, -1).astype(np.int32)
         B["group_off"] = (go[g0:g1 + 1] - a0).astype(np.uint32)
+        nb.src_offset = a0                                   # alignment index of the slice's first alignment in the parent
         nb.src = self.src[a0:a1] if self.src is not None and len(self.src) else None
         nb.names = self.names[g0:g1] if self.names else []
         d = nb.desc

@@ -93,6 +93,32 @@ def test_contexts_in_parallel():
                 c.close()
 
 
+def test_rows_checksum_matches_oracle():
+    """bench.py's full-size parity property: the order-independent row checksum of the engine's output (both row layouts,
+    bundle slices through parallel contexts) equals the oracle's on the same bundle."""
+    import ctypes as C
+    wl = common.make_workload("default", 47, n_names=3000)
+    ix, p, b = wl["index"], wl["params"], wl["batches"][0]
+    o = oracle_lib.PortOut()
+    assert oracle_lib.port().brb_port_project(C.byref(ix.desc), C.byref(p), C.byref(b.desc), C.byref(o)) == 0
+    want = engine.rows_checksum(o)
+    oracle_lib.port().brb_port_free(C.byref(o))
+    assert want[1] > 1000
+    G = b.desc.n_groups
+    parts = [b.slice_groups(G * i // 5, G * (i + 1) // 5) for i in range(5)]
+    with engine.Engine(ix) as eng:
+        for ordered in (0, 1):
+            eng.set_option(capi.OPT_ORDERED_ROWS, ordered)
+            assert engine.rows_checksum(eng.project(p, b, raw=True)) == want
+        ctxs = [eng.context() for _ in range(2)]
+        try:
+            res = engine.project_pipelined(ctxs, p, parts, checksum=True)
+            assert (sum(r[4] for r in res) & 0xFFFFFFFFFFFFFFFF, sum(r[0] for r in res)) == want
+        finally:
+            for c in ctxs:
+                c.close()
+
+
 def test_multiple_bundles_and_ragged():
     wl = common.make_workload("default", 41, n_names=3000, chunk_size=700)
     assert len(wl["batches"]) > 3
