@@ -86,19 +86,28 @@ def _traffic(names):
         return None, None, None
 
 
-def workload(seed, names):
+def workload(seed, names, kind="c2"):
+    """c2 (default, the configuration the metric is quoted on): stranded paired-end reads.  c5: the multi-mapping stress
+    shape of BASELINE.json configs[4] -- unstranded (both strand tables searched), 1 + Geometric(5) fragments per read
+    name capped at 50 (many secondary alignments, large name groups)."""
     from bramble_b200 import synth_fast as sf
     A = sf.make_annotation(2002)
     ix = sf.build_index(A)
-    B = sf.make_short_batch(A, ix, seed, names, stranded="fr")
+    if kind == "c5":
+        B = sf.make_short_batch(A, ix, seed, names, stranded=None, multi_mean=5.0)
+    else:
+        B = sf.make_short_batch(A, ix, seed, names, stranded="fr")
     return A, ix, B
 
 
-def ref_cmd(cores):
-    return ["--fr", "-p", str(max(1, min(cores, 255)))]
+WORKLOAD_FLAGS = {"c2": ["--fr"], "c5": []}
 
 
-def time_reference(A, ix, B, n_small, n_big, cores, repeats=1, binary=None, extra=()):
+def ref_cmd(cores, kind="c2"):
+    return WORKLOAD_FLAGS[kind] + ["-p", str(max(1, min(cores, 255)))]
+
+
+def time_reference(A, ix, B, n_small, n_big, cores, repeats=1, binary=None, extra=(), kind="c2"):
     """Reference C++ (oracle/_ref/bramble_ref, unmodified sources) on a bounded sample of the same
     workload.  Throughput is MARGINAL: (aln_big - aln_small) / (t_big - t_small), which removes the GTF
     load + index build the reference pays once per run.  BGZF level 1 for the output, all host cores."""
@@ -122,7 +131,7 @@ def time_reference(A, ix, B, n_small, n_big, cores, repeats=1, binary=None, extr
             wd = tempfile.mkdtemp(dir=d)
             env = dict(os.environ, BRB_SHIM_LEVEL="1")
             t0 = time.perf_counter()
-            r = subprocess.run([ref, bam, "-G", os.path.join(d, "a.gtf"), "-o", os.path.join(wd, "out.bam"), "--quiet"] + ref_cmd(cores) + list(extra),
+            r = subprocess.run([ref, bam, "-G", os.path.join(d, "a.gtf"), "-o", os.path.join(wd, "out.bam"), "--quiet"] + ref_cmd(cores, kind) + list(extra),
                                cwd=wd, env=env, capture_output=True, text=True)
             dt = time.perf_counter() - t0
             if r.returncode != 0:
@@ -130,7 +139,9 @@ def time_reference(A, ix, B, n_small, n_big, cores, repeats=1, binary=None, extr
             best = dt if best is None else min(best, dt)
         out.append((n_aln, best))
     (a0, t0), (a1, t1) = out
-    rate = (a1 - a0) / max(1e-9, (t1 - t0))
+    if t1 - t0 < 0.05:
+        return None                                   # the sample is too small to resolve a marginal rate
+    rate = (a1 - a0) / (t1 - t0)
     return dict(value=rate, n_aln=a1 - a0, seconds=t1 - t0, startup_s=t0, sample=f"first {n_big} read names ({a1} alignments) of the rank-0 shard, "
                 f"marginal over a {n_small}-name run (startup {t0:.1f}s excluded), BAM in -> BAM out, BGZF level 1")
 
@@ -144,6 +155,7 @@ def main():
     ap.add_argument("--names", type=int, default=2_000_000)
     ap.add_argument("--ref-names", type=int, default=150_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="c2", choices=["c2", "c5"], help="c2: the metric's configuration (default); c5: multi-mapping stress shape")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs: resident steps only (also skips the ordered-rows leg)")
     ap.add_argument("--e2e-bundles", type=int, default=8, help="bundles per step on the end-to-end path")
     ap.add_argument("--e2e-contexts", type=int, default=3, help="brb_ctx (host threads / streams) on the end-to-end path")
@@ -154,18 +166,23 @@ def main():
     cores = os.cpu_count() or 1
     unit = "alignments/s"
     metric = "projected alignments/sec (input BAM records consumed)"
-    config = {"workload": "C2: synthetic GENCODE-shaped GTF (252,687 transcripts, 2.24M exons, 25 chromosomes) + --fr paired-end "
-                          f"150bp name-collated reads, {args.names} read names per GPU", "flags": "--fr", "names_per_gpu": args.names,
+    if args.workload == "c5" and args.names == 2_000_000:
+        args.names = 400_000                  # ~10 alignments per name: about the same alignments per GPU as c2
+    if args.workload == "c5" and args.ref_names == 150_000:
+        args.ref_names = 30_000
+    shape = {"c2": "C2: synthetic GENCODE-shaped GTF (252,687 transcripts, 2.24M exons, 25 chromosomes) + --fr paired-end 150bp name-collated reads",
+             "c5": "C5 shape: the same annotation + unstranded paired-end 150bp reads, 1+Geometric(5) fragments per read name (cap 50)"}[args.workload]
+    config = {"workload": f"{shape}, {args.names} read names per GPU", "flags": " ".join(WORKLOAD_FLAGS[args.workload]) or "(default)", "names_per_gpu": args.names,
               "l2": "inputs + intermediates (>1 GB per step) exceed the 126 MB L2"}
 
     if args.impl == "reference":
         if rank != 0:
             return
-        A, ix, B = workload(1000, max(args.ref_names, 2000))
+        A, ix, B = workload(1000, max(args.ref_names, 2000), args.workload)
         vals = []
         res = None
         for _ in range(max(1, min(args.steps, 3))):
-            res = time_reference(A, ix, B, 2000, args.ref_names, cores)
+            res = time_reference(A, ix, B, 2000, args.ref_names, cores, kind=args.workload)
             if res is None:
                 print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/bramble_ref not built (reference sources absent)"}))
                 return
@@ -197,7 +214,7 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     torch.cuda.set_device(local)
-    A, ix, B = workload(1000 + rank, args.names)
+    A, ix, B = workload(1000 + rank, args.names, args.workload)
     n_aln = int(B.desc.n_aln)
     p = capi.resolve_params()            # --fr only affects ingest (strand column), thresholds are the short-read preset
     eng = engine.Engine(ix, device=local)
@@ -304,7 +321,7 @@ def main():
                  "ms_pair": "k_back (pairing + CIGAR merge + rows)", "ms_merge": "k_back_finish (totals)",
                  "ms_rescue": "k_ksw (rescue path only)"}
         top = max(phase, key=lambda k: phase[k])
-        traffic, traffic_by_kernel, traffic_src = _traffic(args.names)
+        traffic, traffic_by_kernel, traffic_src = _traffic(args.names if args.workload == "c2" else -1)
         alg_of = {"ms_lookup": alg_front, "ms_pair": alg - alg_front, "ms_merge": alg - alg_front}
         top_ms = phase[top] / args.steps
         top_alg = alg_of.get(top, alg)
@@ -334,7 +351,7 @@ def main():
                 "work": {"alignments_per_gpu": n_aln, "candidates": int(st.n_candidates), "matches": int(st.n_matches), "records": int(st.n_rec)}}
         if args.gpus == 1 and not args.no_cpu_baseline:
             try:
-                res = time_reference(A, ix, B, 2000, args.ref_names, cores)
+                res = time_reference(A, ix, B, 2000, args.ref_names, cores, kind=args.workload)
             except Exception as e:     # the baseline is a reported number, never a reason to lose the bench line
                 res = None
                 line["cpu_baseline_error"] = str(e)[:200]
@@ -343,7 +360,8 @@ def main():
             # the drop-in CLI (host C++: BGZF/BAM decode, ingest, flush replay, record assembly, BGZF encode; CUDA engine
             # through the C ABI) on the same BAM sample, same flags: end to end INCLUDING BGZF, marginal rate like the reference
             try:
-                cli = time_reference(A, ix, B, 2000, args.ref_names, cores, binary=g.build_cli(), extra=["--level", "1"])
+                cli_names = min(3 * args.ref_names, int(B.desc.n_groups))      # a larger sample: the CLI needs several bundles in flight
+                cli = time_reference(A, ix, B, 2000, cli_names, cores, binary=g.build_cli(), extra=["--level", "1"], kind=args.workload)
                 if cli:
                     line["cli_e2e"] = {"value": cli["value"], "unit": unit, "sample": cli["sample"], "host_threads": min(cores, 255),
                                        "what": "bramble_b200_cli BAM in -> BAM out (1 GPU), marginal over a 2000-name run"}
