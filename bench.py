@@ -37,14 +37,46 @@ def _peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    """SM clock / throttle reasons sampled DURING the timed region: NVML polled every millisecond (the timed region
+    of the resident leg is ~10 ms, shorter than one nvidia-smi call), nvidia-smi as the fallback."""
 
     def __init__(self, gpu):
-        self.gpu, self.rows, self.stop_flag, self.th = gpu, [], False, None
+        self.gpu, self.rows, self.stop_flag, self.th, self.how = gpu, [], False, None, None
 
-    def _run(self):
+    def _nvml_open(self):
+        import pynvml as nv
+        nv.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            ent = vis.split(",")[self.gpu].strip()
+            h = nv.nvmlDeviceGetHandleByIndex(int(ent)) if ent.isdigit() else nv.nvmlDeviceGetHandleByUUID(ent)
+        else:
+            h = nv.nvmlDeviceGetHandleByIndex(self.gpu)
+        self.nv, self.h, self.mx = nv, h, nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+        self._nvml_sample()              # the first call pays the set-up; it is made before the timed region starts
+        self.rows.clear()
+        self.how = "nvml, polled back to back"
+
+    def _nvml_sample(self):
+        nv, h = self.nv, self.h
+        bits = [(nv.nvmlClocksEventReasonHwSlowdown, 0), (nv.nvmlClocksEventReasonHwThermalSlowdown, 1),
+                (nv.nvmlClocksEventReasonSwThermalSlowdown, 2), (nv.nvmlClocksEventReasonSwPowerCap, 3)]
+        r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+        row = [str(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)), str(self.mx), "", "", "", ""]
+        for b, i in bits:
+            if r & b:
+                row[2 + i] = "active"
+        self.rows.append(row)
+
+    def _nvml(self):
+        while not self.stop_flag:
+            self._nvml_sample()
+            time.sleep(0.0005)
+
+    def _smi(self):
         q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        self.how = "nvidia-smi, 0.1 s period"
         while not self.stop_flag:
             try:
                 o = subprocess.run(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={q}", "--format=csv,noheader,nounits"],
@@ -54,6 +86,22 @@ class ClockSampler:
             except Exception:
                 pass
             time.sleep(0.1)
+
+    def prepare(self):
+        """Open NVML (before the barrier that starts the timed region); nvidia-smi is used when that fails."""
+        try:
+            self._nvml_open()
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        if getattr(self, "nv", None) is not None:
+            try:
+                self._nvml()
+                return
+            except Exception:
+                pass
+        self._smi()
 
     def start(self):
         self.th = threading.Thread(target=self._run, daemon=True)
@@ -67,7 +115,8 @@ class ClockSampler:
         mx = max([int(r[1]) for r in self.rows if r[1].isdigit()] or [0])
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = sorted({names[i] for r in self.rows for i in range(4) if len(r) >= 6 and r[2 + i].lower().startswith("active")})
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": reasons, "samples": len(sm)}
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": reasons, "samples": len(sm),
+                "how": self.how}
 
 
 def _traffic(names):
@@ -158,6 +207,7 @@ def main():
     ap.add_argument("--workload", default="c2", choices=["c2", "c5"], help="c2: the metric's configuration (default); c5: multi-mapping stress shape")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs: resident steps only (also skips the ordered-rows leg)")
     ap.add_argument("--e2e-bundles", type=int, default=8, help="bundles per step on the end-to-end path")
+    ap.add_argument("--no-bind", action="store_true", help="N>1: do not pin each rank to the CPUs of its GPU's NUMA node")
     ap.add_argument("--e2e-contexts", type=int, default=3, help="brb_ctx (host threads / streams) on the end-to-end path")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -214,6 +264,10 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     torch.cuda.set_device(local)
+    from bramble_b200 import hostbind
+    # one process per GPU: keep the rank's threads and its pinned staging pages on the GPU's NUMA node
+    host = hostbind.bind_to_gpu_node(local) if (world > 1 and not args.no_bind) else hostbind.describe(local)
+    host["cpus"] = os.cpu_count()
     A, ix, B = workload(1000 + rank, args.names, args.workload)
     n_aln = int(B.desc.n_aln)
     p = capi.resolve_params()            # --fr only affects ingest (strand column), thresholds are the short-read preset
@@ -240,19 +294,23 @@ def main():
         eng.run_resident(p)
     st = eng.stats()
     sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.prepare()
     barrier()
     if rank == 0:
         sampler.start()
     phase = {k: 0.0 for k in ("ms_lookup", "ms_chain", "ms_rescue", "ms_finalize", "ms_pair", "ms_merge")}
     eng.timer_start()
     launches = 0
-    for _ in range(args.steps):
+    per_step = []
+    for _ in range(args.steps):           # nothing but the call and one struct copy between steps: the GPU idles while the host is busy
         eng.run_resident(p)
-        s = eng.stats()
+        per_step.append(eng.stats())
+    ms = eng.timer_stop()
+    for s in per_step:
         launches += int(s.n_launches)
         for k in phase:
             phase[k] += getattr(s, k)
-    ms = eng.timer_stop()
     barrier()
     clocks = sampler.stop() if rank == 0 else None
     # the same with BRB_OPT_ORDERED_ROWS: one more streaming pass (scan + k_place) lays the rows out in emit order on the device
@@ -309,6 +367,13 @@ def main():
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
     total_aln = float(t[2].item()) if world > 1 else float(n_aln)
+    by_rank = [torch.zeros(3, dtype=torch.float64, device=f"cuda:{local}") for _ in range(world)]
+    mine = torch.tensor([e2e_s * 1e3 / max(1, args.steps), float(host["numa_node"] if host["numa_node"] is not None else -1),
+                         float(host["cpus_allowed"])], dtype=torch.float64, device=f"cuda:{local}")
+    if world > 1:
+        dist.all_gather(by_rank, mine)
+    else:
+        by_rank = [mine]
     ms_max, e2e_ms_max = float(tmax[0].item()), float(tmax[1].item())
     if rank == 0:
         peak, peak_src = _peaks()
@@ -318,7 +383,7 @@ def main():
         alg = alg_ref
         achieved = alg / (ms / args.steps / 1e3) / 1e9
         names = {"ms_lookup": "k_front_fast (lookup + evaluate)", "ms_chain": "k_chain (rescue path only)", "ms_finalize": "k_build (rescue path only)",
-                 "ms_pair": "k_back (pairing + CIGAR merge + rows)", "ms_merge": "k_back_finish (totals)",
+                 "ms_pair": "k_back (pairing + CIGAR merge + rows)", "ms_merge": "scan + k_place + k_group_rows (BRB_OPT_ORDERED_ROWS only)",
                  "ms_rescue": "k_ksw (rescue path only)"}
         top = max(phase, key=lambda k: phase[k])
         traffic, traffic_by_kernel, traffic_src = _traffic(args.names if args.workload == "c2" else -1)
@@ -348,6 +413,8 @@ def main():
                                 "the default kernels, the generic front kernel, BRB_OPT_ORDERED_ROWS and the 8-bundle / 3-context end-to-end path (rank 0)",
                     "rows": checks["default"][1], "checksum": "%016x" % checks["default"][0],
                     "agree": len({(int(c[0]), int(c[1])) for c in checks.values()}) == 1},
+                "host": {**host, "e2e_ms_per_step_by_rank": [round(float(x[0].item()), 3) for x in by_rank],
+                         "numa_node_by_rank": [int(x[1].item()) for x in by_rank], "cpus_allowed_by_rank": [int(x[2].item()) for x in by_rank]},
                 "work": {"alignments_per_gpu": n_aln, "candidates": int(st.n_candidates), "matches": int(st.n_matches), "records": int(st.n_rec)}}
         if args.gpus == 1 and not args.no_cpu_baseline:
             try:

@@ -63,8 +63,21 @@ struct Ctl {
   uint32_t n_outw, cap_outw;          // dense output CIGAR words
   uint32_t bad_input;                 // 1: mate link not symmetric, 2: read exons not ascending/disjoint, 3: >= 2^28 CIGAR words in one batch of 32 alignments
   uint32_t ticket;                    // next batch of 32 alignments for k_front (dynamic scheduling)
-  uint32_t ticket_a, ticket_b;        // same for k_pair_a / k_pair_b
+  uint32_t ticket_a, ticket_b;        // k_back: next batch; CTAs that have left (the last one publishes the totals)
 };
+// End of a kernel sequence, ONE thread, every other writer of `ctl` done and fenced: hand the counters to the host
+// through mapped pinned memory (no separate copy operation on the stream) and leave `ctl` ready for the next
+// sequence of the same pool capacities (counters and tickets zero, caps kept), so that a steady-state step needs no
+// host->device initialisation either.
+__device__ __forceinline__ void ctl_publish_and_reset(Ctl* ctl, Ctl* host_result) {
+  static_assert(sizeof(Ctl) % 8 == 0, "Ctl is copied in 8-byte words");
+  volatile unsigned long long* s = reinterpret_cast<volatile unsigned long long*>(ctl);
+  volatile unsigned long long* d = reinterpret_cast<volatile unsigned long long*>(host_result);
+  const uint32_t cc = ctl->cap_cand, ci = ctl->cap_ideal, cr = ctl->cap_rows, ct = ctl->cap_tmpw, co = ctl->cap_outw;
+  for (uint32_t i = 0; i < sizeof(Ctl) / 8; i++) { d[i] = s[i]; s[i] = 0ull; }
+  ctl->cap_cand = cc; ctl->cap_ideal = ci; ctl->cap_rows = cr; ctl->cap_tmpw = ct; ctl->cap_outw = co;
+  __threadfence_system();
+}
 __device__ __forceinline__ bool ctl_overflow(const Ctl* c) {
   return c->n_cand > c->cap_cand || c->n_ideal > c->cap_ideal || c->n_rows > c->cap_rows || c->n_tmpw > c->cap_tmpw ||
          c->n_outw > c->cap_outw || c->bad_input != 0;

@@ -81,6 +81,10 @@ struct brb_ctx {
   brb_index* idx = nullptr;
   cudaStream_t st = nullptr;
   cudaEvent_t ev[8]{};
+  bool ctl_clean = false;           // the device Ctl holds zero counters and ctl_caps (left so by the last sequence's publisher)
+  uint32_t ctl_caps[5]{};
+  int n_sm = 0;                     // cached launch geometry: SM count and resident CTAs per kernel entry
+  std::vector<std::pair<const void*, int>> resident_cache;
   cudaEvent_t tev[2]{};
   // resident batch
   DevBatch b{};
@@ -264,7 +268,7 @@ int brb_ctx_create(brb_index* ix, brb_ctx** out) {
   CU(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));
   for (auto& e : c->ev) CU(cudaEventCreate(&e));
   for (auto& e : c->tev) CU(cudaEventCreate(&e));
-  ENS(c->ctl, sizeof(Ctl)); ENS(c->h_small, 256);
+  ENS(c->ctl, sizeof(Ctl)); ENS(c->h_small, 1024);      // host images of Ctl: [0] initialisation, [512] result
   *out = c;
   return BRB_OK;
 }
@@ -389,10 +393,14 @@ int project_resident(brb_ctx* c, const brb_params& p) {
     c->cap_outw = grown((uint64_t)3 * c->cap_rows + b.n_cigar);
     if (getenv("BRB_TEST_SMALL_POOLS")) c->cap_cand = c->cap_rows = c->cap_ideal = c->cap_tmpw = c->cap_outw = 64;   // tests: force the grow-and-replay path
   }
-  int n_sm = 148;
-  { int sm = 0; if (cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, c->idx->device) == cudaSuccess && sm > 0) n_sm = sm; }
+  if (!c->n_sm) { int sm = 0; c->n_sm = (cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, c->idx->device) == cudaSuccess && sm > 0) ? sm : 148; }
+  const int n_sm = c->n_sm;
   const int ncta = n_sm * 8;
-  auto resident = [&](const void* kern) { int nb = 0; if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, 256, 0) != cudaSuccess || nb < 1) nb = 1; return n_sm * nb; };
+  auto resident = [&](const void* kern) {
+    for (auto& e : c->resident_cache) if (e.first == kern) return e.second;
+    int nb = 0; if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, 256, 0) != cudaSuccess || nb < 1) nb = 1;
+    c->resident_cache.emplace_back(kern, n_sm * nb); return n_sm * nb;
+  };
   // short-read presets: only exon 0 is looked up, candidates verify the later exons themselves (k_front_short)
   const bool short_front = !p.long_reads && !p.ignore_small_exons && !rescue && !c->opt_generic_front;
   const bool fast_front = short_front && !p.filter_by_similarity && !c->opt_no_fastpath;
@@ -403,29 +411,38 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   const bool ordered = c->opt_ordered;
   const int ncta_back = resident(ordered ? (const void*)k_back<true> : (const void*)k_back<false>);
   Ctl* ctl = c->ctl.as<Ctl>();
-  Ctl* hctl = c->h_small.as<Ctl>();
+  static_assert(sizeof(Ctl) <= 512, "two Ctl images in h_small");
+  Ctl* hctl = c->h_small.as<Ctl>();                                               // initialisation image (host -> device)
+  Ctl* hres = reinterpret_cast<Ctl*>(c->h_small.as<char>() + 512);                // result image (written by the device)
   uint64_t L = 0;
+  bool one_front = false, back_finishes = false;      // which phase events this sequence recorded
   for (int attempt = 0;; attempt++) {
     if (attempt > 12) return fail(BRB_E_NOMEM, "pool sizing did not converge");
     { int r = ensure_pools(c, rescue); if (r) return r; }
-    memset(hctl, 0, sizeof(Ctl));
-    hctl->cap_cand = c->cap_cand; hctl->cap_ideal = c->cap_ideal; hctl->cap_rows = c->cap_rows; hctl->cap_tmpw = c->cap_tmpw; hctl->cap_outw = c->cap_outw;
-    CU(cudaMemcpyAsync(ctl, hctl, sizeof(Ctl), cudaMemcpyHostToDevice, st));
+    const uint32_t caps[5] = {c->cap_cand, c->cap_ideal, c->cap_rows, c->cap_tmpw, c->cap_outw};
+    if (!c->ctl_clean || memcmp(caps, c->ctl_caps, sizeof(caps)) != 0) {          // steady state: the previous sequence left Ctl ready
+      memset(hctl, 0, sizeof(Ctl));
+      hctl->cap_cand = c->cap_cand; hctl->cap_ideal = c->cap_ideal; hctl->cap_rows = c->cap_rows; hctl->cap_tmpw = c->cap_tmpw; hctl->cap_outw = c->cap_outw;
+      CU(cudaMemcpyAsync(ctl, hctl, sizeof(Ctl), cudaMemcpyHostToDevice, st));
+      memcpy(c->ctl_caps, caps, sizeof(caps));
+    }
+    c->ctl_clean = false;
     Matches M; M.rec = c->m_rec.as<uint4>();
     M.sim = c->have_scores ? c->m_sim.as<double>() : nullptr; M.clip = c->have_scores ? c->m_clip.as<int32_t>() : nullptr;
     // ---- phase 1: lookup + candidate lists
     CU(cudaEventRecord(c->ev[0], st));
+    one_front = false; back_finishes = false;
     // ---- phases 1..4: lookup, candidates, chain walk, (clip rescue), ideal CIGAR + scores
     if (short_front) {
       if (fast_front) k_front_fast<<<ncta_front, 256, 0, st>>>(ix, b, p, ctl, c->a_cand.as<uint4>(), c->ipool.as<uint32_t>(), M);
       else if (p.filter_by_similarity) k_front_short<true><<<ncta_front, 256, 0, st>>>(ix, b, p, ctl, c->a_cand.as<uint4>(), c->ipool.as<uint32_t>(), M);
       else k_front_short<false><<<ncta_front, 256, 0, st>>>(ix, b, p, ctl, c->a_cand.as<uint4>(), c->ipool.as<uint32_t>(), M);
       L++;
-      CU(cudaEventRecord(c->ev[1], st)); CU(cudaEventRecord(c->ev[2], st)); CU(cudaEventRecord(c->ev[3], st)); CU(cudaEventRecord(c->ev[4], st));
+      CU(cudaEventRecord(c->ev[1], st)); one_front = true;
     } else if (!rescue) {
       k_front<true><<<ncta_front, 256, 0, st>>>(ix, b, p, ctl, c->q_any.as<uint8_t>(), c->a_cand.as<uint4>(), nullptr, nullptr,
                                           c->ipool.as<uint32_t>(), M); L++;
-      CU(cudaEventRecord(c->ev[1], st)); CU(cudaEventRecord(c->ev[2], st)); CU(cudaEventRecord(c->ev[3], st)); CU(cudaEventRecord(c->ev[4], st));
+      CU(cudaEventRecord(c->ev[1], st)); one_front = true;
     } else {
       k_front<false><<<ncta_front, 256, 0, st>>>(ix, b, p, ctl, c->q_any.as<uint8_t>(), c->a_cand.as<uint4>(), c->c_rec.as<uint32_t>(), c->c_task.as<uint32_t>(),
                                            nullptr, M); L++;
@@ -434,11 +451,11 @@ int project_resident(brb_ctx* c, const brb_params& p) {
       F.nguide = c->c_nguide.as<uint32_t>(); F.cap = c->c_cap.as<uint32_t>();
       k_chain<<<ncta, 256, 0, st>>>(ix, b, p, ctl, c->q_any.as<uint8_t>(), c->c_rec.as<uint32_t>(), c->c_task.as<uint32_t>(), F); L++;
       CU(cudaEventRecord(c->ev[2], st));
-      CU(cudaMemcpyAsync(hctl, ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, st));
+      CU(cudaMemcpyAsync(hres, ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, st));
       CU(cudaStreamSynchronize(st));
-      if (hctl->bad_input) break;
-      if (hctl->n_cand > c->cap_cand) { c->cap_cand = grown(hctl->n_cand); c->cap_ideal = std::max(c->cap_ideal, grown((uint64_t)4 * c->cap_cand)); continue; }
-      c->n_cand = hctl->n_cand;
+      if (hres->bad_input) break;
+      if (hres->n_cand > c->cap_cand) { c->cap_cand = grown(hres->n_cand); c->cap_ideal = std::max(c->cap_ideal, grown((uint64_t)4 * c->cap_cand)); continue; }
+      c->n_cand = hres->n_cand;
       if (c->n_cand) { S.n_launches = L; int r = run_rescue(c, p); if (r) return r; L = S.n_launches; }
       CU(cudaEventRecord(c->ev[3], st));
       k_build<<<ncta, 256, 0, st>>>(ix, b, p, ctl, c->q_any.as<uint8_t>(), c->c_task.as<uint32_t>(), F, c->r_left.as<RescueSeg>(),
@@ -456,42 +473,43 @@ int project_resident(brb_ctx* c, const brb_params& p) {
     ProvRows pr; pr.row = c->p_row.as<uint4>(); pr.pool = c->p_pool.as<uint32_t>();
     pr.sim = c->have_scores ? c->p_sim.as<double>() : nullptr; pr.clip = c->have_scores ? c->p_clip.as<int32_t>() : nullptr;
     if (ordered) {
-      k_back<true><<<ncta_back, 256, 0, st>>>(b, ctl, pv, c->c_stage.as<uint4>(), c->tpool.as<uint32_t>(), tl, pr, o); L++;
+      k_back<true><<<ncta_back, 256, 0, st>>>(b, ctl, pv, c->c_stage.as<uint4>(), c->tpool.as<uint32_t>(), tl, pr, o, hres); L++;
       CU(cudaEventRecord(c->ev[5], st));
       // ---- phase 6: batch totals -> offsets in bundle order; rows to their final place
       exclusive_scan(tl.agg, c->t_off.as<unsigned long long>(), nbat, c->scan_tmp.as<unsigned long long>(), st, &L);
       k_place<<<grid_for(nbat, 8), 256, 0, st>>>(b, ctl, tl, c->t_off.as<unsigned long long>(), pr, o); L++;   // one warp per batch
       k_group_rows<<<grid_for(b.n_groups + 1, 256), 256, 0, st>>>(b, ctl, c->a_roff.as<uint32_t>(), c->g_roff.as<uint32_t>()); L++;
     } else {
-      k_back<false><<<ncta_back, 256, 0, st>>>(b, ctl, pv, c->c_stage.as<uint4>(), c->tpool.as<uint32_t>(), tl, pr, o); L++;
-      CU(cudaEventRecord(c->ev[5], st));
-      k_back_finish<<<1, 1, 0, st>>>(ctl, o); L++;
+      k_back<false><<<ncta_back, 256, 0, st>>>(b, ctl, pv, c->c_stage.as<uint4>(), c->tpool.as<uint32_t>(), tl, pr, o, hres); L++;
+      CU(cudaEventRecord(c->ev[5], st)); back_finishes = true;       // the last CTA to leave publishes the totals
     }
-    CU(cudaEventRecord(c->ev[6], st));
-    CU(cudaMemcpyAsync(hctl, ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    if (!back_finishes) { k_publish<<<1, 1, 0, st>>>(ctl, hres); L++; CU(cudaEventRecord(c->ev[6], st)); }
+    CU(cudaStreamSynchronize(st));                          // the counters are in hres (mapped pinned memory) once the sequence has drained
     CU(cudaGetLastError());
-    if (hctl->bad_input) break;
+    c->ctl_clean = true;
+    if (hres->bad_input) break;
     bool again = false;
-    if (hctl->n_cand > c->cap_cand) { c->cap_cand = grown((uint64_t)hctl->n_cand + std::min<uint64_t>((n + 31) / 32, (uint64_t)148 * 8 * 8) * POOL_CHUNK); c->cap_ideal = std::max(c->cap_ideal, grown((uint64_t)4 * c->cap_cand)); again = true; }
-    else if (hctl->n_ideal > c->cap_ideal) { c->cap_ideal = grown(hctl->n_ideal); again = true; }
-    else if (hctl->n_rows > c->cap_rows) { c->cap_rows = grown(hctl->n_rows); c->cap_tmpw = std::max(c->cap_tmpw, grown((uint64_t)8 * c->cap_rows));
+    if (hres->n_cand > c->cap_cand) { c->cap_cand = grown((uint64_t)hres->n_cand + std::min<uint64_t>((n + 31) / 32, (uint64_t)148 * 8 * 8) * POOL_CHUNK); c->cap_ideal = std::max(c->cap_ideal, grown((uint64_t)4 * c->cap_cand)); again = true; }
+    else if (hres->n_ideal > c->cap_ideal) { c->cap_ideal = grown(hres->n_ideal); again = true; }
+    else if (hres->n_rows > c->cap_rows) { c->cap_rows = grown(hres->n_rows); c->cap_tmpw = std::max(c->cap_tmpw, grown((uint64_t)8 * c->cap_rows));
                                            c->cap_outw = std::max(c->cap_outw, grown((uint64_t)3 * c->cap_rows)); again = true; }
-    else if (hctl->n_tmpw > c->cap_tmpw) { c->cap_tmpw = grown(hctl->n_tmpw); again = true; }
-    else if (hctl->n_outw > c->cap_outw) { c->cap_outw = grown(hctl->n_outw); again = true; }
+    else if (hres->n_tmpw > c->cap_tmpw) { c->cap_tmpw = grown(hres->n_tmpw); again = true; }
+    else if (hres->n_outw > c->cap_outw) { c->cap_outw = grown(hres->n_outw); again = true; }
     if (!again) break;
   }
-  if (hctl->bad_input == 3) return fail(BRB_E_UNSUPPORTED, "a batch of 32 alignments emits 2^28 or more CIGAR words");
-  if (hctl->bad_input == 1) return fail(BRB_E_ARG, "mate_idx is not a symmetric single link (src/bramble.cpp:272-311)");
-  if (hctl->bad_input) return fail(BRB_E_ARG, "read exons of an alignment must be ascending and disjoint");
-  c->n_cand = hctl->n_cand; c->n_rec = hctl->n_rows; c->n_out_words = hctl->n_outw;
-  S.n_candidates = hctl->n_cand; S.n_rec = hctl->n_rows; S.n_launches = L; S.n_matches = hctl->n_matches; S.n_rescue = hctl->n_rescue;
-  S.ms_lookup = ms_between(c->ev[0], c->ev[1]); S.ms_chain = ms_between(c->ev[1], c->ev[2]); S.ms_rescue = ms_between(c->ev[2], c->ev[3]);
-  S.ms_finalize = ms_between(c->ev[3], c->ev[4]); S.ms_pair = ms_between(c->ev[4], c->ev[5]); S.ms_merge = ms_between(c->ev[5], c->ev[6]);
-  S.kernel_ms = ms_between(c->ev[0], c->ev[6]);
+  if (hres->bad_input == 3) return fail(BRB_E_UNSUPPORTED, "a batch of 32 alignments emits 2^28 or more CIGAR words");
+  if (hres->bad_input == 1) return fail(BRB_E_ARG, "mate_idx is not a symmetric single link (src/bramble.cpp:272-311)");
+  if (hres->bad_input) return fail(BRB_E_ARG, "read exons of an alignment must be ascending and disjoint");
+  c->n_cand = hres->n_cand; c->n_rec = hres->n_rows; c->n_out_words = hres->n_outw;
+  S.n_candidates = hres->n_cand; S.n_rec = hres->n_rows; S.n_launches = L; S.n_matches = hres->n_matches; S.n_rescue = hres->n_rescue;
+  const cudaEvent_t ev_front_end = one_front ? c->ev[1] : c->ev[4], ev_end = back_finishes ? c->ev[5] : c->ev[6];
+  S.ms_lookup = ms_between(c->ev[0], c->ev[1]);
+  if (!one_front) { S.ms_chain = ms_between(c->ev[1], c->ev[2]); S.ms_rescue = ms_between(c->ev[2], c->ev[3]); S.ms_finalize = ms_between(c->ev[3], c->ev[4]); }
+  S.ms_pair = ms_between(ev_front_end, c->ev[5]); S.ms_merge = back_finishes ? 0.f : ms_between(c->ev[5], c->ev[6]);
+  S.kernel_ms = ms_between(c->ev[0], ev_end);
   // algorithmic bytes, SURVEY.md 8(d) / DESIGN.md: per-alignment SoA + 56 B per index hit + output rows + rescue bases
-  S.alg_bytes_front = (uint64_t)n * 16 + (uint64_t)b.n_exon * 8 + hctl->n_mates * 4 + hctl->n_hits * 56;
-  S.alg_bytes = S.alg_bytes_front + (uint64_t)b.n_cigar * 4 + (uint64_t)hctl->n_rows * 40 + hctl->out_words * 4 + c->rescue_bytes;
+  S.alg_bytes_front = (uint64_t)n * 16 + (uint64_t)b.n_exon * 8 + hres->n_mates * 4 + hres->n_hits * 56;
+  S.alg_bytes = S.alg_bytes_front + (uint64_t)b.n_cigar * 4 + (uint64_t)hres->n_rows * 40 + hres->out_words * 4 + c->rescue_bytes;
   c->have_result = true; c->result_ordered = ordered;
   return BRB_OK;
 }

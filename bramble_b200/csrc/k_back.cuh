@@ -102,11 +102,12 @@ __device__ __forceinline__ bool front_overflow(const Ctl* c) { return c->n_cand 
 // completion order, and a_roff / a_rcnt tell the consumer where the rows of each unit are.
 template <bool ORDERED>
 __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __restrict__ ctl, BackIn v, uint4* __restrict__ gstage, uint32_t* __restrict__ tpool,
-                                                 BatchTotals tl, ProvRows pv_, Rows o) {
+                                                 BatchTotals tl, ProvRows pv_, Rows o, Ctl* __restrict__ host_result) {
   __shared__ uint4 s_stage[8][BACK_STAGE];                 // per match of the batch: tid (NONE: not emitted), CIGAR words, partner, scratch offset
   __shared__ uint16_t s_queue[8][BACK_STAGE];              // matches that need the general merge
   __shared__ uint32_t s_own[8][9][32];                     // per alignment of the batch: off, excl, ro, nrc, mro, mnrc, words of merged rows, rsum, mrsum
-  if (front_overflow(ctl)) return;                         // uniform for the whole grid: nothing was published, nobody waits
+  const bool skip = front_overflow(ctl);                   // uniform for the whole grid (only the front kernels move these counters)
+  if (ORDERED && skip) return;
   const unsigned lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const uint32_t lt_mask = (1u << lane) - 1u;
   uint32_t* s_off = s_own[wid][0]; uint32_t* s_excl = s_own[wid][1]; uint32_t* s_ro = s_own[wid][2]; uint32_t* s_nrc = s_own[wid][3];
@@ -116,7 +117,7 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
   const uint32_t n_batches = (b.n_aln + 31) >> 5;
   const uint32_t cap_tmpw = ctl->cap_tmpw, cap_rows = ctl->cap_rows, cap_outw = ctl->cap_outw;
   WarpPool wp; wp.cur = 0; wp.end = 0;
-  for (;;) {
+  for (; !skip;) {
     uint32_t wb = 0;
     if (lane == 0) wb = atomicAdd(&ctl->ticket_a, 1u);
     wb = __shfl_sync(0xffffffffu, wb, 0);
@@ -301,6 +302,22 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
     }
     __syncwarp();                                           // the staging area is reused by the next batch
   }
+  if (!ORDERED) {                                           // last kernel of the sequence: the last CTA to leave publishes the result
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      if (atomicAdd(&ctl->ticket_b, 1u) == gridDim.x - 1) {
+        __threadfence();
+        if (!skip) {                                        // the totals claimed are the result sizes
+          const unsigned long long tot = atomicAdd(&ctl->claimed, 0ull);
+          const uint32_t R = (uint32_t)tot, W = (uint32_t)(tot >> 32);
+          ctl->n_rows = R; ctl->n_outw = W; ctl->out_words = W;
+          if (R <= cap_rows && W <= cap_outw) o.coff[R] = W;
+        }
+        ctl_publish_and_reset(ctl, host_result);
+      }
+    }
+  }
 }
 
 // Clip-rescue path only: the front kernel cannot know which candidates survive k_ksw / k_build, so the match
@@ -314,13 +331,8 @@ __global__ void __launch_bounds__(256) k_count_valid(DevBatch b, const Ctl* __re
   ac.z = nv; a_cand[a] = ac;
 }
 
-// !ORDERED: the totals k_back claimed are the result sizes.
-__global__ void k_back_finish(Ctl* __restrict__ ctl, Rows o) {
-  if (front_overflow(ctl)) return;
-  const uint32_t R = (uint32_t)ctl->claimed, W = (uint32_t)(ctl->claimed >> 32);
-  ctl->n_rows = R; ctl->n_outw = W; ctl->out_words = W;
-  if (R <= ctl->cap_rows && W <= ctl->cap_outw) o.coff[R] = W;
-}
+// BRB_OPT_ORDERED_ROWS: the sequence ends with k_place / k_group_rows; one thread publishes after them.
+__global__ void k_publish(Ctl* __restrict__ ctl, Ctl* __restrict__ host_result) { ctl_publish_and_reset(ctl, host_result); }
 
 // Rows of batch wb: from where k_back claimed room (tl.claim) to their place in bundle order (t_off = exclusive
 // scan of tl.agg; t_off[n_batches] = totals).  One warp per batch.
