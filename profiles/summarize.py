@@ -17,8 +17,8 @@ open(os.path.join(here, tag + "_launches.csv"), "w").write(open(launches, errors
 generic = [k for k in agg if "k_front<" in k]
 step_total = sum(v[1] for k, v in agg.items() if k not in generic)
 md = [f"# {tag}: ncu summary\n"]
-md.append("Launch list: `ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline`")
-md.append(f"(raw list: {tag}_launches.csv; per-launch times are cold-cache + serialised, compare shares).  The generic front kernel `k_front<1>` runs ONCE, untimed,")
+md.append("Launch list: `ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e`")
+md.append(f"(raw list: {tag}_launches.csv; per-launch times are cold-cache + serialised, compare shares; `--no-e2e` keeps the list to the resident leg the bench line's `value` is timed on).  The generic front kernel `k_front<1>` runs ONCE, untimed,")
 md.append("to obtain the reference-defined algorithmic byte count; shares exclude it.\n")
 md.append("| kernel | launches | total us | share of step | avg us |\n|---|---|---|---|---|")
 for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1]):
