@@ -207,6 +207,8 @@ def main():
     ap.add_argument("--workload", default="c2", choices=["c2", "c5"], help="c2: the metric's configuration (default); c5: multi-mapping stress shape")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs: resident steps only (also skips the ordered-rows leg)")
     ap.add_argument("--e2e-bundles", type=int, default=8, help="bundles per step on the end-to-end path")
+    ap.add_argument("--e2e-rows", default="packed", choices=["packed", "columns"],
+                    help="row layout on the end-to-end path: BRB_OPT_PACKED_ROWS (16-byte records, fewer bytes device->host) or the plain columns")
     ap.add_argument("--no-bind", action="store_true", help="N>1: do not pin each rank to the CPUs of its GPU's NUMA node")
     ap.add_argument("--e2e-contexts", type=int, default=3, help="brb_ctx (host threads / streams) on the end-to-end path")
     args = ap.parse_args()
@@ -327,6 +329,10 @@ def main():
         eng.set_option(capi.OPT_ORDERED_ROWS, 0)
         eng.run_resident(p)
         checks["default"] = engine.rows_checksum(eng.download(B, raw=True))
+        eng.set_option(capi.OPT_PACKED_ROWS, 1)
+        eng.run_resident(p)
+        checks["packed_rows"] = engine.rows_checksum(eng.download(B, raw=True))
+        eng.set_option(capi.OPT_PACKED_ROWS, 0)
     barrier()
     st = eng.stats()
     # ---- end to end through the C ABI with pinned host columns: the step's alignments as `--e2e-bundles` bundles
@@ -341,6 +347,10 @@ def main():
         cuts = [G * i // nbun for i in range(nbun + 1)]
         PBs = [eng.pinned_copy(B.slice_groups(g0, g1)) for g0, g1 in zip(cuts[:-1], cuts[1:])]
         ctxs = [eng.context() for _ in range(max(1, args.e2e_contexts))]
+        e2e_packed = args.e2e_rows == "packed"
+        for c in ctxs:
+            c.set_option(capi.OPT_PACKED_ROWS, int(e2e_packed))
+        eng.set_option(capi.OPT_PACKED_ROWS, int(e2e_packed))
         engine.project_pipelined(ctxs, p, PBs)
         res = engine.project_pipelined(ctxs, p, PBs, checksum=True)
         checks["e2e_bundles"] = (sum(r[4] for r in res) & 0xFFFFFFFFFFFFFFFF, sum(r[0] for r in res))
@@ -360,6 +370,7 @@ def main():
             eng.project(p, PB, raw=True)
         torch.cuda.synchronize()
         e2e_single_s = (time.perf_counter() - t0) / min(3, args.steps)
+        eng.set_option(capi.OPT_PACKED_ROWS, 0)
         barrier()
     t = torch.tensor([ms, e2e_s * 1e3, float(n_aln)], dtype=torch.float64, device=f"cuda:{local}")
     tmax = t.clone()
@@ -396,6 +407,7 @@ def main():
                 "e2e": None if args.no_e2e else {"value": e2e, "unit": unit, "h2d_bytes_per_step": e2e_h2d, "d2h_bytes_per_step": e2e_d2h,
                         "records_per_step": e2e_rec, "bundles_per_step": nbun, "contexts": len(ctxs),
                         "how": "brb_project() per bundle from pinned host columns, one host thread per context",
+                        "rows": "BRB_OPT_PACKED_ROWS: one 16-byte record per row" if args.e2e_rows == "packed" else "columns (22 bytes per row + CIGAR CSR)",
                         "single_call_value": n_aln / e2e_single_s, "single_call_note": "rank 0, one brb_project() call for the whole step, no overlap"},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                              "traffic_by_kernel": traffic_by_kernel, "traffic_source": f"{traffic_src} (ncu --set full, one step)" if traffic_src else None,
@@ -410,7 +422,7 @@ def main():
                                                       "instead of unit blocks + aln_rec_off/aln_rec_cnt"}},
                 "parity_at_bench_size": None if not checks else {
                     "property": "order-independent checksum of all rows (source alignment, tid, pos, strand, flags, CIGAR) and row count agree between "
-                                "the default kernels, the generic front kernel, BRB_OPT_ORDERED_ROWS and the 8-bundle / 3-context end-to-end path (rank 0)",
+                                "the default kernels, the generic front kernel, BRB_OPT_ORDERED_ROWS, BRB_OPT_PACKED_ROWS and the 8-bundle / 3-context end-to-end path (rank 0)",
                     "rows": checks["default"][1], "checksum": "%016x" % checks["default"][0],
                     "agree": len({(int(c[0]), int(c[1])) for c in checks.values()}) == 1},
                 "host": {**host, "e2e_ms_per_step_by_rank": [round(float(x[0].item()), 3) for x in by_rank],
@@ -428,10 +440,10 @@ def main():
             # through the C ABI) on the same BAM sample, same flags: end to end INCLUDING BGZF, marginal rate like the reference
             try:
                 cli_names = min(3 * args.ref_names, int(B.desc.n_groups))      # a larger sample: the CLI needs several bundles in flight
-                cli = time_reference(A, ix, B, 2000, cli_names, cores, binary=g.build_cli(), extra=["--level", "1"], kind=args.workload)
+                cli = time_reference(A, ix, B, 2000, cli_names, cores, repeats=3, binary=g.build_cli(), extra=["--level", "1"], kind=args.workload)   # best of 3 each: start-up (CUDA context) varies by tenths of a second
                 if cli:
                     line["cli_e2e"] = {"value": cli["value"], "unit": unit, "sample": cli["sample"], "host_threads": min(cores, 255),
-                                       "what": "bramble_b200_cli BAM in -> BAM out (1 GPU), marginal over a 2000-name run"}
+                                       "what": "bramble_b200_cli BAM in -> BAM out (1 GPU), marginal over a 2000-name run, best of 3 runs each"}
             except Exception as e:
                 line["cli_e2e_error"] = str(e)[:200]
         emit(line)

@@ -18,6 +18,7 @@ REC_FIRST, REC_PAIRED, REC_SAMETX = 1, 2, 4
 OPT_GENERIC_FRONT = 1
 OPT_NO_FASTPATH = 2
 OPT_ORDERED_ROWS = 3
+OPT_PACKED_ROWS = 4
 
 u8p, i8p = C.POINTER(C.c_uint8), C.POINTER(C.c_int8)
 u32p, i32p = C.POINTER(C.c_uint32), C.POINTER(C.c_int32)
@@ -49,7 +50,7 @@ class BatchOut(C.Structure):
     _fields_ = [("n_rec", C.c_uint32), ("n_cigar_words", C.c_uint64), ("group_rec_off", u32p),
                 ("src_aln", u32p), ("tid", u32p), ("pos", u32p), ("tx_strand", i8p), ("flags", u8p),
                 ("sim_score", f64p), ("clip_score", i32p), ("cigar_off", u32p), ("cigar", u32p),
-                ("aln_rec_off", u32p), ("aln_rec_cnt", u32p)]
+                ("aln_rec_off", u32p), ("aln_rec_cnt", u32p), ("packed_rows", u32p)]
 
 
 class Stats(C.Structure):

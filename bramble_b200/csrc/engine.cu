@@ -90,7 +90,7 @@ struct brb_ctx {
   DevBatch b{};
   Buf in_group_off, in_refid, in_strand, in_exon_off, in_exon_st, in_exon_en, in_cigar_off, in_cigar, in_mate, in_seq_off, in_seq;
   uint64_t in_bytes = 0, n_mates = 0, seq_bytes = 0, rescue_bytes = 0;
-  bool have_batch = false, have_result = false, have_scores = false, opt_generic_front = false, opt_no_fastpath = false, opt_ordered = false, result_ordered = false;
+  bool have_batch = false, have_result = false, have_scores = false, opt_generic_front = false, opt_no_fastpath = false, opt_ordered = false, result_ordered = false, opt_packed = false, result_packed = false;
   // control block + pools (capacities persist across calls and only grow)
   Buf ctl;
   uint32_t cap_cand = 0, cap_ideal = 0, cap_rows = 0, cap_tmpw = 0, cap_outw = 0;
@@ -357,6 +357,7 @@ int ensure_pools(brb_ctx* c, bool rescue) {
   ENS(c->c_stage, C * 16); ENS(c->t_agg, nbat * 8 + 8); ENS(c->t_claim, nbat * 8 + 8); ENS(c->t_off, (nbat + 1) * 8);
   ENS(c->scan_tmp, scan_scratch_words(std::max<size_t>(nbat, 1)) * 8);
   if (c->opt_ordered) { ENS(c->p_row, R * 16); ENS(c->p_pool, (size_t)c->cap_outw * 4); }
+  if (c->opt_packed) ENS(c->p_row, R * 16);
   ENS(c->m_rec, C * 16);
   if (c->have_scores) { ENS(c->m_sim, C * 8); ENS(c->m_clip, C * 4); ENS(c->o_sim, R * 8); ENS(c->o_clip, R * 4); if (c->opt_ordered) { ENS(c->p_sim, R * 8); ENS(c->p_clip, R * 4); } }
   if (rescue) { ENS(c->c_rec, C * 4); ENS(c->c_task, C * 4); ENS(c->c_first, C * 4); ENS(c->c_last, C * 4); ENS(c->c_nseg, C * 4); ENS(c->c_nguide, C * 4); ENS(c->c_cap, C * 4); }
@@ -383,7 +384,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   if (n == 0) {
     ENS(c->g_roff, (size_t)(b.n_groups + 1) * 4); ENS(c->o_coff, 4);
     CU(cudaMemsetAsync(c->g_roff.p, 0, 4, st)); CU(cudaMemsetAsync(c->o_coff.p, 0, 4, st)); CU(cudaStreamSynchronize(st));
-    c->have_result = true; c->result_ordered = c->opt_ordered; return BRB_OK;
+    c->have_result = true; c->result_ordered = c->opt_ordered; c->result_packed = c->opt_packed && !c->opt_ordered; return BRB_OK;
   }
   if (!c->cap_cand) {           // first guess from the batch shape; a pool that overflows grows and the sequence replays
     c->cap_cand = grown((uint64_t)12 * n); c->cap_rows = grown((uint64_t)6 * n);
@@ -408,8 +409,8 @@ int project_resident(brb_ctx* c, const brb_params& p) {
                        : short_front ? (p.filter_by_similarity ? (const void*)k_front_short<true> : (const void*)k_front_short<false>)
                                      : (rescue ? (const void*)k_front<false> : (const void*)k_front<true>);
   const int ncta_front = resident(front_fn);
-  const bool ordered = c->opt_ordered;
-  const int ncta_back = resident(ordered ? (const void*)k_back<true> : (const void*)k_back<false>);
+  const bool ordered = c->opt_ordered, packed = c->opt_packed && !ordered;      // BRB_OPT_ORDERED_ROWS wins when both are set
+  const int ncta_back = resident(ordered ? (const void*)k_back<true, false> : packed ? (const void*)k_back<false, true> : (const void*)k_back<false, false>);
   Ctl* ctl = c->ctl.as<Ctl>();
   static_assert(sizeof(Ctl) <= 512, "two Ctl images in h_small");
   Ctl* hctl = c->h_small.as<Ctl>();                                               // initialisation image (host -> device)
@@ -473,14 +474,16 @@ int project_resident(brb_ctx* c, const brb_params& p) {
     ProvRows pr; pr.row = c->p_row.as<uint4>(); pr.pool = c->p_pool.as<uint32_t>();
     pr.sim = c->have_scores ? c->p_sim.as<double>() : nullptr; pr.clip = c->have_scores ? c->p_clip.as<int32_t>() : nullptr;
     if (ordered) {
-      k_back<true><<<ncta_back, 256, 0, st>>>(b, ctl, pv, c->c_stage.as<uint4>(), c->tpool.as<uint32_t>(), tl, pr, o, hres); L++;
+      k_back<true, false><<<ncta_back, 256, 0, st>>>(b, ctl, pv, c->c_stage.as<uint4>(), c->tpool.as<uint32_t>(), tl, pr, o, hres); L++;
       CU(cudaEventRecord(c->ev[5], st));
       // ---- phase 6: batch totals -> offsets in bundle order; rows to their final place
       exclusive_scan(tl.agg, c->t_off.as<unsigned long long>(), nbat, c->scan_tmp.as<unsigned long long>(), st, &L);
       k_place<<<grid_for(nbat, 8), 256, 0, st>>>(b, ctl, tl, c->t_off.as<unsigned long long>(), pr, o); L++;   // one warp per batch
       k_group_rows<<<grid_for(b.n_groups + 1, 256), 256, 0, st>>>(b, ctl, c->a_roff.as<uint32_t>(), c->g_roff.as<uint32_t>()); L++;
     } else {
-      k_back<false><<<ncta_back, 256, 0, st>>>(b, ctl, pv, c->c_stage.as<uint4>(), c->tpool.as<uint32_t>(), tl, pr, o, hres); L++;
+      if (packed) k_back<false, true><<<ncta_back, 256, 0, st>>>(b, ctl, pv, c->c_stage.as<uint4>(), c->tpool.as<uint32_t>(), tl, pr, o, hres);
+      else k_back<false, false><<<ncta_back, 256, 0, st>>>(b, ctl, pv, c->c_stage.as<uint4>(), c->tpool.as<uint32_t>(), tl, pr, o, hres);
+      L++;
       CU(cudaEventRecord(c->ev[5], st)); back_finishes = true;       // the last CTA to leave publishes the totals
     }
     if (!back_finishes) { k_publish<<<1, 1, 0, st>>>(ctl, hres); L++; CU(cudaEventRecord(c->ev[6], st)); }
@@ -498,6 +501,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
     if (!again) break;
   }
   if (hres->bad_input == 3) return fail(BRB_E_UNSUPPORTED, "a batch of 32 alignments emits 2^28 or more CIGAR words");
+  if (hres->bad_input == 4) return fail(BRB_E_UNSUPPORTED, "BRB_OPT_PACKED_ROWS: the bundle pools 2^27 or more CIGAR words; project it without the option");
   if (hres->bad_input == 1) return fail(BRB_E_ARG, "mate_idx is not a symmetric single link (src/bramble.cpp:272-311)");
   if (hres->bad_input) return fail(BRB_E_ARG, "read exons of an alignment must be ascending and disjoint");
   c->n_cand = hres->n_cand; c->n_rec = hres->n_rows; c->n_out_words = hres->n_outw;
@@ -510,7 +514,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   // algorithmic bytes, SURVEY.md 8(d) / DESIGN.md: per-alignment SoA + 56 B per index hit + output rows + rescue bases
   S.alg_bytes_front = (uint64_t)n * 16 + (uint64_t)b.n_exon * 8 + hres->n_mates * 4 + hres->n_hits * 56;
   S.alg_bytes = S.alg_bytes_front + (uint64_t)b.n_cigar * 4 + (uint64_t)hres->n_rows * 40 + hres->out_words * 4 + c->rescue_bytes;
-  c->have_result = true; c->result_ordered = ordered;
+  c->have_result = true; c->result_ordered = ordered; c->result_packed = packed;
   return BRB_OK;
 }
 
@@ -534,19 +538,20 @@ int brb_batch_download(brb_ctx* c, brb_batch_out* out) {
   const bool sc = c->have_scores && R;
   auto al = [](size_t x) { return (x + 15) & ~(size_t)15; };
   size_t off = 0;
-  const bool ord = c->result_ordered;
+  const bool ord = c->result_ordered, pk = c->result_packed;
   const size_t N = c->b.n_aln;
   const size_t o_groff = off; off += ord ? al((G + 1) * 4) : 0;
   const size_t o_aoff = off; off += al(N * 4);
   const size_t o_acnt = off; off += al(N * 4);
-  const size_t o_src = off; off += al(R * 4);
-  const size_t o_tid = off; off += al(R * 4);
-  const size_t o_pos = off; off += al(R * 4);
+  const size_t o_prow = off; off += pk ? al(R * 16) : 0;
+  const size_t o_src = off; off += pk ? 0 : al(R * 4);
+  const size_t o_tid = off; off += pk ? 0 : al(R * 4);
+  const size_t o_pos = off; off += pk ? 0 : al(R * 4);
   const size_t o_sim = off; off += sc ? al(R * 8) : 0;
   const size_t o_clip = off; off += sc ? al(R * 4) : 0;
-  const size_t o_coff = off; off += al((R + 1) * 4);
-  const size_t o_strand = off; off += al(R);
-  const size_t o_flags = off; off += al(R);
+  const size_t o_coff = off; off += pk ? 0 : al((R + 1) * 4);
+  const size_t o_strand = off; off += pk ? 0 : al(R);
+  const size_t o_flags = off; off += pk ? 0 : al(R);
   const size_t o_cig = off; off += al(W * 4);
   ENS(c->h_out, off + 16);
   uint8_t* h = c->h_out.as<uint8_t>();
@@ -559,24 +564,26 @@ int brb_batch_download(brb_ctx* c, brb_batch_out* out) {
   int rc = ord ? dn(o_groff, c->g_roff, (G + 1) * 4) : 0;
   if (!rc) rc = dn(o_aoff, c->a_roff, N * 4);
   if (!rc) rc = dn(o_acnt, c->a_rcnt, N * 4);
-  if (!rc) rc = dn(o_src, c->o_src, R * 4);
-  if (!rc) rc = dn(o_tid, c->o_tid, R * 4);
-  if (!rc) rc = dn(o_pos, c->o_pos, R * 4);
+  if (!rc && pk) rc = dn(o_prow, c->p_row, R * 16);
+  if (!rc && !pk) rc = dn(o_src, c->o_src, R * 4);
+  if (!rc && !pk) rc = dn(o_tid, c->o_tid, R * 4);
+  if (!rc && !pk) rc = dn(o_pos, c->o_pos, R * 4);
   if (!rc && sc) rc = dn(o_sim, c->o_sim, R * 8);
   if (!rc && sc) rc = dn(o_clip, c->o_clip, R * 4);
-  if (!rc) rc = dn(o_coff, c->o_coff, (R + 1) * 4);
-  if (!rc) rc = dn(o_strand, c->o_strand, R);
-  if (!rc) rc = dn(o_flags, c->o_flags, R);
+  if (!rc && !pk) rc = dn(o_coff, c->o_coff, (R + 1) * 4);
+  if (!rc && !pk) rc = dn(o_strand, c->o_strand, R);
+  if (!rc && !pk) rc = dn(o_flags, c->o_flags, R);
   if (!rc) rc = dn(o_cig, c->opool, W * 4);
   if (rc) return rc;
   CU(cudaStreamSynchronize(c->st));
   out->n_rec = (uint32_t)R; out->n_cigar_words = W;
   out->group_rec_off = ord ? (const uint32_t*)(h + o_groff) : nullptr;
   out->aln_rec_off = (const uint32_t*)(h + o_aoff); out->aln_rec_cnt = (const uint32_t*)(h + o_acnt);
-  out->src_aln = (const uint32_t*)(h + o_src); out->tid = (const uint32_t*)(h + o_tid);
-  out->pos = (const uint32_t*)(h + o_pos); out->tx_strand = (const int8_t*)(h + o_strand); out->flags = h + o_flags;
+  out->packed_rows = pk ? (const uint32_t*)(h + o_prow) : nullptr;
+  out->src_aln = pk ? nullptr : (const uint32_t*)(h + o_src); out->tid = pk ? nullptr : (const uint32_t*)(h + o_tid);
+  out->pos = pk ? nullptr : (const uint32_t*)(h + o_pos); out->tx_strand = pk ? nullptr : (const int8_t*)(h + o_strand); out->flags = pk ? nullptr : h + o_flags;
   out->sim_score = sc ? (const double*)(h + o_sim) : nullptr; out->clip_score = sc ? (const int32_t*)(h + o_clip) : nullptr;
-  out->cigar_off = (const uint32_t*)(h + o_coff); out->cigar = (const uint32_t*)(h + o_cig);
+  out->cigar_off = pk ? nullptr : (const uint32_t*)(h + o_coff); out->cigar = (const uint32_t*)(h + o_cig);
   c->stats.d2h_bytes = bytes;
   return BRB_OK;
 }
@@ -592,6 +599,7 @@ int brb_ctx_set_option(brb_ctx* c, int option, int value) {
   if (option == BRB_OPT_GENERIC_FRONT) { c->opt_generic_front = value != 0; return BRB_OK; }
   if (option == BRB_OPT_NO_FASTPATH) { c->opt_no_fastpath = value != 0; return BRB_OK; }
   if (option == BRB_OPT_ORDERED_ROWS) { c->opt_ordered = value != 0; return BRB_OK; }
+  if (option == BRB_OPT_PACKED_ROWS) { c->opt_packed = value != 0; return BRB_OK; }
   return fail(BRB_E_ARG, "unknown option %d", option);
 }
 

@@ -100,7 +100,10 @@ __device__ __forceinline__ bool front_overflow(const Ctl* c) { return c->n_cand 
 // ORDERED: rows go to a provisional buffer as packed records and k_place moves them into bundle order afterwards.
 // !ORDERED: the claimed place is final -- rows are written straight into the output columns, blocks of 32 alignments in
 // completion order, and a_roff / a_rcnt tell the consumer where the rows of each unit are.
-template <bool ORDERED>
+// PACKED (with !ORDERED): the same, but a row is ONE 16-byte record (brb_batch_out::packed_rows, include/bramble_b200.h): a one-word
+// CIGAR below 2^27 travels inside it, any other CIGAR goes to the pool behind a length word -- the pool then only
+// holds the rare multi-word CIGARs and a short-read row costs 16 bytes on the way back to the host instead of 22.
+template <bool ORDERED, bool PACKED>
 __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __restrict__ ctl, BackIn v, uint4* __restrict__ gstage, uint32_t* __restrict__ tpool,
                                                  BatchTotals tl, ProvRows pv_, Rows o, Ctl* __restrict__ host_result) {
   __shared__ uint4 s_stage[8][BACK_STAGE];                 // per match of the batch: tid (NONE: not emitted), CIGAR words, partner, scratch offset
@@ -172,8 +175,9 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
         }
         tpool[toff] = clr;
       }
-      stage[sidx] = make_uint4(tid, clr + clm, part, fit ? toff : NOFIT);
-      atomicAdd(&s_words[L], clr + clm);
+      const uint32_t hdr = PACKED ? (paired ? 2u : 1u) : 0u;     // PACKED: every pooled CIGAR sits behind its length word
+      stage[sidx] = make_uint4(tid, clr + clm + hdr, part, fit ? toff : NOFIT);
+      atomicAdd(&s_words[L], clr + clm + hdr);
     };
     // ---- phase 1
     for (uint32_t base = 0; base < total; base += 32) {
@@ -201,16 +205,17 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
       const bool emitted = part != NONE, paired = emitted && part != SELF;
       uint4 pr = make_uint4(0, 0, 0, NONE);
       if (paired) pr = __ldg(&v.m_rec[part]);
-      const bool inl = emitted && (mr.y >> 1) == 1 && merge_trivial(mr.z, o_rsum) && (!paired || ((pr.y >> 1) == 1 && merge_trivial(pr.z, o_mrsum)));
+      bool inl = emitted && (mr.y >> 1) == 1 && merge_trivial(mr.z, o_rsum) && (!paired || ((pr.y >> 1) == 1 && merge_trivial(pr.z, o_mrsum)));
+      if (PACKED) inl = inl && ((mr.z | (paired ? pr.z : 0u)) >> 27) == 0;      // the word has to fit the record
       const bool slow = emitted && !inl;
       const uint32_t B_e = __ballot_sync(0xffffffffu, emitted), B_p = __ballot_sync(0xffffffffu, paired), B_s = __ballot_sync(0xffffffffu, slow);
       if (n && incl > base && excl < base + 32) {           // rows / one-word CIGARs of MY alignment in this chunk
         const uint32_t mine = bit_range(excl > base ? excl - base : 0, incl - base < 32 ? incl - base : 32);
         rows += __popc(B_e & mine) + __popc(B_p & mine);
-        words += __popc(B_e & ~B_s & mine) + __popc(B_p & ~B_s & mine);
+        if (!PACKED) words += __popc(B_e & ~B_s & mine) + __popc(B_p & ~B_s & mine);
       }
       const uint32_t sidx = staged ? item : c;
-      if (actv) stage[sidx] = make_uint4(emitted ? tid : NONE, slow ? L : (paired ? 2u : 1u), part, slow ? PENDING : INLINE);
+      if (actv) stage[sidx] = make_uint4(emitted ? tid : NONE, slow ? L : (PACKED ? 0u : (paired ? 2u : 1u)), part, slow ? PENDING : INLINE);
       if (B_s) {
         if (staged) { if (slow) queue[qn + __popc(B_s & lt_mask)] = (uint16_t)item; }
         qn += __popc(B_s);
@@ -250,6 +255,7 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
     const uint32_t row0 = prow0 + irows - rows, word0 = pword0 + iwords - words;
     if (a < b.n_aln) { o.a_roff[a] = ORDERED ? irows - rows : row0; o.a_rcnt[a] = rows; }     // ORDERED: batch-relative, k_place adds the first row of the batch
     if (ORDERED && W_b >= (1u << 28)) { if (lane == 0) atomicMax(&ctl->bad_input, 3u); __syncwarp(); continue; }
+    if (PACKED && (unsigned long long)pword0 + W_b >= (1u << 27)) { if (lane == 0) atomicMax(&ctl->bad_input, 4u); __syncwarp(); continue; }
     if ((unsigned long long)prow0 + R_b > cap_rows || (unsigned long long)pword0 + W_b > cap_outw) { __syncwarp(); continue; }   // the host grows the row pools and replays
     // ---- phase 2: rank inside the unit, rows, CIGAR words
     for (uint32_t base = 0; base < total; base += 32) {
@@ -284,18 +290,23 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
       for (uint32_t e = 0, ne = paired ? 2 : 1; e < ne; e++) {
         if (e) {                                            // the mate row follows the read row
           m = pm; cc = part; aln = (uint32_t)o_mate; fl &= ~BRB_REC_FIRST; wpos = w0 + clr;
-          src = tpool + sg.w + 1 + (s_nrc[L] + (mr.y >> 1) + 2); len = inl ? 1u : sg.y - clr;
+          src = tpool + sg.w + 1 + (s_nrc[L] + (mr.y >> 1) + 2); len = inl ? 1u : sg.y - clr - (PACKED ? 2u : 0u);
+          if (PACKED) wpos = w0 + 1 + clr;
         }
         const uint32_t minus = m.y & 1u, r = row + e;
         uint32_t* pool = ORDERED ? pv_.pool : o.pool;
         if (ORDERED) {
           pv_.row[r] = make_uint4(aln, m.w, m.x, (wpos - pword0) | (minus << 28) | (fl << 29));
           if (v.m_sim) { pv_.sim[r] = v.m_sim[cc]; pv_.clip[r] = v.m_clip[cc]; }
+        } else if (PACKED) {
+          pv_.row[r] = make_uint4(aln, m.w, m.x, (inl ? (m.z | BRB_ROW_INLINE) : wpos) | (minus << 28) | (fl << 29));
+          if (v.m_sim) { o.sim[r] = v.m_sim[cc]; o.clip[r] = v.m_clip[cc]; }
+          if (!inl) pool[wpos++] = len;                     // length word, then the CIGAR
         } else {
           o.src[r] = aln; o.tid[r] = m.w; o.pos[r] = m.x; o.strand[r] = minus ? '-' : '+'; o.flags[r] = (uint8_t)fl; o.coff[r] = wpos;
           if (v.m_sim) { o.sim[r] = v.m_sim[cc]; o.clip[r] = v.m_clip[cc]; }
         }
-        if (inl) pool[wpos] = m.z;
+        if (inl) { if (!PACKED) pool[wpos] = m.z; }
         else if (minus) for (uint32_t i = 0; i < len; i++) pool[wpos + i] = src[len - 1 - i];      // reverse_complement_bam, src/bam.cpp:636-702
         else for (uint32_t i = 0; i < len; i++) pool[wpos + i] = src[i];
       }
@@ -312,7 +323,7 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
           const unsigned long long tot = atomicAdd(&ctl->claimed, 0ull);
           const uint32_t R = (uint32_t)tot, W = (uint32_t)(tot >> 32);
           ctl->n_rows = R; ctl->n_outw = W; ctl->out_words = W;
-          if (R <= cap_rows && W <= cap_outw) o.coff[R] = W;
+          if (!PACKED && R <= cap_rows && W <= cap_outw) o.coff[R] = W;
         }
         ctl_publish_and_reset(ctl, host_result);
       }

@@ -8,6 +8,41 @@ import numpy as np
 from . import capi
 
 
+def _columns(o, copy=False):
+    """Row columns of a raw brb_batch_out in MEMORY order, whichever layout it came in: the structure-of-arrays columns,
+    or BRB_OPT_PACKED_ROWS records (include/bramble_b200.h) unpacked into the same columns (a dense CIGAR CSR rebuilt
+    from the in-record words and the length-prefixed pool)."""
+    n, W = int(o.n_rec), int(o.n_cigar_words)
+
+    def arr(p, cnt, dt=None):
+        if cnt == 0 or not p:          # NULL score columns: all zero (see include/bramble_b200.h)
+            return np.zeros(cnt, dtype=dt or np.uint32)
+        a = np.ctypeslib.as_array(p, shape=(cnt,))
+        return a.astype(dt or a.dtype, copy=True) if (copy or dt) else a
+    d = dict(sim_score=arr(o.sim_score, n, np.float64), clip_score=arr(o.clip_score, n, np.int32))
+    if not getattr(o, "packed_rows", None):      # (the oracle's result struct has the plain columns only)
+        d.update(src_aln=arr(o.src_aln, n), tid=arr(o.tid, n), pos=arr(o.pos, n), tx_strand=arr(o.tx_strand, n, np.int8),
+                 flags=arr(o.flags, n, np.uint8), cigar_off=arr(o.cigar_off, n + 1).astype(np.int64), cigar=arr(o.cigar, W))
+        return d
+    pr = arr(o.packed_rows, 4 * n).reshape(n, 4)
+    w = pr[:, 3]
+    inline, val = ((w >> 27) & 1) == 1, (w & 0x07FFFFFF).astype(np.int64)
+    pool = arr(o.cigar, W)
+    clen = np.ones(n, dtype=np.int64)
+    clen[~inline] = pool[val[~inline]]
+    coff = np.concatenate([[0], np.cumsum(clen)])
+    words = np.zeros(int(coff[-1]), dtype=np.uint32)
+    words[coff[:-1][inline]] = val[inline].astype(np.uint32)
+    lens = clen[~inline]
+    if lens.size:
+        within = np.arange(int(lens.sum()), dtype=np.int64) - np.repeat(np.cumsum(lens) - lens, lens)
+        words[np.repeat(coff[:-1][~inline], lens) + within] = pool[np.repeat(val[~inline] + 1, lens) + within]
+    d.update(src_aln=pr[:, 0].copy(), tid=pr[:, 1].copy(), pos=pr[:, 2].copy(),
+             tx_strand=np.where((w >> 28) & 1, ord("-"), ord("+")).astype(np.int8), flags=(w >> 29).astype(np.uint8),
+             cigar_off=coff, cigar=words)
+    return d
+
+
 def _rows(o, batch):
     """Rows of a brb_batch_out in the reference's emit order: the unit blocks (aln_rec_off / aln_rec_cnt) concatenated in
     alignment order; group_rec_off follows from the block sizes."""
@@ -15,7 +50,7 @@ def _rows(o, batch):
     n_aln, n_groups = int(batch.desc.n_aln), int(batch.desc.n_groups)
 
     def arr(p, cnt, dt):
-        if cnt == 0 or not p:          # NULL score columns: all zero (see include/bramble_b200.h)
+        if cnt == 0 or not p:
             return np.zeros(cnt, dtype=dt)
         return np.ctypeslib.as_array(p, shape=(cnt,)).astype(dt, copy=True)
     aoff, acnt = arr(o.aln_rec_off, n_aln, np.int64), arr(o.aln_rec_cnt, n_aln, np.int64)
@@ -24,15 +59,13 @@ def _rows(o, batch):
     order = np.repeat(aoff - start, acnt) + np.arange(n, dtype=np.int64)        # row index in memory of the k-th row in emit order
     go = batch.arrays["group_off"].astype(np.int64)[:n_groups + 1]
     cum = np.concatenate([[0], np.cumsum(acnt)])
-    d = dict(n_rec=n, group_rec_off=cum[go].astype(np.uint32) if n_aln else np.zeros(n_groups + 1, np.uint32),
-             src_aln=arr(o.src_aln, n, np.uint32)[order],
-             tid=arr(o.tid, n, np.uint32)[order], pos=arr(o.pos, n, np.uint32)[order], tx_strand=arr(o.tx_strand, n, np.int8)[order],
-             flags=arr(o.flags, n, np.uint8)[order], sim_score=arr(o.sim_score, n, np.float64)[order],
-             clip_score=arr(o.clip_score, n, np.int32)[order])
+    col = _columns(o, copy=True)
+    d = dict(n_rec=n, group_rec_off=cum[go].astype(np.uint32) if n_aln else np.zeros(n_groups + 1, np.uint32))
+    for k in ("src_aln", "tid", "pos", "tx_strand", "flags", "sim_score", "clip_score"):
+        d[k] = col[k][order]
     if o.group_rec_off:                                                          # BRB_OPT_ORDERED_ROWS: already in emit order
         assert np.array_equal(order, np.arange(n)) and np.array_equal(arr(o.group_rec_off, n_groups + 1, np.uint32), d["group_rec_off"])
-    co = arr(o.cigar_off, n + 1, np.uint32).astype(np.int64)
-    pool = arr(o.cigar, int(o.n_cigar_words), np.uint32)
+    co, pool = col["cigar_off"], col["cigar"]
     d["cigar_len"] = np.diff(co).astype(np.uint32)[order]
     d["cigars"] = [pool[int(co[r]):int(co[r + 1])].copy() for r in order]
     d["cigar_off"] = (np.cumsum(d["cigar_len"]) - d["cigar_len"]).astype(np.uint32)
@@ -60,6 +93,9 @@ class Context:
         capi.check(self.lib.brb_ctx_stats(self._ctx, C.byref(s)), "brb_ctx_stats")
         return s
 
+    def set_option(self, option, value):
+        capi.check(self.lib.brb_ctx_set_option(self._ctx, int(option), int(value)), "brb_ctx_set_option")
+
     def close(self):
         if self._ctx:
             self.lib.brb_ctx_destroy(self._ctx)
@@ -72,17 +108,16 @@ def rows_checksum(o, src_offset=0):
     n = int(o.n_rec)
     if n == 0:
         return 0, 0
-    def arr(p, cnt):
-        return np.ctypeslib.as_array(p, shape=(cnt,))
+    c = _columns(o)
     M = np.uint64(0x9E3779B97F4A7C15)
     with np.errstate(over="ignore"):
-        co = arr(o.cigar_off, n + 1).astype(np.uint64)
-        pool = arr(o.cigar, int(o.n_cigar_words)).astype(np.uint64)
+        co = c["cigar_off"].astype(np.uint64)
+        pool = c["cigar"].astype(np.uint64)
         wsum = np.concatenate([[np.uint64(0)], np.cumsum(pool * M + (pool >> np.uint64(7)), dtype=np.uint64)])
-        h = (arr(o.src_aln, n).astype(np.uint64) + np.uint64(src_offset)) * M
-        h ^= arr(o.tid, n).astype(np.uint64) * np.uint64(0xC2B2AE3D27D4EB4F)
-        h = h * M + arr(o.pos, n).astype(np.uint64)
-        h = h * M + (arr(o.tx_strand, n).astype(np.uint64) << np.uint64(8)) + arr(o.flags, n).astype(np.uint64)
+        h = (c["src_aln"].astype(np.uint64) + np.uint64(src_offset)) * M
+        h ^= c["tid"].astype(np.uint64) * np.uint64(0xC2B2AE3D27D4EB4F)
+        h = h * M + c["pos"].astype(np.uint64)
+        h = h * M + (c["tx_strand"].astype(np.uint8).astype(np.uint64) << np.uint64(8)) + c["flags"].astype(np.uint64)
         h = h * M + (co[1:] - co[:-1])
         h = h * M + (wsum[co[1:].astype(np.int64)] - wsum[co[:-1].astype(np.int64)])
         return int(h.sum(dtype=np.uint64)), n

@@ -114,7 +114,19 @@ typedef struct brb_batch_out {
   const uint32_t* cigar;
   const uint32_t* aln_rec_off;          /* n_aln: first row of the unit owned by alignment a */
   const uint32_t* aln_rec_cnt;          /* n_aln: its rows (0 for the higher-indexed end of a pair and for units that emit nothing) */
+  const uint32_t* packed_rows;          /* BRB_OPT_PACKED_ROWS only (else NULL): 4 words per row, see below; src_aln, tid, pos,
+                                         * tx_strand, flags and cigar_off are then NULL */
 } brb_batch_out;
+
+/* BRB_OPT_PACKED_ROWS: the row columns as ONE 16-byte record per row -- a third fewer bytes device->host, which is what
+ * bounds the end-to-end rate.  Row r = packed_rows[4r .. 4r+3] = { src_aln, tid, pos, w }; the unit blocks are found
+ * through aln_rec_off / aln_rec_cnt as usual.  A merged CIGAR of one word below 2^27 (every plain short-read row:
+ * one M) sits in w itself; any other CIGAR is in `cigar` behind a length word: cigar[i] = n, cigar[i+1 .. i+n] =
+ * the words, i = BRB_ROW_CIGAR(w).  n_cigar_words counts the pool with its length words. */
+#define BRB_ROW_FLAGS(w)   ((uint32_t)(w) >> 29)                 /* BRB_REC_* */
+#define BRB_ROW_MINUS(w)   (((uint32_t)(w) >> 28) & 1u)          /* tx_strand == '-' */
+#define BRB_ROW_INLINE     (1u << 27)                            /* set: BRB_ROW_CIGAR(w) is the CIGAR word itself */
+#define BRB_ROW_CIGAR(w)   ((uint32_t)(w) & 0x07ffffffu)
 
 typedef struct brb_stats {
   uint64_t n_launches;                  /* kernels launched by the last brb_project* call */
@@ -157,6 +169,7 @@ int brb_ctx_stats(const brb_ctx* ctx, brb_stats* out);
 /* BRB_OPT_ORDERED_ROWS != 0: one more pass on the device moves the unit blocks into the reference's emit order
  * (group_rec_off is then valid and aln_rec_off is ascending).  Costs one streaming copy of the rows. */
 #define BRB_OPT_ORDERED_ROWS 3
+#define BRB_OPT_PACKED_ROWS 4      /* rows as 16-byte records (brb_batch_out::packed_rows); ignored while BRB_OPT_ORDERED_ROWS is set */
 int brb_ctx_set_option(brb_ctx* ctx, int option, int value);
 /* CUDA-event stopwatch on the ctx stream (what bench.py brackets its K timed steps with). */
 int brb_ctx_timer_start(brb_ctx* ctx);

@@ -26,7 +26,7 @@ struct PortEngine : EngineIf {
       if (acnt[a] == 0) aoff[a] = r;
       acnt[a] += (po.flags[r] & BRB_REC_PAIRED) ? 2 : 1;
     }
-    out.aln_rec_off = aoff.data(); out.aln_rec_cnt = acnt.data();
+    out.aln_rec_off = aoff.data(); out.aln_rec_cnt = acnt.data(); out.packed_rows = nullptr;
     return 0;
   }
   std::string last_error() override { return "oracle port error"; }

@@ -18,13 +18,15 @@ def _check(wl, what):
         for bi, b in enumerate(wl["batches"]):
             exp = oracle_lib.port_project(ix, p, b)
             # every front kernel: the default choice (short-read fast-path kernel where it applies), the short-read
-            # kernel without the fast path, and the generic one; rows as unit blocks (default) and in emit order
-            for generic, nofast, ordered in ((0, 0, 0), (0, 1, 0), (1, 0, 0), (0, 0, 1)):
+            # kernel without the fast path, and the generic one; rows as unit blocks (default), in emit order, and as
+            # 16-byte packed records
+            for generic, nofast, ordered, packed in ((0, 0, 0, 0), (0, 1, 0, 0), (1, 0, 0, 0), (0, 0, 1, 0), (0, 0, 0, 1), (1, 0, 0, 1)):
                 eng.set_option(capi.OPT_GENERIC_FRONT, generic)
                 eng.set_option(capi.OPT_NO_FASTPATH, nofast)
                 eng.set_option(capi.OPT_ORDERED_ROWS, ordered)
+                eng.set_option(capi.OPT_PACKED_ROWS, packed)
                 got = eng.project(p, b)
-                oracle_lib.assert_rows_equal(exp, got, f"{what} batch {bi} generic={generic} nofast={nofast} ordered={ordered}")
+                oracle_lib.assert_rows_equal(exp, got, f"{what} batch {bi} generic={generic} nofast={nofast} ordered={ordered} packed={packed}")
                 st = eng.stats()
                 assert st.n_rec == got["n_rec"] and st.n_launches > 0
                 assert st.n_matches == exp["n_matches"]
@@ -107,16 +109,51 @@ def test_rows_checksum_matches_oracle():
     G = b.desc.n_groups
     parts = [b.slice_groups(G * i // 5, G * (i + 1) // 5) for i in range(5)]
     with engine.Engine(ix) as eng:
-        for ordered in (0, 1):
+        for ordered, packed in ((0, 0), (1, 0), (0, 1)):
             eng.set_option(capi.OPT_ORDERED_ROWS, ordered)
-            assert engine.rows_checksum(eng.project(p, b, raw=True)) == want
+            eng.set_option(capi.OPT_PACKED_ROWS, packed)
+            o = eng.project(p, b, raw=True)
+            assert bool(o.packed_rows) == bool(packed) and bool(o.src_aln) != bool(packed)
+            assert engine.rows_checksum(o) == want
         ctxs = [eng.context() for _ in range(2)]
         try:
-            res = engine.project_pipelined(ctxs, p, parts, checksum=True)
-            assert (sum(r[4] for r in res) & 0xFFFFFFFFFFFFFFFF, sum(r[0] for r in res)) == want
+            for packed in (0, 1):
+                for c in ctxs:
+                    c.set_option(capi.OPT_PACKED_ROWS, packed)
+                res = engine.project_pipelined(ctxs, p, parts, checksum=True)
+                assert (sum(r[4] for r in res) & 0xFFFFFFFFFFFFFFFF, sum(r[0] for r in res)) == want
         finally:
             for c in ctxs:
                 c.close()
+
+
+def test_packed_rows_oversized_cigar_word():
+    """BRB_OPT_PACKED_ROWS keeps a one-word CIGAR inside the row record only below 2^27: a 9 Mb single-exon alignment
+    (word 9000000M = 0x8954400 >= 2^27) must come back through the length-prefixed pool, next to ordinary inline rows."""
+    from bramble_b200 import pack, synth
+    ann = synth.Annotation(["chr1"], [20_000_000], [
+        dict(id="G0.t0", gene="G0", chrom=0, strand="+", exons=[(1000, 12_000_000)], family=0),
+        dict(id="G0.t1", gene="G0", chrom=0, strand="+", exons=[(1000, 5000), (6000, 12_000_000)], family=0),
+        dict(id="G1.t0", gene="G1", chrom=0, strand="-", exons=[(13_000_000, 13_001_000), (13_002_000, 13_003_000)], family=1)])
+    tags = [("NH", "C", 1), ("HI", "C", 1), ("AS", "C", 100), ("NM", "C", 0)]
+
+    def rec(name, pos, cigar):
+        return dict(name=name, flag=0, chrom=0, pos=pos, mapq=60, cigar=cigar, mchrom=-1, mpos=-1, isize=0, seq="", qual="", tags=tags)
+    recs = [rec("a", 2000, [("M", 9_000_000)]),                           # inside t0's exon only ... and t1? no: it spans t1's intron
+            rec("b", 7000, [("M", 9_000_000)]),                           # inside t0's exon and t1's second exon
+            rec("c", 2000, [("M", 150)]),                                 # ordinary row, both transcripts
+            rec("d", 13_000_900, [("M", 100), ("N", 999), ("M", 50)])]         # spliced, '-' transcript
+    ix = pack.build_index(ann)
+    p = common.params_for("default")
+    b = pack.pack_batches(recs, ix, ann.chroms)[0]
+    exp = oracle_lib.port_project(ix, p, b)
+    assert exp["n_rec"] == 6 and any(len(c) == 1 and int(c[0]) >> 27 for c in exp["cigars"])
+    with engine.Engine(ix) as eng:
+        for packed in (0, 1):
+            eng.set_option(capi.OPT_PACKED_ROWS, packed)
+            oracle_lib.assert_rows_equal(exp, eng.project(p, b), f"oversized word packed={packed}")
+        raw = eng.project(p, b, raw=True)
+        assert raw.packed_rows and raw.n_cigar_words == 2 * sum(1 for c in exp["cigars"] if int(c[0]) >> 27)    # length word + CIGAR word each
 
 
 def test_multiple_bundles_and_ragged():
