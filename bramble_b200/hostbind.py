@@ -15,9 +15,9 @@ def _parse_cpulist(s):
 
 def gpu_numa_node(device):
     """NUMA node of CUDA device `device` (from its PCI address), or None when the platform does not say."""
-    import torch
-    p = torch.cuda.get_device_properties(device)
     try:
+        import torch
+        p = torch.cuda.get_device_properties(device)
         addr = "%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
         with open(f"/sys/bus/pci/devices/{addr}/numa_node") as fh:
             node = int(fh.read().strip())

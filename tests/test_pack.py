@@ -68,3 +68,16 @@ def test_sort_perm_is_a_permutation_sorted_by_start():
 def test_shard_dealing():
     assert shard.bundles_of_rank(7, 2, 0) == [0, 2, 4, 6] and shard.bundles_of_rank(7, 2, 1) == [1, 3, 5]
     assert [shard.owner_of(k, 4) for k in range(6)] == [0, 1, 2, 3, 0, 1]
+
+
+def test_hostbind_cpulist_and_no_gpu():
+    """Host placement helper: cpulist parsing, and a box without NUMA information (or without a GPU) is left untouched."""
+    import os
+    from bramble_b200 import hostbind
+    assert hostbind._parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    assert hostbind._parse_cpulist("") == set()
+    before = os.sched_getaffinity(0)
+    info = hostbind.bind_to_gpu_node(0)
+    if info["numa_node"] is None:
+        assert not info["bound"] and os.sched_getaffinity(0) == before
+    os.sched_setaffinity(0, before)
