@@ -34,7 +34,7 @@ struct DevIndex {
   const uint32_t* table_off;     // n_tables+1
   const int32_t* st;             // sorted starts (search key, SoA)
   const int32_t* pmax;           // running max of `en` inside each table (monotone -> binary search)
-  const Rec* rec;
+  const uint4* rkey; const uint4* rlink;   // the records' two halves (see rec_key / rec_link)
   const uint32_t* gprev;         // record index of the genomically previous exon of the same tid (NONE if none)
   const uint32_t* bin_off;       // n_tables+1 offsets into bins
   const uint2* bins;             // per table, per bin b: .x = first i with pmax[i] > b<<shift, .y = first i with st[i] >= b<<shift
@@ -85,13 +85,21 @@ __device__ __forceinline__ bool ctl_overflow(const Ctl* c) {
 
 __device__ __forceinline__ uint4 ldg4(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
 
+// Record halves.  VAR_SPLIT_REC=0 (default): the 32-byte records as one interleaved array (key, link, key, link ...) --
+// a candidate that passes the filter finds its link half in the sector its key came in.  VAR_SPLIT_REC=1: two dense
+// arrays (a warp walking consecutive keys touches half the lines); measured slower, 0.627 vs 0.590 ms for k_front_fast
+// on the C2 workload, because 56 % of the candidates go on to read the link half from a second line.
+#ifndef VAR_SPLIT_REC
+#define VAR_SPLIT_REC 0
+#endif
 struct RecKey { int32_t st, en; uint32_t tid, pos_start; };
-__device__ __forceinline__ RecKey rec_key(const Rec* r, uint32_t i) {
-  uint4 v = ldg4(&r[i]); RecKey k; k.st = (int32_t)v.x; k.en = (int32_t)v.y; k.tid = v.z; k.pos_start = v.w; return k;
+__device__ __forceinline__ const uint4* rec_key_ptr(const DevIndex& ix, uint32_t i) { return VAR_SPLIT_REC ? ix.rkey + i : ix.rkey + 2 * (size_t)i; }
+__device__ __forceinline__ RecKey rec_key(const DevIndex& ix, uint32_t i) {
+  uint4 v = ldg4(rec_key_ptr(ix, i)); RecKey k; k.st = (int32_t)v.x; k.en = (int32_t)v.y; k.tid = v.z; k.pos_start = v.w; return k;
 }
 struct RecLink { int32_t gprev_en, gnext_st; uint32_t gnext, meta; };
-__device__ __forceinline__ RecLink rec_link(const Rec* r, uint32_t i) {
-  uint4 v = ldg4(reinterpret_cast<const uint4*>(&r[i]) + 1);
+__device__ __forceinline__ RecLink rec_link(const DevIndex& ix, uint32_t i) {
+  uint4 v = ldg4(VAR_SPLIT_REC ? ix.rlink + i : ix.rkey + 2 * (size_t)i + 1);
   RecLink k; k.gprev_en = (int32_t)v.x; k.gnext_st = (int32_t)v.y; k.gnext = v.z; k.meta = v.w; return k;
 }
 

@@ -233,7 +233,13 @@ int brb_index_create(int device, const brb_index_desc* d, brb_index** out) {
   if (!rc) rc = up(ix->table_off, toff.data(), toff.size() * 4);
   if (!rc) rc = up(ix->st, d->st, n * 4);
   if (!rc) rc = up(ix->pmax, pmax.data(), n * 4);
-  if (!rc) rc = up(ix->rec, rec.data(), n * sizeof(Rec));
+  if (VAR_SPLIT_REC) {                  // keys first, links after them (dev_common.cuh: rec_key / rec_link)
+    static_assert(sizeof(Rec) == 32, "a record is a 16-byte key half and a 16-byte link half");
+    std::vector<uint4> halves(2 * (size_t)n);
+    const uint4* src = reinterpret_cast<const uint4*>(rec.data());
+    for (size_t i = 0; i < n; i++) { halves[i] = src[2 * i]; halves[n + i] = src[2 * i + 1]; }
+    if (!rc) rc = up(ix->rec, halves.data(), halves.size() * sizeof(uint4));
+  } else if (!rc) rc = up(ix->rec, rec.data(), n * sizeof(Rec));
   if (!rc) rc = up(ix->gprev, gprev.data(), n * 4);
   if (!rc) rc = up(ix->bin_off, boff.data(), boff.size() * 4);
   if (!rc) rc = up(ix->bins, bins.data(), bins.size() * sizeof(uint2));
@@ -245,7 +251,7 @@ int brb_index_create(int device, const brb_index_desc* d, brb_index** out) {
   }
   if (rc) { ix->release_all(); delete ix; return rc; }
   ix->d.table_off = ix->table_off.as<uint32_t>(); ix->d.st = ix->st.as<int32_t>(); ix->d.pmax = ix->pmax.as<int32_t>();
-  ix->d.rec = ix->rec.as<Rec>(); ix->d.gprev = ix->gprev.as<uint32_t>();
+  ix->d.rkey = ix->rec.as<uint4>(); ix->d.rlink = ix->rec.as<uint4>() + (VAR_SPLIT_REC ? n : 0); ix->d.gprev = ix->gprev.as<uint32_t>();
   ix->d.bin_off = ix->bin_off.as<uint32_t>(); ix->d.bins = ix->bins.as<uint2>();
   ix->d.chrom_off = ix->d.n_chrom ? ix->chrom_off.as<uint64_t>() : nullptr;
   ix->d.genome = ix->d.n_chrom ? ix->genome.as<uint8_t>() : nullptr;

@@ -95,8 +95,8 @@ __device__ bool walk(const DevIndex& ix, const DevBatch& b, const brb_params& p,
   uint32_t n_seg_total = BUILD ? w.n_seg : 0;
   // segment 0
   uint32_t qs = rx.qs0, qe = rx.qe0;
-  RecKey key = rec_key(ix.rec, first_rec);
-  RecLink lk = rec_link(ix.rec, first_rec);
+  RecKey key = rec_key(ix, first_rec);
+  RecLink lk = rec_link(ix, first_rec);
   Hit h; int status = exon_status(n_ex, 0);
   filter_hit(p, minus, status, qs, qe, (uint32_t)key.st, (uint32_t)key.en, key.pos_start, h);
   uint32_t prev_gs = (uint32_t)key.st, prev_ge = (uint32_t)key.en, prev_qs = qs, prev_qe = qe;
@@ -147,7 +147,7 @@ __device__ bool walk(const DevIndex& ix, const DevBatch& b, const brb_params& p,
     {
       uint32_t r = lk.gnext; int32_t r_st = lk.gnext_st;
       while (r != NONE && r_st < (int32_t)qe) {
-        const RecKey K = rec_key(ix.rec, r); const RecLink Lr = rec_link(ix.rec, r);
+        const RecKey K = rec_key(ix, r); const RecLink Lr = rec_link(ix, r);
         if ((int32_t)qs < K.en) {
           Hit hh;
           if (filter_hit(p, minus, status, qs, qe, (uint32_t)K.st, (uint32_t)K.en, K.pos_start, hh)) {
@@ -169,7 +169,7 @@ __device__ bool walk(const DevIndex& ix, const DevBatch& b, const brb_params& p,
         // getGuideExonForTid on its own coordinates returns that very record
         const uint32_t grec = __ldg(&ix.gprev[rec]);
         if (grec == NONE) return false;             // coordinates (0,0)
-        const RecKey gk = rec_key(ix.rec, grec);
+        const RecKey gk = rec_key(ix, grec);
         if (!BUILD) {
           if ((uint32_t)(gk.en - gk.st) > p.max_error_exon) return false;
           if ((uint32_t)gk.st == prev_gs && (uint32_t)gk.en == prev_ge) return false;
@@ -197,7 +197,7 @@ __device__ bool walk(const DevIndex& ix, const DevBatch& b, const brb_params& p,
   }
   if (BUILD) {
     if (has_rc) {                                   // RIGHTC segment, build_right_clip_segment :548-598
-      RecKey lastk = rec_key(ix.rec, w.last_rec);
+      RecKey lastk = rec_key(ix, w.last_rec);
       last_pos = lastk.pos_start - (uint32_t)rres->rc;
       for (uint32_t x = 0; x < rres->cig_len; x++) {
         const uint32_t wd = rpool[rres->cig_off + x], op = wd & 0xfu, len = wd >> 4;
@@ -217,17 +217,17 @@ __device__ bool walk(const DevIndex& ix, const DevBatch& b, const brb_params& p,
 // exon 0, so the common case is decided by two compares on rec0's own link words.
 __device__ __forceinline__ bool dedupe_first(const DevIndex& ix, const brb_params& p, const ReadExons& rx, int s, uint32_t& rec0) {
   const uint32_t n_ex = rx.n_ex, qs = rx.qs0, qe = rx.qe0;
-  const RecLink lk = rec_link(ix.rec, rec0);
+  const RecLink lk = rec_link(ix, rec0);
   if (lk.gprev_en <= (int32_t)qs && lk.gnext_st >= (int32_t)qe) return true;
   const int status = exon_status(n_ex, 0);
   for (uint32_t r = __ldg(&ix.gprev[rec0]); r != NONE; r = __ldg(&ix.gprev[r])) {      // an earlier surviving hit owns the slot
-    const RecKey k = rec_key(ix.rec, r);
+    const RecKey k = rec_key(ix, r);
     if (k.en <= (int32_t)qs) break;
     if (passes_filter(p, s, status, qs, qe, (uint32_t)k.st, (uint32_t)k.en)) return false;
   }
   uint32_t r = lk.gnext; int32_t r_st = lk.gnext_st;
   while (r != NONE && r_st < (int32_t)qe) {                                            // the last surviving hit provides the content
-    const RecKey k = rec_key(ix.rec, r); const RecLink l2 = rec_link(ix.rec, r);
+    const RecKey k = rec_key(ix, r); const RecLink l2 = rec_link(ix, r);
     if ((int32_t)qs < k.en && passes_filter(p, s, status, qs, qe, (uint32_t)k.st, (uint32_t)k.en)) rec0 = r;
     r = l2.gnext; r_st = l2.gnext_st;
   }
@@ -258,7 +258,7 @@ __device__ __forceinline__ bool build_one(const DevIndex& ix, const DevBatch& b,
     else keep = false;
   }
   if (keep) {
-    M.rec[c] = make_uint4(s ? lp : fp, (m.n << 1) | (uint32_t)s, m.n == 1 ? m.last : ioff, rec_key(ix.rec, w.first_rec).tid);
+    M.rec[c] = make_uint4(s ? lp : fp, (m.n << 1) | (uint32_t)s, m.n == 1 ? m.last : ioff, rec_key(ix, w.first_rec).tid);
     if (M.sim) { M.sim[c] = sim_score; M.clip[c] = m.clip; }
   } else M.rec[c] = make_uint4(0, 0, 0, NONE);
   return keep;
@@ -383,7 +383,7 @@ __device__ __forceinline__ bool eval_short(const DevIndex& ix, const DevBatch& b
   Hit h;
   filter_hit(p, minus, status, qs, qe, (uint32_t)key.st, (uint32_t)key.en, key.pos_start, h);
   const uint32_t first_pos = h.pos; uint32_t last_pos = h.pos;
-  if (n_ex > 1 && lk.gnext != NONE) asm volatile("prefetch.global.L1 [%0];" ::"l"(&ix.rec[lk.gnext]));   // the walk continues there
+  if (n_ex > 1 && lk.gnext != NONE) asm volatile("prefetch.global.L1 [%0];" ::"l"(rec_key_ptr(ix, lk.gnext)));   // the walk continues there
   build_match_short<SIM>(m, status, qs, qe, (uint32_t)key.st, (uint32_t)key.en, h, true, n_ex == 1);
   uint32_t prev_eid = lk.meta & 0xffu;
   for (uint32_t j = 1; j < n_ex; j++) {
@@ -395,7 +395,7 @@ __device__ __forceinline__ bool eval_short(const DevIndex& ix, const DevBatch& b
     if ((int32_t)qs < key.en && passes_filter(p, minus, status, qs, qe, (uint32_t)key.st, (uint32_t)key.en)) return false;   // same guide exon twice: gap 0
     uint32_t r = lk.gnext; int32_t r_st = lk.gnext_st;
     while (r != NONE && r_st < (int32_t)qe) {
-      const RecKey K = rec_key(ix.rec, r); const RecLink Lr = rec_link(ix.rec, r);
+      const RecKey K = rec_key(ix, r); const RecLink Lr = rec_link(ix, r);
       if ((int32_t)qs < K.en) {
         Hit hh;
         if (filter_hit(p, minus, status, qs, qe, (uint32_t)K.st, (uint32_t)K.en, K.pos_start, hh)) { if (cnt == 0) { nk = K; nl = Lr; h = hh; } cnt++; }

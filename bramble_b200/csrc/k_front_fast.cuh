@@ -57,7 +57,7 @@ __device__ __forceinline__ int fast_short(const DevIndex& ix, const DevBatch& b,
       qs = __ldg(&b.exon_st[rx.e0 + j]); qe = __ldg(&b.exon_en[rx.e0 + j]);
       if (qe <= qs) return FAST_DEFER;
       if (r == NONE) return miss;
-      const RecKey k = rec_key(ix.rec, r); const RecLink l = rec_link(ix.rec, r);
+      const RecKey k = rec_key(ix, r); const RecLink l = rec_link(ix, r);
       if ((uint32_t)k.st != qs) return miss;
       const uint32_t eid = l.meta & 0xffu;
       if (((eid - prev_eid) & 0xffu) != 1) return miss;                             // correct_for_gaps, src/evaluate.cpp:131-140
@@ -155,7 +155,7 @@ __global__ void __launch_bounds__(256, VAR_FAST_CTAS) k_front_fast(DevIndex ix, 
           RecKey key; RecLink lk;
           if (ok) {
             ok = dedupe_first(ix, p, ox, s, rec0);
-            if (ok) { key = rec_key(ix.rec, rec0); lk = rec_link(ix.rec, rec0); ok = eval_short<false>(ix, b, p, ox, s, key, lk, ipool + ioff, pos, ilen, word, sim); }
+            if (ok) { key = rec_key(ix, rec0); lk = rec_link(ix, rec0); ok = eval_short<false>(ix, b, p, ox, s, key, lk, ipool + ioff, pos, ilen, word, sim); }
           }
           if (ok) { M.rec[slot] = make_uint4(pos, (ilen << 1) | (uint32_t)s, ilen == 1 ? word : ioff, key.tid); atomicAdd(&s_nv[L], 1u); }
           else M.rec[slot] = make_uint4(0, 0, 0, NONE);
@@ -177,13 +177,13 @@ __global__ void __launch_bounds__(256, VAR_FAST_CTAS) k_front_fast(DevIndex ix, 
       const uint32_t rec0 = s ? s_al[7][L] + (idx - o_n0) : s_al[6][L] + idx;
       bool sv = false, ov = false; RecKey key;
       if (actv) {
-        key = rec_key(ix.rec, rec0);
+        key = rec_key(ix, rec0);
         ov = (int32_t)ox.qs0 < key.en;                     // st < qe holds for every record below hi
         sv = ov && slots_fit && passes_filter(p, s, exon_status(ox.n_ex, 0), ox.qs0, ox.qe0, (uint32_t)key.st, (uint32_t)key.en);
       }
       my_hits += __popc(__ballot_sync(0xffffffffu, ov)) * (lane == 0);
       bool fast = false; uint32_t pos = 0, word = 0;
-      if (sv) { const int v = fast_short(ix, b, strict, ox, s, key, rec_link(ix.rec, rec0), pos, word); fast = v == FAST_MATCH; sv = v != FAST_REJECT; }
+      if (sv) { const int v = fast_short(ix, b, strict, ox, s, key, rec_link(ix, rec0), pos, word); fast = v == FAST_MATCH; sv = v != FAST_REJECT; }
       const uint32_t B_sv = __ballot_sync(0xffffffffu, sv), B_fast = __ballot_sync(0xffffffffu, fast), B_q = B_sv & ~B_fast;
       const uint32_t slot = sbase + wr + __popc(B_sv & lt_mask);
       if (fast) M.rec[slot] = make_uint4(pos, 2u | (uint32_t)s, word, key.tid);

@@ -118,7 +118,7 @@ __global__ void __launch_bounds__(256) k_front(DevIndex ix, DevBatch b, brb_para
         const uint32_t i = o_lo + (item - o_ex);
         bool sv = false;
         if (actv) {
-          const RecKey k = rec_key(ix.rec, i);
+          const RecKey k = rec_key(ix, i);
           sv = (int32_t)rx.qs0 < k.en && passes_filter(p, s, exon_status(rx.n_ex, 0), rx.qs0, rx.qe0, (uint32_t)k.st, (uint32_t)k.en);
         }
         const uint32_t B = __ballot_sync(0xffffffffu, sv);
@@ -242,7 +242,7 @@ __global__ void __launch_bounds__(256, VAR_FRONT_CTAS) k_front_short(DevIndex ix
       uint32_t rec0 = s ? s_al[7][L] + (idx - o_n0) : s_al[6][L] + idx;
       bool sv = false, ov = false; RecKey key;
       if (actv) {
-        key = rec_key(ix.rec, rec0);
+        key = rec_key(ix, rec0);
         ov = (int32_t)ox.qs0 < key.en;                     // st < qe holds for every record below hi
         sv = ov && passes_filter(p, s, o_status, ox.qs0, ox.qe0, (uint32_t)key.st, (uint32_t)key.en);
       }
@@ -252,12 +252,12 @@ __global__ void __launch_bounds__(256, VAR_FRONT_CTAS) k_front_short(DevIndex ix
       const uint32_t ioff = warp_pool_alloc(wp, &ctl->n_ideal, cap_ideal, want, lane, pool_fit);
       bool ok = false; uint32_t pos = 0, ilen = 0, word = 0; double sim = 0.0;
       if (sv && pool_fit && slots_fit) {
-        RecLink lk = rec_link(ix.rec, rec0);
+        RecLink lk = rec_link(ix, rec0);
         ok = true;
         if (lk.gprev_en > (int32_t)ox.qs0 || lk.gnext_st < (int32_t)ox.qe0) {      // a neighbour exon of this tid also overlaps read exon 0
           const uint32_t r1 = rec0;
           ok = dedupe_first(ix, p, ox, s, rec0);
-          if (ok && rec0 != r1) { key = rec_key(ix.rec, rec0); lk = rec_link(ix.rec, rec0); }
+          if (ok && rec0 != r1) { key = rec_key(ix, rec0); lk = rec_link(ix, rec0); }
         }
         if (ok) ok = eval_short<SIM>(ix, b, p, ox, s, key, lk, ipool + ioff, pos, ilen, word, sim);
       }

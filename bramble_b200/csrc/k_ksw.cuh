@@ -163,9 +163,9 @@ __device__ uint32_t collect_exons(const DevIndex& ix, int32_t refid, bool left, 
     i++;
     // transcript-order neighbour away from the read = genomic neighbour on that side; getGuideExonForTid on the
     // neighbour's own coordinates returns that very record (exons of a tid are disjoint)
-    const uint32_t nx = left ? __ldg(&ix.gprev[cur]) : rec_link(ix.rec, cur).gnext;
+    const uint32_t nx = left ? __ldg(&ix.gprev[cur]) : rec_link(ix, cur).gnext;
     if (nx == NONE) { if (i == 1) return 0; break; }
-    const RecKey k = rec_key(ix.rec, nx);
+    const RecKey k = rec_key(ix, nx);
     const uint32_t len = (uint32_t)(k.en - k.st);
     if (WRITE) {
       if (left) { for (uint32_t pos = (uint32_t)k.en; pos > (uint32_t)k.st && w < tlen; pos--) { const uint64_t o = base + (pos - 1) - 1; dst[w++] = o < lim ? ix.genome[o] : 4; } }
@@ -190,13 +190,13 @@ __device__ __forceinline__ bool rescue_inputs(const DevIndex& ix, const DevBatch
   const uint32_t e0 = b.exon_off[a], n_ex = b.exon_off[a + 1] - e0;
   if (side == 0) {
     if (!hl || nl < 5) return false;
-    const RecKey k = rec_key(ix.rec, first_rec); Hit h;
+    const RecKey k = rec_key(ix, first_rec); Hit h;
     filter_hit(p, s, exon_status(n_ex, 0), b.exon_st[e0], b.exon_en[e0], (uint32_t)k.st, (uint32_t)k.en, k.pos_start, h);
     if (h.left_gap > 0) return false;
     total = nl + h.left_ins; rec = first_rec;
   } else {
     if (!hr || nr < 5) return false;
-    const RecKey k = rec_key(ix.rec, last_rec); Hit h;
+    const RecKey k = rec_key(ix, last_rec); Hit h;
     filter_hit(p, s, exon_status(n_ex, n_ex - 1), b.exon_st[e0 + n_ex - 1], b.exon_en[e0 + n_ex - 1], (uint32_t)k.st, (uint32_t)k.en, k.pos_start, h);
     if (h.right_gap > 0) return false;
     total = h.right_ins + nr; rec = last_rec;

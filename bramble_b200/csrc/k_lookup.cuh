@@ -39,7 +39,7 @@ __device__ __forceinline__ void warp_flat_count(const DevIndex& ix, const brb_pa
     const int o_st = __shfl_sync(0xffffffffu, status, L);
     bool ov = false, sv = false;
     if (act) {
-      const RecKey k = rec_key(ix.rec, o_lo + (item - o_ex));
+      const RecKey k = rec_key(ix, o_lo + (item - o_ex));
       ov = (int32_t)o_qs < k.en;                           // st < qe holds for every record below hi
       sv = ov && passes_filter(p, minus, o_st, o_qs, o_qe, (uint32_t)k.st, (uint32_t)k.en);
     }
@@ -70,7 +70,7 @@ __global__ void k_lookup_queries(DevIndex ix, brb_params p, uint32_t nq, const i
     const uint32_t qs = qs_[q], qe = qe_[q];
     uint32_t lo, hi; overlap_range(ix, refid[q], minus, qs, qe, lo, hi);
     for (uint32_t i = lo; i < hi; i++) {
-      RecKey k = rec_key(ix.rec, i);
+      RecKey k = rec_key(ix, i);
       if ((int32_t)qs >= k.en) continue;
       Hit h;
       if (!filter_hit(p, minus, status_[q], qs, qe, (uint32_t)k.st, (uint32_t)k.en, k.pos_start, h)) continue;
