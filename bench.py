@@ -273,7 +273,7 @@ def main():
     torch.cuda.set_device(local)
     from bramble_b200 import hostbind
     # one process per GPU: keep the rank's threads and its pinned staging pages on the GPU's NUMA node
-    host = hostbind.bind_to_gpu_node(local) if (world > 1 and not args.no_bind) else hostbind.describe(local)
+    host = hostbind.bind_to_gpu_node(local, local, int(os.environ.get("LOCAL_WORLD_SIZE", world))) if (world > 1 and not args.no_bind) else hostbind.describe(local)
     host["cpus"] = os.cpu_count()
     A, ix, B = workload(1000 + rank, args.names, args.workload)
     n_aln = int(B.desc.n_aln)
@@ -301,11 +301,9 @@ def main():
         eng.run_resident(p)
     st = eng.stats()
     sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.prepare()
+    sampler.prepare()                     # every rank watches its own GPU; rank 0's samples go into `clocks`, the medians of all into `host`
     barrier()
-    if rank == 0:
-        sampler.start()
+    sampler.start()
     phase = {k: 0.0 for k in ("ms_lookup", "ms_chain", "ms_rescue", "ms_finalize", "ms_pair", "ms_merge")}
     eng.timer_start()
     launches = 0
@@ -319,7 +317,7 @@ def main():
         for k in phase:
             phase[k] += getattr(s, k)
     barrier()
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop()
     # the same with BRB_OPT_ORDERED_ROWS: one more streaming pass (scan + k_place) lays the rows out in emit order on the device
     ms_ordered = ms_packed = None
     if not args.no_e2e:
@@ -388,9 +386,10 @@ def main():
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
     total_aln = float(t[2].item()) if world > 1 else float(n_aln)
-    by_rank = [torch.zeros(3, dtype=torch.float64, device=f"cuda:{local}") for _ in range(world)]
+    by_rank = [torch.zeros(6, dtype=torch.float64, device=f"cuda:{local}") for _ in range(world)]
     mine = torch.tensor([e2e_s * 1e3 / max(1, args.steps), float(host["numa_node"] if host["numa_node"] is not None else -1),
-                         float(host["cpus_allowed"])], dtype=torch.float64, device=f"cuda:{local}")
+                         float(host["cpus_allowed"]), ms / max(1, args.steps), float(clocks["sm_mhz"] or 0),
+                         float(any(r != "sw_power_cap" for r in clocks["reasons"]))], dtype=torch.float64, device=f"cuda:{local}")
     if world > 1:
         dist.all_gather(by_rank, mine)
     else:
@@ -439,7 +438,9 @@ def main():
                     "rows": checks["default"][1], "checksum": "%016x" % checks["default"][0],
                     "agree": len({(int(c[0]), int(c[1])) for c in checks.values()}) == 1},
                 "host": {**host, "e2e_ms_per_step_by_rank": [round(float(x[0].item()), 3) for x in by_rank],
-                         "numa_node_by_rank": [int(x[1].item()) for x in by_rank], "cpus_allowed_by_rank": [int(x[2].item()) for x in by_rank]},
+                         "numa_node_by_rank": [int(x[1].item()) for x in by_rank], "cpus_allowed_by_rank": [int(x[2].item()) for x in by_rank],
+                         "ms_per_step_by_rank": [round(float(x[3].item()), 4) for x in by_rank], "sm_mhz_by_rank": [int(x[4].item()) for x in by_rank],
+                         "slowdown_seen_by_rank": [bool(x[5].item()) for x in by_rank]},
                 "work": {"alignments_per_gpu": n_aln, "candidates": int(st.n_candidates), "matches": int(st.n_matches), "records": int(st.n_rec)}}
         if args.gpus == 1 and not args.no_cpu_baseline:
             try:

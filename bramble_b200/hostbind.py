@@ -31,12 +31,25 @@ def describe(device):
     return {"numa_node": node, "cpus_allowed": len(os.sched_getaffinity(0)), "bound": False}
 
 
-def bind_to_gpu_node(device):
-    """Restrict this process to the CPUs of the GPU's NUMA node (intersected with what it may already use).
-    Returns what was done; a platform without NUMA information is left untouched."""
+def bind_to_gpu_node(device, local_rank=None, local_world=None):
+    """Restrict this process to the CPUs of the GPU's NUMA node (intersected with what it may already use).  On a
+    platform without NUMA information the process is left where it is -- unless local_rank / local_world are
+    given: the allowed CPUs are then dealt out evenly, rank r of n taking the r-th slice, so that the ranks' host
+    threads (each rank's main thread sits in the launch -> synchronise loop of every step) do not preempt one
+    another.  Returns what was done."""
     info = describe(device)
     node = info["numa_node"]
     if node is None:
+        if local_rank is not None and local_world and local_world > 1:
+            cpus = sorted(os.sched_getaffinity(0))
+            per = len(cpus) // local_world
+            if per >= 2:
+                mine = set(cpus[local_rank * per:(local_rank + 1) * per])
+                try:
+                    os.sched_setaffinity(0, mine)
+                    info.update(cpus_allowed=len(mine), bound=True, how="even slice of the allowed CPUs")
+                except OSError:
+                    pass
         return info
     try:
         with open(f"/sys/devices/system/node/node{node}/cpulist") as fh:
