@@ -469,7 +469,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
                                     c->r_right.as<RescueSeg>(), c->rpool.as<uint32_t>(), c->ipool.as<uint32_t>(), M); L++;
       CU(cudaEventRecord(c->ev[4], st));
     }
-    // ---- phase 5: pairing, CIGAR merge, rows in bundle order (one kernel; batch offsets by decoupled look-back)
+    // ---- phase 5: pairing, CIGAR merge, rows (one kernel; row and CIGAR room claimed per batch in completion order)
     BackIn pv; pv.a_cand = c->a_cand.as<uint4>(); pv.m_rec = c->m_rec.as<uint4>(); pv.m_sim = M.sim; pv.m_clip = M.clip; pv.ipool = c->ipool.as<uint32_t>();
     Rows o; o.src = c->o_src.as<uint32_t>(); o.tid = c->o_tid.as<uint32_t>(); o.pos = c->o_pos.as<uint32_t>(); o.strand = c->o_strand.as<int8_t>();
     o.flags = c->o_flags.as<uint8_t>(); o.sim = c->o_sim.as<double>(); o.clip = c->o_clip.as<int32_t>(); o.coff = c->o_coff.as<uint32_t>();

@@ -156,6 +156,7 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
     s_off[lane] = off; s_excl[lane] = excl; s_ro[lane] = ro; s_nrc[lane] = nrc; s_mro[lane] = mro; s_mnrc[lane] = mnrc; s_words[lane] = 0; s_rsum[lane] = rsum; s_mrsum[lane] = mrsum;
     __syncwarp();
     uint32_t rows = 0, words = 0, qn = 0;
+    int32_t adj = 0;                                        // PACKED: CIGAR words of my rows that are not pool words (in-record) minus length words
     // general merge of one emitted row (pair): all lanes call, `go` lanes work
     auto merge_rows = [&](bool go, uint32_t L, uint32_t sidx, uint32_t tid, uint32_t part, const uint4& mr, const uint4& pr) {
       const bool paired = part != SELF;
@@ -213,6 +214,7 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
         const uint32_t mine = bit_range(excl > base ? excl - base : 0, incl - base < 32 ? incl - base : 32);
         rows += __popc(B_e & mine) + __popc(B_p & mine);
         if (!PACKED) words += __popc(B_e & ~B_s & mine) + __popc(B_p & ~B_s & mine);
+        else adj += (int32_t)(__popc(B_e & ~B_s & mine) + __popc(B_p & ~B_s & mine)) - (int32_t)(__popc(B_s & mine) + __popc(B_s & B_p & mine));
       }
       const uint32_t sidx = staged ? item : c;
       if (actv) stage[sidx] = make_uint4(emitted ? tid : NONE, slow ? L : (PACKED ? 0u : (paired ? 2u : 1u)), part, slow ? PENDING : INLINE);
@@ -250,6 +252,10 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
     const unsigned long long agg = (unsigned long long)R_b | ((unsigned long long)W_b << 32);
     unsigned long long claim = 0;
     if (lane == 0) { claim = atomicAdd(&ctl->claimed, agg); if (ORDERED) { tl.agg[wb] = agg; tl.claim[wb] = claim; } }
+    if (PACKED) {                                           // the work counter stays the CIGAR word count of the rows, whatever the layout
+      const int32_t tot = (int32_t)W_b + __reduce_add_sync(0xffffffffu, adj);
+      if (lane == 0) atomicAdd(&ctl->out_words, (unsigned long long)tot);
+    }
     claim = __shfl_sync(0xffffffffu, claim, 0);
     const uint32_t prow0 = (uint32_t)claim, pword0 = (uint32_t)(claim >> 32);
     const uint32_t row0 = prow0 + irows - rows, word0 = pword0 + iwords - words;
@@ -322,7 +328,7 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
         if (!skip) {                                        // the totals claimed are the result sizes
           const unsigned long long tot = atomicAdd(&ctl->claimed, 0ull);
           const uint32_t R = (uint32_t)tot, W = (uint32_t)(tot >> 32);
-          ctl->n_rows = R; ctl->n_outw = W; ctl->out_words = W;
+          ctl->n_rows = R; ctl->n_outw = W; if (!PACKED) ctl->out_words = W;
           if (!PACKED && R <= cap_rows && W <= cap_outw) o.coff[R] = W;
         }
         ctl_publish_and_reset(ctl, host_result);

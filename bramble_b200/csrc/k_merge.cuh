@@ -1,6 +1,6 @@
 // Kernel group 4: CIGAR projection -- merge the alignment's real CIGAR with the ideal (transcript-side)
 // CIGAR of the match.  Replaces merge_ops / merge_cigars / get_new_cigar (reference src/bam.cpp:22-315,
-// 443-472).  Device function, called by k_pair_a for every emitted row.
+// 443-472).  Device function, called by k_back for every emitted row that is not the trivial one-M case.
 #pragma once
 #include "dev_common.cuh"
 

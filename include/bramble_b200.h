@@ -132,7 +132,7 @@ typedef struct brb_stats {
   uint64_t n_launches;                  /* kernels launched by the last brb_project* call */
   float    kernel_ms;                   /* CUDA-event time of those kernels on the ctx stream */
   float    ms_lookup, ms_chain, ms_rescue, ms_finalize, ms_pair, ms_merge;   /* per phase: front kernel (lookup + evaluation; on the
-                                         * clip-rescue path lookup | chain | rescue | build), k_pair_a, scan + k_pair_b */
+                                         * clip-rescue path lookup | chain | rescue | build), k_back, and -- BRB_OPT_ORDERED_ROWS only -- scan + k_place + k_group_rows */
   uint64_t n_candidates, n_matches, n_rescue, n_rec;
   uint64_t alg_bytes;                   /* algorithmic bytes of the batch (DESIGN.md formula) */
   uint64_t h2d_bytes, d2h_bytes;

@@ -17,6 +17,7 @@ def _check(wl, what):
     with engine.Engine(ix) as eng:
         for bi, b in enumerate(wl["batches"]):
             exp = oracle_lib.port_project(ix, p, b)
+            alg = None
             # every front kernel: the default choice (short-read fast-path kernel where it applies), the short-read
             # kernel without the fast path, and the generic one; rows as unit blocks (default), in emit order, and as
             # 16-byte packed records
@@ -29,6 +30,9 @@ def _check(wl, what):
                 oracle_lib.assert_rows_equal(exp, got, f"{what} batch {bi} generic={generic} nofast={nofast} ordered={ordered} packed={packed}")
                 st = eng.stats()
                 assert st.n_rec == got["n_rec"] and st.n_launches > 0
+                if generic == 0 and nofast == 0:          # the work counters do not depend on the row layout
+                    alg = alg if (ordered or packed) else int(st.alg_bytes)
+                    assert int(st.alg_bytes) == alg, (ordered, packed)
                 assert st.n_matches == exp["n_matches"]
                 assert st.n_rescue == exp["n_rescue"]
             n_rec += got["n_rec"]
