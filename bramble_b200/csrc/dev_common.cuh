@@ -41,6 +41,16 @@ struct DevIndex {
   const uint64_t* chrom_off; const uint8_t* genome;   // codes 0..4, or null
 };
 
+// Batches of 32 alignments a persistent warp takes per ticket (one same-address atomic each).  Measured on the C2
+// workload: two per ticket take 5 us off k_front_fast and add 5 us to k_back (uneven batches), four cost both.
+#ifndef VAR_TICKET_FRONT
+#define VAR_TICKET_FRONT 2
+#endif
+#ifndef VAR_TICKET_BACK
+#define VAR_TICKET_BACK 1
+#endif
+constexpr uint32_t kTicketFront = VAR_TICKET_FRONT, kTicketBack = VAR_TICKET_BACK;
+
 struct DevBatch {
   uint32_t n_aln, n_groups, n_exon, n_cigar;
   const uint32_t* group_off; const int32_t* refid; const int8_t* strand;

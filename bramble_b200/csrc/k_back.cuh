@@ -120,10 +120,15 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
   const uint32_t n_batches = (b.n_aln + 31) >> 5;
   const uint32_t cap_tmpw = ctl->cap_tmpw, cap_rows = ctl->cap_rows, cap_outw = ctl->cap_outw;
   WarpPool wp; wp.cur = 0; wp.end = 0;
+  unsigned long long alg_words = 0;
+  uint32_t wb_next = 0, wb_end = 0;
   for (; !skip;) {
-    uint32_t wb = 0;
-    if (lane == 0) wb = atomicAdd(&ctl->ticket_a, 1u);
-    wb = __shfl_sync(0xffffffffu, wb, 0);
+    if (wb_next == wb_end) {                                // batch tickets, kTicketBack batches each
+      uint32_t t = 0;
+      if (lane == 0) t = atomicAdd(&ctl->ticket_a, kTicketBack);
+      wb_next = __shfl_sync(0xffffffffu, t, 0); wb_end = wb_next + kTicketBack;
+    }
+    const uint32_t wb = wb_next++;
     if (wb >= n_batches) break;
     const uint32_t a = wb * 32 + lane;
     uint32_t off = 0, n = 0, m_off = 0, m_n = 0, ro = 0, nrc = 0, mro = 0, mnrc = 0, rsum = 0, mrsum = 0, pflag = 0, nm = 0;
@@ -253,8 +258,7 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
     unsigned long long claim = 0;
     if (lane == 0) { claim = atomicAdd(&ctl->claimed, agg); if (ORDERED) { tl.agg[wb] = agg; tl.claim[wb] = claim; } }
     if (PACKED) {                                           // the work counter stays the CIGAR word count of the rows, whatever the layout
-      const int32_t tot = (int32_t)W_b + __reduce_add_sync(0xffffffffu, adj);
-      if (lane == 0) atomicAdd(&ctl->out_words, (unsigned long long)tot);
+      alg_words += (unsigned long long)((long long)W_b + __reduce_add_sync(0xffffffffu, adj));     // one atomic per warp, when it leaves
     }
     claim = __shfl_sync(0xffffffffu, claim, 0);
     const uint32_t prow0 = (uint32_t)claim, pword0 = (uint32_t)(claim >> 32);
@@ -320,6 +324,7 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
     __syncwarp();                                           // the staging area is reused by the next batch
   }
   if (!ORDERED) {                                           // last kernel of the sequence: the last CTA to leave publishes the result
+    if (PACKED && lane == 0 && alg_words) atomicAdd(&ctl->out_words, alg_words);
     __syncthreads();
     if (threadIdx.x == 0) {
       __threadfence();

@@ -91,10 +91,14 @@ __global__ void __launch_bounds__(256, VAR_FAST_CTAS) k_front_fast(DevIndex ix, 
   WarpPool sp; sp.cur = 0; sp.end = 0; (void)sp;
   unsigned long long my_hits = 0;
   uint32_t bad = 0, n_mates = 0, kept = 0;
+  uint32_t wb_next = 0, wb_end = 0;
   for (;;) {
-    uint32_t wb = 0;                                        // dynamic batch tickets: batches differ a lot in cost (hot genes)
-    if (lane == 0) wb = atomicAdd(&ctl->ticket, 1u);
-    wb = __shfl_sync(0xffffffffu, wb, 0);
+    if (wb_next == wb_end) {                                // dynamic batch tickets (batches differ a lot in cost: hot genes), kTicketFront batches each
+      uint32_t t = 0;
+      if (lane == 0) t = atomicAdd(&ctl->ticket, kTicketFront);
+      wb_next = __shfl_sync(0xffffffffu, t, 0); wb_end = wb_next + kTicketFront;
+    }
+    const uint32_t wb = wb_next++;
     if (wb >= n_batches) break;
     const uint32_t a = wb * 32 + lane;
     ReadExons rx; rx.e0 = 0; rx.n_ex = 0; rx.qs0 = 0; rx.qe0 = 0;
