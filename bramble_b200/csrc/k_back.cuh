@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
   const uint32_t n_batches = (b.n_aln + 31) >> 5;
   const uint32_t cap_tmpw = ctl->cap_tmpw, cap_rows = ctl->cap_rows, cap_outw = ctl->cap_outw;
   WarpPool wp; wp.cur = 0; wp.end = 0;
-  unsigned long long alg_words = 0;
+  uint32_t n_pooled = 0;                                    // PACKED: rows of this lane whose CIGAR went to the pool (behind a length word)
   uint32_t wb_next = 0, wb_end = 0;
   for (; !skip;) {
     if (wb_next == wb_end) {                                // batch tickets, kTicketBack batches each
@@ -161,7 +161,6 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
     s_off[lane] = off; s_excl[lane] = excl; s_ro[lane] = ro; s_nrc[lane] = nrc; s_mro[lane] = mro; s_mnrc[lane] = mnrc; s_words[lane] = 0; s_rsum[lane] = rsum; s_mrsum[lane] = mrsum;
     __syncwarp();
     uint32_t rows = 0, words = 0, qn = 0;
-    int32_t adj = 0;                                        // PACKED: CIGAR words of my rows that are not pool words (in-record) minus length words
     // general merge of one emitted row (pair): all lanes call, `go` lanes work
     auto merge_rows = [&](bool go, uint32_t L, uint32_t sidx, uint32_t tid, uint32_t part, const uint4& mr, const uint4& pr) {
       const bool paired = part != SELF;
@@ -182,6 +181,7 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
         tpool[toff] = clr;
       }
       const uint32_t hdr = PACKED ? (paired ? 2u : 1u) : 0u;     // PACKED: every pooled CIGAR sits behind its length word
+      n_pooled += hdr;
       stage[sidx] = make_uint4(tid, clr + clm + hdr, part, fit ? toff : NOFIT);
       atomicAdd(&s_words[L], clr + clm + hdr);
     };
@@ -219,7 +219,6 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
         const uint32_t mine = bit_range(excl > base ? excl - base : 0, incl - base < 32 ? incl - base : 32);
         rows += __popc(B_e & mine) + __popc(B_p & mine);
         if (!PACKED) words += __popc(B_e & ~B_s & mine) + __popc(B_p & ~B_s & mine);
-        else adj += (int32_t)(__popc(B_e & ~B_s & mine) + __popc(B_p & ~B_s & mine)) - (int32_t)(__popc(B_s & mine) + __popc(B_s & B_p & mine));
       }
       const uint32_t sidx = staged ? item : c;
       if (actv) stage[sidx] = make_uint4(emitted ? tid : NONE, slow ? L : (PACKED ? 0u : (paired ? 2u : 1u)), part, slow ? PENDING : INLINE);
@@ -257,9 +256,6 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
     const unsigned long long agg = (unsigned long long)R_b | ((unsigned long long)W_b << 32);
     unsigned long long claim = 0;
     if (lane == 0) { claim = atomicAdd(&ctl->claimed, agg); if (ORDERED) { tl.agg[wb] = agg; tl.claim[wb] = claim; } }
-    if (PACKED) {                                           // the work counter stays the CIGAR word count of the rows, whatever the layout
-      alg_words += (unsigned long long)((long long)W_b + __reduce_add_sync(0xffffffffu, adj));     // one atomic per warp, when it leaves
-    }
     claim = __shfl_sync(0xffffffffu, claim, 0);
     const uint32_t prow0 = (uint32_t)claim, pword0 = (uint32_t)(claim >> 32);
     const uint32_t row0 = prow0 + irows - rows, word0 = pword0 + iwords - words;
@@ -324,7 +320,10 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
     __syncwarp();                                           // the staging area is reused by the next batch
   }
   if (!ORDERED) {                                           // last kernel of the sequence: the last CTA to leave publishes the result
-    if (PACKED && lane == 0 && alg_words) atomicAdd(&ctl->out_words, alg_words);
+    if (PACKED) {                                           // (out_words is free until the publisher turns it into the CIGAR word count)
+      const uint32_t np = __reduce_add_sync(0xffffffffu, n_pooled);
+      if (lane == 0 && np) atomicAdd(&ctl->out_words, (unsigned long long)np);
+    }
     __syncthreads();
     if (threadIdx.x == 0) {
       __threadfence();
@@ -333,7 +332,10 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
         if (!skip) {                                        // the totals claimed are the result sizes
           const unsigned long long tot = atomicAdd(&ctl->claimed, 0ull);
           const uint32_t R = (uint32_t)tot, W = (uint32_t)(tot >> 32);
-          ctl->n_rows = R; ctl->n_outw = W; if (!PACKED) ctl->out_words = W;
+          ctl->n_rows = R; ctl->n_outw = W;
+          // the work counter is the CIGAR word count of the rows whatever the layout: a pooled row has one length word
+          // too many in W, a row with its word inside the record has none at all
+          ctl->out_words = PACKED ? (unsigned long long)W + R - 2ull * atomicAdd(&ctl->out_words, 0ull) : (unsigned long long)W;
           if (!PACKED && R <= cap_rows && W <= cap_outw) o.coff[R] = W;
         }
         ctl_publish_and_reset(ctl, host_result);
