@@ -305,14 +305,15 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
           pv_.row[r] = make_uint4(aln, m.w, m.x, (wpos - pword0) | (minus << 28) | (fl << 29));
           if (v.m_sim) { pv_.sim[r] = v.m_sim[cc]; pv_.clip[r] = v.m_clip[cc]; }
         } else if (PACKED) {
-          pv_.row[r] = make_uint4(aln, m.w, m.x, (inl ? (m.z | BRB_ROW_INLINE) : wpos) | (minus << 28) | (fl << 29));
+          st_stream(&pv_.row[r], make_uint4(aln, m.w, m.x, (inl ? (m.z | BRB_ROW_INLINE) : wpos) | (minus << 28) | (fl << 29)));
           if (v.m_sim) { o.sim[r] = v.m_sim[cc]; o.clip[r] = v.m_clip[cc]; }
           if (!inl) pool[wpos++] = len;                     // length word, then the CIGAR
         } else {
-          o.src[r] = aln; o.tid[r] = m.w; o.pos[r] = m.x; o.strand[r] = minus ? '-' : '+'; o.flags[r] = (uint8_t)fl; o.coff[r] = wpos;
+          st_stream(&o.src[r], aln); st_stream(&o.tid[r], m.w); st_stream(&o.pos[r], m.x); st_stream(&o.strand[r], (int8_t)(minus ? '-' : '+'));
+          st_stream(&o.flags[r], (uint8_t)fl); st_stream(&o.coff[r], wpos);
           if (v.m_sim) { o.sim[r] = v.m_sim[cc]; o.clip[r] = v.m_clip[cc]; }
         }
-        if (inl) { if (!PACKED) pool[wpos] = m.z; }
+        if (inl) { if (!PACKED) st_stream(&pool[wpos], m.z); }
         else if (minus) for (uint32_t i = 0; i < len; i++) pool[wpos + i] = src[len - 1 - i];      // reverse_complement_bam, src/bam.cpp:636-702
         else for (uint32_t i = 0; i < len; i++) pool[wpos + i] = src[i];
       }

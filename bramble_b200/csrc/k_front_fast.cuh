@@ -161,8 +161,8 @@ __global__ void __launch_bounds__(256, VAR_FAST_CTAS) k_front_fast(DevIndex ix, 
             ok = dedupe_first(ix, p, ox, s, rec0);
             if (ok) { key = rec_key(ix, rec0); lk = rec_link(ix, rec0); ok = eval_short<false>(ix, b, p, ox, s, key, lk, ipool + ioff, pos, ilen, word, sim); }
           }
-          if (ok) { M.rec[slot] = make_uint4(pos, (ilen << 1) | (uint32_t)s, ilen == 1 ? word : ioff, key.tid); atomicAdd(&s_nv[L], 1u); }
-          else M.rec[slot] = make_uint4(0, 0, 0, NONE);
+          if (ok) { st_stream(&M.rec[slot], make_uint4(pos, (ilen << 1) | (uint32_t)s, ilen == 1 ? word : ioff, key.tid)); atomicAdd(&s_nv[L], 1u); }
+          else st_stream(&M.rec[slot], make_uint4(0, 0, 0, NONE));
         }
         __syncwarp();
         if (lane + 32 < qn) { const uint32_t x = q_rec[lane + 32], y = q_own[lane + 32], z = q_slot[lane + 32]; q_rec[lane] = x; q_own[lane] = y; q_slot[lane] = z; }
@@ -190,7 +190,7 @@ __global__ void __launch_bounds__(256, VAR_FAST_CTAS) k_front_fast(DevIndex ix, 
       if (sv) { const int v = fast_short(ix, b, strict, ox, s, key, rec_link(ix, rec0), pos, word); fast = v == FAST_MATCH; sv = v != FAST_REJECT; }
       const uint32_t B_sv = __ballot_sync(0xffffffffu, sv), B_fast = __ballot_sync(0xffffffffu, fast), B_q = B_sv & ~B_fast;
       const uint32_t slot = sbase + wr + __popc(B_sv & lt_mask);
-      if (fast) M.rec[slot] = make_uint4(pos, 2u | (uint32_t)s, word, key.tid);
+      if (fast) st_stream(&M.rec[slot], make_uint4(pos, 2u | (uint32_t)s, word, key.tid));
       else if (sv) { const uint32_t qi = qn + __popc(B_q & lt_mask); q_rec[qi] = rec0; q_own[qi] = L | ((uint32_t)s << 5); q_slot[qi] = slot; }
       wr += __popc(B_sv); qn += __popc(B_q);
       if (n && incl > base && excl < base + 32) {
