@@ -203,7 +203,7 @@ __global__ void __launch_bounds__(256, VAR_FAST_CTAS) k_front_fast(DevIndex ix, 
     nvalid += s_nv[lane];
     kept += nvalid;
     const uint32_t first = sbase + warp_incl_scan(nres, lane) - nres;
-    if (a < b.n_aln) a_cand[a] = make_uint4(first, nres, nvalid, 0);
+    if (a < b.n_aln) st_stream(&a_cand[a], make_uint4(first, nres, nvalid, 0));
     __syncwarp();                                           // the per-alignment facts in shared memory are rewritten by the next batch
   }
   for (int d = 16; d; d >>= 1) { my_hits += __shfl_down_sync(0xffffffffu, my_hits, d); kept += __shfl_down_sync(0xffffffffu, kept, d);
