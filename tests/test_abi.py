@@ -44,3 +44,21 @@ def test_no_device_no_compute():
     from bramble_b200 import engine
     with pytest.raises(capi.EngineError):
         engine.Engine(wl["index"])
+
+
+def test_ctypes_mirrors_match_the_compiled_header(tmp_path):
+    """The ctypes structures are hand-written mirrors: compile the header with gcc and compare sizes and the offsets
+    of the last fields (a field added to one side only moves them)."""
+    import subprocess
+    src = tmp_path / "sizes.c"
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "bramble_b200.h"\n'
+                   'int main(void) { printf("%zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(brb_params), sizeof(brb_batch_in), sizeof(brb_index_desc),\n'
+                   '  sizeof(brb_batch_out), sizeof(brb_stats), offsetof(brb_batch_out, packed_rows), offsetof(brb_batch_out, aln_rec_off),\n'
+                   '  offsetof(brb_stats, alg_bytes_front)); return 0; }\n')
+    exe = tmp_path / "sizes"
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    got = [int(x) for x in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()]
+    want = [C.sizeof(capi.Params), C.sizeof(capi.BatchIn), C.sizeof(capi.IndexDesc), C.sizeof(capi.BatchOut), C.sizeof(capi.Stats),
+            capi.BatchOut.packed_rows.offset, capi.BatchOut.aln_rec_off.offset, capi.Stats.alg_bytes_front.offset]
+    assert got == want
+    assert (capi.OPT_GENERIC_FRONT, capi.OPT_NO_FASTPATH, capi.OPT_ORDERED_ROWS, capi.OPT_PACKED_ROWS) == (1, 2, 3, 4)
