@@ -302,6 +302,9 @@ def main():
     st = eng.stats()
     sampler = ClockSampler(local)
     sampler.prepare()                     # every rank watches its own GPU; rank 0's samples go into `clocks`, the medians of all into `host`
+    import gc
+    gc.collect()
+    gc.disable()                          # a collection pass between two steps is a millisecond of idle GPU in an 11 ms timed region
     barrier()
     sampler.start()
     phase = {k: 0.0 for k in ("ms_lookup", "ms_chain", "ms_rescue", "ms_finalize", "ms_pair", "ms_merge")}
@@ -312,6 +315,7 @@ def main():
         eng.run_resident(p)
         per_step.append(eng.stats())
     ms = eng.timer_stop()
+    gc.enable()
     for s in per_step:
         launches += int(s.n_launches)
         for k in phase:
