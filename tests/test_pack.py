@@ -81,3 +81,27 @@ def test_hostbind_cpulist_and_no_gpu():
     if info["numa_node"] is None:
         assert not info["bound"] and os.sched_getaffinity(0) == before
     os.sched_setaffinity(0, before)
+
+
+def test_hostbind_even_slices_without_numa_information():
+    """One process per GPU on a box that exposes no NUMA node for the device: rank r of n takes the r-th even slice of
+    the allowed CPUs, slices are disjoint, and a box with fewer than two CPUs per rank is left alone."""
+    import os
+    from bramble_b200 import hostbind
+    before = os.sched_getaffinity(0)
+    try:
+        if hostbind.gpu_numa_node(0) is not None or len(before) < 4:
+            return
+        seen = []
+        for r in range(2):
+            os.sched_setaffinity(0, before)
+            info = hostbind.bind_to_gpu_node(0, r, 2)
+            got = os.sched_getaffinity(0)
+            assert info["bound"] and info["cpus_allowed"] == len(got) == len(before) // 2
+            seen.append(got)
+        assert not (seen[0] & seen[1]) and (seen[0] | seen[1]) <= before
+        os.sched_setaffinity(0, before)
+        info = hostbind.bind_to_gpu_node(0, 0, len(before))          # one CPU per rank: not worth pinning
+        assert not info["bound"] and os.sched_getaffinity(0) == before
+    finally:
+        os.sched_setaffinity(0, before)
