@@ -104,7 +104,8 @@ class Context:
 
 def rows_checksum(o, src_offset=0):
     """Order-independent 64-bit checksum of the rows of a raw brb_batch_out (sum of a per-row mix of source alignment,
-    tid, pos, strand, flags, CIGAR length and CIGAR words): equal for any layout of the same row set."""
+    tid, pos, strand, flags, similarity score bits, clip score, CIGAR length and CIGAR words): equal for any layout of
+    the same row set."""
     n = int(o.n_rec)
     if n == 0:
         return 0, 0
@@ -118,6 +119,8 @@ def rows_checksum(o, src_offset=0):
         h ^= c["tid"].astype(np.uint64) * np.uint64(0xC2B2AE3D27D4EB4F)
         h = h * M + c["pos"].astype(np.uint64)
         h = h * M + (c["tx_strand"].astype(np.uint8).astype(np.uint64) << np.uint64(8)) + c["flags"].astype(np.uint64)
+        h = h * M + np.ascontiguousarray(c["sim_score"], dtype=np.float64).view(np.uint64)
+        h = h * M + c["clip_score"].astype(np.int64).astype(np.uint64)
         h = h * M + (co[1:] - co[:-1])
         h = h * M + (wsum[co[1:].astype(np.int64)] - wsum[co[:-1].astype(np.int64)])
         return int(h.sum(dtype=np.uint64)), n

@@ -285,6 +285,32 @@ class Batch:
         return nb
 
 
+def concat_batches(parts):
+    """Bundles (their `arrays` dicts) laid end to end as one bundle: CSR offsets and mate links shifted."""
+    nb = Batch()
+    B = nb.arrays
+    n_al = np.array([0] + [p["refid"].shape[0] for p in parts], dtype=np.int64).cumsum()
+    for k in ("refid", "strand", "exon_st", "exon_en", "cigar"):
+        B[k] = np.ascontiguousarray(np.concatenate([p[k] for p in parts]))
+    for off, dat in (("exon_off", "exon_st"), ("cigar_off", "cigar"), ("group_off", "refid")):
+        base = np.array([0] + [p[dat].shape[0] for p in parts], dtype=np.int64).cumsum()
+        B[off] = np.concatenate([p[off][(1 if i else 0):].astype(np.int64) + base[i] for i, p in enumerate(parts)]).astype(np.uint32)
+    B["mate_idx"] = np.concatenate([np.where(p["mate_idx"] >= 0, p["mate_idx"].astype(np.int64) + n_al[i], -1) for i, p in enumerate(parts)]).astype(np.int32)
+    d = nb.desc
+    d.n_aln, d.n_groups = int(n_al[-1]), int(B["group_off"].shape[0] - 1)
+    for k in ("group_off", "refid", "strand", "exon_off", "exon_st", "exon_en", "cigar_off", "cigar", "mate_idx"):
+        setattr(d, k, capi.ptr(B[k]))
+    if all("group_seq_off" in p for p in parts):
+        base = np.array([0] + [int(p["group_seq_off"][-1]) for p in parts], dtype=np.int64).cumsum()
+        B["group_seq_off"] = np.concatenate([p["group_seq_off"][(1 if i else 0):].astype(np.int64) + base[i] for i, p in enumerate(parts)]).astype(np.uint64)
+        B["seq_codes"] = np.ascontiguousarray(np.concatenate([p["seq_codes"][:int(p["group_seq_off"][-1])] for p in parts] + [np.zeros(1, np.uint8)]))
+        d.group_seq_off = capi.ptr(B["group_seq_off"]); d.seq_codes = capi.ptr(B["seq_codes"])
+    else:
+        d.group_seq_off = None; d.seq_codes = None
+    nb.src = np.arange(d.n_aln, dtype=np.int64)
+    return nb
+
+
 _NT16 = "=ACMGRSVTWYHKDBN"
 
 

@@ -16,6 +16,7 @@ import numpy as np
 
 CIG = {c: i for i, c in enumerate("MIDNSHP=X")}
 _NT16 = {c: i for i, c in enumerate("=ACMGRSVTWYHKDBN")}
+_NT16_TABLE = bytes(_NT16.get(chr(c), 15) for c in range(256))      # letter -> 4-bit BAM code (anything else: N)
 
 
 # ----------------------------------------------------------------------------- annotation
@@ -559,9 +560,7 @@ def _pack_record(r, compute_bin=True):
     seq = r["seq"] or b""
     lq = len(seq)
     if lq:
-        codes = np.frombuffer(bytes(_NT16.get(chr(c), 15) for c in seq), dtype=np.uint8)
-        if lq & 1:
-            codes = np.append(codes, np.uint8(0))
+        codes = np.frombuffer(bytes(seq).translate(_NT16_TABLE) + (b"\0" if lq & 1 else b""), dtype=np.uint8)
         seqb = ((codes[0::2] << 4) | codes[1::2]).astype(np.uint8).tobytes()
     else:
         seqb = b""

@@ -12,6 +12,7 @@
 // so the two disagree unless both implement the reference's semantics.
 #include "brb_port.h"
 #include <algorithm>
+#include <chrono>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
@@ -740,6 +741,7 @@ extern "C" {
 int brb_port_project(const brb_index_desc* ix, const brb_params* p, const brb_batch_in* in, brb_port_out* out) {
   if (!ix || !p || !in || !out) return BRB_E_ARG;
   Ctx c; init_ctx(c, ix, p, in);
+  const auto t_start = std::chrono::steady_clock::now();
   std::vector<OutRec> recs; std::vector<uint32_t> group_rec_off(in->n_groups + 1, 0);
   std::vector<uint8_t> seen(in->n_aln, 0);
   for (uint32_t g = 0; g < in->n_groups; g++) {
@@ -783,6 +785,7 @@ int brb_port_project(const brb_index_desc* ix, const brb_params* p, const brb_ba
   out->tx_strand = dup_vec(strand); out->flags = dup_vec(flags); out->sim_score = dup_vec(sim); out->clip_score = dup_vec(clip);
   out->cigar_off = dup_vec(coff); out->cigar_len = dup_vec(clen); out->cigar = dup_vec(pool);
   out->n_matches = c.n_matches; out->n_rescue = c.n_rescue; out->n_hits = c.n_hits;
+  out->seconds_project = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_start).count();
   return BRB_OK;
 }
 

@@ -13,6 +13,8 @@ typedef struct brb_port_out {           /* malloc'ed by brb_port_project, releas
   uint32_t* group_rec_off; uint32_t* src_aln; uint32_t* tid; uint32_t* pos; int8_t* tx_strand; uint8_t* flags;
   double* sim_score; int32_t* clip_score; uint32_t* cigar_off; uint32_t* cigar_len; uint32_t* cigar;
   uint64_t n_matches, n_rescue, n_hits;  /* work counters (for the algorithmic-bytes formula) */
+  double seconds_project;                /* wall time of the projection itself (index build excluded), one thread: the CPU figure at
+                                          * the boundary of the engine's resident step (columns in, rows out) */
 } brb_port_out;
 
 int brb_port_project(const brb_index_desc* idx, const brb_params* p, const brb_batch_in* in, brb_port_out* out);

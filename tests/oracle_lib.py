@@ -18,7 +18,7 @@ class PortOut(C.Structure):
                 ("src_aln", capi.u32p), ("tid", capi.u32p), ("pos", capi.u32p), ("tx_strand", capi.i8p),
                 ("flags", capi.u8p), ("sim_score", capi.f64p), ("clip_score", capi.i32p), ("cigar_off", capi.u32p),
                 ("cigar_len", capi.u32p), ("cigar", capi.u32p), ("n_matches", C.c_uint64), ("n_rescue", C.c_uint64),
-                ("n_hits", C.c_uint64)]
+                ("n_hits", C.c_uint64), ("seconds_project", C.c_double)]
 
 
 _port = None
