@@ -428,7 +428,7 @@ def main():
         args.ref_names = 30_000
     if args.workload in workloads.LONG and args.ref_names == 150_000:
         args.ref_names = 12_000
-    config = {"workload": f"{workloads.SHAPE[args.workload]}, {args.names} read names per GPU",
+    config = {"id": args.workload, "workload": f"{workloads.SHAPE[args.workload]}, {args.names} read names per GPU",
               "flags": " ".join(workloads.FLAGS[args.workload] + (["-S genome.fa"] if args.workload == "c3" else [])) or "(default)", "names_per_gpu": args.names,
               "l2": "inputs + intermediates (>1 GB per step) exceed the 126 MB L2"}
 

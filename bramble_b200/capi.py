@@ -19,6 +19,7 @@ OPT_GENERIC_FRONT = 1
 OPT_NO_FASTPATH = 2
 OPT_ORDERED_ROWS = 3
 OPT_PACKED_ROWS = 4
+OPT_MERGE_WARP = 5
 
 u8p, i8p = C.POINTER(C.c_uint8), C.POINTER(C.c_int8)
 u32p, i32p = C.POINTER(C.c_uint32), C.POINTER(C.c_int32)
@@ -59,7 +60,7 @@ class Stats(C.Structure):
                 ("ms_pair", C.c_float), ("ms_merge", C.c_float), ("n_candidates", C.c_uint64),
                 ("n_matches", C.c_uint64), ("n_rescue", C.c_uint64), ("n_rec", C.c_uint64),
                 ("alg_bytes", C.c_uint64), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
-                ("alg_bytes_front", C.c_uint64)]
+                ("alg_bytes_front", C.c_uint64), ("ksw_cells", C.c_uint64), ("host_syncs", C.c_uint32), ("reserved_", C.c_uint32)]
 
 
 _PTR = {np.dtype(np.uint8): u8p, np.dtype(np.int8): i8p, np.dtype(np.uint32): u32p, np.dtype(np.int32): i32p,

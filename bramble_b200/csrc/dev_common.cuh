@@ -72,6 +72,7 @@ struct DevBatch {
   const uint32_t* exon_off; const uint32_t* exon_st; const uint32_t* exon_en;
   const uint32_t* cigar_off; const uint32_t* cigar; const int32_t* mate_idx;
   const uint64_t* group_seq_off; const uint8_t* seq; const uint32_t* aln_group;
+  uint32_t back_shift;           // k_back / k_place: log2 of the alignments per batch (5 for short reads, 3 for long reads)
 };
 
 // Device-side control block of one brb_project_resident call: capacities of the pre-allocated pools and the
@@ -81,15 +82,20 @@ struct DevBatch {
 struct Ctl {
   unsigned long long n_hits, out_words, rescue_bytes, n_matches, n_rescue, ksw_max_mat, ksw_max_tlen, n_mates;   // work counters
   unsigned long long claimed;         // k_back: rows | CIGAR words << 32 handed out so far
+  unsigned long long ksw_max_qlen, ksw_cells;   // clip rescue: longest query of a big problem; DP cells (query x target) of all problems
   uint32_t n_cand, cap_cand;          // candidate slots allocated / capacity
   uint32_t n_ideal, cap_ideal;        // ideal-CIGAR pool words
   uint32_t n_rows, cap_rows;          // output rows
   uint32_t n_tmpw, cap_tmpw;          // merge scratch pool words
   uint32_t n_outw, cap_outw;          // dense output CIGAR words
-  uint32_t bad_input;                 // 1: mate link not symmetric, 2: read exons not ascending/disjoint, 3: >= 2^28 CIGAR words in one batch of 32 alignments
+  uint32_t n_tb, cap_tb;              // clip rescue: traceback ops / override-coded clip CIGAR words
+  uint32_t bad_input;                 // 1: mate link not symmetric, 2: read exons not ascending/disjoint, 3: >= 2^28 CIGAR words in one batch of 32 alignments, 4: packed rows, 5: CSR offsets
   uint32_t ticket;                    // next batch of 32 alignments for k_front (dynamic scheduling)
   uint32_t ticket_a, ticket_b;        // k_back: next batch; CTAs that have left (the last one publishes the totals)
+  uint32_t kq_n[5], kq_t[5];          // clip rescue: problems per size class, next problem of each class
+  uint32_t ksw_big_skipped, pad_;     // big problems that did not fit the per-warp scratch (the host grows it and replays)
 };
+constexpr int N_CAPS = 6;
 // End of a kernel sequence, ONE thread, every other writer of `ctl` done and fenced: hand the counters to the host
 // through mapped pinned memory (no separate copy operation on the stream) and leave `ctl` ready for the next
 // sequence of the same pool capacities (counters and tickets zero, caps kept), so that a steady-state step needs no
@@ -98,14 +104,14 @@ __device__ __forceinline__ void ctl_publish_and_reset(Ctl* ctl, Ctl* host_result
   static_assert(sizeof(Ctl) % 8 == 0, "Ctl is copied in 8-byte words");
   volatile unsigned long long* s = reinterpret_cast<volatile unsigned long long*>(ctl);
   volatile unsigned long long* d = reinterpret_cast<volatile unsigned long long*>(host_result);
-  const uint32_t cc = ctl->cap_cand, ci = ctl->cap_ideal, cr = ctl->cap_rows, ct = ctl->cap_tmpw, co = ctl->cap_outw;
+  const uint32_t cc = ctl->cap_cand, ci = ctl->cap_ideal, cr = ctl->cap_rows, ct = ctl->cap_tmpw, co = ctl->cap_outw, cb = ctl->cap_tb;
   for (uint32_t i = 0; i < sizeof(Ctl) / 8; i++) { d[i] = s[i]; s[i] = 0ull; }
-  ctl->cap_cand = cc; ctl->cap_ideal = ci; ctl->cap_rows = cr; ctl->cap_tmpw = ct; ctl->cap_outw = co;
+  ctl->cap_cand = cc; ctl->cap_ideal = ci; ctl->cap_rows = cr; ctl->cap_tmpw = ct; ctl->cap_outw = co; ctl->cap_tb = cb;
   __threadfence_system();
 }
 __device__ __forceinline__ bool ctl_overflow(const Ctl* c) {
   return c->n_cand > c->cap_cand || c->n_ideal > c->cap_ideal || c->n_rows > c->cap_rows || c->n_tmpw > c->cap_tmpw ||
-         c->n_outw > c->cap_outw || c->bad_input != 0;
+         c->n_outw > c->cap_outw || c->n_tb > c->cap_tb || c->bad_input != 0;
 }
 
 __device__ __forceinline__ uint4 ldg4(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }

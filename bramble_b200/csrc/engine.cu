@@ -82,7 +82,7 @@ struct brb_ctx {
   cudaStream_t st = nullptr;
   cudaEvent_t ev[8]{};
   bool ctl_clean = false;           // the device Ctl holds zero counters and ctl_caps (left so by the last sequence's publisher)
-  uint32_t ctl_caps[5]{};
+  uint32_t ctl_caps[N_CAPS]{};
   int n_sm = 0;                     // cached launch geometry: SM count and resident CTAs per kernel entry
   std::vector<std::pair<const void*, int>> resident_cache;
   cudaEvent_t tev[2]{};
@@ -90,10 +90,11 @@ struct brb_ctx {
   DevBatch b{};
   Buf in_group_off, in_refid, in_strand, in_exon_off, in_exon_st, in_exon_en, in_cigar_off, in_cigar, in_mate, in_seq_off, in_seq;
   uint64_t in_bytes = 0, n_mates = 0, seq_bytes = 0, rescue_bytes = 0;
-  bool have_batch = false, have_result = false, have_scores = false, opt_generic_front = false, opt_no_fastpath = false, opt_ordered = false, result_ordered = false, opt_packed = false, result_packed = false;
+  bool have_batch = false, have_result = false, have_scores = false, opt_generic_front = false, opt_no_fastpath = false, opt_ordered = false, result_ordered = false, opt_packed = false, result_packed = false, opt_merge_warp = false;
   // control block + pools (capacities persist across calls and only grow)
   Buf ctl;
-  uint32_t cap_cand = 0, cap_ideal = 0, cap_rows = 0, cap_tmpw = 0, cap_outw = 0;
+  uint32_t cap_cand = 0, cap_ideal = 0, cap_rows = 0, cap_tmpw = 0, cap_outw = 0, cap_tb = 0;
+  bool validated = false;           // the CSR offsets of the resident batch have been checked on the device
   Buf q_any, a_cand, scan_tmp;
   Buf c_rec, c_task, c_first, c_last, c_nseg, c_nguide, c_cap, ipool;
   Buf r_left, r_right, rpool;
@@ -259,6 +260,8 @@ int brb_index_create(int device, const brb_index_desc* d, brb_index** out) {
   return BRB_OK;
 }
 
+int brb_ctx_destroy(brb_ctx* c);
+
 int brb_index_destroy(brb_index* ix) {
   if (!ix) return BRB_OK;
   cudaSetDevice(ix->device);
@@ -271,10 +274,18 @@ int brb_ctx_create(brb_index* ix, brb_ctx** out) {
   if (!ix || !out) return fail(BRB_E_ARG, "brb_ctx_create: null argument");
   CU(cudaSetDevice(ix->device));
   brb_ctx* c = new brb_ctx(); c->idx = ix;
-  CU(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));
-  for (auto& e : c->ev) CU(cudaEventCreate(&e));
-  for (auto& e : c->tev) CU(cudaEventCreate(&e));
-  ENS(c->ctl, sizeof(Ctl)); ENS(c->h_small, 1024);      // host images of Ctl: [0] initialisation, [512] result
+  auto init = [&]() -> int {
+    CU(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));
+    for (auto& e : c->ev) CU(cudaEventCreate(&e));
+    for (auto& e : c->tev) CU(cudaEventCreate(&e));
+    ENS(c->ctl, sizeof(Ctl)); ENS(c->h_small, 1024);      // host images of Ctl: [0] initialisation, [512] result
+    int sm = 0;
+    CU(cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, ix->device));
+    c->n_sm = sm > 0 ? sm : 1;
+    return BRB_OK;
+  };
+  const int rc = init();
+  if (rc != BRB_OK) { brb_ctx_destroy(c); return rc; }     // (keeps the error text of the failing call)
   *out = c;
   return BRB_OK;
 }
@@ -282,7 +293,7 @@ int brb_ctx_create(brb_index* ix, brb_ctx** out) {
 int brb_ctx_destroy(brb_ctx* c) {
   if (!c) return BRB_OK;
   cudaSetDevice(c->idx->device);
-  cudaStreamSynchronize(c->st);
+  if (c->st) cudaStreamSynchronize(c->st);
   for (Buf* b : c->all()) b->release();
   free_rescue_bufs(c);
   c->h_small.release(); c->h_out.release();
@@ -295,10 +306,10 @@ int brb_ctx_destroy(brb_ctx* c) {
 
 // ---- batch upload: one bundle (reference BundleData::reads) as structure-of-arrays.  Content checks that
 // need a pass over the data (symmetric mate links, ascending read exons) run on the device inside k_lookup.
-int brb_batch_upload(brb_ctx* c, const brb_batch_in* in) {
+static int batch_upload_async(brb_ctx* c, const brb_batch_in* in) {
   if (!c || !in) return fail(BRB_E_ARG, "brb_batch_upload: null argument");
   CU(cudaSetDevice(c->idx->device));
-  c->have_batch = c->have_result = false;
+  c->have_batch = c->have_result = false; c->validated = false;
   const uint32_t n = in->n_aln, ng = in->n_groups;
   if (n && (!in->group_off || !in->refid || !in->strand || !in->exon_off || !in->exon_st || !in->exon_en || !in->cigar_off ||
             !in->cigar || !in->mate_idx)) return fail(BRB_E_ARG, "null batch column");
@@ -337,9 +348,17 @@ int brb_batch_upload(brb_ctx* c, const brb_batch_in* in) {
   b.exon_off = c->in_exon_off.as<uint32_t>(); b.exon_st = c->in_exon_st.as<uint32_t>(); b.exon_en = c->in_exon_en.as<uint32_t>();
   b.cigar_off = c->in_cigar_off.as<uint32_t>(); b.cigar = c->in_cigar.as<uint32_t>(); b.mate_idx = c->in_mate.as<int32_t>();
   b.group_seq_off = have_seq ? c->in_seq_off.as<uint64_t>() : nullptr; b.seq = have_seq ? c->in_seq.as<uint8_t>() : nullptr;
-  b.aln_group = nullptr;
+  b.aln_group = nullptr; b.back_shift = 5;
   c->stats.h2d_bytes = c->in_bytes;
   c->have_batch = true;
+  return BRB_OK;
+}
+
+// Public form: on return the caller's columns have been read (they may be reused or freed).
+int brb_batch_upload(brb_ctx* c, const brb_batch_in* in) {
+  const int rc = batch_upload_async(c, in);
+  if (rc) return rc;
+  CU(cudaStreamSynchronize(c->st));
   return BRB_OK;
 }
 
@@ -347,7 +366,10 @@ int brb_batch_upload(brb_ctx* c, const brb_batch_in* in) {
 
 namespace {
 
-int run_rescue(brb_ctx* c, const brb_params& p);   // k_ksw host driver, rescue_host.inl
+int launch_rescue(brb_ctx* c, const brb_params& p, uint64_t* launches);   // clip-rescue phase, rescue_host.inl
+struct RescueBufs;
+bool grow_ksw_big(RescueBufs& R, const Ctl* h);
+RescueBufs& rescue_bufs(brb_ctx* c);
 
 float ms_between(cudaEvent_t a, cudaEvent_t b) { float ms = 0; cudaEventElapsedTime(&ms, a, b); return ms; }
 
@@ -359,7 +381,7 @@ int ensure_pools(brb_ctx* c, bool rescue) {
   const size_t n = b.n_aln, C = c->cap_cand, R = c->cap_rows;
   ENS(c->q_any, (size_t)2 * b.n_exon + 16); ENS(c->a_cand, n * 16);
   ENS(c->a_roff, (n + 1) * 4); ENS(c->a_rcnt, (n + 1) * 4); ENS(c->g_roff, (size_t)(b.n_groups + 1) * 4);
-  const size_t nbat = (n + 31) / 32;
+  const size_t nbat = (n + ((size_t)1 << b.back_shift) - 1) >> b.back_shift;
   ENS(c->c_stage, C * 16); ENS(c->t_agg, nbat * 8 + 8); ENS(c->t_claim, nbat * 8 + 8); ENS(c->t_off, (nbat + 1) * 8);
   ENS(c->scan_tmp, scan_scratch_words(std::max<size_t>(nbat, 1)) * 8);
   if (c->opt_ordered) { ENS(c->p_row, R * 16); ENS(c->p_pool, (size_t)c->cap_outw * 4); }
@@ -379,6 +401,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   const bool rescue = p.long_reads && p.use_fasta;
   if (rescue && !c->idx->d.genome) return fail(BRB_E_UNSUPPORTED, "use_fasta requested but the index holds no genome");
   if (rescue && c->b.n_aln && !c->b.seq) return fail(BRB_E_UNSUPPORTED, "use_fasta requested but the batch carries no read sequences");
+  c->b.back_shift = p.long_reads ? 3u : 5u;           // long reads: 8 alignments per k_back batch (rows of 10^2..10^4 CIGAR words)
   const DevBatch& b = c->b; const DevIndex& ix = c->idx->d;
   cudaStream_t st = c->st;
   brb_stats& S = c->stats;
@@ -394,13 +417,13 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   }
   if (!c->cap_cand) {           // first guess from the batch shape; a pool that overflows grows and the sequence replays
     c->cap_cand = grown((uint64_t)12 * n); c->cap_rows = grown((uint64_t)6 * n);
-    const uint64_t slack = std::min<uint64_t>((n + 31) / 32, (uint64_t)148 * 8 * 8) * POOL_CHUNK;   // unused chunk tails of the persistent warps
+    const uint64_t slack = std::min<uint64_t>((n + 31) / 32, (uint64_t)c->n_sm * 8 * 8) * POOL_CHUNK;   // unused chunk tails of the persistent warps
     c->cap_cand = grown((uint64_t)12 * n + slack);
-    c->cap_ideal = grown((uint64_t)4 * c->cap_cand + b.n_exon + slack); c->cap_tmpw = grown((uint64_t)8 * c->cap_rows + 2 * (uint64_t)b.n_cigar + slack);
+    c->cap_ideal = grown((uint64_t)4 * c->cap_cand + b.n_exon + slack); c->cap_tmpw = grown((uint64_t)8 * c->cap_rows + (p.long_reads ? 6 : 2) * (uint64_t)b.n_cigar + slack);   // long rows: merged CIGAR + the cooperative merge's scratch
     c->cap_outw = grown((uint64_t)3 * c->cap_rows + b.n_cigar);
-    if (getenv("BRB_TEST_SMALL_POOLS")) c->cap_cand = c->cap_rows = c->cap_ideal = c->cap_tmpw = c->cap_outw = 64;   // tests: force the grow-and-replay path
+    c->cap_tb = grown((uint64_t)64 * n);
+    if (getenv("BRB_TEST_SMALL_POOLS")) c->cap_cand = c->cap_rows = c->cap_ideal = c->cap_tmpw = c->cap_outw = c->cap_tb = 64;   // tests: force the grow-and-replay path
   }
-  if (!c->n_sm) { int sm = 0; c->n_sm = (cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, c->idx->device) == cudaSuccess && sm > 0) ? sm : 148; }
   const int n_sm = c->n_sm;
   const int ncta = n_sm * 8;
   auto resident = [&](const void* kern) {
@@ -416,26 +439,34 @@ int project_resident(brb_ctx* c, const brb_params& p) {
                                      : (rescue ? (const void*)k_front<false> : (const void*)k_front<true>);
   const int ncta_front = resident(front_fn);
   const bool ordered = c->opt_ordered, packed = c->opt_packed && !ordered;      // BRB_OPT_ORDERED_ROWS wins when both are set
-  const int ncta_back = resident(ordered ? (const void*)k_back<true, false> : packed ? (const void*)k_back<false, true> : (const void*)k_back<false, false>);
+  const bool lng = p.long_reads;
+  const int ncta_back = lng ? resident(ordered ? (const void*)k_back<true, false, true> : packed ? (const void*)k_back<false, true, true> : (const void*)k_back<false, false, true>)
+                            : resident(ordered ? (const void*)k_back<true, false, false> : packed ? (const void*)k_back<false, true, false> : (const void*)k_back<false, false, false>);
   Ctl* ctl = c->ctl.as<Ctl>();
   static_assert(sizeof(Ctl) <= 512, "two Ctl images in h_small");
   Ctl* hctl = c->h_small.as<Ctl>();                                               // initialisation image (host -> device)
   Ctl* hres = reinterpret_cast<Ctl*>(c->h_small.as<char>() + 512);                // result image (written by the device)
   uint64_t L = 0;
+  uint32_t n_syncs = 0;                               // host round trips of the call (one per sequence; more only when a pool had to grow)
   bool one_front = false, back_finishes = false;      // which phase events this sequence recorded
   for (int attempt = 0;; attempt++) {
     if (attempt > 12) return fail(BRB_E_NOMEM, "pool sizing did not converge");
     { int r = ensure_pools(c, rescue); if (r) return r; }
-    const uint32_t caps[5] = {c->cap_cand, c->cap_ideal, c->cap_rows, c->cap_tmpw, c->cap_outw};
+    const uint32_t caps[N_CAPS] = {c->cap_cand, c->cap_ideal, c->cap_rows, c->cap_tmpw, c->cap_outw, c->cap_tb};
     if (!c->ctl_clean || memcmp(caps, c->ctl_caps, sizeof(caps)) != 0) {          // steady state: the previous sequence left Ctl ready
       memset(hctl, 0, sizeof(Ctl));
       hctl->cap_cand = c->cap_cand; hctl->cap_ideal = c->cap_ideal; hctl->cap_rows = c->cap_rows; hctl->cap_tmpw = c->cap_tmpw; hctl->cap_outw = c->cap_outw;
+      hctl->cap_tb = c->cap_tb;
       CU(cudaMemcpyAsync(ctl, hctl, sizeof(Ctl), cudaMemcpyHostToDevice, st));
       memcpy(c->ctl_caps, caps, sizeof(caps));
     }
     c->ctl_clean = false;
     Matches M; M.rec = c->m_rec.as<uint4>();
     M.sim = c->have_scores ? c->m_sim.as<double>() : nullptr; M.clip = c->have_scores ? c->m_clip.as<int32_t>() : nullptr;
+    if (!c->validated) {          // CSR offsets of the batch: once per upload, before any kernel trusts them
+      k_validate_batch<<<grid_for(std::max<size_t>(std::max<size_t>(n, b.n_groups) + 1, 1), 256), 256, 0, st>>>(b, ctl); L++;
+      c->validated = true;
+    }
     // ---- phase 1: lookup + candidate lists
     CU(cudaEventRecord(c->ev[0], st));
     one_front = false; back_finishes = false;
@@ -458,12 +489,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
       F.nguide = c->c_nguide.as<uint32_t>(); F.cap = c->c_cap.as<uint32_t>();
       k_chain<<<ncta, 256, 0, st>>>(ix, b, p, ctl, c->q_any.as<uint8_t>(), c->c_rec.as<uint32_t>(), c->c_task.as<uint32_t>(), F); L++;
       CU(cudaEventRecord(c->ev[2], st));
-      CU(cudaMemcpyAsync(hres, ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, st));
-      CU(cudaStreamSynchronize(st));
-      if (hres->bad_input) break;
-      if (hres->n_cand > c->cap_cand) { c->cap_cand = grown(hres->n_cand); c->cap_ideal = std::max(c->cap_ideal, grown((uint64_t)4 * c->cap_cand)); continue; }
-      c->n_cand = hres->n_cand;
-      if (c->n_cand) { S.n_launches = L; int r = run_rescue(c, p); if (r) return r; L = S.n_launches; }
+      { int r = launch_rescue(c, p, &L); if (r) return r; }      // plan -> size-class DP kernels -> clip segments: no host round trip
       CU(cudaEventRecord(c->ev[3], st));
       k_build<<<ncta, 256, 0, st>>>(ix, b, p, ctl, c->q_any.as<uint8_t>(), c->c_task.as<uint32_t>(), F, c->r_left.as<RescueSeg>(),
                                     c->r_right.as<RescueSeg>(), c->rpool.as<uint32_t>(), c->ipool.as<uint32_t>(), M); L++;
@@ -475,30 +501,37 @@ int project_resident(brb_ctx* c, const brb_params& p) {
     o.flags = c->o_flags.as<uint8_t>(); o.sim = c->o_sim.as<double>(); o.clip = c->o_clip.as<int32_t>(); o.coff = c->o_coff.as<uint32_t>();
     o.pool = c->opool.as<uint32_t>(); o.a_roff = c->a_roff.as<uint32_t>(); o.a_rcnt = c->a_rcnt.as<uint32_t>();
     if (rescue) { k_count_valid<<<grid_for(n, 256), 256, 0, st>>>(b, ctl, c->a_cand.as<uint4>(), c->m_rec.as<uint4>()); L++; }
-    const uint32_t nbat = (n + 31) / 32;
+    const uint32_t nbat = (uint32_t)((n + (1u << b.back_shift) - 1) >> b.back_shift);
     BatchTotals tl; tl.agg = c->t_agg.as<unsigned long long>(); tl.claim = c->t_claim.as<unsigned long long>();
     ProvRows pr; pr.row = c->p_row.as<uint4>(); pr.pool = c->p_pool.as<uint32_t>();
     pr.sim = c->have_scores ? c->p_sim.as<double>() : nullptr; pr.clip = c->have_scores ? c->p_clip.as<int32_t>() : nullptr;
     if (ordered) {
-      k_back<true, false><<<ncta_back, 256, 0, st>>>(b, ctl, pv, c->c_stage.as<uint4>(), c->tpool.as<uint32_t>(), tl, pr, o, hres); L++;
+      if (lng) k_back<true, false, true><<<ncta_back, 256, 0, st>>>(b, ctl, pv, c->c_stage.as<uint4>(), c->tpool.as<uint32_t>(), tl, pr, o, hres);
+      else k_back<true, false, false><<<ncta_back, 256, 0, st>>>(b, ctl, pv, c->c_stage.as<uint4>(), c->tpool.as<uint32_t>(), tl, pr, o, hres);
+      L++;
       CU(cudaEventRecord(c->ev[5], st));
       // ---- phase 6: batch totals -> offsets in bundle order; rows to their final place
       exclusive_scan(tl.agg, c->t_off.as<unsigned long long>(), nbat, c->scan_tmp.as<unsigned long long>(), st, &L);
       k_place<<<grid_for(nbat, 8), 256, 0, st>>>(b, ctl, tl, c->t_off.as<unsigned long long>(), pr, o); L++;   // one warp per batch
       k_group_rows<<<grid_for(b.n_groups + 1, 256), 256, 0, st>>>(b, ctl, c->a_roff.as<uint32_t>(), c->g_roff.as<uint32_t>()); L++;
     } else {
-      if (packed) k_back<false, true><<<ncta_back, 256, 0, st>>>(b, ctl, pv, c->c_stage.as<uint4>(), c->tpool.as<uint32_t>(), tl, pr, o, hres);
-      else k_back<false, false><<<ncta_back, 256, 0, st>>>(b, ctl, pv, c->c_stage.as<uint4>(), c->tpool.as<uint32_t>(), tl, pr, o, hres);
+      if (packed && lng) k_back<false, true, true><<<ncta_back, 256, 0, st>>>(b, ctl, pv, c->c_stage.as<uint4>(), c->tpool.as<uint32_t>(), tl, pr, o, hres);
+      else if (packed) k_back<false, true, false><<<ncta_back, 256, 0, st>>>(b, ctl, pv, c->c_stage.as<uint4>(), c->tpool.as<uint32_t>(), tl, pr, o, hres);
+      else if (lng) k_back<false, false, true><<<ncta_back, 256, 0, st>>>(b, ctl, pv, c->c_stage.as<uint4>(), c->tpool.as<uint32_t>(), tl, pr, o, hres);
+      else k_back<false, false, false><<<ncta_back, 256, 0, st>>>(b, ctl, pv, c->c_stage.as<uint4>(), c->tpool.as<uint32_t>(), tl, pr, o, hres);
       L++;
       CU(cudaEventRecord(c->ev[5], st)); back_finishes = true;       // the last CTA to leave publishes the totals
     }
     if (!back_finishes) { k_publish<<<1, 1, 0, st>>>(ctl, hres); L++; CU(cudaEventRecord(c->ev[6], st)); }
     CU(cudaStreamSynchronize(st));                          // the counters are in hres (mapped pinned memory) once the sequence has drained
+    n_syncs++;
     CU(cudaGetLastError());
     c->ctl_clean = true;
     if (hres->bad_input) break;
     bool again = false;
-    if (hres->n_cand > c->cap_cand) { c->cap_cand = grown((uint64_t)hres->n_cand + std::min<uint64_t>((n + 31) / 32, (uint64_t)148 * 8 * 8) * POOL_CHUNK); c->cap_ideal = std::max(c->cap_ideal, grown((uint64_t)4 * c->cap_cand)); again = true; }
+    if (hres->n_cand > c->cap_cand) { c->cap_cand = grown((uint64_t)hres->n_cand + std::min<uint64_t>((n + 31) / 32, (uint64_t)c->n_sm * 8 * 8) * POOL_CHUNK); c->cap_ideal = std::max(c->cap_ideal, grown((uint64_t)4 * c->cap_cand)); again = true; }
+    else if (hres->n_tb > c->cap_tb) { c->cap_tb = grown(hres->n_tb); again = true; }
+    else if (rescue && grow_ksw_big(rescue_bufs(c), hres)) again = true;
     else if (hres->n_ideal > c->cap_ideal) { c->cap_ideal = grown(hres->n_ideal); again = true; }
     else if (hres->n_rows > c->cap_rows) { c->cap_rows = grown(hres->n_rows); c->cap_tmpw = std::max(c->cap_tmpw, grown((uint64_t)8 * c->cap_rows));
                                            c->cap_outw = std::max(c->cap_outw, grown((uint64_t)3 * c->cap_rows)); again = true; }
@@ -508,6 +541,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   }
   if (hres->bad_input == 3) return fail(BRB_E_UNSUPPORTED, "a batch of 32 alignments emits 2^28 or more CIGAR words");
   if (hres->bad_input == 4) return fail(BRB_E_UNSUPPORTED, "BRB_OPT_PACKED_ROWS: the bundle pools 2^27 or more CIGAR words; project it without the option");
+  if (hres->bad_input == 5) return fail(BRB_E_ARG, "CSR offsets (group_off / exon_off / cigar_off) must start at 0, be non-decreasing and end at the column sizes");
   if (hres->bad_input == 1) return fail(BRB_E_ARG, "mate_idx is not a symmetric single link (src/bramble.cpp:272-311)");
   if (hres->bad_input) return fail(BRB_E_ARG, "read exons of an alignment must be ascending and disjoint");
   c->n_cand = hres->n_cand; c->n_rec = hres->n_rows; c->n_out_words = hres->n_outw;
@@ -519,7 +553,8 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   S.kernel_ms = ms_between(c->ev[0], ev_end);
   // algorithmic bytes, SURVEY.md 8(d) / DESIGN.md: per-alignment SoA + 56 B per index hit + output rows + rescue bases
   S.alg_bytes_front = (uint64_t)n * 16 + (uint64_t)b.n_exon * 8 + hres->n_mates * 4 + hres->n_hits * 56;
-  S.alg_bytes = S.alg_bytes_front + (uint64_t)b.n_cigar * 4 + (uint64_t)hres->n_rows * 40 + hres->out_words * 4 + c->rescue_bytes;
+  S.alg_bytes = S.alg_bytes_front + (uint64_t)b.n_cigar * 4 + (uint64_t)hres->n_rows * 40 + hres->out_words * 4 + hres->rescue_bytes;
+  S.ksw_cells = hres->ksw_cells; S.host_syncs = n_syncs;
   c->have_result = true; c->result_ordered = ordered; c->result_packed = packed;
   return BRB_OK;
 }
@@ -595,7 +630,7 @@ int brb_batch_download(brb_ctx* c, brb_batch_out* out) {
 }
 
 int brb_project(brb_ctx* c, const brb_params* p, const brb_batch_in* in, brb_batch_out* out) {
-  int rc = brb_batch_upload(c, in); if (rc) return rc;
+  int rc = batch_upload_async(c, in); if (rc) return rc;        // (the copies are ordered before the kernels on the ctx stream; the call returns after the download)
   rc = brb_project_resident(c, p); if (rc) return rc;
   return brb_batch_download(c, out);
 }
@@ -606,6 +641,7 @@ int brb_ctx_set_option(brb_ctx* c, int option, int value) {
   if (option == BRB_OPT_NO_FASTPATH) { c->opt_no_fastpath = value != 0; return BRB_OK; }
   if (option == BRB_OPT_ORDERED_ROWS) { c->opt_ordered = value != 0; return BRB_OK; }
   if (option == BRB_OPT_PACKED_ROWS) { c->opt_packed = value != 0; return BRB_OK; }
+  if (option == BRB_OPT_MERGE_WARP) { c->opt_merge_warp = value != 0; return BRB_OK; }
   return fail(BRB_E_ARG, "unknown option %d", option);
 }
 
@@ -661,21 +697,32 @@ int brb_merge_cigars(brb_ctx* c, uint32_t n, const uint32_t* real_off, const uin
   CU(cudaSetDevice(c->idx->device));
   if (!n) return BRB_OK;
   const size_t nr = real_off[n], ni = ideal_off[n], no = out_off[n];
-  Buf d_ro, d_r, d_io, d_i, d_oo, d_ol, d_o;
+  Buf d_ro, d_r, d_io, d_i, d_oo, d_ol, d_o, d_so, d_s;
   int rc = 0;
   auto up = [&](Buf& b, const void* src, size_t bytes) { if (rc) return; rc = b.ensure(bytes ? bytes : 4); if (!rc && bytes && cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, c->st) != cudaSuccess) rc = fail(BRB_E_CUDA, "upload failed"); };
   up(d_ro, real_off, (size_t)(n + 1) * 4); up(d_r, real, nr * 4); up(d_io, ideal_off, (size_t)(n + 1) * 4); up(d_i, ideal, ni * 4);
   up(d_oo, out_off, (size_t)(n + 1) * 4);
+  std::vector<uint32_t> scr_off(n + 1, 0);
+  if (c->opt_merge_warp) {                        // BRB_OPT_MERGE_WARP: the warp-cooperative code (one warp per pair) instead of one thread per pair
+    for (uint32_t i = 0; i < n; i++) scr_off[i + 1] = scr_off[i] + merge_warp_scratch(real_off[i + 1] - real_off[i], ideal_off[i + 1] - ideal_off[i]);
+    up(d_so, scr_off.data(), (size_t)(n + 1) * 4);
+    if (!rc) rc = d_s.ensure((size_t)scr_off[n] * 4 + 4);
+  }
   if (!rc) rc = d_ol.ensure((size_t)n * 4);
   if (!rc) rc = d_o.ensure(std::max<size_t>(no, 1) * 4);
   if (!rc) {
-    k_merge_pairs<<<grid_for(n, 128), 128, 0, c->st>>>(n, d_ro.as<uint32_t>(), d_r.as<uint32_t>(), d_io.as<uint32_t>(), d_i.as<uint32_t>(),
-                                                       d_oo.as<uint32_t>(), d_ol.as<uint32_t>(), d_o.as<uint32_t>());
+    if (c->opt_merge_warp)
+      k_merge_pairs_warp<<<grid_for((size_t)n * 32, 128), 128, 0, c->st>>>(n, d_ro.as<uint32_t>(), d_r.as<uint32_t>(), d_io.as<uint32_t>(), d_i.as<uint32_t>(),
+                                                                          d_oo.as<uint32_t>(), d_so.as<uint32_t>(), d_ol.as<uint32_t>(), d_o.as<uint32_t>(), d_s.as<uint32_t>());
+    else
+      k_merge_pairs<<<grid_for(n, 128), 128, 0, c->st>>>(n, d_ro.as<uint32_t>(), d_r.as<uint32_t>(), d_io.as<uint32_t>(), d_i.as<uint32_t>(),
+                                                         d_oo.as<uint32_t>(), d_ol.as<uint32_t>(), d_o.as<uint32_t>());
     cudaMemcpyAsync(out_len, d_ol.p, (size_t)n * 4, cudaMemcpyDeviceToHost, c->st);
     if (no) cudaMemcpyAsync(out, d_o.p, no * 4, cudaMemcpyDeviceToHost, c->st);
     cudaError_t e = cudaStreamSynchronize(c->st);
     if (e != cudaSuccess) rc = fail(BRB_E_CUDA, "brb_merge_cigars: %s", cudaGetErrorString(e));
   }
+  d_so.release(); d_s.release();
   d_ro.release(); d_r.release(); d_io.release(); d_i.release(); d_oo.release(); d_ol.release(); d_o.release();
   return rc;
 }

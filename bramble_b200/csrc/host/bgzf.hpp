@@ -79,7 +79,9 @@ class BgzfReader {
     if (inflateInit2(&zs, -15) != Z_OK) throw std::runtime_error("inflateInit2");
     zs.next_in = const_cast<uint8_t*>(comp.data()); zs.avail_in = (uInt)clen; zs.next_out = out.data(); zs.avail_out = isize;
     const int rc = inflate(&zs, Z_FINISH); inflateEnd(&zs);
-    if (rc != Z_STREAM_END) throw std::runtime_error("BGZF inflate failed");
+    if (rc != Z_STREAM_END || zs.total_out != isize) throw std::runtime_error("BGZF inflate failed");
+    const uint32_t want = comp[clen] | (comp[clen + 1] << 8) | (comp[clen + 2] << 16) | ((uint32_t)comp[clen + 3] << 24);
+    if ((uint32_t)crc32(crc32(0, nullptr, 0), out.data(), isize) != want) throw std::runtime_error("BGZF block CRC mismatch (corrupt input)");
   }
   bool fill() {
     for (;;) {
@@ -164,8 +166,9 @@ class BgzfWriter {
     pool_.clear();
     drain(true);
     static const uint8_t eof[28] = {0x1f, 0x8b, 8, 4, 0, 0, 0, 0, 0, 0xff, 6, 0, 'B', 'C', 2, 0, 0x1b, 0, 3, 0, 0, 0, 0, 0, 0, 0, 0, 0};
-    fwrite(eof, 1, 28, f_);
-    fclose(f_); f_ = nullptr;
+    const bool ok = fwrite(eof, 1, 28, f_) == 28 && !failed_;
+    FILE* f = f_; f_ = nullptr;
+    if (fclose(f) != 0 || !ok) throw std::runtime_error("writing the output BAM failed (" + (err_.empty() ? std::string("I/O error, disk full?") : err_) + ")");
   }
  private:
   struct Job { std::vector<uint8_t> in, out; bool ready = false; };
@@ -189,9 +192,10 @@ class BgzfWriter {
   void compress(Job& j) {
     j.out.resize(compressBound((uLong)j.in.size()) + 32);
     z_stream zs; memset(&zs, 0, sizeof zs);
-    deflateInit2(&zs, level_, Z_DEFLATED, -15, 8, Z_DEFAULT_STRATEGY);
+    if (deflateInit2(&zs, level_, Z_DEFLATED, -15, 8, Z_DEFAULT_STRATEGY) != Z_OK) { fail("deflateInit2 failed"); j.out.clear(); return; }
     zs.next_in = j.in.data(); zs.avail_in = (uInt)j.in.size(); zs.next_out = j.out.data() + 18; zs.avail_out = (uInt)(j.out.size() - 26);
-    deflate(&zs, Z_FINISH); const size_t clen = zs.total_out; deflateEnd(&zs);
+    const int rc = deflate(&zs, Z_FINISH); const size_t clen = zs.total_out; deflateEnd(&zs);
+    if (rc != Z_STREAM_END) { fail("deflate failed"); j.out.clear(); return; }
     static const uint8_t head[16] = {0x1f, 0x8b, 8, 4, 0, 0, 0, 0, 0, 0xff, 6, 0, 'B', 'C', 2, 0};
     memcpy(j.out.data(), head, 16);
     const uint16_t bs = (uint16_t)(clen + 25); memcpy(j.out.data() + 16, &bs, 2);
@@ -203,9 +207,12 @@ class BgzfWriter {
     for (;;) {
       Job* j = nullptr;
       { std::unique_lock<std::mutex> lk(m_); if (order_.empty()) return; if (!order_.front()->ready) { if (!all) return; lk.unlock(); std::this_thread::yield(); continue; } j = order_.front(); order_.pop_front(); }
-      fwrite(j->out.data(), 1, j->out.size(), f_); delete j;
+      if (fwrite(j->out.data(), 1, j->out.size(), f_) != j->out.size()) fail("short write");
+      delete j;
     }
   }
+  void fail(const char* what) { std::unique_lock<std::mutex> lk(m_); failed_ = true; if (err_.empty()) err_ = what; }
+  bool failed_ = false; std::string err_;
   FILE* f_ = nullptr; int level_; std::vector<uint8_t> cur_;
   std::vector<std::thread> pool_; std::mutex m_; std::condition_variable cv_;
   std::deque<Job*> order_, todo_; bool done_ = false;

@@ -77,6 +77,7 @@ Options parse(int argc, char** argv) {
   if (const char* g = getenv("BRB_GPUS")) o.gpus = atoi(g);      // same as --gpus, without changing the @PG CL: text
   if (const char* t = getenv("BRB_THREADS")) o.threads = atoi(t);   // same as -p, without changing the @PG CL: text
   if (const char* l = getenv("BRB_LEVEL")) o.level = atoi(l);
+  if (const char* c = getenv("BRB_CHUNK")) o.chunk = (uint32_t)strtoul(c, nullptr, 10);   // same as --chunk, without changing the @PG CL: text
   if (o.in_bam.empty()) usage("in.bam is required");
   if (o.out_bam.empty()) usage("-o is required");         // required in code, src/bramble.cpp:477-478
   return o;
@@ -268,8 +269,12 @@ int main(int argc, char** argv) {
     for (size_t i = 0; i < ih.ref_names.size(); i++) { auto it = A.refid_of.find(ih.ref_names[i]); if (it != A.refid_of.end()) ref2refid[i] = it->second; }
 
     const int n_gpu = std::max(1, o.gpus);
+    // BRB_GPU_MAP=d0,d1,...: CUDA device of dealer slot k (default: slot k -> device k).  "0,0" runs the whole --gpus 2 path
+    // (dealer, one worker and one index copy per slot, ordered merge) on a single device.
+    std::vector<int> gpu_map(n_gpu); for (int g = 0; g < n_gpu; g++) gpu_map[g] = g;
+    if (const char* gm = getenv("BRB_GPU_MAP")) { int k = 0; for (const char* q = gm; *q && k < n_gpu; k++) { gpu_map[k] = atoi(q); q = strchr(q, ','); if (!q) break; q++; } }
     std::vector<std::unique_ptr<EngineIf>> engines;
-    for (int g = 0; g < n_gpu; g++) { engines.emplace_back(make_engine()); engines.back()->open(g, cols.desc); }
+    for (int g = 0; g < n_gpu; g++) { engines.emplace_back(make_engine()); engines.back()->open(gpu_map[g], cols.desc); }
 
     BgzfWriter out(o.out_bam, o.level, std::max(1, o.threads));
     { std::vector<uint8_t> hb; auto put = [&](const void* p, size_t n) { hb.insert(hb.end(), (const uint8_t*)p, (const uint8_t*)p + n); };
@@ -366,10 +371,14 @@ int main(int argc, char** argv) {
       bundle = new_bundle(); hashread.clear();
     };
     std::vector<uint8_t> rec;
+    std::string producer_err;
+    try {
     for (;;) {
+      { std::unique_lock<std::mutex> lk(m); if (!err.empty()) break; }     // a worker failed: stop reading, nothing would consume the bundles
       int32_t bs = 0;
       const auto tr0 = timing ? clk::now() : clk::time_point();
       if (in.read(&bs, 4) != 4) break;
+      if (bs < 32) throw std::runtime_error("malformed BAM record (block_size < 32)");
       rec.resize(bs); if (in.read(rec.data(), bs) != (size_t)bs) throw std::runtime_error("truncated BAM record");
       if (timing) t_read += secs(tr0, clk::now());
       st.total_reads++;
@@ -400,8 +409,9 @@ int main(int argc, char** argv) {
       prev_name = name;
     }
     push_bundle();
+    } catch (const std::exception& e) { producer_err = e.what(); }        // (truncated record, inflate / CRC error): report it after the threads are joined
     const auto t_loop_end = clk::now();
-    { std::unique_lock<std::mutex> lk(m); eof = true; } cv.notify_all();
+    { std::unique_lock<std::mutex> lk(m); eof = true; if (!producer_err.empty() && err.empty()) err = producer_err; } cv.notify_all();
     for (auto& t : threads) t.join();
     wthread.join();
     if (!err.empty()) { fprintf(stderr, "error: %s\n", err.c_str()); return 1; }

@@ -98,7 +98,7 @@ __device__ __forceinline__ uint32_t real_msum(const uint32_t* __restrict__ real,
 }
 __device__ __forceinline__ bool merge_trivial(uint32_t iword, uint32_t msum) { return (iword & 0xfu) == CM && msum && msum == (iword >> 4); }
 
-__device__ __forceinline__ bool front_overflow(const Ctl* c) { return c->n_cand > c->cap_cand || c->n_ideal > c->cap_ideal || c->bad_input != 0; }
+__device__ __forceinline__ bool front_overflow(const Ctl* c) { return c->n_cand > c->cap_cand || c->n_ideal > c->cap_ideal || c->n_tb > c->cap_tb || c->bad_input != 0; }
 
 // ORDERED: rows go to a provisional buffer as packed records and k_place moves them into bundle order afterwards.
 // !ORDERED: the claimed place is final -- rows are written straight into the output columns, blocks of 32 alignments in
@@ -106,8 +106,10 @@ __device__ __forceinline__ bool front_overflow(const Ctl* c) { return c->n_cand 
 // PACKED (with !ORDERED): the same, but a row is ONE 16-byte record (brb_batch_out::packed_rows, include/bramble_b200.h): a one-word
 // CIGAR below 2^27 travels inside it, any other CIGAR goes to the pool behind a length word -- the pool then only
 // holds the rare multi-word CIGARs and a short-read row costs 16 bytes on the way back to the host instead of 22.
-template <bool ORDERED, bool PACKED>
-__global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __restrict__ ctl, BackIn v, uint4* __restrict__ gstage, uint32_t* __restrict__ tpool,
+// LONG (long-read mode): small batches, rows with long CIGARs merged and copied by the whole warp.  A separate
+// instantiation, so that the short-read kernel keeps its registers (48 at 5 CTAs per SM) for the code it actually runs.
+template <bool ORDERED, bool PACKED, bool LONG>
+__global__ void __launch_bounds__(256, LONG ? 3 : VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __restrict__ ctl, BackIn v, uint4* __restrict__ gstage, uint32_t* __restrict__ tpool,
                                                  BatchTotals tl, ProvRows pv_, Rows o, Ctl* __restrict__ host_result) {
   __shared__ uint4 s_stage[8][BACK_STAGE];                 // per match of the batch: tid (NONE: not emitted), CIGAR words, partner, scratch offset
   __shared__ uint16_t s_queue[8][BACK_STAGE];              // matches that need the general merge
@@ -120,7 +122,10 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
   uint32_t* s_mro = s_own[wid][4]; uint32_t* s_mnrc = s_own[wid][5]; uint32_t* s_words = s_own[wid][6];
   uint32_t* s_rsum = s_own[wid][7]; uint32_t* s_mrsum = s_own[wid][8];
   uint16_t* queue = s_queue[wid];
-  const uint32_t n_batches = (b.n_aln + 31) >> 5;
+  // alignments per batch: 32 (short reads: lane = alignment), fewer for long reads, whose rows are 10^2..10^4 CIGAR words each --
+  // with 32 of them per ticket a bundle has fewer batches than the GPU has warps and the slowest batch is the kernel time
+  const uint32_t BS = LONG ? b.back_shift : 5u, BA = 1u << BS;
+  const uint32_t n_batches = (b.n_aln + BA - 1) >> BS;
   const uint32_t cap_tmpw = ctl->cap_tmpw, cap_rows = ctl->cap_rows, cap_outw = ctl->cap_outw;
   WarpPool wp; wp.cur = 0; wp.end = 0;
   uint32_t n_pooled = 0;                                    // PACKED: rows of this lane whose CIGAR went to the pool (behind a length word)
@@ -133,11 +138,12 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
     }
     const uint32_t wb = wb_next++;
     if (wb >= n_batches) break;
-    const uint32_t a = wb * 32 + lane;
+    const uint32_t a = wb * BA + lane;
+    const bool in_batch = lane < BA && a < b.n_aln;
     uint32_t off = 0, n = 0, m_off = 0, m_n = 0, ro = 0, nrc = 0, mro = 0, mnrc = 0, rsum = 0, mrsum = 0, pflag = 0, nm = 0;
     int32_t mate = -1;
     bool owner = false;
-    if (a < b.n_aln) {
+    if (in_batch) {
       const uint4 ac = __ldg(&v.a_cand[a]);
       mate = __ldg(&b.mate_idx[a]);
       ro = __ldg(&b.cigar_off[a]); nrc = __ldg(&b.cigar_off[a + 1]) - ro;
@@ -154,9 +160,9 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
       }
     }
     {                                                       // ... and an owner takes its mate's from the mate's lane when that is in the batch
-      const uint32_t ml = (uint32_t)mate - wb * 32;
+      const uint32_t ml = (uint32_t)mate - wb * BA;
       const uint32_t got = __shfl_sync(0xffffffffu, rsum, ml & 31u);
-      if (owner && nm) mrsum = ml < 32u ? got : real_msum(b.cigar + mro, mnrc);
+      if (owner && nm) mrsum = ml < BA ? got : real_msum(b.cigar + mro, mnrc);
     }
     const uint32_t incl = warp_incl_scan(n, lane), excl = incl - n, total = __shfl_sync(0xffffffffu, incl, 31);
     const bool staged = total <= BACK_STAGE;
@@ -187,6 +193,34 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
       n_pooled += hdr;
       stage[sidx] = make_uint4(tid, clr + clm + hdr, part, fit ? toff : NOFIT);
       atomicAdd(&s_words[L], clr + clm + hdr);
+    };
+    // the same for ONE row (pair) by the whole warp: long CIGARs (k_merge.cuh: merge_cigars_warp).  Arguments are warp-uniform.
+    auto merge_rows_coop = [&](uint32_t L, uint32_t sidx, uint32_t tid, uint32_t part, const uint4& mr, const uint4& pr) {
+      const bool paired = part != SELF;
+      const uint32_t l_nrc = s_nrc[L], l_mnrc = s_mnrc[L], ni_r = mr.y >> 1, ni_m = pr.y >> 1;
+      const uint32_t cap_r = l_nrc + ni_r + 2, cap_m = paired ? l_mnrc + ni_m + 2 : 0;
+      const uint32_t scr_r = merge_warp_scratch(l_nrc, ni_r), scr_m = paired ? merge_warp_scratch(l_mnrc, ni_m) : 0;
+      bool fit;
+      uint32_t toff = warp_pool_alloc(wp, &ctl->n_tmpw, cap_tmpw, lane == 0 ? 1 + cap_r + cap_m + (scr_r > scr_m ? scr_r : scr_m) : 0, lane, fit);
+      toff = __shfl_sync(0xffffffffu, toff, 0);
+      uint32_t clr = 0, clm = 0;
+      if (fit) {
+        uint32_t* scr = tpool + toff + 1 + cap_r + cap_m;
+        if (ni_r == 1 && merge_trivial(mr.z, s_rsum[L])) { if (lane == 0) tpool[toff + 1] = mr.z; clr = 1; }
+        else clr = merge_cigars_any_warp(b.cigar + s_ro[L], l_nrc, v.ipool + mr.z, ni_r, mr.z, tpool + toff + 1, scr, lane);
+        if (paired) {
+          if (ni_m == 1 && merge_trivial(pr.z, s_mrsum[L])) { if (lane == 0) tpool[toff + 1 + cap_r] = pr.z; clm = 1; }
+          else clm = merge_cigars_any_warp(b.cigar + s_mro[L], l_mnrc, v.ipool + pr.z, ni_m, pr.z, tpool + toff + 1 + cap_r, scr, lane);
+        }
+        if (lane == 0) tpool[toff] = clr;
+      }
+      const uint32_t hdr = PACKED ? (paired ? 2u : 1u) : 0u;
+      if (lane == 0) {
+        n_pooled += hdr;
+        stage[sidx] = make_uint4(tid, clr + clm + hdr, part, fit ? toff : NOFIT);
+        atomicAdd(&s_words[L], clr + clm + hdr);
+      }
+      __syncwarp();
     };
     // ---- phase 1
     for (uint32_t base = 0; base < total; base += 32) {
@@ -255,7 +289,16 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
         mr = __ldg(&v.m_rec[c]);
         if (part != SELF) pr = __ldg(&v.m_rec[part]);
       }
-      merge_rows(go, L, sidx, tid, part, mr, pr);
+      // rows with long CIGARs go through the warp one at a time, the others lane by lane
+      const bool big = LONG && go && (s_nrc[L] + (mr.y >> 1) >= MERGE_COOP_MIN || (part != SELF && s_mnrc[L] + (pr.y >> 1) >= MERGE_COOP_MIN));
+      merge_rows(go && !big, L, sidx, tid, part, mr, pr);
+      if (LONG) for (uint32_t Bm = __ballot_sync(0xffffffffu, big); Bm; Bm &= Bm - 1) {
+        const int src = __ffs(Bm) - 1;
+        const uint4 bmr = make_uint4(__shfl_sync(0xffffffffu, mr.x, src), __shfl_sync(0xffffffffu, mr.y, src), __shfl_sync(0xffffffffu, mr.z, src), __shfl_sync(0xffffffffu, mr.w, src));
+        const uint4 bpr = make_uint4(__shfl_sync(0xffffffffu, pr.x, src), __shfl_sync(0xffffffffu, pr.y, src), __shfl_sync(0xffffffffu, pr.z, src), __shfl_sync(0xffffffffu, pr.w, src));
+        merge_rows_coop(__shfl_sync(0xffffffffu, L, src), __shfl_sync(0xffffffffu, sidx, src), __shfl_sync(0xffffffffu, tid, src),
+                        __shfl_sync(0xffffffffu, part, src), bmr, bpr);
+      }
     }
     __syncwarp();
     words += s_words[lane];
@@ -269,7 +312,7 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
     claim = __shfl_sync(0xffffffffu, claim, 0);
     const uint32_t prow0 = (uint32_t)claim, pword0 = (uint32_t)(claim >> 32);
     const uint32_t row0 = prow0 + irows - rows, word0 = pword0 + iwords - words;
-    if (a < b.n_aln) { o.a_roff[a] = ORDERED ? irows - rows : row0; o.a_rcnt[a] = rows; }     // ORDERED: batch-relative, k_place adds the first row of the batch
+    if (in_batch) { o.a_roff[a] = ORDERED ? irows - rows : row0; o.a_rcnt[a] = rows; }     // ORDERED: batch-relative, k_place adds the first row of the batch
     if (ORDERED && W_b >= (1u << 28)) { if (lane == 0) atomicMax(&ctl->bad_input, 3u); __syncwarp(); continue; }
     if (PACKED && (unsigned long long)pword0 + W_b >= (1u << 27)) { if (lane == 0) atomicMax(&ctl->bad_input, 4u); __syncwarp(); continue; }
     if ((unsigned long long)prow0 + R_b > cap_rows || (unsigned long long)pword0 + W_b > cap_outw) { __syncwarp(); continue; }   // the host grows the row pools and replays
@@ -281,51 +324,66 @@ __global__ void __launch_bounds__(256, VAR_BACK_CTAS) k_back(DevBatch b, Ctl* __
       const uint32_t o_off = __shfl_sync(0xffffffffu, off, L), o_n = __shfl_sync(0xffffffffu, n, L), o_ex = __shfl_sync(0xffffffffu, excl, L);
       const uint32_t o_row0 = __shfl_sync(0xffffffffu, row0, L), o_word0 = __shfl_sync(0xffffffffu, word0, L);
       const int32_t o_mate = __shfl_sync(0xffffffffu, mate, L);
-      if (!actv) continue;
       const uint32_t c = o_off + (item - o_ex);
       const uint32_t s0 = staged ? o_ex : o_off, sidx = staged ? item : c;
-      const uint4 sg = stage[sidx];
+      uint4 sg = make_uint4(NONE, 0, 0, NOFIT);
+      if (actv) sg = stage[sidx];
       const uint32_t tid = sg.x;
-      if (tid == NONE || sg.w == NOFIT) continue;
-      // rank among the emitted matches of the read: ascending tid, slot order among equals; CIGAR words before me
-      uint32_t rank = 0, wpre = 0;
+      // CIGAR copies of this lane's row(s), done after the row columns: short ones by the lane, long ones by the whole warp
+      const uint32_t* j_src[2] = {nullptr, nullptr}; uint32_t j_dst[2] = {0, 0}, j_len[2] = {0, 0}, j_minus = 0;
+      uint32_t* pool = ORDERED ? pv_.pool : o.pool;
+      if (tid != NONE && sg.w != NOFIT) {
+        // rank among the emitted matches of the read: ascending tid, slot order among equals; CIGAR words before me
+        uint32_t rank = 0, wpre = 0;
 #pragma unroll kUnroll
-      for (uint32_t k = 0; k < o_n; k++) {
-        const uint2 e = *reinterpret_cast<const uint2*>(&stage[s0 + k]);
-        if (e.x < tid || (e.x == tid && s0 + k < sidx)) { rank++; wpre += e.y; }        // (NONE is never below a tid)
+        for (uint32_t k = 0; k < o_n; k++) {
+          const uint2 e = *reinterpret_cast<const uint2*>(&stage[s0 + k]);
+          if (e.x < tid || (e.x == tid && s0 + k < sidx)) { rank++; wpre += e.y; }        // (NONE is never below a tid)
+        }
+        const uint32_t part = sg.z;
+        const bool paired = part != SELF, inl = sg.w == INLINE;
+        const uint4 mr = __ldg(&v.m_rec[c]);
+        const uint32_t row = o_row0 + (paired ? 2 * rank : rank), w0 = o_word0 + wpre;
+        const uint32_t clr = inl ? 1u : tpool[sg.w];
+        uint4 m = mr; uint32_t cc = c, aln = wb * BA + L, fl = BRB_REC_FIRST, wpos = w0, len = clr;
+        const uint32_t* src = tpool + sg.w + 1;
+        uint4 pm = make_uint4(0, 0, 0, NONE);
+        if (paired) { pm = __ldg(&v.m_rec[part]); fl |= BRB_REC_PAIRED | (pm.w == tid ? BRB_REC_SAMETX : 0); }
+        for (uint32_t e = 0, ne = paired ? 2 : 1; e < ne; e++) {
+          if (e) {                                            // the mate row follows the read row
+            m = pm; cc = part; aln = (uint32_t)o_mate; fl &= ~BRB_REC_FIRST; wpos = w0 + clr;
+            src = tpool + sg.w + 1 + (s_nrc[L] + (mr.y >> 1) + 2); len = inl ? 1u : sg.y - clr - (PACKED ? 2u : 0u);
+            if (PACKED) wpos = w0 + 1 + clr;
+          }
+          const uint32_t minus = m.y & 1u, r = row + e;
+          if (ORDERED) {
+            pv_.row[r] = make_uint4(aln, m.w, m.x, (wpos - pword0) | (minus << 28) | (fl << 29));
+            if (v.m_sim) { pv_.sim[r] = v.m_sim[cc]; pv_.clip[r] = v.m_clip[cc]; }
+          } else if (PACKED) {
+            st_stream(&pv_.row[r], make_uint4(aln, m.w, m.x, (inl ? (m.z | BRB_ROW_INLINE) : wpos) | (minus << 28) | (fl << 29)));
+            if (v.m_sim) { o.sim[r] = v.m_sim[cc]; o.clip[r] = v.m_clip[cc]; }
+            if (!inl) pool[wpos++] = len;                     // length word, then the CIGAR
+          } else {
+            st_stream(&o.src[r], aln); st_stream(&o.tid[r], m.w); st_stream(&o.pos[r], m.x); st_stream(&o.strand[r], (int8_t)(minus ? '-' : '+'));
+            st_stream(&o.flags[r], (uint8_t)fl); st_stream(&o.coff[r], wpos);
+            if (v.m_sim) { o.sim[r] = v.m_sim[cc]; o.clip[r] = v.m_clip[cc]; }
+          }
+          if (inl) { if (!PACKED) st_stream(&pool[wpos], m.z); }
+          else { j_src[e] = src; j_dst[e] = wpos; j_len[e] = len; j_minus |= minus << e; }
+        }
       }
-      const uint32_t part = sg.z;
-      const bool paired = part != SELF, inl = sg.w == INLINE;
-      const uint4 mr = __ldg(&v.m_rec[c]);
-      const uint32_t row = o_row0 + (paired ? 2 * rank : rank), w0 = o_word0 + wpre;
-      const uint32_t clr = inl ? 1u : tpool[sg.w];
-      uint4 m = mr; uint32_t cc = c, aln = wb * 32 + L, fl = BRB_REC_FIRST, wpos = w0, len = clr;
-      const uint32_t* src = tpool + sg.w + 1;
-      uint4 pm = make_uint4(0, 0, 0, NONE);
-      if (paired) { pm = __ldg(&v.m_rec[part]); fl |= BRB_REC_PAIRED | (pm.w == tid ? BRB_REC_SAMETX : 0); }
-      for (uint32_t e = 0, ne = paired ? 2 : 1; e < ne; e++) {
-        if (e) {                                            // the mate row follows the read row
-          m = pm; cc = part; aln = (uint32_t)o_mate; fl &= ~BRB_REC_FIRST; wpos = w0 + clr;
-          src = tpool + sg.w + 1 + (s_nrc[L] + (mr.y >> 1) + 2); len = inl ? 1u : sg.y - clr - (PACKED ? 2u : 0u);
-          if (PACKED) wpos = w0 + 1 + clr;
+#pragma unroll
+      for (int e = 0; e < 2; e++) {
+        const uint32_t len = j_len[e]; const bool minus = (j_minus >> e) & 1u;
+        const bool wide = LONG && len >= 32;                  // (reversed for '-' transcripts: reverse_complement_bam, src/bam.cpp:636-702)
+        if (len && !wide) { if (minus) for (uint32_t i = 0; i < len; i++) pool[j_dst[e] + i] = j_src[e][len - 1 - i]; else for (uint32_t i = 0; i < len; i++) pool[j_dst[e] + i] = j_src[e][i]; }
+        if (LONG) for (uint32_t Bw = __ballot_sync(0xffffffffu, wide); Bw; Bw &= Bw - 1) {
+          const int sl = __ffs(Bw) - 1;
+          const uint32_t* bs = reinterpret_cast<const uint32_t*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(j_src[e]), sl));
+          const uint32_t bd = __shfl_sync(0xffffffffu, j_dst[e], sl), bl = __shfl_sync(0xffffffffu, len, sl);
+          const bool bm = __shfl_sync(0xffffffffu, (uint32_t)minus, sl);
+          if (bm) for (uint32_t i = lane; i < bl; i += 32) pool[bd + i] = bs[bl - 1 - i]; else for (uint32_t i = lane; i < bl; i += 32) pool[bd + i] = bs[i];
         }
-        const uint32_t minus = m.y & 1u, r = row + e;
-        uint32_t* pool = ORDERED ? pv_.pool : o.pool;
-        if (ORDERED) {
-          pv_.row[r] = make_uint4(aln, m.w, m.x, (wpos - pword0) | (minus << 28) | (fl << 29));
-          if (v.m_sim) { pv_.sim[r] = v.m_sim[cc]; pv_.clip[r] = v.m_clip[cc]; }
-        } else if (PACKED) {
-          st_stream(&pv_.row[r], make_uint4(aln, m.w, m.x, (inl ? (m.z | BRB_ROW_INLINE) : wpos) | (minus << 28) | (fl << 29)));
-          if (v.m_sim) { o.sim[r] = v.m_sim[cc]; o.clip[r] = v.m_clip[cc]; }
-          if (!inl) pool[wpos++] = len;                     // length word, then the CIGAR
-        } else {
-          st_stream(&o.src[r], aln); st_stream(&o.tid[r], m.w); st_stream(&o.pos[r], m.x); st_stream(&o.strand[r], (int8_t)(minus ? '-' : '+'));
-          st_stream(&o.flags[r], (uint8_t)fl); st_stream(&o.coff[r], wpos);
-          if (v.m_sim) { o.sim[r] = v.m_sim[cc]; o.clip[r] = v.m_clip[cc]; }
-        }
-        if (inl) { if (!PACKED) st_stream(&pool[wpos], m.z); }
-        else if (minus) for (uint32_t i = 0; i < len; i++) pool[wpos + i] = src[len - 1 - i];      // reverse_complement_bam, src/bam.cpp:636-702
-        else for (uint32_t i = 0; i < len; i++) pool[wpos + i] = src[i];
       }
     }
     __syncwarp();                                           // the staging area is reused by the next batch
@@ -374,7 +432,8 @@ __global__ void k_publish(Ctl* __restrict__ ctl, Ctl* __restrict__ host_result) 
 __global__ void __launch_bounds__(256, VAR_PLACE_CTAS) k_place(DevBatch b, Ctl* __restrict__ ctl, BatchTotals tl, const unsigned long long* __restrict__ t_off,
                                                ProvRows pv, Rows o) {
   if (front_overflow(ctl)) return;
-  const uint32_t n_batches = (b.n_aln + 31) >> 5;
+  const uint32_t BS = b.back_shift, BA = 1u << BS;
+  const uint32_t n_batches = (b.n_aln + BA - 1) >> BS;
   const unsigned long long tot = t_off[n_batches];
   const uint32_t R = (uint32_t)tot, W = (uint32_t)(tot >> 32);
   if (blockIdx.x == 0 && threadIdx.x == 0) { ctl->n_rows = R; ctl->n_outw = W; ctl->out_words = W; }
@@ -386,8 +445,8 @@ __global__ void __launch_bounds__(256, VAR_PLACE_CTAS) k_place(DevBatch b, Ctl* 
     const unsigned long long agg = tl.agg[wb], src = tl.claim[wb], dst = t_off[wb];
     const uint32_t R_b = (uint32_t)agg, W_b = (uint32_t)(agg >> 32);
     const uint32_t srow = (uint32_t)src, sword = (uint32_t)(src >> 32), drow = (uint32_t)dst, dword = (uint32_t)(dst >> 32);
-    const uint32_t a = wb * 32 + lane;
-    if (a < b.n_aln) o.a_roff[a] += drow;
+    const uint32_t a = wb * BA + lane;
+    if (lane < BA && a < b.n_aln) o.a_roff[a] += drow;
     for (uint32_t r0 = 0; r0 < R_b; r0 += 32 * VAR_PLACE_ROWS) {            // several rows per lane in flight
       uint4 x[VAR_PLACE_ROWS];
 #pragma unroll

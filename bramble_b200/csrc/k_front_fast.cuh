@@ -77,6 +77,7 @@ __global__ void __launch_bounds__(256, VAR_FAST_CTAS) k_front_fast(DevIndex ix, 
                                                        uint4* __restrict__ a_cand, uint32_t* __restrict__ ipool, Matches M) {
   __shared__ uint32_t s_all[8][9][32];                    // per alignment of the batch: qs0, qe0, e0, n_ex, excl, n0, lo0, lo1, matches from the queue
   __shared__ uint32_t s_q[8][3][FQ_CAP];                  // queue: record, owner lane | strand << 5, slot
+  if (ctl->bad_input) return;                             // k_validate_batch rejected the CSR offsets: nothing may follow them
   const unsigned lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const uint32_t lt_mask = (1u << lane) - 1u;
   uint32_t (*s_al)[32] = s_all[wid];

@@ -31,6 +31,7 @@ __global__ void __launch_bounds__(256) k_front(DevIndex ix, DevBatch b, brb_para
                                                uint8_t* q_any, uint4* __restrict__ a_cand,
                                                uint32_t* __restrict__ c_rec, uint32_t* __restrict__ c_task,
                                                uint32_t* __restrict__ ipool, Matches M) {
+  if (ctl->bad_input) return;                             // k_validate_batch rejected the CSR offsets: nothing may follow them
   const unsigned lane = threadIdx.x & 31;
   const uint32_t n_batches = (b.n_aln + 31) >> 5;
   const uint32_t cap_cand = ctl->cap_cand, cap_ideal = ctl->cap_ideal;       // constant during the launch
@@ -180,6 +181,7 @@ __global__ void __launch_bounds__(256) k_front(DevIndex ix, DevBatch b, brb_para
 template <bool SIM>
 __global__ void __launch_bounds__(256, VAR_FRONT_CTAS) k_front_short(DevIndex ix, DevBatch b, brb_params p, Ctl* __restrict__ ctl,
                                                         uint4* __restrict__ a_cand, uint32_t* __restrict__ ipool, Matches M) {
+  if (ctl->bad_input) return;                             // k_validate_batch rejected the CSR offsets: nothing may follow them
   const unsigned lane = threadIdx.x & 31;
   __shared__ uint32_t s_all[8][9][32];
   uint32_t (*s_al)[32] = s_all[threadIdx.x >> 5];

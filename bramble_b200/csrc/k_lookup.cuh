@@ -21,6 +21,19 @@ __device__ __forceinline__ bool task_active(const brb_params& p, int8_t read_str
   return true;
 }
 
+// The three CSR offset arrays of a bundle (brb_batch_in): non-decreasing and inside their columns.  Runs once per upload,
+// before any kernel follows an offset; a violation sets bad_input = 5 and every kernel of the sequence returns at once.
+__global__ void __launch_bounds__(256) k_validate_batch(DevBatch b, Ctl* __restrict__ ctl) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  bool bad = false;
+  if (i < b.n_aln) {
+    const uint32_t e0 = b.exon_off[i], e1 = b.exon_off[i + 1], c0 = b.cigar_off[i], c1 = b.cigar_off[i + 1];
+    bad = e1 < e0 || e1 > b.n_exon || c1 < c0 || c1 > b.n_cigar;
+  }
+  if (i < b.n_groups) { const uint32_t g0 = b.group_off[i], g1 = b.group_off[i + 1]; bad = bad || g1 < g0 || g1 > b.n_aln; }
+  if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicMax(&ctl->bad_input, 5u);
+}
+
 struct FlatOut { uint32_t nf, first, last, nhit; };   // survivors, first survivor, last survivor + 1, overlapping records
 
 // Warp-cooperative filtered scan of 32 index ranges, counting pass.  Lane inputs: lo, n (0 = nothing), qs, qe,

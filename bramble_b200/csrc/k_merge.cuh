@@ -135,6 +135,223 @@ __device__ __noinline__ uint32_t merge_cigars(const uint32_t* __restrict__ real,
   return n;
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Warp-cooperative merge_cigars for long CIGARs (long reads: 10^2..10^4 ops).  Same result as the serial code above, word
+// for word; the serial two-cursor loop is re-expressed so that every real op can work out its own output pieces:
+//   * both CIGARs advance along one axis: a real op consumes its length unless it is N or I, an ideal op unless it is D or
+//     the override D.  Inclusive prefix sums give every op its interval [s, e) on that axis.
+//   * a consuming real op emits one piece per ideal op it overlaps (merge_ops of the pair, nothing for real D under an
+//     ideal S/I), the ideal Ds located in [s, e) in between, and -- once the ideal CIGAR is used up -- the rest of itself
+//     verbatim.  Real I emits itself; real N nothing (or itself when the ideal CIGAR is already used up).  Whatever the
+//     ideal CIGAR has left when the real one ends is copied verbatim.  Ties on one coordinate resolve like the serial
+//     loop's if-chain: real N/I first, then the ideal Ds, then the next chunk.
+//   * the pieces, in real-op order, are exactly the serial loop's add() calls; one run-length pass coalesces them.
+// The leading-clip phases (1) and (2) run as in the serial code (a handful of iterations, every lane redundantly); the
+// I-between-clips fix-up (4)/(5) runs on lane 0 in the rare case it applies.  A zero-length real op (not valid BAM)
+// makes the serial loop's tie order depend on it: such a CIGAR is handed back (MERGE_SERIAL) and merged by the serial code.
+// tools/merge_proto.cpp is this formulation as plain loops, checked against the oracle on 3M random CIGAR pairs.
+constexpr uint32_t MERGE_SERIAL = 0xffffffffu;
+constexpr uint32_t MERGE_COOP_MIN = 48;          // real + ideal ops from which a row is merged by the whole warp
+
+// scratch words merge_cigars_warp needs besides `out` (capacity n_real + n_ideal + 2)
+__host__ __device__ __forceinline__ uint32_t merge_warp_scratch(uint32_t n_real, uint32_t n_ideal) { return n_real + 3 * n_ideal + 16; }
+
+__device__ __noinline__ uint32_t merge_cigars_warp(const uint32_t* __restrict__ real, uint32_t nR, const uint32_t* __restrict__ ideal_, uint32_t nI,
+                                                   uint32_t iword, uint32_t* __restrict__ out, uint32_t* __restrict__ scr, unsigned lane) {
+  auto ideal = [&](uint32_t k) -> uint32_t { return nI == 1 ? iword : ideal_[k]; };
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  uint32_t* EI = scr;                                  // [nI] inclusive prefix sums of the ideal ops' consumed lengths
+  uint32_t* pc = scr + nI + 1;                         // pieces, (len << 4) | op
+  uint32_t np = 0;
+  auto add = [&](uint32_t op, uint32_t len) { if (len && op != OP_SKIP) { if (lane == 0) pc[np] = (len << 4) | op; np++; } };
+  // ---- phases (1), (2): leading hard / soft clip, as in merge_cigars (uniform: every lane runs them, lane 0 writes)
+  uint32_t front_hard = 0, front_soft = 0, ci = 0;
+  if (nR > 0 && (real[0] & 0xfu) == CH) { front_hard = real[0] >> 4; ci++; }
+  if (ci < nR && (real[ci] & 0xfu) == CS) front_soft = real[ci] >> 4;
+  uint32_t ri = 0, ii = 0, rpos = 0, ipos = 0, clips = front_hard;
+  while (clips > 0 && ri < nR) {
+    const uint32_t rw = real[ri], avail = (rw >> 4) - rpos, chunk = clips < avail ? clips : avail;
+    add(rw & 0xfu, chunk); clips -= chunk; rpos += chunk;
+    if (rpos >= (rw >> 4)) { ri++; rpos = 0; }
+  }
+  clips = front_soft;
+  while (clips > 0 && ri < nR) {
+    const uint32_t rw = real[ri], rop = rw & 0xfu, rrem = (rw >> 4) - rpos;
+    const bool have_i = ii < nI;
+    const uint32_t iw = have_i ? ideal(ii) : 0, iop = have_i ? (iw & 0xfu) : 0xffu, irem = have_i ? (iw >> 4) - ipos : 0xffffffffu;
+    const bool ov = have_i && (iop == OV_M || iop == OV_D || iop == OV_I || iop == OV_S);
+    if (ov && iop == OV_D) { add(merge_ops(rop, iop), irem); ipos += irem; if (ipos >= (iw >> 4)) { ii++; ipos = 0; } }
+    else {
+      uint32_t chunk = clips; if (chunk > rrem) chunk = rrem; if (ov && chunk > irem) chunk = irem;
+      add(merge_ops(rop, iop), chunk); clips -= chunk; rpos += chunk;
+      if (rpos >= (rw >> 4)) { ri++; rpos = 0; }
+      if (ov) { ipos += chunk; if (ipos >= (iw >> 4)) { ii++; ipos = 0; } }
+    }
+  }
+  const uint32_t nr = nR - ri, ni = nI - ii;
+  // ---- prefix sums of the ideal side
+  uint32_t SI = 0;
+  for (uint32_t base = 0; base < ni; base += 32) {
+    const uint32_t m = base + lane;
+    uint32_t c = 0;
+    if (m < ni) { const uint32_t iw = ideal(ii + m), op = iw & 0xfu; c = (op == CD || op == OV_D) ? 0u : (iw >> 4) - (m == 0 ? ipos : 0u); }
+    const uint32_t incl = warp_incl_scan(c, lane) + SI;
+    if (m < ni) EI[m] = incl;
+    SI = __shfl_sync(0xffffffffu, incl, 31);
+  }
+  __syncwarp();
+  auto ilen = [&](uint32_t m) { return (ideal(ii + m) >> 4) - (m == 0 ? ipos : 0u); };
+  auto icons = [&](uint32_t m) { const uint32_t op = ideal(ii + m) & 0xfu; return (op == CD || op == OV_D) ? 0u : ilen(m); };
+  // ideal cursor when the real side stands at coordinate x: ops that end before x, and a positive-length consumer that
+  // ends exactly at x, are done; zero-consumers located at x are still pending
+  auto ii_at = [&](uint32_t x) {
+    uint32_t lo = 0, n = ni;
+    while (n > 0) { const uint32_t h = n >> 1; if (EI[lo + h] < x) { lo += h + 1; n -= h + 1; } else n = h; }
+    if (lo < ni && EI[lo] == x && icons(lo) > 0) lo++;
+    return lo;
+  };
+  // ---- the real side, 32 ops at a time (lane = op)
+  uint32_t S0 = 0;
+  for (uint32_t base = 0; base < nr; base += 32) {
+    const uint32_t k = base + lane;
+    const bool act = k < nr;
+    uint32_t rop = CN, rlen = 0;
+    if (act) { const uint32_t rw = real[ri + k]; rop = rw & 0xfu; rlen = (rw >> 4) - (k == 0 ? rpos : 0u); }
+    if (__any_sync(0xffffffffu, act && rlen == 0)) return MERGE_SERIAL;
+    const bool zero_op = rop == CN || rop == CI;
+    const uint32_t cons = (act && !zero_op) ? rlen : 0u;
+    const uint32_t e = warp_incl_scan(cons, lane) + S0, s = e - cons;
+    S0 = __shfl_sync(0xffffffffu, e, 31);
+    // the op's pieces: counted (the first two are kept in registers), then written at their place in real-op order
+    uint32_t cnt = 0, p0 = 0, p1 = 0;
+    auto emit = [&](uint32_t op, uint32_t len, uint32_t* dst) {
+      if (len == 0 || op == OP_SKIP) return;
+      const uint32_t w = (len << 4) | op;
+      if (dst) dst[cnt] = w; else if (cnt == 0) p0 = w; else if (cnt == 1) p1 = w;
+      cnt++;
+    };
+    auto pieces_of = [&](uint32_t* dst) {
+      cnt = 0;
+      if (!act) return;
+      if (zero_op) {
+        if (rop == CI) emit(CI, rlen, dst);
+        else if (!(ii_at(s) < ni)) emit(CN, rlen, dst);       // the ideal CIGAR is used up: real ops are copied verbatim
+        return;
+      }
+      uint32_t m = ii_at(s), cur = s;
+      for (; m < ni; m++) {
+        const uint32_t iw = ideal(ii + m), iop = iw & 0xfu, il = (iw >> 4) - (m == 0 ? ipos : 0u);
+        const uint32_t ic = (iop == CD || iop == OV_D) ? 0u : il, em = EI[m], sm = em - ic;
+        if (ic == 0) {                                        // zero-consumer at coordinate em
+          if (em >= e) break;                                 // it waits for the real op that starts there
+          if (iop == CD || iop == OV_D) emit(CD, il, dst);
+          continue;
+        }
+        if (sm >= e) break;
+        const uint32_t a = sm > cur ? sm : cur, bnd = em < e ? em : e;
+        if (!(rop == CD && (iop == CS || iop == OV_S || iop == CI || iop == OV_I))) emit(merge_ops(rop, iop), bnd - a, dst);
+        cur = bnd;
+        if (em > e) break;                                    // the ideal op continues under the next real op
+      }
+      if (m >= ni) { const uint32_t from = SI > s ? SI : s; if (e > from) emit(rop, e - from, dst); }     // ideal used up: the rest verbatim
+    };
+    pieces_of(nullptr);
+    const uint32_t mine = cnt;
+    const uint32_t incl = warp_incl_scan(mine, lane), off = np + incl - mine;
+    if (mine == 1) pc[off] = p0;
+    else if (mine == 2) { pc[off] = p0; pc[off + 1] = p1; }
+    else if (mine > 2) pieces_of(pc + off);
+    np += __shfl_sync(0xffffffffu, incl, 31);
+  }
+  // ---- real side used up: the rest of the ideal CIGAR verbatim
+  {
+    const uint32_t SR = S0, m0 = ii_at(SR);
+    for (uint32_t base = m0; base < ni; base += 32) {
+      const uint32_t m = base + lane;
+      uint32_t w = 0;
+      if (m < ni) {
+        const uint32_t iw = ideal(ii + m), iop = iw & 0xfu, il = (iw >> 4) - (m == 0 ? ipos : 0u);
+        const uint32_t ic = (iop == CD || iop == OV_D) ? 0u : il, em = EI[m], sm = em - ic;
+        const uint32_t len = ic == 0 ? il : em - (sm > SR ? sm : SR);
+        if (len) w = (len << 4) | iop;
+      }
+      const uint32_t V = __ballot_sync(0xffffffffu, w != 0);
+      if (w) pc[np + __popc(V & lt_mask)] = w;
+      np += __popc(V);
+    }
+  }
+  __syncwarp();
+  // ---- run-length coalescing of the pieces into `out`
+  uint32_t n_out = 0, open_w = 0; bool have_open = false, saw_i = false;
+  for (uint32_t base = 0; base < np; base += 32) {
+    const uint32_t i = base + lane;
+    const bool v = i < np;
+    const uint32_t w = v ? pc[i] : 0u, op = w & 0xfu, len = w >> 4;
+    uint32_t prev_op = __shfl_up_sync(0xffffffffu, op, 1);
+    if (lane == 0) prev_op = have_open ? (open_w & 0xfu) : 0xffu;
+    const bool head = v && op != prev_op;
+    const uint32_t H = __ballot_sync(0xffffffffu, head), V = __ballot_sync(0xffffffffu, v);
+    const uint32_t L = warp_incl_scan(len, lane);                       // (invalid lanes add 0)
+    const int last_v = 31 - __clz(V);
+    if (H == 0) { open_w += __shfl_sync(0xffffffffu, L, last_v) << 4; continue; }
+    const int first_h = __ffs(H) - 1;
+    // the pieces before the first head extend the open run, which is then closed
+    const uint32_t before = first_h > 0 ? __shfl_sync(0xffffffffu, L, first_h - 1) : 0u;
+    if (have_open && lane == 0) out[n_out - 1] = open_w + (before << 4);
+    // every head but the last closes inside this tile
+    const uint32_t above = H & ~((2u << lane) - 1u);                    // heads after me
+    const int next_h = above ? __ffs(above) - 1 : -1;
+    const uint32_t run_end = __shfl_sync(0xffffffffu, L, next_h > 0 ? next_h - 1 : last_v);
+    const uint32_t L_before_me = L - len;
+    if (head) {
+      const uint32_t word = ((run_end - L_before_me) << 4) | op;
+      const uint32_t idx = n_out + __popc(H & lt_mask);
+      if (next_h >= 0) out[idx] = word;
+      if (op == CI) saw_i = true;
+    }
+    const int last_h = 31 - __clz(H);
+    const uint32_t last_word = (((__shfl_sync(0xffffffffu, L, last_v) - __shfl_sync(0xffffffffu, L_before_me, last_h)) << 4)) | __shfl_sync(0xffffffffu, op, last_h);
+    n_out += __popc(H); open_w = last_word; have_open = true;
+  }
+  if (have_open && lane == 0) out[n_out - 1] = open_w;
+  __syncwarp();
+  if (!__any_sync(0xffffffffu, saw_i)) return n_out;
+  // ---- (4) an I between clips becomes that clip, (5) re-coalesce: only ever matters when such an I exists
+  bool hit = false;
+  for (uint32_t i = 1 + lane; i + 1 < n_out; i += 32) {
+    if ((out[i] & 0xfu) != CI) continue;
+    const uint32_t prev = out[i - 1] & 0xfu, next = out[i + 1] & 0xfu;
+    if ((prev == CS || prev == CH) && (next == CS || next == CH)) hit = true;
+  }
+  if (!__any_sync(0xffffffffu, hit)) return n_out;
+  uint32_t n = 0;
+  if (lane == 0) {
+    for (uint32_t i = 1; i + 1 < n_out; i++) {
+      if ((out[i] & 0xfu) != CI) continue;
+      const uint32_t prev = out[i - 1] & 0xfu, next = out[i + 1] & 0xfu;
+      if ((prev == CS || prev == CH) && (next == CS || next == CH)) out[i] = ((out[i] >> 4) << 4) | prev;
+    }
+    for (uint32_t i = 0; i < n_out; i++) {
+      const uint32_t op = out[i] & 0xfu, len = out[i] >> 4;
+      if (n > 0 && (out[n - 1] & 0xfu) == op) out[n - 1] += (len << 4); else out[n++] = (len << 4) | op;
+    }
+  }
+  __syncwarp();
+  return __shfl_sync(0xffffffffu, n, 0);
+}
+
+// One merge by the whole warp, whatever its shape (cooperative code, serial code on lane 0 where that is required).
+__device__ __forceinline__ uint32_t merge_cigars_any_warp(const uint32_t* __restrict__ real, uint32_t nR, const uint32_t* __restrict__ ideal, uint32_t nI,
+                                                          uint32_t iword, uint32_t* __restrict__ out, uint32_t* __restrict__ scr, unsigned lane) {
+  uint32_t n = merge_cigars_warp(real, nR, ideal, nI, iword, out, scr, lane);
+  if (n == MERGE_SERIAL) {
+    __syncwarp();
+    if (lane == 0) n = merge_cigars(real, nR, ideal, nI, iword, out);
+    n = __shfl_sync(0xffffffffu, n, 0);
+  }
+  return n;
+}
+
 // Standalone entry for the parity tests (brb_merge_cigars).
 __global__ void k_merge_pairs(uint32_t n, const uint32_t* real_off, const uint32_t* real, const uint32_t* ideal_off,
                               const uint32_t* ideal, const uint32_t* out_off, uint32_t* out_len, uint32_t* out) {
@@ -143,6 +360,18 @@ __global__ void k_merge_pairs(uint32_t n, const uint32_t* real_off, const uint32
   const uint32_t ni = ideal_off[i + 1] - ideal_off[i];
   out_len[i] = merge_cigars(real + real_off[i], real_off[i + 1] - real_off[i], ideal + ideal_off[i], ni, ni == 1 ? ideal[ideal_off[i]] : 0,
                             out + out_off[i]);
+}
+
+// The same pairs, one warp each, through the cooperative code.
+__global__ void k_merge_pairs_warp(uint32_t n, const uint32_t* real_off, const uint32_t* real, const uint32_t* ideal_off,
+                                   const uint32_t* ideal, const uint32_t* out_off, const uint32_t* scr_off, uint32_t* out_len, uint32_t* out, uint32_t* scr) {
+  const uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const unsigned lane = threadIdx.x & 31;
+  if (i >= n) return;
+  const uint32_t ni = ideal_off[i + 1] - ideal_off[i];
+  const uint32_t len = merge_cigars_any_warp(real + real_off[i], real_off[i + 1] - real_off[i], ideal + ideal_off[i], ni, ni == 1 ? ideal[ideal_off[i]] : 0,
+                                             out + out_off[i], scr + scr_off[i], lane);
+  if (lane == 0) out_len[i] = len;
 }
 
 }  // namespace brb

@@ -1,84 +1,95 @@
 // Host driver of the clip-rescue phase + brb_ksw_extend (included at the end of engine.cu).
+// No host round trip inside the phase: the plan kernel sorts the problems into size-class queues on the device, every
+// class kernel is launched with a fixed persistent grid and takes its problems by ticket, pools have capacities that
+// persist across calls (a bundle that needs more is counted, the host grows the pool and replays the whole sequence).
 namespace {
 
-struct KswScratch { Buf pmat, state; uint32_t warps = 0; size_t pmat_stride = 0; uint32_t state_stride = 0; };
+struct KswClassCfg { int G, W, ctas_per_sm; };
+constexpr KswClassCfg kKswCfg[4] = {{8, 2, 4}, {16, 2, 4}, {32, 2, 4}, {32, 8, 1}};
+inline uint32_t ksw_rows_cap(int cls) { const int qmax = kKswCfg[cls].G * kKswCfg[cls].W * 2; return (uint32_t)(2 * qmax + KSW_TAIL - 1); }
+inline size_t ksw_group_bytes(int cls) { return (size_t)ksw_rows_cap(cls) * kKswCfg[cls].G * kKswCfg[cls].W * 2; }
 
-// Sizes the per-warp scratch of k_ksw for the largest problem and launches it.
-int launch_ksw(cudaStream_t st, KswProblems P, unsigned long long max_mat, unsigned long long max_tlen, KswScratch& S, uint64_t* launches) {
-  uint32_t ctas = 148 * 4;
-  if ((uint64_t)ctas * KSW_WARPS > P.n) ctas = (uint32_t)((P.n + KSW_WARPS - 1) / KSW_WARPS);
-  if (ctas == 0) ctas = 1;
-  size_t stride = ((size_t)max_mat + 127) & ~(size_t)127; if (stride == 0) stride = 128;
-  const size_t budget = (size_t)24 << 30;
-  while (ctas > 1 && stride * ctas * KSW_WARPS > budget) ctas /= 2;
-  S.warps = ctas * KSW_WARPS; S.pmat_stride = stride;
-  ENS(S.pmat, stride * S.warps);
-  S.state_stride = 0;
-  if (max_tlen + 1 > (unsigned long long)KSW_SH_T) {
-    S.state_stride = (uint32_t)((max_tlen + 1 + 15) & ~15ull);
-    ENS(S.state, (size_t)S.state_stride * 4 * S.warps);
-  }
-  k_ksw<<<ctas, 32 * KSW_WARPS, 0, st>>>(P, S.pmat.as<uint8_t>(), S.pmat_stride, S.state.as<int8_t>(), S.state_stride);
-  (*launches)++;
-  return 0;
-}
-
-struct RescueBufs { Buf qlen, tlen, tbcap, q_off, t_off, tb_off, qbuf, tbuf, tb, kout, aln_group; KswScratch ks; };
+struct RescueBufs {
+  Buf qlen, tlen, tb_off, queue, tb, kout, aln_group, pmat[4], big_pmat, big_seq, big_state;
+  uint32_t ctas[4] = {0, 0, 0, 0};
+  size_t big_mat = 0; uint32_t big_len = 0, big_state_len = 0, big_ctas = 0;     // per-warp scratch of k_ksw_big (capacities persist)
+};
 RescueBufs& rescue_bufs(brb_ctx* c) { if (!c->rb) c->rb = new RescueBufs(); return *c->rb; }
 void free_rescue_bufs(brb_ctx* c) {
   if (!c->rb) return;
   RescueBufs& R = *c->rb;
-  for (Buf* b : {&R.qlen, &R.tlen, &R.tbcap, &R.q_off, &R.t_off, &R.tb_off, &R.qbuf, &R.tbuf, &R.tb, &R.kout, &R.aln_group, &R.ks.pmat, &R.ks.state}) b->release();
+  for (Buf* b : {&R.qlen, &R.tlen, &R.tb_off, &R.queue, &R.tb, &R.kout, &R.aln_group, &R.pmat[0], &R.pmat[1], &R.pmat[2], &R.pmat[3], &R.big_pmat, &R.big_seq, &R.big_state}) b->release();
   delete c->rb; c->rb = nullptr;
 }
 
-int run_rescue(brb_ctx* c, const brb_params& p) {
+// Scratch of the class kernels (fixed per class and SM count) and of the big-problem kernel (sized by what the last sequence asked for).
+int ensure_ksw_scratch(RescueBufs& R, int n_sm) {
+  for (int k = 0; k < 4; k++) {
+    R.ctas[k] = (uint32_t)(n_sm * kKswCfg[k].ctas_per_sm);
+    ENS(R.pmat[k], (size_t)R.ctas[k] * KSW_WARPS * (32 / kKswCfg[k].G) * ksw_group_bytes(k));
+  }
+  R.big_ctas = (uint32_t)n_sm;
+  const size_t warps = (size_t)R.big_ctas * KSW_WARPS;
+  ENS(R.big_pmat, std::max<size_t>(R.big_mat, 128) * warps); ENS(R.big_seq, (size_t)std::max<uint32_t>(R.big_len, 16) * 2 * warps);
+  ENS(R.big_state, (size_t)std::max<uint32_t>(R.big_state_len, 16) * 4 * warps);
+  return 0;
+}
+
+template <int G, int W>
+void launch_ksw_class(cudaStream_t st, uint32_t ctas, const DevIndex& ix, const DevBatch& b, const KswSrc& S, const KswWork& K, int cls, uint32_t n_direct, Ctl* ctl, uint8_t* pmat) {
+  k_ksw_group<G, W><<<ctas, 32 * KSW_WARPS, 0, st>>>(ix, b, S, K, cls, n_direct, ctl, pmat, ksw_rows_cap(cls));
+}
+
+// The DP kernels of all classes on the queues that `ctl` / K describe.  n_direct != nullptr: explicit problem counts (brb_ksw_extend).
+void launch_ksw_all(cudaStream_t st, RescueBufs& R, const DevIndex& ix, const DevBatch& b, const KswSrc& S, const KswWork& K, Ctl* ctl, const uint32_t* n_direct, uint64_t* L) {
+  auto nd = [&](int k) { return n_direct ? n_direct[k] : 0u; };
+  if (!n_direct || nd(0)) { launch_ksw_class<8, 2>(st, R.ctas[0], ix, b, S, K, 0, nd(0), ctl, R.pmat[0].as<uint8_t>()); (*L)++; }
+  if (!n_direct || nd(1)) { launch_ksw_class<16, 2>(st, R.ctas[1], ix, b, S, K, 1, nd(1), ctl, R.pmat[1].as<uint8_t>()); (*L)++; }
+  if (!n_direct || nd(2)) { launch_ksw_class<32, 2>(st, R.ctas[2], ix, b, S, K, 2, nd(2), ctl, R.pmat[2].as<uint8_t>()); (*L)++; }
+  if (!n_direct || nd(3)) { launch_ksw_class<32, 8>(st, R.ctas[3], ix, b, S, K, 3, nd(3), ctl, R.pmat[3].as<uint8_t>()); (*L)++; }
+  if (!n_direct || nd(4)) {
+    KswBig B; B.pmat = R.big_pmat.as<uint8_t>(); B.pmat_stride = R.big_mat; B.seq = R.big_seq.as<uint8_t>(); B.seq_stride = R.big_len;
+    B.state = R.big_state.as<int8_t>(); B.state_stride = R.big_state_len;
+    k_ksw_big<<<R.big_ctas, 32 * KSW_WARPS, 0, st>>>(ix, b, S, K, nd(4), ctl, B); (*L)++;
+  }
+}
+
+// After a sequence: did the big-problem kernel skip anything?  Then its scratch grows to what the plan kernel saw.
+bool grow_ksw_big(RescueBufs& R, const Ctl* h) {
+  if (!h->ksw_big_skipped) return false;
+  R.big_mat = std::max<size_t>(R.big_mat, (((size_t)h->ksw_max_mat + 127) & ~(size_t)127));
+  R.big_len = std::max<uint32_t>(R.big_len, (uint32_t)((std::max(h->ksw_max_qlen, h->ksw_max_tlen) + 16 + 15) & ~15ull));
+  if (h->ksw_max_tlen + 1 > (unsigned long long)KSW_SH_T) R.big_state_len = std::max<uint32_t>(R.big_state_len, (uint32_t)((h->ksw_max_tlen + 1 + 15) & ~15ull));
+  return true;
+}
+
+// plan -> class kernels -> finish, all on the ctx stream; arrays are sized by the pool capacities.
+int launch_rescue(brb_ctx* c, const brb_params& p, uint64_t* L) {
   RescueBufs& R = rescue_bufs(c);
   cudaStream_t st = c->st;
-  uint64_t L = c->stats.n_launches;
-  const uint32_t C = c->n_cand, slots = 2 * C;
+  const size_t C = c->cap_cand, slots = 2 * C;
   DevBatch& b = c->b; const DevIndex& ix = c->idx->d;
   Ctl* ctl = c->ctl.as<Ctl>();
   ENS(R.aln_group, (size_t)b.n_aln * 4);
-  ENS(R.qlen, (size_t)slots * 4); ENS(R.tlen, (size_t)slots * 4); ENS(R.tbcap, (size_t)slots * 4);
-  ENS(R.q_off, (size_t)(slots + 1) * 4); ENS(R.t_off, (size_t)(slots + 1) * 4); ENS(R.tb_off, (size_t)(slots + 1) * 4);
-  ENS(c->r_left, (size_t)C * sizeof(RescueSeg)); ENS(c->r_right, (size_t)C * sizeof(RescueSeg));
-  ENS(R.kout, (size_t)slots * sizeof(KswOut));
-  ENS(c->scan_tmp, scan_scratch_words(slots) * 4);
-  k_aln_group<<<grid_for(b.n_groups, 128), 128, 0, st>>>(b, R.aln_group.as<uint32_t>()); L++;
+  ENS(R.qlen, slots * 4); ENS(R.tlen, slots * 4); ENS(R.tb_off, slots * 4); ENS(R.queue, (size_t)KSW_CLASSES * slots * 4);
+  ENS(c->r_left, C * sizeof(RescueSeg)); ENS(c->r_right, C * sizeof(RescueSeg));
+  ENS(R.kout, slots * sizeof(KswOut));
+  ENS(R.tb, (size_t)c->cap_tb * 4 + 16); ENS(c->rpool, (size_t)c->cap_tb * 4 + 16);
+  { int r = ensure_ksw_scratch(R, c->n_sm); if (r) return r; }
+  k_aln_group<<<grid_for(b.n_groups, 128), 128, 0, st>>>(b, R.aln_group.as<uint32_t>()); (*L)++;
   b.aln_group = R.aln_group.as<uint32_t>();
-  RescuePlan plan; plan.qlen = R.qlen.as<uint32_t>(); plan.tlen = R.tlen.as<uint32_t>(); plan.tbcap = R.tbcap.as<uint32_t>();
-  k_rescue_plan<<<grid_for(slots, 128), 128, 0, st>>>(ix, b, p, C, c->c_task.as<uint32_t>(), c->c_first.as<uint32_t>(), c->c_last.as<uint32_t>(),
-                                                      c->c_cap.as<uint32_t>(), plan, ctl); L++;
-  exclusive_scan(plan.qlen, R.q_off.as<uint32_t>(), slots, c->scan_tmp.as<uint32_t>(), st, &L);
-  exclusive_scan(plan.tlen, R.t_off.as<uint32_t>(), slots, c->scan_tmp.as<uint32_t>(), st, &L);
-  exclusive_scan(plan.tbcap, R.tb_off.as<uint32_t>(), slots, c->scan_tmp.as<uint32_t>(), st, &L);
-  uint32_t* hs = c->h_small.as<uint32_t>();
-  CU(cudaMemcpyAsync(hs, R.q_off.as<uint32_t>() + slots, 4, cudaMemcpyDeviceToHost, st));
-  CU(cudaMemcpyAsync(hs + 1, R.t_off.as<uint32_t>() + slots, 4, cudaMemcpyDeviceToHost, st));
-  CU(cudaMemcpyAsync(hs + 2, R.tb_off.as<uint32_t>() + slots, 4, cudaMemcpyDeviceToHost, st));
-  CU(cudaMemcpyAsync(hs + 4, &ctl->ksw_max_mat, 16, cudaMemcpyDeviceToHost, st));
-  CU(cudaStreamSynchronize(st));
-  const uint32_t Q = hs[0], T = hs[1], TB = hs[2];
-  unsigned long long mx[2]; memcpy(mx, hs + 4, 16);
-  c->rescue_bytes = ((uint64_t)Q + T + 1) / 2;
-  ENS(R.qbuf, (size_t)Q + 16); ENS(R.tbuf, (size_t)T + 16); ENS(R.tb, (size_t)(TB + 4) * 4); ENS(c->rpool, (size_t)(TB + 4) * 4);
-  if (Q) {
-    k_rescue_gather<<<grid_for(slots, 128), 128, 0, st>>>(ix, b, p, C, c->c_task.as<uint32_t>(), c->c_first.as<uint32_t>(), c->c_last.as<uint32_t>(),
-                                                          R.q_off.as<uint32_t>(), R.t_off.as<uint32_t>(), R.qbuf.as<uint8_t>(), R.tbuf.as<uint8_t>()); L++;
-    KswProblems P; P.n = slots; P.q_off = R.q_off.as<uint32_t>(); P.t_off = R.t_off.as<uint32_t>(); P.tb_off = R.tb_off.as<uint32_t>();
-    P.q = R.qbuf.as<uint8_t>(); P.t = R.tbuf.as<uint8_t>(); P.tb = R.tb.as<uint32_t>(); P.out = R.kout.as<KswOut>();
-    int r = launch_ksw(st, P, mx[0], mx[1], R.ks, &L); if (r) return r;
-  }
-  k_rescue_finish<<<grid_for(slots, 128), 128, 0, st>>>(C, R.q_off.as<uint32_t>(), R.tb_off.as<uint32_t>(), R.kout.as<KswOut>(), R.tb.as<uint32_t>(),
-                                                        c->rpool.as<uint32_t>(), c->r_left.as<RescueSeg>(), c->r_right.as<RescueSeg>(),
-                                                        c->c_cap.as<uint32_t>(), ctl); L++;
-  c->stats.n_launches = L;
+  KswWork K; K.qlen = R.qlen.as<uint32_t>(); K.tlen = R.tlen.as<uint32_t>(); K.tb_off = R.tb_off.as<uint32_t>(); K.queue = R.queue.as<uint32_t>();
+  K.queue_stride = (uint32_t)slots; K.tb = R.tb.as<uint32_t>(); K.out = R.kout.as<KswOut>();
+  KswSrc S{}; S.c_task = c->c_task.as<uint32_t>(); S.c_first = c->c_first.as<uint32_t>(); S.c_last = c->c_last.as<uint32_t>();
+  k_rescue_plan<<<c->n_sm * 8, 256, 0, st>>>(ix, b, p, S.c_task, S.c_first, S.c_last, c->c_cap.as<uint32_t>(), K, ctl); (*L)++;
+  launch_ksw_all(st, R, ix, b, S, K, ctl, nullptr, L);
+  k_rescue_finish<<<c->n_sm * 8, 128, 0, st>>>(K, c->rpool.as<uint32_t>(), c->r_left.as<RescueSeg>(), c->r_right.as<RescueSeg>(), c->c_cap.as<uint32_t>(), ctl); (*L)++;
   return 0;
 }
 }  // namespace
 
-// K3/K4 standalone: n independent extension problems (codes 0..4), results as ksw_extz_t fields + forward CIGAR.
+// K3/K4 standalone: n independent extension problems (codes 0..4), results as ksw_extz_t fields + forward CIGAR.  The problems go
+// through the same size-class kernels as the clip rescue of brb_project (a queue per class, built here on the host).
 extern "C" int brb_ksw_extend(brb_ctx* c, uint32_t n, const uint64_t* q_off, const uint8_t* q, const uint64_t* t_off, const uint8_t* t,
                               int32_t* max, int32_t* score, int32_t* max_q, int32_t* max_t, uint8_t* zdropped, uint32_t cigar_cap,
                               uint32_t* n_cigar, uint32_t* cigar_out) {
@@ -86,39 +97,54 @@ extern "C" int brb_ksw_extend(brb_ctx* c, uint32_t n, const uint64_t* q_off, con
   if (brb_device_count() <= 0) return fail(BRB_E_NO_DEVICE, "no CUDA device");
   CU(cudaSetDevice(c->idx->device));
   if (!n) return BRB_OK;
-  std::vector<uint32_t> qo(n + 1), to(n + 1), tbo(n + 1);
-  unsigned long long max_mat = 0, max_tlen = 0;
+  if (!c->n_sm) { int sm = 0; c->n_sm = (cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, c->idx->device) == cudaSuccess && sm > 0) ? sm : 148; }
+  std::vector<uint32_t> qo(n + 1), to(n + 1), tbo(n + 1), queue((size_t)KSW_CLASSES * n);
+  uint32_t cnt[KSW_CLASSES] = {0, 0, 0, 0, 0};
+  RescueBufs R;                                   // a private set: the test entry does not touch the context's rescue state
   tbo[0] = 0;
   for (uint32_t i = 0; i <= n; i++) { qo[i] = (uint32_t)(q_off[i] - q_off[0]); to[i] = (uint32_t)(t_off[i] - t_off[0]); }
   for (uint32_t i = 0; i < n; i++) {
     const unsigned long long ql = qo[i + 1] - qo[i], tl = to[i + 1] - to[i];
     tbo[i + 1] = tbo[i] + (uint32_t)(ql + tl + 2);
-    if (ql && tl) { max_mat = std::max(max_mat, (ql + tl - 1) * std::min(ql, tl)); max_tlen = std::max(max_tlen, tl); }
-  }
-  Buf d_qo, d_to, d_tbo, d_q, d_t, d_tb, d_out; KswScratch ks;
-  int rc = 0; uint64_t L = 0;
-  auto up = [&](Buf& b, const void* src, size_t bytes) { if (rc) return; rc = b.ensure(bytes ? bytes : 4); if (!rc && bytes && cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, c->st) != cudaSuccess) rc = fail(BRB_E_CUDA, "upload failed"); };
-  up(d_qo, qo.data(), (size_t)(n + 1) * 4); up(d_to, to.data(), (size_t)(n + 1) * 4); up(d_tbo, tbo.data(), (size_t)(n + 1) * 4);
-  up(d_q, q + q_off[0], qo[n]); up(d_t, t + t_off[0], to[n]);
-  if (!rc) rc = d_tb.ensure((size_t)(tbo[n] + 4) * 4);
-  if (!rc) rc = d_out.ensure((size_t)n * sizeof(KswOut));
-  std::vector<KswOut> ho(n); std::vector<uint32_t> htb(tbo[n] + 4);
-  if (!rc) {
-    KswProblems P; P.n = n; P.q_off = d_qo.as<uint32_t>(); P.t_off = d_to.as<uint32_t>(); P.tb_off = d_tbo.as<uint32_t>();
-    P.q = d_q.as<uint8_t>(); P.t = d_t.as<uint8_t>(); P.tb = d_tb.as<uint32_t>(); P.out = d_out.as<KswOut>();
-    rc = launch_ksw(c->st, P, max_mat, max_tlen, ks, &L);
-    if (!rc) {
-      cudaMemcpyAsync(ho.data(), d_out.p, (size_t)n * sizeof(KswOut), cudaMemcpyDeviceToHost, c->st);
-      cudaMemcpyAsync(htb.data(), d_tb.p, (size_t)tbo[n] * 4, cudaMemcpyDeviceToHost, c->st);
-      cudaError_t e = cudaStreamSynchronize(c->st);
-      if (e != cudaSuccess) rc = fail(BRB_E_CUDA, "brb_ksw_extend: %s", cudaGetErrorString(e));
+    const int cls = (tl > ql + KSW_TAIL) ? 4 : ksw_class_of((uint32_t)ql);      // (a rescue target is never longer than the query + 40; anything else goes to the general kernel)
+    queue[(size_t)cls * n + cnt[cls]++] = i;
+    if (cls == 4 && ql && tl) {
+      R.big_mat = std::max<size_t>(R.big_mat, (size_t)(((ql + tl - 1) * std::min(ql, tl) + 127) & ~127ull));
+      R.big_len = std::max<uint32_t>(R.big_len, (uint32_t)((std::max(ql, tl) + 16 + 15) & ~15ull));
+      if (tl + 1 > (unsigned long long)KSW_SH_T) R.big_state_len = std::max<uint32_t>(R.big_state_len, (uint32_t)((tl + 1 + 15) & ~15ull));
     }
   }
+  Buf d_qo, d_to, d_q, d_t, d_ctl;
+  int rc = 0; uint64_t L = 0;
+  auto up = [&](Buf& b, const void* src, size_t bytes) { if (rc) return; rc = b.ensure(bytes ? bytes : 4); if (!rc && bytes && cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, c->st) != cudaSuccess) rc = fail(BRB_E_CUDA, "upload failed"); };
+  up(d_qo, qo.data(), (size_t)(n + 1) * 4); up(d_to, to.data(), (size_t)(n + 1) * 4); up(R.tb_off, tbo.data(), (size_t)(n + 1) * 4);
+  up(R.queue, queue.data(), queue.size() * 4);
+  up(d_q, q + q_off[0], qo[n]); up(d_t, t + t_off[0], to[n]);
+  if (!rc) rc = R.tb.ensure((size_t)(tbo[n] + 4) * 4);
+  if (!rc) rc = R.kout.ensure((size_t)n * sizeof(KswOut));
+  if (!rc) rc = d_ctl.ensure(sizeof(Ctl));
+  if (!rc) rc = ensure_ksw_scratch(R, c->n_sm);
+  std::vector<KswOut> ho(n); std::vector<uint32_t> htb(tbo[n] + 4);
+  if (!rc) {
+    cudaMemsetAsync(d_ctl.p, 0, sizeof(Ctl), c->st);
+    cudaMemsetAsync(R.kout.p, 0, (size_t)n * sizeof(KswOut), c->st);
+    KswWork K{}; K.tb_off = R.tb_off.as<uint32_t>(); K.queue = R.queue.as<uint32_t>(); K.queue_stride = n; K.tb = R.tb.as<uint32_t>(); K.out = R.kout.as<KswOut>();
+    KswSrc S{}; S.q = d_q.as<uint8_t>(); S.t = d_t.as<uint8_t>(); S.q_off = d_qo.as<uint32_t>(); S.t_off = d_to.as<uint32_t>();
+    DevBatch nb{};
+    launch_ksw_all(c->st, R, c->idx->d, nb, S, K, d_ctl.as<Ctl>(), cnt, &L);
+    cudaMemcpyAsync(ho.data(), R.kout.p, (size_t)n * sizeof(KswOut), cudaMemcpyDeviceToHost, c->st);
+    cudaMemcpyAsync(htb.data(), R.tb.p, (size_t)tbo[n] * 4, cudaMemcpyDeviceToHost, c->st);
+    cudaError_t e = cudaStreamSynchronize(c->st);
+    if (e != cudaSuccess) rc = fail(BRB_E_CUDA, "brb_ksw_extend: %s", cudaGetErrorString(e));
+  }
   if (!rc) for (uint32_t i = 0; i < n; i++) {
+    const bool empty = qo[i + 1] == qo[i] || to[i + 1] == to[i];          // ksw_reset_extz: nothing aligned
+    if (empty) { max[i] = 0; score[i] = BRB_KSW_NEG_INF; max_q[i] = -1; max_t[i] = -1; zdropped[i] = 0; n_cigar[i] = 0; continue; }
     max[i] = ho[i].max; score[i] = ho[i].score; max_q[i] = ho[i].max_q; max_t[i] = ho[i].max_t; zdropped[i] = (uint8_t)ho[i].zdropped;
     n_cigar[i] = ho[i].n_cig;
     for (uint32_t k = 0; k < ho[i].n_cig && k < cigar_cap && cigar_out; k++) cigar_out[(size_t)i * cigar_cap + k] = htb[tbo[i] + ho[i].n_cig - 1 - k];   // ksw_backtrack's final reversal
   }
-  d_qo.release(); d_to.release(); d_tbo.release(); d_q.release(); d_t.release(); d_tb.release(); d_out.release(); ks.pmat.release(); ks.state.release();
+  d_qo.release(); d_to.release(); d_q.release(); d_t.release(); d_ctl.release();
+  for (Buf* b : {&R.qlen, &R.tlen, &R.tb_off, &R.queue, &R.tb, &R.kout, &R.aln_group, &R.pmat[0], &R.pmat[1], &R.pmat[2], &R.pmat[3], &R.big_pmat, &R.big_seq, &R.big_state}) b->release();
   return rc;
 }

@@ -137,6 +137,9 @@ typedef struct brb_stats {
   uint64_t alg_bytes;                   /* algorithmic bytes of the batch (DESIGN.md formula) */
   uint64_t h2d_bytes, d2h_bytes;
   uint64_t alg_bytes_front;             /* the part of alg_bytes that belongs to the front kernel (alignment columns + index hits) */
+  uint64_t ksw_cells;                   /* clip rescue: DP cells (query length x target length) of all problems of the call */
+  uint32_t host_syncs;                  /* host round trips of the call: 1, plus one per pool that had to grow (the sequence replays) */
+  uint32_t reserved_;
 } brb_stats;
 
 int brb_device_count(void);
@@ -152,7 +155,8 @@ int brb_ctx_destroy(brb_ctx* ctx);
 /* End to end: H2D of the batch, all kernels, D2H of the result, stream synchronised on return. */
 int brb_project(brb_ctx* ctx, const brb_params* p, const brb_batch_in* in, brb_batch_out* out);
 
-/* The same split in three so the kernels can be timed with the batch resident in HBM. */
+/* The same split in three so the kernels can be timed with the batch resident in HBM.  brb_batch_upload returns after the
+ * copies have completed: the caller's columns may be reused at once. */
 int brb_batch_upload(brb_ctx* ctx, const brb_batch_in* in);
 int brb_project_resident(brb_ctx* ctx, const brb_params* p);
 int brb_batch_download(brb_ctx* ctx, brb_batch_out* out);
@@ -170,6 +174,9 @@ int brb_ctx_stats(const brb_ctx* ctx, brb_stats* out);
  * (group_rec_off is then valid and aln_rec_off is ascending).  Costs one streaming copy of the rows. */
 #define BRB_OPT_ORDERED_ROWS 3
 #define BRB_OPT_PACKED_ROWS 4      /* rows as 16-byte records (brb_batch_out::packed_rows); ignored while BRB_OPT_ORDERED_ROWS is set */
+/* BRB_OPT_MERGE_WARP != 0: brb_merge_cigars() runs the warp-cooperative merge (the code long-read rows go through inside
+ * brb_project) instead of the one-thread-per-pair code.  Results are identical; for the parity tests. */
+#define BRB_OPT_MERGE_WARP 5
 int brb_ctx_set_option(brb_ctx* ctx, int option, int value);
 /* CUDA-event stopwatch on the ctx stream (what bench.py brackets its K timed steps with). */
 int brb_ctx_timer_start(brb_ctx* ctx);

@@ -40,8 +40,10 @@ for r in rr[2:]:
     d = dict(zip(h, r)); name = re.sub(r"\(.*", "", d["Kernel Name"]).replace("void ", "").replace("brb::", "").strip()
     md.append(f"| {name} | " + " | ".join(d.get(w, "") for w in want) + " |")
     traffic[name] = to_bytes(d["dram__bytes_read.sum"], units["dram__bytes_read.sum"]) + to_bytes(d["dram__bytes_write.sum"], units["dram__bytes_write.sum"])
-json.dump(traffic, open(os.path.join(here, tag + "_traffic.json"), "w"), indent=1)
 b = json.load(open(bench))
+# provenance: bench.py only quotes this capture while the kernel sources, the workload and its size are the ones it was taken on
+json.dump({"engine_src_sha": b["roofline"].get("engine_src_sha"), "workload": b["config"].get("id"), "names": b["config"].get("names_per_gpu"),
+           "kernels": traffic}, open(os.path.join(here, tag + "_traffic.json"), "w"), indent=1)
 md.append("\nDRAM traffic per launch (read+write): " + ", ".join(f"{k}: {v / 1e9:.2f} GB" for k, v in traffic.items()) +
           f"; sum {sum(traffic.values()) / 1e9:.2f} GB vs {b['roofline']['alg_bytes_per_step'] / 1e9:.2f} GB algorithmic.\n")
 md.append("Live bench line of the same build (no profiler):\n\n```\n" + json.dumps(b, indent=1) + "\n```")

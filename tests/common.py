@@ -51,3 +51,29 @@ def add_micro_introns(ann, seed):
                 gap = int(rng.integers(1, 31))
                 ex[k:k + 1] = [(s, cut), (cut + gap + 1, e)]
                 t["exons"] = ex
+
+
+def ksw_problems(seed=17, n=400, short_max=120):
+    """Random extension problems for ksw2 (codes 0..4): every 4th an unrelated target, the others the query with
+    substitutions / indels / Ns plus a tail (as a clip against its neighbour exon looks); every 10th a long one
+    (300-900 bases, beyond the kernels' shared-memory state); z-drop and `score == NEG_INF` both occur."""
+    rng = np.random.default_rng(seed)
+    qs, ts = [], []
+    for k in range(n):
+        ql = int(rng.integers(1, short_max)) if k % 10 else int(rng.integers(300, 900))
+        q = rng.integers(0, 4, size=ql).astype(np.uint8)
+        kind = k % 4
+        if kind == 0:       # unrelated target
+            t = rng.integers(0, 4, size=int(rng.integers(1, ql + 41))).astype(np.uint8)
+        else:               # target = query with substitutions / indels / Ns, plus a tail
+            t = list(q)
+            for _ in range(int(rng.integers(0, max(2, ql // 12)))):
+                pos = int(rng.integers(0, len(t)))
+                r = rng.random()
+                if r < 0.4: t[pos] = int(rng.integers(0, 5))
+                elif r < 0.7: del t[pos]
+                else: t.insert(pos, int(rng.integers(0, 4)))
+                if not t: t = [0]
+            t = np.array(t + list(rng.integers(0, 4, size=int(rng.integers(0, 41)))), dtype=np.uint8)[:ql + 40]
+        qs.append(q); ts.append(t)
+    return qs, ts

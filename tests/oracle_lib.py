@@ -11,6 +11,7 @@ from bramble_b200 import capi
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PORT = os.path.join(ROOT, "oracle", "libbrb_port.so")
 REF_BIN = os.path.join(ROOT, "oracle", "_ref", "bramble_ref")
+KSW_REF = os.path.join(ROOT, "oracle", "_ref", "libksw_ref.so")      # the reference's own ksw2 translation unit (oracle/Makefile: kswref)
 
 
 class PortOut(C.Structure):

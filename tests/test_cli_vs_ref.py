@@ -138,18 +138,50 @@ def test_cli_multi_bundle_overrides_and_flush_chunks():
     assert a == b, explain(a, b, d)
 
 
+def _three_bundle_input():
+    """> 200k alignments: three bundles of the reference's size (>= 100 000 alignments, cut at a read name)."""
+    from bramble_b200 import synth_fast as sf
+    A = sf.make_annotation(9, n_chrom=3, n_genes=400)
+    ix = sf.build_index(A)
+    B = sf.make_short_batch(A, ix, 10, 100000, stranded=None, multi=0.15)
+    assert B.desc.n_aln > 205000
+    d = tempfile.mkdtemp(prefix="brb_cli_")
+    sf.write_gtf(A, d + "/a.gtf")
+
+    class Ann:
+        chroms, chrom_len = A.chroms, A.chrom_len
+    synth.write_bam(d + "/in.bam", Ann, sf.to_records(B))
+    return d
+
+
+def _dealer_run(env):
+    d = _three_bundle_input()
+    old = {k: os.environ.get(k) for k in env}
+    os.environ.update(env)
+    try:
+        a, b = run_both(d, CLI, [], extra=[])
+    finally:
+        for k, v in old.items():
+            if v is None:
+                del os.environ[k]
+            else:
+                os.environ[k] = v
+    assert a == b, explain(a, b, d)
+
+
+@needs_ref
+@pytest.mark.gpu
+def test_cli_dealer_two_slots_on_one_device():
+    """The --gpus 2 code path -- bundle k to dealer slot k mod 2 (one worker thread, one index copy and one context per slot),
+    ordered merge of the output -- with both slots mapped to device 0 (BRB_GPU_MAP), so that it runs on a 1-GPU box:
+    three bundles, byte-identical to the reference."""
+    _dealer_run({"BRB_GPUS": "2", "BRB_GPU_MAP": "0,0", "BRB_THREADS": "4"})
+
+
 @needs_ref
 @pytest.mark.gpu
 def test_cli_two_gpus_ordered_merge():
     from bramble_b200 import capi
     if capi.lib().brb_device_count() < 2:
-        pytest.skip("needs 2 GPUs")
-    wl = common.make_workload("default", 23, n_names=1500, n_genes=40)
-    d = tempfile.mkdtemp(prefix="brb_cli_")
-    args = write_inputs(wl, d, "default")
-    os.environ["BRB_GPUS"] = "2"
-    try:
-        a, b = run_both(d, CLI, args)
-    finally:
-        del os.environ["BRB_GPUS"]
-    assert a == b, explain(a, b, d)
+        pytest.skip("needs 2 GPUs (the same dealer path runs on one device in test_cli_dealer_two_slots_on_one_device)")
+    _dealer_run({"BRB_GPUS": "2", "BRB_THREADS": "4"})

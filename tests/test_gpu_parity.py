@@ -227,24 +227,52 @@ def test_lookup_kernel():
         assert np.array_equal(hits[q, :k], eh[q, :k])
 
 
-def test_merge_kernel_golden_and_random():
-    from test_oracle_golden import UPDATE_CIGAR_CASES, cig
-    wl = common.make_workload("default", 81, n_names=20)
-    rng = np.random.default_rng(5)
-    reals = [cig(r) for r, _, _ in UPDATE_CIGAR_CASES]
-    ideals = [cig(i) for _, i, _ in UPDATE_CIGAR_CASES]
-    ops_r = [0, 1, 2, 3, 4, 5, 7, 8]
-    ops_i = [0, 1, 2, 4, 10, 11, 12, 13]
-    for _ in range(3000):
-        nr, ni = int(rng.integers(0, 9)), int(rng.integers(0, 9))
-        reals.append(np.array([(int(rng.integers(1, 40)) << 4) | int(rng.choice(ops_r)) for _ in range(nr)], np.uint32))
-        ideals.append(np.array([(int(rng.integers(1, 40)) << 4) | int(rng.choice(ops_i)) for _ in range(ni)], np.uint32))
+def _random_cigar_pairs(seed, n, max_real, max_ideal, zeros=False):
+    rng = np.random.default_rng(seed)
+    ops_r = [0, 1, 2, 3, 4, 5, 7, 8, 0, 0, 1, 2]
+    ops_i = [0, 1, 2, 4, 10, 11, 12, 13, 0, 0, 2]
+    reals, ideals = [], []
+    for _ in range(n):
+        nr, ni = int(rng.integers(0, max_real + 1)), int(rng.integers(0, max_ideal + 1))
+        r = [(int(rng.integers(1, 40)) << 4) | int(rng.choice(ops_r)) for _ in range(nr)]
+        i = [(int(rng.integers(0 if zeros else 1, 60)) << 4) | int(rng.choice(ops_i)) for _ in range(ni)]
+        if nr and rng.random() < 0.4:                       # BAM-shaped ends: [H] [S] ... [S]
+            r[0] = (r[0] >> 4 << 4) | (5 if rng.random() < 0.4 else 4)
+            if nr > 1 and rng.random() < 0.5: r[1] = (r[1] >> 4 << 4) | 4
+            if rng.random() < 0.5: r[-1] = (r[-1] >> 4 << 4) | 4
+        if ni and rng.random() < 0.4:                       # clip-rescue segments lead with override ops
+            for k in range(min(ni, 3)):
+                i[k] = (i[k] >> 4 << 4) | int(rng.integers(10, 14))
+        if zeros and nr and rng.random() < 0.1:             # a zero-length real op (not valid BAM): the cooperative code hands the pair to the serial one
+            r[int(rng.integers(0, nr))] &= 0xf
+        reals.append(np.array(r, np.uint32)); ideals.append(np.array(i, np.uint32))
+    return reals, ideals
+
+
+def _merge_on_gpu(eng, reals, ideals, warp):
     real_off = np.concatenate([[0], np.cumsum([len(x) for x in reals])]).astype(np.uint32)
     ideal_off = np.concatenate([[0], np.cumsum([len(x) for x in ideals])]).astype(np.uint32)
-    real = np.concatenate(reals).astype(np.uint32); ideal = np.concatenate(ideals).astype(np.uint32)
+    real = np.concatenate(reals + [np.zeros(1, np.uint32)]).astype(np.uint32); ideal = np.concatenate(ideals + [np.zeros(1, np.uint32)]).astype(np.uint32)
+    eng.set_option(capi.OPT_MERGE_WARP, int(warp))
+    try:
+        return eng.merge_cigars(real_off, real, ideal_off, ideal)
+    finally:
+        eng.set_option(capi.OPT_MERGE_WARP, 0)
+
+
+@pytest.mark.parametrize("warp", [False, True])
+def test_merge_kernel_golden_and_random(warp):
+    """merge_cigars on the device -- one thread per pair (short-read rows) and the warp-cooperative code (long-read rows) -- against
+    the oracle: the reference's 7 update_cigar vectors, 3000 short random pairs, 600 long ones (up to 700 real / 60 ideal ops)."""
+    from test_oracle_golden import UPDATE_CIGAR_CASES, cig, port_merge
+    wl = common.make_workload("default", 81, n_names=20)
+    reals = [cig(r) for r, _, _ in UPDATE_CIGAR_CASES]
+    ideals = [cig(i) for _, i, _ in UPDATE_CIGAR_CASES]
+    for seed, n, mr, mi, z in ((5, 3000, 8, 8, False), (6, 400, 120, 20, True), (7, 200, 700, 60, False)):
+        a, b = _random_cigar_pairs(seed, n, mr, mi, z)
+        reals += a; ideals += b
     with engine.Engine(wl["index"]) as eng:
-        got = eng.merge_cigars(real_off, real, ideal_off, ideal)
-    from test_oracle_golden import port_merge
+        got = _merge_on_gpu(eng, reals, ideals, warp)
     exp = port_merge(reals, ideals)
     for k, (g, e) in enumerate(zip(got, exp)):
         assert np.array_equal(g, e), (k, reals[k], ideals[k], g, e)
@@ -255,25 +283,8 @@ def test_merge_kernel_golden_and_random():
 def test_ksw_kernel_golden_and_random():
     from test_oracle_golden import KSW_Q, KSW_T, codes, port_ksw
     wl = common.make_workload("default", 91, n_names=20)
-    rng = np.random.default_rng(17)
-    qs, ts = [codes(KSW_Q)], [codes(KSW_T)]
-    for k in range(400):
-        ql = int(rng.integers(1, 120)) if k % 10 else int(rng.integers(300, 900))
-        q = rng.integers(0, 4, size=ql).astype(np.uint8)
-        kind = k % 4
-        if kind == 0:       # unrelated target
-            t = rng.integers(0, 4, size=int(rng.integers(1, ql + 41))).astype(np.uint8)
-        else:               # target = query with substitutions / indels / Ns, plus a tail
-            t = list(q)
-            for _ in range(int(rng.integers(0, max(2, ql // 12)))):
-                pos = int(rng.integers(0, len(t)))
-                r = rng.random()
-                if r < 0.4: t[pos] = int(rng.integers(0, 5))
-                elif r < 0.7: del t[pos]
-                else: t.insert(pos, int(rng.integers(0, 4)))
-                if not t: t = [0]
-            t = np.array(t + list(rng.integers(0, 4, size=int(rng.integers(0, 41)))), dtype=np.uint8)[:ql + 40]
-        qs.append(q); ts.append(t)
+    rq, rt = common.ksw_problems(17, 400)
+    qs, ts = [codes(KSW_Q)] + rq, [codes(KSW_T)] + rt
     with engine.Engine(wl["index"]) as eng:
         got = eng.ksw_extend(qs, ts, cigar_cap=2048)
     exp = port_ksw(qs, ts, cap=2048)

@@ -3,7 +3,10 @@ for this path."""
 import ctypes as C
 import re
 
+import os
+
 import numpy as np
+import pytest
 
 from bramble_b200 import capi, pack, synth
 import oracle_lib
@@ -101,7 +104,7 @@ def codes(s):
     return np.array(["ACGT".find(c) if c in "ACGT" else 4 for c in s], dtype=np.uint8)
 
 
-def port_ksw(queries, targets, cap=256):
+def port_ksw(queries, targets, cap=256, fn=None):
     n = len(queries)
     q_off = np.concatenate([[0], np.cumsum([len(q) for q in queries])]).astype(np.uint64)
     t_off = np.concatenate([[0], np.cumsum([len(t) for t in targets])]).astype(np.uint64)
@@ -109,7 +112,7 @@ def port_ksw(queries, targets, cap=256):
     t = np.ascontiguousarray(np.concatenate(list(targets) + [np.zeros(1, np.uint8)]).astype(np.uint8))
     mx = np.zeros(n, np.int32); sc = np.zeros(n, np.int32); mq = np.zeros(n, np.int32); mt = np.zeros(n, np.int32)
     zd = np.zeros(n, np.uint8); nc = np.zeros(n, np.uint32); cg = np.zeros((n, cap), np.uint32)
-    rc = oracle_lib.port().brb_port_ksw_extend(n, capi.ptr(q_off), capi.ptr(q), capi.ptr(t_off), capi.ptr(t), capi.ptr(mx), capi.ptr(sc),
+    rc = (fn or oracle_lib.port().brb_port_ksw_extend)(n, capi.ptr(q_off), capi.ptr(q), capi.ptr(t_off), capi.ptr(t), capi.ptr(mx), capi.ptr(sc),
                                                capi.ptr(mq), capi.ptr(mt), capi.ptr(zd), cap, capi.ptr(nc), capi.ptr(cg.reshape(-1)))
     assert rc == 0
     return dict(max=mx, score=sc, max_q=mq, max_t=mt, zdropped=zd, n_cigar=nc, cigars=[cg[i, :min(int(nc[i]), cap)].copy() for i in range(n)])
@@ -121,3 +124,26 @@ def test_ksw2_smoke_vector():
     assert (int(r["max"][0]), int(r["score"][0]), int(r["max_t"][0]), int(r["max_q"][0]), int(r["zdropped"][0])) == (37, 11, 53, 54, 0)
     ops = "".join(f"{int(w) >> 4}{'MID'[int(w) & 15]}" for w in r["cigars"][0])
     assert ops == "7M1D26M2I20M"
+
+
+@pytest.mark.skipif(not os.path.exists(oracle_lib.KSW_REF), reason="oracle/_ref/libksw_ref.so not built (no reference sources)")
+def test_ksw_port_matches_reference_translation_unit():
+    """The restatement of ksw_extz2_sse + ksw_backtrack (oracle/brb_port.cpp, oracle/shim/ksw2.h) against the reference's OWN
+    translation unit (subprojects/packagefiles/ksw2/ksw2_extz2_sse.cpp, compiled unmodified) on the problems the GPU kernel
+    is tested on plus 2000 more: max, score (incl. NEG_INF), end cell, z-drop flag and CIGAR, problem by problem."""
+    import ctypes as C
+    import common
+    lib = C.CDLL(oracle_lib.KSW_REF)
+    lib.brb_ref_ksw_extend.argtypes = oracle_lib.port().brb_port_ksw_extend.argtypes
+    qs, ts = [codes(KSW_Q)], [codes(KSW_T)]
+    for seed, n, smax in ((17, 400, 120), (18, 1000, 60), (19, 1000, 400)):
+        a, b = common.ksw_problems(seed, n, smax)
+        qs += a; ts += b
+    ref = port_ksw(qs, ts, cap=2048, fn=lib.brb_ref_ksw_extend)
+    got = port_ksw(qs, ts, cap=2048)
+    for k in ("max", "score", "max_q", "max_t", "zdropped", "n_cigar"):
+        assert np.array_equal(got[k], ref[k]), k
+    for i, (g, e) in enumerate(zip(got["cigars"], ref["cigars"])):
+        assert np.array_equal(g, e), i
+    assert (int(ref["max"][0]), int(ref["score"][0]), int(ref["max_t"][0]), int(ref["max_q"][0])) == (37, 11, 53, 54)
+    assert ref["zdropped"].sum() > 100 and (ref["score"] > -0x40000000).sum() > 300 and (ref["score"] == -0x40000000).sum() > 300
