@@ -20,6 +20,7 @@ OPT_NO_FASTPATH = 2
 OPT_ORDERED_ROWS = 3
 OPT_PACKED_ROWS = 4
 OPT_MERGE_WARP = 5
+OPT_FLUSH_TAGS = 6
 
 u8p, i8p = C.POINTER(C.c_uint8), C.POINTER(C.c_int8)
 u32p, i32p = C.POINTER(C.c_uint32), C.POINTER(C.c_int32)
@@ -44,14 +45,15 @@ class BatchIn(C.Structure):
     _fields_ = [("n_aln", C.c_uint32), ("n_groups", C.c_uint32), ("group_off", u32p), ("refid", i32p),
                 ("strand", i8p), ("exon_off", u32p), ("exon_st", u32p), ("exon_en", u32p),
                 ("cigar_off", u32p), ("cigar", u32p), ("mate_idx", i32p), ("group_seq_off", u64p),
-                ("seq_codes", u8p)]
+                ("seq_codes", u8p), ("group_name_off", u64p), ("name_bytes", u8p)]
 
 
 class BatchOut(C.Structure):
     _fields_ = [("n_rec", C.c_uint32), ("n_cigar_words", C.c_uint64), ("group_rec_off", u32p),
                 ("src_aln", u32p), ("tid", u32p), ("pos", u32p), ("tx_strand", i8p), ("flags", u8p),
                 ("sim_score", f64p), ("clip_score", i32p), ("cigar_off", u32p), ("cigar", u32p),
-                ("aln_rec_off", u32p), ("aln_rec_cnt", u32p), ("packed_rows", u32p)]
+                ("aln_rec_off", u32p), ("aln_rec_cnt", u32p), ("packed_rows", u32p),
+                ("hi", i32p), ("nh", i32p), ("mapq", u8p), ("primary", u8p)]
 
 
 class Stats(C.Structure):

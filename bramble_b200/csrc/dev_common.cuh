@@ -92,7 +92,7 @@ struct Ctl {
   uint32_t bad_input;                 // 1: mate link not symmetric, 2: read exons not ascending/disjoint, 3: >= 2^28 CIGAR words in one batch of 32 alignments, 4: packed rows, 5: CSR offsets
   uint32_t ticket;                    // next batch of 32 alignments for k_front (dynamic scheduling)
   uint32_t ticket_a, ticket_b;        // k_back: next batch; CTAs that have left (the last one publishes the totals)
-  uint32_t kq_n[5], kq_t[5];          // clip rescue: problems per size class, next problem of each class
+  uint32_t kq_n[6], kq_t[6];          // clip rescue: problems per size class, next problem of each class
   uint32_t ksw_big_skipped, pad_;     // big problems that did not fit the per-warp scratch (the host grows it and replays)
 };
 constexpr int N_CAPS = 6;

@@ -20,6 +20,7 @@
 #include "k_ksw.cuh"
 #include "k_back.cuh"
 #include "k_merge.cuh"
+#include "k_flush.cuh"
 
 using namespace brb;
 
@@ -88,7 +89,9 @@ struct brb_ctx {
   cudaEvent_t tev[2]{};
   // resident batch
   DevBatch b{};
-  Buf in_group_off, in_refid, in_strand, in_exon_off, in_exon_st, in_exon_en, in_cigar_off, in_cigar, in_mate, in_seq_off, in_seq;
+  Buf in_group_off, in_refid, in_strand, in_exon_off, in_exon_st, in_exon_en, in_cigar_off, in_cigar, in_mate, in_seq_off, in_seq, in_name_off, in_names;
+  Buf f_hi, f_nh, f_mapq, f_prim;   // BRB_OPT_FLUSH_TAGS results per row
+  bool have_names = false, opt_flush_tags = false, result_tags = false;
   uint64_t in_bytes = 0, n_mates = 0, seq_bytes = 0, rescue_bytes = 0;
   bool have_batch = false, have_result = false, have_scores = false, opt_generic_front = false, opt_no_fastpath = false, opt_ordered = false, result_ordered = false, opt_packed = false, result_packed = false, opt_merge_warp = false;
   // control block + pools (capacities persist across calls and only grow)
@@ -107,7 +110,7 @@ struct brb_ctx {
   brb_stats stats{};
   std::vector<Buf*> all() {
     return {&in_group_off, &in_refid, &in_strand, &in_exon_off, &in_exon_st, &in_exon_en, &in_cigar_off, &in_cigar, &in_mate, &in_seq_off,
-            &in_seq, &ctl, &q_any, &a_cand, &scan_tmp, &c_rec, &c_task, &c_first, &c_last, &c_nseg, &c_nguide, &c_cap, &ipool,
+            &in_seq, &in_name_off, &in_names, &f_hi, &f_nh, &f_mapq, &f_prim, &ctl, &q_any, &a_cand, &scan_tmp, &c_rec, &c_task, &c_first, &c_last, &c_nseg, &c_nguide, &c_cap, &ipool,
             &r_left, &r_right, &rpool, &m_rec, &m_sim, &m_clip, &c_stage, &t_agg, &t_claim, &t_off, &p_row, &p_pool, &p_sim, &p_clip, &a_roff, &a_rcnt, &g_roff,
             &o_src, &o_tid, &o_pos, &o_strand, &o_flags, &o_sim, &o_clip, &o_coff, &tpool, &opool};
   }
@@ -341,6 +344,11 @@ static int batch_upload_async(brb_ctx* c, const brb_batch_in* in) {
     if (!rc) rc = up(c->in_seq, in->seq_codes, (size_t)in->group_seq_off[ng]);
     c->seq_bytes = in->group_seq_off[ng];
   }
+  c->have_names = n && in->group_name_off && in->name_bytes;
+  if (!rc && c->have_names) {
+    rc = up(c->in_name_off, in->group_name_off, (size_t)(ng + 1) * 8);
+    if (!rc) rc = up(c->in_names, in->name_bytes, (size_t)in->group_name_off[ng]);
+  }
   if (rc) return rc;
   DevBatch& b = c->b;
   b.n_aln = n; b.n_groups = n ? ng : 0; b.n_exon = n_exon; b.n_cigar = n_cigar;
@@ -388,7 +396,7 @@ int ensure_pools(brb_ctx* c, bool rescue) {
   if (c->opt_packed) ENS(c->p_row, R * 16);
   ENS(c->m_rec, C * 16);
   if (c->have_scores) { ENS(c->m_sim, C * 8); ENS(c->m_clip, C * 4); ENS(c->o_sim, R * 8); ENS(c->o_clip, R * 4); if (c->opt_ordered) { ENS(c->p_sim, R * 8); ENS(c->p_clip, R * 4); } }
-  if (rescue) { ENS(c->c_rec, C * 4); ENS(c->c_task, C * 4); ENS(c->c_first, C * 4); ENS(c->c_last, C * 4); ENS(c->c_nseg, C * 4); ENS(c->c_nguide, C * 4); ENS(c->c_cap, C * 4); }
+  if (rescue || c->b.back_shift == 3) { ENS(c->c_rec, C * 4); ENS(c->c_task, C * 4); ENS(c->c_first, C * 4); ENS(c->c_last, C * 4); ENS(c->c_nseg, C * 4); ENS(c->c_nguide, C * 4); ENS(c->c_cap, C * 4); }
   ENS(c->ipool, (size_t)c->cap_ideal * 4);
   ENS(c->o_src, R * 4); ENS(c->o_tid, R * 4); ENS(c->o_pos, R * 4); ENS(c->o_strand, R); ENS(c->o_flags, R);
   ENS(c->o_coff, (R + 1) * 4);
@@ -432,11 +440,14 @@ int project_resident(brb_ctx* c, const brb_params& p) {
     c->resident_cache.emplace_back(kern, n_sm * nb); return n_sm * nb;
   };
   // short-read presets: only exon 0 is looked up, candidates verify the later exons themselves (k_front_short)
+  // long reads: lookup + candidate list (k_front<false>), then one thread per candidate for the chain walk (k_chain) and the ideal
+  // CIGAR (k_build) -- a read of a 200-isoform, 300-exon gene would otherwise keep one warp busy for the whole kernel
+  const bool split = rescue || p.long_reads;
   const bool short_front = !p.long_reads && !p.ignore_small_exons && !rescue && !c->opt_generic_front;
   const bool fast_front = short_front && !p.filter_by_similarity && !c->opt_no_fastpath;
   const void* front_fn = fast_front ? (const void*)k_front_fast
                        : short_front ? (p.filter_by_similarity ? (const void*)k_front_short<true> : (const void*)k_front_short<false>)
-                                     : (rescue ? (const void*)k_front<false> : (const void*)k_front<true>);
+                                     : (split ? (const void*)k_front<false> : (const void*)k_front<true>);
   const int ncta_front = resident(front_fn);
   const bool ordered = c->opt_ordered, packed = c->opt_packed && !ordered;      // BRB_OPT_ORDERED_ROWS wins when both are set
   const bool lng = p.long_reads;
@@ -477,7 +488,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
       else k_front_short<false><<<ncta_front, 256, 0, st>>>(ix, b, p, ctl, c->a_cand.as<uint4>(), c->ipool.as<uint32_t>(), M);
       L++;
       CU(cudaEventRecord(c->ev[1], st)); one_front = true;
-    } else if (!rescue) {
+    } else if (!split) {
       k_front<true><<<ncta_front, 256, 0, st>>>(ix, b, p, ctl, c->q_any.as<uint8_t>(), c->a_cand.as<uint4>(), nullptr, nullptr,
                                           c->ipool.as<uint32_t>(), M); L++;
       CU(cudaEventRecord(c->ev[1], st)); one_front = true;
@@ -489,10 +500,10 @@ int project_resident(brb_ctx* c, const brb_params& p) {
       F.nguide = c->c_nguide.as<uint32_t>(); F.cap = c->c_cap.as<uint32_t>();
       k_chain<<<ncta, 256, 0, st>>>(ix, b, p, ctl, c->q_any.as<uint8_t>(), c->c_rec.as<uint32_t>(), c->c_task.as<uint32_t>(), F); L++;
       CU(cudaEventRecord(c->ev[2], st));
-      { int r = launch_rescue(c, p, &L); if (r) return r; }      // plan -> size-class DP kernels -> clip segments: no host round trip
+      if (rescue) { int r = launch_rescue(c, p, &L); if (r) return r; }      // plan -> size-class DP kernels -> clip segments: no host round trip
       CU(cudaEventRecord(c->ev[3], st));
-      k_build<<<ncta, 256, 0, st>>>(ix, b, p, ctl, c->q_any.as<uint8_t>(), c->c_task.as<uint32_t>(), F, c->r_left.as<RescueSeg>(),
-                                    c->r_right.as<RescueSeg>(), c->rpool.as<uint32_t>(), c->ipool.as<uint32_t>(), M); L++;
+      k_build<<<ncta, 256, 0, st>>>(ix, b, p, ctl, c->q_any.as<uint8_t>(), c->c_task.as<uint32_t>(), F, rescue ? c->r_left.as<RescueSeg>() : nullptr,
+                                    rescue ? c->r_right.as<RescueSeg>() : nullptr, c->rpool.as<uint32_t>(), c->ipool.as<uint32_t>(), M); L++;
       CU(cudaEventRecord(c->ev[4], st));
     }
     // ---- phase 5: pairing, CIGAR merge, rows (one kernel; row and CIGAR room claimed per batch in completion order)
@@ -500,7 +511,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
     Rows o; o.src = c->o_src.as<uint32_t>(); o.tid = c->o_tid.as<uint32_t>(); o.pos = c->o_pos.as<uint32_t>(); o.strand = c->o_strand.as<int8_t>();
     o.flags = c->o_flags.as<uint8_t>(); o.sim = c->o_sim.as<double>(); o.clip = c->o_clip.as<int32_t>(); o.coff = c->o_coff.as<uint32_t>();
     o.pool = c->opool.as<uint32_t>(); o.a_roff = c->a_roff.as<uint32_t>(); o.a_rcnt = c->a_rcnt.as<uint32_t>();
-    if (rescue) { k_count_valid<<<grid_for(n, 256), 256, 0, st>>>(b, ctl, c->a_cand.as<uint4>(), c->m_rec.as<uint4>()); L++; }
+    if (split) { k_count_valid<<<grid_for(n, 256), 256, 0, st>>>(b, ctl, c->a_cand.as<uint4>(), c->m_rec.as<uint4>()); L++; }
     const uint32_t nbat = (uint32_t)((n + (1u << b.back_shift) - 1) >> b.back_shift);
     BatchTotals tl; tl.agg = c->t_agg.as<unsigned long long>(); tl.claim = c->t_claim.as<unsigned long long>();
     ProvRows pr; pr.row = c->p_row.as<uint4>(); pr.pool = c->p_pool.as<uint32_t>();
@@ -538,6 +549,22 @@ int project_resident(brb_ctx* c, const brb_params& p) {
     else if (hres->n_tmpw > c->cap_tmpw) { c->cap_tmpw = grown(hres->n_tmpw); again = true; }
     else if (hres->n_outw > c->cap_outw) { c->cap_outw = grown(hres->n_outw); again = true; }
     if (!again) break;
+  }
+  c->result_tags = false;
+  if (c->opt_flush_tags && !hres->bad_input) {            // per-name HI / NH / MAPQ / primary on the finished rows
+    if (packed) return fail(BRB_E_UNSUPPORTED, "BRB_OPT_FLUSH_TAGS is not available together with BRB_OPT_PACKED_ROWS");
+    if (!c->have_names) return fail(BRB_E_ARG, "BRB_OPT_FLUSH_TAGS needs brb_batch_in::group_name_off / name_bytes");
+    const size_t R = std::max<uint32_t>(hres->n_rows, 1);
+    ENS(c->f_hi, R * 4); ENS(c->f_nh, R * 4); ENS(c->f_mapq, R); ENS(c->f_prim, R);
+    FlushIn fi; fi.a_roff = c->a_roff.as<uint32_t>(); fi.a_rcnt = c->a_rcnt.as<uint32_t>(); fi.flags = c->o_flags.as<uint8_t>();
+    fi.sim = c->have_scores ? c->o_sim.as<double>() : nullptr; fi.name_off = c->in_name_off.as<uint64_t>(); fi.names = c->in_names.as<uint8_t>();
+    fi.cap_rows = c->cap_rows;
+    FlushOut fo; fo.hi = c->f_hi.as<int32_t>(); fo.nh = c->f_nh.as<int32_t>(); fo.mapq = c->f_mapq.as<uint8_t>(); fo.primary = c->f_prim.as<uint8_t>();
+    CU(cudaEventRecord(c->ev[7], st));
+    k_flush_tags<<<grid_for(b.n_groups, 128), 128, 0, st>>>(b, fi, fo, p.long_reads != 0); L++;
+    CU(cudaStreamSynchronize(st)); n_syncs++;
+    CU(cudaGetLastError());
+    c->result_tags = true;
   }
   if (hres->bad_input == 3) return fail(BRB_E_UNSUPPORTED, "a batch of 32 alignments emits 2^28 or more CIGAR words");
   if (hres->bad_input == 4) return fail(BRB_E_UNSUPPORTED, "BRB_OPT_PACKED_ROWS: the bundle pools 2^27 or more CIGAR words; project it without the option");
@@ -594,6 +621,11 @@ int brb_batch_download(brb_ctx* c, brb_batch_out* out) {
   const size_t o_strand = off; off += pk ? 0 : al(R);
   const size_t o_flags = off; off += pk ? 0 : al(R);
   const size_t o_cig = off; off += al(W * 4);
+  const bool tg = c->result_tags && R;
+  const size_t o_hi = off; off += tg ? al(R * 4) : 0;
+  const size_t o_nh = off; off += tg ? al(R * 4) : 0;
+  const size_t o_mq = off; off += tg ? al(R) : 0;
+  const size_t o_pr = off; off += tg ? al(R) : 0;
   ENS(c->h_out, off + 16);
   uint8_t* h = c->h_out.as<uint8_t>();
   uint64_t bytes = 0;
@@ -615,6 +647,10 @@ int brb_batch_download(brb_ctx* c, brb_batch_out* out) {
   if (!rc && !pk) rc = dn(o_strand, c->o_strand, R);
   if (!rc && !pk) rc = dn(o_flags, c->o_flags, R);
   if (!rc) rc = dn(o_cig, c->opool, W * 4);
+  if (!rc && tg) rc = dn(o_hi, c->f_hi, R * 4);
+  if (!rc && tg) rc = dn(o_nh, c->f_nh, R * 4);
+  if (!rc && tg) rc = dn(o_mq, c->f_mapq, R);
+  if (!rc && tg) rc = dn(o_pr, c->f_prim, R);
   if (rc) return rc;
   CU(cudaStreamSynchronize(c->st));
   out->n_rec = (uint32_t)R; out->n_cigar_words = W;
@@ -625,6 +661,8 @@ int brb_batch_download(brb_ctx* c, brb_batch_out* out) {
   out->pos = pk ? nullptr : (const uint32_t*)(h + o_pos); out->tx_strand = pk ? nullptr : (const int8_t*)(h + o_strand); out->flags = pk ? nullptr : h + o_flags;
   out->sim_score = sc ? (const double*)(h + o_sim) : nullptr; out->clip_score = sc ? (const int32_t*)(h + o_clip) : nullptr;
   out->cigar_off = pk ? nullptr : (const uint32_t*)(h + o_coff); out->cigar = (const uint32_t*)(h + o_cig);
+  out->hi = tg ? (const int32_t*)(h + o_hi) : nullptr; out->nh = tg ? (const int32_t*)(h + o_nh) : nullptr;
+  out->mapq = tg ? h + o_mq : nullptr; out->primary = tg ? h + o_pr : nullptr;
   c->stats.d2h_bytes = bytes;
   return BRB_OK;
 }
@@ -642,6 +680,7 @@ int brb_ctx_set_option(brb_ctx* c, int option, int value) {
   if (option == BRB_OPT_ORDERED_ROWS) { c->opt_ordered = value != 0; return BRB_OK; }
   if (option == BRB_OPT_PACKED_ROWS) { c->opt_packed = value != 0; return BRB_OK; }
   if (option == BRB_OPT_MERGE_WARP) { c->opt_merge_warp = value != 0; return BRB_OK; }
+  if (option == BRB_OPT_FLUSH_TAGS) { c->opt_flush_tags = value != 0; return BRB_OK; }
   return fail(BRB_E_ARG, "unknown option %d", option);
 }
 

@@ -157,6 +157,8 @@ struct Bundle {
   std::vector<uint8_t> raw; std::vector<uint64_t> rec_off; std::vector<uint32_t> rec_len;       // record bodies
   std::vector<uint32_t> group_off, exon_off, exon_st, exon_en, cigar_off, cigar; std::vector<int32_t> refid, mate; std::vector<int8_t> strand;
   std::vector<uint64_t> seq_off; std::vector<uint8_t> seq;
+  std::vector<uint64_t> name_off; std::vector<uint8_t> names;                // read name per group (the engine's on-device flush bookkeeping hashes them)
+  std::vector<int32_t> hi, nh; std::vector<uint8_t> mapq, prim; bool have_tags = false;   // BRB_OPT_FLUSH_TAGS results, when the engine provides them
   // result (copied out of the engine's staging)
   std::vector<uint32_t> a_roff, a_rcnt, src, tid, pos, coff, cig; std::vector<int8_t> tstrand; std::vector<uint8_t> flags; std::vector<double> sim; std::vector<int32_t> clip;
   // assembled output records of the bundle (uncompressed BAM bytes) and its share of the final report
@@ -172,6 +174,7 @@ void fill_batch(const Bundle& b, bool use_fasta, brb_batch_in& in) {
   in.strand = b.strand.data(); in.exon_off = b.exon_off.data(); in.exon_st = b.exon_st.data(); in.exon_en = b.exon_en.data();
   in.cigar_off = b.cigar_off.data(); in.cigar = b.cigar.data(); in.mate_idx = b.mate.data();
   in.group_seq_off = use_fasta ? b.seq_off.data() : nullptr; in.seq_codes = use_fasta ? (b.seq.empty() ? (const uint8_t*)"" : b.seq.data()) : nullptr;
+  in.group_name_off = b.name_off.data(); in.name_bytes = b.names.empty() ? (const uint8_t*)"" : b.names.data();
 }
 
 void store_result(Bundle& b, const brb_batch_out& o) {
@@ -181,6 +184,8 @@ void store_result(Bundle& b, const brb_batch_out& o) {
   if (o.sim_score) b.sim.assign(o.sim_score, o.sim_score + R); else b.sim.assign(R, 0.0);      // NULL: every score is 0 (header)
   if (o.clip_score) b.clip.assign(o.clip_score, o.clip_score + R); else b.clip.assign(R, 0);
   b.coff.assign(o.cigar_off, o.cigar_off + R + 1); b.cig.assign(o.cigar, o.cigar + o.n_cigar_words);
+  b.have_tags = o.hi && o.nh && o.mapq && o.primary;
+  if (b.have_tags) { b.hi.assign(o.hi, o.hi + R); b.nh.assign(o.nh, o.nh + R); b.mapq.assign(o.mapq, o.mapq + R); b.prim.assign(o.primary, o.primary + R); }
 }
 
 uint32_t get_mapq(uint32_t nh, bool lng) {                 // src/core.cpp:46-58
@@ -193,12 +198,22 @@ int32_t get_rand(uint32_t x, uint64_t seed_key) {          // src/core.cpp:214-2
 
 // flush() + write_to_bam of the reference for one bundle's rows.
 void assemble_bundle(const Bundle& b, bool lng, Stats& st, std::vector<uint8_t>& out) {
-  struct Unit { uint32_t row; bool paired; int32_t hi_r = 0, hi_m = 0; bool primary = false; uint32_t nh = 0, mapq = 0; };
+  struct Unit { uint32_t row; bool paired; uint32_t group; int32_t hi_r = 0, hi_m = 0; bool primary = false; uint32_t nh = 0, mapq = 0; };
   std::unordered_map<std::string, std::vector<Unit>> pairs_by_name;
   uint32_t n_pairs = 0; std::vector<uint8_t> aux;
   auto flush = [&]() {
     std::vector<Unit*> filtered;
     for (auto& [read_name, pairs] : pairs_by_name) {
+      // HI / NH / MAPQ / primary: from the device when the engine computed them (brb_batch_out::hi ...) -- unless the name came in as
+      // more than one group inside this chunk (input not name-collated) or the device left the tie to us (primary == 2)
+      bool from_device = b.have_tags;
+      for (size_t i = 0; from_device && i < pairs.size(); i++) if (pairs[i].group != pairs[0].group || b.prim[pairs[i].row] == 2) from_device = false;
+      if (from_device) {
+        const int total = b.nh[pairs[0].row];
+        for (auto& u : pairs) { u.hi_r = b.hi[u.row]; if (u.paired) u.hi_m = b.hi[u.row + 1]; u.primary = b.prim[u.row] == 1; u.nh = (uint32_t)total; u.mapq = b.mapq[u.row]; filtered.push_back(&u); }
+        st.total_complete += total; if (total == 1) st.total_unique++;
+        continue;
+      }
       double best_score = -std::numeric_limits<double>::infinity(); int count_at_best = 0; size_t best = pairs.size(); int32_t hit_index = 1; int total = 0;
       auto score_of = [&](const Unit& u) { double s = b.sim[u.row]; if (u.paired) s = std::max(s, b.sim[u.row + 1]); return s; };
       for (size_t i = 0; i < pairs.size(); i++) {
@@ -239,7 +254,7 @@ void assemble_bundle(const Bundle& b, bool lng, Stats& st, std::vector<uint8_t>&
       for (uint32_t r = lo; r < hi;) {
         const bool paired = b.flags[r] & BRB_REC_PAIRED;
         const RecView v = b.view(b.src[r]);
-        pairs_by_name[std::string(v.name())].push_back(Unit{r, paired});
+        pairs_by_name[std::string(v.name())].push_back(Unit{r, paired, g});
         n_pairs++; r += paired ? 2 : 1; any = true;
       }
     }
@@ -363,6 +378,8 @@ int main(int argc, char** argv) {
           b.seq_off.push_back(b.seq.size());
         }
       }
+      b.name_off.assign(1, 0);
+      for (size_t g = 0; g + 1 < b.group_off.size(); g++) { const RecView v = b.view(b.group_off[g]); const char* nm = v.name(); b.names.insert(b.names.end(), nm, nm + strlen(nm)); b.name_off.push_back(b.names.size()); }
       b.index = n_bundles++;
       const auto tw = clk::now();
       { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return inflight.size() < (size_t)(2 * n_gpu + 2 + n_asm) || !err.empty(); }); todo[b.index % n_gpu].push_back(bundle); inflight.push_back(bundle); }

@@ -324,6 +324,56 @@ __global__ void __launch_bounds__(256, LONG ? 3 : VAR_BACK_CTAS) k_back(DevBatch
       const uint32_t o_off = __shfl_sync(0xffffffffu, off, L), o_n = __shfl_sync(0xffffffffu, n, L), o_ex = __shfl_sync(0xffffffffu, excl, L);
       const uint32_t o_row0 = __shfl_sync(0xffffffffu, row0, L), o_word0 = __shfl_sync(0xffffffffu, word0, L);
       const int32_t o_mate = __shfl_sync(0xffffffffu, mate, L);
+      if (!LONG) {                                            // short reads: every lane writes its own row(s) and CIGAR words
+        if (!actv) continue;
+        const uint32_t c = o_off + (item - o_ex);
+        const uint32_t s0 = staged ? o_ex : o_off, sidx = staged ? item : c;
+        const uint4 sg = stage[sidx];
+        const uint32_t tid = sg.x;
+        if (tid == NONE || sg.w == NOFIT) continue;
+        // rank among the emitted matches of the read: ascending tid, slot order among equals; CIGAR words before me
+        uint32_t rank = 0, wpre = 0;
+#pragma unroll kUnroll
+        for (uint32_t k = 0; k < o_n; k++) {
+          const uint2 e = *reinterpret_cast<const uint2*>(&stage[s0 + k]);
+          if (e.x < tid || (e.x == tid && s0 + k < sidx)) { rank++; wpre += e.y; }        // (NONE is never below a tid)
+        }
+        const uint32_t part = sg.z;
+        const bool paired = part != SELF, inl = sg.w == INLINE;
+        const uint4 mr = __ldg(&v.m_rec[c]);
+        const uint32_t row = o_row0 + (paired ? 2 * rank : rank), w0 = o_word0 + wpre;
+        const uint32_t clr = inl ? 1u : tpool[sg.w];
+        uint4 m = mr; uint32_t cc = c, aln = wb * BA + L, fl = BRB_REC_FIRST, wpos = w0, len = clr;
+        const uint32_t* src = tpool + sg.w + 1;
+        uint4 pm = make_uint4(0, 0, 0, NONE);
+        if (paired) { pm = __ldg(&v.m_rec[part]); fl |= BRB_REC_PAIRED | (pm.w == tid ? BRB_REC_SAMETX : 0); }
+        for (uint32_t e = 0, ne = paired ? 2 : 1; e < ne; e++) {
+          if (e) {                                            // the mate row follows the read row
+            m = pm; cc = part; aln = (uint32_t)o_mate; fl &= ~BRB_REC_FIRST; wpos = w0 + clr;
+            src = tpool + sg.w + 1 + (s_nrc[L] + (mr.y >> 1) + 2); len = inl ? 1u : sg.y - clr - (PACKED ? 2u : 0u);
+            if (PACKED) wpos = w0 + 1 + clr;
+          }
+          const uint32_t minus = m.y & 1u, r = row + e;
+          uint32_t* pool = ORDERED ? pv_.pool : o.pool;
+          if (ORDERED) {
+            pv_.row[r] = make_uint4(aln, m.w, m.x, (wpos - pword0) | (minus << 28) | (fl << 29));
+            if (v.m_sim) { pv_.sim[r] = v.m_sim[cc]; pv_.clip[r] = v.m_clip[cc]; }
+          } else if (PACKED) {
+            st_stream(&pv_.row[r], make_uint4(aln, m.w, m.x, (inl ? (m.z | BRB_ROW_INLINE) : wpos) | (minus << 28) | (fl << 29)));
+            if (v.m_sim) { o.sim[r] = v.m_sim[cc]; o.clip[r] = v.m_clip[cc]; }
+            if (!inl) pool[wpos++] = len;                     // length word, then the CIGAR
+          } else {
+            st_stream(&o.src[r], aln); st_stream(&o.tid[r], m.w); st_stream(&o.pos[r], m.x); st_stream(&o.strand[r], (int8_t)(minus ? '-' : '+'));
+            st_stream(&o.flags[r], (uint8_t)fl); st_stream(&o.coff[r], wpos);
+            if (v.m_sim) { o.sim[r] = v.m_sim[cc]; o.clip[r] = v.m_clip[cc]; }
+          }
+          if (inl) { if (!PACKED) st_stream(&pool[wpos], m.z); }
+          else if (minus) for (uint32_t i = 0; i < len; i++) pool[wpos + i] = src[len - 1 - i];      // reverse_complement_bam, src/bam.cpp:636-702
+          else for (uint32_t i = 0; i < len; i++) pool[wpos + i] = src[i];
+        }
+        continue;
+      }
+      // long reads: the same, with the CIGAR copies of long rows done by the whole warp
       const uint32_t c = o_off + (item - o_ex);
       const uint32_t s0 = staged ? o_ex : o_off, sidx = staged ? item : c;
       uint4 sg = make_uint4(NONE, 0, 0, NOFIT);
@@ -385,7 +435,7 @@ __global__ void __launch_bounds__(256, LONG ? 3 : VAR_BACK_CTAS) k_back(DevBatch
           if (bm) for (uint32_t i = lane; i < bl; i += 32) pool[bd + i] = bs[bl - 1 - i]; else for (uint32_t i = lane; i < bl; i += 32) pool[bd + i] = bs[i];
         }
       }
-    }
+        }
     __syncwarp();                                           // the staging area is reused by the next batch
   }
   if (!ORDERED) {                                           // last kernel of the sequence: the last CTA to leave publishes the result

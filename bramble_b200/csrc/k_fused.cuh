@@ -33,7 +33,10 @@ __global__ void __launch_bounds__(256) k_front(DevIndex ix, DevBatch b, brb_para
                                                uint32_t* __restrict__ ipool, Matches M) {
   if (ctl->bad_input) return;                             // k_validate_batch rejected the CSR offsets: nothing may follow them
   const unsigned lane = threadIdx.x & 31;
-  const uint32_t n_batches = (b.n_aln + 31) >> 5;
+  // alignments per batch: 32, or 8 for long reads (b.back_shift == 3) -- a long read is tens of exon queries and up to hundreds of
+  // candidate walks, and with 32 of them per ticket a bundle of 10^5 reads has fewer batches than the GPU has warps
+  const uint32_t BS = b.back_shift, BA = 1u << BS;
+  const uint32_t n_batches = (b.n_aln + BA - 1) >> BS;
   const uint32_t cap_cand = ctl->cap_cand, cap_ideal = ctl->cap_ideal;       // constant during the launch
   WarpPool wp; wp.cur = 0; wp.end = 0;
   unsigned long long my_hits = 0;
@@ -43,8 +46,8 @@ __global__ void __launch_bounds__(256) k_front(DevIndex ix, DevBatch b, brb_para
     if (lane == 0) wb = atomicAdd(&ctl->ticket, 1u);
     wb = __shfl_sync(0xffffffffu, wb, 0);
     if (wb >= n_batches) break;
-    const uint32_t a = wb * 32 + lane;
-    const bool valid = a < b.n_aln;
+    const uint32_t a = wb * BA + lane;
+    const bool valid = lane < BA && a < b.n_aln;
     uint32_t e0 = 0, n_ex = 0; int32_t refid = -1; bool act[2] = {false, false};
     if (valid) {
       e0 = __ldg(&b.exon_off[a]); n_ex = __ldg(&b.exon_off[a + 1]) - e0; refid = __ldg(&b.refid[a]);
@@ -128,7 +131,7 @@ __global__ void __launch_bounds__(256) k_front(DevIndex ix, DevBatch b, brb_para
         const uint32_t o_mine = __shfl_sync(0xffffffffu, mine, L), o_wr = __shfl_sync(0xffffffffu, written, L);
         const uint32_t o_dst = __shfl_sync(0xffffffffu, dst, L);
         const uint32_t slot = o_dst + o_wr + __popc(B & o_mine & ((1u << lane) - 1u));
-        const uint32_t task = 2 * (wb * 32 + L) + s;
+        const uint32_t task = 2 * (wb * BA + L) + s;
         written += __popc(B & mine);
         if (!FUSED) {
           if (sv && slots_fit) { c_rec[slot] = i; c_task[slot] = task; }

@@ -27,9 +27,10 @@ struct KswOut { int32_t max, score, max_q, max_t; uint32_t zdropped, n_cig; };
 
 constexpr int KSW_SH_T = 768;          // k_ksw_big: cells of difference state kept in shared memory per warp
 constexpr int KSW_WARPS = 4;           // warps per CTA
-constexpr int KSW_CLASSES = 5;         // query length <= 32, 64, 128, 512, beyond
+constexpr int KSW_CLASSES = 6;         // query length <= 32, 64, 128, 256, 512, beyond
+constexpr int KSW_BIG = KSW_CLASSES - 1;
 constexpr int KSW_TAIL = 40;           // the target is at most the query length + 40 (src/evaluate.cpp:368-395, 600-656)
-__host__ __device__ __forceinline__ int ksw_class_of(uint32_t qlen) { return qlen <= 32 ? 0 : qlen <= 64 ? 1 : qlen <= 128 ? 2 : qlen <= 512 ? 3 : 4; }
+__host__ __device__ __forceinline__ int ksw_class_of(uint32_t qlen) { return qlen <= 32 ? 0 : qlen <= 64 ? 1 : qlen <= 128 ? 2 : qlen <= 256 ? 3 : qlen <= 512 ? 4 : 5; }
 
 // DP + traceback for one problem by one warp (big problems).  `tb` receives the run-length ops in TRACEBACK order
 // (last alignment op first; op 0=M 1=I 2=D), i.e. ksw2's cigar before its final reversal.
@@ -244,7 +245,7 @@ __global__ void __launch_bounds__(256) k_rescue_plan(DevIndex ix, DevBatch b, br
       q0 = __shfl_sync(0xffffffffu, q0, __ffs(B) - 1);
       if (cls == k) K.queue[(size_t)k * K.queue_stride + q0 + __popc(B & lt_mask)] = slot;
     }
-    if (cls == 4) {                                        // scratch sizing of k_ksw_big: largest direction matrix, longest query and target
+    if (cls == KSW_BIG) {                                  // scratch sizing of k_ksw_big: largest direction matrix, longest query and target
       atomicMax(&ctl->ksw_max_mat, (unsigned long long)(qlen + tlen - 1) * (qlen < tlen ? qlen : tlen));
       atomicMax(&ctl->ksw_max_tlen, (unsigned long long)tlen); atomicMax(&ctl->ksw_max_qlen, (unsigned long long)qlen);
     }
@@ -427,13 +428,13 @@ __global__ void __launch_bounds__(32 * KSW_WARPS) k_ksw_big(DevIndex ix, DevBatc
   if (!n_direct && ctl_overflow(ctl)) return;
   const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t w = blockIdx.x * KSW_WARPS + wib;
-  const uint32_t n_prob = n_direct ? n_direct : ctl->kq_n[4];
-  const uint32_t* queue = K.queue + (size_t)4 * K.queue_stride;
+  const uint32_t n_prob = n_direct ? n_direct : ctl->kq_n[KSW_BIG];
+  const uint32_t* queue = K.queue + (size_t)KSW_BIG * K.queue_stride;
   uint8_t* pmat = B.pmat + (size_t)w * B.pmat_stride;
   uint8_t* qbuf = B.seq + (size_t)w * B.seq_stride * 2; uint8_t* tbuf = qbuf + B.seq_stride;
   for (;;) {
     uint32_t pi = 0;
-    if (lane == 0) pi = atomicAdd(&ctl->kq_t[4], 1u);
+    if (lane == 0) pi = atomicAdd(&ctl->kq_t[KSW_BIG], 1u);
     pi = __shfl_sync(0xffffffffu, pi, 0);
     if (pi >= n_prob) break;
     const uint32_t slot = queue[pi];

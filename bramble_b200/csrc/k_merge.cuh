@@ -153,16 +153,60 @@ __device__ __noinline__ uint32_t merge_cigars(const uint32_t* __restrict__ real,
 constexpr uint32_t MERGE_SERIAL = 0xffffffffu;
 constexpr uint32_t MERGE_COOP_MIN = 48;          // real + ideal ops from which a row is merged by the whole warp
 
+// merge_ops as a table for the cooperative code (the if-chain, inlined at several places, was a tenth of its instructions
+// and a good part of its code size): row r = 16 nibbles, nibble i = merge_ops(r, i), 15 = nothing is emitted.  The swallow
+// rule of the main loop (real D under an ideal S / I) is folded in.  Built at compile time from the chain itself.
+constexpr uint32_t merge_ops_c(uint32_t r, uint32_t i) {
+  const bool rMS = (r == CM || r == CS);
+  if (rMS && i == OV_S) return CS;
+  if (rMS && i == OV_M) return CM;
+  if (rMS && i == OV_I) return CI;
+  if (rMS && i == OV_D) return CD;
+  if (r == CD && (i == CS || i == OV_S)) return 15;
+  if (r == CD && i == OV_M) return CD;
+  if (r == CI && i == OV_S) return CS;
+  if (r == CI && i == OV_M) return CI;
+  if (i == OV_S) return CS;
+  if (i == OV_M) return CM;
+  if (i == OV_I) return CI;
+  if (i == OV_D) return CD;
+  if (r == CP) return i;
+  if (r == CH) return CH;
+  if (r == CI && i == CS) return CS;
+  if (i == CS || i == CD || i == CI) return i;
+  if (r == CS || r == CD || r == CI) return r;
+  if (i == CM || i == CEQ) return CM;
+  if (i == CX) return CX;
+  if (r == CM || r == CEQ) return CM;
+  if (r == CX) return CX;
+  return i;
+}
+constexpr unsigned long long merge_ops_row(uint32_t r) {
+  unsigned long long w = 0;
+  for (uint32_t i = 0; i < 16; i++) {
+    uint32_t v = merge_ops_c(r, i);
+    if (r == CD && (i == CS || i == OV_S || i == CI || i == OV_I)) v = 15;      // main loop: both sides advance, nothing is emitted
+    w |= (unsigned long long)(v & 15u) << (4 * i);
+  }
+  return w;
+}
+__constant__ unsigned long long c_merge_rows[16] = {
+  merge_ops_row(0), merge_ops_row(1), merge_ops_row(2), merge_ops_row(3), merge_ops_row(4), merge_ops_row(5), merge_ops_row(6), merge_ops_row(7),
+  merge_ops_row(8), merge_ops_row(9), merge_ops_row(10), merge_ops_row(11), merge_ops_row(12), merge_ops_row(13), merge_ops_row(14), merge_ops_row(15)};
+// (an ideal op that passes through unchanged can only be 0..13: the value 15 is free to mean "nothing")
+__device__ __forceinline__ uint32_t merge_ops_tab(uint32_t r, uint32_t i) { return (uint32_t)(c_merge_rows[r & 15u] >> (4 * (i & 15u))) & 15u; }
+
 // scratch words merge_cigars_warp needs besides `out` (capacity n_real + n_ideal + 2)
-__host__ __device__ __forceinline__ uint32_t merge_warp_scratch(uint32_t n_real, uint32_t n_ideal) { return n_real + 3 * n_ideal + 16; }
+__host__ __device__ __forceinline__ uint32_t merge_warp_scratch(uint32_t n_real, uint32_t n_ideal) { return n_real + 4 * n_ideal + 16; }
 
 __device__ __noinline__ uint32_t merge_cigars_warp(const uint32_t* __restrict__ real, uint32_t nR, const uint32_t* __restrict__ ideal_, uint32_t nI,
                                                    uint32_t iword, uint32_t* __restrict__ out, uint32_t* __restrict__ scr, unsigned lane) {
-  auto ideal = [&](uint32_t k) -> uint32_t { return nI == 1 ? iword : ideal_[k]; };
   const uint32_t lt_mask = (1u << lane) - 1u;
   uint32_t* EI = scr;                                  // [nI] inclusive prefix sums of the ideal ops' consumed lengths
-  uint32_t* pc = scr + nI + 1;                         // pieces, (len << 4) | op
+  uint32_t* IW = scr + nI + 1;                         // [nI] the ideal words from the cursor on (first one already shortened by ipos)
+  uint32_t* pc = scr + 2 * nI + 2;                     // pieces, (len << 4) | op
   uint32_t np = 0;
+  auto ideal = [&](uint32_t k) -> uint32_t { return nI == 1 ? iword : ideal_[k]; };
   auto add = [&](uint32_t op, uint32_t len) { if (len && op != OP_SKIP) { if (lane == 0) pc[np] = (len << 4) | op; np++; } };
   // ---- phases (1), (2): leading hard / soft clip, as in merge_cigars (uniform: every lane runs them, lane 0 writes)
   uint32_t front_hard = 0, front_soft = 0, ci = 0;
@@ -189,29 +233,22 @@ __device__ __noinline__ uint32_t merge_cigars_warp(const uint32_t* __restrict__ 
     }
   }
   const uint32_t nr = nR - ri, ni = nI - ii;
-  // ---- prefix sums of the ideal side
+  // ---- the ideal side from the cursor on: words and prefix sums of the consumed lengths
   uint32_t SI = 0;
   for (uint32_t base = 0; base < ni; base += 32) {
     const uint32_t m = base + lane;
-    uint32_t c = 0;
-    if (m < ni) { const uint32_t iw = ideal(ii + m), op = iw & 0xfu; c = (op == CD || op == OV_D) ? 0u : (iw >> 4) - (m == 0 ? ipos : 0u); }
+    uint32_t c = 0, w = 0;
+    if (m < ni) { w = ideal(ii + m); if (m == 0) w -= ipos << 4; const uint32_t op = w & 0xfu; c = (op == CD || op == OV_D) ? 0u : (w >> 4); }
     const uint32_t incl = warp_incl_scan(c, lane) + SI;
-    if (m < ni) EI[m] = incl;
+    if (m < ni) { EI[m] = incl; IW[m] = w; }
     SI = __shfl_sync(0xffffffffu, incl, 31);
   }
   __syncwarp();
-  auto ilen = [&](uint32_t m) { return (ideal(ii + m) >> 4) - (m == 0 ? ipos : 0u); };
-  auto icons = [&](uint32_t m) { const uint32_t op = ideal(ii + m) & 0xfu; return (op == CD || op == OV_D) ? 0u : ilen(m); };
-  // ideal cursor when the real side stands at coordinate x: ops that end before x, and a positive-length consumer that
-  // ends exactly at x, are done; zero-consumers located at x are still pending
-  auto ii_at = [&](uint32_t x) {
-    uint32_t lo = 0, n = ni;
-    while (n > 0) { const uint32_t h = n >> 1; if (EI[lo + h] < x) { lo += h + 1; n -= h + 1; } else n = h; }
-    if (lo < ni && EI[lo] == x && icons(lo) > 0) lo++;
-    return lo;
-  };
-  // ---- the real side, 32 ops at a time (lane = op)
-  uint32_t S0 = 0;
+  // An ideal op is DONE at real coordinate x when it ends before x, or ends at x after consuming something; zero-consumers
+  // (D, override D, empty ops) located at x are still pending there.  `adv` moves a cursor past everything done at x.
+  auto done_at = [&](uint32_t m, uint32_t x) { const uint32_t em = EI[m]; if (em < x) return true; if (em > x) return false; const uint32_t w = IW[m], op = w & 0xfu; return op != CD && op != OV_D && (w >> 4) > 0; };
+  // ---- the real side, 32 ops at a time (lane = op); the pieces of a tile go to `pc` in real-op order
+  uint32_t S0 = 0, m_tile = 0;                         // coordinate and ideal cursor at the start of the tile
   for (uint32_t base = 0; base < nr; base += 32) {
     const uint32_t k = base + lane;
     const bool act = k < nr;
@@ -221,56 +258,58 @@ __device__ __noinline__ uint32_t merge_cigars_warp(const uint32_t* __restrict__ 
     const bool zero_op = rop == CN || rop == CI;
     const uint32_t cons = (act && !zero_op) ? rlen : 0u;
     const uint32_t e = warp_incl_scan(cons, lane) + S0, s = e - cons;
+    while (m_tile < ni && done_at(m_tile, S0)) m_tile++;          // (uniform)
     S0 = __shfl_sync(0xffffffffu, e, 31);
-    // the op's pieces: counted (the first two are kept in registers), then written at their place in real-op order
-    uint32_t cnt = 0, p0 = 0, p1 = 0;
-    auto emit = [&](uint32_t op, uint32_t len, uint32_t* dst) {
-      if (len == 0 || op == OP_SKIP) return;
+    uint32_t m = m_tile;
+    if (act) while (m < ni && done_at(m, s)) m++;                 // the ideal cursor when this op is at the front
+    // the op's pieces (at most 3 are kept; more -- several ideal Ds under one real op -- is left to the serial code)
+    uint32_t cnt = 0, p0 = 0, p1 = 0, p2 = 0;
+    auto emit = [&](uint32_t op, uint32_t len) {
+      if (len == 0 || op == 15u) return;
       const uint32_t w = (len << 4) | op;
-      if (dst) dst[cnt] = w; else if (cnt == 0) p0 = w; else if (cnt == 1) p1 = w;
+      if (cnt == 0) p0 = w; else if (cnt == 1) p1 = w; else p2 = w;
       cnt++;
     };
-    auto pieces_of = [&](uint32_t* dst) {
-      cnt = 0;
-      if (!act) return;
+    if (act) {
       if (zero_op) {
-        if (rop == CI) emit(CI, rlen, dst);
-        else if (!(ii_at(s) < ni)) emit(CN, rlen, dst);       // the ideal CIGAR is used up: real ops are copied verbatim
-        return;
-      }
-      uint32_t m = ii_at(s), cur = s;
-      for (; m < ni; m++) {
-        const uint32_t iw = ideal(ii + m), iop = iw & 0xfu, il = (iw >> 4) - (m == 0 ? ipos : 0u);
-        const uint32_t ic = (iop == CD || iop == OV_D) ? 0u : il, em = EI[m], sm = em - ic;
-        if (ic == 0) {                                        // zero-consumer at coordinate em
-          if (em >= e) break;                                 // it waits for the real op that starts there
-          if (iop == CD || iop == OV_D) emit(CD, il, dst);
-          continue;
+        if (rop == CI) emit(CI, rlen);
+        else if (m >= ni) emit(CN, rlen);                         // the ideal CIGAR is used up: real ops are copied verbatim
+      } else {
+        uint32_t cur = s;
+        for (; m < ni; m++) {
+          const uint32_t iw = IW[m], iop = iw & 0xfu, il = iw >> 4;
+          const uint32_t ic = (iop == CD || iop == OV_D) ? 0u : il, em = EI[m], sm = em - ic;
+          if (ic == 0) {                                          // zero-consumer at coordinate em
+            if (em >= e) break;                                   // it waits for the real op that starts there
+            if (il) emit(CD, il);
+            continue;
+          }
+          if (sm >= e) break;
+          const uint32_t a = sm > cur ? sm : cur, bnd = em < e ? em : e;
+          emit(merge_ops_tab(rop, iop), bnd - a);
+          cur = bnd;
+          if (em > e) break;                                      // the ideal op continues under the next real op
         }
-        if (sm >= e) break;
-        const uint32_t a = sm > cur ? sm : cur, bnd = em < e ? em : e;
-        if (!(rop == CD && (iop == CS || iop == OV_S || iop == CI || iop == OV_I))) emit(merge_ops(rop, iop), bnd - a, dst);
-        cur = bnd;
-        if (em > e) break;                                    // the ideal op continues under the next real op
+        if (m >= ni) { const uint32_t from = SI > s ? SI : s; if (e > from) emit(rop, e - from); }     // ideal used up: the rest verbatim
       }
-      if (m >= ni) { const uint32_t from = SI > s ? SI : s; if (e > from) emit(rop, e - from, dst); }     // ideal used up: the rest verbatim
-    };
-    pieces_of(nullptr);
-    const uint32_t mine = cnt;
-    const uint32_t incl = warp_incl_scan(mine, lane), off = np + incl - mine;
-    if (mine == 1) pc[off] = p0;
-    else if (mine == 2) { pc[off] = p0; pc[off + 1] = p1; }
-    else if (mine > 2) pieces_of(pc + off);
+    }
+    if (__any_sync(0xffffffffu, cnt > 3)) return MERGE_SERIAL;
+    const uint32_t incl = warp_incl_scan(cnt, lane), off = np + incl - cnt;
+    if (cnt > 0) pc[off] = p0;
+    if (cnt > 1) pc[off + 1] = p1;
+    if (cnt > 2) pc[off + 2] = p2;
     np += __shfl_sync(0xffffffffu, incl, 31);
   }
   // ---- real side used up: the rest of the ideal CIGAR verbatim
   {
-    const uint32_t SR = S0, m0 = ii_at(SR);
+    const uint32_t SR = S0;
+    uint32_t m0 = m_tile;
+    while (m0 < ni && done_at(m0, SR)) m0++;
     for (uint32_t base = m0; base < ni; base += 32) {
       const uint32_t m = base + lane;
       uint32_t w = 0;
       if (m < ni) {
-        const uint32_t iw = ideal(ii + m), iop = iw & 0xfu, il = (iw >> 4) - (m == 0 ? ipos : 0u);
+        const uint32_t iw = IW[m], iop = iw & 0xfu, il = iw >> 4;
         const uint32_t ic = (iop == CD || iop == OV_D) ? 0u : il, em = EI[m], sm = em - ic;
         const uint32_t len = ic == 0 ? il : em - (sm > SR ? sm : SR);
         if (len) w = (len << 4) | iop;
@@ -281,8 +320,8 @@ __device__ __noinline__ uint32_t merge_cigars_warp(const uint32_t* __restrict__ 
     }
   }
   __syncwarp();
-  // ---- run-length coalescing of the pieces into `out`
-  uint32_t n_out = 0, open_w = 0; bool have_open = false, saw_i = false;
+  // ---- run-length coalescing of the pieces into `out`; on the way: is there an I run between two clip runs (step (4))?
+  uint32_t n_out = 0, open_w = 0; bool have_open = false, fix = false, open_susp = false;
   for (uint32_t base = 0; base < np; base += 32) {
     const uint32_t i = base + lane;
     const bool v = i < np;
@@ -302,28 +341,26 @@ __device__ __noinline__ uint32_t merge_cigars_warp(const uint32_t* __restrict__ 
     const uint32_t above = H & ~((2u << lane) - 1u);                    // heads after me
     const int next_h = above ? __ffs(above) - 1 : -1;
     const uint32_t run_end = __shfl_sync(0xffffffffu, L, next_h > 0 ? next_h - 1 : last_v);
+    const uint32_t next_op = __shfl_sync(0xffffffffu, op, next_h > 0 ? next_h : 0);
     const uint32_t L_before_me = L - len;
+    // an I run whose neighbours are both clip runs: (previous run = prev_op of its head; next run = the next head's op)
+    const bool susp = head && op == CI && (prev_op == CS || prev_op == CH);
+    if (susp && next_h >= 0 && (next_op == CS || next_op == CH)) fix = true;
+    if (open_susp && (int)lane == first_h && (op == CS || op == CH)) fix = true;
     if (head) {
       const uint32_t word = ((run_end - L_before_me) << 4) | op;
       const uint32_t idx = n_out + __popc(H & lt_mask);
       if (next_h >= 0) out[idx] = word;
-      if (op == CI) saw_i = true;
     }
     const int last_h = 31 - __clz(H);
     const uint32_t last_word = (((__shfl_sync(0xffffffffu, L, last_v) - __shfl_sync(0xffffffffu, L_before_me, last_h)) << 4)) | __shfl_sync(0xffffffffu, op, last_h);
+    open_susp = __shfl_sync(0xffffffffu, (uint32_t)susp, last_h) != 0;
     n_out += __popc(H); open_w = last_word; have_open = true;
   }
   if (have_open && lane == 0) out[n_out - 1] = open_w;
   __syncwarp();
-  if (!__any_sync(0xffffffffu, saw_i)) return n_out;
-  // ---- (4) an I between clips becomes that clip, (5) re-coalesce: only ever matters when such an I exists
-  bool hit = false;
-  for (uint32_t i = 1 + lane; i + 1 < n_out; i += 32) {
-    if ((out[i] & 0xfu) != CI) continue;
-    const uint32_t prev = out[i - 1] & 0xfu, next = out[i + 1] & 0xfu;
-    if ((prev == CS || prev == CH) && (next == CS || next == CH)) hit = true;
-  }
-  if (!__any_sync(0xffffffffu, hit)) return n_out;
+  if (!__any_sync(0xffffffffu, fix)) return n_out;
+  // ---- (4) an I between clips becomes that clip, (5) re-coalesce (rare: lane 0)
   uint32_t n = 0;
   if (lane == 0) {
     for (uint32_t i = 1; i + 1 < n_out; i++) {

@@ -5,26 +5,41 @@
 namespace {
 
 struct KswClassCfg { int G, W, ctas_per_sm; };
-constexpr KswClassCfg kKswCfg[4] = {{8, 2, 4}, {16, 2, 4}, {32, 2, 4}, {32, 8, 1}};
+constexpr int kKswReg = KSW_CLASSES - 1;          // classes served by the register kernel
+constexpr KswClassCfg kKswCfg[kKswReg] = {{8, 2, 4}, {16, 2, 4}, {32, 2, 4}, {32, 4, 2}, {32, 8, 1}};
 inline uint32_t ksw_rows_cap(int cls) { const int qmax = kKswCfg[cls].G * kKswCfg[cls].W * 2; return (uint32_t)(2 * qmax + KSW_TAIL - 1); }
 inline size_t ksw_group_bytes(int cls) { return (size_t)ksw_rows_cap(cls) * kKswCfg[cls].G * kKswCfg[cls].W * 2; }
 
 struct RescueBufs {
-  Buf qlen, tlen, tb_off, queue, tb, kout, aln_group, pmat[4], big_pmat, big_seq, big_state;
-  uint32_t ctas[4] = {0, 0, 0, 0};
+  Buf qlen, tlen, tb_off, queue, tb, kout, aln_group, pmat[kKswReg], big_pmat, big_seq, big_state;
+  uint32_t ctas[kKswReg] = {};
+  cudaStream_t side[KSW_CLASSES] = {};            // the class kernels are independent: each runs on its own stream between two events
+  cudaEvent_t ev_fork = nullptr, ev_join[KSW_CLASSES] = {};
+  std::vector<Buf*> all() { std::vector<Buf*> v = {&qlen, &tlen, &tb_off, &queue, &tb, &kout, &aln_group, &big_pmat, &big_seq, &big_state}; for (auto& b : pmat) v.push_back(&b); return v; }
+  void release() {
+    for (Buf* b : all()) b->release();
+    for (auto& s : side) if (s) { cudaStreamDestroy(s); s = nullptr; }
+    if (ev_fork) { cudaEventDestroy(ev_fork); ev_fork = nullptr; }
+    for (auto& e : ev_join) if (e) { cudaEventDestroy(e); e = nullptr; }
+  }
   size_t big_mat = 0; uint32_t big_len = 0, big_state_len = 0, big_ctas = 0;     // per-warp scratch of k_ksw_big (capacities persist)
 };
 RescueBufs& rescue_bufs(brb_ctx* c) { if (!c->rb) c->rb = new RescueBufs(); return *c->rb; }
 void free_rescue_bufs(brb_ctx* c) {
   if (!c->rb) return;
-  RescueBufs& R = *c->rb;
-  for (Buf* b : {&R.qlen, &R.tlen, &R.tb_off, &R.queue, &R.tb, &R.kout, &R.aln_group, &R.pmat[0], &R.pmat[1], &R.pmat[2], &R.pmat[3], &R.big_pmat, &R.big_seq, &R.big_state}) b->release();
+  c->rb->release();
   delete c->rb; c->rb = nullptr;
 }
 
 // Scratch of the class kernels (fixed per class and SM count) and of the big-problem kernel (sized by what the last sequence asked for).
 int ensure_ksw_scratch(RescueBufs& R, int n_sm) {
-  for (int k = 0; k < 4; k++) {
+  if (!R.ev_fork) {
+    if (cudaEventCreateWithFlags(&R.ev_fork, cudaEventDisableTiming) != cudaSuccess) return fail(BRB_E_CUDA, "cudaEventCreate failed");
+    for (int k = 0; k < KSW_CLASSES; k++)
+      if (cudaStreamCreateWithFlags(&R.side[k], cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&R.ev_join[k], cudaEventDisableTiming) != cudaSuccess)
+        return fail(BRB_E_CUDA, "rescue side streams: %s", cudaGetErrorString(cudaGetLastError()));
+  }
+  for (int k = 0; k < kKswReg; k++) {
     R.ctas[k] = (uint32_t)(n_sm * kKswCfg[k].ctas_per_sm);
     ENS(R.pmat[k], (size_t)R.ctas[k] * KSW_WARPS * (32 / kKswCfg[k].G) * ksw_group_bytes(k));
   }
@@ -40,17 +55,32 @@ void launch_ksw_class(cudaStream_t st, uint32_t ctas, const DevIndex& ix, const 
   k_ksw_group<G, W><<<ctas, 32 * KSW_WARPS, 0, st>>>(ix, b, S, K, cls, n_direct, ctl, pmat, ksw_rows_cap(cls));
 }
 
-// The DP kernels of all classes on the queues that `ctl` / K describe.  n_direct != nullptr: explicit problem counts (brb_ksw_extend).
+// The DP kernels of all classes on the queues that `ctl` / K describe, side by side: the longest problems (fewest, slowest) first.
+// n_direct != nullptr: explicit problem counts (brb_ksw_extend).
 void launch_ksw_all(cudaStream_t st, RescueBufs& R, const DevIndex& ix, const DevBatch& b, const KswSrc& S, const KswWork& K, Ctl* ctl, const uint32_t* n_direct, uint64_t* L) {
   auto nd = [&](int k) { return n_direct ? n_direct[k] : 0u; };
-  if (!n_direct || nd(0)) { launch_ksw_class<8, 2>(st, R.ctas[0], ix, b, S, K, 0, nd(0), ctl, R.pmat[0].as<uint8_t>()); (*L)++; }
-  if (!n_direct || nd(1)) { launch_ksw_class<16, 2>(st, R.ctas[1], ix, b, S, K, 1, nd(1), ctl, R.pmat[1].as<uint8_t>()); (*L)++; }
-  if (!n_direct || nd(2)) { launch_ksw_class<32, 2>(st, R.ctas[2], ix, b, S, K, 2, nd(2), ctl, R.pmat[2].as<uint8_t>()); (*L)++; }
-  if (!n_direct || nd(3)) { launch_ksw_class<32, 8>(st, R.ctas[3], ix, b, S, K, 3, nd(3), ctl, R.pmat[3].as<uint8_t>()); (*L)++; }
-  if (!n_direct || nd(4)) {
-    KswBig B; B.pmat = R.big_pmat.as<uint8_t>(); B.pmat_stride = R.big_mat; B.seq = R.big_seq.as<uint8_t>(); B.seq_stride = R.big_len;
-    B.state = R.big_state.as<int8_t>(); B.state_stride = R.big_state_len;
-    k_ksw_big<<<R.big_ctas, 32 * KSW_WARPS, 0, st>>>(ix, b, S, K, nd(4), ctl, B); (*L)++;
+  cudaEventRecord(R.ev_fork, st);
+  for (int k = KSW_CLASSES - 1; k >= 0; k--) {
+    if (n_direct && !nd(k)) continue;
+    cudaStream_t s = R.side[k];
+    cudaStreamWaitEvent(s, R.ev_fork, 0);
+    if (k == KSW_BIG) {
+      KswBig B; B.pmat = R.big_pmat.as<uint8_t>(); B.pmat_stride = R.big_mat; B.seq = R.big_seq.as<uint8_t>(); B.seq_stride = R.big_len;
+      B.state = R.big_state.as<int8_t>(); B.state_stride = R.big_state_len;
+      k_ksw_big<<<R.big_ctas, 32 * KSW_WARPS, 0, s>>>(ix, b, S, K, nd(k), ctl, B);
+    } else {
+      uint8_t* pm = R.pmat[k].as<uint8_t>();
+      switch (k) {
+        case 0: launch_ksw_class<8, 2>(s, R.ctas[0], ix, b, S, K, 0, nd(0), ctl, pm); break;
+        case 1: launch_ksw_class<16, 2>(s, R.ctas[1], ix, b, S, K, 1, nd(1), ctl, pm); break;
+        case 2: launch_ksw_class<32, 2>(s, R.ctas[2], ix, b, S, K, 2, nd(2), ctl, pm); break;
+        case 3: launch_ksw_class<32, 4>(s, R.ctas[3], ix, b, S, K, 3, nd(3), ctl, pm); break;
+        default: launch_ksw_class<32, 8>(s, R.ctas[4], ix, b, S, K, 4, nd(4), ctl, pm); break;
+      }
+    }
+    (*L)++;
+    cudaEventRecord(R.ev_join[k], s);
+    cudaStreamWaitEvent(st, R.ev_join[k], 0);
   }
 }
 
@@ -99,16 +129,16 @@ extern "C" int brb_ksw_extend(brb_ctx* c, uint32_t n, const uint64_t* q_off, con
   if (!n) return BRB_OK;
   if (!c->n_sm) { int sm = 0; c->n_sm = (cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, c->idx->device) == cudaSuccess && sm > 0) ? sm : 148; }
   std::vector<uint32_t> qo(n + 1), to(n + 1), tbo(n + 1), queue((size_t)KSW_CLASSES * n);
-  uint32_t cnt[KSW_CLASSES] = {0, 0, 0, 0, 0};
+  uint32_t cnt[KSW_CLASSES] = {};
   RescueBufs R;                                   // a private set: the test entry does not touch the context's rescue state
   tbo[0] = 0;
   for (uint32_t i = 0; i <= n; i++) { qo[i] = (uint32_t)(q_off[i] - q_off[0]); to[i] = (uint32_t)(t_off[i] - t_off[0]); }
   for (uint32_t i = 0; i < n; i++) {
     const unsigned long long ql = qo[i + 1] - qo[i], tl = to[i + 1] - to[i];
     tbo[i + 1] = tbo[i] + (uint32_t)(ql + tl + 2);
-    const int cls = (tl > ql + KSW_TAIL) ? 4 : ksw_class_of((uint32_t)ql);      // (a rescue target is never longer than the query + 40; anything else goes to the general kernel)
+    const int cls = (tl > ql + KSW_TAIL) ? KSW_BIG : ksw_class_of((uint32_t)ql);      // (a rescue target is never longer than the query + 40; anything else goes to the general kernel)
     queue[(size_t)cls * n + cnt[cls]++] = i;
-    if (cls == 4 && ql && tl) {
+    if (cls == KSW_BIG && ql && tl) {
       R.big_mat = std::max<size_t>(R.big_mat, (size_t)(((ql + tl - 1) * std::min(ql, tl) + 127) & ~127ull));
       R.big_len = std::max<uint32_t>(R.big_len, (uint32_t)((std::max(ql, tl) + 16 + 15) & ~15ull));
       if (tl + 1 > (unsigned long long)KSW_SH_T) R.big_state_len = std::max<uint32_t>(R.big_state_len, (uint32_t)((tl + 1 + 15) & ~15ull));
@@ -145,6 +175,6 @@ extern "C" int brb_ksw_extend(brb_ctx* c, uint32_t n, const uint64_t* q_off, con
     for (uint32_t k = 0; k < ho[i].n_cig && k < cigar_cap && cigar_out; k++) cigar_out[(size_t)i * cigar_cap + k] = htb[tbo[i] + ho[i].n_cig - 1 - k];   // ksw_backtrack's final reversal
   }
   d_qo.release(); d_to.release(); d_q.release(); d_t.release(); d_ctl.release();
-  for (Buf* b : {&R.qlen, &R.tlen, &R.tb_off, &R.queue, &R.tb, &R.kout, &R.aln_group, &R.pmat[0], &R.pmat[1], &R.pmat[2], &R.pmat[3], &R.big_pmat, &R.big_seq, &R.big_state}) b->release();
+  R.release();
   return rc;
 }

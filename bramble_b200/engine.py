@@ -63,6 +63,9 @@ def _rows(o, batch):
     d = dict(n_rec=n, group_rec_off=cum[go].astype(np.uint32) if n_aln else np.zeros(n_groups + 1, np.uint32))
     for k in ("src_aln", "tid", "pos", "tx_strand", "flags", "sim_score", "clip_score"):
         d[k] = col[k][order]
+    if getattr(o, "hi", None):                                                   # BRB_OPT_FLUSH_TAGS
+        for k, dt in (("hi", np.int32), ("nh", np.int32), ("mapq", np.uint8), ("primary", np.uint8)):
+            d[k] = arr(getattr(o, k), n, dt)[order]
     if o.group_rec_off:                                                          # BRB_OPT_ORDERED_ROWS: already in emit order
         assert np.array_equal(order, np.arange(n)) and np.array_equal(arr(o.group_rec_off, n_groups + 1, np.uint32), d["group_rec_off"])
     co, pool = col["cigar_off"], col["cigar"]

@@ -248,6 +248,16 @@ class Batch:
             d.seq_codes = None
         return self
 
+    def attach_names(self, group_names):
+        """Read names per group (brb_batch_in::group_name_off / name_bytes): what BRB_OPT_FLUSH_TAGS hashes for the primary tie-break."""
+        enc = [n.encode() if isinstance(n, str) else bytes(n) for n in group_names]
+        assert len(enc) == int(self.desc.n_groups)
+        A = self.arrays
+        A["group_name_off"] = np.concatenate([[0], np.cumsum([len(x) for x in enc])]).astype(np.uint64)
+        A["name_bytes"] = np.frombuffer(b"".join(enc) + b"\0", dtype=np.uint8).copy()
+        self.desc.group_name_off = capi.ptr(A["group_name_off"]); self.desc.name_bytes = capi.ptr(A["name_bytes"])
+        return self
+
     def slice_groups(self, g0, g1):
         """Read-name groups [g0, g1) as a bundle of their own (mates never leave their group, src/bramble.cpp:272-311)."""
         A = self.arrays

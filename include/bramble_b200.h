@@ -85,6 +85,8 @@ typedef struct brb_batch_in {
   const int32_t*  mate_idx;             /* n_aln: batch-local index of the linked mate or -1 (process_pairs) */
   const uint64_t* group_seq_off;        /* n_groups+1 base offsets into seq_codes; NULL unless use_fasta */
   const uint8_t*  seq_codes;            /* group-shared read sequence (src/core.cpp:353-378), codes 0..4 */
+  const uint64_t* group_name_off;       /* n_groups+1 byte offsets into name_bytes; NULL unless BRB_OPT_FLUSH_TAGS is used */
+  const uint8_t*  name_bytes;           /* the read names (QNAME without the terminator), group after group */
 } brb_batch_in;
 
 /* One row per output BAM record.  Rows come in UNIT blocks: the unit owned by alignment a (an unpaired alignment, or
@@ -116,6 +118,12 @@ typedef struct brb_batch_out {
   const uint32_t* aln_rec_cnt;          /* n_aln: its rows (0 for the higher-indexed end of a pair and for units that emit nothing) */
   const uint32_t* packed_rows;          /* BRB_OPT_PACKED_ROWS only (else NULL): 4 words per row, see below; src_aln, tid, pos,
                                          * tx_strand, flags and cigar_off are then NULL */
+  /* BRB_OPT_FLUSH_TAGS only (else NULL): the per-name results of the reference's flush() (src/core.cpp:237-332), per row */
+  const int32_t*  hi;                   /* HI tag: 1-based counter over the records of the read name in emit order */
+  const int32_t*  nh;                   /* NH tag: records of the read name */
+  const uint8_t*  mapq;                 /* get_mapq(nh) (src/core.cpp:46-58) */
+  const uint8_t*  primary;              /* 1: the record belongs to the name's primary unit, 0: secondary, 2: tie whose library draw would
+                                         * have been rejected and repeated (probability k / 2^64): the caller decides that name itself */
 } brb_batch_out;
 
 /* BRB_OPT_PACKED_ROWS: the row columns as ONE 16-byte record per row -- a third fewer bytes device->host, which is what
@@ -177,6 +185,11 @@ int brb_ctx_stats(const brb_ctx* ctx, brb_stats* out);
 /* BRB_OPT_MERGE_WARP != 0: brb_merge_cigars() runs the warp-cooperative merge (the code long-read rows go through inside
  * brb_project) instead of the one-thread-per-pair code.  Results are identical; for the parity tests. */
 #define BRB_OPT_MERGE_WARP 5
+/* BRB_OPT_FLUSH_TAGS != 0: HI / NH / MAPQ and the primary choice -- incl. the reference's tie-break
+ * uniform_int_distribution(mt19937_64(std::hash(read_name))) -- are computed on the device per read-name group
+ * (brb_batch_out::hi, nh, mapq, primary).  Needs brb_batch_in::group_name_off / name_bytes; not available together with
+ * BRB_OPT_PACKED_ROWS.  A read name is assumed to form ONE group of the bundle (name-collated input). */
+#define BRB_OPT_FLUSH_TAGS 6
 int brb_ctx_set_option(brb_ctx* ctx, int option, int value);
 /* CUDA-event stopwatch on the ctx stream (what bench.py brackets its K timed steps with). */
 int brb_ctx_timer_start(brb_ctx* ctx);

@@ -15,6 +15,9 @@
 #include <chrono>
 #include <cstdlib>
 #include <cstring>
+#include <string>
+#include <random>
+#include <limits>
 #include <vector>
 
 namespace {
@@ -821,6 +824,39 @@ int brb_port_merge_cigars(uint32_t n, const uint32_t* real_off, const uint32_t* 
     merge_cigars(real + real_off[i], real_off[i + 1] - real_off[i], ideal + ideal_off[i], ideal_off[i + 1] - ideal_off[i], m);
     out_len[i] = (uint32_t)m.size();
     memcpy(out + out_off[i], m.data(), m.size() * 4);
+  }
+  return BRB_OK;
+}
+
+// ---- src/core.cpp:237-332 flush(): per name, in emit order; :46-58 get_mapq; :214-218 get_rand (the real library)
+int brb_port_flush_tags(uint32_t n_groups, const uint32_t* group_rec_off, const uint8_t* flags, const double* sim,
+                        const uint64_t* name_off, const uint8_t* names, int long_reads,
+                        int32_t* hi, int32_t* nh, uint8_t* mapq, uint8_t* primary) {
+  for (uint32_t g = 0; g < n_groups; g++) {
+    const uint32_t r0 = group_rec_off[g], r1 = group_rec_off[g + 1];
+    if (r0 == r1) continue;
+    struct Unit { uint32_t row; bool paired; };
+    std::vector<Unit> pairs;
+    for (uint32_t r = r0; r < r1;) { const bool pr = flags[r] & BRB_REC_PAIRED; pairs.push_back({r, pr}); r += pr ? 2 : 1; }
+    auto score_of = [&](const Unit& u) { double s = sim ? sim[u.row] : 0.0; if (u.paired && sim) s = std::max(s, sim[u.row + 1]); return s; };
+    double best_score = -std::numeric_limits<double>::infinity(); int count_at_best = 0; size_t best = pairs.size(); int32_t hit_index = 1; int total = 0;
+    for (size_t i = 0; i < pairs.size(); i++) {
+      hi[pairs[i].row] = hit_index++; total++;
+      if (pairs[i].paired) { hi[pairs[i].row + 1] = hit_index++; total++; }
+      const double ps = score_of(pairs[i]);
+      if (ps > best_score) { best_score = ps; best = i; count_at_best = 1; } else if (ps == best_score) count_at_best++;
+    }
+    if (count_at_best > 1) {
+      std::vector<size_t> tied;
+      for (size_t i = 0; i < pairs.size(); i++) if (score_of(pairs[i]) == best_score) tied.push_back(i);
+      const std::string name((const char*)names + name_off[g], (size_t)(name_off[g + 1] - name_off[g]));
+      std::mt19937_64 gen(std::hash<std::string>{}(name));
+      std::uniform_int_distribution<uint32_t> dis(0, (uint32_t)tied.size() - 1);
+      best = tied[dis(gen)];
+    }
+    const uint32_t mq = !long_reads ? (total == 1 ? 255 : total == 2 ? 3 : (total == 3 || total == 4) ? 1 : 0) : (total > 1 ? 0 : 3);
+    for (size_t i = 0; i < pairs.size(); i++)
+      for (uint32_t e = 0; e < (pairs[i].paired ? 2u : 1u); e++) { const uint32_t r = pairs[i].row + e; nh[r] = total; mapq[r] = (uint8_t)mq; primary[r] = i == best; }
   }
   return BRB_OK;
 }

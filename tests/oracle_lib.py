@@ -36,8 +36,22 @@ def port():
         lib.brb_port_merge_cigars.argtypes = [C.c_uint32, capi.u32p, capi.u32p, capi.u32p, capi.u32p, capi.u32p, capi.u32p, capi.u32p]
         lib.brb_port_ksw_extend.argtypes = [C.c_uint32, capi.u64p, capi.u8p, capi.u64p, capi.u8p, capi.i32p, capi.i32p, capi.i32p,
                                             capi.i32p, capi.u8p, C.c_uint32, capi.u32p, capi.u32p]
+        lib.brb_port_flush_tags.argtypes = [C.c_uint32, capi.u32p, capi.u8p, capi.f64p, capi.u64p, capi.u8p, C.c_int, capi.i32p, capi.i32p, capi.u8p, capi.u8p]
         _port = lib
     return _port
+
+
+def port_flush_tags(rows, batch, long_reads):
+    """HI / NH / MAPQ / primary of the rows of `port_project` (emit order) with the real libstdc++ hash and RNG."""
+    n = int(rows["n_rec"])
+    hi = np.zeros(max(n, 1), np.int32); nh = np.zeros(max(n, 1), np.int32); mq = np.zeros(max(n, 1), np.uint8); pr = np.zeros(max(n, 1), np.uint8)
+    gro = np.ascontiguousarray(rows["group_rec_off"], dtype=np.uint32)
+    fl = np.ascontiguousarray(rows["flags"] if n else np.zeros(1, np.uint8), dtype=np.uint8)
+    sim = np.ascontiguousarray(rows["sim_score"] if n else np.zeros(1), dtype=np.float64)
+    rc = port().brb_port_flush_tags(int(batch.desc.n_groups), capi.ptr(gro), capi.ptr(fl), capi.ptr(sim), capi.ptr(batch.arrays["group_name_off"]),
+                                    capi.ptr(batch.arrays["name_bytes"]), int(long_reads), capi.ptr(hi), capi.ptr(nh), capi.ptr(mq), capi.ptr(pr))
+    assert rc == 0
+    return dict(hi=hi[:n], nh=nh[:n], mapq=mq[:n], primary=pr[:n])
 
 
 def rows_from(o, n_groups):

@@ -346,3 +346,38 @@ def test_c2_shape_hot_genes(stranded, multi_mean):
             st = eng.stats()
             assert st.n_matches == exp["n_matches"] and got["n_rec"] > 10000
         assert exp["n_hits"] > 0
+
+
+@pytest.mark.parametrize("kind", ["c5", "lr"])
+def test_flush_tags_on_device_match_libstdcxx(kind):
+    """BRB_OPT_FLUSH_TAGS: HI / NH / MAPQ and the primary choice per read name, computed on the device -- incl. the restated
+    std::hash<std::string> -> std::mt19937_64 -> std::uniform_int_distribution tie-break -- against the oracle, which runs the
+    reference's flush() arithmetic with the real libstdc++.  c5: multi-mappers, every multi-record name ties (scores are 0);
+    lr: similarity scores decide, ties are rare."""
+    if kind == "c5":
+        from bramble_b200 import synth_fast as sf
+        A = sf.make_annotation(5005, n_chrom=3, n_genes=600, paralog_families=60)
+        ix = sf.build_index(A)
+        b = sf.make_short_batch(A, ix, 77, 30000, stranded=None, multi_mean=5.0, paired_frac=0.6)
+        names = [f"r{k:09d}" if k % 7 else f"read/{k}:a-rather-longer-name#{k * 977}" for k in range(int(b.desc.n_groups))]
+        p = capi.resolve_params()
+    else:
+        wl = common.make_workload("lr", 61, n_names=4000, n_genes=120, n_chrom=2)
+        ix, p, b = wl["index"], wl["params"], wl["batches"][0]
+        go = b.arrays["group_off"]
+        names = [b.names[int(go[g])] for g in range(int(b.desc.n_groups))]
+    b.attach_names(names)
+    exp = oracle_lib.port_project(ix, p, b)
+    tags = oracle_lib.port_flush_tags(exp, b, bool(p.long_reads))
+    with engine.Engine(ix) as eng:
+        for ordered in (0, 1):
+            eng.set_option(capi.OPT_ORDERED_ROWS, ordered)
+            eng.set_option(capi.OPT_FLUSH_TAGS, 1)
+            got = eng.project(p, b)
+            oracle_lib.assert_rows_equal(exp, got, kind)
+            for k in ("hi", "nh", "mapq", "primary"):
+                assert np.array_equal(got[k], tags[k]), (kind, ordered, k, np.nonzero(got[k] != tags[k])[0][:5])
+        eng.set_option(capi.OPT_PACKED_ROWS, 1); eng.set_option(capi.OPT_ORDERED_ROWS, 0)
+        with pytest.raises(capi.EngineError):
+            eng.project(p, b)
+    assert int((tags["nh"] > 1).sum()) > 1000 and 0 < int(tags["primary"].sum()) < len(tags["primary"])
