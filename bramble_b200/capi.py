@@ -38,7 +38,7 @@ class IndexDesc(C.Structure):
     _fields_ = [("n_tables", C.c_uint32), ("table_off", u64p), ("st", i32p), ("en", i32p), ("tid", u32p),
                 ("exon_id", u8p), ("pos_start", u32p), ("prev_st", u32p), ("prev_en", u32p),
                 ("next_st", u32p), ("next_en", u32p), ("has_prev_next", u8p), ("transcript_len", u32p),
-                ("n_chrom", C.c_uint32), ("chrom_off", u64p), ("genome_codes", u8p)]
+                ("n_chrom", C.c_uint32), ("genome_format", C.c_uint32), ("chrom_off", u64p), ("genome_codes", u8p)]
 
 
 class BatchIn(C.Structure):

@@ -38,8 +38,10 @@ struct DevIndex {
   const uint32_t* gprev;         // record index of the genomically previous exon of the same tid (NONE if none)
   const uint32_t* bin_off;       // n_tables+1 offsets into bins
   const uint2* bins;             // per table, per bin b: .x = first i with pmax[i] > b<<shift, .y = first i with st[i] >= b<<shift
-  const uint64_t* chrom_off; const uint8_t* genome;   // codes 0..4, or null
+  const uint64_t* chrom_off; const uint8_t* genome;   // base codes 0..4, TWO per byte (low nibble = even offset), or null
 };
+// base code at offset o (in bases from the start of the first chromosome)
+__device__ __forceinline__ uint32_t genome_code(const DevIndex& ix, uint64_t o) { return (uint32_t)(__ldg(&ix.genome[o >> 1]) >> ((o & 1) << 2)) & 15u; }
 
 // Batches of 32 alignments a persistent warp takes per ticket (one same-address atomic each).  Measured on the C2
 // workload: two per ticket take 5 us off k_front_fast and add 5 us to k_back (uneven batches), four cost both.

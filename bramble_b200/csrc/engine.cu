@@ -21,6 +21,7 @@
 #include "k_back.cuh"
 #include "k_merge.cuh"
 #include "k_flush.cuh"
+#include "k_index.cuh"
 
 using namespace brb;
 
@@ -149,116 +150,106 @@ int brb_index_create(int device, const brb_index_desc* d, brb_index** out) {
   if (n >= 0xfffffff0ull) return fail(BRB_E_ARG, "too many index records");
   if (n && (!d->st || !d->en || !d->tid || !d->exon_id || !d->pos_start || !d->prev_st || !d->prev_en || !d->next_st ||
             !d->next_en || !d->has_prev_next || !d->transcript_len)) return fail(BRB_E_ARG, "null index column");
+  if (d->genome_format > 1) return fail(BRB_E_ARG, "unknown genome_format %u", d->genome_format);
   std::vector<uint32_t> toff(d->n_tables + 1, 0);
-  std::vector<int32_t> pmax(n);
-  std::vector<Rec> rec(n);
-  std::vector<uint32_t> gprev(n, NONE);
-  uint64_t span = 0;
   for (uint32_t t = 0; t < d->n_tables; t++) {
     toff[t] = (uint32_t)d->table_off[t];
     if (d->table_off[t + 1] < d->table_off[t]) return fail(BRB_E_ARG, "table_off not monotone");
-    int32_t m = INT32_MIN, prev = INT32_MIN;
-    for (uint64_t i = d->table_off[t]; i < d->table_off[t + 1]; i++) {
-      if (d->st[i] < prev) return fail(BRB_E_ARG, "table %u is not sorted by start", t);
-      if (d->st[i] < 0 || d->en[i] <= d->st[i]) return fail(BRB_E_ARG, "record %llu: empty or negative interval", (unsigned long long)i);
-      prev = d->st[i];
-      m = std::max(m, d->en[i]); pmax[i] = m;
-      Rec& r = rec[i];
-      r.st = d->st[i]; r.en = d->en[i]; r.tid = d->tid[i]; r.pos_start = d->pos_start[i];
-      r.gprev_en = 0; r.gnext_st = INT32_MAX; r.gnext = NONE;
-      r.meta = (uint32_t)d->exon_id[i] | ((uint32_t)(d->has_prev_next[i] & 1) << 8) | ((uint32_t)((d->has_prev_next[i] >> 1) & 1) << 9);
-    }
-    if (d->table_off[t + 1] > d->table_off[t]) span += (uint64_t)m;
   }
   toff[d->n_tables] = (uint32_t)n;
-  // exon chains: records of a table grouped by tid, ascending start
+  CU(cudaSetDevice(device));
+  brb_index* ix = new brb_index(); ix->device = device;
+  // the host's share of the build ends here (the order of the records is the caller's: brb_sort_by_start); everything derived
+  // from the sorted columns -- running max, exon chains, bin directory, records, validation -- is computed on the device (k_index.cuh)
+  Buf c_en, c_tid, c_eid, c_pos, c_ps, c_pe, c_ns, c_ne, c_hpn, c_err, c_cnt, c_gnext, g_tmp;
+  std::vector<Buf*> tmp = {&c_en, &c_tid, &c_eid, &c_pos, &c_ps, &c_pe, &c_ns, &c_ne, &c_hpn, &c_err, &c_cnt, &c_gnext, &g_tmp};
+  int rc = 0;
+  auto done = [&](int code) { for (Buf* b : tmp) b->release(); if (code) { ix->release_all(); delete ix; } return code; };
+  auto up = [&](Buf& b, const void* src, size_t bytes, bool resident) -> int {
+    int r = b.ensure(bytes ? bytes : 16); if (r) return r;
+    if (bytes && cudaMemcpy(b.p, src, bytes, cudaMemcpyHostToDevice) != cudaSuccess) return fail(BRB_E_CUDA, "index upload failed");
+    if (resident) ix->bytes += bytes;
+    return 0;
+  };
+  if (!rc) rc = up(ix->table_off, toff.data(), toff.size() * 4, true);
+  if (!rc) rc = up(ix->st, d->st, n * 4, true);
+  if (!rc) rc = up(c_en, d->en, n * 4, false);
+  if (!rc) rc = up(c_tid, d->tid, n * 4, false);
+  if (!rc) rc = up(c_eid, d->exon_id, n, false);
+  if (!rc) rc = up(c_pos, d->pos_start, n * 4, false);
+  if (!rc) rc = up(c_ps, d->prev_st, n * 4, false);
+  if (!rc) rc = up(c_pe, d->prev_en, n * 4, false);
+  if (!rc) rc = up(c_ns, d->next_st, n * 4, false);
+  if (!rc) rc = up(c_ne, d->next_en, n * 4, false);
+  if (!rc) rc = up(c_hpn, d->has_prev_next, n, false);
+  if (!rc) rc = ix->pmax.ensure(n * 4 + 16);
+  if (!rc) rc = ix->gprev.ensure(n * 4 + 16);
+  if (!rc) rc = c_gnext.ensure(n * 4 + 16);
+  if (!rc) rc = ix->rec.ensure(n * sizeof(Rec) + 32);
+  if (!rc) rc = c_err.ensure(sizeof(IndexErr));
+  if (rc) return done(rc);
+  ix->bytes += n * 4 * 2 + n * sizeof(Rec);
+  IndexCols C; C.n = (uint32_t)n; C.n_tables = d->n_tables; C.table_off = ix->table_off.as<uint32_t>(); C.st = ix->st.as<int32_t>(); C.en = c_en.as<int32_t>();
+  C.tid = c_tid.as<uint32_t>(); C.exon_id = c_eid.as<uint8_t>(); C.pos_start = c_pos.as<uint32_t>(); C.prev_st = c_ps.as<uint32_t>(); C.prev_en = c_pe.as<uint32_t>();
+  C.next_st = c_ns.as<uint32_t>(); C.next_en = c_ne.as<uint32_t>(); C.hpn = c_hpn.as<uint8_t>();
+  IndexErr* derr = c_err.as<IndexErr>(); IndexErr herr{};
+  cudaMemset(derr, 0, sizeof(IndexErr));
+  if (d->n_tables) k_index_pmax<<<d->n_tables, 32>>>(C, ix->pmax.as<int32_t>(), derr);
+  if (n) k_index_links<<<grid_for(n, 256), 256>>>(C, ix->gprev.as<uint32_t>(), c_gnext.as<uint32_t>(), derr);
+  if (cudaMemcpy(&herr, derr, sizeof herr, cudaMemcpyDeviceToHost) != cudaSuccess) return done(fail(BRB_E_CUDA, "index build failed: %s", cudaGetErrorString(cudaGetLastError())));
+  if (herr.code == 1) return done(fail(BRB_E_ARG, "table %u is not sorted by start", herr.aux));
+  if (herr.code == 2) return done(fail(BRB_E_ARG, "record %u: empty or negative interval", herr.rec));
+  if (herr.code == 3) return done(fail(BRB_E_UNSUPPORTED, "transcript %u has overlapping exons (records %u, %u); the reference's GTF loader merges those (gclib/gff.cpp:988)", d->tid[herr.rec], herr.aux, herr.rec));
+  if (herr.code == 4) return done(fail(BRB_E_ARG, "record %u: prev/next columns do not describe the neighbouring exons of transcript %u", herr.rec, herr.aux));
   uint32_t max_chain = 0;
-  {
-    std::vector<uint32_t> ord;
-    for (uint32_t t = 0; t < d->n_tables; t++) {
-      const uint32_t b = toff[t], e = toff[t + 1];
-      const bool minus = t & 1;
-      ord.resize(e - b);
-      for (uint32_t i = b; i < e; i++) ord[i - b] = i;
-      std::sort(ord.begin(), ord.end(), [&](uint32_t x, uint32_t y) { return d->tid[x] != d->tid[y] ? d->tid[x] < d->tid[y] : (d->st[x] != d->st[y] ? d->st[x] < d->st[y] : x < y); });
-      uint32_t run = 0;
-      for (size_t k = 0; k < ord.size(); k++) {
-        const uint32_t i = ord[k];
-        run = (k > 0 && d->tid[ord[k - 1]] == d->tid[i]) ? run + 1 : 1; max_chain = std::max(max_chain, run);
-        const bool has_p = k > 0 && d->tid[ord[k - 1]] == d->tid[i], has_n = k + 1 < ord.size() && d->tid[ord[k + 1]] == d->tid[i];
-        if (has_p) {
-          const uint32_t q = ord[k - 1];
-          if (d->en[q] > d->st[i]) return fail(BRB_E_UNSUPPORTED, "transcript %u has overlapping exons (records %u, %u); the reference's GTF loader merges those (gclib/gff.cpp:988)", d->tid[i], q, i);
-          gprev[i] = q; rec[i].gprev_en = d->en[q];
-        }
-        if (has_n) { const uint32_t q = ord[k + 1]; rec[i].gnext = q; rec[i].gnext_st = d->st[q]; }
-        // neighbour columns are in TRANSCRIPT order: '+' prev = genomic prev, '-' prev = genomic next
-        const bool hp = d->has_prev_next[i] & 1, hn = (d->has_prev_next[i] >> 1) & 1;
-        const bool g_has_p = minus ? hn : hp, g_has_n = minus ? hp : hn;
-        const uint32_t gp_st = minus ? d->next_st[i] : d->prev_st[i], gp_en = minus ? d->next_en[i] : d->prev_en[i];
-        const uint32_t gn_st = minus ? d->prev_st[i] : d->next_st[i], gn_en = minus ? d->prev_en[i] : d->next_en[i];
-        bool okc = g_has_p == has_p && g_has_n == has_n;
-        if (okc && has_p) okc = gp_st == (uint32_t)d->st[ord[k - 1]] && gp_en == (uint32_t)d->en[ord[k - 1]];
-        if (okc && !has_p) okc = gp_st == 0 && gp_en == 0;
-        if (okc && has_n) okc = gn_st == (uint32_t)d->st[ord[k + 1]] && gn_en == (uint32_t)d->en[ord[k + 1]];
-        if (okc && !has_n) okc = gn_st == 0 && gn_en == 0;
-        if (!okc) return fail(BRB_E_ARG, "record %u: prev/next columns do not describe the neighbouring exons of transcript %u", i, d->tid[i]);
-      }
-    }
+  if (n) {
+    const uint32_t n_tid = herr.max_tid + 1;
+    rc = c_cnt.ensure((size_t)n_tid * 4); if (rc) return done(rc);
+    cudaMemset(c_cnt.p, 0, (size_t)n_tid * 4);
+    k_index_chain_count<<<grid_for(n, 256), 256>>>(C, ix->gprev.as<uint32_t>(), c_cnt.as<uint32_t>());
+    k_index_chain_max<<<grid_for(n_tid, 256), 256>>>(n_tid, c_cnt.as<uint32_t>(), derr);
   }
   // bin directory: 2^shift bases per bin, about two bins per record overall
+  const uint64_t span = herr.span;
   uint32_t shift = 4;
   { const uint64_t target = std::max<uint64_t>(2 * n, 1024); while (shift < 24 && (span >> shift) > target) shift++; }
   if (const char* e = getenv("BRB_BIN_SHIFT")) { int v = atoi(e); if (v >= 2 && v <= 28) shift = (uint32_t)v; }
+  std::vector<int32_t> tmax(d->n_tables, 0);            // the last running maximum of every table fixes its number of bins
+  for (uint32_t t = 0; t < d->n_tables; t++)
+    if (toff[t + 1] > toff[t] && cudaMemcpy(&tmax[t], ix->pmax.as<int32_t>() + toff[t + 1] - 1, 4, cudaMemcpyDeviceToHost) != cudaSuccess) return done(fail(BRB_E_CUDA, "index build failed"));
   std::vector<uint32_t> boff(d->n_tables + 1, 0);
-  for (uint32_t t = 0; t < d->n_tables; t++) {
-    const uint32_t b = toff[t], e = toff[t + 1];
-    boff[t + 1] = boff[t] + (e > b ? ((uint32_t)pmax[e - 1] >> shift) + 2 : 0);
-  }
-  std::vector<uint2> bins(boff[d->n_tables]);
-  for (uint32_t t = 0; t < d->n_tables; t++) {
-    const uint32_t b = toff[t], e = toff[t + 1], nb = boff[t + 1] - boff[t];
-    uint32_t il = b, ih = b;
-    for (uint32_t k = 0; k < nb; k++) {
-      const int64_t x = (int64_t)k << shift;
-      while (il < e && (int64_t)pmax[il] <= x) il++;
-      while (ih < e && (int64_t)d->st[ih] < x) ih++;
-      bins[boff[t] + k] = make_uint2(il, ih);
+  for (uint32_t t = 0; t < d->n_tables; t++) boff[t + 1] = boff[t] + (toff[t + 1] > toff[t] ? ((uint32_t)tmax[t] >> shift) + 2 : 0);
+  rc = up(ix->bin_off, boff.data(), boff.size() * 4, true); if (rc) return done(rc);
+  rc = ix->bins.ensure((size_t)boff[d->n_tables] * sizeof(uint2) + 16); if (rc) return done(rc);
+  ix->bytes += (size_t)boff[d->n_tables] * sizeof(uint2);
+  if (boff[d->n_tables]) k_index_bins<<<grid_for(boff[d->n_tables], 256), 256>>>(C, ix->pmax.as<int32_t>(), ix->bin_off.as<uint32_t>(), shift, ix->bins.as<uint2>());
+  if (n) k_index_recs<<<grid_for(n, 256), 256>>>(C, ix->gprev.as<uint32_t>(), c_gnext.as<uint32_t>(), ix->rec.as<uint4>(), VAR_SPLIT_REC != 0);
+  static_assert(sizeof(Rec) == 32, "a record is a 16-byte key half and a 16-byte link half");
+  ix->d.n_tables = d->n_tables; ix->d.n_rec = n; ix->d.n_chrom = 0; ix->d.bin_shift = shift;
+  // genome: resident as two 4-bit codes per byte, whichever way it comes in
+  if (d->genome_codes && d->chrom_off && d->n_chrom) {
+    const uint64_t nb = d->chrom_off[d->n_chrom];
+    rc = up(ix->chrom_off, d->chrom_off, (size_t)(d->n_chrom + 1) * 8, true); if (rc) return done(rc);
+    if (d->genome_format == 1) { rc = up(ix->genome, d->genome_codes, (nb + 1) / 2, true); if (rc) return done(rc); }
+    else {
+      rc = up(g_tmp, d->genome_codes, nb, false); if (rc) return done(rc);
+      rc = ix->genome.ensure((nb + 1) / 2 + 16); if (rc) return done(rc);
+      ix->bytes += (nb + 1) / 2;
+      if (nb) k_pack_genome<<<grid_for((nb + 1) / 2, 256), 256>>>(g_tmp.as<uint8_t>(), nb, ix->genome.as<uint8_t>());
     }
-  }
-  CU(cudaSetDevice(device));
-  brb_index* ix = new brb_index(); ix->device = device;
-  int rc = 0;
-  auto up = [&](Buf& b, const void* src, size_t bytes) -> int {
-    int r = b.ensure(bytes ? bytes : 16); if (r) return r;
-    if (bytes && cudaMemcpy(b.p, src, bytes, cudaMemcpyHostToDevice) != cudaSuccess) return fail(BRB_E_CUDA, "index upload failed");
-    ix->bytes += bytes; return 0;
-  };
-  if (!rc) rc = up(ix->table_off, toff.data(), toff.size() * 4);
-  if (!rc) rc = up(ix->st, d->st, n * 4);
-  if (!rc) rc = up(ix->pmax, pmax.data(), n * 4);
-  if (VAR_SPLIT_REC) {                  // keys first, links after them (dev_common.cuh: rec_key / rec_link)
-    static_assert(sizeof(Rec) == 32, "a record is a 16-byte key half and a 16-byte link half");
-    std::vector<uint4> halves(2 * (size_t)n);
-    const uint4* src = reinterpret_cast<const uint4*>(rec.data());
-    for (size_t i = 0; i < n; i++) { halves[i] = src[2 * i]; halves[n + i] = src[2 * i + 1]; }
-    if (!rc) rc = up(ix->rec, halves.data(), halves.size() * sizeof(uint4));
-  } else if (!rc) rc = up(ix->rec, rec.data(), n * sizeof(Rec));
-  if (!rc) rc = up(ix->gprev, gprev.data(), n * 4);
-  if (!rc) rc = up(ix->bin_off, boff.data(), boff.size() * 4);
-  if (!rc) rc = up(ix->bins, bins.data(), bins.size() * sizeof(uint2));
-  ix->d.n_tables = d->n_tables; ix->d.n_rec = n; ix->d.n_chrom = 0; ix->d.bin_shift = shift; ix->d.max_chain = max_chain;
-  if (!rc && d->genome_codes && d->chrom_off && d->n_chrom) {
-    rc = up(ix->chrom_off, d->chrom_off, (size_t)(d->n_chrom + 1) * 8);
-    if (!rc) rc = up(ix->genome, d->genome_codes, d->chrom_off[d->n_chrom]);
     ix->d.n_chrom = d->n_chrom;
   }
-  if (rc) { ix->release_all(); delete ix; return rc; }
+  if (cudaMemcpy(&herr, derr, sizeof herr, cudaMemcpyDeviceToHost) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess)
+    return done(fail(BRB_E_CUDA, "index build failed: %s", cudaGetErrorString(cudaGetLastError())));
+  if (herr.code == 4) return done(fail(BRB_E_ARG, "transcript %u: the prev/next columns do not connect its exons into one chain", herr.aux));
+  max_chain = herr.max_chain;
+  ix->d.max_chain = max_chain;
   ix->d.table_off = ix->table_off.as<uint32_t>(); ix->d.st = ix->st.as<int32_t>(); ix->d.pmax = ix->pmax.as<int32_t>();
   ix->d.rkey = ix->rec.as<uint4>(); ix->d.rlink = ix->rec.as<uint4>() + (VAR_SPLIT_REC ? n : 0); ix->d.gprev = ix->gprev.as<uint32_t>();
   ix->d.bin_off = ix->bin_off.as<uint32_t>(); ix->d.bins = ix->bins.as<uint2>();
   ix->d.chrom_off = ix->d.n_chrom ? ix->chrom_off.as<uint64_t>() : nullptr;
   ix->d.genome = ix->d.n_chrom ? ix->genome.as<uint8_t>() : nullptr;
+  done(0);
   *out = ix;
   return BRB_OK;
 }

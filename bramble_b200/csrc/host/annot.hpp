@@ -122,7 +122,8 @@ inline void load_annotation(const std::string& path, Annotation& A) {
   A.tx.swap(tx);
 }
 
-// FASTA -> per-refid code strings (A,C,G,T -> 0..3, everything else 4; GFaSeqGet::copyRange upper-cases, src/g2t.cpp:50-55)
+// FASTA -> base codes per refid (A,C,G,T -> 0..3, everything else 4; GFaSeqGet::copyRange upper-cases, src/g2t.cpp:50-55), packed two per
+// byte for the upload (brb_index_desc::genome_format 1: base o in byte o / 2, low nibble = even o; chrom_off counts bases)
 inline void load_genome(const std::string& path, const Annotation& A, std::vector<uint64_t>& chrom_off, std::vector<uint8_t>& codes) {
   FILE* f = fopen(path.c_str(), "r");
   if (!f) throw std::runtime_error("could not open genome FASTA " + path);
@@ -142,7 +143,14 @@ inline void load_genome(const std::string& path, const Annotation& A, std::vecto
   }
   free(line); fclose(f);
   chrom_off.assign(1, 0); codes.clear();
-  for (auto& v : seqs) { codes.insert(codes.end(), v.begin(), v.end()); chrom_off.push_back(codes.size()); }
+  uint64_t nb = 0;
+  for (auto& v : seqs) {
+    codes.resize((nb + v.size() + 1) / 2, 0);
+    for (size_t i = 0; i < v.size(); i++, nb++) { if (nb & 1) codes[nb >> 1] |= (uint8_t)(v[i] << 4); else codes[nb >> 1] = v[i]; }
+    std::vector<uint8_t>().swap(v);
+    chrom_off.push_back(nb);
+  }
+  if (nb & 1) codes[nb >> 1] |= 4 << 4;
 }
 
 // build_g2t_tree (src/bramble.cpp:132-211) into flat columns; tid = position in A.tx (== output header order).
@@ -193,7 +201,7 @@ inline void build_index_columns(const Annotation& A, IndexColumns& C) {
   d.exon_id = C.exon_id.data(); d.pos_start = C.pos_start.data(); d.prev_st = C.prev_st.data(); d.prev_en = C.prev_en.data();
   d.next_st = C.next_st.data(); d.next_en = C.next_en.data(); d.has_prev_next = C.hpn.data(); d.transcript_len = C.tlen.data();
   d.n_chrom = C.genome.empty() ? 0 : (uint32_t)n_ref; d.chrom_off = C.genome.empty() ? nullptr : C.chrom_off.data();
-  d.genome_codes = C.genome.empty() ? nullptr : C.genome.data();
+  d.genome_codes = C.genome.empty() ? nullptr : C.genome.data(); d.genome_format = 1;
 }
 
 }  // namespace brbhost

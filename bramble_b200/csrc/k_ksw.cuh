@@ -165,7 +165,7 @@ __device__ __forceinline__ void gather_target(const DevIndex& ix, int32_t refid,
     const uint32_t len = (uint32_t)(k.en - k.st), take = len < tlen - w ? len : tlen - w;
     for (uint32_t i = gl; i < take; i += nl) {
       const uint64_t o = left ? base + ((uint32_t)k.en - 1 - i) - 1 : base + ((uint32_t)k.st + i) - 1;      // 1-based coordinate -> 0-based offset
-      dst[w + i] = o < lim ? ix.genome[o] : 4;
+      dst[w + i] = o < lim ? (uint8_t)genome_code(ix, o) : 4;
     }
     w += take; cur = nx;
   }

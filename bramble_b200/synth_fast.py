@@ -276,9 +276,12 @@ def build_index(A, genome_codes=None):
         by_ref = [np.zeros(0, np.uint8)] * n_ref
         for c in seen:
             by_ref[ix.refid_of[A.chroms[c]]] = genome_codes[c]
-        ix.arrays["genome_codes"] = np.ascontiguousarray(np.concatenate(by_ref))
+        flat = np.concatenate(by_ref + [np.full(1, 4, np.uint8)])                    # (pad to an even count)
+        nb = int(sum(len(g) for g in by_ref))
+        flat = flat[:nb + (nb & 1)]
+        ix.arrays["genome_codes"] = np.ascontiguousarray(flat[0::2] | (flat[1::2] << 4))   # two codes per byte: brb_index_desc::genome_format 1
         ix.arrays["chrom_off"] = np.concatenate([[0], np.cumsum([len(g) for g in by_ref])]).astype(np.uint64)
-        d.n_chrom = n_ref
+        d.n_chrom = n_ref; d.genome_format = 1
         d.chrom_off = capi.ptr(ix.arrays["chrom_off"]); d.genome_codes = capi.ptr(ix.arrays["genome_codes"])
     ix.refid_of_chrom = refid_of_chrom
     return ix

@@ -51,7 +51,10 @@ typedef struct brb_params {
 /* Flattened interval table = the reference's per-(refid,strand) IITree<int,IITData> arrays
  * (include/g2t.h:27-43, src/g2t.cpp:34-62) concatenated; table t = 2*refid + (strand=='-').
  * Records of one table are in the reference's own order (std::sort by start on the reference's
- * insertion sequence, cgranges IITree::index), so "hit order" == ascending record index. */
+ * insertion sequence, cgranges IITree::index; brb_sort_by_start yields it), so "hit order" == ascending record index.
+ * That order is the host's only share of the index build: brb_index_create uploads the columns and derives the
+ * max-augmentation, the exon chains, the bin directory and the device records on the GPU, validating on the way
+ * (sorted tables, disjoint ascending exons per transcript, consistent neighbour columns). */
 typedef struct brb_index_desc {
   uint32_t n_tables;                    /* 2 * number of annotated chromosomes */
   const uint64_t* table_off;            /* n_tables+1 offsets into the record arrays */
@@ -65,9 +68,12 @@ typedef struct brb_index_desc {
   const uint8_t*  has_prev_next;        /* bit0 has_prev, bit1 has_next */
   const uint32_t* transcript_len;
   /* genome, only for use_fasta: per-refid base codes 0..3 = A,C,G,T, 4 = anything else (the ksw2
-   * encoding of reference src/evaluate.cpp:299-305), one byte per base, 0-based genomic offset. */
+   * encoding of reference src/evaluate.cpp:299-305), 0-based genomic offset.  genome_format 0: one code per byte;
+   * 1: two codes per byte (base o in byte o / 2, low nibble = even o) -- half the upload.  Resident on the device it is
+   * always the packed form. */
   uint32_t n_chrom;
-  const uint64_t* chrom_off;            /* n_chrom+1 offsets into genome_codes, or NULL */
+  uint32_t genome_format;
+  const uint64_t* chrom_off;            /* n_chrom+1 offsets (in bases) into the genome, or NULL */
   const uint8_t*  genome_codes;         /* or NULL */
 } brb_index_desc;
 

@@ -250,7 +250,7 @@ void exon_codes(const Ctx& c, int refid, const GExon& g, std::vector<uint8_t>& o
   uint64_t base = c.ix->chrom_off[refid], lim = c.ix->chrom_off[refid + 1];
   for (uint64_t pos = g.start; pos < g.end; pos++) {        // 1-based [start, end)
     uint64_t o = base + pos - 1;
-    out.push_back(o < lim ? c.ix->genome_codes[o] : 4);
+    out.push_back(o < lim ? (c.ix->genome_format == 1 ? (uint8_t)((c.ix->genome_codes[o >> 1] >> ((o & 1) * 4)) & 15) : c.ix->genome_codes[o]) : 4);
   }
 }
 
