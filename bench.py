@@ -309,17 +309,14 @@ def measure_workload(W, args, local, cores, peak, with_cpu=True):
         B, p = W.B, W.params
         n_aln = int(B.desc.n_aln)
         eng.upload(B)
-        alg = alg_front = None
-        if not W.long:                     # reference-defined algorithmic bytes: every read exon looked up (generic front kernel), untimed
-            eng.set_option(capi.OPT_GENERIC_FRONT, 1)
-            eng.run_resident(p)
-            alg, alg_front = int(eng.stats().alg_bytes), int(eng.stats().alg_bytes_front)
-            eng.set_option(capi.OPT_GENERIC_FRONT, 0)
+        # reference-defined algorithmic bytes: every read exon looked up and every hit counted (BRB_OPT_GENERIC_FRONT), once, untimed
+        eng.set_option(capi.OPT_GENERIC_FRONT, 1)
+        eng.run_resident(p)
+        alg, alg_front = int(eng.stats().alg_bytes), int(eng.stats().alg_bytes_front)
+        eng.set_option(capi.OPT_GENERIC_FRONT, 0)
         for _ in range(3):
             eng.run_resident(p)
         st = eng.stats()
-        if W.long:
-            alg, alg_front = int(st.alg_bytes), int(st.alg_bytes_front)
         steps = max(2, min(args.steps, int(1500.0 / max(st.kernel_ms, 0.05))))       # bounded: ~1.5 s of timed steps at most
         ms, launches, phase = timed_resident(eng, p, steps)
         st = eng.stats()

@@ -75,6 +75,7 @@ struct DevBatch {
   const uint32_t* cigar_off; const uint32_t* cigar; const int32_t* mate_idx;
   const uint64_t* group_seq_off; const uint8_t* seq; const uint32_t* aln_group;
   uint32_t back_shift;           // k_back / k_place: log2 of the alignments per batch (5 for short reads, 3 for long reads)
+  uint32_t count_hits;           // k_front: count EVERY index hit of every read exon (the reference-defined figure); else later exons stop at the first survivor
 };
 
 // Device-side control block of one brb_project_resident call: capacities of the pre-allocated pools and the

@@ -347,7 +347,7 @@ static int batch_upload_async(brb_ctx* c, const brb_batch_in* in) {
   b.exon_off = c->in_exon_off.as<uint32_t>(); b.exon_st = c->in_exon_st.as<uint32_t>(); b.exon_en = c->in_exon_en.as<uint32_t>();
   b.cigar_off = c->in_cigar_off.as<uint32_t>(); b.cigar = c->in_cigar.as<uint32_t>(); b.mate_idx = c->in_mate.as<int32_t>();
   b.group_seq_off = have_seq ? c->in_seq_off.as<uint64_t>() : nullptr; b.seq = have_seq ? c->in_seq.as<uint8_t>() : nullptr;
-  b.aln_group = nullptr; b.back_shift = 5;
+  b.aln_group = nullptr; b.back_shift = 5; b.count_hits = 0;
   c->stats.h2d_bytes = c->in_bytes;
   c->have_batch = true;
   return BRB_OK;
@@ -400,6 +400,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   const bool rescue = p.long_reads && p.use_fasta;
   if (rescue && !c->idx->d.genome) return fail(BRB_E_UNSUPPORTED, "use_fasta requested but the index holds no genome");
   if (rescue && c->b.n_aln && !c->b.seq) return fail(BRB_E_UNSUPPORTED, "use_fasta requested but the batch carries no read sequences");
+  c->b.count_hits = c->opt_generic_front ? 1u : 0u;
   c->b.back_shift = p.long_reads ? 3u : 5u;           // long reads: 8 alignments per k_back batch (rows of 10^2..10^4 CIGAR words)
   const DevBatch& b = c->b; const DevIndex& ix = c->idx->d;
   cudaStream_t st = c->st;

@@ -4,9 +4,15 @@
 // (reference src/bramble.cpp:528-535): exons of a transcript sorted and overlapping/adjacent ones merged
 // (gclib/gff.cpp:988-1079), transcripts ordered by gfo_cmpByLoc (gclib/gff.cpp:75-91: chromosome NAME strcmp,
 // start, level, end, ID), refid = order of first appearance of the chromosome in the file; then
-// build_g2t_tree (src/bramble.cpp:132-211).  Supported input: GTF with exon lines (transcript lines optional)
-// and GFF3 with ID=/Parent= on mRNA|transcript + exon lines; other gclib features (CDS-only models, gene
-// segments, discontinuous features) are not handled.
+// build_g2t_tree (src/bramble.cpp:132-211).  Supported input: GTF (GENCODE / Ensembl / StringTie style: gene, transcript,
+// exon, CDS, UTR, codon rows; transcript rows optional) and GFF3 with ID=/Parent= on gene, mRNA|transcript|*RNA and exon
+// rows.  Two gclib details that decide the transcript ORDER (hence tids and the @SQ lines) are kept:
+//   * gff_level (gclib/gff.cpp:1436-1450): a transcript whose ROW names a parent gene that was seen earlier in the file is
+//     level 1, every other transcript (no gene rows in the file, or built from exon rows only) level 0 -- and the level
+//     sorts before the end coordinate and the ID (gfo_cmpByLoc);
+//   * an exon row with several parents (GFF3) is added to the parents already seen; if none is, only the first one is
+//     created from it (gclib/gff.cpp:1743-1760).
+// Not handled: CDS-only models (no exon rows), trans-spliced / discontinuous features with a repeated ID.
 #pragma once
 #include <algorithm>
 #include <cstdint>
@@ -24,7 +30,7 @@ namespace brbhost {
 
 struct Transcript {
   std::string id, chrom; int refid = -1; char strand = '.';
-  uint32_t start = 0, end = 0; int level = 1; bool has_line = false;
+  uint32_t start = 0, end = 0; int level = 0; bool has_line = false;
   std::vector<std::pair<uint32_t, uint32_t>> exons;     // 1-based inclusive, ascending after finalize()
   uint32_t tlen = 0;
 };
@@ -60,6 +66,7 @@ inline void load_annotation(const std::string& path, Annotation& A) {
   FILE* f = fopen(path.c_str(), "r");
   if (!f) throw std::runtime_error("could not open reference annotation file " + path);
   std::unordered_map<std::string, size_t> by_id;
+  std::unordered_map<std::string, bool> gene_seen;      // IDs of the gene rows read so far (GTF: gene_id; GFF3: ID)
   std::vector<Transcript> tx;
   char* line = nullptr; size_t cap = 0; ssize_t n;
   auto get_tx = [&](const std::string& id, const std::string& chrom, char strand) -> Transcript& {
@@ -85,20 +92,30 @@ inline void load_annotation(const std::string& path, Annotation& A) {
     if (feat == "exon") {
       std::string id = gff3 ? attr_value(attrs, "Parent", true) : attr_value(attrs, "transcript_id", false);
       if (id.empty()) continue;
-      size_t start = 0;                              // GFF3: an exon may list several parents
-      while (start <= id.size()) {
+      std::vector<std::string> parents;              // GFF3: an exon may list several parents
+      for (size_t start = 0; start <= id.size();) {
         size_t c = gff3 ? id.find(',', start) : std::string::npos;
-        std::string one = id.substr(start, c == std::string::npos ? std::string::npos : c - start);
-        Transcript& t = get_tx(one, col[0], strand);
-        t.exons.emplace_back(std::min(s, e), std::max(s, e));
+        parents.push_back(id.substr(start, c == std::string::npos ? std::string::npos : c - start));
         if (c == std::string::npos) break;
         start = c + 1;
       }
+      bool any_known = false;
+      for (auto& one : parents) if (by_id.count(one)) any_known = true;
+      for (size_t k = 0; k < parents.size(); k++) {
+        if (any_known ? !by_id.count(parents[k]) : k > 0) continue;      // parents not seen yet do not get the exon; with none seen the first is created from it
+        Transcript& t = get_tx(parents[k], col[0], strand);
+        t.exons.emplace_back(std::min(s, e), std::max(s, e));
+      }
+    } else if (feat == "gene") {
+      const std::string id = gff3 ? attr_value(attrs, "ID", true) : attr_value(attrs, "gene_id", false);
+      if (!id.empty()) gene_seen[id] = true;
     } else if (feat == "transcript" || feat == "mRNA" || feat.find("RNA") != std::string::npos || feat == "primary_transcript") {
       std::string id = gff3 ? attr_value(attrs, "ID", true) : attr_value(attrs, "transcript_id", false);
       if (id.empty()) continue;
       Transcript& t = get_tx(id, col[0], strand);
       t.start = std::min(s, e); t.end = std::max(s, e); t.has_line = true;
+      const std::string gene = gff3 ? attr_value(attrs, "Parent", true) : attr_value(attrs, "gene_id", false);
+      t.level = (!gene.empty() && gene_seen.count(gene)) ? 1 : 0;        // updateParent: level of the parent gene + 1
     }
   }
   free(line); fclose(f);

@@ -33,9 +33,7 @@ __global__ void __launch_bounds__(256) k_front(DevIndex ix, DevBatch b, brb_para
                                                uint32_t* __restrict__ ipool, Matches M) {
   if (ctl->bad_input) return;                             // k_validate_batch rejected the CSR offsets: nothing may follow them
   const unsigned lane = threadIdx.x & 31;
-  // alignments per batch: 32, or 8 for long reads (b.back_shift == 3) -- a long read is tens of exon queries and up to hundreds of
-  // candidate walks, and with 32 of them per ticket a bundle of 10^5 reads has fewer batches than the GPU has warps
-  const uint32_t BS = b.back_shift, BA = 1u << BS;
+  constexpr uint32_t BS = 5, BA = 1u << BS;                // alignments per batch (the later exons are flattened over the lanes: full batches pay)
   const uint32_t n_batches = (b.n_aln + BA - 1) >> BS;
   const uint32_t cap_cand = ctl->cap_cand, cap_ideal = ctl->cap_ideal;       // constant during the launch
   WarpPool wp; wp.cur = 0; wp.end = 0;
@@ -59,39 +57,82 @@ __global__ void __launch_bounds__(256) k_front(DevIndex ix, DevBatch b, brb_para
     }
     bool fail[2]; uint32_t ncand[2] = {0, 0}, clo[2] = {0, 0}, chi[2] = {0, 0};
     uint32_t st0 = 0, en0 = 0;                              // exon 0 (kept for pass 2)
-    // ---- pass 1
+    // ---- pass 1a: exon 0 of every alignment, both strands: the candidate lists (all hits enumerated)
+    if (valid && n_ex) {
+      st0 = __ldg(&b.exon_st[e0]); en0 = __ldg(&b.exon_en[e0]);
+      uint32_t pe = en0; if (en0 < st0) bad = 2;
+      for (uint32_t j = 1; j < n_ex; j++) {                 // read exons ascending and disjoint (CIGAR order)
+        const uint32_t qs = __ldg(&b.exon_st[e0 + j]), qe = __ldg(&b.exon_en[e0 + j]);
+        if (qe < qs || qs < pe) bad = 2;
+        pe = qe;
+      }
+    }
 #pragma unroll
     for (int s = 0; s < 2; s++) {
       fail[s] = (n_ex == 0);
-      const uint32_t maxj = __reduce_max_sync(0xffffffffu, (valid && (act[s] || s == 0)) ? n_ex : 0u);
-      uint32_t prev_en = 0;
-      for (uint32_t j = 0; j < maxj; j++) {
-        const bool in = valid && j < n_ex;
-        const bool have = in && act[s] && !fail[s];
-        uint32_t qs = 0, qe = 0, lo = 0, n = 0; int status = 0;
-        if (in && (have || s == 0)) {
-          qs = __ldg(&b.exon_st[e0 + j]); qe = __ldg(&b.exon_en[e0 + j]);
-          if (s == 0) { if (qe < qs || (j > 0 && qs < prev_en)) bad = 2; prev_en = qe; }   // read exons ascending and disjoint (CIGAR order)
-          if (j == 0) { st0 = qs; en0 = qe; }
-        }
-        if (have) {
-          status = exon_status(n_ex, j);
-          uint32_t hi; overlap_range(ix, refid, s, qs, qe, lo, hi); n = hi - lo;
-        }
-        FlatOut f;
-        warp_flat_count(ix, p, s, lane, lo, n, qs, qe, status, f);
-        if (have) {
-          my_hits += f.nhit;
-          if (status == MIDDLE_EXON) q_any[2 * (e0 + j) + s] = f.nf ? 1 : 0;     // only a MIDDLE exon can become an INS_EXON segment
-          if (j == 0) { ncand[s] = f.nf; clo[s] = f.first; chi[s] = f.last; }
-          if (f.nf == 0) {
-            // src/evaluate.cpp:249-281: only a small MIDDLE exon may be skipped (data is non-empty for j>0)
-            const bool small = (qe - qs <= p.max_error_exon);
-            if (!(status == MIDDLE_EXON && p.ignore_small_exons && small)) fail[s] = true;
-          }
-        }
+      const bool have = valid && n_ex && act[s];
+      uint32_t lo = 0, n = 0; const int status = exon_status(n_ex, 0);
+      if (have) { uint32_t hi; overlap_range(ix, refid, s, st0, en0, lo, hi); n = hi - lo; }
+      FlatOut f;
+      warp_flat_count(ix, p, s, lane, lo, n, st0, en0, status, f);
+      if (have) {
+        my_hits += f.nhit;
+        ncand[s] = f.nf; clo[s] = f.first; chi[s] = f.last;
+        if (f.nf == 0) fail[s] = true;                      // exon 0 is FIRST or ONLY: never a skippable small middle exon
       }
       if (fail[s] || !act[s]) ncand[s] = 0;
+    }
+    // ---- pass 1b: the later exons of the strands still alive, as ONE flat list of queries (lane = query): a read of a 300-exon
+    //      gene is 10-20 rounds of 32 queries instead of 300 rounds with one busy lane.  A later exon only has to have A surviving
+    //      hit (else the strand fails, or the exon becomes an INS_EXON segment): unless the caller wants every hit counted
+    //      (b.count_hits: the reference-defined figure for the roofline numerator) only the first PROBE records of a range are
+    //      examined, the rest only for the queries that found nothing there.
+    {
+      constexpr uint32_t PROBE = 32;
+      const uint32_t smask = (valid && n_ex > 1) ? ((act[0] && !fail[0]) ? 1u : 0u) | ((act[1] && !fail[1]) ? 2u : 0u) : 0u;
+      const uint32_t nq = (n_ex > 1 ? n_ex - 1 : 0) * (uint32_t)__popc(smask);
+      const uint32_t incl_q = warp_incl_scan(nq, lane), excl_q = incl_q - nq, total_q = __shfl_sync(0xffffffffu, incl_q, 31);
+      uint32_t failed = 0;                                  // strands of MY alignment that a later exon failed (filled through the ballots below)
+      for (uint32_t base = 0; base < total_q; base += 32) {
+        const uint32_t item = base + lane;
+        const bool actq = item < total_q;
+        const unsigned L = warp_owner(incl_q, actq ? item : total_q - 1);
+        const uint32_t o_ex = __shfl_sync(0xffffffffu, excl_q, L), o_e0 = __shfl_sync(0xffffffffu, e0, L), o_n = __shfl_sync(0xffffffffu, n_ex, L);
+        const uint32_t o_sm = __shfl_sync(0xffffffffu, smask, L); const int32_t o_ref = __shfl_sync(0xffffffffu, refid, L);
+        uint32_t lo = 0, n = 0, qs = 0, qe = 0, j = 0; int s = 0, status = 0;
+        if (actq) {
+          const uint32_t idx = item - o_ex, per = o_n - 1;
+          s = o_sm == 3 ? (int)(idx / per) : (o_sm == 2 ? 1 : 0); j = 1 + idx % per;
+          qs = __ldg(&b.exon_st[o_e0 + j]); qe = __ldg(&b.exon_en[o_e0 + j]);
+          status = exon_status(o_n, j);
+          uint32_t hi; overlap_range(ix, o_ref, s, qs, qe, lo, hi); n = hi - lo;
+        }
+        const uint32_t n1 = b.count_hits ? n : (n < PROBE ? n : PROBE);
+        FlatOut f;
+        warp_flat_count(ix, p, s, lane, lo, n1, qs, qe, status, f);
+        uint32_t nf = f.nf, nhit = f.nhit;
+        const bool more = actq && nf == 0 && n1 < n;
+        if (__any_sync(0xffffffffu, more)) {
+          FlatOut g;
+          warp_flat_count(ix, p, s, lane, lo + n1, more ? n - n1 : 0, qs, qe, status, g);
+          nf += g.nf; nhit += g.nhit;
+        }
+        bool fl = false;
+        if (actq) {
+          my_hits += nhit;
+          if (status == MIDDLE_EXON) q_any[2 * (o_e0 + j) + s] = nf ? 1 : 0;     // only a MIDDLE exon can become an INS_EXON segment
+          // src/evaluate.cpp:249-281: only a small MIDDLE exon may be skipped (data is non-empty for j>0)
+          fl = nf == 0 && !(status == MIDDLE_EXON && p.ignore_small_exons && (qe - qs <= p.max_error_exon));
+        }
+        // tell the owners: for every failing query, its owner lane and strand
+        for (uint32_t F = __ballot_sync(0xffffffffu, fl); F; F &= F - 1) {
+          const int src = __ffs(F) - 1;
+          const unsigned ownerL = __shfl_sync(0xffffffffu, L, src); const int fs = __shfl_sync(0xffffffffu, s, src);
+          if (lane == ownerL) failed |= 1u << fs;
+        }
+      }
+      if (failed & 1u) { fail[0] = true; ncand[0] = 0; }
+      if (failed & 2u) { fail[1] = true; ncand[1] = 0; }
     }
     // ---- candidate slots of the batch
     const uint32_t tot = ncand[0] + ncand[1];

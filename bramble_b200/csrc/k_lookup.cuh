@@ -38,8 +38,10 @@ struct FlatOut { uint32_t nf, first, last, nhit; };   // survivors, first surviv
 
 // Warp-cooperative filtered scan of 32 index ranges, counting pass.  Lane inputs: lo, n (0 = nothing), qs, qe,
 // status; lane outputs: FlatOut of its own range.
+// `minus` is per lane (the strand of the lane's query).
 __device__ __forceinline__ void warp_flat_count(const DevIndex& ix, const brb_params& p, bool minus, unsigned lane,
                                                 uint32_t lo, uint32_t n, uint32_t qs, uint32_t qe, int status, FlatOut& o) {
+  status |= minus ? 4 : 0;
   const uint32_t incl = warp_incl_scan(n, lane), excl = incl - n;
   const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
   o.nf = 0; o.first = 0; o.last = 0; o.nhit = 0;
@@ -49,12 +51,12 @@ __device__ __forceinline__ void warp_flat_count(const DevIndex& ix, const brb_pa
     const unsigned L = warp_owner(incl, act ? item : total - 1);
     const uint32_t o_lo = __shfl_sync(0xffffffffu, lo, L), o_ex = __shfl_sync(0xffffffffu, excl, L);
     const uint32_t o_qs = __shfl_sync(0xffffffffu, qs, L), o_qe = __shfl_sync(0xffffffffu, qe, L);
-    const int o_st = __shfl_sync(0xffffffffu, status, L);
+    const int o_sm = __shfl_sync(0xffffffffu, status, L), o_st = o_sm & 3;
     bool ov = false, sv = false;
     if (act) {
       const RecKey k = rec_key(ix, o_lo + (item - o_ex));
       ov = (int32_t)o_qs < k.en;                           // st < qe holds for every record below hi
-      sv = ov && passes_filter(p, minus, o_st, o_qs, o_qe, (uint32_t)k.st, (uint32_t)k.en);
+      sv = ov && passes_filter(p, (o_sm & 4) != 0, o_st, o_qs, o_qe, (uint32_t)k.st, (uint32_t)k.en);
     }
     const uint32_t B = __ballot_sync(0xffffffffu, sv), H = __ballot_sync(0xffffffffu, ov);
     if (n && incl > base && excl < base + 32) {            // bits of this chunk that belong to MY range

@@ -178,8 +178,9 @@ int brb_batch_download(brb_ctx* ctx, brb_batch_out* out);
 int brb_ctx_stats(const brb_ctx* ctx, brb_stats* out);
 /* Options of a context.  BRB_OPT_GENERIC_FRONT != 0: use the generic lookup/evaluate kernel (every read exon is
  * looked up, as the reference does) even where the short-read kernel (exon 0 only, later exons verified along
- * the transcript's exon chain) applies.  Results are identical; brb_stats.alg_bytes is the reference-defined
- * figure only on the generic path (it counts the index hits of ALL exons). */
+ * the transcript's exon chain) applies -- and, in the long-read modes, count EVERY hit of every read exon (by default a
+ * later exon only has to have a surviving hit and the scan of its range stops there).  Results are identical;
+ * brb_stats.alg_bytes is the reference-defined figure only with this option (it counts the index hits of ALL exons). */
 #define BRB_OPT_GENERIC_FRONT 1
 /* BRB_OPT_NO_FASTPATH != 0: short-read preset without the fast path for perfectly spliced candidates (every surviving
  * candidate goes through the general evaluation).  Results are identical; for tests and A/B timing. */
