@@ -22,6 +22,7 @@
 #include "k_merge.cuh"
 #include "k_flush.cuh"
 #include "k_index.cuh"
+#include "k_deflate.cuh"
 
 using namespace brb;
 
@@ -92,6 +93,7 @@ struct brb_ctx {
   DevBatch b{};
   Buf in_group_off, in_refid, in_strand, in_exon_off, in_exon_st, in_exon_en, in_cigar_off, in_cigar, in_mate, in_seq_off, in_seq, in_name_off, in_names;
   Buf f_hi, f_nh, f_mapq, f_prim;   // BRB_OPT_FLUSH_TAGS results per row
+  Buf z_in, z_slots, z_sizes, z_crcs, z_tot, z_off, z_out, z_ticket; HBuf z_host;   // brb_bgzf_compress
   bool have_names = false, opt_flush_tags = false, result_tags = false;
   uint64_t in_bytes = 0, n_mates = 0, seq_bytes = 0, rescue_bytes = 0;
   bool have_batch = false, have_result = false, have_scores = false, opt_generic_front = false, opt_no_fastpath = false, opt_ordered = false, result_ordered = false, opt_packed = false, result_packed = false, opt_merge_warp = false;
@@ -111,7 +113,7 @@ struct brb_ctx {
   brb_stats stats{};
   std::vector<Buf*> all() {
     return {&in_group_off, &in_refid, &in_strand, &in_exon_off, &in_exon_st, &in_exon_en, &in_cigar_off, &in_cigar, &in_mate, &in_seq_off,
-            &in_seq, &in_name_off, &in_names, &f_hi, &f_nh, &f_mapq, &f_prim, &ctl, &q_any, &a_cand, &scan_tmp, &c_rec, &c_task, &c_first, &c_last, &c_nseg, &c_nguide, &c_cap, &ipool,
+            &in_seq, &in_name_off, &in_names, &f_hi, &f_nh, &f_mapq, &f_prim, &z_in, &z_slots, &z_sizes, &z_crcs, &z_tot, &z_off, &z_out, &z_ticket, &ctl, &q_any, &a_cand, &scan_tmp, &c_rec, &c_task, &c_first, &c_last, &c_nseg, &c_nguide, &c_cap, &ipool,
             &r_left, &r_right, &rpool, &m_rec, &m_sim, &m_clip, &c_stage, &t_agg, &t_claim, &t_off, &p_row, &p_pool, &p_sim, &p_clip, &a_roff, &a_rcnt, &g_roff,
             &o_src, &o_tid, &o_pos, &o_strand, &o_flags, &o_sim, &o_clip, &o_coff, &tpool, &opool};
   }
@@ -290,7 +292,7 @@ int brb_ctx_destroy(brb_ctx* c) {
   if (c->st) cudaStreamSynchronize(c->st);
   for (Buf* b : c->all()) b->release();
   free_rescue_bufs(c);
-  c->h_small.release(); c->h_out.release();
+  c->h_small.release(); c->h_out.release(); c->z_host.release();
   for (auto& e : c->ev) if (e) cudaEventDestroy(e);
   for (auto& e : c->tev) if (e) cudaEventDestroy(e);
   if (c->st) cudaStreamDestroy(c->st);
@@ -694,6 +696,43 @@ int brb_ctx_timer_stop(brb_ctx* c, float* ms) {
 int brb_ctx_stats(const brb_ctx* c, brb_stats* out) {
   if (!c || !out) return fail(BRB_E_ARG, "brb_ctx_stats: null argument");
   *out = c->stats; return BRB_OK;
+}
+
+// ---- BGZF encoder (k_deflate.cuh): n bytes -> complete BGZF blocks (0xff00 input bytes each, the last one shorter), on the ctx stream.
+int brb_bgzf_compress(brb_ctx* c, const uint8_t* data, uint64_t n, const uint8_t** out, uint64_t* out_bytes) {
+  if (!c || !out || !out_bytes || (n && !data)) return fail(BRB_E_ARG, "brb_bgzf_compress: null argument");
+  if (brb_device_count() <= 0) return fail(BRB_E_NO_DEVICE, "no CUDA device");
+  CU(cudaSetDevice(c->idx->device));
+  *out = nullptr; *out_bytes = 0;
+  if (!n) return BRB_OK;
+  const uint64_t nb64 = (n + BGZF_IN - 1) / BGZF_IN;
+  if (nb64 > 0x3fffffffull) return fail(BRB_E_ARG, "brb_bgzf_compress: input too large for one call");
+  const uint32_t nb = (uint32_t)nb64;
+  ENS(c->z_in, n + 16); ENS(c->z_slots, (size_t)nb * BGZF_SLOT); ENS(c->z_sizes, (size_t)nb * 4); ENS(c->z_crcs, (size_t)nb * 4);
+  ENS(c->z_tot, (size_t)nb * 8 + 8); ENS(c->z_off, (size_t)(nb + 1) * 8); ENS(c->z_ticket, 16);
+  ENS(c->scan_tmp, scan_scratch_words(nb) * 8);
+  ENS(c->z_out, n + (size_t)nb * 64 + 64);                       // (a stored block adds 5 + 26 bytes to its input)
+  ENS(c->z_host, n + (size_t)nb * 64 + 64);
+  cudaStream_t st = c->st;
+  CU(cudaMemsetAsync(c->z_in.as<uint8_t>() + (n & ~(uint64_t)3), 0, 16 - (n & 3), st));     // the word loads may read up to 7 bytes past the end
+  CU(cudaMemcpyAsync(c->z_in.p, data, n, cudaMemcpyHostToDevice, st));
+  CU(cudaMemsetAsync(c->z_ticket.p, 0, 16, st));
+  DeflateJob J; J.in = c->z_in.as<uint8_t>(); J.n = n; J.slots = c->z_slots.as<uint8_t>(); J.sizes = c->z_sizes.as<uint32_t>(); J.crcs = c->z_crcs.as<uint32_t>();
+  J.n_blocks = nb; J.ticket = c->z_ticket.as<uint32_t>();
+  const uint32_t ctas = std::min<uint32_t>((nb + DEFLATE_WARPS - 1) / DEFLATE_WARPS, (uint32_t)c->n_sm * 8);
+  uint64_t L = 0;
+  k_bgzf_deflate<<<ctas, 32 * DEFLATE_WARPS, 0, st>>>(J);
+  k_bgzf_sizes<<<grid_for(nb, 256), 256, 0, st>>>(J, c->z_tot.as<unsigned long long>());
+  exclusive_scan(c->z_tot.as<unsigned long long>(), c->z_off.as<unsigned long long>(), nb, c->scan_tmp.as<unsigned long long>(), st, &L);
+  k_bgzf_pack<<<nb, 256, 0, st>>>(J, c->z_off.as<unsigned long long>(), c->z_out.as<uint8_t>());
+  unsigned long long total = 0;
+  CU(cudaMemcpyAsync(&total, c->z_off.as<unsigned long long>() + nb, 8, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(c->z_host.p, c->z_out.p, total, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  *out = c->z_host.as<uint8_t>(); *out_bytes = total;
+  return BRB_OK;
 }
 
 // ---- standalone kernels for the parity tests (host buffers in, host buffers out)

@@ -259,6 +259,12 @@ class Engine:
                                              capi.ptr(out_off), capi.ptr(out_len), capi.ptr(out)), "brb_merge_cigars")
         return [out[int(o):int(o) + int(l)].copy() for o, l in zip(out_off[:-1], out_len)]
 
+    def bgzf_compress(self, data):
+        """bytes -> BGZF blocks (bytes), compressed on the device."""
+        out = C.c_void_p(); n = C.c_uint64()
+        capi.check(self.lib.brb_bgzf_compress(self._ctx, bytes(data), len(data), C.byref(out), C.byref(n)), "brb_bgzf_compress")
+        return C.string_at(out.value, n.value) if n.value else b""
+
     def ksw_extend(self, queries, targets, cigar_cap=256):
         n = len(queries)
         q_off = np.concatenate([[0], np.cumsum([len(q) for q in queries])]).astype(np.uint64)

@@ -219,6 +219,12 @@ int brb_ksw_extend(brb_ctx* ctx, uint32_t n, const uint64_t* q_off, const uint8_
                    const uint8_t* t, int32_t* max, int32_t* score, int32_t* max_q, int32_t* max_t,
                    uint8_t* zdropped, uint32_t cigar_cap, uint32_t* n_cigar, uint32_t* cigar_out);
 
+/* BGZF encoder on the device: `n` bytes in, complete BGZF blocks out (every block covers 0xff00 input bytes, the last one
+ * what is left; no EOF marker block) -- what htslib's bgzf_write + deflate do behind the reference's sam_write1
+ * (gclib/GSam.h:553,642-645).  LZ77 + fixed Huffman codes per block, CRC-32 and ISIZE filled in; any inflater reads it.
+ * `*out` points into pinned memory owned by the ctx, valid until the next call on it. */
+int brb_bgzf_compress(brb_ctx* ctx, const uint8_t* data, uint64_t n, const uint8_t** out, uint64_t* out_bytes);
+
 /* ---- host-side helpers (no device work) ---- */
 /* Permutation cgranges' IITree::index() applies to one tree: libstdc++ std::sort (unstable) by start
  * only, on the reference's insertion sequence (src/g2t.cpp:57-62).  perm[k] = input index of sorted record k. */

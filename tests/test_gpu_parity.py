@@ -381,3 +381,43 @@ def test_flush_tags_on_device_match_libstdcxx(kind):
         with pytest.raises(capi.EngineError):
             eng.project(p, b)
     assert int((tags["nh"] > 1).sum()) > 1000 and 0 < int(tags["primary"].sum()) < len(tags["primary"])
+
+
+def _bgzf_blocks(buf):
+    """[(payload, crc, isize)] of a BGZF byte string; checks the fixed header fields."""
+    import struct
+    out, p = [], 0
+    while p < len(buf):
+        assert buf[p:p + 4] == b"\x1f\x8b\x08\x04" and buf[p + 10:p + 16] == b"\x06\x00BC\x02\x00", p
+        bsize = struct.unpack_from("<H", buf, p + 16)[0] + 1
+        crc, isize = struct.unpack_from("<II", buf, p + bsize - 8)
+        out.append((buf[p + 18:p + bsize - 8], crc, isize))
+        p += bsize
+    assert p == len(buf)
+    return out
+
+
+def test_bgzf_device_encoder_round_trips():
+    """brb_bgzf_compress (LZ77 + fixed Huffman + CRC-32 on the device): every block inflates (zlib) to its 0xff00-byte share of the
+    input, CRC32 and ISIZE are right, blocks stay within 64 KiB -- on incompressible, repetitive and BAM-shaped input."""
+    import zlib
+    from bramble_b200 import synth
+    wl = common.make_workload("default", 131, n_names=400)
+    rng = np.random.default_rng(9)
+    bam = b"".join(synth._pack_record(r) for r in wl["recs"] if not r["flag"] & 4)
+    cases = [b"", b"A", bytes(rng.integers(0, 256, size=200000, dtype=np.uint8)), b"ACGTTGCAAC" * 30000, bam, bam[:0xff00], bam[:0xff00 + 1],
+             bytes(rng.integers(0, 4, size=150000, dtype=np.uint8)), (bam[:5000] * 40)[:0xff00 * 3 - 7]]
+    with engine.Engine(wl["index"]) as eng:
+        for k, data in enumerate(cases):
+            z = eng.bgzf_compress(data)
+            blocks = _bgzf_blocks(z)
+            assert len(blocks) == (len(data) + 0xff00 - 1) // 0xff00, k
+            got = b""
+            for payload, crc, isize in blocks:
+                assert len(payload) + 26 <= 65536
+                raw = zlib.decompress(payload, -15)
+                assert len(raw) == isize and (zlib.crc32(raw) & 0xffffffff) == crc, k
+                got += raw
+            assert got == data, k
+            if k in (3, 4):
+                assert len(z) < len(data) // 2, (k, len(z), len(data))          # repeats are found
