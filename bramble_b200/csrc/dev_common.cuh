@@ -201,6 +201,20 @@ __device__ __forceinline__ void overlap_range(const DevIndex& ix, int32_t refid,
   hi = l; lo = l2 < hi ? l2 : hi;
 }
 
+// First record of table t (refid, strand) whose start is >= x, through the bin directory (the `hi` half of overlap_range).
+__device__ __forceinline__ uint32_t st_lower_bound(const DevIndex& ix, int32_t refid, bool minus, uint32_t x) {
+  if (refid < 0 || (uint32_t)refid * 2u + 1u >= ix.n_tables) return 0;
+  const uint32_t t = (uint32_t)refid * 2u + (minus ? 1u : 0u);
+  const uint32_t bo = __ldg(&ix.bin_off[t]), nb = __ldg(&ix.bin_off[t + 1]) - bo;
+  if (nb < 2) return 0;
+  uint32_t b1 = x >> ix.bin_shift;
+  if (b1 > nb - 2) b1 = nb - 2;
+  const uint2 B0 = __ldg(&ix.bins[bo + b1]), B1 = __ldg(&ix.bins[bo + b1 + 1]);
+  uint32_t l = B0.y, n = B1.y - B0.y;
+  while (n > 0) { const uint32_t h = n >> 1; if (__ldg(&ix.st[l + h]) < (int32_t)x) { l += h + 1; n -= h + 1; } else n = h; }
+  return l;
+}
+
 // ---- warp helpers
 __device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, unsigned lane) {
 #pragma unroll

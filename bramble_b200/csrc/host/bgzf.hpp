@@ -157,6 +157,11 @@ class BgzfWriter {
     }
   }
   void flush_block() { if (!cur_.empty()) submit(); }   // htslib flushes after the header
+  // ready-made BGZF blocks (compressed elsewhere: the engine's device encoder), appended after everything written so far
+  void write_raw(const void* src, size_t n) {
+    flush_block(); drain(true);
+    if (n && fwrite(src, 1, n, f_) != n) fail("short write");
+  }
   void close() {
     if (!f_) return;
     flush_block();

@@ -298,22 +298,62 @@ int main(int argc, char** argv) {
       for (auto& t : A.tx) if (t.tlen > 0) { int32_t l = (int32_t)t.id.size() + 1; put(&l, 4); put(t.id.c_str(), l); uint32_t ln = t.tlen; put(&ln, 4); }
       out.write(hb.data(), hb.size()); out.flush_block(); }
 
-    // pipeline: producer (this thread) -> per-GPU worker -> ordered assembler/writer
+    // pipeline: producer (this thread: record walk + bundle cut) -> column extraction (pool) -> per-GPU worker -> flush replay +
+    // record assembly (pool) -> ordered writer (BGZF blocks compressed on the device, or by the host pool)
     const bool timing = getenv("BRB_CLI_TIMING") != nullptr;      // stage seconds on stderr at the end
     using clk = std::chrono::steady_clock;
     auto secs = [](clk::time_point a, clk::time_point b) { return std::chrono::duration<double>(b - a).count(); };
-    double t_read = 0, t_ingest = 0, t_wait_push = 0, t_project = 0, t_store = 0, t_assemble = 0, t_write = 0;
+    double t_read = 0, t_ingest = 0, t_wait_push = 0, t_project = 0, t_store = 0, t_assemble = 0, t_write = 0, t_extract = 0;
     const auto t_begin = clk::now();
     Stats st; std::mutex m; std::condition_variable cv;
+    std::deque<std::shared_ptr<Bundle>> to_ingest;            // cut by the producer, waiting for their columns
     std::vector<std::deque<std::shared_ptr<Bundle>>> todo(n_gpu); std::deque<std::shared_ptr<Bundle>> inflight; bool eof = false; std::string err;
     std::deque<std::shared_ptr<Bundle>> to_assemble;          // projected, waiting for flush replay + record assembly
+    uint64_t n_cut = 0, n_ingested = 0;
     int workers_left = n_gpu;
     const int n_asm = std::max(1, o.threads);
+    const bool dev_deflate = getenv("BRB_HOST_DEFLATE") == nullptr;      // BGZF blocks of the output are compressed by the engine when it can
+    // ingest of one bundle (reference process_reads, src/bramble.cpp:329-435, per record): read exons, CIGAR words, strand,
+    // annotated chromosome, mate links (process_pairs :272-311), group names and -- with -S -- the group-shared sequence
+    auto ingest_bundle = [&](Bundle& b) -> std::string {
+      const uint32_t n = (uint32_t)b.rec_off.size();
+      std::unordered_map<std::string, uint32_t> hashread;
+      b.exon_off.assign(1, 0); b.cigar_off.assign(1, 0); b.seq_off.assign(1, 0); b.name_off.assign(1, 0);
+      b.refid.reserve(n); b.mate.assign(n, -1); b.strand.reserve(n);
+      for (uint32_t a = 0; a < n; a++) {
+        const RecView w = b.view(a);
+        if (!read_exons(w, b.exon_st, b.exon_en)) return std::string("Error: invalid CIGAR record for ") + w.name() + " !";
+        b.exon_off.push_back((uint32_t)b.exon_st.size());
+        for (uint32_t i = 0; i < w.n_cigar(); i++) b.cigar.push_back(rd32(w.cigar() + 4 * i));
+        b.cigar_off.push_back((uint32_t)b.cigar.size());
+        b.strand.push_back(lng ? '.' : get_strand(w, o.fr, o.rf));
+        const int32_t t = w.tid(); b.refid.push_back(t >= 0 && (size_t)t < ref2refid.size() ? ref2refid[t] : -1);
+        if ((w.flag() & 1) && w.tid() == w.mtid()) {          // process_pairs, src/bramble.cpp:272-311
+          const int32_t start = w.pos() + 1, mate_start = w.mpos() < 0 ? 0 : w.mpos() + 1;
+          const std::string name = w.name();
+          auto it = hashread.find(name + '-' + std::to_string(mate_start));
+          if (it != hashread.end()) { const uint32_t mt = it->second; if (b.mate[a] < 0) b.mate[a] = (int32_t)mt; if (b.mate[mt] < 0) b.mate[mt] = (int32_t)a; hashread.erase(it); }
+          else hashread[name + '-' + std::to_string(start)] = a;
+        }
+      }
+      static const char nt16[] = "=ACMGRSVTWYHKDBN";
+      for (size_t g = 0; g + 1 < b.group_off.size(); g++) {
+        if (params.use_fasta) {                              // group-shared sequence = first record of the group with l_qseq > 0 (src/core.cpp:353-378)
+          for (uint32_t a = b.group_off[g]; a < b.group_off[g + 1]; a++) {
+            const RecView v = b.view(a); const int32_t lq = v.l_seq();
+            if (lq > 0) { const uint8_t* sq = v.seq(); for (int32_t i = 0; i < lq; i++) { const char c = nt16[(sq[i >> 1] >> ((~i & 1) << 2)) & 0xf]; b.seq.push_back(c == 'A' ? 0 : c == 'C' ? 1 : c == 'G' ? 2 : c == 'T' ? 3 : 4); } break; }
+          }
+          b.seq_off.push_back(b.seq.size());
+        }
+        const RecView v = b.view(b.group_off[g]); const char* nm = v.name(); b.names.insert(b.names.end(), nm, nm + strlen(nm)); b.name_off.push_back(b.names.size());
+      }
+      return std::string();
+    };
     auto worker = [&](int g) {
       for (;;) {
         std::shared_ptr<Bundle> b;
-        { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return eof || !todo[g].empty() || !err.empty(); });
-          if (!err.empty() || (todo[g].empty() && eof)) { workers_left--; cv.notify_all(); return; }
+        { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return (eof && n_ingested == n_cut) || !todo[g].empty() || !err.empty(); });
+          if (!err.empty() || (todo[g].empty() && eof && n_ingested == n_cut)) { workers_left--; cv.notify_all(); return; }
           if (todo[g].empty()) continue;
           b = todo[g].front(); todo[g].pop_front(); }
         brb_batch_in bi{}; fill_batch(*b, params.use_fasta, bi); brb_batch_out bo{};
@@ -328,16 +368,25 @@ int main(int argc, char** argv) {
         to_assemble.push_back(b); cv.notify_all();
       }
     };
-    // flush replay + record assembly of whole bundles on `-p` threads (bundles are independent: a read name never
-    // spans two of them); the writer below keeps the bundle order
+    // pool threads: column extraction of freshly cut bundles, and flush replay + record assembly of projected ones (bundles are
+    // independent: a read name never spans two of them); the writer below keeps the bundle order
     auto assembler = [&]() {
       for (;;) {
-        std::shared_ptr<Bundle> b;
-        { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return !err.empty() || !to_assemble.empty() || workers_left == 0; });
+        std::shared_ptr<Bundle> b; bool do_ingest = false;
+        { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return !err.empty() || !to_assemble.empty() || !to_ingest.empty() || workers_left == 0; });
           if (!err.empty()) return;
-          if (to_assemble.empty()) { if (workers_left == 0) return; continue; }
-          b = to_assemble.front(); to_assemble.pop_front(); }
+          if (!to_assemble.empty()) { b = to_assemble.front(); to_assemble.pop_front(); }
+          else if (!to_ingest.empty()) { b = to_ingest.front(); to_ingest.pop_front(); do_ingest = true; }
+          else { if (workers_left == 0) return; continue; } }
         const auto t0 = clk::now();
+        if (do_ingest) {
+          const std::string e = ingest_bundle(*b);
+          std::unique_lock<std::mutex> lk(m);
+          t_extract += secs(t0, clk::now());
+          if (!e.empty()) { if (err.empty()) err = e; cv.notify_all(); return; }
+          todo[b->index % n_gpu].push_back(b); n_ingested++; cv.notify_all();
+          continue;
+        }
         Stats bs; assemble_bundle(*b, lng, bs, b->out);
         b->dropped = bs.dropped; b->total_complete = bs.total_complete; b->total_unique = bs.total_unique;
         b->raw.clear(); b->raw.shrink_to_fit();
@@ -352,7 +401,11 @@ int main(int argc, char** argv) {
         { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return !err.empty() || (!inflight.empty() && inflight.front()->assembled) || (eof && inflight.empty()); });
           if (!err.empty()) return; if (inflight.empty()) return; b = inflight.front(); inflight.pop_front(); cv.notify_all(); }
         const auto t1 = clk::now();
-        out.write(b->out.data(), b->out.size());
+        try {
+          const uint8_t* z = nullptr; size_t zn = 0;
+          if (dev_deflate && !b->out.empty() && engines[b->index % n_gpu]->bgzf_compress(b->out.data(), b->out.size(), z, zn)) out.write_raw(z, zn);
+          else out.write(b->out.data(), b->out.size());
+        } catch (const std::exception& e) { std::unique_lock<std::mutex> lk(m); if (err.empty()) err = e.what(); cv.notify_all(); return; }
         st.dropped += b->dropped; st.total_complete += b->total_complete; st.total_unique += b->total_unique;
         t_write += secs(t1, clk::now());
       }
@@ -362,30 +415,18 @@ int main(int argc, char** argv) {
     std::thread wthread(writer);
 
     auto bundle = std::make_shared<Bundle>(); uint64_t n_bundles = 0;
-    std::unordered_map<std::string, uint32_t> hashread; std::string prev_name; std::vector<std::string> names;
-    auto new_bundle = [&]() { auto b = std::make_shared<Bundle>(); b->group_off.push_back(0); b->exon_off.push_back(0); b->cigar_off.push_back(0); b->seq_off.push_back(0); return b; };
+    std::string prev_name;
+    auto new_bundle = [&]() { auto b = std::make_shared<Bundle>(); b->group_off.push_back(0); return b; };
     bundle = new_bundle();
     auto push_bundle = [&]() {
-      if (bundle->n_aln() == 0) return;
-      Bundle& b = *bundle; b.group_off.push_back(b.n_aln());
-      if (params.use_fasta) {                                // group-shared sequence = first record of the group with l_qseq > 0 (src/core.cpp:353-378)
-        static const char nt16[] = "=ACMGRSVTWYHKDBN";
-        for (size_t g = 0; g + 1 < b.group_off.size(); g++) {
-          for (uint32_t a = b.group_off[g]; a < b.group_off[g + 1]; a++) {
-            const RecView v = b.view(a); const int32_t lq = v.l_seq();
-            if (lq > 0) { const uint8_t* s = v.seq(); for (int32_t i = 0; i < lq; i++) { const char c = nt16[(s[i >> 1] >> ((~i & 1) << 2)) & 0xf]; b.seq.push_back(c == 'A' ? 0 : c == 'C' ? 1 : c == 'G' ? 2 : c == 'T' ? 3 : 4); } break; }
-          }
-          b.seq_off.push_back(b.seq.size());
-        }
-      }
-      b.name_off.assign(1, 0);
-      for (size_t g = 0; g + 1 < b.group_off.size(); g++) { const RecView v = b.view(b.group_off[g]); const char* nm = v.name(); b.names.insert(b.names.end(), nm, nm + strlen(nm)); b.name_off.push_back(b.names.size()); }
+      if (bundle->rec_off.empty()) return;
+      Bundle& b = *bundle; b.group_off.push_back((uint32_t)b.rec_off.size());
       b.index = n_bundles++;
       const auto tw = clk::now();
-      { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return inflight.size() < (size_t)(2 * n_gpu + 2 + n_asm) || !err.empty(); }); todo[b.index % n_gpu].push_back(bundle); inflight.push_back(bundle); }
+      { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return inflight.size() < (size_t)(2 * n_gpu + 2 + n_asm) || !err.empty(); }); to_ingest.push_back(bundle); inflight.push_back(bundle); n_cut++; }
       cv.notify_all();
       t_wait_push += secs(tw, clk::now());
-      bundle = new_bundle(); hashread.clear();
+      bundle = new_bundle();
     };
     std::vector<uint8_t> rec;
     std::string producer_err;
@@ -401,29 +442,14 @@ int main(int argc, char** argv) {
       st.total_reads++;
       const RecView v{rec.data(), (uint32_t)bs};
       if (v.flag() & 4) { st.unmapped++; continue; }
-      const std::string name = v.name();
-      const uint32_t id = bundle->n_aln();
-      const bool new_name = (id == 0) || name != prev_name;
+      const char* name = v.name();
+      const uint32_t id = (uint32_t)bundle->rec_off.size();
+      const bool new_name = (id == 0) || prev_name != name;
       if (id >= o.chunk && new_name) push_bundle();
-      Bundle& b = *bundle; const uint32_t a = b.n_aln();
+      Bundle& b = *bundle; const uint32_t a = (uint32_t)b.rec_off.size();
       if (a > 0 && new_name) b.group_off.push_back(a);
       b.rec_off.push_back(b.raw.size()); b.rec_len.push_back((uint32_t)bs); b.raw.insert(b.raw.end(), rec.begin(), rec.end());
-      const RecView w = b.view(a);
-      if (!read_exons(w, b.exon_st, b.exon_en)) { fprintf(stderr, "Error: invalid CIGAR record for %s !\n", w.name()); exit(1); }
-      b.exon_off.push_back((uint32_t)b.exon_st.size());
-      for (uint32_t i = 0; i < w.n_cigar(); i++) b.cigar.push_back(rd32(w.cigar() + 4 * i));
-      b.cigar_off.push_back((uint32_t)b.cigar.size());
-      b.strand.push_back(lng ? '.' : get_strand(w, o.fr, o.rf));
-      const int32_t t = w.tid(); b.refid.push_back(t >= 0 && (size_t)t < ref2refid.size() ? ref2refid[t] : -1);
-      b.mate.push_back(-1);
-      if ((w.flag() & 1) && w.tid() == w.mtid()) {          // process_pairs, src/bramble.cpp:272-311
-        const int32_t start = w.pos() + 1, mate_start = w.mpos() < 0 ? 0 : w.mpos() + 1;
-        const std::string mate_key = name + '-' + std::to_string(mate_start);
-        auto it = hashread.find(mate_key);
-        if (it != hashread.end()) { const uint32_t mt = it->second; if (b.mate[a] < 0) b.mate[a] = (int32_t)mt; if (b.mate[mt] < 0) b.mate[mt] = (int32_t)a; hashread.erase(it); }
-        else hashread[name + '-' + std::to_string(start)] = a;
-      }
-      prev_name = name;
+      if (new_name) prev_name = name;
     }
     push_bundle();
     } catch (const std::exception& e) { producer_err = e.what(); }        // (truncated record, inflate / CRC error): report it after the threads are joined
@@ -431,15 +457,15 @@ int main(int argc, char** argv) {
     { std::unique_lock<std::mutex> lk(m); eof = true; if (!producer_err.empty() && err.empty()) err = producer_err; } cv.notify_all();
     for (auto& t : threads) t.join();
     wthread.join();
-    if (!err.empty()) { fprintf(stderr, "error: %s\n", err.c_str()); return 1; }
+    if (!err.empty()) { fprintf(stderr, err.compare(0, 6, "Error:") == 0 ? "%s\n" : "error: %s\n", err.c_str()); return 1; }
     const auto t_joined = clk::now();
     out.close();
     if (timing) {
       const double total = secs(t_begin, clk::now());
       t_ingest = secs(t_begin, t_loop_end) - t_read - t_wait_push;
-      fprintf(stderr, "[timing] pipeline %.3fs: producer read+inflate %.3f, ingest %.3f, blocked on queue %.3f | engine project %.3f, copy-out %.3f | "
-                      "writer assemble %.3f, BGZF write %.3f | final drain %.3f\n",
-              total, t_read, t_ingest, t_wait_push, t_project, t_store, t_assemble, t_write, secs(t_joined, clk::now()));
+      fprintf(stderr, "[timing] pipeline %.3fs: producer read+inflate %.3f, record walk %.3f, blocked on queue %.3f | pool: column extraction %.3f, "
+                      "flush replay + assembly %.3f | engine project %.3f, copy-out %.3f | writer (BGZF %s) %.3f | final drain %.3f\n",
+              total, t_read, t_ingest, t_wait_push, t_extract, t_assemble, t_project, t_store, dev_deflate ? "on the device" : "host pool", t_write, secs(t_joined, clk::now()));
     }
     if (!o.quiet) {
       printf("\n[bramble_b200] final report:\n# input alignments:   %llu\n# unmapped reads:     %llu\n# dropped alignments: %llu\n# total alignments:   %llu\n# unique alignments:  %llu\n\n",

@@ -5,8 +5,8 @@
 namespace brbhost {
 namespace {
 struct CudaEngine : EngineIf {
-  brb_index* ix = nullptr; brb_ctx* ctx = nullptr;
-  ~CudaEngine() override { if (ctx) brb_ctx_destroy(ctx); if (ix) brb_index_destroy(ix); }
+  brb_index* ix = nullptr; brb_ctx* ctx = nullptr; brb_ctx* zctx = nullptr;       // zctx: the writer thread's context (own stream) for the BGZF encoder
+  ~CudaEngine() override { if (zctx) brb_ctx_destroy(zctx); if (ctx) brb_ctx_destroy(ctx); if (ix) brb_index_destroy(ix); }
   void open(int device, const brb_index_desc& desc) override {
     if (brb_device_count() <= device) throw std::runtime_error("no CUDA device " + std::to_string(device) + " (bramble_b200 has no CPU path)");
     if (brb_index_create(device, &desc, &ix) != BRB_OK) throw std::runtime_error(std::string("brb_index_create: ") + brb_last_error());
@@ -15,6 +15,13 @@ struct CudaEngine : EngineIf {
   }
   int project(const brb_params& p, const brb_batch_in& in, brb_batch_out& out) override { return brb_project(ctx, &p, &in, &out); }
   std::string last_error() override { return brb_last_error(); }
+  bool bgzf_compress(const uint8_t* data, size_t n, const uint8_t*& out, size_t& out_n) override {
+    if (!zctx && brb_ctx_create(ix, &zctx) != BRB_OK) throw std::runtime_error(std::string("brb_ctx_create: ") + brb_last_error());
+    uint64_t zn = 0;
+    if (brb_bgzf_compress(zctx, data, n, &out, &zn) != BRB_OK) throw std::runtime_error(std::string("brb_bgzf_compress: ") + brb_last_error());
+    out_n = (size_t)zn;
+    return true;
+  }
 };
 }  // namespace
 EngineIf* make_engine() { return new CudaEngine(); }

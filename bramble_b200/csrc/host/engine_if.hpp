@@ -12,6 +12,9 @@ struct EngineIf {
   virtual void open(int device, const brb_index_desc& desc) = 0;                 // throws std::runtime_error
   virtual int project(const brb_params& p, const brb_batch_in& in, brb_batch_out& out) = 0;   // out valid until the next call
   virtual std::string last_error() = 0;
+  // BGZF blocks of `n` bytes, compressed by the engine (callable from another thread than project()); false: not available,
+  // the caller compresses on the host.  `out` stays valid until the next call.
+  virtual bool bgzf_compress(const uint8_t*, size_t, const uint8_t*&, size_t&) { return false; }
 };
 EngineIf* make_engine();
 }  // namespace brbhost

@@ -106,6 +106,13 @@ __global__ void __launch_bounds__(256) k_front(DevIndex ix, DevBatch b, brb_para
           qs = __ldg(&b.exon_st[o_e0 + j]); qe = __ldg(&b.exon_en[o_e0 + j]);
           status = exon_status(o_n, j);
           uint32_t hi; overlap_range(ix, o_ref, s, qs, qe, lo, hi); n = hi - lo;
+          // a later exon (MIDDLE or LAST) only accepts guide exons that START within the junction tolerances of its own start
+          // (src/g2t.cpp:156-190): in a gene with hundreds of isoforms the overlap range is hundreds of records, that window a few
+          if (!b.count_hits && n > PROBE) {
+            const uint32_t w0 = st_lower_bound(ix, o_ref, s, qs > p.max_junc_gap ? qs - p.max_junc_gap : 0u), w1 = st_lower_bound(ix, o_ref, s, qs + p.max_junc_ins + 1);
+            const uint32_t a0 = w0 > lo ? w0 : lo, a1 = w1 < hi ? w1 : hi;
+            lo = a0; n = a1 > a0 ? a1 - a0 : 0;
+          }
         }
         const uint32_t n1 = b.count_hits ? n : (n < PROBE ? n : PROBE);
         FlatOut f;

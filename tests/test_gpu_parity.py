@@ -419,5 +419,5 @@ def test_bgzf_device_encoder_round_trips():
                 assert len(raw) == isize and (zlib.crc32(raw) & 0xffffffff) == crc, k
                 got += raw
             assert got == data, k
-            if k in (3, 4):
-                assert len(z) < len(data) // 2, (k, len(z), len(data))          # repeats are found
+            if k in (3, 8):
+                assert len(z) < len(data) // 4, (k, len(z), len(data))          # repeats are found (the BAM case has random bases and qualities)
