@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(32 * DEFLATE_WARPS) k_bgzf_deflate(DeflateJob 
       __syncwarp();
       if (can) tab[h] = (uint16_t)p;
       __syncwarp();
-      if (cand != 0xffff && cand < p) {
+      if (cand != 0xffff && cand < p && p - cand <= 32768u) {          // (deflate distances end at 32 KiB; the block is up to 0xff00 bytes)
         uint32_t l = 0; const uint32_t maxl = n - p < 258u ? n - p : 258u;
         while (l + 4 <= maxl) { const uint32_t x = load_u32_at(inw, cand + l) ^ load_u32_at(inw, p + l); if (x) { l += (__ffs(x) - 1) >> 3; break; } l += 4; }
         if (l + 4 > maxl) while (l < maxl && in[cand + l] == in[p + l]) l++;     // (tail, or the word loop stopped short of a difference)

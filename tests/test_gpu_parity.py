@@ -406,7 +406,8 @@ def test_bgzf_device_encoder_round_trips():
     rng = np.random.default_rng(9)
     bam = b"".join(synth._pack_record(r) for r in wl["recs"] if not r["flag"] & 4)
     cases = [b"", b"A", bytes(rng.integers(0, 256, size=200000, dtype=np.uint8)), b"ACGTTGCAAC" * 30000, bam, bam[:0xff00], bam[:0xff00 + 1],
-             bytes(rng.integers(0, 4, size=150000, dtype=np.uint8)), (bam[:5000] * 40)[:0xff00 * 3 - 7]]
+             bytes(rng.integers(0, 4, size=150000, dtype=np.uint8)), (bam[:5000] * 40)[:0xff00 * 3 - 7],
+             (bytes(rng.integers(0, 256, size=40000, dtype=np.uint8)) * 4)[:0xff00 * 2]]      # repeats 40 000 bytes apart: beyond deflate's 32 KiB window
     with engine.Engine(wl["index"]) as eng:
         for k, data in enumerate(cases):
             z = eng.bgzf_compress(data)
