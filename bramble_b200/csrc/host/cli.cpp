@@ -19,6 +19,7 @@
 #include <optional>
 #include <random>
 #include <string>
+#include <string_view>
 #include <thread>
 #include <unordered_map>
 #include <unordered_set>
@@ -162,7 +163,10 @@ struct Bundle {
   // result (copied out of the engine's staging)
   std::vector<uint32_t> a_roff, a_rcnt, src, tid, pos, coff, cig; std::vector<int8_t> tstrand; std::vector<uint8_t> flags; std::vector<double> sim; std::vector<int32_t> clip;
   // assembled output records of the bundle (uncompressed BAM bytes) and its share of the final report
-  std::vector<uint8_t> out; uint64_t dropped = 0, total_complete = 0, total_unique = 0; bool assembled = false;
+  // flush chunks of the bundle (reference CHUNK_SIZE = 5000 pairs, src/core.cpp:27,421-423): group ranges, and the output records
+  // of each chunk (uncompressed BAM bytes), assembled independently of one another
+  std::vector<std::pair<uint32_t, uint32_t>> chunks; std::vector<size_t> chunk_buckets; std::vector<std::vector<uint8_t>> parts; uint32_t parts_left = 0;
+  uint64_t dropped = 0, total_complete = 0, total_unique = 0; bool assembled = false;
   RecView view(uint32_t a) const { return RecView{raw.data() + rec_off[a], rec_len[a]}; }
   uint32_t n_aln() const { return (uint32_t)refid.size(); }
 };
@@ -196,58 +200,37 @@ int32_t get_rand(uint32_t x, uint64_t seed_key) {          // src/core.cpp:214-2
   std::mt19937_64 gen(seed_key); std::uniform_int_distribution<uint32_t> dis(0, x - 1); return dis(gen);
 }
 
-// flush() + write_to_bam of the reference for one bundle's rows.
-void assemble_bundle(const Bundle& b, bool lng, Stats& st, std::vector<uint8_t>& out) {
+// The flush chunks of a bundle: the reference appends a group's pairs and flushes once 5000 or more have accumulated, checking only at
+// the end of a group (src/core.cpp:384-423); the last chunk is whatever is left.
+// The records of a chunk leave in the iteration order of the reference's name -> pairs map, ONE map per bundle that is clear()ed
+// after each flush (src/core.cpp:234,330): clear() keeps the bucket array, so the order inside chunk k depends on how far the
+// earlier chunks grew it.  A stand-in map with the same key sequence is run here to record the bucket count each chunk starts
+// from; the chunks are then assembled independently, each in a map rehash()ed to that count.
+void plan_chunks(Bundle& b) {
+  const uint32_t G = (uint32_t)b.group_off.size() - 1;
+  uint32_t n_pairs = 0, g0 = 0;
+  b.chunks.clear(); b.chunk_buckets.clear();
+  std::unordered_map<std::string_view, char> names;
+  size_t buckets = names.bucket_count();
+  for (uint32_t g = 0; g < G; g++) {
+    bool any = false;
+    for (uint32_t a = b.group_off[g]; a < b.group_off[g + 1]; a++)
+      for (uint32_t r = b.a_roff[a], hi = r + b.a_rcnt[a]; r < hi;) {
+        if (!any) names.try_emplace(std::string_view(b.view(b.src[r]).name()), 0);       // one name per group
+        any = true; n_pairs++; r += (b.flags[r] & BRB_REC_PAIRED) ? 2 : 1;
+      }
+    if (n_pairs >= 5000) { b.chunks.emplace_back(g0, g + 1); b.chunk_buckets.push_back(buckets); g0 = g + 1; n_pairs = 0; names.clear(); buckets = names.bucket_count(); }
+  }
+  if (g0 < G) { b.chunks.emplace_back(g0, G); b.chunk_buckets.push_back(buckets); }
+}
+
+// flush() + write_to_bam of the reference for the groups [g0, g1) of a bundle (one flush chunk).
+void assemble_chunk(const Bundle& b, uint32_t g0, uint32_t g1, size_t start_buckets, bool lng, Stats& st, std::vector<uint8_t>& out) {
   struct Unit { uint32_t row; bool paired; uint32_t group; int32_t hi_r = 0, hi_m = 0; bool primary = false; uint32_t nh = 0, mapq = 0; };
   std::unordered_map<std::string, std::vector<Unit>> pairs_by_name;
-  uint32_t n_pairs = 0; std::vector<uint8_t> aux;
-  auto flush = [&]() {
-    std::vector<Unit*> filtered;
-    for (auto& [read_name, pairs] : pairs_by_name) {
-      // HI / NH / MAPQ / primary: from the device when the engine computed them (brb_batch_out::hi ...) -- unless the name came in as
-      // more than one group inside this chunk (input not name-collated) or the device left the tie to us (primary == 2)
-      bool from_device = b.have_tags;
-      for (size_t i = 0; from_device && i < pairs.size(); i++) if (pairs[i].group != pairs[0].group || b.prim[pairs[i].row] == 2) from_device = false;
-      if (from_device) {
-        const int total = b.nh[pairs[0].row];
-        for (auto& u : pairs) { u.hi_r = b.hi[u.row]; if (u.paired) u.hi_m = b.hi[u.row + 1]; u.primary = b.prim[u.row] == 1; u.nh = (uint32_t)total; u.mapq = b.mapq[u.row]; filtered.push_back(&u); }
-        st.total_complete += total; if (total == 1) st.total_unique++;
-        continue;
-      }
-      double best_score = -std::numeric_limits<double>::infinity(); int count_at_best = 0; size_t best = pairs.size(); int32_t hit_index = 1; int total = 0;
-      auto score_of = [&](const Unit& u) { double s = b.sim[u.row]; if (u.paired) s = std::max(s, b.sim[u.row + 1]); return s; };
-      for (size_t i = 0; i < pairs.size(); i++) {
-        Unit& u = pairs[i]; u.hi_r = hit_index++; total++;
-        if (u.paired) { u.hi_m = hit_index++; total++; }
-        const double ps = score_of(u);
-        if (ps > best_score) { best_score = ps; best = i; count_at_best = 1; } else if (ps == best_score) count_at_best++;
-      }
-      if (best != pairs.size()) {
-        if (count_at_best == 1) pairs[best].primary = true;
-        else {
-          std::vector<size_t> tied;
-          for (size_t i = 0; i < pairs.size(); i++) if (score_of(pairs[i]) == best_score) tied.push_back(i);
-          const uint64_t seed_key = std::hash<std::string>{}(read_name);
-          pairs[tied[get_rand((uint32_t)tied.size(), seed_key)]].primary = true;
-        }
-      }
-      st.total_complete += total; if (total == 1) st.total_unique++;
-      for (auto& u : pairs) { u.nh = (uint32_t)total; u.mapq = get_mapq((uint32_t)total, lng); filtered.push_back(&u); }
-    }
-    for (Unit* u : filtered) {
-      for (int k = 0; k < (u->paired ? 2 : 1); k++) {
-        const uint32_t r = u->row + k, other = u->row + (1 - k);
-        OutInfo o{}; o.tid = b.tid[r]; o.pos = b.pos[r]; o.strand = (char)b.tstrand[r]; o.paired = u->paired; o.same_tx = b.flags[r] & BRB_REC_SAMETX;
-        o.primary = u->primary; o.long_reads = lng; o.mapq = u->mapq; o.nh = (int32_t)u->nh; o.hi = k == 0 ? u->hi_r : u->hi_m;
-        o.sim = b.sim[r]; o.clip = b.clip[r]; o.cigar = b.cig.data() + b.coff[r]; o.n_cigar = b.coff[r + 1] - b.coff[r];
-        if (u->paired) { o.mate_tid = b.tid[other]; o.mate_pos = b.pos[other]; }
-        assemble_record(b.view(b.src[r]), o, aux, out);
-      }
-    }
-    pairs_by_name.clear(); n_pairs = 0;
-  };
-  const uint32_t G = (uint32_t)b.group_off.size() - 1;
-  for (uint32_t g = 0; g < G; g++) {
+  if (start_buckets != pairs_by_name.bucket_count()) pairs_by_name.rehash(start_buckets);    // the bucket array the earlier chunks left behind
+  std::vector<uint8_t> aux;
+  for (uint32_t g = g0; g < g1; g++) {
     bool any = false;
     for (uint32_t a = b.group_off[g]; a < b.group_off[g + 1]; a++) {       // unit blocks of the group, in alignment order = emit order
       const uint32_t lo = b.a_roff[a], hi = lo + b.a_rcnt[a];
@@ -255,13 +238,53 @@ void assemble_bundle(const Bundle& b, bool lng, Stats& st, std::vector<uint8_t>&
         const bool paired = b.flags[r] & BRB_REC_PAIRED;
         const RecView v = b.view(b.src[r]);
         pairs_by_name[std::string(v.name())].push_back(Unit{r, paired, g});
-        n_pairs++; r += paired ? 2 : 1; any = true;
+        r += paired ? 2 : 1; any = true;
       }
     }
     if (!any) st.dropped++;
-    if (n_pairs >= 5000) flush();                          // CHUNK_SIZE, src/core.cpp:27,421-423
   }
-  if (!pairs_by_name.empty()) flush();
+  std::vector<Unit*> filtered;
+  for (auto& [read_name, pairs] : pairs_by_name) {
+    // HI / NH / MAPQ / primary: from the device when the engine computed them (brb_batch_out::hi ...) -- unless the name came in as
+    // more than one group inside this chunk (input not name-collated) or the device left the tie to us (primary == 2)
+    bool from_device = b.have_tags;
+    for (size_t i = 0; from_device && i < pairs.size(); i++) if (pairs[i].group != pairs[0].group || b.prim[pairs[i].row] == 2) from_device = false;
+    if (from_device) {
+      const int total = b.nh[pairs[0].row];
+      for (auto& u : pairs) { u.hi_r = b.hi[u.row]; if (u.paired) u.hi_m = b.hi[u.row + 1]; u.primary = b.prim[u.row] == 1; u.nh = (uint32_t)total; u.mapq = b.mapq[u.row]; filtered.push_back(&u); }
+      st.total_complete += total; if (total == 1) st.total_unique++;
+      continue;
+    }
+    double best_score = -std::numeric_limits<double>::infinity(); int count_at_best = 0; size_t best = pairs.size(); int32_t hit_index = 1; int total = 0;
+    auto score_of = [&](const Unit& u) { double s = b.sim[u.row]; if (u.paired) s = std::max(s, b.sim[u.row + 1]); return s; };
+    for (size_t i = 0; i < pairs.size(); i++) {
+      Unit& u = pairs[i]; u.hi_r = hit_index++; total++;
+      if (u.paired) { u.hi_m = hit_index++; total++; }
+      const double ps = score_of(u);
+      if (ps > best_score) { best_score = ps; best = i; count_at_best = 1; } else if (ps == best_score) count_at_best++;
+    }
+    if (best != pairs.size()) {
+      if (count_at_best == 1) pairs[best].primary = true;
+      else {
+        std::vector<size_t> tied;
+        for (size_t i = 0; i < pairs.size(); i++) if (score_of(pairs[i]) == best_score) tied.push_back(i);
+        const uint64_t seed_key = std::hash<std::string>{}(read_name);
+        pairs[tied[get_rand((uint32_t)tied.size(), seed_key)]].primary = true;
+      }
+    }
+    st.total_complete += total; if (total == 1) st.total_unique++;
+    for (auto& u : pairs) { u.nh = (uint32_t)total; u.mapq = get_mapq((uint32_t)total, lng); filtered.push_back(&u); }
+  }
+  for (Unit* u : filtered) {
+    for (int k = 0; k < (u->paired ? 2 : 1); k++) {
+      const uint32_t r = u->row + k, other = u->row + (1 - k);
+      OutInfo o{}; o.tid = b.tid[r]; o.pos = b.pos[r]; o.strand = (char)b.tstrand[r]; o.paired = u->paired; o.same_tx = b.flags[r] & BRB_REC_SAMETX;
+      o.primary = u->primary; o.long_reads = lng; o.mapq = u->mapq; o.nh = (int32_t)u->nh; o.hi = k == 0 ? u->hi_r : u->hi_m;
+      o.sim = b.sim[r]; o.clip = b.clip[r]; o.cigar = b.cig.data() + b.coff[r]; o.n_cigar = b.coff[r + 1] - b.coff[r];
+      if (u->paired) { o.mate_tid = b.tid[other]; o.mate_pos = b.pos[other]; }
+      assemble_record(b.view(b.src[r]), o, aux, out);
+    }
+  }
 }
 
 }  // namespace
@@ -368,43 +391,62 @@ int main(int argc, char** argv) {
         to_assemble.push_back(b); cv.notify_all();
       }
     };
-    // pool threads: column extraction of freshly cut bundles, and flush replay + record assembly of projected ones (bundles are
-    // independent: a read name never spans two of them); the writer below keeps the bundle order
+    // pool threads: column extraction of freshly cut bundles, and flush replay + record assembly of projected ones -- one task per
+    // flush chunk (a read name never spans two chunks, the chunks of a bundle are independent); the writer below keeps the order
+    std::deque<std::pair<std::shared_ptr<Bundle>, uint32_t>> chunk_tasks;
     auto assembler = [&]() {
       for (;;) {
-        std::shared_ptr<Bundle> b; bool do_ingest = false;
-        { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return !err.empty() || !to_assemble.empty() || !to_ingest.empty() || workers_left == 0; });
+        std::shared_ptr<Bundle> b; int what = 0; uint32_t k = 0;       // 1 ingest, 2 plan the chunks of a projected bundle, 3 one chunk
+        { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return !err.empty() || !chunk_tasks.empty() || !to_assemble.empty() || !to_ingest.empty() || workers_left == 0; });
           if (!err.empty()) return;
-          if (!to_assemble.empty()) { b = to_assemble.front(); to_assemble.pop_front(); }
-          else if (!to_ingest.empty()) { b = to_ingest.front(); to_ingest.pop_front(); do_ingest = true; }
+          if (!chunk_tasks.empty()) { b = chunk_tasks.front().first; k = chunk_tasks.front().second; chunk_tasks.pop_front(); what = 3; }
+          else if (!to_assemble.empty()) { b = to_assemble.front(); to_assemble.pop_front(); what = 2; }
+          else if (!to_ingest.empty()) { b = to_ingest.front(); to_ingest.pop_front(); what = 1; }
           else { if (workers_left == 0) return; continue; } }
         const auto t0 = clk::now();
-        if (do_ingest) {
+        if (what == 1) {
           const std::string e = ingest_bundle(*b);
           std::unique_lock<std::mutex> lk(m);
           t_extract += secs(t0, clk::now());
           if (!e.empty()) { if (err.empty()) err = e; cv.notify_all(); return; }
           todo[b->index % n_gpu].push_back(b); n_ingested++; cv.notify_all();
-          continue;
+        } else if (what == 2) {
+          plan_chunks(*b);
+          b->parts.assign(b->chunks.size(), std::vector<uint8_t>());
+          std::unique_lock<std::mutex> lk(m);
+          t_assemble += secs(t0, clk::now());
+          b->parts_left = (uint32_t)b->chunks.size();
+          if (b->chunks.empty()) b->assembled = true;
+          for (uint32_t i = 0; i < b->chunks.size(); i++) chunk_tasks.emplace_back(b, i);
+          cv.notify_all();
+        } else {
+          Stats bs; assemble_chunk(*b, b->chunks[k].first, b->chunks[k].second, b->chunk_buckets[k], lng, bs, b->parts[k]);
+          std::unique_lock<std::mutex> lk(m);
+          t_assemble += secs(t0, clk::now());
+          b->dropped += bs.dropped; b->total_complete += bs.total_complete; b->total_unique += bs.total_unique;
+          if (--b->parts_left == 0) { b->assembled = true; b->raw.clear(); b->raw.shrink_to_fit(); }
+          cv.notify_all();
         }
-        Stats bs; assemble_bundle(*b, lng, bs, b->out);
-        b->dropped = bs.dropped; b->total_complete = bs.total_complete; b->total_unique = bs.total_unique;
-        b->raw.clear(); b->raw.shrink_to_fit();
-        std::unique_lock<std::mutex> lk(m);
-        t_assemble += secs(t0, clk::now());
-        b->assembled = true; cv.notify_all();
       }
     };
     auto writer = [&]() {
+      std::vector<uint8_t> joined;
       for (;;) {
         std::shared_ptr<Bundle> b;
         { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return !err.empty() || (!inflight.empty() && inflight.front()->assembled) || (eof && inflight.empty()); });
           if (!err.empty()) return; if (inflight.empty()) return; b = inflight.front(); inflight.pop_front(); cv.notify_all(); }
         const auto t1 = clk::now();
         try {
-          const uint8_t* z = nullptr; size_t zn = 0;
-          if (dev_deflate && !b->out.empty() && engines[b->index % n_gpu]->bgzf_compress(b->out.data(), b->out.size(), z, zn)) out.write_raw(z, zn);
-          else out.write(b->out.data(), b->out.size());
+          if (dev_deflate) {                                   // a few chunks per call: one upload, one kernel sequence, one download
+            size_t k = 0;
+            while (k < b->parts.size()) {
+              joined.clear();
+              while (k < b->parts.size() && (joined.empty() || joined.size() + b->parts[k].size() <= ((size_t)48 << 20))) { joined.insert(joined.end(), b->parts[k].begin(), b->parts[k].end()); std::vector<uint8_t>().swap(b->parts[k]); k++; }
+              const uint8_t* z = nullptr; size_t zn = 0;
+              if (!joined.empty() && engines[b->index % n_gpu]->bgzf_compress(joined.data(), joined.size(), z, zn)) out.write_raw(z, zn);
+              else out.write(joined.data(), joined.size());
+            }
+          } else for (auto& part : b->parts) { out.write(part.data(), part.size()); std::vector<uint8_t>().swap(part); }
         } catch (const std::exception& e) { std::unique_lock<std::mutex> lk(m); if (err.empty()) err = e.what(); cv.notify_all(); return; }
         st.dropped += b->dropped; st.total_complete += b->total_complete; st.total_unique += b->total_unique;
         t_write += secs(t1, clk::now());
@@ -428,7 +470,6 @@ int main(int argc, char** argv) {
       t_wait_push += secs(tw, clk::now());
       bundle = new_bundle();
     };
-    std::vector<uint8_t> rec;
     std::string producer_err;
     try {
     for (;;) {
@@ -437,19 +478,27 @@ int main(int argc, char** argv) {
       const auto tr0 = timing ? clk::now() : clk::time_point();
       if (in.read(&bs, 4) != 4) break;
       if (bs < 32) throw std::runtime_error("malformed BAM record (block_size < 32)");
-      rec.resize(bs); if (in.read(rec.data(), bs) != (size_t)bs) throw std::runtime_error("truncated BAM record");
+      // the record is read straight to the end of the current bundle's buffer (and moved only when it turns out to open the next bundle)
+      size_t at = bundle->raw.size();
+      bundle->raw.resize(at + bs);
+      if (in.read(bundle->raw.data() + at, bs) != (size_t)bs) throw std::runtime_error("truncated BAM record");
       if (timing) t_read += secs(tr0, clk::now());
       st.total_reads++;
-      const RecView v{rec.data(), (uint32_t)bs};
-      if (v.flag() & 4) { st.unmapped++; continue; }
-      const char* name = v.name();
+      RecView v{bundle->raw.data() + at, (uint32_t)bs};
+      if (v.flag() & 4) { st.unmapped++; bundle->raw.resize(at); continue; }
       const uint32_t id = (uint32_t)bundle->rec_off.size();
-      const bool new_name = (id == 0) || prev_name != name;
-      if (id >= o.chunk && new_name) push_bundle();
+      const bool new_name = (id == 0) || prev_name != v.name();
+      if (id >= o.chunk && new_name) {
+        std::vector<uint8_t> moved(bundle->raw.begin() + at, bundle->raw.end());
+        bundle->raw.resize(at);
+        push_bundle();
+        bundle->raw = std::move(moved); at = 0;
+        v = RecView{bundle->raw.data(), (uint32_t)bs};
+      }
       Bundle& b = *bundle; const uint32_t a = (uint32_t)b.rec_off.size();
       if (a > 0 && new_name) b.group_off.push_back(a);
-      b.rec_off.push_back(b.raw.size()); b.rec_len.push_back((uint32_t)bs); b.raw.insert(b.raw.end(), rec.begin(), rec.end());
-      if (new_name) prev_name = name;
+      b.rec_off.push_back(at); b.rec_len.push_back((uint32_t)bs);
+      if (new_name) prev_name = v.name();
     }
     push_bundle();
     } catch (const std::exception& e) { producer_err = e.what(); }        // (truncated record, inflate / CRC error): report it after the threads are joined

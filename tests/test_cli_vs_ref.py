@@ -103,6 +103,33 @@ def test_host_threads_do_not_change_the_output(mode):
     assert outs[0] == outs[1] and len(outs[0]) > 100000
 
 
+@needs_ref
+def test_flush_chunks_assembled_in_parallel_keep_the_reference_order():
+    """Several 5000-pair flush chunks in one bundle: the reference reuses ONE name map across them (clear() keeps its bucket
+    array), so the record order inside chunk k depends on the earlier chunks; the CLI assembles the chunks on pool threads
+    from the recorded bucket counts and must still write the reference's bytes."""
+    from bramble_b200 import synth_fast as sf
+    A = sf.make_annotation(11, n_chrom=2, n_genes=200)
+    ix = sf.build_index(A)
+    B = sf.make_short_batch(A, ix, 12, 24000, stranded=None, multi=0.15)
+    d = tempfile.mkdtemp(prefix="brb_cli_")
+    sf.write_gtf(A, d + "/a.gtf")
+
+    class Ann:
+        chroms, chrom_len = A.chroms, A.chrom_len
+    synth.write_bam(d + "/in.bam", Ann, sf.to_records(B))
+    old = os.environ.get("BRB_THREADS")
+    os.environ["BRB_THREADS"] = "5"
+    try:
+        a, b = run_both(d, PORT_CLI, [])
+    finally:
+        if old is None:
+            del os.environ["BRB_THREADS"]
+        else:
+            os.environ["BRB_THREADS"] = old
+    assert a == b, explain(a, b, d)
+
+
 def _pg_strip(stream):
     """drop the trailing extra flags our runs add to the @PG CL: field (--gpus N)"""
     return stream
