@@ -68,6 +68,18 @@ template <typename T> __device__ __forceinline__ void st_stream(T* p, T v) {
 #endif
 }
 
+// Loads of batch columns and match records that are read once per bundle: VAR_STREAM_LOADS >= 1 marks the front kernel's,
+// >= 2 the back kernel's too, evict-first (ld.global.cs), so that the index (plain loads) outlives them in L2.
+#ifndef VAR_STREAM_LOADS
+#define VAR_STREAM_LOADS 0
+#endif
+template <int LEVEL, typename T> __device__ __forceinline__ T ld_stream(const T* p) {
+#if VAR_STREAM_LOADS
+  if (VAR_STREAM_LOADS >= LEVEL) return __ldcs(p);
+#endif
+  return __ldg(p);
+}
+
 struct DevBatch {
   uint32_t n_aln, n_groups, n_exon, n_cigar;
   const uint32_t* group_off; const int32_t* refid; const int8_t* strand;
@@ -135,6 +147,11 @@ struct RecLink { int32_t gprev_en, gnext_st; uint32_t gnext, meta; };
 __device__ __forceinline__ RecLink rec_link(const DevIndex& ix, uint32_t i) {
   uint4 v = ldg4(VAR_SPLIT_REC ? ix.rlink + i : ix.rkey + 2 * (size_t)i + 1);
   RecLink k; k.gprev_en = (int32_t)v.x; k.gnext_st = (int32_t)v.y; k.gnext = v.z; k.meta = v.w; return k;
+}
+// the second half of the link half only: .x = gnext, .y = meta
+__device__ __forceinline__ uint2 rec_link_tail(const DevIndex& ix, uint32_t i) {
+  const uint4* q = VAR_SPLIT_REC ? ix.rlink + i : ix.rkey + 2 * (size_t)i + 1;
+  return __ldg(reinterpret_cast<const uint2*>(q) + 1);
 }
 
 __device__ __forceinline__ int exon_status(uint32_t n, uint32_t j) {   // src/evaluate.cpp:44-56

@@ -91,7 +91,7 @@ struct BatchTotals { unsigned long long* agg; unsigned long long* claim; };
 __device__ __forceinline__ uint32_t real_msum(const uint32_t* __restrict__ real, uint32_t n) {
   uint32_t sum = 0;
   for (uint32_t i = 0; i < n; i++) {
-    const uint32_t rw = __ldg(&real[i]), op = rw & 0xfu;
+    const uint32_t rw = ld_stream<2>(&real[i]), op = rw & 0xfu;
     if (op == CM || op == CEQ || op == CX) sum += rw >> 4; else if (op != CN) return 0;
   }
   return sum;
@@ -144,17 +144,17 @@ __global__ void __launch_bounds__(256, LONG ? 3 : VAR_BACK_CTAS) k_back(DevBatch
     int32_t mate = -1;
     bool owner = false;
     if (in_batch) {
-      const uint4 ac = __ldg(&v.a_cand[a]);
-      mate = __ldg(&b.mate_idx[a]);
-      ro = __ldg(&b.cigar_off[a]); nrc = __ldg(&b.cigar_off[a + 1]) - ro;
+      const uint4 ac = ld_stream<2>(&v.a_cand[a]);
+      mate = ld_stream<2>(&b.mate_idx[a]);
+      ro = ld_stream<2>(&b.cigar_off[a]); nrc = ld_stream<2>(&b.cigar_off[a + 1]) - ro;
       if (ac.z) rsum = real_msum(b.cigar + ro, nrc);          // every lane sums its OWN real CIGAR ...
       owner = (mate < 0 || (uint32_t)mate > a) && ac.z;       // unit owner with at least one match
       if (owner) {
         off = ac.x; n = ac.y;
         if (mate >= 0) {
-          const uint4 mc = __ldg(&v.a_cand[mate]);
+          const uint4 mc = ld_stream<2>(&v.a_cand[mate]);
           m_off = mc.x; m_n = mc.y; nm = mc.z;
-          mro = __ldg(&b.cigar_off[mate]); mnrc = __ldg(&b.cigar_off[mate + 1]) - mro;
+          mro = ld_stream<2>(&b.cigar_off[mate]); mnrc = ld_stream<2>(&b.cigar_off[mate + 1]) - mro;
         }
         pflag = (nm == 0 ? 1u : 0u) | ((ac.z == 1 && nm == 1) ? 2u : 0u);
       }
@@ -233,7 +233,7 @@ __global__ void __launch_bounds__(256, LONG ? 3 : VAR_BACK_CTAS) k_back(DevBatch
       const uint32_t o_moff = __shfl_sync(0xffffffffu, m_off, L), o_mn = __shfl_sync(0xffffffffu, m_n, L);
       const uint32_t o_rsum = __shfl_sync(0xffffffffu, rsum, L), o_mrsum = __shfl_sync(0xffffffffu, mrsum, L);
       uint4 mr = make_uint4(0, 0, 0, NONE);
-      if (actv) mr = __ldg(&v.m_rec[c]);
+      if (actv) mr = ld_stream<2>(&v.m_rec[c]);
       const uint32_t tid = mr.w;
       uint32_t part = NONE;
       if (tid != NONE) {

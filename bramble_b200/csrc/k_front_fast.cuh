@@ -41,29 +41,33 @@ namespace brb {
 //                has to be exon_id + 1 (correct_for_gaps) and, for a middle exon, end exactly at the read exon's end.
 //   FAST_DEFER   anything else: the general path decides.
 enum { FAST_DEFER = 0, FAST_MATCH = 1, FAST_REJECT = 2 };
+// Only the KEY half of the exon-0 record is needed unless the read is spliced: the index build has checked that the exons of a
+// transcript are disjoint and ascending (k_index_links, codes 3/4), so once read exon 0 is known to lie inside guide exon 0
+// (st <= qs, qe <= en) no neighbour exon of the tid can overlap it -- the link half (exon_id, chain successor) is fetched for
+// spliced reads only.  The same holds under the last read exon (qe <= en of its guide exon).
 __device__ __forceinline__ int fast_short(const DevIndex& ix, const DevBatch& b, bool strict, const ReadExons& rx, int s, const RecKey& key0,
-                                          const RecLink& lk0, uint32_t& pos, uint32_t& word) {
+                                          uint32_t rec0, uint32_t& pos, uint32_t& word) {
   uint32_t qs = rx.qs0, qe = rx.qe0;
   if ((uint32_t)key0.st > qs || qe <= qs) return FAST_DEFER;                        // left soft clip / empty read exon
-  if (lk0.gprev_en > (int32_t)qs || lk0.gnext_st < (int32_t)qe) return FAST_DEFER;   // a neighbour exon of this tid overlaps read exon 0 too
   const uint32_t first_pos = (qs - (uint32_t)key0.st) + key0.pos_start;             // src/g2t.cpp:160-163
   uint32_t total = qe - qs;
   int32_t k_en = key0.en; uint32_t k_pos_start = key0.pos_start;
   if (rx.n_ex > 1) {
     if (qe != (uint32_t)key0.en) return FAST_DEFER;
     const int miss = strict ? FAST_REJECT : FAST_DEFER;
+    const RecLink lk0 = rec_link(ix, rec0);
     uint32_t prev_eid = lk0.meta & 0xffu, r = lk0.gnext;
     for (uint32_t j = 1; j < rx.n_ex; j++) {
       qs = __ldg(&b.exon_st[rx.e0 + j]); qe = __ldg(&b.exon_en[rx.e0 + j]);
       if (qe <= qs) return FAST_DEFER;
       if (r == NONE) return miss;
-      const RecKey k = rec_key(ix, r); const RecLink l = rec_link(ix, r);
+      const RecKey k = rec_key(ix, r); const uint2 l = rec_link_tail(ix, r);         // .x successor, .y meta
       if ((uint32_t)k.st != qs) return miss;
-      const uint32_t eid = l.meta & 0xffu;
+      const uint32_t eid = l.y & 0xffu;
       if (((eid - prev_eid) & 0xffu) != 1) return miss;                             // correct_for_gaps, src/evaluate.cpp:131-140
       if (j + 1 < rx.n_ex) { if ((uint32_t)k.en != qe) return miss; }
-      else if (qe > (uint32_t)k.en || l.gnext_st < (int32_t)qe) return FAST_DEFER;   // right soft clip / a second record under the last read exon
-      total += qe - qs; prev_eid = eid; r = l.gnext; k_en = k.en; k_pos_start = k.pos_start;
+      else if (qe > (uint32_t)k.en) return FAST_DEFER;                               // right soft clip
+      total += qe - qs; prev_eid = eid; r = l.x; k_en = k.en; k_pos_start = k.pos_start;
     }
   } else if (qe > (uint32_t)key0.en) return FAST_DEFER;                             // right soft clip
   pos = s ? ((uint32_t)k_en - qe) + k_pos_start : first_pos;                         // src/g2t.cpp:196-199; rcpos follows the last guide exon
@@ -105,17 +109,17 @@ __global__ void __launch_bounds__(256, VAR_FAST_CTAS) k_front_fast(DevIndex ix, 
     ReadExons rx; rx.e0 = 0; rx.n_ex = 0; rx.qs0 = 0; rx.qe0 = 0;
     uint32_t lo0 = 0, n0 = 0, lo1 = 0, n1 = 0;
     if (a < b.n_aln) {
-      rx.e0 = __ldg(&b.exon_off[a]); rx.n_ex = __ldg(&b.exon_off[a + 1]) - rx.e0;
-      const int32_t refid = __ldg(&b.refid[a]);
-      const int8_t sd = b.strand[a];
-      const int32_t m = __ldg(&b.mate_idx[a]);             // process_pairs links are single and symmetric (src/bramble.cpp:272-311)
-      if (m >= 0 && ((uint32_t)m >= b.n_aln || (uint32_t)m == a || __ldg(&b.mate_idx[m]) != (int32_t)a)) bad = 1;
+      rx.e0 = ld_stream<1>(&b.exon_off[a]); rx.n_ex = ld_stream<1>(&b.exon_off[a + 1]) - rx.e0;
+      const int32_t refid = ld_stream<1>(&b.refid[a]);
+      const int8_t sd = ld_stream<1>(&b.strand[a]);
+      const int32_t m = ld_stream<1>(&b.mate_idx[a]);             // process_pairs links are single and symmetric (src/bramble.cpp:272-311)
+      if (m >= 0 && ((uint32_t)m >= b.n_aln || (uint32_t)m == a || ld_stream<1>(&b.mate_idx[m]) != (int32_t)a)) bad = 1;
       if (m >= 0) n_mates++;
       if (rx.n_ex) {
-        rx.qs0 = __ldg(&b.exon_st[rx.e0]); rx.qe0 = __ldg(&b.exon_en[rx.e0]);
+        rx.qs0 = ld_stream<1>(&b.exon_st[rx.e0]); rx.qe0 = ld_stream<1>(&b.exon_en[rx.e0]);
         uint32_t pe = rx.qe0; if (rx.qe0 < rx.qs0) bad = 2;
         for (uint32_t j = 1; j < rx.n_ex; j++) {            // read exons ascending and disjoint (CIGAR order)
-          const uint32_t qs = __ldg(&b.exon_st[rx.e0 + j]), qe = __ldg(&b.exon_en[rx.e0 + j]);
+          const uint32_t qs = ld_stream<1>(&b.exon_st[rx.e0 + j]), qe = ld_stream<1>(&b.exon_en[rx.e0 + j]);
           if (qe < qs || qs < pe) bad = 2;
           pe = qe;
         }
@@ -188,7 +192,7 @@ __global__ void __launch_bounds__(256, VAR_FAST_CTAS) k_front_fast(DevIndex ix, 
       }
       my_hits += __popc(__ballot_sync(0xffffffffu, ov)) * (lane == 0);
       bool fast = false; uint32_t pos = 0, word = 0;
-      if (sv) { const int v = fast_short(ix, b, strict, ox, s, key, rec_link(ix, rec0), pos, word); fast = v == FAST_MATCH; sv = v != FAST_REJECT; }
+      if (sv) { const int v = fast_short(ix, b, strict, ox, s, key, rec0, pos, word); fast = v == FAST_MATCH; sv = v != FAST_REJECT; }
       const uint32_t B_sv = __ballot_sync(0xffffffffu, sv), B_fast = __ballot_sync(0xffffffffu, fast), B_q = B_sv & ~B_fast;
       const uint32_t slot = sbase + wr + __popc(B_sv & lt_mask);
       if (fast) st_stream(&M.rec[slot], make_uint4(pos, 2u | (uint32_t)s, word, key.tid));
