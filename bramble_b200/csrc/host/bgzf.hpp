@@ -49,6 +49,13 @@ class BgzfReader {
     }
     return got;
   }
+  // The rest of the current inflated block, or the whole next one (false at EOF): the record walk of the CLI takes the stream block by
+  // block instead of paying two read() calls per record.  The bytes stay valid until the next call.
+  bool next_chunk(const uint8_t*& p, size_t& n) {
+    if (pos_ == buf_.size()) { if (!(pool_.empty() ? fill() : next_block())) return false; }
+    p = buf_.data() + pos_; n = buf_.size() - pos_; pos_ = buf_.size();
+    return true;
+  }
  private:
   struct Job { std::vector<uint8_t> comp, out; size_t clen = 0; uint32_t isize = 0; bool ready = false; std::string err; };
   // next compressed block from the file: false at EOF

@@ -472,34 +472,46 @@ int main(int argc, char** argv) {
     };
     std::string producer_err;
     try {
+    // The inflated stream is appended to the current bundle's buffer block by block and the records are walked in place
+    // (rec_off points at the record body, behind its block_size word); when a record opens the next bundle, the unparsed tail
+    // of the buffer -- less than a BGZF block and a record -- moves over.
+    size_t scan = 0, last_raw = (size_t)o.chunk * 400;
+    bundle->raw.reserve(last_raw); bundle->rec_off.reserve(o.chunk + 64); bundle->rec_len.reserve(o.chunk + 64);
     for (;;) {
       { std::unique_lock<std::mutex> lk(m); if (!err.empty()) break; }     // a worker failed: stop reading, nothing would consume the bundles
-      int32_t bs = 0;
+      const uint8_t* blk = nullptr; size_t blk_n = 0;
       const auto tr0 = timing ? clk::now() : clk::time_point();
-      if (in.read(&bs, 4) != 4) break;
-      if (bs < 32) throw std::runtime_error("malformed BAM record (block_size < 32)");
-      // the record is read straight to the end of the current bundle's buffer (and moved only when it turns out to open the next bundle)
-      size_t at = bundle->raw.size();
-      bundle->raw.resize(at + bs);
-      if (in.read(bundle->raw.data() + at, bs) != (size_t)bs) throw std::runtime_error("truncated BAM record");
+      if (!in.next_chunk(blk, blk_n)) break;
+      bundle->raw.insert(bundle->raw.end(), blk, blk + blk_n);
       if (timing) t_read += secs(tr0, clk::now());
-      st.total_reads++;
-      RecView v{bundle->raw.data() + at, (uint32_t)bs};
-      if (v.flag() & 4) { st.unmapped++; bundle->raw.resize(at); continue; }
-      const uint32_t id = (uint32_t)bundle->rec_off.size();
-      const bool new_name = (id == 0) || prev_name != v.name();
-      if (id >= o.chunk && new_name) {
-        std::vector<uint8_t> moved(bundle->raw.begin() + at, bundle->raw.end());
-        bundle->raw.resize(at);
-        push_bundle();
-        bundle->raw = std::move(moved); at = 0;
-        v = RecView{bundle->raw.data(), (uint32_t)bs};
+      for (;;) {
+        std::vector<uint8_t>& raw = bundle->raw;
+        if (scan + 4 > raw.size()) break;
+        const int32_t bs = rdi32(raw.data() + scan);
+        if (bs < 32) throw std::runtime_error("malformed BAM record (block_size < 32)");
+        if (scan + 4 + (size_t)bs > raw.size()) break;
+        const RecView v{raw.data() + scan + 4, (uint32_t)bs};
+        if (v.flag() & 4) { st.total_reads++; st.unmapped++; scan += 4 + (size_t)bs; continue; }
+        const uint32_t id = (uint32_t)bundle->rec_off.size();
+        const bool new_name = (id == 0) || prev_name != v.name();
+        if (id >= o.chunk && new_name) {                       // cut here: this record is parsed again as the first one of the next bundle
+          std::vector<uint8_t> tail(raw.begin() + scan, raw.end());
+          raw.resize(scan); last_raw = raw.size();
+          push_bundle();
+          bundle->raw.reserve(last_raw + last_raw / 8 + (1 << 20)); bundle->rec_off.reserve(o.chunk + 64); bundle->rec_len.reserve(o.chunk + 64);
+          bundle->raw.insert(bundle->raw.end(), tail.begin(), tail.end()); scan = 0;
+          continue;
+        }
+        Bundle& b = *bundle;
+        if (id > 0 && new_name) b.group_off.push_back(id);
+        b.rec_off.push_back(scan + 4); b.rec_len.push_back((uint32_t)bs);
+        if (new_name) prev_name = v.name();
+        st.total_reads++;
+        scan += 4 + (size_t)bs;
       }
-      Bundle& b = *bundle; const uint32_t a = (uint32_t)b.rec_off.size();
-      if (a > 0 && new_name) b.group_off.push_back(a);
-      b.rec_off.push_back(at); b.rec_len.push_back((uint32_t)bs);
-      if (new_name) prev_name = v.name();
     }
+    if (producer_err.empty() && scan != bundle->raw.size()) { std::unique_lock<std::mutex> lk(m); if (err.empty()) throw std::runtime_error("truncated BAM record"); }
+    bundle->raw.resize(scan);
     push_bundle();
     } catch (const std::exception& e) { producer_err = e.what(); }        // (truncated record, inflate / CRC error): report it after the threads are joined
     const auto t_loop_end = clk::now();
