@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <ctime>
 #include <string>
 #include <vector>
 
@@ -23,6 +24,7 @@
 #include "k_flush.cuh"
 #include "k_index.cuh"
 #include "k_deflate.cuh"
+#include "k_emit.cuh"
 
 using namespace brb;
 
@@ -71,7 +73,9 @@ struct RescueBufs;                       // rescue_host.inl
 }  // namespace
 
 struct brb_ctx;
-namespace { void free_rescue_bufs(brb_ctx* c); }
+namespace { void free_rescue_bufs(brb_ctx* c);
+struct RowView { const uint32_t* src; const uint32_t* tid; const uint32_t* pos; const int8_t* strand; const uint8_t* flags; const double* sim; const int32_t* clip; const uint32_t* coff; const uint32_t* pool; };
+}
 struct brb_index {
   int device = 0;
   DevIndex d{};
@@ -94,6 +98,7 @@ struct brb_ctx {
   Buf in_group_off, in_refid, in_strand, in_exon_off, in_exon_st, in_exon_en, in_cigar_off, in_cigar, in_mate, in_seq_off, in_seq, in_name_off, in_names;
   Buf f_hi, f_nh, f_mapq, f_prim;   // BRB_OPT_FLUSH_TAGS results per row
   Buf z_in, z_slots, z_sizes, z_crcs, z_tot, z_off, z_out, z_ticket; HBuf z_host;   // brb_bgzf_compress
+  Buf e_raw, e_off, e_len, e_units, e_plan, e_sizes, e_offs, e_err;                // brb_emit_bgzf
   bool have_names = false, opt_flush_tags = false, result_tags = false;
   uint64_t in_bytes = 0, n_mates = 0, seq_bytes = 0, rescue_bytes = 0;
   bool have_batch = false, have_result = false, have_scores = false, opt_generic_front = false, opt_no_fastpath = false, opt_ordered = false, result_ordered = false, opt_packed = false, result_packed = false, opt_merge_warp = false;
@@ -110,10 +115,12 @@ struct brb_ctx {
   HBuf h_small, h_out;
   RescueBufs* rb = nullptr;
   uint32_t n_cand = 0, n_rec = 0; uint64_t n_out_words = 0;
+  RowView rv{}; Buf res_slab;         // where the rows of the resident result are: the o_* buffers, or res_slab after brb_ctx_move_result
+  uint32_t res_n_aln = 0; bool res_foreign = false;      // alignments of the batch the resident result belongs to; result moved in from another ctx (brb_ctx_move_result)
   brb_stats stats{};
   std::vector<Buf*> all() {
     return {&in_group_off, &in_refid, &in_strand, &in_exon_off, &in_exon_st, &in_exon_en, &in_cigar_off, &in_cigar, &in_mate, &in_seq_off,
-            &in_seq, &in_name_off, &in_names, &f_hi, &f_nh, &f_mapq, &f_prim, &z_in, &z_slots, &z_sizes, &z_crcs, &z_tot, &z_off, &z_out, &z_ticket, &ctl, &q_any, &a_cand, &scan_tmp, &c_rec, &c_task, &c_first, &c_last, &c_nseg, &c_nguide, &c_cap, &ipool,
+            &in_seq, &in_name_off, &in_names, &f_hi, &f_nh, &f_mapq, &f_prim, &z_in, &z_slots, &z_sizes, &z_crcs, &z_tot, &z_off, &z_out, &z_ticket, &e_raw, &e_off, &e_len, &e_units, &e_plan, &e_sizes, &e_offs, &e_err, &res_slab, &ctl, &q_any, &a_cand, &scan_tmp, &c_rec, &c_task, &c_first, &c_last, &c_nseg, &c_nguide, &c_cap, &ipool,
             &r_left, &r_right, &rpool, &m_rec, &m_sim, &m_clip, &c_stage, &t_agg, &t_claim, &t_off, &p_row, &p_pool, &p_sim, &p_clip, &a_roff, &a_rcnt, &g_roff,
             &o_src, &o_tid, &o_pos, &o_strand, &o_flags, &o_sim, &o_clip, &o_coff, &tpool, &opool};
   }
@@ -415,7 +422,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   if (n == 0) {
     ENS(c->g_roff, (size_t)(b.n_groups + 1) * 4); ENS(c->o_coff, 4);
     CU(cudaMemsetAsync(c->g_roff.p, 0, 4, st)); CU(cudaMemsetAsync(c->o_coff.p, 0, 4, st)); CU(cudaStreamSynchronize(st));
-    c->have_result = true; c->result_ordered = c->opt_ordered; c->result_packed = c->opt_packed && !c->opt_ordered; return BRB_OK;
+    c->have_result = true; c->res_n_aln = c->b.n_aln; c->res_foreign = false; c->rv = RowView{c->o_src.as<uint32_t>(), c->o_tid.as<uint32_t>(), c->o_pos.as<uint32_t>(), c->o_strand.as<int8_t>(), c->o_flags.as<uint8_t>(), c->have_scores ? c->o_sim.as<double>() : nullptr, c->have_scores ? c->o_clip.as<int32_t>() : nullptr, c->o_coff.as<uint32_t>(), c->opool.as<uint32_t>()}; c->result_ordered = c->opt_ordered; c->result_packed = c->opt_packed && !c->opt_ordered; return BRB_OK;
   }
   if (!c->cap_cand) {           // first guess from the batch shape; a pool that overflows grows and the sequence replays
     c->cap_cand = grown((uint64_t)12 * n); c->cap_rows = grown((uint64_t)6 * n);
@@ -576,7 +583,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   S.alg_bytes_front = (uint64_t)n * 16 + (uint64_t)b.n_exon * 8 + hres->n_mates * 4 + hres->n_hits * 56;
   S.alg_bytes = S.alg_bytes_front + (uint64_t)b.n_cigar * 4 + (uint64_t)hres->n_rows * 40 + hres->out_words * 4 + hres->rescue_bytes;
   S.ksw_cells = hres->ksw_cells; S.host_syncs = n_syncs;
-  c->have_result = true; c->result_ordered = ordered; c->result_packed = packed;
+  c->have_result = true; c->res_n_aln = c->b.n_aln; c->res_foreign = false; c->rv = RowView{c->o_src.as<uint32_t>(), c->o_tid.as<uint32_t>(), c->o_pos.as<uint32_t>(), c->o_strand.as<int8_t>(), c->o_flags.as<uint8_t>(), c->have_scores ? c->o_sim.as<double>() : nullptr, c->have_scores ? c->o_clip.as<int32_t>() : nullptr, c->o_coff.as<uint32_t>(), c->opool.as<uint32_t>()}; c->result_ordered = ordered; c->result_packed = packed;
   return BRB_OK;
 }
 
@@ -595,6 +602,7 @@ int brb_project_resident(brb_ctx* c, const brb_params* p) {
 int brb_batch_download(brb_ctx* c, brb_batch_out* out) {
   if (!c || !out) return fail(BRB_E_ARG, "brb_batch_download: null argument");
   if (!c->have_result) return fail(BRB_E_ARG, "no result resident: call brb_project_resident first");
+  if (c->res_foreign) return fail(BRB_E_ARG, "the resident result was moved in from another ctx (brb_ctx_move_result): only brb_emit_bgzf reads it");
   CU(cudaSetDevice(c->idx->device));
   const size_t R = c->n_rec, W = c->n_out_words, G = c->b.n_groups;
   const bool sc = c->have_scores && R;
@@ -699,23 +707,18 @@ int brb_ctx_stats(const brb_ctx* c, brb_stats* out) {
 }
 
 // ---- BGZF encoder (k_deflate.cuh): n bytes -> complete BGZF blocks (0xff00 input bytes each, the last one shorter), on the ctx stream.
-int brb_bgzf_compress(brb_ctx* c, const uint8_t* data, uint64_t n, const uint8_t** out, uint64_t* out_bytes) {
-  if (!c || !out || !out_bytes || (n && !data)) return fail(BRB_E_ARG, "brb_bgzf_compress: null argument");
-  if (brb_device_count() <= 0) return fail(BRB_E_NO_DEVICE, "no CUDA device");
-  CU(cudaSetDevice(c->idx->device));
-  *out = nullptr; *out_bytes = 0;
-  if (!n) return BRB_OK;
+}  // extern "C"
+namespace {
+// BGZF blocks of the n bytes at z_in (device; 16 readable bytes behind them): kernels + the copy of the blocks to pinned host memory
+int deflate_resident(brb_ctx* c, uint64_t n, const uint8_t** out, uint64_t* out_bytes) {
   const uint64_t nb64 = (n + BGZF_IN - 1) / BGZF_IN;
-  if (nb64 > 0x3fffffffull) return fail(BRB_E_ARG, "brb_bgzf_compress: input too large for one call");
+  if (nb64 > 0x3fffffffull) return fail(BRB_E_ARG, "BGZF encoder: input too large for one call");
   const uint32_t nb = (uint32_t)nb64;
-  ENS(c->z_in, n + 16); ENS(c->z_slots, (size_t)nb * BGZF_SLOT); ENS(c->z_sizes, (size_t)nb * 4); ENS(c->z_crcs, (size_t)nb * 4);
+  ENS(c->z_slots, (size_t)nb * BGZF_SLOT); ENS(c->z_sizes, (size_t)nb * 4); ENS(c->z_crcs, (size_t)nb * 4);
   ENS(c->z_tot, (size_t)nb * 8 + 8); ENS(c->z_off, (size_t)(nb + 1) * 8); ENS(c->z_ticket, 16);
   ENS(c->scan_tmp, scan_scratch_words(nb) * 8);
   ENS(c->z_out, n + (size_t)nb * 64 + 64);                       // (a stored block adds 5 + 26 bytes to its input)
-  ENS(c->z_host, n + (size_t)nb * 64 + 64);
   cudaStream_t st = c->st;
-  CU(cudaMemsetAsync(c->z_in.as<uint8_t>() + (n & ~(uint64_t)3), 0, 16 - (n & 3), st));     // the word loads may read up to 7 bytes past the end
-  CU(cudaMemcpyAsync(c->z_in.p, data, n, cudaMemcpyHostToDevice, st));
   CU(cudaMemsetAsync(c->z_ticket.p, 0, 16, st));
   DeflateJob J; J.in = c->z_in.as<uint8_t>(); J.n = n; J.slots = c->z_slots.as<uint8_t>(); J.sizes = c->z_sizes.as<uint32_t>(); J.crcs = c->z_crcs.as<uint32_t>();
   J.n_blocks = nb; J.ticket = c->z_ticket.as<uint32_t>();
@@ -729,10 +732,116 @@ int brb_bgzf_compress(brb_ctx* c, const uint8_t* data, uint64_t n, const uint8_t
   CU(cudaMemcpyAsync(&total, c->z_off.as<unsigned long long>() + nb, 8, cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
   CU(cudaGetLastError());
+  ENS(c->z_host, total + 64);                                    // pinned: sized by what the blocks came to, not by the worst case
   CU(cudaMemcpyAsync(c->z_host.p, c->z_out.p, total, cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
   *out = c->z_host.as<uint8_t>(); *out_bytes = total;
   return BRB_OK;
+}
+}  // namespace
+extern "C" {
+
+int brb_bgzf_compress(brb_ctx* c, const uint8_t* data, uint64_t n, const uint8_t** out, uint64_t* out_bytes) {
+  if (!c || !out || !out_bytes || (n && !data)) return fail(BRB_E_ARG, "brb_bgzf_compress: null argument");
+  if (brb_device_count() <= 0) return fail(BRB_E_NO_DEVICE, "no CUDA device");
+  CU(cudaSetDevice(c->idx->device));
+  *out = nullptr; *out_bytes = 0;
+  if (!n) return BRB_OK;
+  ENS(c->z_in, n + 16);
+  CU(cudaMemsetAsync(c->z_in.as<uint8_t>() + (n & ~(uint64_t)3), 0, 16 - (n & 3), c->st));     // the word loads may read up to 7 bytes past the end
+  CU(cudaMemcpyAsync(c->z_in.p, data, n, cudaMemcpyHostToDevice, c->st));
+  return deflate_resident(c, n, out, out_bytes);
+}
+
+// The resident result rows change hands: a device-to-device copy (a few MB per bundle) into ONE allocation of `to`, so that `from`
+// keeps its own buffers for the next bundle and nothing is allocated in steady state.
+int brb_ctx_move_result(brb_ctx* from, brb_ctx* to) {
+  if (!from || !to || from == to) return fail(BRB_E_ARG, "brb_ctx_move_result: two different contexts are needed");
+  if (from->idx != to->idx) return fail(BRB_E_ARG, "brb_ctx_move_result: the contexts belong to different indexes");
+  if (!from->have_result) return fail(BRB_E_ARG, "brb_ctx_move_result: no result resident in the source ctx");
+  if (from->result_packed || from->result_ordered) return fail(BRB_E_UNSUPPORTED, "brb_ctx_move_result moves the plain row columns (no BRB_OPT_PACKED_ROWS / BRB_OPT_ORDERED_ROWS)");
+  CU(cudaSetDevice(from->idx->device));
+  const size_t R = from->n_rec, W = from->n_out_words; const bool sc = from->have_scores && R;
+  auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
+  size_t off = 0;
+  const size_t p_src = off; off += al(R * 4); const size_t p_tid = off; off += al(R * 4); const size_t p_pos = off; off += al(R * 4);
+  const size_t p_str = off; off += al(R); const size_t p_fl = off; off += al(R);
+  const size_t p_sim = off; off += sc ? al(R * 8) : 0; const size_t p_clip = off; off += sc ? al(R * 4) : 0;
+  const size_t p_coff = off; off += al((R + 1) * 4); const size_t p_pool = off; off += al(W * 4);
+  CU(cudaStreamSynchronize(to->st));                            // (a brb_emit_bgzf on the previous rows of `to` has returned, but be sure)
+  ENS(to->res_slab, off + 256);
+  uint8_t* d = to->res_slab.as<uint8_t>(); const RowView& v = from->rv; cudaStream_t st = from->st;
+  auto cp = [&](size_t dst, const void* src, size_t n) { return (n && R) ? cudaMemcpyAsync(d + dst, src, n, cudaMemcpyDeviceToDevice, st) : cudaSuccess; };   // (no rows: nothing to read)
+  CU(cp(p_src, v.src, R * 4)); CU(cp(p_tid, v.tid, R * 4)); CU(cp(p_pos, v.pos, R * 4)); CU(cp(p_str, v.strand, R)); CU(cp(p_fl, v.flags, R));
+  if (sc) { CU(cp(p_sim, v.sim, R * 8)); CU(cp(p_clip, v.clip, R * 4)); }
+  CU(cp(p_coff, v.coff, (R + 1) * 4)); CU(cp(p_pool, v.pool, W * 4));
+  CU(cudaStreamSynchronize(st));
+  to->rv = RowView{(const uint32_t*)(d + p_src), (const uint32_t*)(d + p_tid), (const uint32_t*)(d + p_pos), (const int8_t*)(d + p_str), d + p_fl,
+                   sc ? (const double*)(d + p_sim) : nullptr, sc ? (const int32_t*)(d + p_clip) : nullptr, (const uint32_t*)(d + p_coff), (const uint32_t*)(d + p_pool)};
+  to->n_rec = from->n_rec; to->n_out_words = from->n_out_words; to->res_n_aln = from->res_n_aln; to->have_scores = from->have_scores;
+  to->result_ordered = false; to->result_packed = false; to->result_tags = false;
+  to->have_result = true; to->res_foreign = true;
+  from->have_result = false;
+  return BRB_OK;
+}
+
+// Output records of the resident result, assembled and BGZF-compressed on the device (k_emit.cuh + k_deflate.cuh).
+int brb_emit_bgzf(brb_ctx* c, const brb_params* p, const brb_emit_in* in, const uint8_t** out, uint64_t* out_bytes, uint64_t* raw_out_bytes) {
+  if (!c || !p || !in || !out || !out_bytes) return fail(BRB_E_ARG, "brb_emit_bgzf: null argument");
+  if (brb_device_count() <= 0) return fail(BRB_E_NO_DEVICE, "no CUDA device");
+  if (!c->have_result) return fail(BRB_E_ARG, "brb_emit_bgzf: no result resident (call brb_project first)");
+  if (c->result_packed || c->result_ordered) return fail(BRB_E_UNSUPPORTED, "brb_emit_bgzf needs the plain row columns (no BRB_OPT_PACKED_ROWS / BRB_OPT_ORDERED_ROWS)");
+  const uint32_t N = c->res_n_aln, U = in->n_units;
+  if (N && (!in->raw || !in->rec_off || !in->rec_len)) return fail(BRB_E_ARG, "brb_emit_bgzf: null record arrays");
+  if (U && !in->units) return fail(BRB_E_ARG, "brb_emit_bgzf: null units");
+  CU(cudaSetDevice(c->idx->device));
+  *out = nullptr; *out_bytes = 0; if (raw_out_bytes) *raw_out_bytes = 0;
+  if (!U) return BRB_OK;
+  cudaStream_t st = c->st;
+  static const bool timing = getenv("BRB_EMIT_TIMING") != nullptr;      // stage milliseconds on stderr (adds stream synchronisations)
+  double t_prev = 0; std::string tline;
+  auto now_ms = [] { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e3 + ts.tv_nsec / 1e6; };
+  auto lap = [&](const char* what) { if (!timing) return; cudaStreamSynchronize(st); const double t = now_ms(); char b2[64]; snprintf(b2, sizeof b2, " %s %.2f", what, t - t_prev); tline += b2; t_prev = t; };
+  if (timing) t_prev = now_ms();
+  ENS(c->e_raw, in->raw_bytes + 16); ENS(c->e_off, (size_t)N * 8 + 16); ENS(c->e_len, (size_t)N * 4 + 16); ENS(c->e_units, (size_t)U * 16);
+  ENS(c->e_plan, (size_t)N * sizeof(EmitPlan) + 16); ENS(c->e_sizes, (size_t)U * 8 + 16); ENS(c->e_offs, (size_t)(U + 1) * 8); ENS(c->e_err, 16);
+  ENS(c->scan_tmp, scan_scratch_words(U) * 8);
+  CU(cudaMemcpyAsync(c->e_raw.p, in->raw, in->raw_bytes, cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(c->e_off.p, in->rec_off, (size_t)N * 8, cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(c->e_len.p, in->rec_len, (size_t)N * 4, cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(c->e_units.p, in->units, (size_t)U * 16, cudaMemcpyHostToDevice, st));
+  CU(cudaMemsetAsync(c->e_err.p, 0, 16, st));
+  lap("alloc+h2d");
+  EmitIn E{};
+  E.raw = c->e_raw.as<uint8_t>(); E.raw_bytes = in->raw_bytes; E.rec_off = c->e_off.as<uint64_t>(); E.rec_len = c->e_len.as<uint32_t>(); E.n_aln = N;
+  E.n_units = U; E.units = c->e_units.as<uint4>();
+  const RowView& rv = c->rv; const bool sc = c->have_scores && c->n_rec;
+  E.n_rows = c->n_rec; E.src = rv.src; E.tid = rv.tid; E.pos = rv.pos; E.strand = rv.strand; E.flags = rv.flags;
+  E.sim = sc ? rv.sim : nullptr; E.clip = sc ? rv.clip : nullptr; E.coff = rv.coff; E.pool = rv.pool; E.long_reads = p->long_reads ? 1u : 0u;
+  EmitPlan* plan = c->e_plan.as<EmitPlan>(); uint32_t* err = c->e_err.as<uint32_t>();
+  unsigned long long* sizes = c->e_sizes.as<unsigned long long>(); unsigned long long* offs = c->e_offs.as<unsigned long long>();
+  uint64_t L = 0;
+  if (N) k_emit_plan<<<grid_for(N, 128), 128, 0, st>>>(E, plan, err);
+  k_emit_sizes<<<grid_for(U, 256), 256, 0, st>>>(E, plan, sizes, err);
+  exclusive_scan(sizes, offs, U, c->scan_tmp.as<unsigned long long>(), st, &L);
+  struct { unsigned long long total; } h_tot{0}; uint32_t h_err[4] = {0, 0, 0, 0};
+  CU(cudaMemcpyAsync(&h_tot.total, offs + U, 8, cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(h_err, err, 16, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  CU(cudaGetLastError());
+  lap("plan+sizes+scan");
+  if (h_err[0] == 1) return fail(BRB_E_ARG, "brb_emit_bgzf: malformed input record (fixed fields run past block_size, or rec_off / rec_len outside raw)");
+  if (h_err[0]) return fail(BRB_E_ARG, "brb_emit_bgzf: a unit names a row or an alignment that does not exist");
+  const uint64_t total = h_tot.total;
+  if (raw_out_bytes) *raw_out_bytes = total;
+  if (!total) return BRB_OK;
+  ENS(c->z_in, total + 16);
+  CU(cudaMemsetAsync(c->z_in.as<uint8_t>() + (total & ~(uint64_t)3), 0, 16 - (total & 3), st));
+  k_emit_write<<<std::min<uint32_t>(grid_for(U, 8), (uint32_t)c->n_sm * 16), 256, 0, st>>>(E, plan, offs, c->z_in.as<uint8_t>());
+  lap("write");
+  const int rc = deflate_resident(c, total, out, out_bytes);
+  if (timing) { lap("deflate+d2h"); fprintf(stderr, "[emit] %u units, %llu -> %llu bytes:%s ms\n", U, (unsigned long long)total, (unsigned long long)*out_bytes, tline.c_str()); }
+  return rc;
 }
 
 // ---- standalone kernels for the parity tests (host buffers in, host buffers out)

@@ -166,6 +166,9 @@ struct Bundle {
   // flush chunks of the bundle (reference CHUNK_SIZE = 5000 pairs, src/core.cpp:27,421-423): group ranges, and the output records
   // of each chunk (uncompressed BAM bytes), assembled independently of one another
   std::vector<std::pair<uint32_t, uint32_t>> chunks; std::vector<size_t> chunk_buckets; std::vector<std::vector<uint8_t>> parts; uint32_t parts_left = 0;
+  // device record assembly (brb_emit_bgzf): the engine slot the rows are resident in, and per chunk the emitted units in output order
+  // (4 words each: first row, HI, NH, MAPQ | primary << 8) instead of the record bytes
+  int slot = -1; std::vector<std::vector<uint32_t>> unit_parts; bool emit_claimed = false, emitted = false; std::vector<uint8_t> zout;
   uint64_t dropped = 0, total_complete = 0, total_unique = 0; bool assembled = false;
   RecView view(uint32_t a) const { return RecView{raw.data() + rec_off[a], rec_len[a]}; }
   uint32_t n_aln() const { return (uint32_t)refid.size(); }
@@ -224,12 +227,13 @@ void plan_chunks(Bundle& b) {
   if (g0 < G) { b.chunks.emplace_back(g0, G); b.chunk_buckets.push_back(buckets); }
 }
 
-// flush() + write_to_bam of the reference for the groups [g0, g1) of a bundle (one flush chunk).
-void assemble_chunk(const Bundle& b, uint32_t g0, uint32_t g1, size_t start_buckets, bool lng, Stats& st, std::vector<uint8_t>& out) {
-  struct Unit { uint32_t row; bool paired; uint32_t group; int32_t hi_r = 0, hi_m = 0; bool primary = false; uint32_t nh = 0, mapq = 0; };
+// flush() of the reference for the groups [g0, g1) of a bundle (one flush chunk): emit(unit) is called once per BamInfo, in the
+// order write_to_bam sees them.
+struct Unit { uint32_t row; bool paired; uint32_t group; int32_t hi_r = 0, hi_m = 0; bool primary = false; uint32_t nh = 0, mapq = 0; };
+template <typename Emit>
+void replay_chunk(const Bundle& b, uint32_t g0, uint32_t g1, size_t start_buckets, bool lng, Stats& st, Emit&& emit) {
   std::unordered_map<std::string, std::vector<Unit>> pairs_by_name;
   if (start_buckets != pairs_by_name.bucket_count()) pairs_by_name.rehash(start_buckets);    // the bucket array the earlier chunks left behind
-  std::vector<uint8_t> aux;
   for (uint32_t g = g0; g < g1; g++) {
     bool any = false;
     for (uint32_t a = b.group_off[g]; a < b.group_off[g + 1]; a++) {       // unit blocks of the group, in alignment order = emit order
@@ -275,7 +279,14 @@ void assemble_chunk(const Bundle& b, uint32_t g0, uint32_t g1, size_t start_buck
     st.total_complete += total; if (total == 1) st.total_unique++;
     for (auto& u : pairs) { u.nh = (uint32_t)total; u.mapq = get_mapq((uint32_t)total, lng); filtered.push_back(&u); }
   }
-  for (Unit* u : filtered) {
+  for (Unit* u : filtered) emit(*u);
+}
+
+// ... + write_to_bam on the host: the record bytes of the chunk
+void assemble_chunk(const Bundle& b, uint32_t g0, uint32_t g1, size_t start_buckets, bool lng, Stats& st, std::vector<uint8_t>& out) {
+  std::vector<uint8_t> aux;
+  replay_chunk(b, g0, g1, start_buckets, lng, st, [&](const Unit& un) {
+    const Unit* u = &un;
     for (int k = 0; k < (u->paired ? 2 : 1); k++) {
       const uint32_t r = u->row + k, other = u->row + (1 - k);
       OutInfo o{}; o.tid = b.tid[r]; o.pos = b.pos[r]; o.strand = (char)b.tstrand[r]; o.paired = u->paired; o.same_tx = b.flags[r] & BRB_REC_SAMETX;
@@ -284,7 +295,15 @@ void assemble_chunk(const Bundle& b, uint32_t g0, uint32_t g1, size_t start_buck
       if (u->paired) { o.mate_tid = b.tid[other]; o.mate_pos = b.pos[other]; }
       assemble_record(b.view(b.src[r]), o, aux, out);
     }
-  }
+  });
+}
+
+// ... or only the ORDER and the tag values, for the engine to build the bytes from its resident rows (brb_emit_in::units)
+void units_of_chunk(const Bundle& b, uint32_t g0, uint32_t g1, size_t start_buckets, bool lng, Stats& st, std::vector<uint32_t>& units) {
+  replay_chunk(b, g0, g1, start_buckets, lng, st, [&](const Unit& u) {
+    if (u.paired && u.hi_m != u.hi_r + 1) throw std::runtime_error("internal: HI of a mate record is not HI + 1");
+    units.push_back(u.row); units.push_back((uint32_t)u.hi_r); units.push_back(u.nh); units.push_back((u.mapq & 0xffu) | (u.primary ? 0x100u : 0u));
+  });
 }
 
 }  // namespace
@@ -326,7 +345,7 @@ int main(int argc, char** argv) {
     const bool timing = getenv("BRB_CLI_TIMING") != nullptr;      // stage seconds on stderr at the end
     using clk = std::chrono::steady_clock;
     auto secs = [](clk::time_point a, clk::time_point b) { return std::chrono::duration<double>(b - a).count(); };
-    double t_read = 0, t_ingest = 0, t_wait_push = 0, t_project = 0, t_store = 0, t_assemble = 0, t_write = 0, t_extract = 0;
+    double t_read = 0, t_ingest = 0, t_wait_push = 0, t_project = 0, t_store = 0, t_assemble = 0, t_write = 0, t_extract = 0, t_emit = 0;
     const auto t_begin = clk::now();
     Stats st; std::mutex m; std::condition_variable cv;
     std::deque<std::shared_ptr<Bundle>> to_ingest;            // cut by the producer, waiting for their columns
@@ -336,6 +355,11 @@ int main(int argc, char** argv) {
     int workers_left = n_gpu;
     const int n_asm = std::max(1, o.threads);
     const bool dev_deflate = getenv("BRB_HOST_DEFLATE") == nullptr;      // BGZF blocks of the output are compressed by the engine when it can
+    // ... and the records themselves are assembled there too (brb_emit_bgzf): the host only replays flush() for the order and the tags
+    const bool dev_emit = dev_deflate && engines[0]->can_emit() && getenv("BRB_HOST_ASSEMBLY") == nullptr;
+    std::vector<std::vector<int>> free_slots(n_gpu);
+    for (int g = 0; g < n_gpu; g++) for (int s2 = engines[g]->slots(); s2-- > 0;) free_slots[g].push_back(s2);
+    int planning = 0;                                         // bundles whose flush chunks are being cut (their chunk tasks are about to appear)
     // ingest of one bundle (reference process_reads, src/bramble.cpp:329-435, per record): read exons, CIGAR words, strand,
     // annotated chromosome, mate links (process_pairs :272-311), group names and -- with -S -- the group-shared sequence
     auto ingest_bundle = [&](Bundle& b) -> std::string {
@@ -379,15 +403,20 @@ int main(int argc, char** argv) {
           if (!err.empty() || (todo[g].empty() && eof && n_ingested == n_cut)) { workers_left--; cv.notify_all(); return; }
           if (todo[g].empty()) continue;
           b = todo[g].front(); todo[g].pop_front(); }
+        // the rows stay resident in one of the engine's slots until the writer has had the records built from them
+        { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return !free_slots[g].empty() || !err.empty(); });
+          if (!err.empty()) { workers_left--; cv.notify_all(); return; }
+          b->slot = free_slots[g].back(); free_slots[g].pop_back(); }
         brb_batch_in bi{}; fill_batch(*b, params.use_fasta, bi); brb_batch_out bo{};
         const auto t0 = clk::now();
-        const int rc = engines[g]->project(params, bi, bo);
+        const int rc = engines[g]->project_slot(b->slot, params, bi, bo);
         const auto t1 = clk::now();
         if (rc == 0) store_result(*b, bo);
         const auto t2 = clk::now();
         std::unique_lock<std::mutex> lk(m);
         t_project += secs(t0, t1); t_store += secs(t1, t2);
         if (rc != 0) { err = engines[g]->last_error(); workers_left--; cv.notify_all(); return; }
+        if (!dev_emit) { free_slots[g].push_back(b->slot); b->slot = -1; }
         to_assemble.push_back(b); cv.notify_all();
       }
     };
@@ -397,12 +426,12 @@ int main(int argc, char** argv) {
     auto assembler = [&]() {
       for (;;) {
         std::shared_ptr<Bundle> b; int what = 0; uint32_t k = 0;       // 1 ingest, 2 plan the chunks of a projected bundle, 3 one chunk
-        { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return !err.empty() || !chunk_tasks.empty() || !to_assemble.empty() || !to_ingest.empty() || workers_left == 0; });
+        { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return !err.empty() || !chunk_tasks.empty() || !to_assemble.empty() || !to_ingest.empty() || (workers_left == 0 && planning == 0); });
           if (!err.empty()) return;
           if (!chunk_tasks.empty()) { b = chunk_tasks.front().first; k = chunk_tasks.front().second; chunk_tasks.pop_front(); what = 3; }
-          else if (!to_assemble.empty()) { b = to_assemble.front(); to_assemble.pop_front(); what = 2; }
+          else if (!to_assemble.empty()) { b = to_assemble.front(); to_assemble.pop_front(); what = 2; planning++; }
           else if (!to_ingest.empty()) { b = to_ingest.front(); to_ingest.pop_front(); what = 1; }
-          else { if (workers_left == 0) return; continue; } }
+          else { if (workers_left == 0 && planning == 0) return; continue; } }
         const auto t0 = clk::now();
         if (what == 1) {
           const std::string e = ingest_bundle(*b);
@@ -412,32 +441,71 @@ int main(int argc, char** argv) {
           todo[b->index % n_gpu].push_back(b); n_ingested++; cv.notify_all();
         } else if (what == 2) {
           plan_chunks(*b);
-          b->parts.assign(b->chunks.size(), std::vector<uint8_t>());
+          if (dev_emit) b->unit_parts.assign(b->chunks.size(), std::vector<uint32_t>()); else b->parts.assign(b->chunks.size(), std::vector<uint8_t>());
           std::unique_lock<std::mutex> lk(m);
           t_assemble += secs(t0, clk::now());
+          planning--;
           b->parts_left = (uint32_t)b->chunks.size();
           if (b->chunks.empty()) b->assembled = true;
           for (uint32_t i = 0; i < b->chunks.size(); i++) chunk_tasks.emplace_back(b, i);
           cv.notify_all();
         } else {
-          Stats bs; assemble_chunk(*b, b->chunks[k].first, b->chunks[k].second, b->chunk_buckets[k], lng, bs, b->parts[k]);
+          Stats bs; std::string e;
+          try {
+            if (dev_emit) units_of_chunk(*b, b->chunks[k].first, b->chunks[k].second, b->chunk_buckets[k], lng, bs, b->unit_parts[k]);
+            else assemble_chunk(*b, b->chunks[k].first, b->chunks[k].second, b->chunk_buckets[k], lng, bs, b->parts[k]);
+          } catch (const std::exception& ex) { e = ex.what(); }
           std::unique_lock<std::mutex> lk(m);
           t_assemble += secs(t0, clk::now());
+          if (!e.empty()) { if (err.empty()) err = e; cv.notify_all(); return; }
           b->dropped += bs.dropped; b->total_complete += bs.total_complete; b->total_unique += bs.total_unique;
-          if (--b->parts_left == 0) { b->assembled = true; b->raw.clear(); b->raw.shrink_to_fit(); }
+          if (--b->parts_left == 0) { b->assembled = true; if (!dev_emit) { b->raw.clear(); b->raw.shrink_to_fit(); } }
           cv.notify_all();
         }
+      }
+    };
+    // device record path: one emitter thread per engine turns its oldest assembled bundle into BGZF blocks (brb_emit_bgzf on the rows the
+    // bundle left in its slot); the writer only appends the blocks in bundle order
+    auto emitter = [&](int g) {                                   // the bundles of engine g, oldest first
+      for (;;) {
+        std::shared_ptr<Bundle> b;
+        auto next = [&]() -> std::shared_ptr<Bundle> {
+          for (auto& x : inflight) if ((int)(x->index % n_gpu) == g && !x->emit_claimed) return x->assembled ? x : nullptr;
+          return nullptr; };
+        { std::unique_lock<std::mutex> lk(m);
+          cv.wait(lk, [&] { return !err.empty() || (eof && inflight.empty()) || next() != nullptr; });
+          if (!err.empty() || (eof && inflight.empty())) return;
+          b = next();
+          if (!b) continue;
+          b->emit_claimed = true; }
+        const auto t1 = clk::now();
+        try {
+          std::vector<uint32_t> units;
+          for (auto& part : b->unit_parts) { units.insert(units.end(), part.begin(), part.end()); std::vector<uint32_t>().swap(part); }
+          if (!units.empty()) {
+            brb_emit_in ei{}; ei.raw = b->raw.data(); ei.raw_bytes = b->raw.size(); ei.rec_off = b->rec_off.data(); ei.rec_len = b->rec_len.data();
+            ei.n_units = (uint32_t)(units.size() / 4); ei.units = units.data();
+            const uint8_t* z = nullptr; size_t zn = 0;
+            engines[g]->emit(b->slot, params, ei, z, zn);
+            b->zout.assign(z, z + zn);
+          }
+        } catch (const std::exception& e) { std::unique_lock<std::mutex> lk(m); if (err.empty()) err = e.what(); cv.notify_all(); return; }
+        std::unique_lock<std::mutex> lk(m);
+        t_emit += secs(t1, clk::now());
+        free_slots[g].push_back(b->slot); b->slot = -1; b->emitted = true; b->raw.clear(); b->raw.shrink_to_fit();
+        cv.notify_all();
       }
     };
     auto writer = [&]() {
       std::vector<uint8_t> joined;
       for (;;) {
         std::shared_ptr<Bundle> b;
-        { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return !err.empty() || (!inflight.empty() && inflight.front()->assembled) || (eof && inflight.empty()); });
+        { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return !err.empty() || (!inflight.empty() && (dev_emit ? inflight.front()->emitted : inflight.front()->assembled)) || (eof && inflight.empty()); });
           if (!err.empty()) return; if (inflight.empty()) return; b = inflight.front(); inflight.pop_front(); cv.notify_all(); }
         const auto t1 = clk::now();
         try {
-          if (dev_deflate) {                                   // a few chunks per call: one upload, one kernel sequence, one download
+          if (dev_emit) { if (!b->zout.empty()) out.write_raw(b->zout.data(), b->zout.size()); }
+          else if (dev_deflate) {                              // a few chunks per call: one upload, one kernel sequence, one download
             size_t k = 0;
             while (k < b->parts.size()) {
               joined.clear();
@@ -454,6 +522,7 @@ int main(int argc, char** argv) {
     };
     std::vector<std::thread> threads; for (int g = 0; g < n_gpu; g++) threads.emplace_back(worker, g);
     for (int i = 0; i < n_asm; i++) threads.emplace_back(assembler);
+    if (dev_emit) for (int g = 0; g < n_gpu; g++) threads.emplace_back(emitter, g);
     std::thread wthread(writer);
 
     auto bundle = std::make_shared<Bundle>(); uint64_t n_bundles = 0;
@@ -525,8 +594,10 @@ int main(int argc, char** argv) {
       const double total = secs(t_begin, clk::now());
       t_ingest = secs(t_begin, t_loop_end) - t_read - t_wait_push;
       fprintf(stderr, "[timing] pipeline %.3fs: producer read+inflate %.3f, record walk %.3f, blocked on queue %.3f | pool: column extraction %.3f, "
-                      "flush replay + assembly %.3f | engine project %.3f, copy-out %.3f | writer (BGZF %s) %.3f | final drain %.3f\n",
-              total, t_read, t_ingest, t_wait_push, t_extract, t_assemble, t_project, t_store, dev_deflate ? "on the device" : "host pool", t_write, secs(t_joined, clk::now()));
+                      "flush replay%s %.3f | engine project %.3f, copy-out %.3f | writer (%s) %.3f%s | final drain %.3f\n",
+              total, t_read, t_ingest, t_wait_push, t_extract, dev_emit ? "" : " + assembly", t_assemble, t_project, t_store,
+              dev_emit ? "records + BGZF on the device" : dev_deflate ? "BGZF on the device" : "BGZF host pool", t_write,
+              dev_emit ? (" + brb_emit_bgzf (emitter threads) " + std::to_string(t_emit)).c_str() : "", secs(t_joined, clk::now()));
     }
     if (!o.quiet) {
       printf("\n[bramble_b200] final report:\n# input alignments:   %llu\n# unmapped reads:     %llu\n# dropped alignments: %llu\n# total alignments:   %llu\n# unique alignments:  %llu\n\n",

@@ -15,6 +15,13 @@ struct EngineIf {
   // BGZF blocks of `n` bytes, compressed by the engine (callable from another thread than project()); false: not available,
   // the caller compresses on the host.  `out` stays valid until the next call.
   virtual bool bgzf_compress(const uint8_t*, size_t, const uint8_t*&, size_t&) { return false; }
+  // Output records assembled AND compressed by the engine from the rows a project_slot() call left resident in `slot`
+  // (brb_emit_bgzf): slots() contexts per engine, so that a bundle's rows can wait on the device for the host's flush order
+  // while the next bundles are projected.  can_emit() false: the caller assembles the records itself.
+  virtual int slots() { return 1; }
+  virtual int project_slot(int, const brb_params& p, const brb_batch_in& in, brb_batch_out& out) { return project(p, in, out); }
+  virtual bool can_emit() { return false; }
+  virtual void emit(int, const brb_params&, const brb_emit_in&, const uint8_t*&, size_t&) {}
 };
 EngineIf* make_engine();
 }  // namespace brbhost

@@ -225,6 +225,34 @@ int brb_ksw_extend(brb_ctx* ctx, uint32_t n, const uint64_t* q_off, const uint8_
  * `*out` points into pinned memory owned by the ctx, valid until the next call on it. */
 int brb_bgzf_compress(brb_ctx* ctx, const uint8_t* data, uint64_t n, const uint8_t** out, uint64_t* out_bytes);
 
+/* Output records on the device: what the reference's write_to_bam builds per row (src/core.cpp:96-212 with update_cigar,
+ * set_mate_info, reverse_complement_bam, set_nh_tag / set_hi_tag / set_as_tag of src/bam.cpp:475-702) from the rows of the
+ * ctx's resident result (the last brb_project / brb_project_resident call, plain columns) and the bundle's INPUT records,
+ * followed by the BGZF encoder above.  The caller keeps what the reference's flush() decides on the host -- the ORDER of the
+ * units and, where it wants, their tag values -- and passes one unit per emitted BamInfo, in output order:
+ *   units[4u + 0]  first row of the unit (a paired unit emits rows r and r + 1: read, then mate)
+ *   units[4u + 1]  HI of its first record (the mate record gets HI + 1, as in the reference's counter)
+ *   units[4u + 2]  NH
+ *   units[4u + 3]  MAPQ | primary << 8
+ * raw / rec_off / rec_len: body of input alignment a (the bytes behind its block_size word) = raw[rec_off[a] .. + rec_len[a]).
+ * The uncompressed record stream (raw_out_bytes bytes, optional) stays in device memory; `*out` = its BGZF blocks in pinned
+ * memory owned by the ctx, valid until the next call on it. */
+/* Hands the resident result rows of `from` over to `to` (another ctx of the same index; a device-to-device copy of a few MB), so
+ * that `from` can project the next bundle while the rows wait for brb_emit_bgzf.  Afterwards `from` holds no result, and the
+ * result in `to` can only be read by brb_emit_bgzf (its batch did not come along). */
+int brb_ctx_move_result(brb_ctx* from, brb_ctx* to);
+
+typedef struct brb_emit_in {
+  const uint8_t*  raw;
+  uint64_t        raw_bytes;
+  const uint64_t* rec_off;              /* n_aln of the resident batch */
+  const uint32_t* rec_len;
+  uint32_t        n_units;
+  const uint32_t* units;                /* 4 * n_units words */
+} brb_emit_in;
+int brb_emit_bgzf(brb_ctx* ctx, const brb_params* params, const brb_emit_in* in, const uint8_t** out, uint64_t* out_bytes,
+                  uint64_t* raw_out_bytes);
+
 /* ---- host-side helpers (no device work) ---- */
 /* Permutation cgranges' IITree::index() applies to one tree: libstdc++ std::sort (unstable) by start
  * only, on the reference's insertion sequence (src/g2t.cpp:57-62).  perm[k] = input index of sorted record k. */

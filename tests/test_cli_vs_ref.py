@@ -148,6 +148,30 @@ def test_cli_is_byte_identical_to_reference(mode):
 
 @needs_ref
 @pytest.mark.gpu
+@pytest.mark.parametrize("env", [{"BRB_HOST_ASSEMBLY": "1"}, {"BRB_HOST_DEFLATE": "1"}, {"BRB_SLOTS": "1"}])
+@pytest.mark.parametrize("mode", ["default", "lr"])
+def test_cli_host_side_output_paths_agree(mode, env):
+    """The default output path builds and compresses the records on the device (brb_emit_bgzf).  The older paths stay selectable and
+    must write the same stream: records assembled by the host pool + device BGZF (BRB_HOST_ASSEMBLY), everything on the host
+    (BRB_HOST_DEFLATE); BRB_SLOTS=1 leaves the device path a single row holder."""
+    wl = common.make_workload(mode, 23, n_names=1500, n_genes=40)
+    d = tempfile.mkdtemp(prefix="brb_cli_")
+    args = write_inputs(wl, d, mode)
+    old = {k: os.environ.get(k) for k in env}
+    os.environ.update(env)
+    try:
+        a, b = run_both(d, CLI, args)
+    finally:
+        for k, v in old.items():
+            if v is None:
+                del os.environ[k]
+            else:
+                os.environ[k] = v
+    assert a == b, explain(a, b, d)
+
+
+@needs_ref
+@pytest.mark.gpu
 def test_cli_multi_bundle_overrides_and_flush_chunks():
     """>100k alignments (two bundles, many 5000-pair flush chunks) + threshold overrides."""
     from bramble_b200 import synth_fast as sf
