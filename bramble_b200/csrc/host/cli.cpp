@@ -319,7 +319,8 @@ int main(int argc, char** argv) {
     IndexColumns cols;
     if (!o.fasta.empty()) load_genome(o.fasta, A, cols.chrom_off, cols.genome);
     build_index_columns(A, cols);
-    BgzfReader in(o.in_bam, std::min(o.threads, 8));
+    const int n_inflate = getenv("BRB_INFLATE_THREADS") ? std::max(1, atoi(getenv("BRB_INFLATE_THREADS"))) : std::min(o.threads, 8);
+    BgzfReader in(o.in_bam, n_inflate);
     const InHeader ih = read_bam_header(in);
     const std::string header = make_header(ih, A, o);
     std::vector<int> ref2refid(ih.ref_names.size(), -1);

@@ -265,6 +265,22 @@ class Engine:
         capi.check(self.lib.brb_bgzf_compress(self._ctx, bytes(data), len(data), C.byref(out), C.byref(n)), "brb_bgzf_compress")
         return C.string_at(out.value, n.value) if n.value else b""
 
+    def emit_bgzf(self, params, raw, rec_off, rec_len, units, ctx=None):
+        """Output records of the resident result (last project() on this engine's ctx, or `ctx`), assembled and BGZF-compressed on the
+        device: raw = the bundle's input record bodies (bytes), rec_off / rec_len per alignment, units = (n, 4) uint32 in output
+        order (first row, HI, NH, MAPQ | primary << 8).  Returns (BGZF bytes, uncompressed size)."""
+        raw = np.frombuffer(bytes(raw) + b"\0", dtype=np.uint8)
+        rec_off = np.ascontiguousarray(rec_off, dtype=np.uint64); rec_len = np.ascontiguousarray(rec_len, dtype=np.uint32)
+        units = np.ascontiguousarray(units, dtype=np.uint32).reshape(-1)
+        ei = capi.EmitIn(raw.ctypes.data, len(raw) - 1, capi.ptr(rec_off if len(rec_off) else np.zeros(1, np.uint64)),
+                         capi.ptr(rec_len if len(rec_len) else np.zeros(1, np.uint32)), len(units) // 4, capi.ptr(units if len(units) else np.zeros(4, np.uint32)))
+        out = C.c_void_p(); n = C.c_uint64(); rawn = C.c_uint64()
+        capi.check(self.lib.brb_emit_bgzf(ctx._ctx if ctx is not None else self._ctx, C.byref(params), C.byref(ei), C.byref(out), C.byref(n), C.byref(rawn)), "brb_emit_bgzf")
+        return (C.string_at(out.value, n.value) if n.value else b""), rawn.value
+
+    def move_result(self, to_ctx):
+        capi.check(self.lib.brb_ctx_move_result(self._ctx, to_ctx._ctx), "brb_ctx_move_result")
+
     def ksw_extend(self, queries, targets, cigar_cap=256):
         n = len(queries)
         q_off = np.concatenate([[0], np.cumsum([len(q) for q in queries])]).astype(np.uint64)

@@ -569,7 +569,10 @@ def _pack_record(r, compute_bin=True):
     for tag, ty, val in r.get("tags", []):
         aux += tag.encode() + ty.encode()
         if ty == "A": aux += val.encode()
-        elif ty == "Z": aux += val.encode() + b"\0"
+        elif ty in ("Z", "H"): aux += val.encode() + b"\0"
+        elif ty == "B":                                  # (subtype, values)
+            sub, vals = val
+            aux += sub.encode() + struct.pack("<I", len(vals)) + struct.pack("<%d%s" % (len(vals), {"c": "b", "C": "B", "s": "h", "S": "H", "i": "i", "I": "I", "f": "f"}[sub]), *vals)
         else: aux += struct.pack("<" + {"c": "b", "C": "B", "s": "h", "S": "H", "i": "i", "I": "I", "f": "f"}[ty], val)
     rl = _rlen(cig) or 1
     b_ = _reg2bin(r["pos"], r["pos"] + rl) if (compute_bin and r["pos"] >= 0) else 4680

@@ -228,6 +228,52 @@ is not emitted (:1075-1076).""")
 aux_carry_through: one read on three isoforms; input tags in odd order and types.  Output aux = input minus NH, XS and HI, in input
 order, then NH:i (record count of the name) and HI:i (src/core.cpp:115-124, src/bam.cpp:590-620).""")
 
+    # 9 -- record bytes: reverse complement of an odd-length read, missing qualities, array / hex / string tags kept, duplicate and
+    #      oddly typed NH / HI / XS, mate fields of pairs on a '-' transcript and across two transcripts
+    ann = synth.Annotation(["chr1"], [300000], [tx("G11.t1", "-", [(260000, 260500), (261000, 261400)]), tx("G11.t2", "+", [(270000, 270600)]),
+                                               tx("G11.t3", "+", [(270000, 270600), (271000, 271200)])])
+    zoo = [("NH", "s", 300), ("XA", "B", ("s", [-3, 7, 30000])), ("XS", "A", "-"), ("HI", "S", 65535), ("MD", "Z", "101"), ("NH", "i", 9), ("XH", "H", "1AE301"),
+           ("XS", "A", "+"), ("XB", "B", ("C", [])), ("XF", "f", 1.25), ("HI", "c", -1)]
+    r_odd = rec("z_odd", 16, 260100, [("M", 101)], tags=zoo)
+    r_noq = rec("z_noq", 0, 260150, [("M", 75)], tags=[("XS", "A", "-")]); r_noq["qual"] = None
+    r_spl = rec("z_spl", 16, 260451, [("M", 50), ("N", 499), ("M", 51)], tags=zoo[2:])
+    recs = [r_odd, r_noq, r_spl,
+            rec("z_pair", 99, 260050, [("M", 99)], 260300, tags=zoo[:4]), rec("z_pair", 147, 260300, [("M", 100)], 260050, tags=[("XS", "A", "-")] + zoo[4:7]),
+            rec("z_two", 99, 270100, [("M", 100)], 270350, tags=[]), rec("z_two", 147, 270350, [("M", 100)], 270100, tags=[("NH", "C", 1)])]
+
+    def chk(got):
+        by = {}
+        for x in got:
+            by.setdefault(x[0], []).append(x)
+        assert len(by["z_odd"]) == 1 and len(by["z_noq"]) == 1 and len(by["z_spl"]) == 1 and len(by["z_pair"]) == 2 and len(by["z_two"]) == 4, {k: len(v) for k, v in by.items()}
+        aux = by["z_odd"][0][5]
+        assert aux.startswith(b"XABs\x03\x00\x00\x00") and b"MDZ101\x00NHi\x09\x00\x00\x00XHH1AE301\x00XSA+XBBC\x00\x00\x00\x00XFf" in aux, aux    # first NH / XS / HI only
+        assert aux.count(b"HIc\xff") == 1 and aux.endswith(b"NHi\x01\x00\x00\x00HIi\x01\x00\x00\x00"), aux
+    fixture("record_bytes_zoo", ann, recs, [], chk, doc="""
+record_bytes_zoo: what write_to_bam does to the bytes of a record (src/core.cpp:96-212, src/bam.cpp:475-702): an odd-length read and a
+spliced read on a '-' transcript (sequence reverse-complemented nibble by nibble, qualities reversed, CIGAR reversed, flag 16 toggled), a read
+without qualities (0xff kept as is), B / H / Z / f tags carried through, only the FIRST NH, XS and HI dropped whatever their type, pairs
+on a '-' transcript (MREVERSE from the own strand, signed TLEN) and a pair that lands on two transcripts twice (4 records).""")
+
+    # 10 -- the same for long reads: ts dropped instead of XS, AS rewritten from its value whatever the integer type
+    ann = synth.Annotation(["chr1"], [300000], [tx("G12.t1", "-", [(280000, 280900)]), tx("G12.t2", "+", [(281500, 282400)])])
+    recs = []
+    for k, (ty, val) in enumerate([("c", -5), ("C", 200), ("s", -300), ("S", 60000), ("i", 123456), ("I", 77)]):
+        recs.append(rec("l%d" % k, 0 if k % 2 else 16, (280100 if k % 3 else 281600) + 10 * k, [("M", 301 + k)],
+                        tags=[("ts", "A", "+"), ("XS", "A", "-"), ("AS", ty, val), ("NM", "i", k), ("ts", "A", "-"), ("AS", "i", 1)]))
+    recs.append(rec("l_noas", 0, 280300, [("M", 250)], tags=[("NM", "i", 3)]))
+
+    def chk(got):
+        assert len(got) == 7, got
+        for x in got:
+            aux = x[5]
+            if x[0] != "l_noas":
+                assert aux.startswith(b"XSA-NMi") and aux.count(b"tsA") == 1 and aux.count(b"ASi") == 2, aux      # first ts and first AS gone, the second ones stay
+            assert aux[-21:-18] == b"NHi" and aux[-14:-11] == b"ASi" and aux[-7:-4] == b"HIi", aux
+    fixture("record_bytes_zoo_lr", ann, recs, ["--lr"], chk, doc="""
+record_bytes_zoo_lr: (--lr) the first ts is dropped (XS stays), the first AS is read as an integer of whatever type it has, dropped, and a new
+AS:i = (AS + clip score) * similarity is appended between NH:i and HI:i (set_as_tag, src/bam.cpp:622-634); a read without AS gets AS:i from 0.""")
+
 
 if __name__ == "__main__":
     main()

@@ -422,3 +422,162 @@ def test_bgzf_device_encoder_round_trips():
             assert got == data, k
             if k in (3, 8):
                 assert len(z) < len(data) // 4, (k, len(z), len(data))          # repeats are found (the BAM case has random bases and qualities)
+
+
+# ---- brb_emit_bgzf: output records assembled on the device
+
+def _aux_skip(a, s):
+    """end of the aux value whose TYPE byte is at a[s], or None (htslib skip_aux)"""
+    if s >= len(a):
+        return None
+    t = chr(a[s]); s += 1
+    size = {"A": 1, "c": 1, "C": 1, "s": 2, "S": 2, "i": 4, "I": 4, "f": 4, "d": 8}
+    if t in "ZH":
+        e = a.find(b"\0", s)
+        return None if e < 0 else e + 1
+    if t == "B":
+        if len(a) - s < 5:
+            return None
+        sz = size.get(chr(a[s]), 0)
+        n = int.from_bytes(a[s + 1:s + 5], "little"); s += 5
+        return None if (not sz or len(a) - s < sz * n) else s + sz * n
+    sz = size.get(t, 0)
+    return None if (not sz or len(a) - s < sz) else s + sz
+
+
+def _aux_find(a, tag):
+    s = 0
+    while s is not None and len(a) - s >= 3:
+        if a[s:s + 2] == tag:
+            return s + 2
+        s = _aux_skip(a, s + 2)
+    return -1
+
+
+def _aux_del(a, tag):
+    o = _aux_find(a, tag)
+    if o < 0:
+        return a
+    e = _aux_skip(a, o)
+    return a if e is None else a[:o - 2] + a[e:]
+
+
+def _py_record(body, lng, tid, pos, minus, paired, same_tx, primary, mapq, nh, hi, sim, clip, cigar, mate_tid, mate_pos):
+    """write_to_bam of the reference for one row, tag edit by tag edit (src/core.cpp:96-212, src/bam.cpp:475-702): an independent
+    restatement for this test (the product's host path is pinned on the reference binary by the CLI tests)."""
+    import struct
+    l_name, n_cig, flag, lq = body[8], struct.unpack_from("<H", body, 12)[0], struct.unpack_from("<H", body, 14)[0], struct.unpack_from("<i", body, 16)[0]
+    p_seq = 32 + l_name + 4 * n_cig; seqb = (lq + 1) // 2
+    seq, qual, aux = body[p_seq:p_seq + seqb], body[p_seq + seqb:p_seq + seqb + lq], bytes(body[p_seq + seqb + lq:])
+    aux = _aux_del(aux, b"NH") + b"NHi" + struct.pack("<i", nh)
+    aux = _aux_del(aux, b"ts" if lng else b"XS")
+    if lng:
+        o = _aux_find(aux, b"AS"); v = 0
+        if o >= 0:
+            t = chr(aux[o]); fmt = {"c": "<b", "C": "<B", "s": "<h", "S": "<H", "i": "<i", "I": "<I"}.get(t)
+            v = struct.unpack_from(fmt, aux, o + 1)[0] if fmt else 0
+            aux = _aux_del(aux, b"AS")
+        aux += b"ASi" + struct.pack("<i", int((float(v) + float(clip)) * sim))
+    aux = _aux_del(aux, b"HI") + b"HIi" + struct.pack("<i", hi)
+    flag = (flag & ~0x100) if primary else (flag | 0x100)
+    if minus:
+        if lq > 0:
+            comp = {1: 8, 8: 1, 2: 4, 4: 2}
+            nib = [(seq[j >> 1] >> (0 if j & 1 else 4)) & 15 for j in range(lq)]
+            rc = [comp.get(n, 15) for n in reversed(nib)] + [0]
+            seq = bytes((rc[2 * k] << 4) | rc[2 * k + 1] for k in range(seqb))
+            if qual[0] != 0xff:
+                qual = qual[::-1]
+        flag ^= 16
+    if not paired:
+        flag &= ~(1 | 2 | 32); mtid, mpos, isize = -1, -1, 0
+    else:
+        flag |= 1
+        if minus:
+            flag |= 32
+        if same_tx:
+            mtid, mpos = tid, mate_pos; flag |= 2
+            isize = (mate_pos + lq) - pos if pos <= mate_pos else -((pos + lq) - mate_pos)
+        else:
+            mtid, mpos, isize = mate_tid, mate_pos, 0; flag &= ~2
+    head = bytearray(body[:32 + l_name])
+    struct.pack_into("<ii", head, 0, tid, pos); head[9] = mapq & 0xff
+    struct.pack_into("<HH", head, 12, len(cigar), flag); struct.pack_into("<iii", head, 20, mtid, mpos, isize)
+    out = bytes(head) + struct.pack("<%dI" % len(cigar), *[int(c) for c in cigar]) + seq + qual + aux
+    return struct.pack("<i", len(out)) + out
+
+
+@pytest.mark.parametrize("mode", ["default", "lr"])
+def test_emit_records_on_device_match_restatement(mode):
+    """brb_emit_bgzf: BAM records built on the device from the resident rows + the input records, then BGZF: inflated, they must be the
+    records a tag-by-tag Python restatement of write_to_bam builds from the downloaded rows -- random aux tag sets (NH / HI / AS / XS / ts
+    in every integer type, duplicates, B / Z / H / f tags, a malformed tail), odd read lengths, missing qualities, arbitrary unit order
+    and tag values.  Also: the rows moved to another ctx first (brb_ctx_move_result), and the error paths."""
+    import zlib
+    from bramble_b200 import synth
+    wl = common.make_workload(mode, 211, n_names=700, n_genes=40)
+    lng = wl["mode"]["long"]
+    rng = np.random.default_rng(5)
+    b = wl["batches"][0]
+    pool = [("NH", "C", 3), ("NH", "i", 70000), ("HI", "s", -2), ("HI", "C", 9), ("AS", "c", -7), ("AS", "S", 40000), ("AS", "i", 250), ("AS", "I", 12), ("NM", "C", 1),
+            ("MD", "Z", "50A49"), ("XH", "H", "0AFF"), ("XB", "B", ("S", [1, 2, 65535])), ("XE", "B", ("i", [])), ("XF", "f", 0.5), ("ZZ", "Z", "")]
+    bodies = []
+    for a, ri in enumerate(b.src):
+        r = dict(wl["recs"][int(ri)])
+        strand_tags = [t for t in r.get("tags", []) if t[0] in ("XS", "ts")]            # (they decide the strand: kept as they are, in front)
+        extra = [pool[int(k)] for k in rng.permutation(len(pool))[:int(rng.integers(0, 9))]]
+        r["tags"] = strand_tags + extra + ([("ts", "A", "+")] if lng and a % 5 == 0 else []) + ([("XS", "A", "-")] if a % 7 == 0 and strand_tags else [])
+        if a % 11 == 0:
+            r["qual"] = None
+        body = synth._pack_record(r)[4:]
+        if a % 13 == 0:
+            body += b"XXZunterminated"                                                   # a tag no walk can skip: everything behind it is out of reach
+        bodies.append(body)
+    rec_len = np.array([len(x) for x in bodies], np.uint32)
+    rec_off = (np.cumsum(rec_len) - rec_len).astype(np.uint64)
+    raw = b"".join(bodies)
+    p = wl["params"]
+    with engine.Engine(wl["index"]) as eng:
+        out = eng.project(p, b, raw=True)                          # rows in the device's own order: that is what a unit's row index means
+        n = int(out.n_rec)
+        o = engine._columns(out, copy=True)
+        co = o["cigar_off"]
+        assert n > 500
+        # units in a shuffled order with arbitrary tag values
+        flags = o["flags"]; firsts = [r for r in range(n) if flags[r] & 1]
+        order = rng.permutation(len(firsts))
+        units = np.array([[firsts[k], int(rng.integers(1, 50)), int(rng.integers(1, 90)), int(rng.integers(0, 256)) | (int(rng.integers(0, 2)) << 8)] for k in order], np.uint32)
+        want = b""
+        for row, hi, nh, mq in units:
+            paired, same = bool(flags[row] & 2), bool(flags[row] & 4)
+            for e in range(2 if paired else 1):
+                r, other = int(row) + e, int(row) + (1 - e)
+                a = int(o["src_aln"][r])
+                want += _py_record(bodies[a], lng, int(o["tid"][r]), int(o["pos"][r]), o["tx_strand"][r] == ord("-"), paired, same, bool(mq >> 8), int(mq) & 255, int(nh), int(hi) + e,
+                                   float(o["sim_score"][r]), int(o["clip_score"][r]), o["cigar"][int(co[r]):int(co[r + 1])], int(o["tid"][other]) if paired else -1, int(o["pos"][other]) if paired else -1)
+
+        def inflate(z):
+            return b"".join(zlib.decompress(pl, -15) for pl, _, _ in _bgzf_blocks(z))
+        z, rawn = eng.emit_bgzf(p, raw, rec_off, rec_len, units)
+        got = inflate(z)
+        assert rawn == len(want) and got == want, (mode, rawn, len(want), next((i for i, (x, y) in enumerate(zip(got, want)) if x != y), None))
+        # the same from a second context that only received the rows
+        holder = engine.Context(eng)                               # (the rows of the projection above: a new one may finish its batches in another order)
+        eng.move_result(holder)
+        z2, _ = eng.emit_bgzf(p, raw, rec_off, rec_len, units, ctx=holder)
+        assert inflate(z2) == want
+        with pytest.raises(capi.EngineError):                      # ... and the source holds no result any more
+            eng.emit_bgzf(p, raw, rec_off, rec_len, units)
+        # error paths: a unit naming a row that does not exist; a record whose fixed fields overrun its length
+        out = eng.project(p, b, raw=True)
+        o = engine._columns(out, copy=True)
+        units = np.array([[r, 1, 1, 255] for r in range(n) if o["flags"][r] & 1], np.uint32)
+        bad = units.copy(); bad[3, 0] = n + 5
+        with pytest.raises(capi.EngineError):
+            eng.emit_bgzf(p, raw, rec_off, rec_len, bad)
+        short = rec_len.copy(); short[int(o["src_aln"][int(units[0, 0])])] = 40
+        with pytest.raises(capi.EngineError):
+            eng.emit_bgzf(p, raw, rec_off, short, units)
+        z3, _ = eng.emit_bgzf(p, raw, rec_off, rec_len, units[:0])
+        assert z3 == b""
+        holder.close()
