@@ -53,7 +53,8 @@ class BatchOut(C.Structure):
                 ("src_aln", u32p), ("tid", u32p), ("pos", u32p), ("tx_strand", i8p), ("flags", u8p),
                 ("sim_score", f64p), ("clip_score", i32p), ("cigar_off", u32p), ("cigar", u32p),
                 ("aln_rec_off", u32p), ("aln_rec_cnt", u32p), ("packed_rows", u32p),
-                ("hi", i32p), ("nh", i32p), ("mapq", u8p), ("primary", u8p)]
+                ("hi", i32p), ("nh", i32p), ("mapq", u8p), ("primary", u8p),
+                ("batch_rec_off", u32p), ("aln_rec_cnt16", C.POINTER(C.c_uint16))]
 
 
 class Stats(C.Structure):

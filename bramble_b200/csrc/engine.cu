@@ -101,7 +101,7 @@ struct brb_ctx {
   Buf e_raw, e_off, e_len, e_units, e_plan, e_sizes, e_offs, e_err;                // brb_emit_bgzf
   bool have_names = false, opt_flush_tags = false, result_tags = false;
   uint64_t in_bytes = 0, n_mates = 0, seq_bytes = 0, rescue_bytes = 0;
-  bool have_batch = false, have_result = false, have_scores = false, opt_generic_front = false, opt_no_fastpath = false, opt_ordered = false, result_ordered = false, opt_packed = false, result_packed = false, opt_merge_warp = false;
+  bool have_batch = false, have_result = false, have_scores = false, opt_generic_front = false, opt_no_fastpath = false, opt_ordered = false, result_ordered = false, opt_packed = false, result_packed = false, opt_merge_warp = false, opt_compact = false, result_compact = false;
   // control block + pools (capacities persist across calls and only grow)
   Buf ctl;
   uint32_t cap_cand = 0, cap_ideal = 0, cap_rows = 0, cap_tmpw = 0, cap_outw = 0, cap_tb = 0;
@@ -356,7 +356,7 @@ static int batch_upload_async(brb_ctx* c, const brb_batch_in* in) {
   b.exon_off = c->in_exon_off.as<uint32_t>(); b.exon_st = c->in_exon_st.as<uint32_t>(); b.exon_en = c->in_exon_en.as<uint32_t>();
   b.cigar_off = c->in_cigar_off.as<uint32_t>(); b.cigar = c->in_cigar.as<uint32_t>(); b.mate_idx = c->in_mate.as<int32_t>();
   b.group_seq_off = have_seq ? c->in_seq_off.as<uint64_t>() : nullptr; b.seq = have_seq ? c->in_seq.as<uint8_t>() : nullptr;
-  b.aln_group = nullptr; b.back_shift = 5; b.count_hits = 0;
+  b.aln_group = nullptr; b.back_shift = 5; b.count_hits = 0; b.compact_rows = 0;
   c->stats.h2d_bytes = c->in_bytes;
   c->have_batch = true;
   return BRB_OK;
@@ -410,6 +410,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   if (rescue && !c->idx->d.genome) return fail(BRB_E_UNSUPPORTED, "use_fasta requested but the index holds no genome");
   if (rescue && c->b.n_aln && !c->b.seq) return fail(BRB_E_UNSUPPORTED, "use_fasta requested but the batch carries no read sequences");
   c->b.count_hits = c->opt_generic_front ? 1u : 0u;
+  c->b.compact_rows = (c->opt_compact && c->opt_packed && !c->opt_ordered && !p.long_reads) ? 1u : 0u;
   c->b.back_shift = p.long_reads ? 3u : 5u;           // long reads: 8 alignments per k_back batch (rows of 10^2..10^4 CIGAR words)
   const DevBatch& b = c->b; const DevIndex& ix = c->idx->d;
   cudaStream_t st = c->st;
@@ -422,7 +423,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   if (n == 0) {
     ENS(c->g_roff, (size_t)(b.n_groups + 1) * 4); ENS(c->o_coff, 4);
     CU(cudaMemsetAsync(c->g_roff.p, 0, 4, st)); CU(cudaMemsetAsync(c->o_coff.p, 0, 4, st)); CU(cudaStreamSynchronize(st));
-    c->have_result = true; c->res_n_aln = c->b.n_aln; c->res_foreign = false; c->rv = RowView{c->o_src.as<uint32_t>(), c->o_tid.as<uint32_t>(), c->o_pos.as<uint32_t>(), c->o_strand.as<int8_t>(), c->o_flags.as<uint8_t>(), c->have_scores ? c->o_sim.as<double>() : nullptr, c->have_scores ? c->o_clip.as<int32_t>() : nullptr, c->o_coff.as<uint32_t>(), c->opool.as<uint32_t>()}; c->result_ordered = c->opt_ordered; c->result_packed = c->opt_packed && !c->opt_ordered; return BRB_OK;
+    c->have_result = true; c->res_n_aln = c->b.n_aln; c->res_foreign = false; c->rv = RowView{c->o_src.as<uint32_t>(), c->o_tid.as<uint32_t>(), c->o_pos.as<uint32_t>(), c->o_strand.as<int8_t>(), c->o_flags.as<uint8_t>(), c->have_scores ? c->o_sim.as<double>() : nullptr, c->have_scores ? c->o_clip.as<int32_t>() : nullptr, c->o_coff.as<uint32_t>(), c->opool.as<uint32_t>()}; c->result_ordered = c->opt_ordered; c->result_packed = c->opt_packed && !c->opt_ordered; c->result_compact = false; return BRB_OK;
   }
   if (!c->cap_cand) {           // first guess from the batch shape; a pool that overflows grows and the sequence replays
     c->cap_cand = grown((uint64_t)12 * n); c->cap_rows = grown((uint64_t)6 * n);
@@ -568,6 +569,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
     c->result_tags = true;
   }
   if (hres->bad_input == 3) return fail(BRB_E_UNSUPPORTED, "a batch of 32 alignments emits 2^28 or more CIGAR words");
+  if (hres->bad_input == 6) return fail(BRB_E_UNSUPPORTED, "BRB_OPT_PACKED_ROWS = 2: a unit of 65536 rows or more; project the bundle with the option at 0 or 1");
   if (hres->bad_input == 4) return fail(BRB_E_UNSUPPORTED, "BRB_OPT_PACKED_ROWS: the bundle pools 2^27 or more CIGAR words; project it without the option");
   if (hres->bad_input == 5) return fail(BRB_E_ARG, "CSR offsets (group_off / exon_off / cigar_off) must start at 0, be non-decreasing and end at the column sizes");
   if (hres->bad_input == 1) return fail(BRB_E_ARG, "mate_idx is not a symmetric single link (src/bramble.cpp:272-311)");
@@ -583,7 +585,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   S.alg_bytes_front = (uint64_t)n * 16 + (uint64_t)b.n_exon * 8 + hres->n_mates * 4 + hres->n_hits * 56;
   S.alg_bytes = S.alg_bytes_front + (uint64_t)b.n_cigar * 4 + (uint64_t)hres->n_rows * 40 + hres->out_words * 4 + hres->rescue_bytes;
   S.ksw_cells = hres->ksw_cells; S.host_syncs = n_syncs;
-  c->have_result = true; c->res_n_aln = c->b.n_aln; c->res_foreign = false; c->rv = RowView{c->o_src.as<uint32_t>(), c->o_tid.as<uint32_t>(), c->o_pos.as<uint32_t>(), c->o_strand.as<int8_t>(), c->o_flags.as<uint8_t>(), c->have_scores ? c->o_sim.as<double>() : nullptr, c->have_scores ? c->o_clip.as<int32_t>() : nullptr, c->o_coff.as<uint32_t>(), c->opool.as<uint32_t>()}; c->result_ordered = ordered; c->result_packed = packed;
+  c->have_result = true; c->res_n_aln = c->b.n_aln; c->res_foreign = false; c->rv = RowView{c->o_src.as<uint32_t>(), c->o_tid.as<uint32_t>(), c->o_pos.as<uint32_t>(), c->o_strand.as<int8_t>(), c->o_flags.as<uint8_t>(), c->have_scores ? c->o_sim.as<double>() : nullptr, c->have_scores ? c->o_clip.as<int32_t>() : nullptr, c->o_coff.as<uint32_t>(), c->opool.as<uint32_t>()}; c->result_ordered = ordered; c->result_packed = packed; c->result_compact = packed && c->b.compact_rows;
   return BRB_OK;
 }
 
@@ -608,12 +610,12 @@ int brb_batch_download(brb_ctx* c, brb_batch_out* out) {
   const bool sc = c->have_scores && R;
   auto al = [](size_t x) { return (x + 15) & ~(size_t)15; };
   size_t off = 0;
-  const bool ord = c->result_ordered, pk = c->result_packed;
-  const size_t N = c->b.n_aln;
+  const bool ord = c->result_ordered, pk = c->result_packed, cm = c->result_compact;
+  const size_t N = c->b.n_aln, NB = (N + 31) >> 5;
   const size_t o_groff = off; off += ord ? al((G + 1) * 4) : 0;
-  const size_t o_aoff = off; off += al(N * 4);
-  const size_t o_acnt = off; off += al(N * 4);
-  const size_t o_prow = off; off += pk ? al(R * 16) : 0;
+  const size_t o_aoff = off; off += al(cm ? NB * 4 : N * 4);              // compact: one row offset per batch of 32 alignments ...
+  const size_t o_acnt = off; off += al(cm ? N * 2 : N * 4);               // ... and 16-bit unit sizes
+  const size_t o_prow = off; off += pk ? al(R * (cm ? 12 : 16)) : 0;
   const size_t o_src = off; off += pk ? 0 : al(R * 4);
   const size_t o_tid = off; off += pk ? 0 : al(R * 4);
   const size_t o_pos = off; off += pk ? 0 : al(R * 4);
@@ -637,9 +639,9 @@ int brb_batch_download(brb_ctx* c, brb_batch_out* out) {
     bytes += n; return 0;
   };
   int rc = ord ? dn(o_groff, c->g_roff, (G + 1) * 4) : 0;
-  if (!rc) rc = dn(o_aoff, c->a_roff, N * 4);
-  if (!rc) rc = dn(o_acnt, c->a_rcnt, N * 4);
-  if (!rc && pk) rc = dn(o_prow, c->p_row, R * 16);
+  if (!rc) rc = dn(o_aoff, c->a_roff, cm ? NB * 4 : N * 4);
+  if (!rc) rc = dn(o_acnt, c->a_rcnt, cm ? N * 2 : N * 4);
+  if (!rc && pk) rc = dn(o_prow, c->p_row, R * (cm ? 12 : 16));
   if (!rc && !pk) rc = dn(o_src, c->o_src, R * 4);
   if (!rc && !pk) rc = dn(o_tid, c->o_tid, R * 4);
   if (!rc && !pk) rc = dn(o_pos, c->o_pos, R * 4);
@@ -657,7 +659,8 @@ int brb_batch_download(brb_ctx* c, brb_batch_out* out) {
   CU(cudaStreamSynchronize(c->st));
   out->n_rec = (uint32_t)R; out->n_cigar_words = W;
   out->group_rec_off = ord ? (const uint32_t*)(h + o_groff) : nullptr;
-  out->aln_rec_off = (const uint32_t*)(h + o_aoff); out->aln_rec_cnt = (const uint32_t*)(h + o_acnt);
+  out->aln_rec_off = cm ? nullptr : (const uint32_t*)(h + o_aoff); out->aln_rec_cnt = cm ? nullptr : (const uint32_t*)(h + o_acnt);
+  out->batch_rec_off = cm ? (const uint32_t*)(h + o_aoff) : nullptr; out->aln_rec_cnt16 = cm ? (const uint16_t*)(h + o_acnt) : nullptr;
   out->packed_rows = pk ? (const uint32_t*)(h + o_prow) : nullptr;
   out->src_aln = pk ? nullptr : (const uint32_t*)(h + o_src); out->tid = pk ? nullptr : (const uint32_t*)(h + o_tid);
   out->pos = pk ? nullptr : (const uint32_t*)(h + o_pos); out->tx_strand = pk ? nullptr : (const int8_t*)(h + o_strand); out->flags = pk ? nullptr : h + o_flags;
@@ -680,7 +683,7 @@ int brb_ctx_set_option(brb_ctx* c, int option, int value) {
   if (option == BRB_OPT_GENERIC_FRONT) { c->opt_generic_front = value != 0; return BRB_OK; }
   if (option == BRB_OPT_NO_FASTPATH) { c->opt_no_fastpath = value != 0; return BRB_OK; }
   if (option == BRB_OPT_ORDERED_ROWS) { c->opt_ordered = value != 0; return BRB_OK; }
-  if (option == BRB_OPT_PACKED_ROWS) { c->opt_packed = value != 0; return BRB_OK; }
+  if (option == BRB_OPT_PACKED_ROWS) { c->opt_packed = value != 0; c->opt_compact = value == 2; return BRB_OK; }
   if (option == BRB_OPT_MERGE_WARP) { c->opt_merge_warp = value != 0; return BRB_OK; }
   if (option == BRB_OPT_FLUSH_TAGS) { c->opt_flush_tags = value != 0; return BRB_OK; }
   return fail(BRB_E_ARG, "unknown option %d", option);

@@ -312,6 +312,11 @@ __global__ void __launch_bounds__(256, LONG ? 3 : VAR_BACK_CTAS) k_back(DevBatch
     claim = __shfl_sync(0xffffffffu, claim, 0);
     const uint32_t prow0 = (uint32_t)claim, pword0 = (uint32_t)(claim >> 32);
     const uint32_t row0 = prow0 + irows - rows, word0 = pword0 + iwords - words;
+    if (PACKED && !LONG && b.compact_rows) {                  // one row offset per batch + 16-bit unit sizes (units follow each other in alignment order)
+      if (in_batch) reinterpret_cast<uint16_t*>(o.a_rcnt)[a] = (uint16_t)rows;
+      if (lane == 0) o.a_roff[wb] = prow0;
+      if (__any_sync(0xffffffffu, rows > 0xffffu)) { if (lane == 0) atomicMax(&ctl->bad_input, 6u); __syncwarp(); continue; }
+    } else
     if (in_batch) { o.a_roff[a] = ORDERED ? irows - rows : row0; o.a_rcnt[a] = rows; }     // ORDERED: batch-relative, k_place adds the first row of the batch
     if (ORDERED && W_b >= (1u << 28)) { if (lane == 0) atomicMax(&ctl->bad_input, 3u); __syncwarp(); continue; }
     if (PACKED && (unsigned long long)pword0 + W_b >= (1u << 27)) { if (lane == 0) atomicMax(&ctl->bad_input, 4u); __syncwarp(); continue; }
@@ -359,7 +364,9 @@ __global__ void __launch_bounds__(256, LONG ? 3 : VAR_BACK_CTAS) k_back(DevBatch
             pv_.row[r] = make_uint4(aln, m.w, m.x, (wpos - pword0) | (minus << 28) | (fl << 29));
             if (v.m_sim) { pv_.sim[r] = v.m_sim[cc]; pv_.clip[r] = v.m_clip[cc]; }
           } else if (PACKED) {
-            st_stream(&pv_.row[r], make_uint4(aln, m.w, m.x, (inl ? (m.z | BRB_ROW_INLINE) : wpos) | (minus << 28) | (fl << 29)));
+            const uint32_t w = (inl ? (m.z | BRB_ROW_INLINE) : wpos) | (minus << 28) | (fl << 29);
+            if (b.compact_rows) { uint32_t* q = reinterpret_cast<uint32_t*>(pv_.row) + 3 * (size_t)r; st_stream(q, m.w); st_stream(q + 1, m.x); st_stream(q + 2, w); }
+            else st_stream(&pv_.row[r], make_uint4(aln, m.w, m.x, w));
             if (v.m_sim) { o.sim[r] = v.m_sim[cc]; o.clip[r] = v.m_clip[cc]; }
             if (!inl) pool[wpos++] = len;                     // length word, then the CIGAR
           } else {

@@ -8,10 +8,26 @@ import numpy as np
 from . import capi
 
 
-def _columns(o, copy=False):
+def _unit_blocks(o, n_aln):
+    """(first row, rows) of the unit block owned by every alignment: aln_rec_off / aln_rec_cnt, or -- BRB_OPT_PACKED_ROWS = 2 --
+    rebuilt from one row offset per batch of 32 alignments and the 16-bit unit sizes."""
+    if getattr(o, "aln_rec_cnt16", None):
+        cnt = np.ctypeslib.as_array(o.aln_rec_cnt16, shape=(n_aln,)).astype(np.int64)
+        nb = (n_aln + 31) // 32
+        boff = np.ctypeslib.as_array(o.batch_rec_off, shape=(nb,)).astype(np.int64)
+        pad = np.zeros(nb * 32, np.int64); pad[:n_aln] = cnt
+        within = np.cumsum(pad.reshape(nb, 32), axis=1) - pad.reshape(nb, 32)
+        return (boff[:, None] + within).reshape(-1)[:n_aln], cnt
+    if n_aln == 0:
+        return np.zeros(0, np.int64), np.zeros(0, np.int64)
+    return (np.ctypeslib.as_array(o.aln_rec_off, shape=(n_aln,)).astype(np.int64), np.ctypeslib.as_array(o.aln_rec_cnt, shape=(n_aln,)).astype(np.int64))
+
+
+def _columns(o, copy=False, batch=None):
     """Row columns of a raw brb_batch_out in MEMORY order, whichever layout it came in: the structure-of-arrays columns,
     or BRB_OPT_PACKED_ROWS records (include/bramble_b200.h) unpacked into the same columns (a dense CIGAR CSR rebuilt
-    from the in-record words and the length-prefixed pool)."""
+    from the in-record words and the length-prefixed pool).  The compact layout (option value 2) leaves the source alignment
+    out: it follows from the unit blocks and the batch's mate links, so `batch` is needed."""
     n, W = int(o.n_rec), int(o.n_cigar_words)
 
     def arr(p, cnt, dt=None):
@@ -24,7 +40,19 @@ def _columns(o, copy=False):
         d.update(src_aln=arr(o.src_aln, n), tid=arr(o.tid, n), pos=arr(o.pos, n), tx_strand=arr(o.tx_strand, n, np.int8),
                  flags=arr(o.flags, n, np.uint8), cigar_off=arr(o.cigar_off, n + 1).astype(np.int64), cigar=arr(o.cigar, W))
         return d
-    pr = arr(o.packed_rows, 4 * n).reshape(n, 4)
+    compact = bool(getattr(o, "aln_rec_cnt16", None))
+    if compact:
+        p3 = arr(o.packed_rows, 3 * n).reshape(n, 3)
+        assert batch is not None, "compact rows: the batch is needed to name the source alignments"
+        n_aln = int(batch.desc.n_aln)
+        aoff, acnt = _unit_blocks(o, n_aln)
+        owner = np.zeros(n, np.int64)
+        owner[(np.repeat(aoff, acnt) + (np.arange(int(acnt.sum())) - np.repeat(np.cumsum(acnt) - acnt, acnt)))] = np.repeat(np.arange(n_aln), acnt)
+        first = ((p3[:, 2] >> 29) & 1) == 1
+        src = np.where(first, owner, batch.arrays["mate_idx"].astype(np.int64)[owner]).astype(np.uint32)
+        pr = np.concatenate([src[:, None], p3], axis=1)
+    else:
+        pr = arr(o.packed_rows, 4 * n).reshape(n, 4)
     w = pr[:, 3]
     inline, val = ((w >> 27) & 1) == 1, (w & 0x07FFFFFF).astype(np.int64)
     pool = arr(o.cigar, W)
@@ -53,13 +81,13 @@ def _rows(o, batch):
         if cnt == 0 or not p:
             return np.zeros(cnt, dtype=dt)
         return np.ctypeslib.as_array(p, shape=(cnt,)).astype(dt, copy=True)
-    aoff, acnt = arr(o.aln_rec_off, n_aln, np.int64), arr(o.aln_rec_cnt, n_aln, np.int64)
+    aoff, acnt = _unit_blocks(o, n_aln)
     assert int(acnt.sum()) == n, "unit blocks do not cover the rows"
     start = np.cumsum(acnt) - acnt
     order = np.repeat(aoff - start, acnt) + np.arange(n, dtype=np.int64)        # row index in memory of the k-th row in emit order
     go = batch.arrays["group_off"].astype(np.int64)[:n_groups + 1]
     cum = np.concatenate([[0], np.cumsum(acnt)])
-    col = _columns(o, copy=True)
+    col = _columns(o, copy=True, batch=batch)
     d = dict(n_rec=n, group_rec_off=cum[go].astype(np.uint32) if n_aln else np.zeros(n_groups + 1, np.uint32))
     for k in ("src_aln", "tid", "pos", "tx_strand", "flags", "sim_score", "clip_score"):
         d[k] = col[k][order]
@@ -105,14 +133,14 @@ class Context:
             self._ctx = C.c_void_p()
 
 
-def rows_checksum(o, src_offset=0):
+def rows_checksum(o, src_offset=0, batch=None):
     """Order-independent 64-bit checksum of the rows of a raw brb_batch_out (sum of a per-row mix of source alignment,
     tid, pos, strand, flags, similarity score bits, clip score, CIGAR length and CIGAR words): equal for any layout of
     the same row set."""
     n = int(o.n_rec)
     if n == 0:
         return 0, 0
-    c = _columns(o)
+    c = _columns(o, batch=batch)
     M = np.uint64(0x9E3779B97F4A7C15)
     with np.errstate(over="ignore"):
         co = c["cigar_off"].astype(np.uint64)
@@ -146,7 +174,7 @@ def project_pipelined(contexts, params, bundles, raw=True, checksum=False):
             if not raw:
                 return o
             st = c.stats()
-            cs = rows_checksum(o, b.src_offset)[0] if checksum else 0
+            cs = rows_checksum(o, b.src_offset, batch=b)[0] if checksum else 0
             return (int(o.n_rec), int(o.n_cigar_words), int(st.h2d_bytes), int(st.d2h_bytes), cs)
         finally:
             free.put(c)

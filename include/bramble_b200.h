@@ -130,6 +130,10 @@ typedef struct brb_batch_out {
   const uint8_t*  mapq;                 /* get_mapq(nh) (src/core.cpp:46-58) */
   const uint8_t*  primary;              /* 1: the record belongs to the name's primary unit, 0: secondary, 2: tie whose library draw would
                                          * have been rejected and repeated (probability k / 2^64): the caller decides that name itself */
+  /* BRB_OPT_PACKED_ROWS = 2 only (else NULL; aln_rec_off / aln_rec_cnt are then NULL instead): */
+  const uint32_t* batch_rec_off;        /* (n_aln + 31) / 32: first row of the units owned by alignments 32k .. 32k + 31; their blocks follow
+                                         * each other in alignment order */
+  const uint16_t* aln_rec_cnt16;        /* n_aln: rows of the unit owned by alignment a */
 } brb_batch_out;
 
 /* BRB_OPT_PACKED_ROWS: the row columns as ONE 16-byte record per row -- a third fewer bytes device->host, which is what
@@ -137,6 +141,10 @@ typedef struct brb_batch_out {
  * through aln_rec_off / aln_rec_cnt as usual.  A merged CIGAR of one word below 2^27 (every plain short-read row:
  * one M) sits in w itself; any other CIGAR is in `cigar` behind a length word: cigar[i] = n, cigar[i+1 .. i+n] =
  * the words, i = BRB_ROW_CIGAR(w).  n_cigar_words counts the pool with its length words. */
+/* BRB_OPT_PACKED_ROWS = 2 ("compact", short-read modes): 12 bytes per row, packed_rows[3r .. 3r+2] = { tid, pos, w } -- the source
+ * alignment is implied by the unit block the row sits in (BRB_REC_FIRST rows belong to the owner a, the others to mate_idx[a]) --
+ * and the unit blocks are found through batch_rec_off / aln_rec_cnt16 (2.1 bytes per alignment instead of 8).  Another quarter
+ * off the device->host bytes. */
 #define BRB_ROW_FLAGS(w)   ((uint32_t)(w) >> 29)                 /* BRB_REC_* */
 #define BRB_ROW_MINUS(w)   (((uint32_t)(w) >> 28) & 1u)          /* tx_strand == '-' */
 #define BRB_ROW_INLINE     (1u << 27)                            /* set: BRB_ROW_CIGAR(w) is the CIGAR word itself */
