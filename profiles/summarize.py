@@ -1,8 +1,10 @@
 #!/usr/bin/env python
 """Round summary from the ncu artefacts a gpurun call brought back:
-  summarize.py TAG launches.csv full.ncu-rep bench.json  ->  profiles/TAG_launches.csv, TAG_traffic.json, TAG_summary.md"""
+  summarize.py TAG launches.csv full.ncu-rep bench.json ["bench.py arguments of the profiled command"]
+  ->  profiles/TAG_launches.csv, TAG_traffic.json, TAG_summary.md"""
 import csv, io, json, os, re, subprocess, sys
 tag, launches, rep, bench = sys.argv[1:5]
+cmd_args = sys.argv[5] if len(sys.argv) > 5 else "--steps 2 --warmup 3 --no-cpu-baseline --no-e2e --no-workloads"
 here = os.path.dirname(os.path.abspath(__file__))
 rows = [r for r in csv.reader(open(launches, errors="replace")) if len(r) > 10 and r[0].isdigit()]
 agg = {}
@@ -14,12 +16,12 @@ for r in rows:
     elif unit in ("ms", "msecond"): us *= 1e3
     a = agg.setdefault(name, [0, 0.0]); a[0] += 1; a[1] += us
 open(os.path.join(here, tag + "_launches.csv"), "w").write(open(launches, errors="replace").read())
-generic = [k for k in agg if "k_front<" in k]
+generic = ([k for k in agg if "k_front<1>" in k] if "k_front_fast" in agg else []) + [k for k in agg if k.startswith(("k_index_", "k_validate_batch", "k_pack_genome", "at::"))]    # once per index / upload: not part of a step
 step_total = sum(v[1] for k, v in agg.items() if k not in generic)
 md = [f"# {tag}: ncu summary\n"]
-md.append("Launch list: `ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e`")
-md.append(f"(raw list: {tag}_launches.csv; per-launch times are cold-cache + serialised, compare shares; `--no-e2e` keeps the list to the resident leg the bench line's `value` is timed on).  The generic front kernel `k_front<1>` runs ONCE, untimed,")
-md.append("to obtain the reference-defined algorithmic byte count; shares exclude it.\n")
+md.append(f"Launch list: `ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv python bench.py {cmd_args}`")
+md.append(f"(raw list: {tag}_launches.csv; per-launch times are cold-cache + serialised, compare shares; `--no-e2e` keeps the list to the resident leg the bench line's `value` is timed on).  The generic front kernel `k_front<1>` (short-read workloads) runs ONCE, untimed,")
+md.append("to obtain the reference-defined algorithmic byte count; shares exclude it and the once-per-index / once-per-upload kernels (`k_index_*`, `k_validate_batch`).\n")
 md.append("| kernel | launches | total us | share of step | avg us |\n|---|---|---|---|---|")
 for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1]):
     md.append(f"| {k} | {v[0]} | {v[1]:.1f} | {'-' if k in generic else f'{v[1] / step_total:.3f}'} | {v[1] / v[0]:.1f} |")
