@@ -87,6 +87,7 @@ struct DevBatch {
   const uint32_t* cigar_off; const uint32_t* cigar; const int32_t* mate_idx;
   const uint64_t* group_seq_off; const uint8_t* seq; const uint32_t* aln_group;
   uint32_t back_shift;           // k_back / k_place: log2 of the alignments per batch (5 for short reads, 3 for long reads)
+  uint32_t front_shift;          // k_front: the same for the front kernel (long reads: 3, or 0 when the engine has measured that to be faster on this data)
   uint32_t compact_rows;         // k_back<.., PACKED, ..>: 12-byte rows without the source alignment, 16-bit unit sizes and one row offset per batch (BRB_OPT_PACKED_ROWS = 2)
   uint32_t count_hits;           // k_front: count EVERY index hit of every read exon (the reference-defined figure); else later exons stop at the first survivor
 };

@@ -116,6 +116,7 @@ struct brb_ctx {
   RescueBufs* rb = nullptr;
   uint32_t n_cand = 0, n_rec = 0; uint64_t n_out_words = 0;
   RowView rv{}; Buf res_slab;         // where the rows of the resident result are: the o_* buffers, or res_slab after brb_ctx_move_result
+  uint32_t tune_calls = 0; float tune_ms[2] = {0.f, 0.f};      // long reads: front-kernel time per alignment with 8 / 1 alignments per ticket
   uint32_t res_n_aln = 0; bool res_foreign = false;      // alignments of the batch the resident result belongs to; result moved in from another ctx (brb_ctx_move_result)
   brb_stats stats{};
   std::vector<Buf*> all() {
@@ -356,7 +357,7 @@ static int batch_upload_async(brb_ctx* c, const brb_batch_in* in) {
   b.exon_off = c->in_exon_off.as<uint32_t>(); b.exon_st = c->in_exon_st.as<uint32_t>(); b.exon_en = c->in_exon_en.as<uint32_t>();
   b.cigar_off = c->in_cigar_off.as<uint32_t>(); b.cigar = c->in_cigar.as<uint32_t>(); b.mate_idx = c->in_mate.as<int32_t>();
   b.group_seq_off = have_seq ? c->in_seq_off.as<uint64_t>() : nullptr; b.seq = have_seq ? c->in_seq.as<uint8_t>() : nullptr;
-  b.aln_group = nullptr; b.back_shift = 5; b.count_hits = 0; b.compact_rows = 0;
+  b.aln_group = nullptr; b.back_shift = 5; b.front_shift = 5; b.count_hits = 0; b.compact_rows = 0;
   c->stats.h2d_bytes = c->in_bytes;
   c->have_batch = true;
   return BRB_OK;
@@ -396,7 +397,7 @@ int ensure_pools(brb_ctx* c, bool rescue) {
   if (c->opt_packed) ENS(c->p_row, R * 16);
   ENS(c->m_rec, C * 16);
   if (c->have_scores) { ENS(c->m_sim, C * 8); ENS(c->m_clip, C * 4); ENS(c->o_sim, R * 8); ENS(c->o_clip, R * 4); if (c->opt_ordered) { ENS(c->p_sim, R * 8); ENS(c->p_clip, R * 4); } }
-  if (rescue || c->b.back_shift == 3) { ENS(c->c_rec, C * 4); ENS(c->c_task, C * 4); ENS(c->c_first, C * 4); ENS(c->c_last, C * 4); ENS(c->c_nseg, C * 4); ENS(c->c_nguide, C * 4); ENS(c->c_cap, C * 4); }
+  if (rescue || c->b.back_shift < 5) { ENS(c->c_rec, C * 4); ENS(c->c_task, C * 4); ENS(c->c_first, C * 4); ENS(c->c_last, C * 4); ENS(c->c_nseg, C * 4); ENS(c->c_nguide, C * 4); ENS(c->c_cap, C * 4); }
   ENS(c->ipool, (size_t)c->cap_ideal * 4);
   ENS(c->o_src, R * 4); ENS(c->o_tid, R * 4); ENS(c->o_pos, R * 4); ENS(c->o_strand, R); ENS(c->o_flags, R);
   ENS(c->o_coff, (R + 1) * 4);
@@ -411,6 +412,17 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   if (rescue && c->b.n_aln && !c->b.seq) return fail(BRB_E_UNSUPPORTED, "use_fasta requested but the batch carries no read sequences");
   c->b.count_hits = c->opt_generic_front ? 1u : 0u;
   c->b.compact_rows = (c->opt_compact && c->opt_packed && !c->opt_ordered && !p.long_reads) ? 1u : 0u;
+  // Long reads: the front kernel takes 8 alignments per ticket, or 1 -- which is faster depends on the data (ONT-like bundles: 8, 0.09 vs
+  // 0.23 ms; bundles whose work sits in a few reads of 200-isoform genes: 1, 0.45 vs 0.73 ms), and nothing in the batch says which.  So
+  // each context measures: first call 8, second call 1, then the faster one per alignment, probed again every 64 calls.  The results do
+  // not depend on the choice (BRB_FRONT_SHIFT pins it).
+  static const int pin_shift = [] { const char* e = getenv("BRB_FRONT_SHIFT"); return e ? std::max(0, std::min(5, atoi(e))) : -1; }();
+  uint32_t fshift = 5;
+  if (p.long_reads) {
+    const uint32_t k = c->tune_calls % 64;
+    fshift = pin_shift >= 0 ? (uint32_t)pin_shift : k == 0 ? 3u : k == 1 ? 0u : (c->tune_ms[1] < c->tune_ms[0] ? 0u : 3u);
+  }
+  c->b.front_shift = fshift;
   c->b.back_shift = p.long_reads ? 3u : 5u;           // long reads: 8 alignments per k_back batch (rows of 10^2..10^4 CIGAR words)
   const DevBatch& b = c->b; const DevIndex& ix = c->idx->d;
   cudaStream_t st = c->st;
@@ -578,6 +590,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   S.n_candidates = hres->n_cand; S.n_rec = hres->n_rows; S.n_launches = L; S.n_matches = hres->n_matches; S.n_rescue = hres->n_rescue;
   const cudaEvent_t ev_front_end = one_front ? c->ev[1] : c->ev[4], ev_end = back_finishes ? c->ev[5] : c->ev[6];
   S.ms_lookup = ms_between(c->ev[0], c->ev[1]);
+  if (p.long_reads && n) { c->tune_ms[c->b.front_shift == 0 ? 1 : 0] = S.ms_lookup / (float)n; c->tune_calls++; }
   if (!one_front) { S.ms_chain = ms_between(c->ev[1], c->ev[2]); S.ms_rescue = ms_between(c->ev[2], c->ev[3]); S.ms_finalize = ms_between(c->ev[3], c->ev[4]); }
   S.ms_pair = ms_between(ev_front_end, c->ev[5]); S.ms_merge = back_finishes ? 0.f : ms_between(c->ev[5], c->ev[6]);
   S.kernel_ms = ms_between(c->ev[0], ev_end);

@@ -33,10 +33,10 @@ __global__ void __launch_bounds__(256) k_front(DevIndex ix, DevBatch b, brb_para
                                                uint32_t* __restrict__ ipool, Matches M) {
   if (ctl->bad_input) return;                             // k_validate_batch rejected the CSR offsets: nothing may follow them
   const unsigned lane = threadIdx.x & 31;
-  // alignments per batch (b.back_shift): 32, or 8 for long reads.  The kernel waits on dependent index loads (bin directory -> binary
+  // alignments per batch (b.front_shift): 32; for long reads 8, or 1 when a few reads carry most of the work (genes with hundreds of isoforms).  The kernel waits on dependent index loads (bin directory -> binary
   // search -> records), so it wants many warps in flight: a bundle of 10^5 long reads is only ~3000 batches of 32, fewer than the
   // resident warps.  The exon queries of a batch are flattened over the lanes, so small batches do not idle lanes.
-  const uint32_t BS = b.back_shift, BA = 1u << BS;
+  const uint32_t BS = b.front_shift, BA = 1u << BS;
   const uint32_t n_batches = (b.n_aln + BA - 1) >> BS;
   const uint32_t cap_cand = ctl->cap_cand, cap_ideal = ctl->cap_ideal;       // constant during the launch
   WarpPool wp; wp.cur = 0; wp.end = 0;
