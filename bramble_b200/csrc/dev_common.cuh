@@ -110,7 +110,8 @@ struct Ctl {
   uint32_t ticket;                    // next batch of 32 alignments for k_front (dynamic scheduling)
   uint32_t ticket_a, ticket_b;        // k_back: next batch; CTAs that have left (the last one publishes the totals)
   uint32_t kq_n[6], kq_t[6];          // clip rescue: problems per size class, next problem of each class
-  uint32_t ksw_big_skipped, pad_;     // big problems that did not fit the per-warp scratch (the host grows it and replays)
+  uint32_t ksw_big_skipped;           // big problems that did not fit the per-warp scratch (the host grows it and replays)
+  uint32_t ticket_m;                  // k_merge_long: next 32 candidate slots
 };
 constexpr int N_CAPS = 6;
 // End of a kernel sequence, ONE thread, every other writer of `ctl` done and fenced: hand the counters to the host

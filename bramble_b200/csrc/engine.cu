@@ -109,7 +109,7 @@ struct brb_ctx {
   Buf q_any, a_cand, scan_tmp;
   Buf c_rec, c_task, c_first, c_last, c_nseg, c_nguide, c_cap, ipool;
   Buf r_left, r_right, rpool;
-  Buf m_rec, m_sim, m_clip, c_stage, t_agg, t_claim, t_off, p_row, p_pool, p_sim, p_clip;
+  Buf c_mg, m_rec, m_sim, m_clip, c_stage, t_agg, t_claim, t_off, p_row, p_pool, p_sim, p_clip;
   Buf a_roff, a_rcnt, g_roff;
   Buf o_src, o_tid, o_pos, o_strand, o_flags, o_sim, o_clip, o_coff, tpool, opool;
   HBuf h_small, h_out;
@@ -122,7 +122,7 @@ struct brb_ctx {
   std::vector<Buf*> all() {
     return {&in_group_off, &in_refid, &in_strand, &in_exon_off, &in_exon_st, &in_exon_en, &in_cigar_off, &in_cigar, &in_mate, &in_seq_off,
             &in_seq, &in_name_off, &in_names, &f_hi, &f_nh, &f_mapq, &f_prim, &z_in, &z_slots, &z_sizes, &z_crcs, &z_tot, &z_off, &z_out, &z_ticket, &e_raw, &e_off, &e_len, &e_units, &e_plan, &e_sizes, &e_offs, &e_err, &res_slab, &ctl, &q_any, &a_cand, &scan_tmp, &c_rec, &c_task, &c_first, &c_last, &c_nseg, &c_nguide, &c_cap, &ipool,
-            &r_left, &r_right, &rpool, &m_rec, &m_sim, &m_clip, &c_stage, &t_agg, &t_claim, &t_off, &p_row, &p_pool, &p_sim, &p_clip, &a_roff, &a_rcnt, &g_roff,
+            &r_left, &r_right, &rpool, &c_mg, &m_rec, &m_sim, &m_clip, &c_stage, &t_agg, &t_claim, &t_off, &p_row, &p_pool, &p_sim, &p_clip, &a_roff, &a_rcnt, &g_roff,
             &o_src, &o_tid, &o_pos, &o_strand, &o_flags, &o_sim, &o_clip, &o_coff, &tpool, &opool};
   }
 };
@@ -396,6 +396,7 @@ int ensure_pools(brb_ctx* c, bool rescue) {
   if (c->opt_ordered) { ENS(c->p_row, R * 16); ENS(c->p_pool, (size_t)c->cap_outw * 4); }
   if (c->opt_packed) ENS(c->p_row, R * 16);
   ENS(c->m_rec, C * 16);
+  if (c->b.back_shift < 5) ENS(c->c_mg, C * 8);              // long reads: where k_merge_long left the merged CIGAR of every match
   if (c->have_scores) { ENS(c->m_sim, C * 8); ENS(c->m_clip, C * 4); ENS(c->o_sim, R * 8); ENS(c->o_clip, R * 4); if (c->opt_ordered) { ENS(c->p_sim, R * 8); ENS(c->p_clip, R * 4); } }
   if (rescue || c->b.back_shift < 5) { ENS(c->c_rec, C * 4); ENS(c->c_task, C * 4); ENS(c->c_first, C * 4); ENS(c->c_last, C * 4); ENS(c->c_nseg, C * 4); ENS(c->c_nguide, C * 4); ENS(c->c_cap, C * 4); }
   ENS(c->ipool, (size_t)c->cap_ideal * 4);
@@ -522,10 +523,12 @@ int project_resident(brb_ctx* c, const brb_params& p) {
     }
     // ---- phase 5: pairing, CIGAR merge, rows (one kernel; row and CIGAR room claimed per batch in completion order)
     BackIn pv; pv.a_cand = c->a_cand.as<uint4>(); pv.m_rec = c->m_rec.as<uint4>(); pv.m_sim = M.sim; pv.m_clip = M.clip; pv.ipool = c->ipool.as<uint32_t>();
+    pv.mg = c->c_mg.as<uint2>();
     Rows o; o.src = c->o_src.as<uint32_t>(); o.tid = c->o_tid.as<uint32_t>(); o.pos = c->o_pos.as<uint32_t>(); o.strand = c->o_strand.as<int8_t>();
     o.flags = c->o_flags.as<uint8_t>(); o.sim = c->o_sim.as<double>(); o.clip = c->o_clip.as<int32_t>(); o.coff = c->o_coff.as<uint32_t>();
     o.pool = c->opool.as<uint32_t>(); o.a_roff = c->a_roff.as<uint32_t>(); o.a_rcnt = c->a_rcnt.as<uint32_t>();
     if (split) { k_count_valid<<<grid_for(n, 256), 256, 0, st>>>(b, ctl, c->a_cand.as<uint4>(), c->m_rec.as<uint4>()); L++; }
+    if (lng) { k_merge_long<<<resident((const void*)k_merge_long), 256, 0, st>>>(b, ctl, c->c_task.as<uint32_t>(), pv, c->tpool.as<uint32_t>(), c->c_mg.as<uint2>()); L++; }
     const uint32_t nbat = (uint32_t)((n + (1u << b.back_shift) - 1) >> b.back_shift);
     BatchTotals tl; tl.agg = c->t_agg.as<unsigned long long>(); tl.claim = c->t_claim.as<unsigned long long>();
     ProvRows pr; pr.row = c->p_row.as<uint4>(); pr.pool = c->p_pool.as<uint32_t>();

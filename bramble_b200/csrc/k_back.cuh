@@ -60,6 +60,7 @@ constexpr int kUnroll = VAR_UNROLL;
 constexpr uint32_t INLINE = 0xffffffffu;   // Stage.w: every merged CIGAR of the row(s) is the one-word ideal CIGAR itself
 constexpr uint32_t PENDING = 0xfffffffeu;  // Stage.w: general merge queued
 constexpr uint32_t NOFIT = 0xfffffffdu;    // Stage.w: the scratch pool is exhausted (the host grows it and replays)
+constexpr uint32_t PREMERGED = 0xfffffffcu; // Stage.w (long reads): the merged CIGARs of the row(s) are where BackIn::mg says
 constexpr uint32_t BACK_STAGE = VAR_BACK_STAGE;       // matches per batch staged in shared memory
 
 // match record written by the front kernels, one uint4 per candidate slot:
@@ -70,6 +71,7 @@ struct BackIn {
   const uint4* m_rec;
   const double* m_sim; const int32_t* m_clip;      // null when every score is 0
   const uint32_t* ipool;        // ideal CIGARs longer than one word
+  const uint2* mg;              // long reads: merged CIGAR of every match, made by k_merge_long: .x offset in the scratch pool (NONE: the one-word case, the word is m_rec.z; NOFIT: pool exhausted), .y words
 };
 struct Rows {
   uint32_t* src; uint32_t* tid; uint32_t* pos; int8_t* strand; uint8_t* flags; double* sim; int32_t* clip;
@@ -194,34 +196,6 @@ __global__ void __launch_bounds__(256, LONG ? 3 : VAR_BACK_CTAS) k_back(DevBatch
       stage[sidx] = make_uint4(tid, clr + clm + hdr, part, fit ? toff : NOFIT);
       atomicAdd(&s_words[L], clr + clm + hdr);
     };
-    // the same for ONE row (pair) by the whole warp: long CIGARs (k_merge.cuh: merge_cigars_warp).  Arguments are warp-uniform.
-    auto merge_rows_coop = [&](uint32_t L, uint32_t sidx, uint32_t tid, uint32_t part, const uint4& mr, const uint4& pr) {
-      const bool paired = part != SELF;
-      const uint32_t l_nrc = s_nrc[L], l_mnrc = s_mnrc[L], ni_r = mr.y >> 1, ni_m = pr.y >> 1;
-      const uint32_t cap_r = l_nrc + ni_r + 2, cap_m = paired ? l_mnrc + ni_m + 2 : 0;
-      const uint32_t scr_r = merge_warp_scratch(l_nrc, ni_r), scr_m = paired ? merge_warp_scratch(l_mnrc, ni_m) : 0;
-      bool fit;
-      uint32_t toff = warp_pool_alloc(wp, &ctl->n_tmpw, cap_tmpw, lane == 0 ? 1 + cap_r + cap_m + (scr_r > scr_m ? scr_r : scr_m) : 0, lane, fit);
-      toff = __shfl_sync(0xffffffffu, toff, 0);
-      uint32_t clr = 0, clm = 0;
-      if (fit) {
-        uint32_t* scr = tpool + toff + 1 + cap_r + cap_m;
-        if (ni_r == 1 && merge_trivial(mr.z, s_rsum[L])) { if (lane == 0) tpool[toff + 1] = mr.z; clr = 1; }
-        else clr = merge_cigars_any_warp(b.cigar + s_ro[L], l_nrc, v.ipool + mr.z, ni_r, mr.z, tpool + toff + 1, scr, lane);
-        if (paired) {
-          if (ni_m == 1 && merge_trivial(pr.z, s_mrsum[L])) { if (lane == 0) tpool[toff + 1 + cap_r] = pr.z; clm = 1; }
-          else clm = merge_cigars_any_warp(b.cigar + s_mro[L], l_mnrc, v.ipool + pr.z, ni_m, pr.z, tpool + toff + 1 + cap_r, scr, lane);
-        }
-        if (lane == 0) tpool[toff] = clr;
-      }
-      const uint32_t hdr = PACKED ? (paired ? 2u : 1u) : 0u;
-      if (lane == 0) {
-        n_pooled += hdr;
-        stage[sidx] = make_uint4(tid, clr + clm + hdr, part, fit ? toff : NOFIT);
-        atomicAdd(&s_words[L], clr + clm + hdr);
-      }
-      __syncwarp();
-    };
     // ---- phase 1
     for (uint32_t base = 0; base < total; base += 32) {
       const uint32_t item = base + lane;
@@ -265,6 +239,19 @@ __global__ void __launch_bounds__(256, LONG ? 3 : VAR_BACK_CTAS) k_back(DevBatch
         if (!PACKED) words += __popc(B_e & ~B_s & mine) + __popc(B_p & ~B_s & mine);
       }
       const uint32_t sidx = staged ? item : c;
+      if (LONG) {                                             // the merges are done (k_merge_long): a slow row only needs their sizes
+        uint32_t wds = PACKED ? 0u : (paired ? 2u : 1u), where = INLINE;
+        if (slow) {
+          const uint2 gr = __ldg(&v.mg[c]), gm = paired ? __ldg(&v.mg[part]) : make_uint2(NONE, 0u);
+          const bool fit = gr.x != NOFIT && gm.x != NOFIT;
+          const uint32_t hdr = PACKED ? (paired ? 2u : 1u) : 0u;
+          wds = fit ? gr.y + gm.y + hdr : 0u; where = fit ? PREMERGED : NOFIT;
+          n_pooled += hdr;
+          atomicAdd(&s_words[L], wds);
+        }
+        if (actv) stage[sidx] = make_uint4(emitted ? tid : NONE, wds, part, where);
+        continue;
+      }
       if (actv) stage[sidx] = make_uint4(emitted ? tid : NONE, slow ? L : (PACKED ? 0u : (paired ? 2u : 1u)), part, slow ? PENDING : INLINE);
       if (B_s) {
         if (staged) { if (slow) queue[qn + __popc(B_s & lt_mask)] = (uint16_t)item; }
@@ -272,8 +259,8 @@ __global__ void __launch_bounds__(256, LONG ? 3 : VAR_BACK_CTAS) k_back(DevBatch
       }
     }
     __syncwarp();
-    // ---- phase 1b: the general merges, 32 at a time (staged: from the queue; otherwise a second walk over the items)
-    for (uint32_t qi = 0, qe = qn ? (staged ? qn : total) : 0; qi < qe; qi += 32) {
+    // ---- phase 1b (short reads): the general merges, 32 at a time (staged: from the queue; otherwise a second walk over the items)
+    if (!LONG) for (uint32_t qi = 0, qe = qn ? (staged ? qn : total) : 0; qi < qe; qi += 32) {
       bool go = qi + lane < qe;
       uint32_t sidx = 0, L = 0, c = 0;
       if (staged) { if (go) { sidx = queue[qi + lane]; L = stage[sidx].y; c = s_off[L] + (sidx - s_excl[L]); } }
@@ -289,16 +276,7 @@ __global__ void __launch_bounds__(256, LONG ? 3 : VAR_BACK_CTAS) k_back(DevBatch
         mr = __ldg(&v.m_rec[c]);
         if (part != SELF) pr = __ldg(&v.m_rec[part]);
       }
-      // rows with long CIGARs go through the warp one at a time, the others lane by lane
-      const bool big = LONG && go && (s_nrc[L] + (mr.y >> 1) >= MERGE_COOP_MIN || (part != SELF && s_mnrc[L] + (pr.y >> 1) >= MERGE_COOP_MIN));
-      merge_rows(go && !big, L, sidx, tid, part, mr, pr);
-      if (LONG) for (uint32_t Bm = __ballot_sync(0xffffffffu, big); Bm; Bm &= Bm - 1) {
-        const int src = __ffs(Bm) - 1;
-        const uint4 bmr = make_uint4(__shfl_sync(0xffffffffu, mr.x, src), __shfl_sync(0xffffffffu, mr.y, src), __shfl_sync(0xffffffffu, mr.z, src), __shfl_sync(0xffffffffu, mr.w, src));
-        const uint4 bpr = make_uint4(__shfl_sync(0xffffffffu, pr.x, src), __shfl_sync(0xffffffffu, pr.y, src), __shfl_sync(0xffffffffu, pr.z, src), __shfl_sync(0xffffffffu, pr.w, src));
-        merge_rows_coop(__shfl_sync(0xffffffffu, L, src), __shfl_sync(0xffffffffu, sidx, src), __shfl_sync(0xffffffffu, tid, src),
-                        __shfl_sync(0xffffffffu, part, src), bmr, bpr);
-      }
+      merge_rows(go, L, sidx, tid, part, mr, pr);
     }
     __syncwarp();
     words += s_words[lane];
@@ -401,15 +379,18 @@ __global__ void __launch_bounds__(256, LONG ? 3 : VAR_BACK_CTAS) k_back(DevBatch
         const bool paired = part != SELF, inl = sg.w == INLINE;
         const uint4 mr = __ldg(&v.m_rec[c]);
         const uint32_t row = o_row0 + (paired ? 2 * rank : rank), w0 = o_word0 + wpre;
-        const uint32_t clr = inl ? 1u : tpool[sg.w];
+        // a merged CIGAR made by k_merge_long sits in the scratch pool; the one-word case is the match record's own word
+        const uint2 gr = inl ? make_uint2(NONE, 1u) : __ldg(&v.mg[c]);
+        const uint2 gm = (inl || !paired) ? make_uint2(NONE, 1u) : __ldg(&v.mg[part]);
+        const uint32_t clr = gr.y;
         uint4 m = mr; uint32_t cc = c, aln = wb * BA + L, fl = BRB_REC_FIRST, wpos = w0, len = clr;
-        const uint32_t* src = tpool + sg.w + 1;
+        const uint32_t* src = gr.x == NONE ? &v.m_rec[c].z : tpool + gr.x;
         uint4 pm = make_uint4(0, 0, 0, NONE);
         if (paired) { pm = __ldg(&v.m_rec[part]); fl |= BRB_REC_PAIRED | (pm.w == tid ? BRB_REC_SAMETX : 0); }
         for (uint32_t e = 0, ne = paired ? 2 : 1; e < ne; e++) {
           if (e) {                                            // the mate row follows the read row
             m = pm; cc = part; aln = (uint32_t)o_mate; fl &= ~BRB_REC_FIRST; wpos = w0 + clr;
-            src = tpool + sg.w + 1 + (s_nrc[L] + (mr.y >> 1) + 2); len = inl ? 1u : sg.y - clr - (PACKED ? 2u : 0u);
+            src = gm.x == NONE ? &v.m_rec[part].z : tpool + gm.x; len = gm.y;
             if (PACKED) wpos = w0 + 1 + clr;
           }
           const uint32_t minus = m.y & 1u, r = row + e;
@@ -479,6 +460,62 @@ __global__ void __launch_bounds__(256) k_count_valid(DevBatch b, const Ctl* __re
   uint4 ac = a_cand[a]; uint32_t nv = 0;
   for (uint32_t c = ac.x, e = ac.x + ac.y; c < e; c++) nv += m_rec[c].w != NONE;
   ac.z = nv; a_cand[a] = ac;
+}
+
+// Long reads: the merged CIGAR of every match, BEFORE pairing.  A row's CIGAR depends on its alignment (real CIGAR) and its transcript
+// (ideal CIGAR) only, and a long-read bundle emits practically every match, so the 10^2..10^4-word merges do not have to sit inside the
+// pairing kernel: here they run one warp per match (merge_cigars_warp, k_merge.cuh; short ones by lane 0) with their own occupancy, and
+// k_back<.., LONG> only copies.  The one-word case (ideal = one M of the real CIGAR's M/=/X sum) is recognised and left alone, as in k_back.
+__global__ void __launch_bounds__(256, 4) k_merge_long(DevBatch b, Ctl* __restrict__ ctl, const uint32_t* __restrict__ c_task, BackIn v,
+                                                       uint32_t* __restrict__ tpool, uint2* __restrict__ mg) {
+  if (front_overflow(ctl)) return;
+  const unsigned lane = threadIdx.x & 31;
+  const uint32_t n_cand = ctl->n_cand, cap_tmpw = ctl->cap_tmpw;
+  WarpPool wp; wp.cur = 0; wp.end = 0;
+  for (;;) {
+    uint32_t c0 = 0;
+    if (lane == 0) c0 = atomicAdd(&ctl->ticket_m, 32u);
+    c0 = __shfl_sync(0xffffffffu, c0, 0);
+    if (c0 >= n_cand) break;
+    const uint32_t c = c0 + lane;
+    uint4 mr = make_uint4(0, 0, 0, NONE);
+    if (c < n_cand) mr = __ldg(&v.m_rec[c]);
+    uint32_t ro = 0, nR = 0;
+    if (mr.w != NONE) { const uint32_t a = __ldg(&c_task[c]) >> 1; ro = __ldg(&b.cigar_off[a]); nR = __ldg(&b.cigar_off[a + 1]) - ro; }
+    // short CIGARs: every lane merges its own match
+    const bool small = mr.w != NONE && nR + (mr.y >> 1) < MERGE_COOP_MIN;
+    {
+      bool triv = false;
+      if (small && (mr.y >> 1) == 1) triv = merge_trivial(mr.z, real_msum(b.cigar + ro, nR));
+      bool fit;
+      const uint32_t toff = warp_pool_alloc(wp, &ctl->n_tmpw, cap_tmpw, (small && !triv) ? nR + (mr.y >> 1) + 2 : 0u, lane, fit);
+      if (small) {
+        if (triv) mg[c] = make_uint2(NONE, 1u);
+        else if (!fit) mg[c] = make_uint2(NOFIT, 0u);
+        else mg[c] = make_uint2(toff, merge_cigars(b.cigar + ro, nR, v.ipool + mr.z, mr.y >> 1, mr.z, tpool + toff));
+      }
+    }
+    for (uint32_t Bv = __ballot_sync(0xffffffffu, mr.w != NONE && !small); Bv; Bv &= Bv - 1) {        // long ones: one match at a time, by the whole warp
+      const int src = __ffs(Bv) - 1;
+      const uint32_t cc = c0 + (uint32_t)src, nI = __shfl_sync(0xffffffffu, mr.y, src) >> 1, z = __shfl_sync(0xffffffffu, mr.z, src);
+      const uint32_t r0 = __shfl_sync(0xffffffffu, ro, src), nr = __shfl_sync(0xffffffffu, nR, src);
+      const uint32_t* real = b.cigar + r0;
+      if (nI == 1 && (z & 0xfu) == CM) {                       // merge_trivial: M/=/X sum of an M/N-only real CIGAR == the ideal M
+        uint32_t sum = 0; bool other = false;
+        for (uint32_t i = lane; i < nr; i += 32) { const uint32_t rw = __ldg(&real[i]), op = rw & 0xfu; if (op == CM || op == CEQ || op == CX) sum += rw >> 4; else if (op != CN) other = true; }
+        sum = __reduce_add_sync(0xffffffffu, sum);
+        if (!__any_sync(0xffffffffu, other) && sum && sum == (z >> 4)) { if (lane == 0) mg[cc] = make_uint2(NONE, 1u); continue; }
+      }
+      const uint32_t cap = nr + nI + 2;
+      bool fit;
+      uint32_t toff = warp_pool_alloc(wp, &ctl->n_tmpw, cap_tmpw, lane == 0 ? cap + merge_warp_scratch(nr, nI) : 0u, lane, fit);
+      toff = __shfl_sync(0xffffffffu, toff, 0);
+      if (!fit) { if (lane == 0) mg[cc] = make_uint2(NOFIT, 0u); continue; }
+      const uint32_t len = merge_cigars_any_warp(real, nr, v.ipool + z, nI, z, tpool + toff, tpool + toff + cap, lane);
+      if (lane == 0) mg[cc] = make_uint2(toff, len);
+      __syncwarp();
+    }
+  }
 }
 
 // BRB_OPT_ORDERED_ROWS: the sequence ends with k_place / k_group_rows; one thread publishes after them.
