@@ -334,7 +334,10 @@ def measure_workload(W, args, local, cores, peak, with_cpu=True):
                             "top_kernel": names.get(top, top), "top_kernel_share": phase[top] / max(1e-9, sum(phase.values()))}}
         if W.name == "c3" and st.n_rescue:
             rec["roofline"]["rescue"] = {"problems_per_step": int(st.n_rescue), "ms_per_step": phase["ms_rescue"],
-                                         "dp_cells_per_step": int(getattr(st, "ksw_cells", 0)) or None}
+                                         "dp_cells_per_step": int(getattr(st, "ksw_cells", 0)) or None,
+                                         "dp_cells_run_per_step": int(getattr(st, "ksw_cells_run", 0)) or None,
+                                         "note": "dp_cells = query x target over all clip-rescue problems (what the reference computes); dp_cells_run = after "
+                                                 "sharing the DP between identical problems of one read (same clip, same neighbour exons)"}
             if rec["roofline"]["rescue"]["dp_cells_per_step"]:
                 rec["roofline"]["rescue"]["cell_updates_per_s"] = rec["roofline"]["rescue"]["dp_cells_per_step"] / max(1e-9, phase["ms_rescue"] / 1e3)
         if args.no_e2e:

@@ -63,7 +63,7 @@ class Stats(C.Structure):
                 ("ms_pair", C.c_float), ("ms_merge", C.c_float), ("n_candidates", C.c_uint64),
                 ("n_matches", C.c_uint64), ("n_rescue", C.c_uint64), ("n_rec", C.c_uint64),
                 ("alg_bytes", C.c_uint64), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
-                ("alg_bytes_front", C.c_uint64), ("ksw_cells", C.c_uint64), ("host_syncs", C.c_uint32), ("reserved_", C.c_uint32)]
+                ("alg_bytes_front", C.c_uint64), ("ksw_cells", C.c_uint64), ("host_syncs", C.c_uint32), ("reserved_", C.c_uint32), ("ksw_cells_run", C.c_uint64)]
 
 
 _PTR = {np.dtype(np.uint8): u8p, np.dtype(np.int8): i8p, np.dtype(np.uint32): u32p, np.dtype(np.int32): i32p,

@@ -100,6 +100,7 @@ struct Ctl {
   unsigned long long n_hits, out_words, rescue_bytes, n_matches, n_rescue, ksw_max_mat, ksw_max_tlen, n_mates;   // work counters
   unsigned long long claimed;         // k_back: rows | CIGAR words << 32 handed out so far
   unsigned long long ksw_max_qlen, ksw_cells;   // clip rescue: longest query of a big problem; DP cells (query x target) of all problems
+  unsigned long long ksw_cells_run;             // ... of the problems that ran (identical problems of a read share one DP)
   uint32_t n_cand, cap_cand;          // candidate slots allocated / capacity
   uint32_t n_ideal, cap_ideal;        // ideal-CIGAR pool words
   uint32_t n_rows, cap_rows;          // output rows

@@ -600,7 +600,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   // algorithmic bytes, SURVEY.md 8(d) / DESIGN.md: per-alignment SoA + 56 B per index hit + output rows + rescue bases
   S.alg_bytes_front = (uint64_t)n * 16 + (uint64_t)b.n_exon * 8 + hres->n_mates * 4 + hres->n_hits * 56;
   S.alg_bytes = S.alg_bytes_front + (uint64_t)b.n_cigar * 4 + (uint64_t)hres->n_rows * 40 + hres->out_words * 4 + hres->rescue_bytes;
-  S.ksw_cells = hres->ksw_cells; S.host_syncs = n_syncs;
+  S.ksw_cells = hres->ksw_cells; S.ksw_cells_run = hres->ksw_cells_run; S.host_syncs = n_syncs;
   c->have_result = true; c->res_n_aln = c->b.n_aln; c->res_foreign = false; c->rv = RowView{c->o_src.as<uint32_t>(), c->o_tid.as<uint32_t>(), c->o_pos.as<uint32_t>(), c->o_strand.as<int8_t>(), c->o_flags.as<uint8_t>(), c->have_scores ? c->o_sim.as<double>() : nullptr, c->have_scores ? c->o_clip.as<int32_t>() : nullptr, c->o_coff.as<uint32_t>(), c->opool.as<uint32_t>()}; c->result_ordered = ordered; c->result_packed = packed; c->result_compact = packed && c->b.compact_rows;
   return BRB_OK;
 }

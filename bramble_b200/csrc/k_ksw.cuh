@@ -139,8 +139,9 @@ __device__ __forceinline__ void get_clips(const uint32_t* cg, uint32_t n, bool& 
 
 // Total length of the neighbour exons of `rec` walking away from the read until the query is covered (collect_left_exons
 // :333-365 / collect_right_exons :513-546); 0 = no rescue (no neighbour at the first step).
-__device__ uint32_t collect_len(const DevIndex& ix, bool left, uint32_t rec, uint32_t qlen) {
+__device__ uint32_t collect_len(const DevIndex& ix, bool left, uint32_t rec, uint32_t qlen, unsigned long long* key = nullptr) {
   uint32_t gathered = 0, i = 0, cur = rec;
+  unsigned long long h = 0x9E3779B97F4A7C15ull;          // (key: a mix of the coordinates of the exons walked -- they ARE the target)
   while (qlen > gathered) {
     i++;
     // transcript-order neighbour away from the read = genomic neighbour on that side; getGuideExonForTid on the
@@ -149,8 +150,22 @@ __device__ uint32_t collect_len(const DevIndex& ix, bool left, uint32_t rec, uin
     if (nx == NONE) { if (i == 1) return 0; break; }
     const RecKey k = rec_key(ix, nx);
     gathered += (uint32_t)(k.en - k.st); cur = nx;
+    h = (h ^ (((unsigned long long)(uint32_t)k.st << 32) | (uint32_t)k.en)) * 0xC2B2AE3D27D4EB4Full; h ^= h >> 29;
   }
+  if (key) *key = h;
   return gathered;
+}
+// Do two rescues of the same read and side read the same target?  Both chains are walked the way collect_len walks them.
+__device__ bool same_target(const DevIndex& ix, bool left, uint32_t rec1, uint32_t rec2, uint32_t qlen) {
+  uint32_t gathered = 0, c1 = rec1, c2 = rec2;
+  while (qlen > gathered) {
+    const uint32_t n1 = left ? __ldg(&ix.gprev[c1]) : rec_link(ix, c1).gnext, n2 = left ? __ldg(&ix.gprev[c2]) : rec_link(ix, c2).gnext;
+    if (n1 == NONE || n2 == NONE) return n1 == n2;
+    const RecKey k1 = rec_key(ix, n1), k2 = rec_key(ix, n2);
+    if (k1.st != k2.st || k1.en != k2.en) return false;
+    gathered += (uint32_t)(k1.en - k1.st); c1 = n1; c2 = n2;
+  }
+  return true;
 }
 
 // The target of a rescue, written by the `nl` lanes of a group (lane gl of them): tlen codes into dst -- left: already
@@ -202,30 +217,57 @@ struct KswWork {
   uint32_t* queue;                                        // [KSW_CLASSES][2 * cap_cand]
   uint32_t queue_stride;
   uint32_t* tb; KswOut* out;                              // traceback pool [cap_tb], results per slot
+  unsigned long long* key; uint32_t* rec; uint32_t* rep;  // [2 * cap_cand] target key, start record, and the slot whose DP this slot shares (itself: it runs its own)
 };
 
-__global__ void __launch_bounds__(256) k_rescue_plan(DevIndex ix, DevBatch b, brb_params p, const uint32_t* __restrict__ c_task,
-                                                     const uint32_t* __restrict__ c_first, const uint32_t* __restrict__ c_last,
-                                                     const uint32_t* __restrict__ c_cap, KswWork K, Ctl* __restrict__ ctl) {
+// Pass 1: per slot the problem's sizes, its start record and the key of its target.
+__global__ void __launch_bounds__(256) k_rescue_sizes(DevIndex ix, DevBatch b, brb_params p, const uint32_t* __restrict__ c_task,
+                                                      const uint32_t* __restrict__ c_first, const uint32_t* __restrict__ c_last,
+                                                      const uint32_t* __restrict__ c_cap, KswWork K, Ctl* __restrict__ ctl) {
+  if (ctl_overflow(ctl)) return;
+  const uint32_t slots = 2 * ctl->n_cand;
+  for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < slots; slot += gridDim.x * blockDim.x) {
+    const uint32_t c = slot >> 1; const int side = slot & 1;
+    uint32_t qlen = 0, tlen = 0, rec = NONE; unsigned long long key = 0;
+    if (c_cap[c]) {
+      const uint32_t task = c_task[c], a = task >> 1; const int s = task & 1;
+      uint32_t total;
+      if (rescue_inputs(ix, b, p, a, s, c_first[c], c_last[c], side, rec, total)) {
+        const uint32_t got = collect_len(ix, side == 0, rec, total, &key);
+        if (got) { qlen = total; tlen = got < total + KSW_TAIL ? got : total + KSW_TAIL; }   // align_reversed keeps the last qlen+40; right truncates to qlen+40
+      }
+    }
+    K.qlen[slot] = qlen; K.tlen[slot] = tlen; K.key[slot] = key; K.rec[slot] = rec;
+  }
+}
+
+// Pass 2: identical problems of one read (same side, same clip, same neighbour exons -- the isoforms of a gene mostly share them) run
+// ONE DP: a slot looks back over the earlier candidates of its alignment for the first one with the same sizes and key, checks the
+// exon coordinates themselves, and shares that slot's result (K.rep).  Every slot keeps its own room for the clip CIGAR; only
+// representatives get traceback work and a place in the queue of their size class.
+__global__ void __launch_bounds__(256) k_rescue_plan(DevIndex ix, DevBatch b, const uint32_t* __restrict__ c_task, const uint4* __restrict__ a_cand,
+                                                     KswWork K, Ctl* __restrict__ ctl) {
   if (ctl_overflow(ctl)) return;
   const uint32_t slots = 2 * ctl->n_cand, cap_tb = ctl->cap_tb;
   const unsigned lane = threadIdx.x & 31;
   const uint32_t lt_mask = (1u << lane) - 1u;
-  unsigned long long cells = 0;
+  unsigned long long cells = 0, cells_run = 0;
   for (uint32_t base = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; base < slots; base += gridDim.x * blockDim.x) {
     const uint32_t slot = base + lane;
-    uint32_t qlen = 0, tlen = 0;
+    uint32_t qlen = 0, tlen = 0, rep = slot;
     if (slot < slots) {
-      const uint32_t c = slot >> 1; const int side = slot & 1;
-      if (c_cap[c]) {
-        const uint32_t task = c_task[c], a = task >> 1; const int s = task & 1;
-        uint32_t rec, total;
-        if (rescue_inputs(ix, b, p, a, s, c_first[c], c_last[c], side, rec, total)) {
-          const uint32_t got = collect_len(ix, side == 0, rec, total);
-          if (got) { qlen = total; tlen = got < total + KSW_TAIL ? got : total + KSW_TAIL; }   // align_reversed keeps the last qlen+40; right truncates to qlen+40
+      qlen = K.qlen[slot]; tlen = K.tlen[slot];
+      if (qlen) {
+        const uint32_t c = slot >> 1, side = slot & 1u, a = c_task[c] >> 1;
+        const unsigned long long key = K.key[slot];
+        for (uint32_t c2 = a_cand[a].x; c2 < c; c2++) {
+          const uint32_t s2 = 2 * c2 + side;
+          if (K.qlen[s2] == qlen && K.tlen[s2] == tlen && K.key[s2] == key && (c_task[c2] >> 1) == a &&
+              same_target(ix, side == 0, K.rec[slot], K.rec[s2], qlen)) { rep = s2; break; }
         }
       }
     }
+    const bool runs = qlen && rep == slot;
     // traceback / clip-CIGAR room: one atomic per warp
     const uint32_t want = qlen ? qlen + tlen + 2 : 0;
     const uint32_t incl = warp_incl_scan(want, lane), tot = __shfl_sync(0xffffffffu, incl, 31);
@@ -233,9 +275,8 @@ __global__ void __launch_bounds__(256) k_rescue_plan(DevIndex ix, DevBatch b, br
     if (lane == 31 && tot) tb0 = atomicAdd(&ctl->n_tb, tot);
     tb0 = __shfl_sync(0xffffffffu, tb0, 31);
     const bool fits = (unsigned long long)tb0 + tot <= cap_tb;
-    if (slot < slots) { K.qlen[slot] = fits ? qlen : 0; K.tlen[slot] = tlen; K.tb_off[slot] = tb0 + incl - want; }
-    if (!fits) qlen = 0;                                   // the host grows the pool and replays
-    const int cls = qlen ? ksw_class_of(qlen) : -1;
+    if (slot < slots) { K.tb_off[slot] = tb0 + incl - want; K.rep[slot] = rep; }
+    const int cls = (runs && fits) ? ksw_class_of(qlen) : -1;                    // (no room: the host grows the pool and replays)
 #pragma unroll
     for (int k = 0; k < KSW_CLASSES; k++) {                // queue of its class: one atomic per warp and class
       const uint32_t B = __ballot_sync(0xffffffffu, cls == k);
@@ -250,9 +291,10 @@ __global__ void __launch_bounds__(256) k_rescue_plan(DevIndex ix, DevBatch b, br
       atomicMax(&ctl->ksw_max_tlen, (unsigned long long)tlen); atomicMax(&ctl->ksw_max_qlen, (unsigned long long)qlen);
     }
     if (qlen) cells += (unsigned long long)qlen * tlen;
+    if (runs) cells_run += (unsigned long long)qlen * tlen;
   }
-  for (int d = 16; d; d >>= 1) cells += __shfl_down_sync(0xffffffffu, cells, d);
-  if (lane == 0 && cells) { atomicAdd(&ctl->ksw_cells, cells); }
+  for (int d = 16; d; d >>= 1) { cells += __shfl_down_sync(0xffffffffu, cells, d); cells_run += __shfl_down_sync(0xffffffffu, cells_run, d); }
+  if (lane == 0 && cells) { atomicAdd(&ctl->ksw_cells, cells); atomicAdd(&ctl->ksw_cells_run, cells_run); }
 }
 
 // Where a problem's sequences come from: the batch (rescue) or explicit arrays (brb_ksw_extend, the parity tests).
@@ -481,10 +523,11 @@ __global__ void __launch_bounds__(128) k_rescue_finish(KswWork K, uint32_t* __re
     RescueSeg sgm; sgm.ok = 0; sgm.score = 0; sgm.rc = 0; sgm.cig_off = 0; sgm.cig_len = 0;
     const uint32_t qlen = K.qlen[slot];
     if (qlen) {
-      const KswOut o = K.out[slot];
+      const uint32_t rs = K.rep ? K.rep[slot] : slot;                       // the slot that ran the DP of this problem
+      const KswOut o = K.out[rs];
       const uint32_t tbo = K.tb_off[slot];
       if (o.max >= 10 && o.score != BRB_KSW_NEG_INF) {
-        const uint32_t* T = K.tb + tbo; const uint32_t n = o.n_cig;          // T[0] is the LAST op of the forward ksw cigar
+        const uint32_t* T = K.tb + K.tb_off[rs]; const uint32_t n = o.n_cig;          // T[0] is the LAST op of the forward ksw cigar
         int32_t qc = 0, rc = 0;
         for (uint32_t k = 0; k < n; k++) { const uint32_t op = T[k] & 0xfu, len = T[k] >> 4; if (op == 0 || op == 1) qc += len; if (op == 0 || op == 2) rc += len; }
         uint32_t* out = rpool + tbo; uint32_t m = 0;

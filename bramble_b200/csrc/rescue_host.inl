@@ -11,11 +11,11 @@ inline uint32_t ksw_rows_cap(int cls) { const int qmax = kKswCfg[cls].G * kKswCf
 inline size_t ksw_group_bytes(int cls) { return (size_t)ksw_rows_cap(cls) * kKswCfg[cls].G * kKswCfg[cls].W * 2; }
 
 struct RescueBufs {
-  Buf qlen, tlen, tb_off, queue, tb, kout, aln_group, pmat[kKswReg], big_pmat, big_seq, big_state;
+  Buf qlen, tlen, tb_off, queue, tb, kout, aln_group, key, rec, rep, pmat[kKswReg], big_pmat, big_seq, big_state;
   uint32_t ctas[kKswReg] = {};
   cudaStream_t side[KSW_CLASSES] = {};            // the class kernels are independent: each runs on its own stream between two events
   cudaEvent_t ev_fork = nullptr, ev_join[KSW_CLASSES] = {};
-  std::vector<Buf*> all() { std::vector<Buf*> v = {&qlen, &tlen, &tb_off, &queue, &tb, &kout, &aln_group, &big_pmat, &big_seq, &big_state}; for (auto& b : pmat) v.push_back(&b); return v; }
+  std::vector<Buf*> all() { std::vector<Buf*> v = {&qlen, &tlen, &tb_off, &queue, &tb, &kout, &aln_group, &key, &rec, &rep, &big_pmat, &big_seq, &big_state}; for (auto& b : pmat) v.push_back(&b); return v; }
   void release() {
     for (Buf* b : all()) b->release();
     for (auto& s : side) if (s) { cudaStreamDestroy(s); s = nullptr; }
@@ -102,6 +102,7 @@ int launch_rescue(brb_ctx* c, const brb_params& p, uint64_t* L) {
   Ctl* ctl = c->ctl.as<Ctl>();
   ENS(R.aln_group, (size_t)b.n_aln * 4);
   ENS(R.qlen, slots * 4); ENS(R.tlen, slots * 4); ENS(R.tb_off, slots * 4); ENS(R.queue, (size_t)KSW_CLASSES * slots * 4);
+  ENS(R.key, slots * 8); ENS(R.rec, slots * 4); ENS(R.rep, slots * 4);
   ENS(c->r_left, C * sizeof(RescueSeg)); ENS(c->r_right, C * sizeof(RescueSeg));
   ENS(R.kout, slots * sizeof(KswOut));
   ENS(R.tb, (size_t)c->cap_tb * 4 + 16); ENS(c->rpool, (size_t)c->cap_tb * 4 + 16);
@@ -110,8 +111,10 @@ int launch_rescue(brb_ctx* c, const brb_params& p, uint64_t* L) {
   b.aln_group = R.aln_group.as<uint32_t>();
   KswWork K; K.qlen = R.qlen.as<uint32_t>(); K.tlen = R.tlen.as<uint32_t>(); K.tb_off = R.tb_off.as<uint32_t>(); K.queue = R.queue.as<uint32_t>();
   K.queue_stride = (uint32_t)slots; K.tb = R.tb.as<uint32_t>(); K.out = R.kout.as<KswOut>();
+  K.key = R.key.as<unsigned long long>(); K.rec = R.rec.as<uint32_t>(); K.rep = R.rep.as<uint32_t>();
   KswSrc S{}; S.c_task = c->c_task.as<uint32_t>(); S.c_first = c->c_first.as<uint32_t>(); S.c_last = c->c_last.as<uint32_t>();
-  k_rescue_plan<<<c->n_sm * 8, 256, 0, st>>>(ix, b, p, S.c_task, S.c_first, S.c_last, c->c_cap.as<uint32_t>(), K, ctl); (*L)++;
+  k_rescue_sizes<<<c->n_sm * 8, 256, 0, st>>>(ix, b, p, S.c_task, S.c_first, S.c_last, c->c_cap.as<uint32_t>(), K, ctl); (*L)++;
+  k_rescue_plan<<<c->n_sm * 8, 256, 0, st>>>(ix, b, S.c_task, c->a_cand.as<uint4>(), K, ctl); (*L)++;
   launch_ksw_all(st, R, ix, b, S, K, ctl, nullptr, L);
   k_rescue_finish<<<c->n_sm * 8, 128, 0, st>>>(K, c->rpool.as<uint32_t>(), c->r_left.as<RescueSeg>(), c->r_right.as<RescueSeg>(), c->c_cap.as<uint32_t>(), ctl); (*L)++;
   return 0;

@@ -162,6 +162,7 @@ typedef struct brb_stats {
   uint64_t ksw_cells;                   /* clip rescue: DP cells (query length x target length) of all problems of the call */
   uint32_t host_syncs;                  /* host round trips of the call: 1, plus one per pool that had to grow (the sequence replays) */
   uint32_t reserved_;
+  uint64_t ksw_cells_run;               /* ... of the problems whose DP ran: identical problems of one read (same clip, same neighbour exons) share one */
 } brb_stats;
 
 int brb_device_count(void);
