@@ -9,6 +9,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <ctime>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -27,6 +28,38 @@
 #include "k_emit.cuh"
 
 using namespace brb;
+
+// ---- brb_merge_cigars_static: the scratch of the warp-cooperative CIGAR merge in a fixed array instead of a cudaMalloc'ed pool.
+// Every GPU that loads the library holds these 4 MiB (+ 256 bytes) until the process exits.  In HOST code the name below is only a
+// stand-in for the symbol: the device address comes from cudaGetSymbolAddress (static_scratch(), once per device).
+#define BRB_STATIC_SCRATCH_WORDS (1u << 20)
+static __device__ __align__(256) uint32_t g_static_scratch[64 + BRB_STATIC_SCRATCH_WORDS];     // [0..63]: status words (word 0 = pairs merged serially)
+
+namespace {
+// The pairs of brb_merge_cigars, persistent warps: warp w owns the slice scr + w * slice_words; a pair that needs more than a slice
+// (the caller's bounds were too small) is merged by lane 0 with the serial code, which needs no scratch, and counted in status[0].
+__global__ void __launch_bounds__(128) k_merge_pairs_static(uint32_t n, const uint32_t* __restrict__ real_off, const uint32_t* __restrict__ real,
+                                                            const uint32_t* __restrict__ ideal_off, const uint32_t* __restrict__ ideal,
+                                                            const uint32_t* __restrict__ out_off, uint32_t* __restrict__ out_len, uint32_t* __restrict__ out,
+                                                            uint32_t* __restrict__ scr, uint32_t slice_words, uint32_t* __restrict__ status) {
+  const unsigned lane = threadIdx.x & 31;
+  const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
+  uint32_t* mine = scr + (size_t)w * slice_words;
+  for (uint32_t i = w; i < n; i += n_warps) {
+    const uint32_t r0 = real_off[i], nR = real_off[i + 1] - r0, i0 = ideal_off[i], nI = ideal_off[i + 1] - i0;
+    const uint32_t iword = nI == 1 ? ideal[i0] : 0;
+    uint32_t len = 0;
+    if (merge_warp_scratch(nR, nI) <= slice_words) len = merge_cigars_any_warp(real + r0, nR, ideal + i0, nI, iword, out + out_off[i], mine, lane);
+    else {
+      if (lane == 0) { len = merge_cigars(real + r0, nR, ideal + i0, nI, iword, out + out_off[i]); atomicAdd(&status[0], 1u); }
+      len = __shfl_sync(0xffffffffu, len, 0);
+    }
+    if (lane == 0) out_len[i] = len;
+    __syncwarp();                                           // the slice is reused by the warp's next pair
+  }
+}
+__global__ void k_copy_status(const uint32_t* __restrict__ status, uint32_t* __restrict__ dst) { *dst = status[0]; }
+}  // namespace
 
 namespace {
 
@@ -923,6 +956,47 @@ int brb_merge_cigars(brb_ctx* c, uint32_t n, const uint32_t* real_off, const uin
   d_so.release(); d_s.release();
   d_ro.release(); d_r.release(); d_io.release(); d_i.release(); d_oo.release(); d_ol.release(); d_o.release();
   return rc;
+}
+
+// Device address of g_static_scratch on `device` (made current by the caller): asked for once per device, no allocation involved.
+static int static_scratch(int device, uint32_t** out) {
+  static std::mutex mu; static uint32_t* addr[64] = {};
+  if (device < 0 || device >= 64) return fail(BRB_E_ARG, "brb_merge_cigars_static: device %d out of range", device);
+  std::lock_guard<std::mutex> lk(mu);
+  if (!addr[device]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess || !p) { cudaGetLastError(); return fail(BRB_E_CUDA, "cudaGetSymbolAddress(g_static_scratch) on device %d: %s", device, cudaGetErrorString(e)); }
+    addr[device] = static_cast<uint32_t*>(p);
+  }
+  *out = addr[device];
+  return BRB_OK;
+}
+
+int brb_merge_cigars_static(int device, void* stream, uint32_t n, uint32_t max_real_ops, uint32_t max_ideal_ops,
+                            const uint32_t* d_real_off, const uint32_t* d_real, const uint32_t* d_ideal_off, const uint32_t* d_ideal,
+                            const uint32_t* d_out_off, uint32_t* d_out_len, uint32_t* d_out, uint32_t* d_n_serial) {
+  if (n && (!d_real_off || !d_real || !d_ideal_off || !d_ideal || !d_out_off || !d_out_len || !d_out)) return fail(BRB_E_ARG, "brb_merge_cigars_static: null argument");
+  if (brb_device_count() <= device || device < 0) return fail(BRB_E_NO_DEVICE, "no CUDA device %d", device);
+  const uint64_t slice = (uint64_t)max_real_ops + 4ull * max_ideal_ops + 16;                   // merge_warp_scratch of the largest pair
+  if (slice > BRB_STATIC_SCRATCH_WORDS)
+    return fail(BRB_E_ARG, "brb_merge_cigars_static: max_real_ops + 4 * max_ideal_ops + 16 = %llu scratch words per pair exceed the static scratch of %u words; "
+                           "use brb_merge_cigars (allocating) for CIGARs of that size", (unsigned long long)slice, BRB_STATIC_SCRATCH_WORDS);
+  CU(cudaSetDevice(device));
+  uint32_t* base = nullptr;
+  { const int rc = static_scratch(device, &base); if (rc) return rc; }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CU(cudaMemsetAsync(base, 0, 256, st));                     // the status words start at zero; the merge scratch is written before it is read
+  if (n) {
+    // persistent warps, one slice each: as many as the array holds (>= 1), as the pairs need, and as a B200 keeps resident
+    const uint64_t fit = BRB_STATIC_SCRATCH_WORDS / slice, want = std::min<uint64_t>(n, 148ull * 64);
+    const unsigned block = fit >= 4 ? 128u : 32u, wpb = block / 32;
+    const unsigned ctas = (unsigned)std::max<uint64_t>(1, std::min<uint64_t>((want + wpb - 1) / wpb, fit / wpb));
+    k_merge_pairs_static<<<ctas, block, 0, st>>>(n, d_real_off, d_real, d_ideal_off, d_ideal, d_out_off, d_out_len, d_out, base + 64, (uint32_t)slice, base);
+    CU(cudaGetLastError());
+  }
+  if (d_n_serial) { k_copy_status<<<1, 1, 0, st>>>(base, d_n_serial); CU(cudaGetLastError()); }
+  return BRB_OK;
 }
 
 }  // extern "C"

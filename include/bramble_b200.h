@@ -222,6 +222,23 @@ int brb_lookup(brb_ctx* ctx, const brb_params* p, uint32_t n_query, const int32_
 int brb_merge_cigars(brb_ctx* ctx, uint32_t n, const uint32_t* real_off, const uint32_t* real,
                      const uint32_t* ideal_off, const uint32_t* ideal, uint32_t* out_off /* n+1, in: capacity layout */,
                      uint32_t* out_len, uint32_t* out);
+/* The same merge WITHOUT any allocation.  No counterpart in the reference: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The scratch of the
+ * warp-cooperative merge lives in a fixed __device__ array of the library: 4 MiB (2^20 words) + 256 status bytes, held by every GPU
+ * that loads the library until the process exits.
+ *   - ALL array arguments are DEVICE pointers owned by the caller (layouts as brb_merge_cigars: CSR offsets of n+1 entries; pair i
+ *     writes at d_out + d_out_off[i], room for real + ideal + 2 words, and its length to d_out_len[i]).
+ *   - max_real_ops / max_ideal_ops: upper bounds on the op counts of any pair.  A pair needs max_real_ops + 4 * max_ideal_ops + 16
+ *     scratch words; beyond 2^20 the call is rejected with BRB_E_ARG (use brb_merge_cigars).  A pair that exceeds the bounds the
+ *     caller gave is still merged correctly, serially by one lane; *d_n_serial (device, optional) receives how many did.
+ *   - `stream` is a cudaStream_t (NULL: the default stream).  The call only enqueues (one memset of the status words, which must
+ *     start at zero, one or two kernels) and returns; it calls no cudaMalloc / cudaFree and synchronises nothing.
+ *   - Every call on a device shares the one array, which keeps the last call's contents: two calls that overlap on the GPU (different
+ *     streams, or different host threads) race.  Serialise them on one stream or with events. */
+int brb_merge_cigars_static(int device, void* stream, uint32_t n, uint32_t max_real_ops, uint32_t max_ideal_ops,
+                            const uint32_t* d_real_off, const uint32_t* d_real, const uint32_t* d_ideal_off, const uint32_t* d_ideal,
+                            const uint32_t* d_out_off, uint32_t* d_out_len, uint32_t* d_out, uint32_t* d_n_serial);
+
 /* K3/K4: ksw_extz2 with bramble's fixed parameters (src/evaluate.cpp:285-317) for n problems.
  * Sequences are codes 0..4.  cigar_out row i holds up to cigar_cap words (len<<4|op, op 0=M,1=I,2=D). */
 int brb_ksw_extend(brb_ctx* ctx, uint32_t n, const uint64_t* q_off, const uint8_t* q, const uint64_t* t_off,
