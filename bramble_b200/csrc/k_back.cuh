@@ -480,10 +480,24 @@ __global__ void __launch_bounds__(256, 4) k_merge_long(DevBatch b, Ctl* __restri
     const uint32_t c = c0 + lane;
     uint4 mr = make_uint4(0, 0, 0, NONE);
     if (c < n_cand) mr = __ldg(&v.m_rec[c]);
-    uint32_t ro = 0, nR = 0;
-    if (mr.w != NONE) { const uint32_t a = __ldg(&c_task[c]) >> 1; ro = __ldg(&b.cigar_off[a]); nR = __ldg(&b.cigar_off[a + 1]) - ro; }
+    uint32_t ro = 0, nR = 0, rep = c;
+    if (mr.w != NONE) {
+      const uint32_t a = __ldg(&c_task[c]) >> 1; ro = __ldg(&b.cigar_off[a]); nR = __ldg(&b.cigar_off[a + 1]) - ro;
+      // An earlier match of the SAME alignment with the same ideal CIGAR (isoforms that share the exons under the read) has the same
+      // merged CIGAR: the merge runs once (for the earliest such match among this warp's 32 slots) and the others point at its result.
+      const uint32_t nI = mr.y >> 1, first = __ldg(&v.a_cand[a].x);
+      uint32_t lo = first > c0 ? first : c0; if (c - lo > 16) lo = c - 16;
+      for (uint32_t c2 = lo; c2 < c; c2++) {
+        const uint4 m2 = __ldg(&v.m_rec[c2]);
+        if (m2.w == NONE || (m2.y >> 1) != nI || (__ldg(&c_task[c2]) >> 1) != a) continue;
+        bool same = nI == 1 ? m2.z == mr.z : true;
+        if (nI != 1) for (uint32_t i = 0; i < nI && same; i++) same = __ldg(&v.ipool[m2.z + i]) == __ldg(&v.ipool[mr.z + i]);
+        if (same) { rep = c2; break; }
+      }
+    }
+    const bool dup = rep != c;
     // short CIGARs: every lane merges its own match
-    const bool small = mr.w != NONE && nR + (mr.y >> 1) < MERGE_COOP_MIN;
+    const bool small = mr.w != NONE && !dup && nR + (mr.y >> 1) < MERGE_COOP_MIN;
     {
       bool triv = false;
       if (small && (mr.y >> 1) == 1) triv = merge_trivial(mr.z, real_msum(b.cigar + ro, nR));
@@ -495,7 +509,7 @@ __global__ void __launch_bounds__(256, 4) k_merge_long(DevBatch b, Ctl* __restri
         else mg[c] = make_uint2(toff, merge_cigars(b.cigar + ro, nR, v.ipool + mr.z, mr.y >> 1, mr.z, tpool + toff));
       }
     }
-    for (uint32_t Bv = __ballot_sync(0xffffffffu, mr.w != NONE && !small); Bv; Bv &= Bv - 1) {        // long ones: one match at a time, by the whole warp
+    for (uint32_t Bv = __ballot_sync(0xffffffffu, mr.w != NONE && !dup && !small); Bv; Bv &= Bv - 1) {        // long ones: one match at a time, by the whole warp
       const int src = __ffs(Bv) - 1;
       const uint32_t cc = c0 + (uint32_t)src, nI = __shfl_sync(0xffffffffu, mr.y, src) >> 1, z = __shfl_sync(0xffffffffu, mr.z, src);
       const uint32_t r0 = __shfl_sync(0xffffffffu, ro, src), nr = __shfl_sync(0xffffffffu, nR, src);
@@ -515,6 +529,8 @@ __global__ void __launch_bounds__(256, 4) k_merge_long(DevBatch b, Ctl* __restri
       if (lane == 0) mg[cc] = make_uint2(toff, len);
       __syncwarp();
     }
+    __syncwarp();                                             // the representatives' results are in mg
+    if (dup) mg[c] = mg[rep];
   }
 }
 
