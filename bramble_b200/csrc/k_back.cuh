@@ -486,7 +486,7 @@ __global__ void __launch_bounds__(256, 4) k_merge_long(DevBatch b, Ctl* __restri
       // An earlier match of the SAME alignment with the same ideal CIGAR (isoforms that share the exons under the read) has the same
       // merged CIGAR: the merge runs once (for the earliest such match among this warp's 32 slots) and the others point at its result.
       const uint32_t nI = mr.y >> 1, first = __ldg(&v.a_cand[a].x);
-      uint32_t lo = first > c0 ? first : c0; if (c - lo > 16) lo = c - 16;
+      const uint32_t lo = first > c0 ? first : c0;             // (the SAME window start for every slot of the alignment: the earliest equal slot is then nobody's duplicate)
       for (uint32_t c2 = lo; c2 < c; c2++) {
         const uint4 m2 = __ldg(&v.m_rec[c2]);
         if (m2.w == NONE || (m2.y >> 1) != nI || (__ldg(&c_task[c2]) >> 1) != a) continue;

@@ -294,11 +294,13 @@ __device__ __noinline__ uint32_t merge_cigars_warp(const uint32_t* __restrict__ 
       }
     }
     if (__any_sync(0xffffffffu, cnt > 3)) return MERGE_SERIAL;
-    const uint32_t incl = warp_incl_scan(cnt, lane), off = np + incl - cnt;
+    // exclusive prefix of counts 0..3: two ballots instead of a shuffle scan
+    const uint32_t B0 = __ballot_sync(0xffffffffu, cnt & 1u), B1 = __ballot_sync(0xffffffffu, cnt & 2u);
+    const uint32_t off = np + __popc(B0 & lt_mask) + 2 * __popc(B1 & lt_mask);
     if (cnt > 0) pc[off] = p0;
     if (cnt > 1) pc[off + 1] = p1;
     if (cnt > 2) pc[off + 2] = p2;
-    np += __shfl_sync(0xffffffffu, incl, 31);
+    np += __popc(B0) + 2 * __popc(B1);
   }
   // ---- real side used up: the rest of the ideal CIGAR verbatim
   {
