@@ -129,6 +129,7 @@ def _declare(lib):
     lib.brb_ksw_extend.argtypes = [C.c_void_p, C.c_uint32, u64p, u8p, u64p, u8p, i32p, i32p, i32p, i32p, u8p,
                                    C.c_uint32, u32p, u32p]
     lib.brb_bgzf_compress.argtypes = [C.c_void_p, C.c_char_p, C.c_uint64, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
+    lib.brb_bgzf_inflate.argtypes = [C.c_void_p, C.c_char_p, C.c_uint64, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
     lib.brb_emit_bgzf.argtypes = [C.c_void_p, C.POINTER(Params), C.POINTER(EmitIn), C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     lib.brb_ctx_move_result.argtypes = [C.c_void_p, C.c_void_p]
     lib.brb_merge_cigars_static.argtypes = [C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32] + [C.c_void_p] * 8     # device pointers
@@ -138,7 +139,7 @@ def _declare(lib):
     for f in ("brb_index_create", "brb_index_destroy", "brb_ctx_create", "brb_ctx_destroy", "brb_project",
               "brb_batch_upload", "brb_project_resident", "brb_batch_download", "brb_ctx_stats", "brb_ctx_set_option", "brb_ctx_timer_start",
               "brb_ctx_timer_stop", "brb_lookup",
-              "brb_merge_cigars", "brb_ksw_extend", "brb_sort_by_start", "brb_host_alloc", "brb_host_free", "brb_bgzf_compress", "brb_emit_bgzf", "brb_ctx_move_result", "brb_merge_cigars_static"):
+              "brb_merge_cigars", "brb_ksw_extend", "brb_sort_by_start", "brb_host_alloc", "brb_host_free", "brb_bgzf_compress", "brb_emit_bgzf", "brb_ctx_move_result", "brb_merge_cigars_static", "brb_bgzf_inflate"):
         getattr(lib, f).restype = C.c_int
     return lib
 

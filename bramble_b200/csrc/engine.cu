@@ -26,6 +26,7 @@
 #include "k_index.cuh"
 #include "k_deflate.cuh"
 #include "k_emit.cuh"
+#include "k_inflate.cuh"
 
 using namespace brb;
 
@@ -132,6 +133,7 @@ struct brb_ctx {
   Buf f_hi, f_nh, f_mapq, f_prim;   // BRB_OPT_FLUSH_TAGS results per row
   Buf z_in, z_slots, z_sizes, z_crcs, z_tot, z_off, z_out, z_ticket; HBuf z_host;   // brb_bgzf_compress
   Buf e_raw, e_off, e_len, e_units, e_plan, e_sizes, e_offs, e_err;                // brb_emit_bgzf
+  Buf i_in, i_meta, i_out, i_ctl; HBuf i_host, i_hmeta;                           // brb_bgzf_inflate
   bool have_names = false, opt_flush_tags = false, result_tags = false;
   uint64_t in_bytes = 0, n_mates = 0, seq_bytes = 0, rescue_bytes = 0;
   bool have_batch = false, have_result = false, have_scores = false, opt_generic_front = false, opt_no_fastpath = false, opt_ordered = false, result_ordered = false, opt_packed = false, result_packed = false, opt_merge_warp = false, opt_compact = false, result_compact = false;
@@ -154,7 +156,7 @@ struct brb_ctx {
   brb_stats stats{};
   std::vector<Buf*> all() {
     return {&in_group_off, &in_refid, &in_strand, &in_exon_off, &in_exon_st, &in_exon_en, &in_cigar_off, &in_cigar, &in_mate, &in_seq_off,
-            &in_seq, &in_name_off, &in_names, &f_hi, &f_nh, &f_mapq, &f_prim, &z_in, &z_slots, &z_sizes, &z_crcs, &z_tot, &z_off, &z_out, &z_ticket, &e_raw, &e_off, &e_len, &e_units, &e_plan, &e_sizes, &e_offs, &e_err, &res_slab, &ctl, &q_any, &a_cand, &scan_tmp, &c_rec, &c_task, &c_first, &c_last, &c_nseg, &c_nguide, &c_cap, &ipool,
+            &in_seq, &in_name_off, &in_names, &f_hi, &f_nh, &f_mapq, &f_prim, &z_in, &z_slots, &z_sizes, &z_crcs, &z_tot, &z_off, &z_out, &z_ticket, &e_raw, &e_off, &e_len, &e_units, &e_plan, &e_sizes, &e_offs, &e_err, &i_in, &i_meta, &i_out, &i_ctl, &res_slab, &ctl, &q_any, &a_cand, &scan_tmp, &c_rec, &c_task, &c_first, &c_last, &c_nseg, &c_nguide, &c_cap, &ipool,
             &r_left, &r_right, &rpool, &c_mg, &m_rec, &m_sim, &m_clip, &c_stage, &t_agg, &t_claim, &t_off, &p_row, &p_pool, &p_sim, &p_clip, &a_roff, &a_rcnt, &g_roff,
             &o_src, &o_tid, &o_pos, &o_strand, &o_flags, &o_sim, &o_clip, &o_coff, &tpool, &opool};
   }
@@ -803,6 +805,64 @@ int brb_bgzf_compress(brb_ctx* c, const uint8_t* data, uint64_t n, const uint8_t
   CU(cudaMemsetAsync(c->z_in.as<uint8_t>() + (n & ~(uint64_t)3), 0, 16 - (n & 3), c->st));     // the word loads may read up to 7 bytes past the end
   CU(cudaMemcpyAsync(c->z_in.p, data, n, cudaMemcpyHostToDevice, c->st));
   return deflate_resident(c, n, out, out_bytes);
+}
+
+// BGZF blocks in, their inflated bytes out (k_inflate.cuh).  The host only walks the block headers (BC subfield -> block size, footer ->
+// ISIZE) to place every block; Huffman decoding, LZ77 copies and the CRC-32 / ISIZE verification run on the device.
+int brb_bgzf_inflate(brb_ctx* c, const uint8_t* data, uint64_t n, const uint8_t** out, uint64_t* out_bytes) {
+  if (!c || !out || !out_bytes || (n && !data)) return fail(BRB_E_ARG, "brb_bgzf_inflate: null argument");
+  if (brb_device_count() <= 0) return fail(BRB_E_NO_DEVICE, "no CUDA device");
+  CU(cudaSetDevice(c->idx->device));
+  *out = nullptr; *out_bytes = 0;
+  if (!n) return BRB_OK;
+  // ---- block directory
+  uint64_t nb = 0, total = 0;
+  for (uint64_t p = 0; p < n; nb++) {
+    if (n - p < 28 || data[p] != 0x1f || data[p + 1] != 0x8b || data[p + 2] != 8 || !(data[p + 3] & 4)) return fail(BRB_E_ARG, "brb_bgzf_inflate: not a BGZF block at byte %llu", (unsigned long long)p);
+    const uint32_t xlen = data[p + 10] | (data[p + 11] << 8);
+    if (n - p < 12ull + xlen + 8) return fail(BRB_E_ARG, "brb_bgzf_inflate: truncated block at byte %llu", (unsigned long long)p);
+    uint32_t bsize = 0; bool found = false;
+    for (uint32_t q = 0; q + 4 <= xlen;) {
+      const uint8_t* x = data + p + 12 + q; const uint32_t slen = x[2] | (x[3] << 8);
+      if (x[0] == 'B' && x[1] == 'C' && slen == 2 && q + 6 <= xlen) { bsize = x[4] | (x[5] << 8); found = true; }
+      q += 4 + slen;
+    }
+    if (!found || (uint64_t)bsize + 1 < 12ull + xlen + 8 || n - p < (uint64_t)bsize + 1) return fail(BRB_E_ARG, "brb_bgzf_inflate: bad or truncated block at byte %llu", (unsigned long long)p);
+    p += (uint64_t)bsize + 1;
+  }
+  if (nb > 0x3fffffffull) return fail(BRB_E_ARG, "brb_bgzf_inflate: too many blocks for one call");
+  ENS(c->i_hmeta, nb * 20 + 64);
+  uint64_t* h_in = c->i_hmeta.as<uint64_t>(); uint64_t* h_out = h_in + nb; uint32_t* h_clen = reinterpret_cast<uint32_t*>(h_out + nb);
+  { uint64_t k = 0;
+    for (uint64_t p = 0; p < n; k++) {
+      const uint32_t xlen = data[p + 10] | (data[p + 11] << 8);
+      uint32_t bsize = 0;
+      for (uint32_t q = 0; q + 4 <= xlen;) { const uint8_t* x = data + p + 12 + q; const uint32_t slen = x[2] | (x[3] << 8); if (x[0] == 'B' && x[1] == 'C' && slen == 2) bsize = x[4] | (x[5] << 8); q += 4 + slen; }
+      const uint64_t end = p + bsize + 1;
+      h_in[k] = p + 12 + xlen; h_clen[k] = (uint32_t)(end - 8 - h_in[k]); h_out[k] = total;
+      total += (uint32_t)data[end - 4] | ((uint32_t)data[end - 3] << 8) | ((uint32_t)data[end - 2] << 16) | ((uint32_t)data[end - 1] << 24);
+      p = end;
+    } }
+  ENS(c->i_in, n + 16); ENS(c->i_meta, nb * 20 + 64); ENS(c->i_out, total + 16); ENS(c->i_ctl, 16);
+  cudaStream_t st = c->st;
+  CU(cudaMemcpyAsync(c->i_in.p, data, n, cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(c->i_meta.p, c->i_hmeta.p, nb * 20, cudaMemcpyHostToDevice, st));
+  CU(cudaMemsetAsync(c->i_ctl.p, 0, 16, st));
+  InflateJob J; J.in = c->i_in.as<uint8_t>(); J.in_off = c->i_meta.as<uint64_t>(); J.out_off = J.in_off + nb; J.clen = reinterpret_cast<const uint32_t*>(J.out_off + nb);
+  J.out = c->i_out.as<uint8_t>(); J.n_blocks = (uint32_t)nb; J.ticket = c->i_ctl.as<uint32_t>(); J.err = J.ticket + 2;
+  const uint32_t ctas = std::min<uint32_t>((uint32_t)((nb + INFLATE_WARPS - 1) / INFLATE_WARPS), (uint32_t)c->n_sm * 8);
+  k_bgzf_inflate<<<ctas, 32 * INFLATE_WARPS, 0, st>>>(J);
+  uint32_t h_ctl[4] = {0, 0, 0, 0};
+  CU(cudaMemcpyAsync(h_ctl, c->i_ctl.p, 16, cudaMemcpyDeviceToHost, st));
+  if (total) { ENS(c->i_host, total + 64); CU(cudaMemcpyAsync(c->i_host.p, c->i_out.p, total, cudaMemcpyDeviceToHost, st)); }
+  CU(cudaStreamSynchronize(st));
+  CU(cudaGetLastError());
+  if (h_ctl[2]) {
+    static const char* what[] = {"", "bad block type", "bad stored-block length", "bad code lengths", "bad symbol or distance", "output does not match ISIZE", "CRC-32 mismatch", "compressed data ran out"};
+    return fail(BRB_E_ARG, "brb_bgzf_inflate: block %u: %s", h_ctl[2] - 1, what[h_ctl[3] < 8 ? h_ctl[3] : 0]);
+  }
+  *out = total ? c->i_host.as<uint8_t>() : (const uint8_t*)""; *out_bytes = total;
+  return BRB_OK;
 }
 
 // The resident result rows change hands: a device-to-device copy (a few MB per bundle) into ONE allocation of `to`, so that `from`

@@ -293,6 +293,12 @@ class Engine:
         capi.check(self.lib.brb_bgzf_compress(self._ctx, bytes(data), len(data), C.byref(out), C.byref(n)), "brb_bgzf_compress")
         return C.string_at(out.value, n.value) if n.value else b""
 
+    def bgzf_inflate(self, data):
+        """complete BGZF blocks (bytes) -> their inflated bytes, decoded and CRC-checked on the device."""
+        out = C.c_void_p(); n = C.c_uint64()
+        capi.check(self.lib.brb_bgzf_inflate(self._ctx, bytes(data), len(data), C.byref(out), C.byref(n)), "brb_bgzf_inflate")
+        return C.string_at(out.value, n.value) if n.value else b""
+
     def emit_bgzf(self, params, raw, rec_off, rec_len, units, ctx=None):
         """Output records of the resident result (last project() on this engine's ctx, or `ctx`), assembled and BGZF-compressed on the
         device: raw = the bundle's input record bodies (bytes), rec_off / rec_len per alignment, units = (n, 4) uint32 in output

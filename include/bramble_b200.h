@@ -251,6 +251,12 @@ int brb_ksw_extend(brb_ctx* ctx, uint32_t n, const uint64_t* q_off, const uint8_
  * `*out` points into pinned memory owned by the ctx, valid until the next call on it. */
 int brb_bgzf_compress(brb_ctx* ctx, const uint8_t* data, uint64_t n, const uint8_t** out, uint64_t* out_bytes);
 
+/* BGZF decoder on the device: `n` bytes holding complete BGZF blocks back to back (any piece of a BAM file cut at block boundaries)
+ * in, their inflated bytes out -- what htslib's bgzf_read + inflate do behind the reference's sam_read1 (gclib/GSam.h:489-499).  Full
+ * RFC 1951 (stored, fixed and dynamic Huffman blocks); CRC-32 and ISIZE of every block are verified.  Malformed input: BRB_E_ARG with
+ * the block number in brb_last_error().  `*out` points into pinned memory owned by the ctx, valid until the next call on it. */
+int brb_bgzf_inflate(brb_ctx* ctx, const uint8_t* bgzf, uint64_t n, const uint8_t** out, uint64_t* out_bytes);
+
 /* Output records on the device: what the reference's write_to_bam builds per row (src/core.cpp:96-212 with update_cigar,
  * set_mate_info, reverse_complement_bam, set_nh_tag / set_hi_tag / set_as_tag of src/bam.cpp:475-702) from the rows of the
  * ctx's resident result (the last brb_project / brb_project_resident call, plain columns) and the bundle's INPUT records,

@@ -585,3 +585,55 @@ def test_emit_records_on_device_match_restatement(mode):
         z3, _ = eng.emit_bgzf(p, raw, rec_off, rec_len, units[:0])
         assert z3 == b""
         holder.close()
+
+
+def test_bgzf_device_decoder_matches_zlib():
+    """brb_bgzf_inflate (Huffman decode + LZ77 copies + CRC-32 check on the device, one warp per block): BGZF blocks written by zlib at
+    levels 0 / 1 / 6 / 9 (stored, fixed and dynamic blocks), by the device encoder (fixed codes), with several deflate blocks inside one
+    BGZF block, with long overlapping matches, plus the empty EOF block -- must come back as the original bytes; a flipped payload byte
+    and a wrong CRC must be refused."""
+    import struct
+    import zlib
+    from bramble_b200 import synth
+    wl = common.make_workload("default", 133, n_names=500)
+    rng = np.random.default_rng(11)
+    bam = b"".join(synth._pack_record(r) for r in wl["recs"] if not r["flag"] & 4)
+
+    def blocks(data, level, step=0xff00):
+        return b"".join(synth._bgzf_block(data[i:i + step], level) for i in range(0, len(data), step))
+
+    def multi(data, level):                                  # several deflate blocks (sync flushes add empty stored blocks) in ONE BGZF block
+        co = zlib.compressobj(level, zlib.DEFLATED, -15)
+        k = len(data) // 3
+        c = co.compress(data[:k]) + co.flush(zlib.Z_SYNC_FLUSH) + co.compress(data[k:2 * k]) + co.flush(zlib.Z_FULL_FLUSH) + co.compress(data[2 * k:]) + co.flush()
+        return (b"\x1f\x8b\x08\x04\0\0\0\0\0\xff\x06\0BC\x02\0" + struct.pack("<H", len(c) + 25) + c + struct.pack("<II", zlib.crc32(data) & 0xffffffff, len(data)))
+
+    noise = bytes(rng.integers(0, 256, size=150000, dtype=np.uint8))
+    runs = b"A" * 70000 + b"ACGT" * 20000 + bytes(rng.integers(0, 4, size=60000, dtype=np.uint8)) + b"\0" * 65000
+    with engine.Engine(wl["index"]) as eng:
+        cases = []
+        for level in (0, 1, 6, 9):
+            cases.append((f"bam level {level}", bam, blocks(bam, level)))
+            cases.append((f"runs level {level}", runs, blocks(runs, level)))
+        cases.append(("noise level 6", noise, blocks(noise, 6)))
+        cases.append(("small blocks", bam[:50000], blocks(bam[:50000], 6, step=777)))
+        cases.append(("multi", bam[:60000], multi(bam[:60000], 6) + multi(runs[:65000], 1)))
+        cases[-1] = ("multi", bam[:60000] + runs[:65000], cases[-1][2])
+        cases.append(("device encoder", bam, eng.bgzf_compress(bam)))
+        cases.append(("with EOF block", bam[:1000], blocks(bam[:1000], 6) + synth._BGZF_EOF))
+        cases.append(("only EOF", b"", synth._BGZF_EOF))
+        cases.append(("nothing", b"", b""))
+        for name, want, z in cases:
+            got = eng.bgzf_inflate(z)
+            assert got == want, (name, len(got), len(want), next((i for i, (x, y) in enumerate(zip(got, want)) if x != y), None))
+        z = bytearray(blocks(bam, 6))
+        z[len(z) // 2] ^= 0x55                                   # somewhere inside a payload
+        with pytest.raises(capi.EngineError):
+            eng.bgzf_inflate(bytes(z))
+        z = bytearray(blocks(bam[:40000], 6))
+        z[-8] ^= 1                                              # the footer's CRC-32
+        with pytest.raises(capi.EngineError, match="CRC"):
+            eng.bgzf_inflate(bytes(z))
+        with pytest.raises(capi.EngineError):
+            eng.bgzf_inflate(blocks(bam[:40000], 6)[:-5])       # truncated
+        assert eng.bgzf_inflate(blocks(bam, 1)) == bam          # the context is fine after the refusals
