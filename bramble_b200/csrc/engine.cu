@@ -851,7 +851,11 @@ int brb_bgzf_inflate(brb_ctx* c, const uint8_t* data, uint64_t n, const uint8_t*
   InflateJob J; J.in = c->i_in.as<uint8_t>(); J.in_off = c->i_meta.as<uint64_t>(); J.out_off = J.in_off + nb; J.clen = reinterpret_cast<const uint32_t*>(J.out_off + nb);
   J.out = c->i_out.as<uint8_t>(); J.n_blocks = (uint32_t)nb; J.ticket = c->i_ctl.as<uint32_t>(); J.err = J.ticket + 2;
   const uint32_t ctas = std::min<uint32_t>((uint32_t)((nb + INFLATE_WARPS - 1) / INFLATE_WARPS), (uint32_t)c->n_sm * 8);
+  static const bool timing = getenv("BRB_INFLATE_TIMING") != nullptr;     // kernel milliseconds on stderr
+  if (timing) CU(cudaEventRecord(c->tev[0], st));
   k_bgzf_inflate<<<ctas, 32 * INFLATE_WARPS, 0, st>>>(J);
+  if (timing) { CU(cudaEventRecord(c->tev[1], st)); CU(cudaEventSynchronize(c->tev[1])); float ms = 0; cudaEventElapsedTime(&ms, c->tev[0], c->tev[1]);
+                fprintf(stderr, "[inflate] %llu blocks, %llu -> %llu bytes: kernel %.3f ms\n", (unsigned long long)nb, (unsigned long long)n, (unsigned long long)total, ms); }
   uint32_t h_ctl[4] = {0, 0, 0, 0};
   CU(cudaMemcpyAsync(h_ctl, c->i_ctl.p, 16, cudaMemcpyDeviceToHost, st));
   if (total) { ENS(c->i_host, total + 64); CU(cudaMemcpyAsync(c->i_host.p, c->i_out.p, total, cudaMemcpyDeviceToHost, st)); }

@@ -8,6 +8,7 @@
 #include <cstring>
 #include <condition_variable>
 #include <deque>
+#include <functional>
 #include <mutex>
 #include <stdexcept>
 #include <string>
@@ -19,15 +20,23 @@ namespace brbhost {
 // Reader.  threads <= 1: blocks are inflated on the calling thread.  threads > 1: a feeder thread walks the file
 // block by block (the BC field gives every block's size without touching the payload), a pool inflates the
 // independent blocks, read() consumes them in file order.
+// With a piece inflater (the engine's brb_bgzf_inflate): the feeder cuts the file into PIECES of whole blocks (1 MiB first, for a quick
+// start, then 8 MiB), two workers hand them to the inflater -- which may decline (returns false): the piece is then inflated here,
+// block by block, and that is also where a corrupt block gets its error message.
 class BgzfReader {
  public:
-  explicit BgzfReader(const std::string& path, int threads = 1) {
+  using PieceInflater = std::function<bool(int worker, const uint8_t* bgzf, size_t n, std::vector<uint8_t>& out)>;
+  explicit BgzfReader(const std::string& path, int threads = 1, PieceInflater ext = nullptr) : ext_(std::move(ext)) {
     f_ = fopen(path.c_str(), "rb");
     if (!f_) throw std::runtime_error("cannot open " + path);
     setvbuf(f_, nullptr, _IOFBF, 1 << 20);
-    if (threads > 1) {
+    if (ext_) {
+      max_jobs_ = 4;
+      for (int i = 0; i < 2; i++) pool_.emplace_back([this, i] { worker(i); });
+      feeder_ = std::thread([this] { feed_pieces(); });
+    } else if (threads > 1) {
       max_jobs_ = (size_t)threads * 8;
-      for (int i = 0; i < threads; i++) pool_.emplace_back([this] { worker(); });
+      for (int i = 0; i < threads; i++) pool_.emplace_back([this] { worker(0); });
       feeder_ = std::thread([this] { feed(); });
     }
   }
@@ -57,7 +66,7 @@ class BgzfReader {
     return true;
   }
  private:
-  struct Job { std::vector<uint8_t> comp, out; size_t clen = 0; uint32_t isize = 0; bool ready = false; std::string err; };
+  struct Job { std::vector<uint8_t> comp, out; size_t clen = 0; uint32_t isize = 0; bool ready = false, piece = false; std::string err; };
   // next compressed block from the file: false at EOF
   bool read_block(std::vector<uint8_t>& comp, size_t& clen, uint32_t& isize) {
     uint8_t h[12];
@@ -115,13 +124,74 @@ class BgzfReader {
     { std::unique_lock<std::mutex> lk(m_); eof_ = true; }
     cv_.notify_all(); cv_ready_.notify_all();
   }
-  void worker() {
+  // one whole block (header, payload, footer) appended to dst; false at EOF
+  bool read_raw_block(std::vector<uint8_t>& dst) {
+    uint8_t h[12];
+    if (fread(h, 1, 12, f_) != 12) return false;
+    if (h[0] != 0x1f || h[1] != 0x8b) throw std::runtime_error("not a BGZF file");
+    const unsigned xlen = h[10] | (h[11] << 8);
+    const size_t at = dst.size();
+    dst.resize(at + 12 + xlen);
+    memcpy(dst.data() + at, h, 12);
+    if (xlen && fread(dst.data() + at + 12, 1, xlen, f_) != xlen) { dst.resize(at); return false; }
+    unsigned bsize = 0; bool found = false;
+    for (size_t p = 0; p + 4 <= xlen;) {
+      const uint8_t* x = dst.data() + at + 12 + p; const unsigned slen = x[2] | (x[3] << 8);
+      if (x[0] == 'B' && x[1] == 'C' && slen == 2) { bsize = x[4] | (x[5] << 8); found = true; }
+      p += 4 + slen;
+    }
+    if (!found || (size_t)bsize + 1 < 12 + (size_t)xlen + 8) throw std::runtime_error("BGZF block without BC field");
+    const size_t rest = (size_t)bsize + 1 - 12 - xlen;
+    dst.resize(at + 12 + xlen + rest);
+    if (fread(dst.data() + at + 12 + xlen, 1, rest, f_) != rest) { dst.resize(at); return false; }
+    return true;
+  }
+  void feed_pieces() {
+    try {
+      size_t want = 1 << 20; bool more = true;
+      while (more) {
+        Job* j = new Job();
+        j->comp.reserve(want + (64 << 10));
+        while (j->comp.size() < want && (more = read_raw_block(j->comp))) {}
+        j->clen = j->comp.size(); j->piece = true;
+        if (j->clen == 0) { delete j; break; }
+        want = 8 << 20;
+        std::unique_lock<std::mutex> lk(m_);
+        cv_room_.wait(lk, [this] { return stop_ || order_.size() < max_jobs_; });
+        if (stop_) { delete j; return; }
+        order_.push_back(j); todo_.push_back(j);
+        cv_.notify_one();
+      }
+    } catch (const std::exception& e) { std::unique_lock<std::mutex> lk(m_); feed_err_ = e.what(); }
+    { std::unique_lock<std::mutex> lk(m_); eof_ = true; }
+    cv_.notify_all(); cv_ready_.notify_all();
+  }
+  // a piece on the host: its blocks one after the other
+  static void inflate_piece(const std::vector<uint8_t>& piece, std::vector<uint8_t>& out) {
+    out.clear();
+    std::vector<uint8_t> comp, one;
+    for (size_t p = 0; p < piece.size();) {
+      const unsigned xlen = piece[p + 10] | (piece[p + 11] << 8);
+      unsigned bsize = 0;
+      for (size_t q = 0; q + 4 <= xlen;) { const uint8_t* x = piece.data() + p + 12 + q; const unsigned slen = x[2] | (x[3] << 8); if (x[0] == 'B' && x[1] == 'C' && slen == 2) bsize = x[4] | (x[5] << 8); q += 4 + slen; }
+      const size_t end = p + bsize + 1, clen = end - 8 - (p + 12 + xlen);
+      comp.assign(piece.begin() + p + 12 + xlen, piece.begin() + end);
+      const uint32_t isize = comp[clen + 4] | (comp[clen + 5] << 8) | (comp[clen + 6] << 16) | ((uint32_t)comp[clen + 7] << 24);
+      inflate_block(comp, clen, isize, one);
+      out.insert(out.end(), one.begin(), one.end());
+      p = end;
+    }
+  }
+  void worker(int id) {
     for (;;) {
       Job* j = nullptr;
       { std::unique_lock<std::mutex> lk(m_); cv_.wait(lk, [this] { return stop_ || eof_ || !todo_.empty(); });
         if (todo_.empty()) { if (stop_ || eof_) return; continue; }
         j = todo_.front(); todo_.pop_front(); }
-      try { inflate_block(j->comp, j->clen, j->isize, j->out); } catch (const std::exception& e) { j->err = e.what(); }
+      try {
+        if (!j->piece) inflate_block(j->comp, j->clen, j->isize, j->out);
+        else if (!ext_(id, j->comp.data(), j->clen, j->out)) inflate_piece(j->comp, j->out);
+      } catch (const std::exception& e) { j->err = e.what(); }
       { std::unique_lock<std::mutex> lk(m_); j->ready = true; }
       cv_ready_.notify_all();
     }
@@ -142,6 +212,7 @@ class BgzfReader {
   FILE* f_ = nullptr; std::vector<uint8_t> buf_, comp_, extra_; size_t pos_ = 0;
   std::vector<std::thread> pool_; std::thread feeder_; std::mutex m_; std::condition_variable cv_, cv_room_, cv_ready_;
   std::deque<Job*> order_, todo_; size_t max_jobs_ = 0; bool stop_ = false, eof_ = false; std::string feed_err_;
+  PieceInflater ext_;
 };
 
 class BgzfWriter {

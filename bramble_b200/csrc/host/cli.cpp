@@ -319,13 +319,6 @@ int main(int argc, char** argv) {
     IndexColumns cols;
     if (!o.fasta.empty()) load_genome(o.fasta, A, cols.chrom_off, cols.genome);
     build_index_columns(A, cols);
-    const int n_inflate = getenv("BRB_INFLATE_THREADS") ? std::max(1, atoi(getenv("BRB_INFLATE_THREADS"))) : std::min(o.threads, 8);
-    BgzfReader in(o.in_bam, n_inflate);
-    const InHeader ih = read_bam_header(in);
-    const std::string header = make_header(ih, A, o);
-    std::vector<int> ref2refid(ih.ref_names.size(), -1);
-    for (size_t i = 0; i < ih.ref_names.size(); i++) { auto it = A.refid_of.find(ih.ref_names[i]); if (it != A.refid_of.end()) ref2refid[i] = it->second; }
-
     const int n_gpu = std::max(1, o.gpus);
     // BRB_GPU_MAP=d0,d1,...: CUDA device of dealer slot k (default: slot k -> device k).  "0,0" runs the whole --gpus 2 path
     // (dealer, one worker and one index copy per slot, ordered merge) on a single device.
@@ -333,6 +326,26 @@ int main(int argc, char** argv) {
     if (const char* gm = getenv("BRB_GPU_MAP")) { int k = 0; for (const char* q = gm; *q && k < n_gpu; k++) { gpu_map[k] = atoi(q); q = strchr(q, ','); if (!q) break; q++; } }
     std::vector<std::unique_ptr<EngineIf>> engines;
     for (int g = 0; g < n_gpu; g++) { engines.emplace_back(make_engine()); engines.back()->open(gpu_map[g], cols.desc); }
+
+    // the input: inflated by a host pool, or -- BRB_DEVICE_INFLATE=1 -- in pieces by engine 0 (brb_bgzf_inflate).  The device decoder does a
+    // whole file at ~27 GB/s but a call takes 5 ms however small (one warp per 64 KiB block), so for inputs of a few bundles the host pool
+    // is as fast (measured: producer 0.13 s vs 0.09 s on a 55 MB BAM); it pays on long inputs and on hosts with few cores.
+    // (the reader is declared after the engines: its threads are gone before the engines are)
+    const int n_inflate = getenv("BRB_INFLATE_THREADS") ? std::max(1, atoi(getenv("BRB_INFLATE_THREADS"))) : std::min(o.threads, 8);
+    BgzfReader::PieceInflater dev_inflate = nullptr;
+    if (getenv("BRB_DEVICE_INFLATE")) {
+      std::vector<uint8_t> probe;
+      if (engines[0]->bgzf_inflate(0, nullptr, 0, probe)) {
+        EngineIf* e0 = engines[0].get();
+        dev_inflate = [e0](int w, const uint8_t* z, size_t n, std::vector<uint8_t>& out) { return e0->bgzf_inflate(w, z, n, out); };
+      }
+    }
+    if (!dev_inflate && getenv("BRB_TEST_PIECES")) dev_inflate = [](int, const uint8_t*, size_t, std::vector<uint8_t>&) { return false; };   // tests: the piece reader with every piece declined (inflated by the host, block by block)
+    BgzfReader in(o.in_bam, n_inflate, dev_inflate);
+    const InHeader ih = read_bam_header(in);
+    const std::string header = make_header(ih, A, o);
+    std::vector<int> ref2refid(ih.ref_names.size(), -1);
+    for (size_t i = 0; i < ih.ref_names.size(); i++) { auto it = A.refid_of.find(ih.ref_names[i]); if (it != A.refid_of.end()) ref2refid[i] = it->second; }
 
     BgzfWriter out(o.out_bam, o.level, std::max(1, o.threads));
     { std::vector<uint8_t> hb; auto put = [&](const void* p, size_t n) { hb.insert(hb.end(), (const uint8_t*)p, (const uint8_t*)p + n); };

@@ -10,9 +10,9 @@ struct CudaEngine : EngineIf {
   // ctx: the projecting context (the only one whose pools ever grow).  holders: contexts that only KEEP the rows of a projected bundle
   // (brb_ctx_move_result) while the host replays flush() for the order.  ectx: the context of the emitter thread -- record assembly
   // and BGZF scratch, one set per engine.  zctx: the writer thread's context for the plain BGZF encoder (host-assembled records).
-  brb_index* ix = nullptr; brb_ctx* ctx = nullptr; brb_ctx* zctx = nullptr; brb_ctx* ectx = nullptr;
+  brb_index* ix = nullptr; brb_ctx* ctx = nullptr; brb_ctx* zctx = nullptr; brb_ctx* ectx = nullptr; brb_ctx* ictx[2] = {nullptr, nullptr};   // ictx: the reader's two inflate workers
   std::vector<brb_ctx*> holders;
-  ~CudaEngine() override { for (brb_ctx* c : holders) brb_ctx_destroy(c); if (ectx) brb_ctx_destroy(ectx); if (zctx) brb_ctx_destroy(zctx); if (ctx) brb_ctx_destroy(ctx); if (ix) brb_index_destroy(ix); }
+  ~CudaEngine() override { for (brb_ctx* c : ictx) if (c) brb_ctx_destroy(c); for (brb_ctx* c : holders) brb_ctx_destroy(c); if (ectx) brb_ctx_destroy(ectx); if (zctx) brb_ctx_destroy(zctx); if (ctx) brb_ctx_destroy(ctx); if (ix) brb_index_destroy(ix); }
   static void need(int rc, const char* what) { if (rc != BRB_OK) throw std::runtime_error(std::string(what) + ": " + brb_last_error()); }
   void open(int device, const brb_index_desc& desc) override {
     if (brb_device_count() <= device) throw std::runtime_error("no CUDA device " + std::to_string(device) + " (bramble_b200 has no CPU path)");
@@ -29,6 +29,14 @@ struct CudaEngine : EngineIf {
     uint64_t zn = 0;
     need(brb_bgzf_compress(zctx, data, n, &out, &zn), "brb_bgzf_compress");
     out_n = (size_t)zn;
+    return true;
+  }
+  bool bgzf_inflate(int w, const uint8_t* z, size_t n, std::vector<uint8_t>& out) override {
+    if (w < 0 || w > 1) return false;
+    if (!ictx[w]) need(brb_ctx_create(ix, &ictx[w]), "brb_ctx_create");
+    const uint8_t* p = nullptr; uint64_t m = 0;
+    if (brb_bgzf_inflate(ictx[w], z, n, &p, &m) != BRB_OK) return false;        // (a malformed block: the host decoder names it)
+    out.assign(p, p + m);
     return true;
   }
   int slots() override { static const int n = [] { const char* e = getenv("BRB_SLOTS"); const int v = e ? atoi(e) : 4; return v < 1 ? 1 : v > 16 ? 16 : v; }(); return n; }

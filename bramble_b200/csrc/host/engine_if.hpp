@@ -4,6 +4,7 @@
 // (ingest, flush replay, record assembly, BGZF) can be checked byte-for-byte without a GPU.
 #pragma once
 #include <string>
+#include <vector>
 #include "../../../include/bramble_b200.h"
 
 namespace brbhost {
@@ -18,6 +19,9 @@ struct EngineIf {
   // Output records assembled AND compressed by the engine from the rows a project_slot() call left resident in `slot`
   // (brb_emit_bgzf): slots() contexts per engine, so that a bundle's rows can wait on the device for the host's flush order
   // while the next bundles are projected.  can_emit() false: the caller assembles the records itself.
+  // a piece of a BGZF file (whole blocks) inflated by the engine (brb_bgzf_inflate), callable from two reader threads (worker 0 / 1);
+  // false: not available or refused (malformed block) -- the caller inflates the piece itself
+  virtual bool bgzf_inflate(int, const uint8_t*, size_t, std::vector<uint8_t>&) { return false; }
   virtual int slots() { return 1; }
   virtual int project_slot(int, const brb_params& p, const brb_batch_in& in, brb_batch_out& out) { return project(p, in, out); }
   virtual bool can_emit() { return false; }

@@ -130,6 +130,26 @@ def test_flush_chunks_assembled_in_parallel_keep_the_reference_order():
     assert a == b, explain(a, b, d)
 
 
+@needs_ref
+def test_piece_reader_with_host_decoder():
+    """The input reader in piece mode (whole BGZF blocks, 1 MiB then 8 MiB, handed to the engine's decoder) with every piece declined: the
+    host inflates them block by block.  Also: a corrupt block is reported, not written through."""
+    wl = common.make_workload("default", 31, n_names=6000, n_genes=40)
+    d = tempfile.mkdtemp(prefix="brb_cli_")
+    args = write_inputs(wl, d, "default")
+    os.environ["BRB_TEST_PIECES"] = "1"
+    try:
+        a, b = run_both(d, PORT_CLI, args)
+        assert a == b and len(a) > 1000000, explain(a, b, d)
+        z = bytearray(open(d + "/in.bam", "rb").read())
+        z[len(z) // 2] ^= 0x40
+        open(d + "/bad.bam", "wb").write(bytes(z))
+        r = subprocess.run(["bramble", "../bad.bam", "-G", "../a.gtf", "-o", "bad_out.bam", "--quiet"], executable=PORT_CLI, cwd=d + "/our", capture_output=True, text=True)
+        assert r.returncode == 1 and "error" in r.stderr.lower(), (r.returncode, r.stderr[-300:])
+    finally:
+        del os.environ["BRB_TEST_PIECES"]
+
+
 def _pg_strip(stream):
     """drop the trailing extra flags our runs add to the @PG CL: field (--gpus N)"""
     return stream
@@ -148,12 +168,13 @@ def test_cli_is_byte_identical_to_reference(mode):
 
 @needs_ref
 @pytest.mark.gpu
-@pytest.mark.parametrize("env", [{"BRB_HOST_ASSEMBLY": "1"}, {"BRB_HOST_DEFLATE": "1"}, {"BRB_SLOTS": "1"}])
+@pytest.mark.parametrize("env", [{"BRB_HOST_ASSEMBLY": "1"}, {"BRB_HOST_DEFLATE": "1"}, {"BRB_SLOTS": "1"}, {"BRB_DEVICE_INFLATE": "1"}])
 @pytest.mark.parametrize("mode", ["default", "lr"])
 def test_cli_host_side_output_paths_agree(mode, env):
     """The default output path builds and compresses the records on the device (brb_emit_bgzf).  The older paths stay selectable and
     must write the same stream: records assembled by the host pool + device BGZF (BRB_HOST_ASSEMBLY), everything on the host
-    (BRB_HOST_DEFLATE); BRB_SLOTS=1 leaves the device path a single row holder."""
+    (BRB_HOST_DEFLATE); BRB_SLOTS=1 leaves the device path a single row holder; BRB_DEVICE_INFLATE=1 has the input BGZF blocks decoded by the
+    engine (brb_bgzf_inflate) instead of the host pool."""
     wl = common.make_workload(mode, 23, n_names=1500, n_genes=40)
     d = tempfile.mkdtemp(prefix="brb_cli_")
     args = write_inputs(wl, d, mode)
