@@ -22,12 +22,18 @@
 #define VAR_FRONT_CTAS 5
 #endif
 
+// Resident CTAs per SM the long-read front kernel (k_front<false>) is compiled for: it waits on chains of dependent index loads, so it
+// wants warps in flight more than registers (tools/variants.py + tools/time_variants_lr.sh: c4 front 0.45 ms at 4, 0.41 at 6 and 8).
+#ifndef VAR_FRONT_SPLIT_CTAS
+#define VAR_FRONT_SPLIT_CTAS 6
+#endif
+
 namespace brb {
 
 // a_cand[a] = { first candidate slot, #slots ('+' task first, then '-'), #slots that hold a match, - }
 // (on the clip-rescue path the match count is filled in later by k_count_valid)
 template <bool FUSED>
-__global__ void __launch_bounds__(256) k_front(DevIndex ix, DevBatch b, brb_params p, Ctl* __restrict__ ctl,
+__global__ void __launch_bounds__(256, FUSED ? 1 : VAR_FRONT_SPLIT_CTAS) k_front(DevIndex ix, DevBatch b, brb_params p, Ctl* __restrict__ ctl,
                                                uint8_t* q_any, uint4* __restrict__ a_cand,
                                                uint32_t* __restrict__ c_rec, uint32_t* __restrict__ c_task,
                                                uint32_t* __restrict__ ipool, Matches M) {
