@@ -345,7 +345,7 @@ def measure_workload(W, args, local, cores, peak, with_cpu=True):
         # end to end: one brb_project() call from pinned host columns (H2D + kernels + D2H)
         PB = eng.pinned_copy(B)
         try:
-            eng.set_option(capi.OPT_PACKED_ROWS, 0 if W.long else 2)
+            eng.set_option(capi.OPT_PACKED_ROWS, 0 if W.long else 3)
             eng.project(p, PB, raw=True)
             t0 = time.perf_counter()
             reps = 3
@@ -411,8 +411,8 @@ def main():
     ap.add_argument("--only-workloads", default=None, help="comma list: restrict the sub-records (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs: resident steps only (also skips the ordered-rows leg, the sustained loop and the sub-records' extras)")
     ap.add_argument("--e2e-bundles", type=int, default=8, help="bundles per step on the end-to-end path")
-    ap.add_argument("--e2e-rows", default="compact", choices=["compact", "packed", "columns"],
-                    help="row layout on the end-to-end path: BRB_OPT_PACKED_ROWS = 2 (12-byte rows + 16-bit unit sizes), = 1 (16-byte records) or the plain columns")
+    ap.add_argument("--e2e-rows", default="compact8", choices=["compact8", "compact", "packed", "columns"],
+                    help="row layout on the end-to-end path: BRB_OPT_PACKED_ROWS = 3 (8-byte rows + 16-bit unit sizes), = 2 (12-byte rows), = 1 (16-byte records) or the plain columns")
     ap.add_argument("--no-bind", action="store_true", help="N>1: do not pin each rank to the CPUs of its GPU's NUMA node")
     ap.add_argument("--e2e-contexts", type=int, default=3, help="brb_ctx (host threads / streams) on the end-to-end path")
     ap.add_argument("--sustained-s", type=float, default=2.0, help="length of the sustained resident loop")
@@ -565,6 +565,9 @@ def main():
             eng.set_option(capi.OPT_PACKED_ROWS, 2)
             eng.run_resident(p)
             checks["compact_rows"] = engine.rows_checksum(eng.download(B, raw=True), batch=B)
+            eng.set_option(capi.OPT_PACKED_ROWS, 3)
+            eng.run_resident(p)
+            checks["compact8_rows"] = engine.rows_checksum(eng.download(B, raw=True), batch=B)
         eng.set_option(capi.OPT_PACKED_ROWS, 0)
     barrier()
     st = eng.stats()
@@ -580,7 +583,7 @@ def main():
         cuts = [G * i // nbun for i in range(nbun + 1)]
         PBs = [eng.pinned_copy(B.slice_groups(g0, g1)) for g0, g1 in zip(cuts[:-1], cuts[1:])]
         ctxs = [eng.context() for _ in range(max(1, args.e2e_contexts))]
-        e2e_packed = 0 if (Wh.long or args.e2e_rows == "columns") else (2 if args.e2e_rows == "compact" else 1)
+        e2e_packed = 0 if (Wh.long or args.e2e_rows == "columns") else {"compact8": 3, "compact": 2, "packed": 1}[args.e2e_rows]
         for c in ctxs:
             c.set_option(capi.OPT_PACKED_ROWS, e2e_packed)
         eng.set_option(capi.OPT_PACKED_ROWS, e2e_packed)
@@ -641,7 +644,8 @@ def main():
                 "e2e": None if args.no_e2e else {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": e2e_h2d, "d2h_bytes_per_step": e2e_d2h,
                         "records_per_step": e2e_rec, "bundles_per_step": nbun, "contexts": len(ctxs),
                         "how": "brb_project() per bundle from pinned host columns, one host thread per context",
-                        "rows": {2: "BRB_OPT_PACKED_ROWS = 2: 12 bytes per row (tid, pos, word), 16-bit unit sizes + one row offset per 32 alignments", 1: "BRB_OPT_PACKED_ROWS = 1: one 16-byte record per row",
+                        "rows": {3: "BRB_OPT_PACKED_ROWS = 3: 8 bytes per row (tid 22 | pos 24 | flags | CIGAR length), 16-bit unit sizes + one row offset per 32 alignments",
+                                 2: "BRB_OPT_PACKED_ROWS = 2: 12 bytes per row (tid, pos, word), 16-bit unit sizes + one row offset per 32 alignments", 1: "BRB_OPT_PACKED_ROWS = 1: one 16-byte record per row",
                                  0: "columns (22 bytes per row + CIGAR CSR)"}[e2e_packed],
                         "single_call_value": n_aln / e2e_single_s, "single_call_note": "rank 0, one brb_project() call for the whole step, no overlap"},
                 "sustained": sustained,

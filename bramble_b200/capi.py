@@ -54,7 +54,7 @@ class BatchOut(C.Structure):
                 ("sim_score", f64p), ("clip_score", i32p), ("cigar_off", u32p), ("cigar", u32p),
                 ("aln_rec_off", u32p), ("aln_rec_cnt", u32p), ("packed_rows", u32p),
                 ("hi", i32p), ("nh", i32p), ("mapq", u8p), ("primary", u8p),
-                ("batch_rec_off", u32p), ("aln_rec_cnt16", C.POINTER(C.c_uint16))]
+                ("batch_rec_off", u32p), ("aln_rec_cnt16", C.POINTER(C.c_uint16)), ("packed_row_words", C.c_uint32)]
 
 
 class Stats(C.Structure):

@@ -88,7 +88,7 @@ struct DevBatch {
   const uint64_t* group_seq_off; const uint8_t* seq; const uint32_t* aln_group;
   uint32_t back_shift;           // k_back / k_place: log2 of the alignments per batch (5 for short reads, 3 for long reads)
   uint32_t front_shift;          // k_front: the same for the front kernel (long reads: 3, or 0 when the engine has measured that to be faster on this data)
-  uint32_t compact_rows;         // k_back<.., PACKED, ..>: 12-byte rows without the source alignment, 16-bit unit sizes and one row offset per batch (BRB_OPT_PACKED_ROWS = 2)
+  uint32_t compact_rows;         // k_back<.., PACKED, ..>: 1 = 12-byte rows without the source alignment, 16-bit unit sizes and one row offset per batch (BRB_OPT_PACKED_ROWS = 2); 2 = the same with 8-byte rows (= 3)
   uint32_t count_hits;           // k_front: count EVERY index hit of every read exon (the reference-defined figure); else later exons stop at the first survivor
 };
 
@@ -107,7 +107,7 @@ struct Ctl {
   uint32_t n_tmpw, cap_tmpw;          // merge scratch pool words
   uint32_t n_outw, cap_outw;          // dense output CIGAR words
   uint32_t n_tb, cap_tb;              // clip rescue: traceback ops / override-coded clip CIGAR words
-  uint32_t bad_input;                 // 1: mate link not symmetric, 2: read exons not ascending/disjoint, 3: >= 2^28 CIGAR words in one batch of 32 alignments, 4: packed rows, 5: CSR offsets, 6: compact rows (a unit of 65536 rows or more)
+  uint32_t bad_input;                 // 1: mate link not symmetric, 2: read exons not ascending/disjoint, 3: >= 2^28 CIGAR words in one batch of 32 alignments, 4: packed rows, 5: CSR offsets, 6: compact rows (a unit of 65536 rows or more), 7: 8-byte rows (tid >= 2^22, pos >= 2^24 or a CIGAR field >= 2^13)
   uint32_t ticket;                    // next batch of 32 alignments for k_front (dynamic scheduling)
   uint32_t ticket_a, ticket_b;        // k_back: next batch; CTAs that have left (the last one publishes the totals)
   uint32_t kq_n[6], kq_t[6];          // clip rescue: problems per size class, next problem of each class

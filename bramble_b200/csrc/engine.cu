@@ -136,7 +136,7 @@ struct brb_ctx {
   Buf i_in, i_meta, i_out, i_ctl; HBuf i_host, i_hmeta;                           // brb_bgzf_inflate
   bool have_names = false, opt_flush_tags = false, result_tags = false;
   uint64_t in_bytes = 0, n_mates = 0, seq_bytes = 0, rescue_bytes = 0;
-  bool have_batch = false, have_result = false, have_scores = false, opt_generic_front = false, opt_no_fastpath = false, opt_ordered = false, result_ordered = false, opt_packed = false, result_packed = false, opt_merge_warp = false, opt_compact = false, result_compact = false;
+  bool have_batch = false, have_result = false, have_scores = false, opt_generic_front = false, opt_no_fastpath = false, opt_ordered = false, result_ordered = false, opt_packed = false, result_packed = false, opt_merge_warp = false, opt_compact = false, result_compact = false; uint32_t compact_level = 0, result_compact_level = 0;
   // control block + pools (capacities persist across calls and only grow)
   Buf ctl;
   uint32_t cap_cand = 0, cap_ideal = 0, cap_rows = 0, cap_tmpw = 0, cap_outw = 0, cap_tb = 0;
@@ -447,7 +447,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   if (rescue && !c->idx->d.genome) return fail(BRB_E_UNSUPPORTED, "use_fasta requested but the index holds no genome");
   if (rescue && c->b.n_aln && !c->b.seq) return fail(BRB_E_UNSUPPORTED, "use_fasta requested but the batch carries no read sequences");
   c->b.count_hits = c->opt_generic_front ? 1u : 0u;
-  c->b.compact_rows = (c->opt_compact && c->opt_packed && !c->opt_ordered && !p.long_reads) ? 1u : 0u;
+  c->b.compact_rows = (c->opt_compact && c->opt_packed && !c->opt_ordered && !p.long_reads) ? c->compact_level : 0u;
   // Long reads: the front kernel takes 8 alignments per ticket, or 1 -- which is faster depends on the data (ONT-like bundles: 8, 0.09 vs
   // 0.23 ms; bundles whose work sits in a few reads of 200-isoform genes: 1, 0.45 vs 0.73 ms), and nothing in the batch says which.  So
   // each context measures: first call 8, second call 1, then the faster one per alignment, probed again every 64 calls.  The results do
@@ -471,7 +471,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   if (n == 0) {
     ENS(c->g_roff, (size_t)(b.n_groups + 1) * 4); ENS(c->o_coff, 4);
     CU(cudaMemsetAsync(c->g_roff.p, 0, 4, st)); CU(cudaMemsetAsync(c->o_coff.p, 0, 4, st)); CU(cudaStreamSynchronize(st));
-    c->have_result = true; c->res_n_aln = c->b.n_aln; c->res_foreign = false; c->rv = RowView{c->o_src.as<uint32_t>(), c->o_tid.as<uint32_t>(), c->o_pos.as<uint32_t>(), c->o_strand.as<int8_t>(), c->o_flags.as<uint8_t>(), c->have_scores ? c->o_sim.as<double>() : nullptr, c->have_scores ? c->o_clip.as<int32_t>() : nullptr, c->o_coff.as<uint32_t>(), c->opool.as<uint32_t>()}; c->result_ordered = c->opt_ordered; c->result_packed = c->opt_packed && !c->opt_ordered; c->result_compact = false; return BRB_OK;
+    c->have_result = true; c->res_n_aln = c->b.n_aln; c->res_foreign = false; c->rv = RowView{c->o_src.as<uint32_t>(), c->o_tid.as<uint32_t>(), c->o_pos.as<uint32_t>(), c->o_strand.as<int8_t>(), c->o_flags.as<uint8_t>(), c->have_scores ? c->o_sim.as<double>() : nullptr, c->have_scores ? c->o_clip.as<int32_t>() : nullptr, c->o_coff.as<uint32_t>(), c->opool.as<uint32_t>()}; c->result_ordered = c->opt_ordered; c->result_packed = c->opt_packed && !c->opt_ordered; c->result_compact = false; c->result_compact_level = 0; return BRB_OK;
   }
   if (!c->cap_cand) {           // first guess from the batch shape; a pool that overflows grows and the sequence replays
     c->cap_cand = grown((uint64_t)12 * n); c->cap_rows = grown((uint64_t)6 * n);
@@ -619,6 +619,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
     c->result_tags = true;
   }
   if (hres->bad_input == 3) return fail(BRB_E_UNSUPPORTED, "a batch of 32 alignments emits 2^28 or more CIGAR words");
+  if (hres->bad_input == 7) return fail(BRB_E_UNSUPPORTED, "BRB_OPT_PACKED_ROWS = 3: a row does not fit 8 bytes (tid >= 2^22, pos >= 2^24, or an M length / CIGAR word count >= 2^13); project the bundle with the option at 2 or less");
   if (hres->bad_input == 6) return fail(BRB_E_UNSUPPORTED, "BRB_OPT_PACKED_ROWS = 2: a unit of 65536 rows or more; project the bundle with the option at 0 or 1");
   if (hres->bad_input == 4) return fail(BRB_E_UNSUPPORTED, "BRB_OPT_PACKED_ROWS: the bundle pools 2^27 or more CIGAR words; project it without the option");
   if (hres->bad_input == 5) return fail(BRB_E_ARG, "CSR offsets (group_off / exon_off / cigar_off) must start at 0, be non-decreasing and end at the column sizes");
@@ -636,7 +637,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
   S.alg_bytes_front = (uint64_t)n * 16 + (uint64_t)b.n_exon * 8 + hres->n_mates * 4 + hres->n_hits * 56;
   S.alg_bytes = S.alg_bytes_front + (uint64_t)b.n_cigar * 4 + (uint64_t)hres->n_rows * 40 + hres->out_words * 4 + hres->rescue_bytes;
   S.ksw_cells = hres->ksw_cells; S.ksw_cells_run = hres->ksw_cells_run; S.host_syncs = n_syncs;
-  c->have_result = true; c->res_n_aln = c->b.n_aln; c->res_foreign = false; c->rv = RowView{c->o_src.as<uint32_t>(), c->o_tid.as<uint32_t>(), c->o_pos.as<uint32_t>(), c->o_strand.as<int8_t>(), c->o_flags.as<uint8_t>(), c->have_scores ? c->o_sim.as<double>() : nullptr, c->have_scores ? c->o_clip.as<int32_t>() : nullptr, c->o_coff.as<uint32_t>(), c->opool.as<uint32_t>()}; c->result_ordered = ordered; c->result_packed = packed; c->result_compact = packed && c->b.compact_rows;
+  c->have_result = true; c->res_n_aln = c->b.n_aln; c->res_foreign = false; c->rv = RowView{c->o_src.as<uint32_t>(), c->o_tid.as<uint32_t>(), c->o_pos.as<uint32_t>(), c->o_strand.as<int8_t>(), c->o_flags.as<uint8_t>(), c->have_scores ? c->o_sim.as<double>() : nullptr, c->have_scores ? c->o_clip.as<int32_t>() : nullptr, c->o_coff.as<uint32_t>(), c->opool.as<uint32_t>()}; c->result_ordered = ordered; c->result_packed = packed; c->result_compact = packed && c->b.compact_rows; c->result_compact_level = c->result_compact ? c->b.compact_rows : 0u;
   return BRB_OK;
 }
 
@@ -666,7 +667,8 @@ int brb_batch_download(brb_ctx* c, brb_batch_out* out) {
   const size_t o_groff = off; off += ord ? al((G + 1) * 4) : 0;
   const size_t o_aoff = off; off += al(cm ? NB * 4 : N * 4);              // compact: one row offset per batch of 32 alignments ...
   const size_t o_acnt = off; off += al(cm ? N * 2 : N * 4);               // ... and 16-bit unit sizes
-  const size_t o_prow = off; off += pk ? al(R * (cm ? 12 : 16)) : 0;
+  const size_t row_bytes = !cm ? 16 : c->result_compact_level == 2 ? 8 : 12;
+  const size_t o_prow = off; off += pk ? al(R * row_bytes) : 0;
   const size_t o_src = off; off += pk ? 0 : al(R * 4);
   const size_t o_tid = off; off += pk ? 0 : al(R * 4);
   const size_t o_pos = off; off += pk ? 0 : al(R * 4);
@@ -692,7 +694,7 @@ int brb_batch_download(brb_ctx* c, brb_batch_out* out) {
   int rc = ord ? dn(o_groff, c->g_roff, (G + 1) * 4) : 0;
   if (!rc) rc = dn(o_aoff, c->a_roff, cm ? NB * 4 : N * 4);
   if (!rc) rc = dn(o_acnt, c->a_rcnt, cm ? N * 2 : N * 4);
-  if (!rc && pk) rc = dn(o_prow, c->p_row, R * (cm ? 12 : 16));
+  if (!rc && pk) rc = dn(o_prow, c->p_row, R * row_bytes);
   if (!rc && !pk) rc = dn(o_src, c->o_src, R * 4);
   if (!rc && !pk) rc = dn(o_tid, c->o_tid, R * 4);
   if (!rc && !pk) rc = dn(o_pos, c->o_pos, R * 4);
@@ -712,7 +714,7 @@ int brb_batch_download(brb_ctx* c, brb_batch_out* out) {
   out->group_rec_off = ord ? (const uint32_t*)(h + o_groff) : nullptr;
   out->aln_rec_off = cm ? nullptr : (const uint32_t*)(h + o_aoff); out->aln_rec_cnt = cm ? nullptr : (const uint32_t*)(h + o_acnt);
   out->batch_rec_off = cm ? (const uint32_t*)(h + o_aoff) : nullptr; out->aln_rec_cnt16 = cm ? (const uint16_t*)(h + o_acnt) : nullptr;
-  out->packed_rows = pk ? (const uint32_t*)(h + o_prow) : nullptr;
+  out->packed_rows = pk ? (const uint32_t*)(h + o_prow) : nullptr; out->packed_row_words = pk ? (uint32_t)(row_bytes / 4) : 0u;
   out->src_aln = pk ? nullptr : (const uint32_t*)(h + o_src); out->tid = pk ? nullptr : (const uint32_t*)(h + o_tid);
   out->pos = pk ? nullptr : (const uint32_t*)(h + o_pos); out->tx_strand = pk ? nullptr : (const int8_t*)(h + o_strand); out->flags = pk ? nullptr : h + o_flags;
   out->sim_score = sc ? (const double*)(h + o_sim) : nullptr; out->clip_score = sc ? (const int32_t*)(h + o_clip) : nullptr;
@@ -734,7 +736,7 @@ int brb_ctx_set_option(brb_ctx* c, int option, int value) {
   if (option == BRB_OPT_GENERIC_FRONT) { c->opt_generic_front = value != 0; return BRB_OK; }
   if (option == BRB_OPT_NO_FASTPATH) { c->opt_no_fastpath = value != 0; return BRB_OK; }
   if (option == BRB_OPT_ORDERED_ROWS) { c->opt_ordered = value != 0; return BRB_OK; }
-  if (option == BRB_OPT_PACKED_ROWS) { c->opt_packed = value != 0; c->opt_compact = value == 2; return BRB_OK; }
+  if (option == BRB_OPT_PACKED_ROWS) { c->opt_packed = value != 0; c->opt_compact = value == 2 || value == 3; c->compact_level = value == 3 ? 2u : value == 2 ? 1u : 0u; return BRB_OK; }
   if (option == BRB_OPT_MERGE_WARP) { c->opt_merge_warp = value != 0; return BRB_OK; }
   if (option == BRB_OPT_FLUSH_TAGS) { c->opt_flush_tags = value != 0; return BRB_OK; }
   return fail(BRB_E_ARG, "unknown option %d", option);

@@ -343,6 +343,13 @@ __global__ void __launch_bounds__(256, LONG ? 3 : VAR_BACK_CTAS) k_back(DevBatch
             if (v.m_sim) { pv_.sim[r] = v.m_sim[cc]; pv_.clip[r] = v.m_clip[cc]; }
           } else if (PACKED) {
             const uint32_t w = (inl ? (m.z | BRB_ROW_INLINE) : wpos) | (minus << 28) | (fl << 29);
+            if (b.compact_rows == 2) {                        // 8 bytes: tid 22 | pos 24 | flags 3 | '-' 1 | inline 1 | 13 bits: M length (inline) or words of the pool entry
+              const uint32_t cl = inl ? (m.z >> 4) : len;
+              if ((m.w >> 22) | (m.x >> 24) | (cl >> 13)) atomicMax(&ctl->bad_input, 7u);
+              st_stream(reinterpret_cast<unsigned long long*>(pv_.row) + r,
+                        (unsigned long long)m.w | ((unsigned long long)m.x << 22) | ((unsigned long long)fl << 46) | ((unsigned long long)minus << 49) |
+                        ((unsigned long long)(inl ? 1u : 0u) << 50) | ((unsigned long long)cl << 51));
+            } else
             if (b.compact_rows) { uint32_t* q = reinterpret_cast<uint32_t*>(pv_.row) + 3 * (size_t)r; st_stream(q, m.w); st_stream(q + 1, m.x); st_stream(q + 2, w); }
             else st_stream(&pv_.row[r], make_uint4(aln, m.w, m.x, w));
             if (v.m_sim) { o.sim[r] = v.m_sim[cc]; o.clip[r] = v.m_clip[cc]; }

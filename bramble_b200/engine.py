@@ -42,14 +42,34 @@ def _columns(o, copy=False, batch=None):
         return d
     compact = bool(getattr(o, "aln_rec_cnt16", None))
     if compact:
-        p3 = arr(o.packed_rows, 3 * n).reshape(n, 3)
         assert batch is not None, "compact rows: the batch is needed to name the source alignments"
         n_aln = int(batch.desc.n_aln)
         aoff, acnt = _unit_blocks(o, n_aln)
         owner = np.zeros(n, np.int64)
         owner[(np.repeat(aoff, acnt) + (np.arange(int(acnt.sum())) - np.repeat(np.cumsum(acnt) - acnt, acnt)))] = np.repeat(np.arange(n_aln), acnt)
+        mates = batch.arrays["mate_idx"].astype(np.int64)
+        if int(getattr(o, "packed_row_words", 3)) == 2:                 # option value 3: one 64-bit word per row (include/bramble_b200.h, BRB_ROW8_*)
+            v = arr(o.packed_rows, 2 * n).view(np.uint64)
+            tid8 = (v & np.uint64(0x3FFFFF)).astype(np.uint32); pos8 = ((v >> np.uint64(22)) & np.uint64(0xFFFFFF)).astype(np.uint32)
+            fl8 = ((v >> np.uint64(46)) & np.uint64(7)).astype(np.uint8); minus8 = ((v >> np.uint64(49)) & np.uint64(1)).astype(bool)
+            inl8 = ((v >> np.uint64(50)) & np.uint64(1)).astype(bool); n8 = (v >> np.uint64(51)).astype(np.int64)
+            pool = arr(o.cigar, W)
+            clen = np.where(inl8, 1, n8)
+            coff = np.concatenate([[0], np.cumsum(clen)])
+            words = np.zeros(int(coff[-1]), dtype=np.uint32)
+            words[coff[:-1][inl8]] = (n8[inl8].astype(np.uint32) << np.uint32(4))               # (len << 4) | M
+            lens = n8[~inl8]
+            if lens.size:                                               # pool entries in row order: entry k starts behind the k earlier ones (and their length words)
+                start = np.cumsum(lens + 1) - (lens + 1)
+                assert np.array_equal(pool[start], lens.astype(np.uint32)), "8-byte rows: pool entries are not in row order"
+                within = np.arange(int(lens.sum()), dtype=np.int64) - np.repeat(np.cumsum(lens) - lens, lens)
+                words[np.repeat(coff[:-1][~inl8], lens) + within] = pool[np.repeat(start + 1, lens) + within]
+            src = np.where((fl8 & 1) == 1, owner, mates[owner]).astype(np.uint32)
+            d.update(src_aln=src, tid=tid8, pos=pos8, tx_strand=np.where(minus8, ord("-"), ord("+")).astype(np.int8), flags=fl8, cigar_off=coff, cigar=words)
+            return d
+        p3 = arr(o.packed_rows, 3 * n).reshape(n, 3)
         first = ((p3[:, 2] >> 29) & 1) == 1
-        src = np.where(first, owner, batch.arrays["mate_idx"].astype(np.int64)[owner]).astype(np.uint32)
+        src = np.where(first, owner, mates[owner]).astype(np.uint32)
         pr = np.concatenate([src[:, None], p3], axis=1)
     else:
         pr = arr(o.packed_rows, 4 * n).reshape(n, 4)

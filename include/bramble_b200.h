@@ -134,6 +134,7 @@ typedef struct brb_batch_out {
   const uint32_t* batch_rec_off;        /* (n_aln + 31) / 32: first row of the units owned by alignments 32k .. 32k + 31; their blocks follow
                                          * each other in alignment order */
   const uint16_t* aln_rec_cnt16;        /* n_aln: rows of the unit owned by alignment a */
+  uint32_t        packed_row_words;     /* 32-bit words per row of packed_rows: 4 (option value 1), 3 (2), 2 (3); 0 when packed_rows is NULL */
 } brb_batch_out;
 
 /* BRB_OPT_PACKED_ROWS: the row columns as ONE 16-byte record per row -- a third fewer bytes device->host, which is what
@@ -145,6 +146,18 @@ typedef struct brb_batch_out {
  * alignment is implied by the unit block the row sits in (BRB_REC_FIRST rows belong to the owner a, the others to mate_idx[a]) --
  * and the unit blocks are found through batch_rec_off / aln_rec_cnt16 (2.1 bytes per alignment instead of 8).  Another quarter
  * off the device->host bytes. */
+/* BRB_OPT_PACKED_ROWS = 3 (short-read modes): as 2 with EIGHT bytes per row, one little-endian 64-bit word
+ *   tid : 22 | pos : 24 | BRB_REC_* flags : 3 | '-' : 1 | inline : 1 | n : 13
+ * inline = 1: the merged CIGAR is the single word (n << 4 | M) -- every plain short-read row.  inline = 0: the CIGAR has n words and sits in
+ * `cigar` behind a length word, and the pool entries come in ROW order: the k-th row with inline = 0 owns the k-th entry (a consumer that
+ * walks the rows keeps one cursor: entry = cigar[cur + 1 .. cur + 1 + n], cur += n + 1).  A bundle with a tid >= 2^22, a pos >= 2^24 or an
+ * n >= 2^13 is refused with BRB_E_UNSUPPORTED (project it with the option at 2). */
+#define BRB_ROW8_TID(v)    ((uint32_t)((v) & 0x3fffffu))
+#define BRB_ROW8_POS(v)    ((uint32_t)(((v) >> 22) & 0xffffffu))
+#define BRB_ROW8_FLAGS(v)  ((uint32_t)(((v) >> 46) & 7u))
+#define BRB_ROW8_MINUS(v)  ((uint32_t)(((v) >> 49) & 1u))
+#define BRB_ROW8_INLINE(v) ((uint32_t)(((v) >> 50) & 1u))
+#define BRB_ROW8_N(v)      ((uint32_t)((v) >> 51))
 #define BRB_ROW_FLAGS(w)   ((uint32_t)(w) >> 29)                 /* BRB_REC_* */
 #define BRB_ROW_MINUS(w)   (((uint32_t)(w) >> 28) & 1u)          /* tx_strand == '-' */
 #define BRB_ROW_INLINE     (1u << 27)                            /* set: BRB_ROW_CIGAR(w) is the CIGAR word itself */

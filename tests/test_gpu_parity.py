@@ -20,8 +20,8 @@ def _check(wl, what):
             alg = None
             # every front kernel: the default choice (short-read fast-path kernel where it applies), the short-read
             # kernel without the fast path, and the generic one; rows as unit blocks (default), in emit order, and as
-            # 16-byte packed records or 12-byte compact ones (long-read modes fall back to the 16-byte records)
-            for generic, nofast, ordered, packed in ((0, 0, 0, 0), (0, 1, 0, 0), (1, 0, 0, 0), (0, 0, 1, 0), (0, 0, 0, 1), (1, 0, 0, 1), (0, 0, 0, 2), (1, 0, 0, 2)):
+            # 16-byte packed records, 12-byte or 8-byte compact ones (long-read modes fall back to the 16-byte records)
+            for generic, nofast, ordered, packed in ((0, 0, 0, 0), (0, 1, 0, 0), (1, 0, 0, 0), (0, 0, 1, 0), (0, 0, 0, 1), (1, 0, 0, 1), (0, 0, 0, 2), (1, 0, 0, 2), (0, 0, 0, 3), (0, 1, 0, 3)):
                 eng.set_option(capi.OPT_GENERIC_FRONT, generic)
                 eng.set_option(capi.OPT_NO_FASTPATH, nofast)
                 eng.set_option(capi.OPT_ORDERED_ROWS, ordered)
@@ -113,19 +113,20 @@ def test_rows_checksum_matches_oracle():
     G = b.desc.n_groups
     parts = [b.slice_groups(G * i // 5, G * (i + 1) // 5) for i in range(5)]
     with engine.Engine(ix) as eng:
-        for ordered, packed in ((0, 0), (1, 0), (0, 1), (0, 2)):
+        for ordered, packed in ((0, 0), (1, 0), (0, 1), (0, 2), (0, 3)):
             eng.set_option(capi.OPT_ORDERED_ROWS, ordered)
             eng.set_option(capi.OPT_PACKED_ROWS, packed)
             o = eng.project(p, b, raw=True)
             assert bool(o.packed_rows) == bool(packed) and bool(o.src_aln) != bool(packed)
-            assert bool(o.aln_rec_cnt16) == (packed == 2) and bool(o.aln_rec_off) != (packed == 2) and bool(o.batch_rec_off) == (packed == 2)
+            assert bool(o.aln_rec_cnt16) == (packed >= 2) and bool(o.aln_rec_off) != (packed >= 2) and bool(o.batch_rec_off) == (packed >= 2)
+            assert o.packed_row_words == {0: 0, 1: 4, 2: 3, 3: 2}[packed]
             assert engine.rows_checksum(o, batch=b) == want
             if packed:                                         # bytes device -> host: 16 per row + 8 per alignment, or 12 + 2.1
-                per_row, per_aln = (12, 2.125) if packed == 2 else (16, 8)
+                per_row, per_aln = {1: (16, 8), 2: (12, 2.125), 3: (8, 2.125)}[packed]
                 assert abs(int(eng.stats().d2h_bytes) - (per_row * o.n_rec + per_aln * b.desc.n_aln + 4 * o.n_cigar_words)) < 256
         ctxs = [eng.context() for _ in range(2)]
         try:
-            for packed in (0, 1, 2):
+            for packed in (0, 1, 2, 3):
                 for c in ctxs:
                     c.set_option(capi.OPT_PACKED_ROWS, packed)
                 res = engine.project_pipelined(ctxs, p, parts, checksum=True)
