@@ -45,7 +45,9 @@ class BatchIn(C.Structure):
     _fields_ = [("n_aln", C.c_uint32), ("n_groups", C.c_uint32), ("group_off", u32p), ("refid", i32p),
                 ("strand", i8p), ("exon_off", u32p), ("exon_st", u32p), ("exon_en", u32p),
                 ("cigar_off", u32p), ("cigar", u32p), ("mate_idx", i32p), ("group_seq_off", u64p),
-                ("seq_codes", u8p), ("group_name_off", u64p), ("name_bytes", u8p)]
+                ("seq_codes", u8p), ("group_name_off", u64p), ("name_bytes", u8p),
+                ("pos0", i32p), ("cigar_cnt16", C.POINTER(C.c_uint16)), ("mate_delta16", C.POINTER(C.c_int16)), ("refid16", C.POINTER(C.c_int16)),
+                ("n_cigar_total", C.c_uint64)]
 
 
 class BatchOut(C.Structure):
@@ -67,7 +69,7 @@ class Stats(C.Structure):
 
 
 _PTR = {np.dtype(np.uint8): u8p, np.dtype(np.int8): i8p, np.dtype(np.uint32): u32p, np.dtype(np.int32): i32p,
-        np.dtype(np.uint64): u64p, np.dtype(np.float64): f64p}
+        np.dtype(np.uint64): u64p, np.dtype(np.float64): f64p, np.dtype(np.uint16): C.POINTER(C.c_uint16), np.dtype(np.int16): C.POINTER(C.c_int16)}
 
 
 def ptr(a, dtype=None):
@@ -118,6 +120,7 @@ def _declare(lib):
     lib.brb_ctx_destroy.argtypes = [C.c_void_p]
     lib.brb_project.argtypes = [C.c_void_p, C.POINTER(Params), C.POINTER(BatchIn), C.POINTER(BatchOut)]
     lib.brb_batch_upload.argtypes = [C.c_void_p, C.POINTER(BatchIn)]
+    lib.brb_batch_read_exons.argtypes = [C.c_void_p, u32p, u32p, u32p, C.c_uint64, C.POINTER(C.c_uint64)]
     lib.brb_project_resident.argtypes = [C.c_void_p, C.POINTER(Params)]
     lib.brb_batch_download.argtypes = [C.c_void_p, C.POINTER(BatchOut)]
     lib.brb_ctx_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
@@ -139,7 +142,7 @@ def _declare(lib):
     for f in ("brb_index_create", "brb_index_destroy", "brb_ctx_create", "brb_ctx_destroy", "brb_project",
               "brb_batch_upload", "brb_project_resident", "brb_batch_download", "brb_ctx_stats", "brb_ctx_set_option", "brb_ctx_timer_start",
               "brb_ctx_timer_stop", "brb_lookup",
-              "brb_merge_cigars", "brb_ksw_extend", "brb_sort_by_start", "brb_host_alloc", "brb_host_free", "brb_bgzf_compress", "brb_emit_bgzf", "brb_ctx_move_result", "brb_merge_cigars_static", "brb_bgzf_inflate"):
+              "brb_merge_cigars", "brb_ksw_extend", "brb_sort_by_start", "brb_host_alloc", "brb_host_free", "brb_bgzf_compress", "brb_emit_bgzf", "brb_ctx_move_result", "brb_merge_cigars_static", "brb_bgzf_inflate", "brb_batch_read_exons"):
         getattr(lib, f).restype = C.c_int
     return lib
 

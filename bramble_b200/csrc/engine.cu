@@ -27,6 +27,7 @@
 #include "k_deflate.cuh"
 #include "k_emit.cuh"
 #include "k_inflate.cuh"
+#include "k_expand.cuh"
 
 using namespace brb;
 
@@ -134,6 +135,7 @@ struct brb_ctx {
   Buf z_in, z_slots, z_sizes, z_crcs, z_tot, z_off, z_out, z_ticket; HBuf z_host;   // brb_bgzf_compress
   Buf e_raw, e_off, e_len, e_units, e_plan, e_sizes, e_offs, e_err;                // brb_emit_bgzf
   Buf i_in, i_meta, i_out, i_ctl; HBuf i_host, i_hmeta;                           // brb_bgzf_inflate
+  Buf x_cnt16, x_cnt32, x_md16, x_r16, x_pos, x_err;                              // compact input columns (k_expand.cuh)
   bool have_names = false, opt_flush_tags = false, result_tags = false;
   uint64_t in_bytes = 0, n_mates = 0, seq_bytes = 0, rescue_bytes = 0;
   bool have_batch = false, have_result = false, have_scores = false, opt_generic_front = false, opt_no_fastpath = false, opt_ordered = false, result_ordered = false, opt_packed = false, result_packed = false, opt_merge_warp = false, opt_compact = false, result_compact = false; uint32_t compact_level = 0, result_compact_level = 0;
@@ -156,7 +158,7 @@ struct brb_ctx {
   brb_stats stats{};
   std::vector<Buf*> all() {
     return {&in_group_off, &in_refid, &in_strand, &in_exon_off, &in_exon_st, &in_exon_en, &in_cigar_off, &in_cigar, &in_mate, &in_seq_off,
-            &in_seq, &in_name_off, &in_names, &f_hi, &f_nh, &f_mapq, &f_prim, &z_in, &z_slots, &z_sizes, &z_crcs, &z_tot, &z_off, &z_out, &z_ticket, &e_raw, &e_off, &e_len, &e_units, &e_plan, &e_sizes, &e_offs, &e_err, &i_in, &i_meta, &i_out, &i_ctl, &res_slab, &ctl, &q_any, &a_cand, &scan_tmp, &c_rec, &c_task, &c_first, &c_last, &c_nseg, &c_nguide, &c_cap, &ipool,
+            &in_seq, &in_name_off, &in_names, &f_hi, &f_nh, &f_mapq, &f_prim, &z_in, &z_slots, &z_sizes, &z_crcs, &z_tot, &z_off, &z_out, &z_ticket, &e_raw, &e_off, &e_len, &e_units, &e_plan, &e_sizes, &e_offs, &e_err, &i_in, &i_meta, &i_out, &i_ctl, &x_cnt16, &x_cnt32, &x_md16, &x_r16, &x_pos, &x_err, &res_slab, &ctl, &q_any, &a_cand, &scan_tmp, &c_rec, &c_task, &c_first, &c_last, &c_nseg, &c_nguide, &c_cap, &ipool,
             &r_left, &r_right, &rpool, &c_mg, &m_rec, &m_sim, &m_clip, &c_stage, &t_agg, &t_claim, &t_off, &p_row, &p_pool, &p_sim, &p_clip, &a_roff, &a_rcnt, &g_roff,
             &o_src, &o_tid, &o_pos, &o_strand, &o_flags, &o_sim, &o_clip, &o_coff, &tpool, &opool};
   }
@@ -350,11 +352,15 @@ static int batch_upload_async(brb_ctx* c, const brb_batch_in* in) {
   CU(cudaSetDevice(c->idx->device));
   c->have_batch = c->have_result = false; c->validated = false;
   const uint32_t n = in->n_aln, ng = in->n_groups;
-  if (n && (!in->group_off || !in->refid || !in->strand || !in->exon_off || !in->exon_st || !in->exon_en || !in->cigar_off ||
-            !in->cigar || !in->mate_idx)) return fail(BRB_E_ARG, "null batch column");
+  const bool cx_exon = in->pos0 != nullptr && !in->exon_off, cx_cig = in->cigar_cnt16 != nullptr && !in->cigar_off;
+  const bool cx_mate = in->mate_delta16 != nullptr && !in->mate_idx, cx_ref = in->refid16 != nullptr && !in->refid;
+  if (n && (!in->group_off || !(in->refid || cx_ref) || !in->strand || !(cx_exon || (in->exon_off && in->exon_st && in->exon_en)) ||
+            !(in->cigar_off || cx_cig) || !in->cigar || !(in->mate_idx || cx_mate))) return fail(BRB_E_ARG, "null batch column");
   if (n >= 0x7ffffff0u) return fail(BRB_E_ARG, "batch too large");
-  const uint32_t n_exon = n ? in->exon_off[n] : 0, n_cigar = n ? in->cigar_off[n] : 0;
-  if (n && (in->group_off[0] != 0 || in->group_off[ng] != n || in->exon_off[0] != 0 || in->cigar_off[0] != 0))
+  if (cx_cig && in->n_cigar_total >= 0xfffffff0ull) return fail(BRB_E_ARG, "batch too large");
+  uint32_t n_exon = (n && !cx_exon) ? in->exon_off[n] : 0;
+  const uint32_t n_cigar = !n ? 0 : cx_cig ? (uint32_t)in->n_cigar_total : in->cigar_off[n];
+  if (n && (in->group_off[0] != 0 || in->group_off[ng] != n || (!cx_exon && in->exon_off[0] != 0) || (!cx_cig && in->cigar_off[0] != 0)))
     return fail(BRB_E_ARG, "inconsistent CSR offsets");
   c->in_bytes = 0;
   auto up = [&](Buf& b, const void* src, size_t bytes) -> int {
@@ -364,15 +370,61 @@ static int batch_upload_async(brb_ctx* c, const brb_batch_in* in) {
   };
   int rc = 0;
   static const uint32_t zero_off[1] = {0};
+  cudaStream_t st = c->st;
+  uint64_t Lx = 0;
   if (!rc) rc = up(c->in_group_off, n ? in->group_off : zero_off, n ? (size_t)(ng + 1) * 4 : 4);
-  if (!rc) rc = up(c->in_refid, in->refid, (size_t)n * 4);
   if (!rc) rc = up(c->in_strand, in->strand, (size_t)n);
-  if (!rc) rc = up(c->in_exon_off, n ? in->exon_off : zero_off, n ? (size_t)(n + 1) * 4 : 4);
-  if (!rc) rc = up(c->in_exon_st, in->exon_st, (size_t)n_exon * 4);
-  if (!rc) rc = up(c->in_exon_en, in->exon_en, (size_t)n_exon * 4);
-  if (!rc) rc = up(c->in_cigar_off, n ? in->cigar_off : zero_off, n ? (size_t)(n + 1) * 4 : 4);
+  if (!rc && !cx_ref) rc = up(c->in_refid, in->refid, (size_t)n * 4);
+  if (!rc && !cx_mate) rc = up(c->in_mate, in->mate_idx, (size_t)n * 4);
+  if (!rc && n && (cx_ref || cx_mate)) {                     // 16-bit links -> the 32-bit columns
+    if (cx_ref) { rc = up(c->x_r16, in->refid16, (size_t)n * 2); if (!rc) rc = c->in_refid.ensure((size_t)n * 4); }
+    if (!rc && cx_mate) { rc = up(c->x_md16, in->mate_delta16, (size_t)n * 2); if (!rc) rc = c->in_mate.ensure((size_t)n * 4); }
+    if (!rc) k_expand_links<<<grid_for(n, 256), 256, 0, st>>>(n, cx_mate ? c->x_md16.as<int16_t>() : nullptr, c->in_mate.as<int32_t>(), cx_ref ? c->x_r16.as<int16_t>() : nullptr, c->in_refid.as<int32_t>());
+  }
+  if (!rc && (cx_exon || cx_cig) && n) { rc = c->x_cnt32.ensure((size_t)n * 4 + 16); if (!rc) rc = c->scan_tmp.ensure(scan_scratch_words(n) * 8); if (!rc) rc = c->x_err.ensure(16); if (!rc && cudaMemsetAsync(c->x_err.p, 0, 16, st) != cudaSuccess) rc = fail(BRB_E_CUDA, "memset failed"); }
+  if (!rc && !cx_cig) rc = up(c->in_cigar_off, n ? in->cigar_off : zero_off, n ? (size_t)(n + 1) * 4 : 4);
+  if (!rc && cx_cig && n) {                                   // 16-bit counts -> CSR offsets (device scan)
+    rc = up(c->x_cnt16, in->cigar_cnt16, (size_t)n * 2);
+    if (!rc) rc = c->in_cigar_off.ensure((size_t)(n + 1) * 4);
+    if (!rc) {
+      k_expand_counts<<<grid_for(n, 256), 256, 0, st>>>(n, c->x_cnt16.as<uint16_t>(), c->x_cnt32.as<uint32_t>());
+      exclusive_scan(c->x_cnt32.as<uint32_t>(), c->in_cigar_off.as<uint32_t>(), n, reinterpret_cast<uint32_t*>(c->scan_tmp.p), st, &Lx);
+    }
+  }
   if (!rc) rc = up(c->in_cigar, in->cigar, (size_t)n_cigar * 4);
-  if (!rc) rc = up(c->in_mate, in->mate_idx, (size_t)n * 4);
+  if (!rc && !cx_exon) {
+    rc = up(c->in_exon_off, n ? in->exon_off : zero_off, n ? (size_t)(n + 1) * 4 : 4);
+    if (!rc) rc = up(c->in_exon_st, in->exon_st, (size_t)n_exon * 4);
+    if (!rc) rc = up(c->in_exon_en, in->exon_en, (size_t)n_exon * 4);
+  }
+  if (!rc && cx_exon && !n) rc = up(c->in_exon_off, zero_off, 4);
+  if (!rc && (cx_exon || cx_cig) && n) {                      // read exons from pos0 + CIGAR: count, scan, fill; the totals come back in one small copy
+    uint32_t* err = c->x_err.as<uint32_t>();
+    if (cx_exon) {
+      rc = up(c->x_pos, in->pos0, (size_t)n * 4);
+      if (!rc) rc = c->in_exon_off.ensure((size_t)(n + 1) * 4);
+      if (!rc) {
+        k_exon_count<<<grid_for(n, 256), 256, 0, st>>>(n, c->x_pos.as<int32_t>(), c->in_cigar_off.as<uint32_t>(), c->in_cigar.as<uint32_t>(), n_cigar, c->x_cnt32.as<uint32_t>(), err);
+        exclusive_scan(c->x_cnt32.as<uint32_t>(), c->in_exon_off.as<uint32_t>(), n, reinterpret_cast<uint32_t*>(c->scan_tmp.p), st, &Lx);
+      }
+    }
+    uint32_t h[3] = {0, 0, 0};                                // first invalid alignment + 1, exon total, CIGAR word total
+    if (!rc) {
+      CU(cudaMemcpyAsync(&h[0], err, 4, cudaMemcpyDeviceToHost, st));
+      if (cx_exon) CU(cudaMemcpyAsync(&h[1], c->in_exon_off.as<uint32_t>() + n, 4, cudaMemcpyDeviceToHost, st));
+      CU(cudaMemcpyAsync(&h[2], c->in_cigar_off.as<uint32_t>() + n, 4, cudaMemcpyDeviceToHost, st));
+      CU(cudaStreamSynchronize(st));
+      CU(cudaGetLastError());
+      if (h[2] != n_cigar) return fail(BRB_E_ARG, "cigar_cnt16 sums to %u words, n_cigar_total says %u", h[2], n_cigar);
+      if (h[0]) return fail(BRB_E_ARG, "invalid CIGAR: alignment %u yields no read exon", h[0] - 1);
+    }
+    if (!rc && cx_exon) {
+      n_exon = h[1];
+      rc = c->in_exon_st.ensure((size_t)n_exon * 4 + 16); if (!rc) rc = c->in_exon_en.ensure((size_t)n_exon * 4 + 16);
+      if (!rc) k_exon_fill<<<grid_for(n, 256), 256, 0, st>>>(n, c->x_pos.as<int32_t>(), c->in_cigar_off.as<uint32_t>(), c->in_cigar.as<uint32_t>(), c->in_exon_off.as<uint32_t>(),
+                                                             c->in_exon_st.as<uint32_t>(), c->in_exon_en.as<uint32_t>());
+    }
+  }
   c->seq_bytes = 0;
   const bool have_seq = n && in->group_seq_off && in->seq_codes;
   if (!rc && have_seq) {
@@ -395,6 +447,20 @@ static int batch_upload_async(brb_ctx* c, const brb_batch_in* in) {
   b.aln_group = nullptr; b.back_shift = 5; b.front_shift = 5; b.count_hits = 0; b.compact_rows = 0;
   c->stats.h2d_bytes = c->in_bytes;
   c->have_batch = true;
+  return BRB_OK;
+}
+
+// The read exons of the resident batch as the engine holds them -- uploaded, or derived on the device from pos0 + CIGAR.
+int brb_batch_read_exons(brb_ctx* c, uint32_t* exon_off, uint32_t* exon_st, uint32_t* exon_en, uint64_t cap, uint64_t* n_exon) {
+  if (!c || !n_exon) return fail(BRB_E_ARG, "brb_batch_read_exons: null argument");
+  if (!c->have_batch) return fail(BRB_E_ARG, "no batch resident: call brb_batch_upload first");
+  CU(cudaSetDevice(c->idx->device));
+  *n_exon = c->b.n_exon;
+  if (c->b.n_exon > cap) return fail(BRB_E_ARG, "brb_batch_read_exons: %u exons, room for %llu", c->b.n_exon, (unsigned long long)cap);
+  if (exon_off) CU(cudaMemcpyAsync(exon_off, c->in_exon_off.p, (size_t)(c->b.n_aln + 1) * 4, cudaMemcpyDeviceToHost, c->st));
+  if (exon_st && c->b.n_exon) CU(cudaMemcpyAsync(exon_st, c->in_exon_st.p, (size_t)c->b.n_exon * 4, cudaMemcpyDeviceToHost, c->st));
+  if (exon_en && c->b.n_exon) CU(cudaMemcpyAsync(exon_en, c->in_exon_en.p, (size_t)c->b.n_exon * 4, cudaMemcpyDeviceToHost, c->st));
+  CU(cudaStreamSynchronize(c->st));
   return BRB_OK;
 }
 

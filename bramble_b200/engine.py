@@ -47,7 +47,7 @@ def _columns(o, copy=False, batch=None):
         aoff, acnt = _unit_blocks(o, n_aln)
         owner = np.zeros(n, np.int64)
         owner[(np.repeat(aoff, acnt) + (np.arange(int(acnt.sum())) - np.repeat(np.cumsum(acnt) - acnt, acnt)))] = np.repeat(np.arange(n_aln), acnt)
-        mates = batch.arrays["mate_idx"].astype(np.int64)
+        mates = getattr(batch, "arrays_full", batch.arrays)["mate_idx"].astype(np.int64)
         if int(getattr(o, "packed_row_words", 3)) == 2:                 # option value 3: one 64-bit word per row (include/bramble_b200.h, BRB_ROW8_*)
             v = arr(o.packed_rows, 2 * n).view(np.uint64)
             tid8 = (v & np.uint64(0x3FFFFF)).astype(np.uint32); pos8 = ((v >> np.uint64(22)) & np.uint64(0xFFFFFF)).astype(np.uint32)
@@ -237,6 +237,14 @@ class Engine:
 
     def upload(self, batch):
         capi.check(self.lib.brb_batch_upload(self._ctx, C.byref(batch.desc)), "brb_batch_upload")
+        self._n_aln_resident = int(batch.desc.n_aln)
+
+    def read_exons(self, cap):
+        """(exon_off, exon_st, exon_en) of the resident batch as the engine holds them."""
+        n_aln = int(self._n_aln_resident)
+        off = np.zeros(n_aln + 1, np.uint32); st = np.zeros(max(1, cap), np.uint32); en = np.zeros(max(1, cap), np.uint32); n = C.c_uint64()
+        capi.check(self.lib.brb_batch_read_exons(self._ctx, capi.ptr(off), capi.ptr(st), capi.ptr(en), cap, C.byref(n)), "brb_batch_read_exons")
+        return off, st[:n.value], en[:n.value]
 
     def run_resident(self, params):
         capi.check(self.lib.brb_project_resident(self._ctx, C.byref(params)), "brb_project_resident")
@@ -263,6 +271,7 @@ class Engine:
         nb = copy.copy(batch)
         nb.desc = capi.BatchIn()
         nb.desc.n_aln, nb.desc.n_groups = batch.desc.n_aln, batch.desc.n_groups
+        nb.desc.n_cigar_total = batch.desc.n_cigar_total
         nb.arrays = {}
         nb._pins = []
         for k, a in batch.arrays.items():

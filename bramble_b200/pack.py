@@ -258,6 +258,44 @@ class Batch:
         self.desc.group_name_off = capi.ptr(A["group_name_off"]); self.desc.name_bytes = capi.ptr(A["name_bytes"])
         return self
 
+    def compact(self, exons=True):
+        """The same bundle with the compact input columns of brb_batch_in (fewer bytes host -> device): 16-bit CIGAR word counts, 16-bit
+        mate deltas and refids, and -- `exons` -- the 0-based position instead of the read-exon arrays (the engine derives the exons
+        from position + CIGAR as the reference's ingest does).  The columns they replace are left out (NULL)."""
+        A = self.arrays
+        n = int(self.desc.n_aln)
+        nb = Batch()
+        B = nb.arrays
+        for k in ("group_off", "strand", "cigar", "group_seq_off", "seq_codes", "group_name_off", "name_bytes"):
+            if k in A:
+                B[k] = A[k]
+        co = A["cigar_off"].astype(np.int64)[:n + 1]
+        cnt = np.diff(co)
+        mate = A["mate_idx"].astype(np.int64)[:n]
+        delta = np.where(mate >= 0, mate - np.arange(n), 0)
+        refid = A["refid"].astype(np.int64)[:n]
+        if n and (cnt.max() > 65535 or np.abs(delta).max() > 32767 or refid.max() > 32767 or refid.min() < -32768):
+            raise ValueError("bundle does not fit the compact columns")
+        B["cigar_cnt16"] = np.ascontiguousarray(cnt, dtype=np.uint16) if n else np.zeros(1, np.uint16)
+        B["mate_delta16"] = np.ascontiguousarray(delta, dtype=np.int16) if n else np.zeros(1, np.int16)
+        B["refid16"] = np.ascontiguousarray(refid, dtype=np.int16) if n else np.zeros(1, np.int16)
+        if exons:
+            eo = A["exon_off"].astype(np.int64)[:n]
+            B["pos0"] = (A["exon_st"].astype(np.int64)[eo] - 1).astype(np.int32) if n else np.zeros(1, np.int32)      # the first read exon starts at pos0 + 1
+        else:
+            for k in ("exon_off", "exon_st", "exon_en"):
+                B[k] = A[k]
+        nb.src, nb.src_offset, nb.names = self.src, self.src_offset, self.names
+        d = nb.desc
+        d.n_aln, d.n_groups = self.desc.n_aln, self.desc.n_groups
+        d.n_cigar_total = int(co[n]) if n else 0
+        for k, a in B.items():
+            if hasattr(d, k):
+                setattr(d, k, capi.ptr(a))
+        # (the decoded columns stay reachable for code that reads them on the host: row unpacking needs mate_idx)
+        nb.arrays_full = A
+        return nb
+
     def slice_groups(self, g0, g1):
         """Read-name groups [g0, g1) as a bundle of their own (mates never leave their group, src/bramble.cpp:272-311)."""
         A = self.arrays

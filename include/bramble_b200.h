@@ -93,6 +93,18 @@ typedef struct brb_batch_in {
   const uint8_t*  seq_codes;            /* group-shared read sequence (src/core.cpp:353-378), codes 0..4 */
   const uint64_t* group_name_off;       /* n_groups+1 byte offsets into name_bytes; NULL unless BRB_OPT_FLUSH_TAGS is used */
   const uint8_t*  name_bytes;           /* the read names (QNAME without the terminator), group after group */
+  /* Compact alternatives (each optional, NULL = not used): what bounds a caller that streams bundles through brb_project() is the
+   * bytes that cross the bus, and four of the columns above can be said in fewer.  When one of these is given, the column it
+   * replaces may be NULL; the engine expands it on the device (k_expand.cuh). */
+  const int32_t*  pos0;                 /* n_aln: 0-based leftmost coordinate (BAM pos).  Replaces exon_off / exon_st / exon_en: the read
+                                         * exons are derived from pos0 + CIGAR on the device exactly as the reference's ingest derives them
+                                         * (GSamRecord::setupCoordinates + process_exons, src/bramble.cpp:246-255; an alignment whose CIGAR
+                                         * yields no exon is the reference's "invalid CIGAR" error: BRB_E_ARG) */
+  const uint16_t* cigar_cnt16;          /* n_aln: CIGAR words per alignment (BAM's n_cigar_op is 16 bits too).  Replaces cigar_off;
+                                         * n_cigar_total must hold their sum */
+  const int16_t*  mate_delta16;         /* n_aln: 0 = no mate, else mate index - own index (mates sit in the same read-name group).  Replaces mate_idx */
+  const int16_t*  refid16;              /* n_aln: as refid.  Replaces refid */
+  uint64_t        n_cigar_total;        /* only read with cigar_cnt16 */
 } brb_batch_in;
 
 /* One row per output BAM record.  Rows come in UNIT blocks: the unit owned by alignment a (an unpaired alignment, or
@@ -195,6 +207,9 @@ int brb_project(brb_ctx* ctx, const brb_params* p, const brb_batch_in* in, brb_b
  * copies have completed: the caller's columns may be reused at once. */
 int brb_batch_upload(brb_ctx* ctx, const brb_batch_in* in);
 int brb_project_resident(brb_ctx* ctx, const brb_params* p);
+/* The read exons of the resident batch as the engine holds them (exon_off: n_aln+1 entries; cap = room in exon_st / exon_en; any of the
+ * three may be NULL): what a batch uploaded with pos0 instead of exon columns was expanded to on the device. */
+int brb_batch_read_exons(brb_ctx* ctx, uint32_t* exon_off, uint32_t* exon_st, uint32_t* exon_en, uint64_t cap, uint64_t* n_exon);
 int brb_batch_download(brb_ctx* ctx, brb_batch_out* out);
 
 int brb_ctx_stats(const brb_ctx* ctx, brb_stats* out);

@@ -26,7 +26,7 @@ def test_all_declared_symbols_are_exported():
 
 def test_struct_sizes_match_header():
     assert C.sizeof(capi.Params) == 24
-    assert C.sizeof(capi.BatchIn) == 8 + 13 * 8
+    assert C.sizeof(capi.BatchIn) == 8 + 13 * 8 + 5 * 8
     assert C.sizeof(capi.IndexDesc) == 8 + 12 * 8 + 8 + 2 * 8
 
 

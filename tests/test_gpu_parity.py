@@ -638,3 +638,70 @@ def test_bgzf_device_decoder_matches_zlib():
         with pytest.raises(capi.EngineError):
             eng.bgzf_inflate(blocks(bam[:40000], 6)[:-5])       # truncated
         assert eng.bgzf_inflate(blocks(bam, 1)) == bam          # the context is fine after the refusals
+
+
+# ---- compact input columns (brb_batch_in::pos0 / cigar_cnt16 / mate_delta16 / refid16)
+
+def test_read_exons_derived_on_device_match_ingest():
+    """pos0 + CIGAR -> read exons on the device (k_expand.cuh) against the Python restatement of the reference's ingest (pack.read_exons, which
+    the CLI tests pin on the reference binary): every CIGAR shape incl. the quirks -- leading N, I between two Ns (no exon closed), D, clips,
+    =/X, N at the end -- and random ones."""
+    from bramble_b200 import pack
+    wl = common.make_workload("default", 141, n_names=20)
+    rng = np.random.default_rng(3)
+    M, I, D, N, S, H, EQ, X = 0, 1, 2, 3, 4, 5, 7, 8
+    shapes = [[(M, 100)], [(S, 5), (M, 50), (N, 200), (M, 45)], [(N, 30), (M, 60)], [(M, 40), (N, 100), (I, 3), (N, 50), (M, 57)],
+              [(M, 40), (I, 3), (N, 100), (M, 57)], [(H, 10), (S, 2), (EQ, 30), (X, 1), (EQ, 20), (D, 4), (M, 10), (N, 1000), (M, 30), (S, 7)],
+              [(M, 10), (N, 20)], [(M, 10), (N, 20), (N, 30), (M, 5)], [(I, 5), (M, 20)], [(M, 20), (D, 5), (N, 7), (D, 2), (M, 9)], [(M, 1)]]
+    for _ in range(400):
+        k = int(rng.integers(1, 12))
+        shapes.append([(int(rng.choice([M, M, M, I, D, N, N, S, EQ, X])), int(rng.integers(1, 300))) for _ in range(k)])
+    cigs, pos, exp_off, exp_st, exp_en = [], [], [0], [], []
+    for sh in shapes:
+        words = [(l << 4) | o for o, l in sh]
+        p0 = int(rng.integers(0, 1 << 27))
+        ex = pack.read_exons(p0, words)
+        cigs.append(np.array(words, np.uint32)); pos.append(p0)
+        exp_st += [s for s, _ in ex]; exp_en += [e for _, e in ex]; exp_off.append(len(exp_st))
+    n = len(cigs)
+    assert n > 300
+    b = pack.Batch()
+    A = b.arrays
+    A["group_off"] = np.arange(n + 1, dtype=np.uint32); A["strand"] = np.full(n, ord("."), np.int8); A["cigar"] = np.concatenate(cigs)
+    A["cigar_cnt16"] = np.array([len(c) for c in cigs], np.uint16); A["mate_delta16"] = np.zeros(n, np.int16); A["refid16"] = np.zeros(n, np.int16)
+    A["pos0"] = np.array(pos, np.int32)
+    b.desc.n_aln = b.desc.n_groups = n; b.desc.n_cigar_total = int(len(A["cigar"]))
+    for k, a in A.items():
+        setattr(b.desc, k, capi.ptr(a))
+    with engine.Engine(wl["index"]) as eng:
+        eng.upload(b)
+        off, st, en = eng.read_exons(len(exp_st) + 10)
+        assert np.array_equal(off, np.array(exp_off, np.uint32)) and np.array_equal(st, np.array(exp_st, np.uint32)) and np.array_equal(en, np.array(exp_en, np.uint32))
+        # no aligned base at position 0 (the last exon end stays 0): the reference's "invalid CIGAR" error
+        A["cigar"][0] = (50 << 4) | S; A["cigar_cnt16"][0] = 1; A["pos0"][0] = 0
+        A["cigar"] = np.concatenate([A["cigar"][:1], np.concatenate(cigs[1:])]); b.desc.cigar = capi.ptr(A["cigar"]); b.desc.n_cigar_total = int(len(A["cigar"]))
+        with pytest.raises(capi.EngineError, match="invalid CIGAR"):
+            eng.upload(b)
+        b.desc.n_cigar_total += 1
+        with pytest.raises(capi.EngineError, match="n_cigar_total"):
+            eng.upload(b)
+
+
+@pytest.mark.parametrize("mode", ["default", "fr", "lr", "lrhq"])
+def test_compact_input_columns_give_the_same_rows(mode):
+    """A bundle uploaded with the compact columns (16-bit CIGAR counts, mate deltas, refids; position instead of the exon arrays) projects
+    to the rows of the plain columns = the oracle's; fewer bytes go up."""
+    wl = common.make_workload(mode, 143, n_names=1200, n_genes=40)
+    ix, p = wl["index"], wl["params"]
+    with engine.Engine(ix) as eng:
+        for b in wl["batches"]:
+            exp = oracle_lib.port_project(ix, p, b)
+            full = eng.project(p, b); h_full = int(eng.stats().h2d_bytes)
+            oracle_lib.assert_rows_equal(exp, full, f"{mode} plain")
+            for exons in (True, False):
+                got = eng.project(p, b.compact(exons=exons))
+                oracle_lib.assert_rows_equal(exp, got, f"{mode} compact exons={exons}")
+                assert int(eng.stats().h2d_bytes) < h_full
+            eng.set_option(capi.OPT_PACKED_ROWS, 3 if not wl["mode"]["long"] else 1)
+            oracle_lib.assert_rows_equal(exp, eng.project(p, b.compact()), f"{mode} compact in, packed out")
+            eng.set_option(capi.OPT_PACKED_ROWS, 0)
