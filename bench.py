@@ -343,10 +343,11 @@ def measure_workload(W, args, local, cores, peak, with_cpu=True):
         if args.no_e2e:
             return rec
         # end to end: one brb_project() call from pinned host columns (H2D + kernels + D2H)
-        PB = eng.pinned_copy(B)
+        want_rows = engine.rows_checksum(eng.download(B, raw=True))          # (the resident result of the timed steps)
+        PB = eng.pinned_copy(B.compact())                                   # compact input columns: 16-bit counts / links, position instead of exon arrays
         try:
             eng.set_option(capi.OPT_PACKED_ROWS, 0 if W.long else 3)
-            eng.project(p, PB, raw=True)
+            got_rows = engine.rows_checksum(eng.project(p, PB, raw=True), batch=PB)
             t0 = time.perf_counter()
             reps = 3
             for _ in range(reps):
@@ -354,7 +355,8 @@ def measure_workload(W, args, local, cores, peak, with_cpu=True):
             dt = (time.perf_counter() - t0) / reps
             s2 = eng.stats()
             rec["e2e"] = {"value": n_aln / dt, "unit": UNIT, "h2d_bytes_per_step": int(s2.h2d_bytes), "d2h_bytes_per_step": int(s2.d2h_bytes),
-                          "how": "one brb_project() call for the bundle from pinned host columns, no overlap between calls"}
+                          "how": "one brb_project() call for the bundle from pinned host columns (compact input columns; rows as 8-byte records for short reads), no overlap between calls",
+                          "rows_agree_with_resident_run": got_rows == want_rows}
             eng.set_option(capi.OPT_PACKED_ROWS, 0)
         finally:
             eng.pinned_free(PB)
@@ -410,9 +412,11 @@ def main():
     ap.add_argument("--no-workloads", action="store_true", help="skip the c1/c3/c4/c5 sub-records of the 1-GPU run")
     ap.add_argument("--only-workloads", default=None, help="comma list: restrict the sub-records (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs: resident steps only (also skips the ordered-rows leg, the sustained loop and the sub-records' extras)")
-    ap.add_argument("--e2e-bundles", type=int, default=8, help="bundles per step on the end-to-end path")
+    ap.add_argument("--e2e-bundles", type=int, default=6, help="bundles per step on the end-to-end path")
     ap.add_argument("--e2e-rows", default="compact8", choices=["compact8", "compact", "packed", "columns"],
                     help="row layout on the end-to-end path: BRB_OPT_PACKED_ROWS = 3 (8-byte rows + 16-bit unit sizes), = 2 (12-byte rows), = 1 (16-byte records) or the plain columns")
+    ap.add_argument("--e2e-input", default="compact", choices=["compact", "columns"],
+                    help="input columns on the end-to-end path: the compact ones of brb_batch_in (pos0, cigar_cnt16, mate_delta16, refid16) or the plain columns")
     ap.add_argument("--no-bind", action="store_true", help="N>1: do not pin each rank to the CPUs of its GPU's NUMA node")
     ap.add_argument("--e2e-contexts", type=int, default=3, help="brb_ctx (host threads / streams) on the end-to-end path")
     ap.add_argument("--sustained-s", type=float, default=2.0, help="length of the sustained resident loop")
@@ -581,7 +585,7 @@ def main():
         G = int(B.desc.n_groups)
         nbun = max(1, min(args.e2e_bundles, G))
         cuts = [G * i // nbun for i in range(nbun + 1)]
-        PBs = [eng.pinned_copy(B.slice_groups(g0, g1)) for g0, g1 in zip(cuts[:-1], cuts[1:])]
+        PBs = [eng.pinned_copy(B.slice_groups(g0, g1).compact() if args.e2e_input == "compact" else B.slice_groups(g0, g1)) for g0, g1 in zip(cuts[:-1], cuts[1:])]
         ctxs = [eng.context() for _ in range(max(1, args.e2e_contexts))]
         e2e_packed = 0 if (Wh.long or args.e2e_rows == "columns") else {"compact8": 3, "compact": 2, "packed": 1}[args.e2e_rows]
         for c in ctxs:
@@ -599,7 +603,7 @@ def main():
         e2e_h2d, e2e_d2h, e2e_rec = sum(r[2] for r in res), sum(r[3] for r in res), sum(r[0] for r in res)
         barrier()
         # the same through ONE call on one context (no overlap), for comparison
-        PB = eng.pinned_copy(B)
+        PB = eng.pinned_copy(B.compact() if args.e2e_input == "compact" else B)
         eng.project(p, PB, raw=True)
         t0 = time.perf_counter()
         for _ in range(min(3, args.steps)):
@@ -644,6 +648,7 @@ def main():
                 "e2e": None if args.no_e2e else {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": e2e_h2d, "d2h_bytes_per_step": e2e_d2h,
                         "records_per_step": e2e_rec, "bundles_per_step": nbun, "contexts": len(ctxs),
                         "how": "brb_project() per bundle from pinned host columns, one host thread per context",
+                        "input": "compact columns (pos0, cigar_cnt16, mate_delta16, refid16)" if args.e2e_input == "compact" else "plain columns",
                         "rows": {3: "BRB_OPT_PACKED_ROWS = 3: 8 bytes per row (tid 22 | pos 24 | flags | CIGAR length), 16-bit unit sizes + one row offset per 32 alignments",
                                  2: "BRB_OPT_PACKED_ROWS = 2: 12 bytes per row (tid, pos, word), 16-bit unit sizes + one row offset per 32 alignments", 1: "BRB_OPT_PACKED_ROWS = 1: one 16-byte record per row",
                                  0: "columns (22 bytes per row + CIGAR CSR)"}[e2e_packed],

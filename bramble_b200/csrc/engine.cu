@@ -1120,8 +1120,9 @@ int brb_merge_cigars_static(int device, void* stream, uint32_t n, uint32_t max_r
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   CU(cudaMemsetAsync(base, 0, 256, st));                     // the status words start at zero; the merge scratch is written before it is read
   if (n) {
-    // persistent warps, one slice each: as many as the array holds (>= 1), as the pairs need, and as a B200 keeps resident
-    const uint64_t fit = BRB_STATIC_SCRATCH_WORDS / slice, want = std::min<uint64_t>(n, 148ull * 64);
+    // persistent warps, one slice each: as many as the array holds (>= 1), as the pairs need, and as the device keeps resident (64 per SM)
+    int n_sm = 0; CU(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, device));
+    const uint64_t fit = BRB_STATIC_SCRATCH_WORDS / slice, want = std::min<uint64_t>(n, (uint64_t)std::max(1, n_sm) * 64);
     const unsigned block = fit >= 4 ? 128u : 32u, wpb = block / 32;
     const unsigned ctas = (unsigned)std::max<uint64_t>(1, std::min<uint64_t>((want + wpb - 1) / wpb, fit / wpb));
     k_merge_pairs_static<<<ctas, block, 0, st>>>(n, d_real_off, d_real, d_ideal_off, d_ideal, d_out_off, d_out_len, d_out, base + 64, (uint32_t)slice, base);
