@@ -136,6 +136,7 @@ struct brb_ctx {
   Buf e_raw, e_off, e_len, e_units, e_plan, e_sizes, e_offs, e_err;                // brb_emit_bgzf
   Buf i_in, i_meta, i_out, i_ctl; HBuf i_host, i_hmeta;                           // brb_bgzf_inflate
   Buf x_cnt16, x_cnt32, x_md16, x_r16, x_pos, x_err;                              // compact input columns (k_expand.cuh)
+  bool expand_pending = false, expand_exons = false, expand_cigar = false; uint32_t expand_n_cigar = 0;   // k_expand_all has run for the resident batch, its totals / verdict not read yet
   bool have_names = false, opt_flush_tags = false, result_tags = false;
   uint64_t in_bytes = 0, n_mates = 0, seq_bytes = 0, rescue_bytes = 0;
   bool have_batch = false, have_result = false, have_scores = false, opt_generic_front = false, opt_no_fastpath = false, opt_ordered = false, result_ordered = false, opt_packed = false, result_packed = false, opt_merge_warp = false, opt_compact = false, result_compact = false; uint32_t compact_level = 0, result_compact_level = 0;
@@ -345,6 +346,20 @@ int brb_ctx_destroy(brb_ctx* c) {
   return BRB_OK;
 }
 
+// What k_expand_all found out about a batch that came with compact columns -- read after a stream synchronisation the caller has done
+// anyway (the public brb_batch_upload, or the end of a projection): the true exon total, and the two refusals.
+static int finish_expand(brb_ctx* c) {
+  if (!c->expand_pending) return BRB_OK;
+  c->expand_pending = false;
+  uint32_t h[4] = {0, 0, 0, 0};
+  CU(cudaMemcpyAsync(h, c->x_err.p, 16, cudaMemcpyDeviceToHost, c->st));     // (the ctx stream is idle here: this returns at once)
+  CU(cudaStreamSynchronize(c->st));
+  if (c->expand_cigar && (h[3] || h[2] != c->expand_n_cigar)) { c->have_batch = false; return fail(BRB_E_ARG, "cigar_cnt16 sums to %u words, n_cigar_total says %u", h[2], c->expand_n_cigar); }
+  if (h[0]) { c->have_batch = false; return fail(BRB_E_ARG, "invalid CIGAR: alignment %u yields no read exon", h[0] - 1); }
+  if (c->expand_exons) c->b.n_exon = h[1];
+  return BRB_OK;
+}
+
 // ---- batch upload: one bundle (reference BundleData::reads) as structure-of-arrays.  Content checks that
 // need a pass over the data (symmetric mate links, ascending read exons) run on the device inside k_lookup.
 static int batch_upload_async(brb_ctx* c, const brb_batch_in* in) {
@@ -371,26 +386,11 @@ static int batch_upload_async(brb_ctx* c, const brb_batch_in* in) {
   int rc = 0;
   static const uint32_t zero_off[1] = {0};
   cudaStream_t st = c->st;
-  uint64_t Lx = 0;
   if (!rc) rc = up(c->in_group_off, n ? in->group_off : zero_off, n ? (size_t)(ng + 1) * 4 : 4);
   if (!rc) rc = up(c->in_strand, in->strand, (size_t)n);
   if (!rc && !cx_ref) rc = up(c->in_refid, in->refid, (size_t)n * 4);
   if (!rc && !cx_mate) rc = up(c->in_mate, in->mate_idx, (size_t)n * 4);
-  if (!rc && n && (cx_ref || cx_mate)) {                     // 16-bit links -> the 32-bit columns
-    if (cx_ref) { rc = up(c->x_r16, in->refid16, (size_t)n * 2); if (!rc) rc = c->in_refid.ensure((size_t)n * 4); }
-    if (!rc && cx_mate) { rc = up(c->x_md16, in->mate_delta16, (size_t)n * 2); if (!rc) rc = c->in_mate.ensure((size_t)n * 4); }
-    if (!rc) k_expand_links<<<grid_for(n, 256), 256, 0, st>>>(n, cx_mate ? c->x_md16.as<int16_t>() : nullptr, c->in_mate.as<int32_t>(), cx_ref ? c->x_r16.as<int16_t>() : nullptr, c->in_refid.as<int32_t>());
-  }
-  if (!rc && (cx_exon || cx_cig) && n) { rc = c->x_cnt32.ensure((size_t)n * 4 + 16); if (!rc) rc = c->scan_tmp.ensure(scan_scratch_words(n) * 8); if (!rc) rc = c->x_err.ensure(16); if (!rc && cudaMemsetAsync(c->x_err.p, 0, 16, st) != cudaSuccess) rc = fail(BRB_E_CUDA, "memset failed"); }
   if (!rc && !cx_cig) rc = up(c->in_cigar_off, n ? in->cigar_off : zero_off, n ? (size_t)(n + 1) * 4 : 4);
-  if (!rc && cx_cig && n) {                                   // 16-bit counts -> CSR offsets (device scan)
-    rc = up(c->x_cnt16, in->cigar_cnt16, (size_t)n * 2);
-    if (!rc) rc = c->in_cigar_off.ensure((size_t)(n + 1) * 4);
-    if (!rc) {
-      k_expand_counts<<<grid_for(n, 256), 256, 0, st>>>(n, c->x_cnt16.as<uint16_t>(), c->x_cnt32.as<uint32_t>());
-      exclusive_scan(c->x_cnt32.as<uint32_t>(), c->in_cigar_off.as<uint32_t>(), n, reinterpret_cast<uint32_t*>(c->scan_tmp.p), st, &Lx);
-    }
-  }
   if (!rc) rc = up(c->in_cigar, in->cigar, (size_t)n_cigar * 4);
   if (!rc && !cx_exon) {
     rc = up(c->in_exon_off, n ? in->exon_off : zero_off, n ? (size_t)(n + 1) * 4 : 4);
@@ -398,31 +398,33 @@ static int batch_upload_async(brb_ctx* c, const brb_batch_in* in) {
     if (!rc) rc = up(c->in_exon_en, in->exon_en, (size_t)n_exon * 4);
   }
   if (!rc && cx_exon && !n) rc = up(c->in_exon_off, zero_off, 4);
-  if (!rc && (cx_exon || cx_cig) && n) {                      // read exons from pos0 + CIGAR: count, scan, fill; the totals come back in one small copy
-    uint32_t* err = c->x_err.as<uint32_t>();
-    if (cx_exon) {
+  c->expand_pending = false;
+  if (!rc && n && (cx_exon || cx_cig || cx_mate || cx_ref)) {  // the compact columns: uploaded as they are, expanded by ONE kernel (k_expand.cuh), no host round trip
+    ExpandJob J{}; J.n = n; J.n_cigar = n_cigar;
+    if (cx_ref) { rc = up(c->x_r16, in->refid16, (size_t)n * 2); if (!rc) rc = c->in_refid.ensure((size_t)n * 4); J.refid16 = c->x_r16.as<int16_t>(); J.refid = c->in_refid.as<int32_t>(); }
+    if (!rc && cx_mate) { rc = up(c->x_md16, in->mate_delta16, (size_t)n * 2); if (!rc) rc = c->in_mate.ensure((size_t)n * 4); J.mate_delta16 = c->x_md16.as<int16_t>(); J.mate_idx = c->in_mate.as<int32_t>(); }
+    if (!rc && cx_cig) { rc = up(c->x_cnt16, in->cigar_cnt16, (size_t)n * 2); if (!rc) rc = c->in_cigar_off.ensure((size_t)(n + 1) * 4); J.cnt16 = c->x_cnt16.as<uint16_t>(); }
+    J.cigar_off = c->in_cigar_off.as<uint32_t>(); J.cigar = c->in_cigar.as<uint32_t>();
+    if (!rc && cx_exon) {
+      // room for the exons: an alignment has at most one exon per CIGAR word, plus one (the host learns the true total with the results)
+      const uint64_t cap = (uint64_t)n_cigar + n;
+      if (cap >= 0xfffffff0ull) return fail(BRB_E_ARG, "batch too large");
       rc = up(c->x_pos, in->pos0, (size_t)n * 4);
       if (!rc) rc = c->in_exon_off.ensure((size_t)(n + 1) * 4);
-      if (!rc) {
-        k_exon_count<<<grid_for(n, 256), 256, 0, st>>>(n, c->x_pos.as<int32_t>(), c->in_cigar_off.as<uint32_t>(), c->in_cigar.as<uint32_t>(), n_cigar, c->x_cnt32.as<uint32_t>(), err);
-        exclusive_scan(c->x_cnt32.as<uint32_t>(), c->in_exon_off.as<uint32_t>(), n, reinterpret_cast<uint32_t*>(c->scan_tmp.p), st, &Lx);
-      }
+      if (!rc) rc = c->in_exon_st.ensure((size_t)cap * 4 + 16);
+      if (!rc) rc = c->in_exon_en.ensure((size_t)cap * 4 + 16);
+      J.pos0 = c->x_pos.as<int32_t>(); J.exon_off = c->in_exon_off.as<uint32_t>(); J.exon_st = c->in_exon_st.as<uint32_t>(); J.exon_en = c->in_exon_en.as<uint32_t>(); J.exon_cap = (uint32_t)cap;
+      n_exon = (uint32_t)cap;                                  // (until the true total is known)
     }
-    uint32_t h[3] = {0, 0, 0};                                // first invalid alignment + 1, exon total, CIGAR word total
+    const uint32_t tiles = (n + 255) / 256;
+    if (!rc) rc = c->x_cnt32.ensure((size_t)(2 * (size_t)tiles + 2) * 8);
+    if (!rc) rc = c->x_err.ensure(16);
     if (!rc) {
-      CU(cudaMemcpyAsync(&h[0], err, 4, cudaMemcpyDeviceToHost, st));
-      if (cx_exon) CU(cudaMemcpyAsync(&h[1], c->in_exon_off.as<uint32_t>() + n, 4, cudaMemcpyDeviceToHost, st));
-      CU(cudaMemcpyAsync(&h[2], c->in_cigar_off.as<uint32_t>() + n, 4, cudaMemcpyDeviceToHost, st));
-      CU(cudaStreamSynchronize(st));
-      CU(cudaGetLastError());
-      if (h[2] != n_cigar) return fail(BRB_E_ARG, "cigar_cnt16 sums to %u words, n_cigar_total says %u", h[2], n_cigar);
-      if (h[0]) return fail(BRB_E_ARG, "invalid CIGAR: alignment %u yields no read exon", h[0] - 1);
-    }
-    if (!rc && cx_exon) {
-      n_exon = h[1];
-      rc = c->in_exon_st.ensure((size_t)n_exon * 4 + 16); if (!rc) rc = c->in_exon_en.ensure((size_t)n_exon * 4 + 16);
-      if (!rc) k_exon_fill<<<grid_for(n, 256), 256, 0, st>>>(n, c->x_pos.as<int32_t>(), c->in_cigar_off.as<uint32_t>(), c->in_cigar.as<uint32_t>(), c->in_exon_off.as<uint32_t>(),
-                                                             c->in_exon_st.as<uint32_t>(), c->in_exon_en.as<uint32_t>());
+      CU(cudaMemsetAsync(c->x_cnt32.p, 0, (size_t)(2 * (size_t)tiles + 2) * 8, st));
+      CU(cudaMemsetAsync(c->x_err.p, 0, 16, st));
+      J.look = c->x_cnt32.as<unsigned long long>(); J.res = c->x_err.as<uint32_t>();
+      k_expand_all<<<std::min<uint32_t>(tiles, (uint32_t)c->n_sm * 8), 256, 0, st>>>(J);
+      c->expand_pending = true; c->expand_exons = cx_exon; c->expand_cigar = cx_cig; c->expand_n_cigar = n_cigar;
     }
   }
   c->seq_bytes = 0;
@@ -469,7 +471,8 @@ int brb_batch_upload(brb_ctx* c, const brb_batch_in* in) {
   const int rc = batch_upload_async(c, in);
   if (rc) return rc;
   CU(cudaStreamSynchronize(c->st));
-  return BRB_OK;
+  CU(cudaGetLastError());
+  return finish_expand(c);
 }
 
 }  // extern "C"
@@ -656,6 +659,7 @@ int project_resident(brb_ctx* c, const brb_params& p) {
     n_syncs++;
     CU(cudaGetLastError());
     c->ctl_clean = true;
+    { const int r = finish_expand(c); if (r) return r; }    // a batch that came with compact columns: its exon total, or its refusal
     if (hres->bad_input) break;
     bool again = false;
     if (hres->n_cand > c->cap_cand) { c->cap_cand = grown((uint64_t)hres->n_cand + std::min<uint64_t>((n + 31) / 32, (uint64_t)c->n_sm * 8 * 8) * POOL_CHUNK); c->cap_ideal = std::max(c->cap_ideal, grown((uint64_t)4 * c->cap_cand)); again = true; }
@@ -792,9 +796,16 @@ int brb_batch_download(brb_ctx* c, brb_batch_out* out) {
 }
 
 int brb_project(brb_ctx* c, const brb_params* p, const brb_batch_in* in, brb_batch_out* out) {
+  static const bool timing = getenv("BRB_PROJECT_TIMING") != nullptr;       // host milliseconds of the three stages on stderr, per call
+  auto now_ms = [] { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e3 + ts.tv_nsec / 1e6; };
+  const double t0 = timing ? now_ms() : 0;
   int rc = batch_upload_async(c, in); if (rc) return rc;        // (the copies are ordered before the kernels on the ctx stream; the call returns after the download)
+  const double t1 = timing ? now_ms() : 0;
   rc = brb_project_resident(c, p); if (rc) return rc;
-  return brb_batch_download(c, out);
+  const double t2 = timing ? now_ms() : 0;
+  rc = brb_batch_download(c, out);
+  if (timing) fprintf(stderr, "[project %p] start %.3f upload %.3f project %.3f (kernels %.3f) download %.3f ms\n", (void*)c, t0, t1 - t0, t2 - t1, c->stats.kernel_ms, now_ms() - t2);
+  return rc;
 }
 
 int brb_ctx_set_option(brb_ctx* c, int option, int value) {
