@@ -105,3 +105,31 @@ def test_hostbind_even_slices_without_numa_information():
         assert not info["bound"] and os.sched_getaffinity(0) == before
     finally:
         os.sched_setaffinity(0, before)
+
+
+def test_compact_columns_say_the_same_bundle():
+    """Batch.compact(): the 16-bit counts / links and the position are the plain columns in fewer bytes -- the offsets are the running sums
+    of the counts, the links resolve to the same mates, and the read exons follow from position + CIGAR by the ingest rule (pack.read_exons,
+    which the engine restates on the device) -- for reference-shaped bundles (pack_batches) and for the bench generator's (synth_fast)."""
+    from bramble_b200 import pack, synth_fast as sf
+    import common
+    batches = []
+    for mode in ("default", "lr"):
+        batches += common.make_workload(mode, 151, n_names=600, n_genes=30)["batches"]
+    A = sf.make_annotation(77, n_chrom=2, n_genes=120)
+    batches.append(sf.make_short_batch(A, sf.build_index(A), 78, 3000, stranded="fr"))
+    for b in batches:
+        n = int(b.desc.n_aln)
+        c = b.compact()
+        X, Y = b.arrays, c.arrays
+        assert c.desc.n_aln == n and int(c.desc.n_cigar_total) == int(X["cigar_off"][n])
+        assert not c.desc.exon_off and not c.desc.cigar_off and not c.desc.mate_idx and not c.desc.refid          # the replaced columns are NULL
+        assert np.array_equal(np.concatenate([[0], np.cumsum(Y["cigar_cnt16"][:n].astype(np.int64))]), X["cigar_off"][:n + 1].astype(np.int64))
+        mate = np.where(Y["mate_delta16"][:n] != 0, np.arange(n) + Y["mate_delta16"][:n].astype(np.int64), -1)
+        assert np.array_equal(mate, X["mate_idx"][:n].astype(np.int64)) and np.array_equal(Y["refid16"][:n].astype(np.int64), X["refid"][:n].astype(np.int64))
+        co, eo = X["cigar_off"].astype(np.int64), X["exon_off"].astype(np.int64)
+        for a in range(0, n, max(1, n // 400)):
+            ex = pack.read_exons(int(Y["pos0"][a]), [int(w) for w in X["cigar"][co[a]:co[a + 1]]])
+            assert [s for s, _ in ex] == list(X["exon_st"][eo[a]:eo[a + 1]]) and [e for _, e in ex] == list(X["exon_en"][eo[a]:eo[a + 1]]), a
+        # (a long-read bundle is CIGAR words: little to gain there; short reads lose a third to a half of their bytes)
+        assert sum(v.nbytes for k, v in Y.items() if hasattr(c.desc, k)) < sum(v.nbytes for k, v in X.items() if hasattr(b.desc, k))
