@@ -46,6 +46,7 @@ class BgzfReader {
     if (feeder_.joinable()) feeder_.join();
     for (auto& t : pool_) t.join();
     for (Job* j : order_) delete j;
+    for (Job* j : free_) delete j;
     if (f_) fclose(f_);
   }
   // reads exactly n bytes unless EOF; returns bytes read
@@ -112,7 +113,7 @@ class BgzfReader {
   void feed() {
     try {
       for (;;) {
-        Job* j = new Job();
+        Job* j = take_job();
         if (!read_block(j->comp, j->clen, j->isize)) { delete j; break; }
         std::unique_lock<std::mutex> lk(m_);
         cv_room_.wait(lk, [this] { return stop_ || order_.size() < max_jobs_; });
@@ -146,6 +147,12 @@ class BgzfReader {
     if (fread(dst.data() + at + 12 + xlen, 1, rest, f_) != rest) { dst.resize(at); return false; }
     return true;
   }
+  // Block jobs are recycled: a fresh pair of 64 KiB vectors per block means page faults and allocator traffic on every pool thread.
+  Job* take_job() {
+    { std::unique_lock<std::mutex> lk(m_); if (!free_.empty()) { Job* j = free_.back(); free_.pop_back(); j->ready = false; j->err.clear(); return j; } }
+    return new Job();
+  }
+  void give_job(Job* j) { std::unique_lock<std::mutex> lk(m_); if (free_.size() < max_jobs_ + 8) free_.push_back(j); else { lk.unlock(); delete j; } }
   void feed_pieces() {
     try {
       size_t want = 1 << 20; bool more = true;
@@ -205,13 +212,14 @@ class BgzfReader {
         j = order_.front(); order_.pop_front(); }
       cv_room_.notify_one();
       if (!j->err.empty()) { const std::string e = j->err; delete j; throw std::runtime_error(e); }
-      buf_.swap(j->out); pos_ = 0; delete j;
+      buf_.swap(j->out); pos_ = 0;
+      if (j->piece) delete j; else give_job(j);             // (block jobs go round: their two 64 KiB buffers keep their pages)
       if (!buf_.empty()) return true;
     }
   }
   FILE* f_ = nullptr; std::vector<uint8_t> buf_, comp_, extra_; size_t pos_ = 0;
   std::vector<std::thread> pool_; std::thread feeder_; std::mutex m_; std::condition_variable cv_, cv_room_, cv_ready_;
-  std::deque<Job*> order_, todo_; size_t max_jobs_ = 0; bool stop_ = false, eof_ = false; std::string feed_err_;
+  std::deque<Job*> order_, todo_; std::vector<Job*> free_; size_t max_jobs_ = 0; bool stop_ = false, eof_ = false; std::string feed_err_;
   PieceInflater ext_;
 };
 

@@ -9,7 +9,7 @@ W = workloads.build('c2', 1000, 300000)
 rb = bench.RefBench(W, {"small": 2000, "cli": 300000})
 import __graft_entry__ as g
 cli = g.build_cli()
-for env in ({}, {"BRB_DEVICE_INFLATE": "1"}):
+for env in ({}, {"BRB_INFLATE_THREADS": "12"}, {"BRB_DEVICE_INFLATE": "1"}):
     for rep in range(2):
         wd = tempfile.mkdtemp(dir=rb.d)
         e = dict(os.environ, BRB_CLI_TIMING="1", **env)
