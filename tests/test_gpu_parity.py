@@ -705,3 +705,20 @@ def test_compact_input_columns_give_the_same_rows(mode):
             eng.set_option(capi.OPT_PACKED_ROWS, 3 if not wl["mode"]["long"] else 1)
             oracle_lib.assert_rows_equal(exp, eng.project(p, b.compact()), f"{mode} compact in, packed out")
             eng.set_option(capi.OPT_PACKED_ROWS, 0)
+
+
+def test_compact_input_edge_cases():
+    """Empty bundle and single-alignment bundles through the compact columns; a compact upload followed by a plain one on the same context."""
+    from bramble_b200 import pack
+    wl = common.make_workload("default", 145, n_names=300, n_genes=20)
+    ix, p, b = wl["index"], wl["params"], wl["batches"][0]
+    with engine.Engine(ix) as eng:
+        empty = b.slice_groups(0, 0)
+        assert eng.project(p, empty.compact())["n_rec"] == 0
+        exp = oracle_lib.port_project(ix, p, b)
+        for g in range(0, int(b.desc.n_groups), max(1, int(b.desc.n_groups) // 12)):
+            one = b.slice_groups(g, g + 1)
+            oracle_lib.assert_rows_equal(oracle_lib.port_project(ix, p, one), eng.project(p, one.compact()), f"group {g}")
+        oracle_lib.assert_rows_equal(exp, eng.project(p, b.compact()), "compact")
+        oracle_lib.assert_rows_equal(exp, eng.project(p, b), "plain after compact")
+        oracle_lib.assert_rows_equal(exp, eng.project(p, b.compact(exons=False)), "compact again")
