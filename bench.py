@@ -389,8 +389,11 @@ def cli_e2e(rb, cores, gpus_list, repeats=2):
     out = {}
     for n in gpus_list:
         leg = rb.leg("cli", ["-p", str(max(1, min(cores, 255))), "--level", "1"], env={"BRB_GPUS": str(n)}, binary=binary, repeats=repeats)
-        if not leg:
-            continue
+        if not leg:                         # the difference of two wall times did not resolve (start-up of N engines is most of both): the pipeline clock still stands
+            _, pipe = rb.run("cli", ["-p", str(max(1, min(cores, 255))), "--level", "1"], {"BRB_GPUS": str(n)}, binary, "a.gtf", repeats)
+            if not pipe:
+                continue
+            leg = {"value": None, "pipeline_s": pipe, "n_aln_big": rb.n["cli"][1]}
         r = {"unit": UNIT, "gpus": n, "host_threads": max(1, min(cores, 255)), "sample": rb.sample_text("cli"), "marginal_value": leg["value"]}
         if leg.get("pipeline_s"):
             r.update(value=leg["n_aln_big"] / leg["pipeline_s"], pipeline_s=leg["pipeline_s"])
